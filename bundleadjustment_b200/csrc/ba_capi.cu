@@ -1,0 +1,919 @@
+// ba_capi.cu -- C ABI (include/ba_b200.h) + host orchestration of the device-resident LM loop.
+//
+// The host only ENQUEUES work: every accept/reject/termination decision is taken by the controller kernels
+// (ba_kernels.cu) from device-resident state; kernels of iterations enqueued after termination early-exit.  The
+// host looks at a mapped `done` word two iterations behind the GPU merely to stop enqueueing.
+#include "ba_launch.h"
+
+#include <nccl.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <string>
+#include <vector>
+
+using namespace ba;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(expr)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (expr);                                                                    \
+        if (e__ != cudaSuccess) return fail(BA_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e__));  \
+    } while (0)
+#define NC(expr)                                                                                     \
+    do {                                                                                             \
+        ncclResult_t r__ = (expr);                                                                   \
+        if (r__ != ncclSuccess) return fail(BA_ERR_NCCL, "%s: %s", #expr, ncclGetErrorString(r__));  \
+    } while (0)
+
+const char *message_text(int msg) {
+    switch (msg) {
+        case MSG_MAX_ITER: return "Maximum number of iterations reached.";
+        case MSG_GRADIENT_TOL: return "Gradient tolerance reached.";
+        case MSG_MIN_RADIUS: return "Minimum trust region radius reached.";
+        case MSG_PARAM_TOL: return "Parameter tolerance reached.";
+        case MSG_FUNCTION_TOL: return "Function tolerance reached.";
+        case MSG_INVALID_STEPS: return "Number of consecutive invalid steps more than Solver::Options::max_num_consecutive_invalid_steps.";
+        case MSG_EVAL_FAILED: return "Residual and Jacobian evaluation failed.";
+        default: return "";
+    }
+}
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    cudaError_t alloc(size_t b) {
+        free();
+        bytes = b;
+        if (b == 0) return cudaSuccess;
+        return cudaMalloc(&p, b);
+    }
+    void free() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+} // namespace
+
+struct ba_handle {
+    int device = 0;
+    ba_options opt;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    cudaEvent_t ev_ring[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool has_problem = false;
+    Ctx ctx;
+    // caller order -> landmark-major position
+    std::vector<int> perm;           // pm position of caller observation i
+    // device buffers
+    DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
+    DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
+    DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
+    DevBuf part, cost_part, sums, maxs, camsums, state, iters, invL, U_loc, bc_loc, sums_loc, maxs_loc;
+    DevBuf cg_r, cg_p, cg_z, cg_q, cg_x, Minv, tp;
+    DevBuf ev_res, ev_jc, ev_jp;     // materialised evaluation outputs
+    int *host_flags = nullptr;       // mapped pinned
+    int *host_flags_dev = nullptr;
+    // NCCL
+    ncclComm_t comm = nullptr;
+    int n_ranks = 1, rank = 0;
+    std::vector<int> cam_obs_count;  // global per-camera observation counts
+    int launches = 0;                // kernels/collectives enqueued by the last solve (bench bookkeeping)
+
+    void free_problem() {
+        DevBuf *all[] = {&cam0, &cam1, &pt0, &pt1, &cam_init, &pt_init, &cam_kind, &cam_K, &cam_extr, &pm_uv, &pm_cam, &pm_pt,
+                         &pt_ptr, &cm_uv, &cm_pt, &chunk_cam, &chunk_beg, &chunk_end, &cam_chunk_ptr, &tab_x, &tab_c, &scale_cam,
+                         &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &sums, &maxs,
+                         &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &ev_res, &ev_jc, &ev_jp};
+        for (DevBuf *b : all) b->free();
+        has_problem = false;
+    }
+};
+
+extern "C" {
+
+int ba_version(void) { return BA_B200_VERSION; }
+const char *ba_last_error(void) { return g_err.c_str(); }
+
+void ba_default_options(ba_options *o) {
+    std::memset(o, 0, sizeof(*o));
+    o->max_num_iterations = 200;          // BAOptimizer(): m_nMaxItPerBA(200), Optimizer.h:203
+    o->num_threads = 4;                   // Optimizer.cpp:88 (unused on the GPU)
+    o->linear_solver = BA_DENSE_SCHUR;    // Optimizer.cpp:85
+    o->jacobi_scaling = 1;
+    o->max_num_consecutive_invalid_steps = 5;
+    o->max_linear_solver_iterations = 500;
+    o->use_huber = 1;
+    o->function_tolerance = 1e-6;
+    o->gradient_tolerance = 1e-10;
+    o->parameter_tolerance = 1e-8;
+    o->initial_trust_region_radius = 1e4;
+    o->max_trust_region_radius = 1e16;
+    o->min_trust_region_radius = 1e-32;
+    o->min_relative_decrease = 1e-3;
+    o->min_lm_diagonal = 1e-6;
+    o->max_lm_diagonal = 1e32;
+    o->huber_delta = std::sqrt(5.991);    // Optimizer.cpp:312
+    o->eta = 1e-1;
+    o->cg_r_tolerance = -1.0;
+}
+
+static int check_device(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(BA_ERR_CUDA, "no CUDA device available (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= n) return fail(BA_ERR_INVALID, "device %d out of range (0..%d)", device, n - 1);
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(BA_ERR_CUDA, "device %d is sm_%d%d; this build targets sm_100a only", device, prop.major, prop.minor);
+    CU(cudaSetDevice(device));
+    return BA_OK;
+}
+
+int ba_create(const ba_options *opt, int device, ba_handle **out) {
+    if (!out) return fail(BA_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    int rc = check_device(device);
+    if (rc) return rc;
+    ba_handle *h = new ba_handle();
+    h->device = device;
+    if (opt) h->opt = *opt; else ba_default_options(&h->opt);
+    std::memset(&h->ctx, 0, sizeof(h->ctx));
+    CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&h->ev_start));
+    CU(cudaEventCreate(&h->ev_stop));
+    for (auto &e : h->ev_ring) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(cudaHostAlloc((void **)&h->host_flags, 64, cudaHostAllocMapped));
+    std::memset(h->host_flags, 0, 64);
+    CU(cudaHostGetDevicePointer((void **)&h->host_flags_dev, h->host_flags, 0));
+    int e = chol_init();
+    if (e) { g_err = std::string("chol_init: ") + cudaGetErrorString((cudaError_t)e); return BA_ERR_CUDA; }
+    *out = h;
+    return BA_OK;
+}
+
+int ba_destroy(ba_handle *h) {
+    if (!h) return BA_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    h->free_problem();
+    if (h->comm) ncclCommDestroy(h->comm);
+    if (h->host_flags) cudaFreeHost(h->host_flags);
+    for (auto &e : h->ev_ring) if (e) cudaEventDestroy(e);
+    if (h->ev_start) cudaEventDestroy(h->ev_start);
+    if (h->ev_stop) cudaEventDestroy(h->ev_stop);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return BA_OK;
+}
+
+int ba_set_options(ba_handle *h, const ba_options *opt) {
+    if (!h || !opt) return fail(BA_ERR_INVALID, "NULL argument");
+    h->opt = *opt;
+    h->ctx.opt = *opt;
+    if (h->has_problem) {
+        // iteration log capacity follows max_num_iterations
+        cudaSetDevice(h->device);
+        CU(h->iters.alloc(sizeof(ba_iteration) * (size_t)(opt->max_num_iterations + 2)));
+        h->ctx.iters = h->iters.as<ba_iteration>();
+    }
+    return BA_OK;
+}
+
+} // extern "C"
+
+// =============================================================================================================
+// problem upload
+// =============================================================================================================
+namespace {
+
+template <typename T>
+int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
+    CU(b.alloc(sizeof(T) * std::max<size_t>(count, 1)));
+    if (count) CU(cudaMemcpyAsync(b.p, src, sizeof(T) * count, cudaMemcpyHostToDevice, s));
+    return BA_OK;
+}
+
+int ensure_dense(ba_handle *h) {
+    const size_t n = (size_t)h->ctx.n;
+    const size_t need = sizeof(double) * (n + 1) * n;
+    if (h->S.bytes < need) {
+        CU(h->S.alloc(need));
+        CU(h->invL.alloc(sizeof(double) * std::max<size_t>(chol_work_doubles((int)n), 1)));
+    }
+    h->ctx.S = h->S.as<double>();
+    return BA_OK;
+}
+
+} // namespace
+
+extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, const uint8_t *cam_fixed,
+                              const float *fixed_extr, const float *K, int32_t n_pt, const double *pt, int32_t n_obs,
+                              const int32_t *obs_cam, const int32_t *obs_pt, const float *obs_uv) {
+    if (!h) return fail(BA_ERR_INVALID, "handle is NULL");
+    if (n_cam <= 0 || n_pt < 0 || n_obs < 0) return fail(BA_ERR_INVALID, "bad sizes n_cam=%d n_pt=%d n_obs=%d", n_cam, n_pt, n_obs);
+    if (!cam || !cam_fixed || !K || (n_pt && !pt) || (n_obs && (!obs_cam || !obs_pt || !obs_uv)))
+        return fail(BA_ERR_INVALID, "NULL array");
+    CU(cudaSetDevice(h->device));
+    const int Nc = n_cam, Np = n_pt, No = n_obs;
+    std::vector<int> pcount(Np, 0), ccount(Nc, 0);
+    for (int i = 0; i < No; ++i) {
+        const int c = obs_cam[i], p = obs_pt[i];
+        if (c < 0 || c >= Nc || p < 0 || p >= Np) return fail(BA_ERR_INVALID, "observation %d references camera %d / landmark %d out of range", i, c, p);
+        if (cam_fixed[c] && !fixed_extr) return fail(BA_ERR_INVALID, "fixed camera %d but fixed_extr is NULL", c);
+        pcount[p]++; ccount[c]++;
+    }
+    h->free_problem();
+    cudaStream_t s = h->stream;
+    Ctx &ctx = h->ctx;
+    std::memset(&ctx, 0, sizeof(ctx));
+    ctx.Nc = Nc; ctx.Np = Np; ctx.No = No; ctx.n = 6 * Nc;
+    ctx.rank = h->rank; ctx.n_ranks = h->n_ranks;
+    ctx.opt = h->opt;
+
+    // ---- landmark-major order: counting sort by landmark, then by camera inside the (short) track ----
+    std::vector<int> pt_ptr(Np + 1, 0);
+    for (int p = 0; p < Np; ++p) pt_ptr[p + 1] = pt_ptr[p] + pcount[p];
+    std::vector<int> order(No);          // pm position -> caller index
+    {
+        std::vector<int> fill(pt_ptr.begin(), pt_ptr.end() - 1);
+        for (int i = 0; i < No; ++i) order[fill[obs_pt[i]]++] = i;
+        for (int p = 0; p < Np; ++p)
+            std::stable_sort(order.begin() + pt_ptr[p], order.begin() + pt_ptr[p + 1],
+                             [&](int a, int b) { return obs_cam[a] < obs_cam[b]; });
+    }
+    h->perm.assign(No, 0);
+    std::vector<float2> pm_uv(No);
+    std::vector<int> pm_cam(No), pm_pt(No);
+    for (int e = 0; e < No; ++e) {
+        const int i = order[e];
+        h->perm[i] = e;
+        pm_uv[e] = make_float2(obs_uv[2 * (size_t)i], obs_uv[2 * (size_t)i + 1]);
+        pm_cam[e] = obs_cam[i];
+        pm_pt[e] = obs_pt[i];
+    }
+    // ---- global per-camera observation counts decide which cameras are part of the problem ----
+    h->cam_obs_count = ccount;
+    if (h->comm) {
+        DevBuf tmp;
+        CU(tmp.alloc(sizeof(int) * Nc));
+        CU(cudaMemcpyAsync(tmp.p, ccount.data(), sizeof(int) * Nc, cudaMemcpyHostToDevice, s));
+        NC(ncclAllReduce(tmp.p, tmp.p, Nc, ncclInt, ncclSum, h->comm, s));
+        CU(cudaMemcpyAsync(h->cam_obs_count.data(), tmp.p, sizeof(int) * Nc, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        tmp.free();
+    }
+    std::vector<int> kind(Nc);
+    for (int c = 0; c < Nc; ++c) kind[c] = cam_fixed[c] ? CAM_FIXED : (h->cam_obs_count[c] > 0 ? CAM_FREE : CAM_INACTIVE);
+    // ---- camera-major copy (free cameras only) + reduction chunks ----
+    std::vector<int> cam_ptr(Nc + 1, 0);
+    for (int c = 0; c < Nc; ++c) cam_ptr[c + 1] = cam_ptr[c] + ((kind[c] == CAM_FREE) ? ccount[c] : 0);
+    const int Ncm = cam_ptr[Nc];
+    std::vector<float2> cm_uv(std::max(Ncm, 1));
+    std::vector<int> cm_pt(std::max(Ncm, 1));
+    {
+        std::vector<int> fill(cam_ptr.begin(), cam_ptr.end() - 1);
+        for (int e = 0; e < No; ++e) {
+            const int c = pm_cam[e];
+            if (kind[c] != CAM_FREE) continue;
+            const int d = fill[c]++;
+            cm_uv[d] = pm_uv[e];
+            cm_pt[d] = pm_pt[e];
+        }
+    }
+    std::vector<int> chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr(Nc + 1, 0);
+    for (int c = 0; c < Nc; ++c) {
+        for (int b = cam_ptr[c]; b < cam_ptr[c + 1]; b += CHUNK) {
+            chunk_cam.push_back(c);
+            chunk_beg.push_back(b);
+            chunk_end.push_back(std::min(b + CHUNK, cam_ptr[c + 1]));
+        }
+        cam_chunk_ptr[c + 1] = (int)chunk_cam.size();
+    }
+    ctx.n_chunks = (int)chunk_cam.size();
+    ctx.n_part = std::max((Np + 127) / 128, 1);
+
+    // ---- upload ----
+    int rc;
+#define UP(buf, ptr, cnt) if ((rc = upload(h->buf, ptr, (size_t)(cnt), s))) return rc
+    UP(cam0, cam, 6 * (size_t)Nc); UP(cam1, cam, 6 * (size_t)Nc); UP(cam_init, cam, 6 * (size_t)Nc);
+    UP(pt0, pt, 3 * (size_t)Np); UP(pt1, pt, 3 * (size_t)Np); UP(pt_init, pt, 3 * (size_t)Np);
+    UP(cam_kind, kind.data(), Nc);
+    UP(cam_K, K, 9 * (size_t)Nc);
+    if (fixed_extr) { UP(cam_extr, fixed_extr, 16 * (size_t)Nc); }
+    else { std::vector<float> z(16 * (size_t)Nc, 0.f); UP(cam_extr, z.data(), z.size()); CU(cudaStreamSynchronize(s)); }
+    UP(pm_uv, pm_uv.data(), No); UP(pm_cam, pm_cam.data(), No); UP(pm_pt, pm_pt.data(), No);
+    UP(pt_ptr, pt_ptr.data(), Np + 1);
+    UP(cm_uv, cm_uv.data(), Ncm); UP(cm_pt, cm_pt.data(), Ncm);
+    UP(chunk_cam, chunk_cam.data(), chunk_cam.size()); UP(chunk_beg, chunk_beg.data(), chunk_beg.size());
+    UP(chunk_end, chunk_end.data(), chunk_end.size()); UP(cam_chunk_ptr, cam_chunk_ptr.data(), Nc + 1);
+#undef UP
+#define AL(buf, bytes) CU(h->buf.alloc(std::max<size_t>((size_t)(bytes), 8)))
+    AL(tab_x, sizeof(CamEntry) * (size_t)Nc); AL(tab_c, sizeof(CamEntry) * (size_t)Nc);
+    AL(scale_cam, 8 * 6 * (size_t)Nc); AL(scale_pt, 8 * 3 * (size_t)Np);
+    AL(U, 8 * 36 * (size_t)Nc); AL(bc, 8 * 6 * (size_t)Nc); AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
+    AL(W, 8 * 18 * (size_t)No); AL(cam_part, 8 * 27 * (size_t)ctx.n_chunks);
+    AL(Vinv, 8 * 6 * (size_t)Np); AL(wv, 8 * 3 * (size_t)Np);
+    AL(rhs, 8 * (size_t)ctx.n); AL(yc, 8 * (size_t)ctx.n);
+    AL(part, 8 * 4 * (size_t)ctx.n_part); AL(cost_part, 8 * (size_t)((No + 127) / 128 + 1));
+    AL(sums, 8 * SUM_COUNT); AL(maxs, 8 * MAX_COUNT); AL(camsums, 8 * CS_COUNT);
+    AL(state, sizeof(LMState)); AL(iters, sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2));
+    AL(cg_r, 8 * (size_t)ctx.n); AL(cg_p, 8 * (size_t)ctx.n); AL(cg_z, 8 * (size_t)ctx.n); AL(cg_q, 8 * (size_t)ctx.n);
+    AL(cg_x, 8 * (size_t)ctx.n); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np);
+#undef AL
+    ctx.cam[0] = h->cam0.as<double>(); ctx.cam[1] = h->cam1.as<double>();
+    ctx.pt[0] = h->pt0.as<double>(); ctx.pt[1] = h->pt1.as<double>();
+    ctx.cam_init = h->cam_init.as<double>(); ctx.pt_init = h->pt_init.as<double>();
+    ctx.cam_kind = h->cam_kind.as<int>(); ctx.cam_K = h->cam_K.as<float>(); ctx.cam_extr = h->cam_extr.as<float>();
+    ctx.pm_uv = h->pm_uv.as<float2>(); ctx.pm_cam = h->pm_cam.as<int>(); ctx.pm_pt = h->pm_pt.as<int>();
+    ctx.pt_ptr = h->pt_ptr.as<int>(); ctx.cm_uv = h->cm_uv.as<float2>(); ctx.cm_pt = h->cm_pt.as<int>();
+    ctx.chunk_cam = h->chunk_cam.as<int>(); ctx.chunk_beg = h->chunk_beg.as<int>(); ctx.chunk_end = h->chunk_end.as<int>();
+    ctx.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
+    ctx.tab_x = h->tab_x.as<CamEntry>(); ctx.tab_c = h->tab_c.as<CamEntry>();
+    ctx.scale_cam = h->scale_cam.as<double>(); ctx.scale_pt = h->scale_pt.as<double>();
+    ctx.U = h->U.as<double>(); ctx.bc = h->bc.as<double>(); ctx.V = h->V.as<double>(); ctx.bp = h->bp.as<double>();
+    ctx.W = h->W.as<double>(); ctx.cam_part = h->cam_part.as<double>(); ctx.Vinv = h->Vinv.as<double>(); ctx.wv = h->wv.as<double>();
+    ctx.rhs = h->rhs.as<double>(); ctx.yc = h->yc.as<double>();
+    ctx.part = h->part.as<double>(); ctx.sums = h->sums.as<double>(); ctx.maxs = h->maxs.as<double>(); ctx.camsums = h->camsums.as<double>();
+    ctx.cg_r = h->cg_r.as<double>(); ctx.cg_p = h->cg_p.as<double>(); ctx.cg_z = h->cg_z.as<double>(); ctx.cg_q = h->cg_q.as<double>();
+    ctx.cg_x = h->cg_x.as<double>(); ctx.Minv = h->Minv.as<double>(); ctx.tp = h->tp.as<double>();
+    ctx.state = h->state.as<LMState>(); ctx.iters = h->iters.as<ba_iteration>();
+    ctx.host_flags = h->host_flags_dev;
+    if (h->comm) {
+        CU(h->U_loc.alloc(8 * 36 * (size_t)Nc)); CU(h->bc_loc.alloc(8 * 6 * (size_t)Nc));
+        CU(h->sums_loc.alloc(8 * SUM_COUNT)); CU(h->maxs_loc.alloc(8 * MAX_COUNT));
+        CU(cudaMemsetAsync(h->sums_loc.p, 0, 8 * SUM_COUNT, s)); CU(cudaMemsetAsync(h->maxs_loc.p, 0, 8 * MAX_COUNT, s));
+        ctx.U_loc = h->U_loc.as<double>(); ctx.bc_loc = h->bc_loc.as<double>();
+        ctx.sums_loc = h->sums_loc.as<double>(); ctx.maxs_loc = h->maxs_loc.as<double>();
+    } else {
+        ctx.U_loc = ctx.U; ctx.bc_loc = ctx.bc; ctx.sums_loc = ctx.sums; ctx.maxs_loc = ctx.maxs;
+    }
+    CU(cudaMemsetAsync(h->sums.p, 0, 8 * SUM_COUNT, s));
+    CU(cudaMemsetAsync(h->maxs.p, 0, 8 * MAX_COUNT, s));
+    CU(cudaMemsetAsync(h->camsums.p, 0, 8 * CS_COUNT, s));
+    launch_init_state(ctx, s);
+    launch_fill(ctx.scale_cam, 6 * (size_t)Nc, 1.0, s);
+    launch_fill(ctx.scale_pt, 3 * (size_t)Np, 1.0, s);
+    launch_cam_prep(ctx, 0, 1, s);      // K / fixed extrinsics of both tables are written once here
+    launch_cam_prep(ctx, 1, 1, s);
+    CU(cudaStreamSynchronize(s));       // host staging vectors die at scope exit
+    CU(cudaGetLastError());
+    h->has_problem = true;
+    return BA_OK;
+}
+
+extern "C" int ba_set_parameters(ba_handle *h, const double *cam, const double *pt) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "no problem set");
+    CU(cudaSetDevice(h->device));
+    const Ctx &ctx = h->ctx;
+    if (cam) {
+        CU(cudaMemcpyAsync(ctx.cam_init, cam, 8 * 6 * (size_t)ctx.Nc, cudaMemcpyHostToDevice, h->stream));
+    }
+    if (pt && ctx.Np) CU(cudaMemcpyAsync(ctx.pt_init, pt, 8 * 3 * (size_t)ctx.Np, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return ba_reset_parameters(h);
+}
+
+extern "C" int ba_reset_parameters(ba_handle *h) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "no problem set");
+    CU(cudaSetDevice(h->device));
+    const Ctx &ctx = h->ctx;
+    cudaStream_t s = h->stream;
+    for (int b = 0; b < 2; ++b) {
+        CU(cudaMemcpyAsync(ctx.cam[b], ctx.cam_init, 8 * 6 * (size_t)ctx.Nc, cudaMemcpyDeviceToDevice, s));
+        if (ctx.Np) CU(cudaMemcpyAsync(ctx.pt[b], ctx.pt_init, 8 * 3 * (size_t)ctx.Np, cudaMemcpyDeviceToDevice, s));
+    }
+    launch_init_state(ctx, s);
+    return BA_OK;
+}
+
+// =============================================================================================================
+// the LM loop (ceres::Solve replacement)
+// =============================================================================================================
+namespace {
+
+// all-reduce helpers (no-ops on a single GPU, where the *_loc buffers alias their reduced counterparts)
+int allreduce_sum(ba_handle *h, const double *src, double *dst, size_t count) {
+    if (!h->comm) return BA_OK;
+    NC(ncclAllReduce(src, dst, count, ncclDouble, ncclSum, h->comm, h->stream));
+    h->launches++;
+    return BA_OK;
+}
+int allreduce_sum(ba_handle *h, double *buf, size_t count) { return allreduce_sum(h, buf, buf, count); }
+int allreduce_max(ba_handle *h, const double *src, double *dst, size_t count) {
+    if (!h->comm) return BA_OK;
+    NC(ncclAllReduce(src, dst, count, ncclDouble, ncclMax, h->comm, h->stream));
+    h->launches++;
+    return BA_OK;
+}
+
+// one linearisation at x: local blocks, then the replicated camera blocks are summed over ranks
+int enqueue_linearize(ba_handle *h, int force) {
+    const Ctx &ctx = h->ctx;
+    launch_linearize_local(ctx, force, h->stream);
+    h->launches += 5;
+    int rc;
+    // out-of-place so that a body that does not re-linearise reproduces the same reduced blocks
+    if ((rc = allreduce_sum(h, ctx.U_loc, ctx.U, 36 * (size_t)ctx.Nc))) return rc;
+    if ((rc = allreduce_sum(h, ctx.bc_loc, ctx.bc, 6 * (size_t)ctx.Nc))) return rc;
+    if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_LIN_BEGIN, ctx.sums + SUM_LIN_BEGIN, SUM_LIN_N))) return rc;
+    if ((rc = allreduce_max(h, ctx.maxs_loc, ctx.maxs, MAX_COUNT))) return rc;
+    launch_cam_norms(ctx, force, h->stream);
+    h->launches += 1;
+    return BA_OK;
+}
+
+// reduced system + solve for the current radius: y_c into ctx.yc
+int enqueue_linear_solve(ba_handle *h) {
+    const Ctx &ctx = h->ctx;
+    cudaStream_t s = h->stream;
+    int rc;
+    launch_point_invert(ctx, -1.0, s);
+    h->launches += 1;
+    if (h->opt.linear_solver == BA_DENSE_SCHUR) {
+        launch_schur_build(ctx, -1.0, s);
+        h->launches += 3;
+        // rhs row of the augmented matrix
+        if (h->comm) {
+            // lower triangle + rhs would do; the full buffer keeps the collective a single contiguous message
+            if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.n))) return rc;
+            if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
+        }
+        CU(cudaMemcpyAsync(ctx.S + (size_t)ctx.n * ctx.n, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToDevice, s));
+        chol_factor_solve(ctx.S, ctx.n, h->invL.as<double>(), ctx.yc, ctx.state, nullptr, s);
+        const int nblk = (ctx.n + CHOL_NB - 1) / CHOL_NB;
+        h->launches += 4 * nblk;
+    } else {
+        launch_pcg_setup(ctx, s);
+        h->launches += 2;
+        if ((rc = allreduce_sum(h, ctx.Minv, 36 * (size_t)ctx.Nc))) return rc;
+        if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
+        launch_pcg_start(ctx, s);
+        h->launches += 1;
+        const int max_it = std::max(1, h->opt.max_linear_solver_iterations);
+        const int R = 4;
+        for (int it = 1; it <= max_it; ++it) {
+            if (it > R) {
+                CU(cudaEventSynchronize(h->ev_ring[it % R]));
+                if (h->host_flags[1] || h->host_flags[0]) break;
+            }
+            launch_pcg_iter_a(ctx, s);
+            if ((rc = allreduce_sum(h, ctx.cg_q, (size_t)ctx.n))) return rc;
+            launch_pcg_iter_b(ctx, s);
+            h->launches += 3;
+            if (it % 10 == 0) {   // residual_reset_period
+                launch_pcg_reset_a(ctx, s);
+                if ((rc = allreduce_sum(h, ctx.cg_z, (size_t)ctx.n))) return rc;
+                launch_pcg_reset_b(ctx, s);
+                h->launches += 3;
+            }
+            launch_pcg_check(ctx, s);
+            h->launches += 1;
+            CU(cudaEventRecord(h->ev_ring[it % R], s));
+        }
+        launch_pcg_finish(ctx, s);
+        h->launches += 1;
+    }
+    return BA_OK;
+}
+
+} // namespace
+
+extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "ba_solve before ba_set_problem");
+    CU(cudaSetDevice(h->device));
+    Ctx &ctx = h->ctx;
+    ctx.opt = h->opt;
+    ctx.rank = h->rank; ctx.n_ranks = h->n_ranks;
+    cudaStream_t s = h->stream;
+    int rc;
+    if (h->iters.bytes < sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2)) {
+        CU(h->iters.alloc(sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2)));
+        ctx.iters = h->iters.as<ba_iteration>();
+    }
+    if (h->opt.linear_solver == BA_DENSE_SCHUR && (rc = ensure_dense(h))) return rc;
+    h->launches = 0;
+    h->host_flags[0] = 0; h->host_flags[1] = 0;
+    CU(cudaEventRecord(h->ev_start, s));
+    launch_init_state(ctx, s);
+    launch_fill(ctx.scale_cam, 6 * (size_t)ctx.Nc, 1.0, s);
+    launch_fill(ctx.scale_pt, 3 * (size_t)ctx.Np, 1.0, s);
+    h->launches += 3;
+    if (h->opt.jacobi_scaling) {
+        // iteration 0: column norms of the unscaled (robustified) Jacobian -> Jacobi scaling, fixed thereafter
+        if ((rc = enqueue_linearize(h, 1))) return rc;
+        launch_compute_scale(ctx, s);
+        h->launches += 1;
+    }
+    cudaEvent_t ev_it[2];
+    ev_it[0] = h->ev_ring[0]; ev_it[1] = h->ev_ring[1];
+    cudaEvent_t ev_lm[2];
+    CU(cudaEventCreateWithFlags(&ev_lm[0], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_lm[1], cudaEventDisableTiming));
+    // At most max_num_iterations + 1 bodies: body k records iteration k and computes step k + 1.
+    const int bodies = h->opt.max_num_iterations + 1;
+    int status = BA_OK;
+    for (int k = 0; k < bodies; ++k) {
+        if (k >= 2) {
+            cudaError_t e = cudaEventSynchronize(ev_lm[k & 1]);    // body k-2 finished: safe to look at its verdict
+            if (e != cudaSuccess) { status = fail(BA_ERR_CUDA, "LM loop: %s", cudaGetErrorString(e)); break; }
+            if (h->host_flags[0]) break;
+        }
+        if ((rc = enqueue_linearize(h, 0))) { status = rc; break; }
+        launch_begin_iteration(ctx, s);
+        if ((rc = enqueue_linear_solve(h))) { status = rc; break; }
+        launch_backsub(ctx, s);
+        launch_eval_candidate(ctx, h->cost_part.as<double>(), s);
+        if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_STEP_BEGIN, ctx.sums + SUM_STEP_BEGIN, SUM_STEP_N))) { status = rc; break; }
+        launch_decide(ctx, s);
+        h->launches += 6;
+        cudaEventRecord(ev_lm[k & 1], s);
+    }
+    cudaEventRecord(h->ev_stop, s);
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaEventDestroy(ev_lm[0]); cudaEventDestroy(ev_lm[1]);
+    if (status) return status;
+    if (e != cudaSuccess) return fail(BA_ERR_CUDA, "LM loop: %s", cudaGetErrorString(e));
+    CU(cudaGetLastError());
+    LMState st;
+    CU(cudaMemcpy(&st, ctx.state, sizeof(st), cudaMemcpyDeviceToHost));
+    if (!st.done) return fail(BA_ERR_STATE, "LM loop ended without a verdict (internal error)");
+    if (summary) {
+        std::memset(summary, 0, sizeof(*summary));
+        summary->termination_type = st.termination;
+        summary->num_iterations = st.n_recorded;
+        summary->num_successful_steps = st.num_successful;
+        summary->num_unsuccessful_steps = st.num_unsuccessful;
+        summary->initial_cost = st.initial_cost;
+        // SetSummaryFinalCost (ceres solver.cc): min over the recorded iteration costs
+        std::vector<ba_iteration> its(std::max(st.n_recorded, 1));
+        CU(cudaMemcpy(its.data(), ctx.iters, sizeof(ba_iteration) * (size_t)st.n_recorded, cudaMemcpyDeviceToHost));
+        double fc = st.initial_cost;
+        for (int i = 0; i < st.n_recorded; ++i) fc = std::min(fc, its[i].cost);
+        summary->final_cost = fc;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, h->ev_start, h->ev_stop);
+        summary->seconds_total = ms * 1e-3;
+        std::snprintf(summary->message, sizeof(summary->message), "%s", message_text(st.msg));
+    }
+    return BA_OK;
+}
+
+extern "C" int ba_get_launch_count(ba_handle *h) { return h ? h->launches : 0; }
+
+extern "C" int ba_get_cameras(ba_handle *h, double *cam) {
+    if (!h || !h->has_problem || !cam) return fail(BA_ERR_STATE, "no problem / NULL output");
+    CU(cudaSetDevice(h->device));
+    LMState st;
+    CU(cudaMemcpy(&st, h->ctx.state, sizeof(st), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(cam, h->ctx.cam[st.cur], 8 * 6 * (size_t)h->ctx.Nc, cudaMemcpyDeviceToHost));
+    return BA_OK;
+}
+
+extern "C" int ba_get_points(ba_handle *h, double *pt) {
+    if (!h || !h->has_problem || (!pt && h->ctx.Np)) return fail(BA_ERR_STATE, "no problem / NULL output");
+    CU(cudaSetDevice(h->device));
+    LMState st;
+    CU(cudaMemcpy(&st, h->ctx.state, sizeof(st), cudaMemcpyDeviceToHost));
+    if (h->ctx.Np) CU(cudaMemcpy(pt, h->ctx.pt[st.cur], 8 * 3 * (size_t)h->ctx.Np, cudaMemcpyDeviceToHost));
+    return BA_OK;
+}
+
+extern "C" int ba_get_iterations(ba_handle *h, ba_iteration *iters, int32_t cap, int32_t *n_written) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "no problem set");
+    CU(cudaSetDevice(h->device));
+    LMState st;
+    CU(cudaMemcpy(&st, h->ctx.state, sizeof(st), cudaMemcpyDeviceToHost));
+    const int n = std::min<int>(cap, st.n_recorded);
+    if (n > 0 && iters) CU(cudaMemcpy(iters, h->ctx.iters, sizeof(ba_iteration) * (size_t)n, cudaMemcpyDeviceToHost));
+    if (n_written) *n_written = n;
+    return BA_OK;
+}
+
+// =============================================================================================================
+// materialised evaluation, reduced system dump
+// =============================================================================================================
+namespace {
+int ensure_eval_buffers(ba_handle *h) {
+    const size_t No = (size_t)h->ctx.No;
+    if (h->ev_res.bytes < 16 * std::max<size_t>(No, 1)) {
+        CU(h->ev_res.alloc(16 * std::max<size_t>(No, 1)));
+        CU(h->ev_jc.alloc(96 * std::max<size_t>(No, 1)));
+        CU(h->ev_jp.alloc(48 * std::max<size_t>(No, 1)));
+    }
+    return BA_OK;
+}
+} // namespace
+
+extern "C" int ba_evaluate(ba_handle *h, double *cost, double *residuals, double *jac_cam, double *jac_pt,
+                           double *grad_cam, double *grad_pt) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "ba_evaluate before ba_set_problem");
+    CU(cudaSetDevice(h->device));
+    Ctx &ctx = h->ctx;
+    ctx.opt = h->opt;
+    cudaStream_t s = h->stream;
+    int rc;
+    if ((rc = ensure_eval_buffers(h))) return rc;
+    const int No = ctx.No, Nc = ctx.Nc, Np = ctx.Np;
+    launch_cam_prep(ctx, 0, 1, s);
+    const int nb = (No + 127) / 128;
+    if (No) launch_materialize(ctx, h->ev_res.as<double>(), h->ev_jc.as<double>(), h->ev_jp.as<double>(), h->cost_part.as<double>(), s);
+    // gradient: unscaled blocks b_c, b_p of a forced linearisation with unit scale
+    if (grad_cam || grad_pt) {
+        launch_fill(ctx.scale_cam, 6 * (size_t)Nc, 1.0, s);
+        launch_fill(ctx.scale_pt, 3 * (size_t)Np, 1.0, s);
+        if ((rc = enqueue_linearize(h, 1))) return rc;
+    }
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    std::vector<double> part(std::max(nb, 1));
+    if (nb) CU(cudaMemcpy(part.data(), h->cost_part.p, 8 * (size_t)nb, cudaMemcpyDeviceToHost));
+    if (cost) {
+        double c = 0;
+        for (int i = 0; i < nb; ++i) c += part[i];
+        if (h->comm) {
+            // sum over ranks through the device
+            CU(cudaMemcpy(h->sums_loc.p, &c, 8, cudaMemcpyHostToDevice));
+            NC(ncclAllReduce(h->sums_loc.p, h->sums_loc.p, 1, ncclDouble, ncclSum, h->comm, s));
+            CU(cudaStreamSynchronize(s));
+            CU(cudaMemcpy(&c, h->sums_loc.p, 8, cudaMemcpyDeviceToHost));
+        }
+        *cost = c;
+    }
+    auto gather = [&](const DevBuf &src, double *dst, int width) -> int {
+        std::vector<double> tmp((size_t)No * width);
+        if (No) CU(cudaMemcpy(tmp.data(), src.p, 8 * tmp.size(), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < No; ++i) std::memcpy(dst + (size_t)i * width, tmp.data() + (size_t)h->perm[i] * width, 8 * (size_t)width);
+        return BA_OK;
+    };
+    if (residuals && (rc = gather(h->ev_res, residuals, 2))) return rc;
+    if (jac_cam && (rc = gather(h->ev_jc, jac_cam, 12))) return rc;
+    if (jac_pt && (rc = gather(h->ev_jp, jac_pt, 6))) return rc;
+    if (grad_cam) {
+        CU(cudaMemcpy(grad_cam, ctx.bc, 8 * 6 * (size_t)Nc, cudaMemcpyDeviceToHost));
+        std::vector<int> kind(Nc);
+        CU(cudaMemcpy(kind.data(), ctx.cam_kind, 4 * (size_t)Nc, cudaMemcpyDeviceToHost));
+        for (int c = 0; c < Nc; ++c) if (kind[c] != CAM_FREE) for (int k = 0; k < 6; ++k) grad_cam[6 * (size_t)c + k] = 0.0;
+    }
+    if (grad_pt && Np) CU(cudaMemcpy(grad_pt, ctx.bp, 8 * 3 * (size_t)Np, cudaMemcpyDeviceToHost));
+    return BA_OK;
+}
+
+extern "C" int ba_evaluate_device(ba_handle *h, int32_t repeats, float *ms_per_call) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "ba_evaluate_device before ba_set_problem");
+    CU(cudaSetDevice(h->device));
+    Ctx &ctx = h->ctx;
+    ctx.opt = h->opt;
+    cudaStream_t s = h->stream;
+    int rc;
+    if ((rc = ensure_eval_buffers(h))) return rc;
+    if (repeats < 1) repeats = 1;
+    CU(cudaEventRecord(h->ev_start, s));
+    for (int r = 0; r < repeats; ++r) {
+        launch_cam_prep(ctx, 0, 1, s);
+        launch_materialize(ctx, h->ev_res.as<double>(), h->ev_jc.as<double>(), h->ev_jp.as<double>(), h->cost_part.as<double>(), s);
+    }
+    CU(cudaEventRecord(h->ev_stop, s));
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, h->ev_start, h->ev_stop));
+    if (ms_per_call) *ms_per_call = ms / repeats;
+    return BA_OK;
+}
+
+extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *rhs, double *cost) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "ba_schur_system before ba_set_problem");
+    if (!(radius > 0)) return fail(BA_ERR_INVALID, "radius must be positive");
+    CU(cudaSetDevice(h->device));
+    Ctx &ctx = h->ctx;
+    ctx.opt = h->opt;
+    ctx.rank = h->rank; ctx.n_ranks = h->n_ranks;
+    cudaStream_t s = h->stream;
+    int rc;
+    if ((rc = ensure_dense(h))) return rc;
+    launch_fill(ctx.scale_cam, 6 * (size_t)ctx.Nc, 1.0, s);
+    launch_fill(ctx.scale_pt, 3 * (size_t)ctx.Np, 1.0, s);
+    if ((rc = enqueue_linearize(h, 1))) return rc;
+    if (h->opt.jacobi_scaling) {
+        launch_compute_scale(ctx, s);
+        if ((rc = enqueue_linearize(h, 1))) return rc;
+    }
+    launch_point_invert(ctx, radius, s);
+    launch_schur_build(ctx, radius, s);
+    if (h->comm) {
+        if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.n))) return rc;
+        if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
+    }
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    if (S) CU(cudaMemcpy(S, ctx.S, 8 * (size_t)ctx.n * ctx.n, cudaMemcpyDeviceToHost));
+    if (rhs) CU(cudaMemcpy(rhs, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToHost));
+    if (cost) CU(cudaMemcpy(cost, ctx.sums + SUM_LIN_COST, 8, cudaMemcpyDeviceToHost));
+    return BA_OK;
+}
+
+// Dense SPD solve utility: exposes the reduced-system Cholesky on its own (tests, micro-benchmarks).
+// A: n x n row-major (lower triangle read), b: n.  x: n.  ms (optional): device time of factor + solve.
+extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats) {
+    if (n <= 0 || !A || !b || !x) return fail(BA_ERR_INVALID, "bad arguments");
+    int rc = check_device(device);
+    if (rc) return rc;
+    int e0 = chol_init();
+    if (e0) return fail(BA_ERR_CUDA, "chol_init: %s", cudaGetErrorString((cudaError_t)e0));
+    const int np = (n + 1) & ~1;          // even order keeps 16-byte row alignment
+    std::vector<double> Ah((size_t)(np + 1) * np, 0.0);
+    for (int i = 0; i < n; ++i) std::memcpy(&Ah[(size_t)i * np], A + (size_t)i * n, 8 * (size_t)n);
+    if (np > n) Ah[(size_t)n * np + n] = 1.0;
+    std::memcpy(&Ah[(size_t)np * np], b, 8 * (size_t)n);
+    DevBuf dA, dA0, dInv, dY, dFail;
+    CU(dA.alloc(8 * Ah.size())); CU(dA0.alloc(8 * Ah.size()));
+    CU(dInv.alloc(8 * chol_work_doubles(np))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
+    CU(cudaMemcpy(dA0.p, Ah.data(), 8 * Ah.size(), cudaMemcpyHostToDevice));
+    CU(cudaMemset(dFail.p, 0, 4));
+    cudaEvent_t e1, e2;
+    CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
+    if (repeats < 1) repeats = 1;
+    float best = 1e30f;
+    for (int r = 0; r < repeats; ++r) {
+        CU(cudaMemcpy(dA.p, dA0.p, 8 * Ah.size(), cudaMemcpyDeviceToDevice));
+        CU(cudaEventRecord(e1, 0));
+        chol_factor_solve(dA.as<double>(), np, dInv.as<double>(), dY.as<double>(), nullptr, dFail.as<int>(), 0);
+        CU(cudaEventRecord(e2, 0));
+        CU(cudaDeviceSynchronize());
+        float t = 0;
+        CU(cudaEventElapsedTime(&t, e1, e2));
+        best = std::min(best, t);
+    }
+    CU(cudaGetLastError());
+    int failed = 0;
+    CU(cudaMemcpy(&failed, dFail.p, 4, cudaMemcpyDeviceToHost));
+    std::vector<double> y(np);
+    CU(cudaMemcpy(y.data(), dY.p, 8 * (size_t)np, cudaMemcpyDeviceToHost));
+    std::memcpy(x, y.data(), 8 * (size_t)n);
+    if (ms) *ms = best;
+    cudaEventDestroy(e1); cudaEventDestroy(e2);
+    dA.free(); dA0.free(); dInv.free(); dY.free(); dFail.free();
+    if (failed) return fail(BA_ERR_INVALID, "matrix is not positive definite");
+    return BA_OK;
+}
+
+// =============================================================================================================
+// batched frame-to-frame pose estimation, pruning
+// =============================================================================================================
+extern "C" void ba_inverse4x4_f32(const float m[16], float out[16]);   // ba_host.cpp
+
+extern "C" int ba_solve_pose_only_batch(const ba_options *opt_in, int device, int32_t B, double *cam, const float *K,
+                                        const int32_t *prob_ptr, const float *Xh, const float *uv, const uint8_t *obs_mask,
+                                        ba_summary *summaries, ba_iteration *iters, int32_t iters_cap) {
+    if (B < 0 || (B && (!cam || !K || !prob_ptr))) return fail(BA_ERR_INVALID, "bad arguments");
+    int rc = check_device(device);
+    if (rc) return rc;
+    if (B == 0) return BA_OK;
+    ba_options opt;
+    if (opt_in) opt = *opt_in; else { ba_default_options(&opt); opt.max_num_iterations = 20; }
+    const int No = prob_ptr[B];
+    for (int b = 0; b < B; ++b)
+        if (prob_ptr[b + 1] < prob_ptr[b]) return fail(BA_ERR_INVALID, "prob_ptr not monotone at %d", b);
+    if (No && (!Xh || !uv)) return fail(BA_ERR_INVALID, "NULL observation arrays");
+    if (iters && iters_cap <= 0) return fail(BA_ERR_INVALID, "iters given but iters_cap <= 0");
+    cudaStream_t s;
+    CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    DevBuf dcam, dK, dptr, dX, duv, dmask, dsum, dit;
+    CU(dcam.alloc(48 * (size_t)B)); CU(dK.alloc(36 * (size_t)B)); CU(dptr.alloc(4 * (size_t)(B + 1)));
+    CU(dX.alloc(16 * std::max<size_t>(No, 1))); CU(duv.alloc(8 * std::max<size_t>(No, 1)));
+    CU(dsum.alloc(sizeof(ba_summary) * (size_t)B));
+    if (obs_mask) CU(dmask.alloc(std::max<size_t>(No, 1)));
+    if (iters) CU(dit.alloc(sizeof(ba_iteration) * (size_t)B * iters_cap));
+    cudaEvent_t e1, e2;
+    CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
+    CU(cudaMemcpyAsync(dcam.p, cam, 48 * (size_t)B, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(dK.p, K, 36 * (size_t)B, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(dptr.p, prob_ptr, 4 * (size_t)(B + 1), cudaMemcpyHostToDevice, s));
+    if (No) {
+        CU(cudaMemcpyAsync(dX.p, Xh, 16 * (size_t)No, cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpyAsync(duv.p, uv, 8 * (size_t)No, cudaMemcpyHostToDevice, s));
+        if (obs_mask) CU(cudaMemcpyAsync(dmask.p, obs_mask, (size_t)No, cudaMemcpyHostToDevice, s));
+    }
+    if (iters) CU(cudaMemsetAsync(dit.p, 0, dit.bytes, s));
+    CU(cudaEventRecord(e1, s));
+    launch_pose_batch(opt, B, dcam.as<double>(), dK.as<float>(), dptr.as<int>(), dX.as<float4>(), duv.as<float2>(),
+                      obs_mask ? dmask.as<uint8_t>() : nullptr, dsum.as<ba_summary>(), iters ? dit.as<ba_iteration>() : nullptr,
+                      iters_cap, s);
+    CU(cudaEventRecord(e2, s));
+    CU(cudaMemcpyAsync(cam, dcam.p, 48 * (size_t)B, cudaMemcpyDeviceToHost, s));
+    std::vector<ba_summary> sm(B);
+    CU(cudaMemcpyAsync(sm.data(), dsum.p, sizeof(ba_summary) * (size_t)B, cudaMemcpyDeviceToHost, s));
+    if (iters) CU(cudaMemcpyAsync(iters, dit.p, dit.bytes, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e1, e2);
+    if (summaries) {
+        for (int b = 0; b < B; ++b) {
+            ba_summary &o = summaries[b];
+            o = sm[b];
+            const int msg = (int)(unsigned char)o.message[0];
+            std::snprintf(o.message, sizeof(o.message), "%s", message_text(msg));
+            o.seconds_total = ms * 1e-3;     // whole batch (one launch)
+            if (iters) {
+                double fc = o.initial_cost;
+                const int n = std::min(o.num_iterations, iters_cap);
+                for (int i = 0; i < n; ++i) fc = std::min(fc, iters[(size_t)b * iters_cap + i].cost);
+                o.final_cost = fc;
+            }
+        }
+    }
+    cudaEventDestroy(e1); cudaEventDestroy(e2);
+    dcam.free(); dK.free(); dptr.free(); dX.free(); duv.free(); dmask.free(); dsum.free(); dit.free();
+    cudaStreamDestroy(s);
+    return BA_OK;
+}
+
+extern "C" int ba_prune_frames(int device, int32_t n_frames, const float *pose, const float *K, const int32_t *frame_ptr,
+                               const float *kp_xy, const int32_t *kp_octave, const float *pt_xyz, const float *pt_min_dist,
+                               const float *pt_max_dist, const uint8_t *has_point, uint8_t *outlier, int32_t consider_outlier) {
+    if (n_frames < 0 || (n_frames && (!pose || !K || !frame_ptr))) return fail(BA_ERR_INVALID, "bad arguments");
+    int rc = check_device(device);
+    if (rc) return rc;
+    if (n_frames == 0) return BA_OK;
+    const int n_kp = frame_ptr[n_frames];
+    if (n_kp == 0) return BA_OK;
+    if (!kp_xy || !kp_octave || !pt_xyz || !pt_min_dist || !pt_max_dist || !has_point || !outlier) return fail(BA_ERR_INVALID, "NULL keypoint arrays");
+    // extr = pose.inverse() in float32, once per frame (Optimizer.cpp:10)
+    std::vector<float> extr(16 * (size_t)n_frames);
+    for (int f = 0; f < n_frames; ++f) ba_inverse4x4_f32(pose + 16 * (size_t)f, extr.data() + 16 * (size_t)f);
+    DevBuf dpose, dextr, dK, dptr, dxy, doct, dpt, dmin, dmax, dhas, dout;
+    CU(dpose.alloc(64 * (size_t)n_frames)); CU(dextr.alloc(64 * (size_t)n_frames)); CU(dK.alloc(36 * (size_t)n_frames));
+    CU(dptr.alloc(4 * (size_t)(n_frames + 1)));
+    CU(dxy.alloc(8 * (size_t)n_kp)); CU(doct.alloc(4 * (size_t)n_kp)); CU(dpt.alloc(12 * (size_t)n_kp));
+    CU(dmin.alloc(4 * (size_t)n_kp)); CU(dmax.alloc(4 * (size_t)n_kp)); CU(dhas.alloc((size_t)n_kp)); CU(dout.alloc((size_t)n_kp));
+    CU(cudaMemcpy(dpose.p, pose, dpose.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dextr.p, extr.data(), dextr.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dK.p, K, dK.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dptr.p, frame_ptr, dptr.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dxy.p, kp_xy, dxy.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(doct.p, kp_octave, doct.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dpt.p, pt_xyz, dpt.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dmin.p, pt_min_dist, dmin.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dmax.p, pt_max_dist, dmax.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dhas.p, has_point, dhas.bytes, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dout.p, outlier, dout.bytes, cudaMemcpyHostToDevice));
+    launch_prune(n_frames, dpose.as<float>(), dextr.as<float>(), dK.as<float>(), dptr.as<int>(), dxy.as<float2>(), doct.as<int>(),
+                 dpt.as<float>(), dmin.as<float>(), dmax.as<float>(), dhas.as<uint8_t>(), dout.as<uint8_t>(), consider_outlier, n_kp, 0);
+    CU(cudaDeviceSynchronize());
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(outlier, dout.p, dout.bytes, cudaMemcpyDeviceToHost));
+    DevBuf *all[] = {&dpose, &dextr, &dK, &dptr, &dxy, &doct, &dpt, &dmin, &dmax, &dhas, &dout};
+    for (DevBuf *b : all) b->free();
+    return BA_OK;
+}
+
+// =============================================================================================================
+// multi-GPU plumbing: NCCL communicator per handle (one process per GPU; the unique id travels through the
+// caller's own control plane, e.g. a torch.distributed broadcast)
+// =============================================================================================================
+extern "C" int ba_comm_unique_id(uint8_t id[128]) {
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    ncclUniqueId uid;
+    NC(ncclGetUniqueId(&uid));
+    std::memcpy(id, &uid, 128);
+    return BA_OK;
+}
+
+extern "C" int ba_comm_init(ba_handle *h, int32_t n_ranks, int32_t rank, const uint8_t id[128]) {
+    if (!h || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(BA_ERR_INVALID, "bad arguments");
+    if (h->has_problem) return fail(BA_ERR_STATE, "ba_comm_init must precede ba_set_problem");
+    CU(cudaSetDevice(h->device));
+    if (h->comm) { ncclCommDestroy(h->comm); h->comm = nullptr; }
+    h->n_ranks = n_ranks; h->rank = rank;
+    if (n_ranks == 1) return BA_OK;
+    ncclUniqueId uid;
+    std::memcpy(&uid, id, 128);
+    NC(ncclCommInitRank(&h->comm, n_ranks, uid, rank));
+    return BA_OK;
+}

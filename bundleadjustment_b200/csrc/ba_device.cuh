@@ -1,0 +1,286 @@
+// ba_device.cuh -- device-side building blocks shared by the BA kernels (sm_100a).
+//
+// Math follows the reference functors (ba_project/src/ba/Optimizer.h:54-76 R1, 96-107 R2, 163-182 R3) with
+// float32 inputs promoted to double exactly where the functors cast to T, and Ceres' HuberLoss + Corrector
+// semantics.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <float.h>
+#include <math.h>
+
+namespace ba {
+
+// ---------------------------------------------------------------------------------------------------------
+// Per-camera table entry, rebuilt once per linearisation point by cam_prep_kernel so that the per-observation
+// kernels never evaluate sincos.  48 doubles = 384 B, 128-bit aligned.
+//   free camera : R (col-major 3x3), dR[3] = dR/dw_k (col-major), t, K (row-major, promoted from f32)
+//   fixed camera: P = 4x4 row-major world->camera extrinsics (promoted from f32) in R[0..8]+dR[0..6], K
+// ---------------------------------------------------------------------------------------------------------
+struct __align__(16) CamEntry {
+    double R[9];
+    double dR[27];
+    double t[3];
+    double K[9];
+};
+static_assert(sizeof(CamEntry) == 48 * 8, "CamEntry layout");
+
+enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
+
+// ceres::AngleAxisToRotationMatrix + closed-form derivative of the branch taken (autodiff-equivalent)
+__device__ __forceinline__ void rodrigues(const double w[3], double R[9], double *dR /*27 or nullptr*/) {
+    const double theta2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+    if (theta2 > DBL_EPSILON) {
+        const double theta = sqrt(theta2);
+        const double k0 = w[0] / theta, k1 = w[1] / theta, k2 = w[2] / theta;
+        double s, c;
+        sincos(theta, &s, &c);
+        const double omc = 1.0 - c;
+        R[0] = c + k0 * k0 * omc;       R[1] = k2 * s + k0 * k1 * omc;  R[2] = -k1 * s + k0 * k2 * omc;
+        R[3] = k0 * k1 * omc - k2 * s;  R[4] = c + k1 * k1 * omc;       R[5] = k0 * s + k1 * k2 * omc;
+        R[6] = k1 * s + k0 * k2 * omc;  R[7] = -k0 * s + k1 * k2 * omc; R[8] = c + k2 * k2 * omc;
+        if (dR) {
+            const double k[3] = {k0, k1, k2};
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                double dk[3];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) dk[i] = ((i == j ? 1.0 : 0.0) - k[i] * k[j]) / theta;
+                const double dth = k[j];
+                double *D = dR + 9 * j;
+#pragma unroll
+                for (int col = 0; col < 3; ++col)
+#pragma unroll
+                    for (int row = 0; row < 3; ++row) {
+                        double v = s * dth * k[row] * k[col] + omc * (dk[row] * k[col] + k[row] * dk[col]);
+                        if (row == col) v += -s * dth;
+                        D[row + 3 * col] = v;
+                    }
+                const double a0 = c * dth * k[0] + s * dk[0];
+                const double a1 = c * dth * k[1] + s * dk[1];
+                const double a2 = c * dth * k[2] + s * dk[2];
+                D[0 + 3 * 1] += -a2; D[0 + 3 * 2] += a1;
+                D[1 + 3 * 0] += a2;  D[1 + 3 * 2] += -a0;
+                D[2 + 3 * 0] += -a1; D[2 + 3 * 1] += a0;
+            }
+        }
+    } else {
+        R[0] = 1.0;   R[1] = w[2];  R[2] = -w[1];
+        R[3] = -w[2]; R[4] = 1.0;   R[5] = w[0];
+        R[6] = w[1];  R[7] = -w[0]; R[8] = 1.0;
+        if (dR) {
+#pragma unroll
+            for (int i = 0; i < 27; ++i) dR[i] = 0.0;
+            // d/dw0: [e0]x ; d/dw1: [e1]x ; d/dw2: [e2]x  (col-major)
+            dR[0 * 9 + 2 + 3 * 1] = 1.0;  dR[0 * 9 + 1 + 3 * 2] = -1.0;
+            dR[1 * 9 + 0 + 3 * 2] = 1.0;  dR[1 * 9 + 2 + 3 * 0] = -1.0;
+            dR[2 * 9 + 1 + 3 * 0] = 1.0;  dR[2 * 9 + 0 + 3 * 1] = -1.0;
+        }
+    }
+}
+
+// ceres::HuberLoss::Evaluate: returns rho'(s) and sets rho0 = rho(s).  a = delta, b = a*a.
+__device__ __forceinline__ double huber_rho(double s, double a, int use_huber, double &rho0) {
+    if (!use_huber) { rho0 = s; return 1.0; }
+    const double b = a * a;
+    if (s > b) {
+        const double r = sqrt(s);
+        rho0 = 2.0 * a * r - b;
+        return fmax(DBL_MIN, a / r);
+    }
+    rho0 = s;
+    return 1.0;
+}
+
+// pinhole tail: q = K p, pix = q.hnormalized(), G = d pix / d p (2x3 row-major)
+__device__ __forceinline__ void project(const double *__restrict__ K, const double p[3], double pix[2], double G[6], bool want_G) {
+    const double q0 = K[0] * p[0] + K[1] * p[1] + K[2] * p[2];
+    const double q1 = K[3] * p[0] + K[4] * p[1] + K[5] * p[2];
+    const double q2 = K[6] * p[0] + K[7] * p[1] + K[8] * p[2];
+    pix[0] = q0 / q2;
+    pix[1] = q1 / q2;
+    if (want_G) {
+        const double iq = 1.0 / q2;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            G[j] = (K[j] - pix[0] * K[6 + j]) * iq;
+            G[3 + j] = (K[3 + j] - pix[1] * K[6 + j]) * iq;
+        }
+    }
+}
+
+// residual only (cost evaluation at a candidate point).  kind: CAM_FREE / CAM_FIXED.
+__device__ __forceinline__ void obs_residual(const CamEntry *__restrict__ ce, int kind, const double X[3], float2 uv, double r[2]) {
+    double p[3];
+    if (kind == CAM_FREE) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) p[i] = ce->R[i] * X[0] + ce->R[i + 3] * X[1] + ce->R[i + 6] * X[2] + ce->t[i];
+    } else {
+        const double *P = ce->R; // 16 contiguous doubles (R[9] then dR[0..6])
+        double ph[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
+        p[0] = ph[0] / ph[3]; p[1] = ph[1] / ph[3]; p[2] = ph[2] / ph[3];
+    }
+    double pix[2];
+    project(ce->K, p, pix, nullptr, false);
+    r[0] = pix[0] - (double)uv.x;
+    r[1] = pix[1] - (double)uv.y;
+}
+
+// residual + Jacobians (unrobustified, unscaled).  Jc 2x6 row-major (zero for fixed), Jp 2x3 row-major.
+template <bool WANT_JC, bool WANT_JP>
+__device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, int kind, const double X[3], float2 uv,
+                                              double r[2], double Jc[12], double Jp[6]) {
+    double p[3], pix[2], G[6];
+    if (kind == CAM_FREE) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) p[i] = ce->R[i] * X[0] + ce->R[i + 3] * X[1] + ce->R[i + 6] * X[2] + ce->t[i];
+        project(ce->K, p, pix, G, true);
+        if (WANT_JP) {
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+                for (int j = 0; j < 3; ++j)
+                    Jp[rr * 3 + j] = G[rr * 3 + 0] * ce->R[0 + 3 * j] + G[rr * 3 + 1] * ce->R[1 + 3 * j] + G[rr * 3 + 2] * ce->R[2 + 3 * j];
+        }
+        if (WANT_JC) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const double *D = ce->dR + 9 * j;
+                double d[3];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) d[i] = D[i] * X[0] + D[i + 3] * X[1] + D[i + 6] * X[2];
+                Jc[j] = G[0] * d[0] + G[1] * d[1] + G[2] * d[2];
+                Jc[6 + j] = G[3] * d[0] + G[4] * d[1] + G[5] * d[2];
+            }
+#pragma unroll
+            for (int j = 0; j < 3; ++j) { Jc[3 + j] = G[j]; Jc[9 + j] = G[3 + j]; }
+        }
+    } else {
+        const double *P = ce->R;
+        double ph[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
+        const double ih = 1.0 / ph[3];
+        p[0] = ph[0] / ph[3]; p[1] = ph[1] / ph[3]; p[2] = ph[2] / ph[3];
+        project(ce->K, p, pix, G, true);
+        if (WANT_JP) {
+            double dp[9];
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) dp[i * 3 + j] = (P[4 * i + j] - p[i] * P[12 + j]) * ih;
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+                for (int j = 0; j < 3; ++j)
+                    Jp[rr * 3 + j] = G[rr * 3 + 0] * dp[j] + G[rr * 3 + 1] * dp[3 + j] + G[rr * 3 + 2] * dp[6 + j];
+        }
+        if (WANT_JC) {
+#pragma unroll
+            for (int j = 0; j < 12; ++j) Jc[j] = 0.0;
+        }
+    }
+    r[0] = pix[0] - (double)uv.x;
+    r[1] = pix[1] - (double)uv.y;
+}
+
+// ---- reductions --------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+// deterministic block sum (fixed tree); result valid in thread 0.  smem: >= 32 doubles.
+__device__ __forceinline__ double block_sum(double v, double *smem) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) smem[wid] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    v = (threadIdx.x < nw) ? smem[threadIdx.x] : 0.0;
+    if (wid == 0) v = warp_sum(v);
+    return v;
+}
+__device__ __forceinline__ double block_max(double v, double *smem) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) smem[wid] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    v = (threadIdx.x < nw) ? smem[threadIdx.x] : 0.0;
+    if (wid == 0) v = warp_max(v);
+    return v;
+}
+
+// symmetric 3x3 SPD inverse via Cholesky (InvertPSDMatrix).  m = {00,01,02,11,12,22}; returns false if not PD.
+__device__ __forceinline__ bool inv_sym3(const double m[6], double inv[6]) {
+    const double l00sq = m[0];
+    if (!(l00sq > 0.0)) return false;
+    const double l00 = sqrt(l00sq);
+    const double l10 = m[1] / l00, l20 = m[2] / l00;
+    const double d1 = m[3] - l10 * l10;
+    if (!(d1 > 0.0)) return false;
+    const double l11 = sqrt(d1);
+    const double l21 = (m[4] - l20 * l10) / l11;
+    const double d2 = m[5] - l20 * l20 - l21 * l21;
+    if (!(d2 > 0.0)) return false;
+    const double l22 = sqrt(d2);
+    // inverse of L (lower)
+    const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
+    const double i10 = -l10 * i00 * i11;
+    const double i21 = -l21 * i11 * i22;
+    const double i20 = -(l20 * i00 + l21 * i10) * i22;
+    // A^-1 = L^-T L^-1
+    inv[0] = i00 * i00 + i10 * i10 + i20 * i20;
+    inv[1] = i10 * i11 + i20 * i21;
+    inv[2] = i20 * i22;
+    inv[3] = i11 * i11 + i21 * i21;
+    inv[4] = i21 * i22;
+    inv[5] = i22 * i22;
+    return true;
+}
+
+// dense 6x6 SPD inverse (row-major full in/out) via Cholesky; returns false if not PD.
+__device__ __forceinline__ bool inv_spd6(const double *A, double *inv) {
+    double L[36];
+#pragma unroll
+    for (int i = 0; i < 36; ++i) L[i] = 0.0;
+    for (int j = 0; j < 6; ++j) {
+        double d = A[j * 6 + j];
+        for (int k = 0; k < j; ++k) d -= L[j * 6 + k] * L[j * 6 + k];
+        if (!(d > 0.0)) return false;
+        d = sqrt(d);
+        L[j * 6 + j] = d;
+        for (int i = j + 1; i < 6; ++i) {
+            double v = A[i * 6 + j];
+            for (int k = 0; k < j; ++k) v -= L[i * 6 + k] * L[j * 6 + k];
+            L[i * 6 + j] = v / d;
+        }
+    }
+    for (int c = 0; c < 6; ++c) {
+        double y[6];
+        for (int i = 0; i < 6; ++i) {
+            double v = (i == c) ? 1.0 : 0.0;
+            for (int k = 0; k < i; ++k) v -= L[i * 6 + k] * y[k];
+            y[i] = v / L[i * 6 + i];
+        }
+        for (int i = 5; i >= 0; --i) {
+            double v = y[i];
+            for (int k = i + 1; k < 6; ++k) v -= L[k * 6 + i] * inv[k * 6 + c];
+            inv[i * 6 + c] = v / L[i * 6 + i];
+        }
+    }
+    return true;
+}
+
+} // namespace ba

@@ -1,0 +1,710 @@
+// ba_kernels.cu -- residual/Jacobian evaluation, normal-equation blocks, Schur assembly, back-substitution and
+// the device-resident trust-region controller.
+//
+// Reference lines replaced: the per-residual AutoDiffCostFunction::Evaluate of AngleReprojectionError and
+// PointOnlyReprojectionError (ba_project/src/ba/Optimizer.h:54-76, 96-107) + HuberLoss (Optimizer.cpp:312) and
+// everything ceres::Solve (Optimizer.cpp:242) does with them per LM iteration.
+#include "ba_launch.h"
+
+namespace ba {
+
+#define DEV_STATE_GUARD(ctx)                 \
+    const LMState *st__ = (ctx).state;       \
+    if (st__->done) return;
+
+// -------------------------------------------------------------------------------------------------------------
+// C1 prologue: per-camera R, dR/dw (no sincos in the per-observation kernels)
+// -------------------------------------------------------------------------------------------------------------
+__global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs need_linearize), 1: candidate*/, int force) {
+    const LMState *st = ctx.state;
+    if (!force) {
+        if (st->done) return;
+        if (which == 0 && !st->need_linearize) return;
+    }
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ctx.Nc) return;
+    const int buf = which == 0 ? st->cur : (st->cur ^ 1);
+    CamEntry *ce = (which == 0 ? ctx.tab_x : ctx.tab_c) + c;
+    const int kind = ctx.cam_kind[c];
+    const float *K = ctx.cam_K + 9 * (size_t)c;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) ce->K[i] = (double)K[i];
+    if (kind == CAM_FIXED) {
+        const float *E = ctx.cam_extr + 16 * (size_t)c;
+        double *P = ce->R;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) P[i] = (double)E[i];
+        return;
+    }
+    const double *x = ctx.cam[buf] + 6 * (size_t)c;
+    double w[3] = {x[0], x[1], x[2]};
+    double R[9], dR[27];
+    rodrigues(w, R, which == 0 ? dR : nullptr);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) ce->R[i] = R[i];
+    if (which == 0) {
+#pragma unroll
+        for (int i = 0; i < 27; ++i) ce->dR[i] = dR[i];
+    }
+    ce->t[0] = x[3]; ce->t[1] = x[4]; ce->t[2] = x[5];
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// C1+C2+C3 (landmark side): one thread per landmark walks its track: residual, analytic Jacobian, Huber
+// corrector, Jacobi scaling, V_p, b_p, W = Jc^T Jp per observation, cost and gradient-norm partials.
+// -------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) linearize_points_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && (st->done || !st->need_linearize)) return;
+    __shared__ double red[32];
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const double *ptx = ctx.pt[st->cur];
+    double cost = 0.0, gsq = 0.0, gmax = 0.0, xsq = 0.0;
+    if (p < ctx.Np) {
+        const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
+        double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
+        if (o1 > o0) {
+            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+            const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
+            for (int o = o0; o < o1; ++o) {
+                const int c = ctx.pm_cam[o];
+                const int kind = ctx.cam_kind[c];
+                const float2 uv = ctx.pm_uv[o];
+                double r[2], Jc[12], Jp[6];
+                obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
+                double rho0;
+                const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+                const double sr = sqrt(rho1);
+                cost += 0.5 * rho0;
+                r[0] *= sr; r[1] *= sr;
+#pragma unroll
+                for (int j = 0; j < 3; ++j) { const double f = sr * sp[j]; Jp[j] *= f; Jp[3 + j] *= f; }
+                V[0] += Jp[0] * Jp[0] + Jp[3] * Jp[3];
+                V[1] += Jp[0] * Jp[1] + Jp[3] * Jp[4];
+                V[2] += Jp[0] * Jp[2] + Jp[3] * Jp[5];
+                V[3] += Jp[1] * Jp[1] + Jp[4] * Jp[4];
+                V[4] += Jp[1] * Jp[2] + Jp[4] * Jp[5];
+                V[5] += Jp[2] * Jp[2] + Jp[5] * Jp[5];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) b[j] += Jp[j] * r[0] + Jp[3 + j] * r[1];
+                double *Wo = ctx.W + 18 * (size_t)o;
+                if (kind == CAM_FREE) {
+                    const double *sc = ctx.scale_cam + 6 * (size_t)c;
+#pragma unroll
+                    for (int a = 0; a < 6; ++a) {
+                        const double f = sr * sc[a];
+                        const double j0 = Jc[a] * f, j1 = Jc[6 + a] * f;
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) Wo[a * 3 + k] = j0 * Jp[k] + j1 * Jp[3 + k];
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 18; ++k) Wo[k] = 0.0;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const double g = b[j] / sp[j];
+                const double d = X[j] - (X[j] + (-g));
+                gsq += d * d;
+                gmax = fmax(gmax, fabs(d));
+                xsq += X[j] * X[j];
+            }
+        }
+        double *Vp = ctx.V + 6 * (size_t)p;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) Vp[k] = V[k];
+        double *bp = ctx.bp + 3 * (size_t)p;
+        bp[0] = b[0]; bp[1] = b[1]; bp[2] = b[2];
+    }
+    cost = block_sum(cost, red);
+    gsq = block_sum(gsq, red);
+    xsq = block_sum(xsq, red);
+    gmax = block_max(gmax, red);
+    if (threadIdx.x == 0) {
+        double *pp = ctx.part + 4 * (size_t)blockIdx.x;
+        pp[0] = cost; pp[1] = gsq; pp[2] = xsq; pp[3] = gmax;
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// C3 (camera side): camera-major pass, one warp per chunk of <= CHUNK observations of ONE camera: U_c, b_c
+// partials by warp-level reduction (deterministic: fixed lane assignment + fixed shuffle tree).
+// -------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) linearize_cams_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && (st->done || !st->need_linearize)) return;
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= ctx.n_chunks) return;
+    const int c = ctx.chunk_cam[w];
+    const int beg = ctx.chunk_beg[w], end = ctx.chunk_end[w];
+    const CamEntry *ce = ctx.tab_x + c;
+    const double *ptx = ctx.pt[st->cur];
+    double sc[6];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) sc[a] = ctx.scale_cam[6 * (size_t)c + a];
+    double acc[27];
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    for (int e = beg + lane; e < end; e += 32) {
+        const int p = ctx.cm_pt[e];
+        const float2 uv = ctx.cm_uv[e];
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        double r[2], Jc[12], Jp[6];
+        obs_linearize<true, false>(ce, CAM_FREE, X, uv, r, Jc, Jp);
+        double rho0;
+        const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+        const double sr = sqrt(rho1);
+        r[0] *= sr; r[1] *= sr;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) { const double f = sr * sc[a]; Jc[a] *= f; Jc[6 + a] *= f; }
+        int k = 0;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = a; b < 6; ++b) acc[k++] += Jc[a] * Jc[b] + Jc[6 + a] * Jc[6 + b];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) acc[21 + a] += Jc[a] * r[0] + Jc[6 + a] * r[1];
+    }
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) {
+        double *dst = ctx.cam_part + 27 * (size_t)w;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) dst[k] = acc[k];
+    }
+}
+
+// per camera: ordered sum of its chunk partials -> U (full 6x6 row-major), b_c
+__global__ void cam_reduce_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && (st->done || !st->need_linearize)) return;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ctx.Nc) return;
+    double acc[27];
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    for (int w = ctx.cam_chunk_ptr[c]; w < ctx.cam_chunk_ptr[c + 1]; ++w) {
+        const double *src = ctx.cam_part + 27 * (size_t)w;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) acc[k] += src[k];
+    }
+    double *U = ctx.U_loc + 36 * (size_t)c;
+    int k = 0;
+#pragma unroll
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+        for (int b = a; b < 6; ++b) { U[a * 6 + b] = acc[k]; U[b * 6 + a] = acc[k]; ++k; }
+#pragma unroll
+    for (int a = 0; a < 6; ++a) ctx.bc_loc[6 * (size_t)c + a] = acc[21 + a];
+}
+
+// landmark-side partials -> sums / maxs (single block, fixed order)
+__global__ void reduce_lin_partials_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && (st->done || !st->need_linearize)) return;
+    __shared__ double red[32];
+    double cost = 0, gsq = 0, xsq = 0, gmax = 0;
+    for (int i = threadIdx.x; i < ctx.n_part; i += blockDim.x) {
+        const double *pp = ctx.part + 4 * (size_t)i;
+        cost += pp[0]; gsq += pp[1]; xsq += pp[2]; gmax = fmax(gmax, pp[3]);
+    }
+    cost = block_sum(cost, red); gsq = block_sum(gsq, red); xsq = block_sum(xsq, red); gmax = block_max(gmax, red);
+    if (threadIdx.x == 0) {
+        ctx.sums_loc[SUM_LIN_COST] = cost; ctx.sums_loc[SUM_LIN_GSQ] = gsq; ctx.sums_loc[SUM_LIN_XSQ] = xsq;
+        ctx.maxs_loc[MAX_LIN_G] = gmax;
+    }
+}
+
+// camera-side gradient / parameter norms from the (all-reduced) b_c; single block
+__global__ void cam_norms_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && (st->done || !st->need_linearize)) return;
+    __shared__ double red[32];
+    const double *x = ctx.cam[st->cur];
+    double gsq = 0, xsq = 0, gmax = 0;
+    for (int i = threadIdx.x; i < 6 * ctx.Nc; i += blockDim.x) {
+        if (ctx.cam_kind[i / 6] != CAM_FREE) continue;
+        const double g = ctx.bc[i] / ctx.scale_cam[i];
+        const double d = x[i] - (x[i] + (-g));
+        gsq += d * d; gmax = fmax(gmax, fabs(d)); xsq += x[i] * x[i];
+    }
+    gsq = block_sum(gsq, red); xsq = block_sum(xsq, red); gmax = block_max(gmax, red);
+    if (threadIdx.x == 0) { ctx.camsums[CS_GSQ] = gsq; ctx.camsums[CS_GMAX] = gmax; ctx.camsums[CS_XSQ] = xsq; }
+}
+
+// Jacobi scaling from the iteration-0 (unscaled) blocks: scale = 1 / (1 + sqrt(diag(J^T J)))
+__global__ void compute_scale_kernel(Ctx ctx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 6 * ctx.Nc) {
+        const int c = i / 6, a = i % 6;
+        ctx.scale_cam[i] = (ctx.cam_kind[c] == CAM_FREE) ? 1.0 / (1.0 + sqrt(ctx.U[36 * (size_t)c + a * 6 + a])) : 1.0;
+    }
+    if (i < 3 * ctx.Np) {
+        const int p = i / 3, a = i % 3;
+        const int idx = (a == 0) ? 0 : (a == 1 ? 3 : 5);
+        const bool active = ctx.pt_ptr[p + 1] > ctx.pt_ptr[p];
+        ctx.scale_pt[i] = active ? 1.0 / (1.0 + sqrt(ctx.V[6 * (size_t)p + idx])) : 1.0;
+    }
+}
+
+__global__ void fill_kernel(double *p, size_t n, double v) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// C4 + C5: LM diagonal, V'^-1, Schur complement S = (U + D_c^2) - sum_p W V'^-1 W^T, rhs = b_c - sum_p W V'^-1 b_p
+// -------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double lm_diag(const Ctx &ctx, double jtj, double radius) {
+    return fmin(fmax(jtj, ctx.opt.min_lm_diagonal), ctx.opt.max_lm_diagonal) / radius;
+}
+
+__global__ void __launch_bounds__(128) point_invert_kernel(Ctx ctx, double radius_override) {
+    const LMState *st = ctx.state;
+    if (radius_override <= 0 && st->done) return;
+    const double radius = radius_override > 0 ? radius_override : st->radius;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ctx.Np) return;
+    const double *V = ctx.V + 6 * (size_t)p;
+    double m[6] = {V[0], V[1], V[2], V[3], V[4], V[5]};
+    m[0] += lm_diag(ctx, V[0], radius);
+    m[3] += lm_diag(ctx, V[3], radius);
+    m[5] += lm_diag(ctx, V[5], radius);
+    double inv[6];
+    if (!inv_sym3(m, inv)) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) inv[k] = nan("");
+    }
+    double *Vi = ctx.Vinv + 6 * (size_t)p;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Vi[k] = inv[k];
+    const double *b = ctx.bp + 3 * (size_t)p;
+    double *w = ctx.wv + 3 * (size_t)p;
+    w[0] = inv[0] * b[0] + inv[1] * b[1] + inv[2] * b[2];
+    w[1] = inv[1] * b[0] + inv[3] * b[1] + inv[4] * b[2];
+    w[2] = inv[2] * b[0] + inv[4] * b[1] + inv[5] * b[2];
+}
+
+// diagonal blocks + rhs initialisation (S has been zeroed).  Only rank 0 contributes the replicated terms.
+__global__ void schur_init_kernel(Ctx ctx, double radius_override) {
+    const LMState *st = ctx.state;
+    if (radius_override <= 0 && st->done) return;
+    const double radius = radius_override > 0 ? radius_override : st->radius;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (camera, row a)
+    if (i >= 6 * ctx.Nc) return;
+    const int c = i / 6, a = i % 6;
+    double *row = ctx.S + (size_t)i * ctx.n + 6 * (size_t)c;
+    const bool lead = ctx.rank == 0;
+    if (ctx.cam_kind[c] == CAM_FREE) {
+        const double *U = ctx.U + 36 * (size_t)c;
+#pragma unroll
+        for (int b = 0; b < 6; ++b) row[b] = lead ? U[a * 6 + b] + (a == b ? lm_diag(ctx, U[a * 6 + a], radius) : 0.0) : 0.0;
+        ctx.rhs[i] = lead ? ctx.bc[i] : 0.0;
+    } else {
+#pragma unroll
+        for (int b = 0; b < 6; ++b) row[b] = (lead && a == b) ? 1.0 : 0.0;
+        ctx.rhs[i] = 0.0;
+    }
+}
+
+// one thread per landmark: all camera pairs of its track (lower blocks), fp64 atomics into S and rhs
+__global__ void __launch_bounds__(128) schur_accum_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && st->done) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ctx.Np) return;
+    const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
+    if (o1 <= o0) return;
+    const double *Vi = ctx.Vinv + 6 * (size_t)p;
+    const double vi[6] = {Vi[0], Vi[1], Vi[2], Vi[3], Vi[4], Vi[5]};
+    const double *wv = ctx.wv + 3 * (size_t)p;
+    const double w3[3] = {wv[0], wv[1], wv[2]};
+    const int n = ctx.n;
+    for (int i = o0; i < o1; ++i) {
+        const int ci = ctx.pm_cam[i];
+        if (ctx.cam_kind[ci] != CAM_FREE) continue;
+        const double *Wi = ctx.W + 18 * (size_t)i;
+        double Y[18];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            const double w0 = Wi[a * 3], w1 = Wi[a * 3 + 1], w2 = Wi[a * 3 + 2];
+            Y[a * 3 + 0] = w0 * vi[0] + w1 * vi[1] + w2 * vi[2];
+            Y[a * 3 + 1] = w0 * vi[1] + w1 * vi[3] + w2 * vi[4];
+            Y[a * 3 + 2] = w0 * vi[2] + w1 * vi[4] + w2 * vi[5];
+            atomicAdd(ctx.rhs + 6 * (size_t)ci + a, -(w0 * w3[0] + w1 * w3[1] + w2 * w3[2]));
+        }
+        for (int j = o0; j < o1; ++j) {
+            const int cj = ctx.pm_cam[j];
+            if (cj > ci || ctx.cam_kind[cj] != CAM_FREE) continue;     // lower blocks only (row ci >= col cj)
+            const double *Wj = ctx.W + 18 * (size_t)j;
+            double wj[18];
+#pragma unroll
+            for (int k = 0; k < 18; ++k) wj[k] = Wj[k];
+            double *dst = ctx.S + (size_t)(6 * ci) * n + 6 * (size_t)cj;
+#pragma unroll
+            for (int a = 0; a < 6; ++a)
+#pragma unroll
+                for (int b = 0; b < 6; ++b)
+                    atomicAdd(dst + (size_t)a * n + b, -(Y[a * 3] * wj[b * 3] + Y[a * 3 + 1] * wj[b * 3 + 1] + Y[a * 3 + 2] * wj[b * 3 + 2]));
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// C7: back-substitution y_p = V'^-1 (b_p - sum W^T y_c), candidate = x + (-y) * scale, model-cost pieces
+// -------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) backsub_kernel(Ctx ctx) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    __shared__ double red[32];
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const double *ptx = ctx.pt[st->cur];
+    double *ptc = ctx.pt[st->cur ^ 1];
+    double dxsq = 0, yb = 0, yhy = 0;
+    if (p < ctx.Np) {
+        const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        if (o1 > o0) {
+            double a3[3] = {0, 0, 0};
+            for (int o = o0; o < o1; ++o) {
+                const int c = ctx.pm_cam[o];
+                if (ctx.cam_kind[c] != CAM_FREE) continue;
+                const double *Wo = ctx.W + 18 * (size_t)o;
+                const double *y = ctx.yc + 6 * (size_t)c;
+#pragma unroll
+                for (int a = 0; a < 6; ++a) {
+                    const double ya = y[a];
+                    a3[0] += Wo[a * 3] * ya; a3[1] += Wo[a * 3 + 1] * ya; a3[2] += Wo[a * 3 + 2] * ya;
+                }
+            }
+            const double *Vi = ctx.Vinv + 6 * (size_t)p;
+            const double *b = ctx.bp + 3 * (size_t)p;
+            const double e0 = b[0] - a3[0], e1 = b[1] - a3[1], e2 = b[2] - a3[2];
+            const double y0 = Vi[0] * e0 + Vi[1] * e1 + Vi[2] * e2;
+            const double y1 = Vi[1] * e0 + Vi[3] * e1 + Vi[4] * e2;
+            const double y2 = Vi[2] * e0 + Vi[4] * e1 + Vi[5] * e2;
+            const double *V = ctx.V + 6 * (size_t)p;
+            yb = y0 * b[0] + y1 * b[1] + y2 * b[2];
+            yhy = y0 * (V[0] * y0 + V[1] * y1 + V[2] * y2) + y1 * (V[1] * y0 + V[3] * y1 + V[4] * y2) +
+                  y2 * (V[2] * y0 + V[4] * y1 + V[5] * y2) + 2.0 * (a3[0] * y0 + a3[1] * y1 + a3[2] * y2);
+            const double *sp = ctx.scale_pt + 3 * (size_t)p;
+            const double c0 = X[0] + (-y0) * sp[0], c1 = X[1] + (-y1) * sp[1], c2 = X[2] + (-y2) * sp[2];
+            ptc[3 * (size_t)p] = c0; ptc[3 * (size_t)p + 1] = c1; ptc[3 * (size_t)p + 2] = c2;
+            const double d0 = X[0] - c0, d1 = X[1] - c1, d2 = X[2] - c2;
+            dxsq = d0 * d0 + d1 * d1 + d2 * d2;
+        } else {
+            ptc[3 * (size_t)p] = X[0]; ptc[3 * (size_t)p + 1] = X[1]; ptc[3 * (size_t)p + 2] = X[2];
+        }
+    }
+    dxsq = block_sum(dxsq, red); yb = block_sum(yb, red); yhy = block_sum(yhy, red);
+    if (threadIdx.x == 0) {
+        double *pp = ctx.part + 4 * (size_t)blockIdx.x;
+        pp[0] = dxsq; pp[1] = yb; pp[2] = yhy; pp[3] = 0.0;
+    }
+}
+
+// cameras: candidate = x + (-y_c) * scale, camera-side model-cost pieces, candidate R table.  Single block.
+__global__ void cam_update_kernel(Ctx ctx) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    __shared__ double red[32];
+    const double *x = ctx.cam[st->cur];
+    double *xc = ctx.cam[st->cur ^ 1];
+    double dxsq = 0, yb = 0, yhy = 0;
+    for (int c = threadIdx.x; c < ctx.Nc; c += blockDim.x) {
+        const int kind = ctx.cam_kind[c];
+        CamEntry *ce = ctx.tab_c + c;
+        double cand[6];
+        if (kind == CAM_FREE) {
+            const double *y = ctx.yc + 6 * (size_t)c;
+            const double *U = ctx.U + 36 * (size_t)c;
+            const double *sc = ctx.scale_cam + 6 * (size_t)c;
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                const double xa = x[6 * (size_t)c + a];
+                cand[a] = xa + (-y[a]) * sc[a];
+                const double d = xa - cand[a];
+                dxsq += d * d;
+                yb += y[a] * ctx.bc[6 * (size_t)c + a];
+                double uy = 0;
+#pragma unroll
+                for (int b = 0; b < 6; ++b) uy += U[a * 6 + b] * y[b];
+                yhy += y[a] * uy;
+            }
+        } else {
+#pragma unroll
+            for (int a = 0; a < 6; ++a) cand[a] = x[6 * (size_t)c + a];
+        }
+#pragma unroll
+        for (int a = 0; a < 6; ++a) xc[6 * (size_t)c + a] = cand[a];
+        if (kind == CAM_FREE) {
+            double R[9];
+            rodrigues(cand, R, nullptr);
+#pragma unroll
+            for (int i = 0; i < 9; ++i) ce->R[i] = R[i];
+            ce->t[0] = cand[3]; ce->t[1] = cand[4]; ce->t[2] = cand[5];
+        }
+        // K (and P for fixed cameras) of tab_c were written once at set_problem time
+    }
+    dxsq = block_sum(dxsq, red); yb = block_sum(yb, red); yhy = block_sum(yhy, red);
+    if (threadIdx.x == 0) { ctx.camsums[CS_DXSQ] = dxsq; ctx.camsums[CS_YB] = yb; ctx.camsums[CS_YHY] = yhy; }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// C8 (ii): cost-only evaluation at the candidate, one thread per observation (landmark-major order)
+// -------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *part_out) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    __shared__ double red[32];
+    const double *ptc = ctx.pt[st->cur ^ 1];
+    double cost = 0.0;
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o < ctx.No) {
+        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const double X[3] = {ptc[3 * (size_t)p], ptc[3 * (size_t)p + 1], ptc[3 * (size_t)p + 2]};
+        double r[2];
+        obs_residual(ctx.tab_c + c, ctx.cam_kind[c], X, ctx.pm_uv[o], r);
+        double rho0;
+        huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+        cost = 0.5 * rho0;
+    }
+    cost = block_sum(cost, red);
+    if (threadIdx.x == 0) part_out[blockIdx.x] = cost;
+}
+
+// step partials -> sums (single block)
+__global__ void reduce_step_partials_kernel(Ctx ctx, const double *cost_part, int n_cost_part) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    __shared__ double red[32];
+    double dxsq = 0, yb = 0, yhy = 0, cc = 0;
+    for (int i = threadIdx.x; i < ctx.n_part; i += blockDim.x) {
+        const double *pp = ctx.part + 4 * (size_t)i;
+        dxsq += pp[0]; yb += pp[1]; yhy += pp[2];
+    }
+    for (int i = threadIdx.x; i < n_cost_part; i += blockDim.x) cc += cost_part[i];
+    dxsq = block_sum(dxsq, red); yb = block_sum(yb, red); yhy = block_sum(yhy, red); cc = block_sum(cc, red);
+    if (threadIdx.x == 0) {
+        ctx.sums_loc[SUM_STEP_DXSQ] = dxsq; ctx.sums_loc[SUM_STEP_YB] = yb; ctx.sums_loc[SUM_STEP_YHY] = yhy;
+        ctx.sums_loc[SUM_CAND_COST] = cc;
+    }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// C8/C9 controller, part 1 (single thread): runs after a (re)linearisation.  Fills gradient norms / cost of the
+// iteration that triggered it, records the iteration (FinalizeIterationAndCheckIfMinimizerCanContinue) and opens
+// the next one.
+// -------------------------------------------------------------------------------------------------------------
+__global__ void lm_begin_iteration_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    if (st->done) return;
+    const ba_options &o = ctx.opt;
+    ba_iteration &it = st->it;
+    if (st->need_linearize) {
+        st->x_cost = ctx.sums[SUM_LIN_COST];
+        it.cost = st->x_cost;
+        it.gradient_max_norm = fmax(ctx.maxs[MAX_LIN_G], ctx.camsums[CS_GMAX]);
+        it.gradient_norm = sqrt(ctx.sums[SUM_LIN_GSQ] + ctx.camsums[CS_GSQ]);
+        st->x_norm = sqrt(ctx.sums[SUM_LIN_XSQ] + ctx.camsums[CS_XSQ]);
+        if (it.iteration == 0) {
+            st->initial_cost = st->x_cost;
+            it.step_is_valid = 1;
+            it.step_is_successful = 1;
+        }
+        st->need_linearize = 0;
+        if (!isfinite(st->x_cost)) {
+            st->termination = BA_FAILURE; st->msg = MSG_EVAL_FAILED; st->done = 1; ctx.host_flags[0] = 1;
+            return;
+        }
+    }
+    // ---- FinalizeIterationAndCheckIfMinimizerCanContinue ----
+    if (it.step_is_successful) ++st->num_successful; else ++st->num_unsuccessful;
+    it.trust_region_radius = st->radius;
+    ctx.iters[st->n_recorded++] = it;
+    bool stop = false;
+    if (it.iteration >= o.max_num_iterations) { st->termination = BA_NO_CONVERGENCE; st->msg = MSG_MAX_ITER; stop = true; }
+    else if (it.step_is_successful && it.gradient_max_norm <= o.gradient_tolerance) { st->termination = BA_CONVERGENCE; st->msg = MSG_GRADIENT_TOL; stop = true; }
+    else if (it.trust_region_radius <= o.min_trust_region_radius) { st->termination = BA_CONVERGENCE; st->msg = MSG_MIN_RADIUS; stop = true; }
+    if (stop) { st->done = 1; __threadfence_system(); ctx.host_flags[0] = 1; return; }
+    // ---- open the next iteration ----
+    const double pg = it.gradient_max_norm, pn = it.gradient_norm;
+    const int next = it.iteration + 1;
+    it.iteration = next;
+    it.step_is_valid = 0; it.step_is_successful = 0; it.linear_solver_iterations = 0;
+    it.cost = 0; it.cost_change = 0; it.step_norm = 0; it.relative_decrease = 0; it.trust_region_radius = 0;
+    it.gradient_max_norm = pg; it.gradient_norm = pn;    // carried over unless the step is accepted
+    it.eta = o.eta;
+    st->chol_fail = 0;
+    st->lin_iters = 0;
+}
+
+// controller, part 2 (single thread): step validity, tolerances, rho test, accept/reject, radius update
+__global__ void lm_decide_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    if (st->done) return;
+    const ba_options &o = ctx.opt;
+    ba_iteration &it = st->it;
+    it.linear_solver_iterations = st->lin_iters;
+    const double yb = ctx.sums[SUM_STEP_YB] + ctx.camsums[CS_YB];
+    const double yhy = ctx.sums[SUM_STEP_YHY] + ctx.camsums[CS_YHY];
+    // model_cost_change = -(J s).(r + J s/2) with s = -y  ==  y.b - y^T (J^T J) y / 2
+    const double mcc = yb - 0.5 * yhy;
+    const double dxsq = ctx.sums[SUM_STEP_DXSQ] + ctx.camsums[CS_DXSQ];
+    const bool solver_ok = !st->chol_fail && isfinite(mcc) && isfinite(dxsq);
+    it.step_is_valid = (solver_ok && mcc > 0.0) ? 1 : 0;
+    if (!it.step_is_valid) {
+        // ---- HandleInvalidStep ----
+        if (++st->num_invalid >= o.max_num_consecutive_invalid_steps) {
+            st->termination = BA_FAILURE; st->msg = MSG_INVALID_STEPS; st->done = 1;
+            __threadfence_system(); ctx.host_flags[0] = 1;
+            return;
+        }
+        st->radius = st->radius / st->decrease_factor;      // StepIsInvalid() == StepRejected(0)
+        st->decrease_factor *= 2.0;
+        it.cost = st->x_cost; it.cost_change = 0; it.step_norm = 0; it.relative_decrease = 0;
+        return;
+    }
+    st->num_invalid = 0;
+    double cand_cost = ctx.sums[SUM_CAND_COST];
+    if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
+    // ---- ParameterToleranceReached ----
+    it.step_norm = sqrt(dxsq);
+    if (it.step_norm <= o.parameter_tolerance * (st->x_norm + o.parameter_tolerance)) {
+        st->termination = BA_CONVERGENCE; st->msg = MSG_PARAM_TOL; st->done = 1;
+        __threadfence_system(); ctx.host_flags[0] = 1;
+        return;                                              // step NOT taken, iteration NOT recorded
+    }
+    // ---- FunctionToleranceReached ----
+    it.cost_change = st->x_cost - cand_cost;
+    if (fabs(it.cost_change) <= o.function_tolerance * st->x_cost) {
+        st->termination = BA_CONVERGENCE; st->msg = MSG_FUNCTION_TOL; st->done = 1;
+        __threadfence_system(); ctx.host_flags[0] = 1;
+        return;
+    }
+    // ---- IsStepSuccessful ----
+    it.relative_decrease = (st->x_cost - cand_cost) / mcc;
+    if (it.relative_decrease > o.min_relative_decrease) {
+        // HandleSuccessfulStep: x <- candidate; the re-linearisation runs at the top of the next body
+        st->cur ^= 1;
+        st->need_linearize = 1;
+        it.step_is_successful = 1;
+        const double t = 2.0 * it.relative_decrease - 1.0;
+        st->radius = st->radius / fmax(1.0 / 3.0, 1.0 - t * t * t);
+        st->radius = fmin(o.max_trust_region_radius, st->radius);
+        st->decrease_factor = 2.0;
+    } else {
+        it.step_is_successful = 0;
+        it.cost = cand_cost;
+        st->radius = st->radius / st->decrease_factor;
+        st->decrease_factor *= 2.0;
+    }
+}
+
+__global__ void lm_init_state_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    memset(st, 0, sizeof(LMState));
+    st->need_linearize = 1;
+    st->radius = ctx.opt.initial_trust_region_radius;
+    st->decrease_factor = 2.0;
+    st->it.eta = ctx.opt.eta;
+    ctx.host_flags[0] = 0;
+    ctx.host_flags[1] = 0;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// Materialised evaluation (ba_evaluate): residual + both Jacobian blocks per observation, robustified, unscaled.
+// 176 B / observation of output; this is the "residual+Jacobian obs/sec" kernel.
+// -------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) evaluate_materialize_kernel(Ctx ctx, double *res, double *jc, double *jp, double *cost_part) {
+    __shared__ double red[32];
+    const LMState *st = ctx.state;
+    const double *ptx = ctx.pt[st->cur];
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;
+    double cost = 0.0;
+    if (o < ctx.No) {
+        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const int kind = ctx.cam_kind[c];
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        double r[2], Jc[12], Jp[6];
+        obs_linearize<true, true>(ctx.tab_x + c, kind, X, ctx.pm_uv[o], r, Jc, Jp);
+        double rho0;
+        const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+        const double sr = sqrt(rho1);
+        cost = 0.5 * rho0;
+        double2 *r2 = reinterpret_cast<double2 *>(res) + o;
+        *r2 = make_double2(r[0] * sr, r[1] * sr);
+        double2 *c2 = reinterpret_cast<double2 *>(jc + 12 * (size_t)o);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) c2[k] = make_double2(Jc[2 * k] * sr, Jc[2 * k + 1] * sr);
+        double2 *p2 = reinterpret_cast<double2 *>(jp + 6 * (size_t)o);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) p2[k] = make_double2(Jp[2 * k] * sr, Jp[2 * k + 1] * sr);
+    }
+    cost = block_sum(cost, red);
+    if (threadIdx.x == 0) cost_part[blockIdx.x] = cost;
+}
+
+// =============================================================================================================
+// host-side launchers
+// =============================================================================================================
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+void launch_init_state(const Ctx &ctx, cudaStream_t s) { lm_init_state_kernel<<<1, 1, 0, s>>>(ctx); }
+
+void launch_fill(double *p, size_t n, double v, cudaStream_t s) {
+    if (n == 0) return;
+    fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
+}
+
+void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
+    cam_prep_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx, which, force);
+}
+
+// landmark + camera side of one linearisation (local part; the caller all-reduces U/bc/sums when sharded)
+void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
+    launch_cam_prep(ctx, 0, force, s);
+    linearize_points_kernel<<<ctx.n_part, 128, 0, s>>>(ctx, force);
+    if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx, force);
+    cam_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx, force);
+    reduce_lin_partials_kernel<<<1, 256, 0, s>>>(ctx, force);
+}
+void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s) { cam_norms_kernel<<<1, 256, 0, s>>>(ctx, force); }
+
+void launch_compute_scale(const Ctx &ctx, cudaStream_t s) {
+    const int n = max(6 * ctx.Nc, 3 * ctx.Np);
+    compute_scale_kernel<<<cdiv(n, 256), 256, 0, s>>>(ctx);
+}
+
+void launch_begin_iteration(const Ctx &ctx, cudaStream_t s) { lm_begin_iteration_kernel<<<1, 1, 0, s>>>(ctx); }
+void launch_decide(const Ctx &ctx, cudaStream_t s) { lm_decide_kernel<<<1, 1, 0, s>>>(ctx); }
+
+void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s) {
+    point_invert_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, radius_override);
+}
+
+void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) {
+    const int force = radius_override > 0;
+    cudaMemsetAsync(ctx.S, 0, sizeof(double) * (size_t)ctx.n * ctx.n, s);
+    schur_init_kernel<<<cdiv(6 * ctx.Nc, 128), 128, 0, s>>>(ctx, radius_override);
+    schur_accum_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, force);
+}
+
+void launch_backsub(const Ctx &ctx, cudaStream_t s) {
+    backsub_kernel<<<ctx.n_part, 128, 0, s>>>(ctx);
+    cam_update_kernel<<<1, 256, 0, s>>>(ctx);
+}
+
+void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s) {
+    const int nb = cdiv(ctx.No, 256);
+    eval_candidate_kernel<<<nb, 256, 0, s>>>(ctx, cost_part);
+    reduce_step_partials_kernel<<<1, 256, 0, s>>>(ctx, cost_part, nb);
+}
+
+void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s) {
+    evaluate_materialize_kernel<<<cdiv(ctx.No, 128), 128, 0, s>>>(ctx, res, jc, jp, cost_part);
+}
+
+} // namespace ba

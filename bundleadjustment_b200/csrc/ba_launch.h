@@ -1,0 +1,55 @@
+// ba_launch.h -- host-side launch wrappers of the kernels (internal).
+#pragma once
+
+#include "ba_solver.cuh"
+
+namespace ba {
+
+// ba_kernels.cu
+void launch_init_state(const Ctx &ctx, cudaStream_t s);
+void launch_fill(double *p, size_t n, double v, cudaStream_t s);
+void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s);
+void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s);
+void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s);
+void launch_compute_scale(const Ctx &ctx, cudaStream_t s);
+void launch_begin_iteration(const Ctx &ctx, cudaStream_t s);
+void launch_decide(const Ctx &ctx, cudaStream_t s);
+void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
+void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
+void launch_backsub(const Ctx &ctx, cudaStream_t s);
+void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
+void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s);
+
+// ba_cholesky.cu -- dense SPD factorisation + solve of the reduced camera system (C6)
+struct CholWork {
+    double *invL = nullptr;     // [nblk][NB*NB] inverses of the diagonal blocks
+    int n = 0;
+    size_t bytes() const;
+};
+constexpr int CHOL_NB = 128;
+int chol_init();                                        // one-time kernel attribute setup; returns cudaError
+size_t chol_work_doubles(int n);
+// A: (n+1) x n row-major (ld = n), lower triangle valid, row n = rhs^T.  On exit y (n) holds the solution.
+// state may be nullptr (standalone use); otherwise kernels early-exit on state->done and report breakdown in
+// state->chol_fail.  fail_flag (device int, may be nullptr) is set on breakdown as well.
+void chol_factor_solve(double *A, int n, double *invL, double *y, LMState *state, int *fail_flag, cudaStream_t s);
+
+// ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
+void launch_pcg_setup(const Ctx &ctx, cudaStream_t s);       // local block-diag(S) + rhs (all-reduce Minv, rhs after)
+void launch_pcg_start(const Ctx &ctx, cudaStream_t s);       // invert blocks, x = 0, r = b
+void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s);      // z = M^-1 r, p, local landmark part of q = S p
+void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s);      // q += (U+D^2) p, alpha, x, r   (after all-reduce of q)
+void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s);     // local landmark part of S x into cg_z
+void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s);     // r = b - S x                   (after all-reduce of cg_z)
+void launch_pcg_check(const Ctx &ctx, cudaStream_t s);       // stop rules
+void launch_pcg_finish(const Ctx &ctx, cudaStream_t s);      // copies x -> yc, lin_iters
+
+// ba_pose_batch.cu
+void launch_pose_batch(const ba_options &opt, int B, double *cam, const float *K, const int *prob_ptr,
+                       const float4 *Xh, const float2 *uv, const uint8_t *mask, ba_summary *summaries,
+                       ba_iteration *iters, int iters_cap, cudaStream_t s);
+void launch_prune(int n_frames, const float *pose, const float *extr, const float *K, const int *frame_ptr, const float2 *kp_xy,
+                  const int *kp_octave, const float *pt_xyz, const float *pt_min, const float *pt_max,
+                  const uint8_t *has_point, uint8_t *outlier, int consider_outlier, int n_kp, cudaStream_t s);
+
+} // namespace ba

@@ -1,0 +1,307 @@
+// ba_pcg.cu -- Schur-Jacobi preconditioned conjugate gradients on the IMPLICIT reduced camera system
+// (SURVEY.md 8a C6'; Ceres ITERATIVE_SCHUR + SCHUR_JACOBI).  Not what the reference configures
+// (ba_project/src/ba/Optimizer.cpp:85 selects DENSE_SCHUR) but what BASELINE.json's K5 prescribes: S is never
+// formed, S x = (U + D_c^2) x - sum_p W_p V_p'^-1 (W_p^T x) is applied from the stored W / V'^-1 blocks.
+// The iteration follows ConjugateGradientsSolver::Solve (Ceres 2.0/2.1): q-tolerance stop rule, residual reset
+// every 10 iterations, optional relative-residual stop.
+#include "ba_launch.h"
+
+namespace ba {
+
+__device__ __forceinline__ double lm_diag_pcg(const Ctx &ctx, double jtj, double radius) {
+    return fmin(fmax(jtj, ctx.opt.min_lm_diagonal), ctx.opt.max_lm_diagonal) / radius;
+}
+
+#define CG_GUARD(st) if ((st)->done || (st)->cg_done) return;
+
+// Sd_c = U_c + D_c^2 (into Minv as scratch), rhs = b_c   (replicated part)
+__global__ void pcg_init_blocks_kernel(Ctx ctx) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 6 * ctx.Nc) return;
+    const int c = i / 6, a = i % 6;
+    double *row = ctx.Minv + 36 * (size_t)c + 6 * a;
+    const bool lead = ctx.rank == 0;
+    if (ctx.cam_kind[c] == CAM_FREE) {
+        const double *U = ctx.U + 36 * (size_t)c;
+#pragma unroll
+        for (int b = 0; b < 6; ++b) row[b] = lead ? U[a * 6 + b] + (a == b ? lm_diag_pcg(ctx, U[a * 6 + a], st->radius) : 0.0) : 0.0;
+        ctx.rhs[i] = lead ? ctx.bc[i] : 0.0;
+    } else {
+#pragma unroll
+        for (int b = 0; b < 6; ++b) row[b] = (lead && a == b) ? 1.0 : 0.0;
+        ctx.rhs[i] = 0.0;
+    }
+}
+
+// landmark contributions to block-diag(S) and rhs
+__global__ void __launch_bounds__(128) pcg_setup_points_kernel(Ctx ctx) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ctx.Np) return;
+    const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
+    if (o1 <= o0) return;
+    const double *Vi = ctx.Vinv + 6 * (size_t)p;
+    const double vi[6] = {Vi[0], Vi[1], Vi[2], Vi[3], Vi[4], Vi[5]};
+    const double *wv = ctx.wv + 3 * (size_t)p;
+    const double w3[3] = {wv[0], wv[1], wv[2]};
+    for (int i = o0; i < o1; ++i) {
+        const int c = ctx.pm_cam[i];
+        if (ctx.cam_kind[c] != CAM_FREE) continue;
+        const double *Wi = ctx.W + 18 * (size_t)i;
+        double w[18], Y[18];
+#pragma unroll
+        for (int k = 0; k < 18; ++k) w[k] = Wi[k];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            Y[a * 3 + 0] = w[a * 3] * vi[0] + w[a * 3 + 1] * vi[1] + w[a * 3 + 2] * vi[2];
+            Y[a * 3 + 1] = w[a * 3] * vi[1] + w[a * 3 + 1] * vi[3] + w[a * 3 + 2] * vi[4];
+            Y[a * 3 + 2] = w[a * 3] * vi[2] + w[a * 3 + 1] * vi[4] + w[a * 3 + 2] * vi[5];
+            atomicAdd(ctx.rhs + 6 * (size_t)c + a, -(w[a * 3] * w3[0] + w[a * 3 + 1] * w3[1] + w[a * 3 + 2] * w3[2]));
+        }
+        double *dst = ctx.Minv + 36 * (size_t)c;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = 0; b < 6; ++b)
+                atomicAdd(dst + a * 6 + b, -(Y[a * 3] * w[b * 3] + Y[a * 3 + 1] * w[b * 3 + 1] + Y[a * 3 + 2] * w[b * 3 + 2]));
+    }
+}
+
+// invert the 6x6 diagonal blocks in place; start CG: x = 0, r = b
+__global__ void pcg_start_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    if (st->done) return;
+    __shared__ double red[32];
+    double nb = 0.0;
+    int bad = 0;
+    for (int c = threadIdx.x; c < ctx.Nc; c += blockDim.x) {
+        double *M = ctx.Minv + 36 * (size_t)c;
+        double A[36], inv[36];
+#pragma unroll
+        for (int k = 0; k < 36; ++k) A[k] = M[k];
+        if (!inv_spd6(A, inv)) {
+            bad = 1;
+#pragma unroll
+            for (int k = 0; k < 36; ++k) inv[k] = 0.0;
+        }
+#pragma unroll
+        for (int k = 0; k < 36; ++k) M[k] = inv[k];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            const double b = ctx.rhs[6 * (size_t)c + a];
+            ctx.cg_x[6 * (size_t)c + a] = 0.0;
+            ctx.cg_r[6 * (size_t)c + a] = b;
+            nb += b * b;
+        }
+    }
+    nb = block_sum(nb, red);
+    bad = __syncthreads_or(bad);
+    if (threadIdx.x == 0) {
+        st->cg_norm_b = sqrt(nb);
+        st->cg_rho = 1.0; st->cg_last_rho = 1.0; st->cg_Q0 = 0.0; st->cg_iter = 0; st->cg_done = 0;
+        if (bad || !isfinite(nb)) { st->chol_fail = 1; st->cg_done = 1; }
+        // |r| <= r_tolerance * |b| at x = 0 (only when the relative-residual rule is enabled)
+        if (ctx.opt.cg_r_tolerance > 0 && sqrt(nb) <= ctx.opt.cg_r_tolerance * sqrt(nb)) st->cg_done = 1;
+        ctx.host_flags[1] = st->cg_done;
+    }
+}
+
+// z = M^-1 r ; rho = r.z ; p = z + beta p.   Single CTA (n <= ~80k).
+__global__ void __launch_bounds__(1024) pcg_precond_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    CG_GUARD(st);
+    __shared__ double red[32];
+    __shared__ double s_beta;
+    __shared__ int s_stop;
+    double rho = 0.0;
+    for (int c = threadIdx.x; c < ctx.Nc; c += blockDim.x) {
+        const double *M = ctx.Minv + 36 * (size_t)c;
+        double r[6];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) r[a] = ctx.cg_r[6 * (size_t)c + a];
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            double z = 0.0;
+#pragma unroll
+            for (int b = 0; b < 6; ++b) z += M[a * 6 + b] * r[b];
+            ctx.cg_z[6 * (size_t)c + a] = z;
+            rho += r[a] * z;
+        }
+    }
+    rho = block_sum(rho, red);
+    if (threadIdx.x == 0) {
+        const int it = st->cg_iter + 1;
+        st->cg_iter = it;
+        st->cg_last_rho = st->cg_rho;
+        st->cg_rho = rho;
+        s_stop = 0;
+        s_beta = 0.0;
+        if (rho == 0.0 || !isfinite(rho)) { s_stop = 1; }
+        else if (it > 1) {
+            s_beta = rho / st->cg_last_rho;
+            if (s_beta == 0.0 || !isfinite(s_beta)) s_stop = 1;
+        }
+        if (s_stop) { st->chol_fail = 1; st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+    }
+    __syncthreads();
+    if (s_stop) return;
+    const double beta = s_beta;
+    const bool first = st->cg_iter == 1;
+    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+        const double z = ctx.cg_z[i];
+        ctx.cg_p[i] = first ? z : z + beta * ctx.cg_p[i];
+        ctx.cg_q[i] = 0.0;
+    }
+}
+
+// q -= sum_p W_p V'^-1 W_p^T v   (landmark-major; v = p or x)
+__global__ void __launch_bounds__(128) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ q) {
+    const LMState *st = ctx.state;
+    CG_GUARD(st);
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ctx.Np) return;
+    const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
+    if (o1 <= o0) return;
+    double a3[3] = {0, 0, 0};
+    for (int o = o0; o < o1; ++o) {
+        const int c = ctx.pm_cam[o];
+        if (ctx.cam_kind[c] != CAM_FREE) continue;
+        const double *Wo = ctx.W + 18 * (size_t)o;
+        const double *x = v + 6 * (size_t)c;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) {
+            const double xa = x[a];
+            a3[0] += Wo[a * 3] * xa; a3[1] += Wo[a * 3 + 1] * xa; a3[2] += Wo[a * 3 + 2] * xa;
+        }
+    }
+    const double *Vi = ctx.Vinv + 6 * (size_t)p;
+    const double t0 = Vi[0] * a3[0] + Vi[1] * a3[1] + Vi[2] * a3[2];
+    const double t1 = Vi[1] * a3[0] + Vi[3] * a3[1] + Vi[4] * a3[2];
+    const double t2 = Vi[2] * a3[0] + Vi[4] * a3[1] + Vi[5] * a3[2];
+    for (int o = o0; o < o1; ++o) {
+        const int c = ctx.pm_cam[o];
+        if (ctx.cam_kind[c] != CAM_FREE) continue;
+        const double *Wo = ctx.W + 18 * (size_t)o;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+            atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
+    }
+}
+
+// out[i] = in[i] + ((U + D^2) v)[i]  helper (per camera row)
+__device__ __forceinline__ double cam_block_row(const Ctx &ctx, const LMState *st, int c, int a, const double *v) {
+    if (ctx.cam_kind[c] != CAM_FREE) return v[6 * (size_t)c + a];
+    const double *U = ctx.U + 36 * (size_t)c;
+    double s = 0.0;
+#pragma unroll
+    for (int b = 0; b < 6; ++b) s += U[a * 6 + b] * v[6 * (size_t)c + b];
+    s += lm_diag_pcg(ctx, U[a * 6 + a], st->radius) * v[6 * (size_t)c + a];
+    return s;
+}
+
+// q += (U + D^2) p ; alpha = rho / p.q ; x += alpha p ; r -= alpha q ; stop rules.   Single CTA.
+__global__ void __launch_bounds__(1024) pcg_update_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    CG_GUARD(st);
+    __shared__ double red[32];
+    __shared__ double s_alpha;
+    __shared__ int s_stop;
+    double pq = 0.0;
+    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+        const double q = ctx.cg_q[i] + cam_block_row(ctx, st, i / 6, i % 6, ctx.cg_p);
+        ctx.cg_q[i] = q;
+        pq += ctx.cg_p[i] * q;
+    }
+    pq = block_sum(pq, red);
+    if (threadIdx.x == 0) {
+        s_stop = 0;
+        s_alpha = 0.0;
+        if (pq <= 0.0 || isinf(pq) || isnan(pq)) {
+            // "Matrix is indefinite, no more progress can be made": keep the current x
+            s_stop = 1;
+        } else {
+            s_alpha = st->cg_rho / pq;
+            if (isinf(s_alpha)) { s_stop = 1; st->chol_fail = 1; }
+        }
+        if (s_stop) { st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+    }
+    __syncthreads();
+    if (s_stop) return;
+    const double alpha = s_alpha;
+    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+        ctx.cg_x[i] += alpha * ctx.cg_p[i];
+        ctx.cg_r[i] -= alpha * ctx.cg_q[i];
+    }
+}
+
+// residual reset: r = b - (q + (U + D^2) x), with q holding the landmark part of S x.   Single CTA.
+__global__ void __launch_bounds__(1024) pcg_residual_reset_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    CG_GUARD(st);
+    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+        const double ax = ctx.cg_z[i] + cam_block_row(ctx, st, i / 6, i % 6, ctx.cg_x);
+        ctx.cg_r[i] = ctx.rhs[i] - ax;
+    }
+}
+
+// Q1 = -x.(b + r); zeta = it (Q1 - Q0) / Q1 < eta -> stop; |r| <= r_tol |b| -> stop; it >= max -> stop
+__global__ void __launch_bounds__(1024) pcg_check_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    CG_GUARD(st);
+    __shared__ double red[32];
+    double s = 0.0, rr = 0.0;
+    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+        const double r = ctx.cg_r[i];
+        s += ctx.cg_x[i] * (ctx.rhs[i] + r);
+        rr += r * r;
+    }
+    s = block_sum(s, red);
+    rr = block_sum(rr, red);
+    if (threadIdx.x == 0) {
+        const int it = st->cg_iter;
+        const double Q1 = -1.0 * s;
+        const double zeta = it * (Q1 - st->cg_Q0) / Q1;
+        bool stop = false;
+        if (zeta < ctx.opt.eta) stop = true;
+        st->cg_Q0 = Q1;
+        if (!stop && ctx.opt.cg_r_tolerance > 0 && sqrt(rr) <= ctx.opt.cg_r_tolerance * st->cg_norm_b) stop = true;
+        if (!stop && it >= ctx.opt.max_linear_solver_iterations) stop = true;
+        if (stop) { st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+    }
+}
+
+__global__ void pcg_finish_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    if (st->done) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < ctx.n) ctx.yc[i] = (ctx.cam_kind[i / 6] == CAM_FREE) ? ctx.cg_x[i] : 0.0;
+    if (i == 0) st->lin_iters = st->cg_iter;
+}
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// local part of the setup; the caller all-reduces Minv (36 Nc) and rhs (6 Nc) when sharded, then calls
+// launch_pcg_iteration repeatedly (first call starts CG).
+void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
+    pcg_init_blocks_kernel<<<cdiv(6 * ctx.Nc, 128), 128, 0, s>>>(ctx);
+    pcg_setup_points_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx);
+}
+void launch_pcg_start(const Ctx &ctx, cudaStream_t s) { pcg_start_kernel<<<1, 256, 0, s>>>(ctx); }
+
+void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s) {      // precondition + direction + local matvec
+    pcg_precond_kernel<<<1, 1024, 0, s>>>(ctx);
+    pcg_matvec_points_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, ctx.cg_p, ctx.cg_q);
+}
+void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) { pcg_update_kernel<<<1, 1024, 0, s>>>(ctx); }
+void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part of S x into cg_z
+    cudaMemsetAsync(ctx.cg_z, 0, sizeof(double) * ctx.n, s);
+    pcg_matvec_points_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, ctx.cg_x, ctx.cg_z);
+}
+void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<1, 1024, 0, s>>>(ctx); }
+void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<1, 1024, 0, s>>>(ctx); }
+void launch_pcg_finish(const Ctx &ctx, cudaStream_t s) { pcg_finish_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
+
+} // namespace ba

@@ -1,0 +1,326 @@
+// ba_pose_batch.cu -- batched frame-to-frame "BA" pose estimation and correspondence pruning.
+//
+// Replaces, per problem, one ceres::Solve of MotionOnlyBAOptimizerAngles::optimizeCameraPose
+// (ba_project/src/ba/Optimizer.cpp:417-498: PoseOnlyAngleReprojectionError<2,6> blocks with HuberLoss on ONE 6-dof
+// parameter block) and BAOptimizer::pruneCorrespondences (Optimizer.cpp:6-79).  With a single parameter block
+// Ceres' Schur ordering eliminates it as the only e-block, i.e. each LM step is the damped 6x6 normal-equation
+// solve ("degenerate case for R3/K3").  One CTA per problem runs the WHOLE trust-region loop.
+#include "ba_launch.h"
+
+namespace ba {
+
+constexpr int PB_THREADS = 128;
+
+struct PoseShared {
+    CamEntry ce;              // R, dR, t, K at the point being evaluated
+    double x[6], cand[6], scale[6];
+    double H[36];             // J^T J (unscaled, robustified)
+    double g[6];              // J^T r (unscaled)
+    double red[4][28];
+    double cost, cand_cost, x_cost, x_norm, radius, decrease_factor, mcc, dxsq;
+    int need_linearize, done, num_invalid, n_recorded, termination, msg, num_successful, num_unsuccessful, solver_fail;
+    double initial_cost;
+    ba_iteration it;
+};
+
+// residual (+ 2x6 Jacobian) of PoseOnlyAngleReprojectionError: p = [R t] * Xh
+template <bool WANT_J>
+__device__ __forceinline__ void pose_obs(const CamEntry &ce, float4 Xh, float2 uv, double r[2], double Jc[12]) {
+    const double X[3] = {(double)Xh.x, (double)Xh.y, (double)Xh.z};
+    const double w = (double)Xh.w;
+    double p[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) p[i] = ce.R[i] * X[0] + ce.R[i + 3] * X[1] + ce.R[i + 6] * X[2] + ce.t[i] * w;
+    double pix[2], G[6];
+    project(ce.K, p, pix, G, WANT_J);
+    r[0] = pix[0] - (double)uv.x;
+    r[1] = pix[1] - (double)uv.y;
+    if (WANT_J) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            const double *D = ce.dR + 9 * j;
+            double d[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) d[i] = D[i] * X[0] + D[i + 3] * X[1] + D[i + 6] * X[2];
+            Jc[j] = G[0] * d[0] + G[1] * d[1] + G[2] * d[2];
+            Jc[6 + j] = G[3] * d[0] + G[4] * d[1] + G[5] * d[2];
+        }
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { Jc[3 + j] = G[j] * w; Jc[9 + j] = G[3 + j] * w; }
+    }
+}
+
+__device__ __forceinline__ void pose_set_cam(PoseShared &S, const double *x, bool derivs) {
+    if (threadIdx.x == 0) {
+        double R[9], dR[27];
+        rodrigues(x, R, derivs ? dR : nullptr);
+        for (int i = 0; i < 9; ++i) S.ce.R[i] = R[i];
+        if (derivs) for (int i = 0; i < 27; ++i) S.ce.dR[i] = dR[i];
+        S.ce.t[0] = x[3]; S.ce.t[1] = x[4]; S.ce.t[2] = x[5];
+    }
+    __syncthreads();
+}
+
+// block reduction of NV values per thread into S.red -> result in S.red[0][*] visible to all after return
+template <int NV>
+__device__ __forceinline__ void pose_reduce(PoseShared &S, double *v) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) v[k] = warp_sum(v[k]);
+    __syncthreads();
+    if (lane == 0)
+        for (int k = 0; k < NV; ++k) S.red[wid][k] = v[k];
+    __syncthreads();
+    if (threadIdx.x < NV) S.red[0][threadIdx.x] = S.red[0][threadIdx.x] + S.red[1][threadIdx.x] + S.red[2][threadIdx.x] + S.red[3][threadIdx.x];
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(PB_THREADS)
+pose_batch_kernel(ba_options opt, int B, double *__restrict__ cam, const float *__restrict__ K, const int *__restrict__ prob_ptr,
+                  const float4 *__restrict__ Xh, const float2 *__restrict__ uv, const uint8_t *__restrict__ mask,
+                  ba_summary *__restrict__ summaries, ba_iteration *__restrict__ iters, int iters_cap) {
+    __shared__ PoseShared S;
+    const int b = blockIdx.x;
+    if (b >= B) return;
+    const int o0 = prob_ptr[b], o1 = prob_ptr[b + 1];
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        for (int k = 0; k < 6; ++k) { S.x[k] = cam[6 * (size_t)b + k]; S.scale[k] = 1.0; }
+        for (int k = 0; k < 9; ++k) S.ce.K[k] = (double)K[9 * (size_t)b + k];
+        S.radius = opt.initial_trust_region_radius; S.decrease_factor = 2.0;
+        S.need_linearize = 1; S.done = 0; S.num_invalid = 0; S.n_recorded = 0; S.termination = BA_NO_CONVERGENCE; S.msg = MSG_NONE;
+        S.num_successful = 0; S.num_unsuccessful = 0; S.initial_cost = 0;
+        memset(&S.it, 0, sizeof(S.it));
+        S.it.eta = opt.eta;
+    }
+    __syncthreads();
+    ba_iteration *my_iters = iters ? iters + (size_t)b * iters_cap : nullptr;
+
+    for (;;) {
+        // ---------------- (re)linearise at x ----------------
+        if (S.need_linearize) {
+            pose_set_cam(S, S.x, true);
+            double v[28];
+#pragma unroll
+            for (int k = 0; k < 28; ++k) v[k] = 0.0;
+            for (int o = o0 + tid; o < o1; o += PB_THREADS) {
+                if (mask && !mask[o]) continue;
+                double r[2], Jc[12];
+                pose_obs<true>(S.ce, Xh[o], uv[o], r, Jc);
+                double rho0;
+                const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], opt.huber_delta, opt.use_huber, rho0);
+                const double sr = sqrt(rho1);
+                r[0] *= sr; r[1] *= sr;
+#pragma unroll
+                for (int a = 0; a < 12; ++a) Jc[a] *= sr;
+                int k = 0;
+#pragma unroll
+                for (int a = 0; a < 6; ++a)
+#pragma unroll
+                    for (int c = a; c < 6; ++c) v[k++] += Jc[a] * Jc[c] + Jc[6 + a] * Jc[6 + c];
+#pragma unroll
+                for (int a = 0; a < 6; ++a) v[21 + a] += Jc[a] * r[0] + Jc[6 + a] * r[1];
+                v[27] += 0.5 * rho0;
+            }
+            pose_reduce<28>(S, v);
+            if (tid == 0) {
+                int k = 0;
+                for (int a = 0; a < 6; ++a)
+                    for (int c = a; c < 6; ++c) { S.H[a * 6 + c] = S.red[0][k]; S.H[c * 6 + a] = S.red[0][k]; ++k; }
+                for (int a = 0; a < 6; ++a) S.g[a] = S.red[0][21 + a];
+                S.x_cost = S.red[0][27];
+            }
+            __syncthreads();
+        }
+        // ---------------- controller part 1 + linear solve (thread 0) ----------------
+        if (tid == 0) {
+            ba_iteration &it = S.it;
+            if (S.need_linearize) {
+                it.cost = S.x_cost;
+                if (it.iteration == 0) {
+                    S.initial_cost = S.x_cost;
+                    it.step_is_valid = 1; it.step_is_successful = 1;
+                    if (opt.jacobi_scaling)
+                        for (int a = 0; a < 6; ++a) S.scale[a] = 1.0 / (1.0 + sqrt(S.H[a * 6 + a]));
+                }
+                double gm = 0, gs = 0, xs = 0;
+                for (int a = 0; a < 6; ++a) {
+                    const double d = S.x[a] - (S.x[a] + (-S.g[a]));
+                    gm = fmax(gm, fabs(d)); gs += d * d; xs += S.x[a] * S.x[a];
+                }
+                it.gradient_max_norm = gm; it.gradient_norm = sqrt(gs); S.x_norm = sqrt(xs);
+                S.need_linearize = 0;
+                if (!isfinite(S.x_cost)) { S.termination = BA_FAILURE; S.msg = MSG_EVAL_FAILED; S.done = 1; }
+            }
+            if (!S.done) {
+                if (it.step_is_successful) ++S.num_successful; else ++S.num_unsuccessful;
+                it.trust_region_radius = S.radius;
+                if (my_iters && S.n_recorded < iters_cap) my_iters[S.n_recorded] = it;
+                ++S.n_recorded;
+                if (it.iteration >= opt.max_num_iterations) { S.termination = BA_NO_CONVERGENCE; S.msg = MSG_MAX_ITER; S.done = 1; }
+                else if (it.step_is_successful && it.gradient_max_norm <= opt.gradient_tolerance) { S.termination = BA_CONVERGENCE; S.msg = MSG_GRADIENT_TOL; S.done = 1; }
+                else if (it.trust_region_radius <= opt.min_trust_region_radius) { S.termination = BA_CONVERGENCE; S.msg = MSG_MIN_RADIUS; S.done = 1; }
+            }
+            if (!S.done) {
+                const double pg = it.gradient_max_norm, pn = it.gradient_norm;
+                const int next = it.iteration + 1;
+                memset(&it, 0, sizeof(it));
+                it.iteration = next; it.gradient_max_norm = pg; it.gradient_norm = pn; it.eta = opt.eta;
+                it.linear_solver_iterations = 1;
+                // (J_s^T J_s + D^2) y = J_s^T r in the Jacobi-scaled space
+                double A[36], bs[6], inv[36], y[6];
+                for (int a = 0; a < 6; ++a) {
+                    for (int c = 0; c < 6; ++c) A[a * 6 + c] = S.H[a * 6 + c] * S.scale[a] * S.scale[c];
+                    bs[a] = S.g[a] * S.scale[a];
+                }
+                double Hs_y = 0;
+                for (int a = 0; a < 6; ++a) {
+                    const double d = fmin(fmax(A[a * 6 + a], opt.min_lm_diagonal), opt.max_lm_diagonal) / S.radius;
+                    inv[a] = d;   // stash
+                }
+                double Ad[36];
+                for (int k = 0; k < 36; ++k) Ad[k] = A[k];
+                for (int a = 0; a < 6; ++a) Ad[a * 6 + a] += inv[a];
+                S.solver_fail = inv_spd6(Ad, inv) ? 0 : 1;
+                double yb = 0;
+                if (!S.solver_fail) {
+                    for (int a = 0; a < 6; ++a) { double s = 0; for (int c = 0; c < 6; ++c) s += inv[a * 6 + c] * bs[c]; y[a] = s; if (!isfinite(s)) S.solver_fail = 1; }
+                }
+                if (!S.solver_fail) {
+                    for (int a = 0; a < 6; ++a) { double s = 0; for (int c = 0; c < 6; ++c) s += A[a * 6 + c] * y[c]; Hs_y += y[a] * s; yb += y[a] * bs[a]; }
+                    S.mcc = yb - 0.5 * Hs_y;
+                    double dx = 0;
+                    for (int a = 0; a < 6; ++a) { S.cand[a] = S.x[a] + (-y[a]) * S.scale[a]; const double d = S.x[a] - S.cand[a]; dx += d * d; }
+                    S.dxsq = dx;
+                } else {
+                    S.mcc = -1.0;
+                    for (int a = 0; a < 6; ++a) S.cand[a] = S.x[a];
+                }
+            }
+        }
+        __syncthreads();
+        if (S.done) break;
+        // ---------------- candidate cost ----------------
+        pose_set_cam(S, S.cand, false);
+        {
+            double c1[1] = {0.0};
+            for (int o = o0 + tid; o < o1; o += PB_THREADS) {
+                if (mask && !mask[o]) continue;
+                double r[2];
+                pose_obs<false>(S.ce, Xh[o], uv[o], r, nullptr);
+                double rho0;
+                huber_rho(r[0] * r[0] + r[1] * r[1], opt.huber_delta, opt.use_huber, rho0);
+                c1[0] += 0.5 * rho0;
+            }
+            pose_reduce<1>(S, c1);
+        }
+        // ---------------- controller part 2 (thread 0) ----------------
+        if (tid == 0) {
+            ba_iteration &it = S.it;
+            double cand_cost = S.red[0][0];
+            it.step_is_valid = (!S.solver_fail && isfinite(S.mcc) && S.mcc > 0.0) ? 1 : 0;
+            if (!it.step_is_valid) {
+                if (++S.num_invalid >= opt.max_num_consecutive_invalid_steps) { S.termination = BA_FAILURE; S.msg = MSG_INVALID_STEPS; S.done = 1; }
+                else {
+                    S.radius /= S.decrease_factor; S.decrease_factor *= 2.0;
+                    it.cost = S.x_cost; it.cost_change = 0; it.step_norm = 0; it.relative_decrease = 0;
+                }
+            } else {
+                S.num_invalid = 0;
+                if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
+                it.step_norm = sqrt(S.dxsq);
+                if (it.step_norm <= opt.parameter_tolerance * (S.x_norm + opt.parameter_tolerance)) { S.termination = BA_CONVERGENCE; S.msg = MSG_PARAM_TOL; S.done = 1; }
+                else {
+                    it.cost_change = S.x_cost - cand_cost;
+                    if (fabs(it.cost_change) <= opt.function_tolerance * S.x_cost) { S.termination = BA_CONVERGENCE; S.msg = MSG_FUNCTION_TOL; S.done = 1; }
+                    else {
+                        it.relative_decrease = (S.x_cost - cand_cost) / S.mcc;
+                        if (it.relative_decrease > opt.min_relative_decrease) {
+                            for (int a = 0; a < 6; ++a) S.x[a] = S.cand[a];
+                            S.need_linearize = 1;
+                            it.step_is_successful = 1;
+                            const double t = 2.0 * it.relative_decrease - 1.0;
+                            S.radius = fmin(opt.max_trust_region_radius, S.radius / fmax(1.0 / 3.0, 1.0 - t * t * t));
+                            S.decrease_factor = 2.0;
+                        } else {
+                            it.step_is_successful = 0;
+                            it.cost = cand_cost;
+                            S.radius /= S.decrease_factor; S.decrease_factor *= 2.0;
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (S.done) break;
+    }
+    if (tid == 0) {
+        for (int k = 0; k < 6; ++k) cam[6 * (size_t)b + k] = S.x[k];
+        if (summaries) {
+            ba_summary sm;
+            memset(&sm, 0, sizeof(sm));
+            sm.termination_type = S.termination;
+            sm.num_iterations = S.n_recorded;
+            sm.num_successful_steps = S.num_successful;
+            sm.num_unsuccessful_steps = S.num_unsuccessful;
+            sm.initial_cost = S.initial_cost;
+            sm.final_cost = S.x_cost;       // refined on the host from the iteration list when it is kept
+            sm.message[0] = (char)S.msg;    // message code; expanded on the host
+            summaries[b] = sm;
+        }
+    }
+}
+
+// pruneCorrespondences, one thread per keypoint, float32 arithmetic as in the reference
+__global__ void prune_kernel(int n_frames, const float *__restrict__ pose, const float *__restrict__ K, const int *__restrict__ frame_ptr,
+                             const float2 *__restrict__ kp_xy, const int *__restrict__ kp_octave, const float *__restrict__ pt_xyz,
+                             const float *__restrict__ pt_min, const float *__restrict__ pt_max, const uint8_t *__restrict__ has_point,
+                             uint8_t *__restrict__ outlier, int consider_outlier, int n_kp, const float *__restrict__ extr) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_kp) return;
+    if (!(consider_outlier || !outlier[i])) return;
+    if (!has_point[i]) return;
+    int lo = 0, hi = n_frames;                 // frame f with frame_ptr[f] <= i < frame_ptr[f+1]
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (frame_ptr[mid] <= i) lo = mid; else hi = mid; }
+    const int f = lo;
+    const float *E = extr + 16 * (size_t)f;
+    const float *P = pose + 16 * (size_t)f;
+    const float *Kf = K + 9 * (size_t)f;
+    const float chiThresh = 5.991f;
+    const float invSigmaP = (float)(1.0 / pow(1.2, (double)kp_octave[i]));
+    const float X0 = pt_xyz[3 * (size_t)i], X1 = pt_xyz[3 * (size_t)i + 1], X2 = pt_xyz[3 * (size_t)i + 2];
+    float ph[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) ph[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(E[r * 4 + 0], X0), __fmul_rn(E[r * 4 + 1], X1)), __fmul_rn(E[r * 4 + 2], X2)), __fmul_rn(E[r * 4 + 3], 1.0f));
+    const float c0 = __fdiv_rn(ph[0], ph[3]), c1 = __fdiv_rn(ph[1], ph[3]), c2 = __fdiv_rn(ph[2], ph[3]);
+    if (c2 <= 0) { outlier[i] = 1; return; }
+    const float dx = __fsub_rn(X0, P[3]), dy = __fsub_rn(X1, P[7]), dz = __fsub_rn(X2, P[11]);
+    const float worldDist = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+    if (worldDist > pt_max[i] || worldDist < pt_min[i]) { outlier[i] = 1; return; }
+    float q[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) q[r] = __fadd_rn(__fadd_rn(__fmul_rn(Kf[r * 3 + 0], c0), __fmul_rn(Kf[r * 3 + 1], c1)), __fmul_rn(Kf[r * 3 + 2], c2));
+    const float px = __fdiv_rn(q[0], q[2]), py = __fdiv_rn(q[1], q[2]);
+    const float ex = __fsub_rn(px, kp_xy[i].x), ey = __fsub_rn(py, kp_xy[i].y);
+    const float dist = __fsqrt_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)));
+    const float chi = __fmul_rn(dist, invSigmaP);
+    if (chi > chiThresh) { outlier[i] = 1; return; }
+    outlier[i] = 0;
+}
+
+void launch_pose_batch(const ba_options &opt, int B, double *cam, const float *K, const int *prob_ptr,
+                       const float4 *Xh, const float2 *uv, const uint8_t *mask, ba_summary *summaries,
+                       ba_iteration *iters, int iters_cap, cudaStream_t s) {
+    if (B <= 0) return;
+    pose_batch_kernel<<<B, PB_THREADS, 0, s>>>(opt, B, cam, K, prob_ptr, Xh, uv, mask, summaries, iters, iters_cap);
+}
+
+void launch_prune(int n_frames, const float *pose, const float *extr, const float *K, const int *frame_ptr, const float2 *kp_xy,
+                  const int *kp_octave, const float *pt_xyz, const float *pt_min, const float *pt_max,
+                  const uint8_t *has_point, uint8_t *outlier, int consider_outlier, int n_kp, cudaStream_t s) {
+    if (n_kp <= 0) return;
+    prune_kernel<<<(n_kp + 255) / 256, 256, 0, s>>>(n_frames, pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max,
+                                                  has_point, outlier, consider_outlier, n_kp, extr);
+}
+
+} // namespace ba

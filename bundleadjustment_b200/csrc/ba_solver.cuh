@@ -1,0 +1,120 @@
+// ba_solver.cuh -- device-resident state of one BA problem / LM solve (internal; the public surface is
+// include/ba_b200.h).
+#pragma once
+
+#include "ba_device.cuh"
+#include "../../include/ba_b200.h"
+
+namespace ba {
+
+// message codes (mapped to Ceres' wording on the host)
+enum : int {
+    MSG_NONE = 0, MSG_MAX_ITER, MSG_GRADIENT_TOL, MSG_MIN_RADIUS, MSG_PARAM_TOL, MSG_FUNCTION_TOL,
+    MSG_INVALID_STEPS, MSG_EVAL_FAILED
+};
+
+// slots of the all-reduced (sum) scalar vector
+enum : int {
+    SUM_LIN_COST = 0,   // cost at x (from the linearisation pass)
+    SUM_LIN_GSQ,        // sum over landmark params of (x - (x - g))^2
+    SUM_LIN_XSQ,        // sum over active landmark params of x^2
+    SUM_STEP_DXSQ,      // sum over landmark params of (x - cand)^2
+    SUM_STEP_YB,        // y_p . b_p
+    SUM_STEP_YHY,       // y_p^T V_p y_p + 2 a_p . y_p
+    SUM_CAND_COST,      // cost at the candidate
+    SUM_COUNT = 8
+};
+constexpr int SUM_LIN_BEGIN = 0, SUM_LIN_N = 3, SUM_STEP_BEGIN = 3, SUM_STEP_N = 4;
+// slots of the all-reduced (max) scalar vector
+enum : int { MAX_LIN_G = 0, MAX_COUNT = 2 };
+// camera-side scalars (replicated, never all-reduced)
+enum : int { CS_GSQ = 0, CS_GMAX, CS_XSQ, CS_DXSQ, CS_YB, CS_YHY, CS_COUNT = 8 };
+
+// Trust-region state (trust_region_minimizer.cc + levenberg_marquardt_strategy.cc), lives in device memory;
+// a copy of `done` is mirrored to mapped host memory so the host can stop enqueueing iterations.
+struct LMState {
+    int done;
+    int need_linearize;
+    int cur;                 // which of the two parameter buffers holds x
+    int num_invalid;
+    int termination;
+    int msg;
+    int chol_fail;           // set by the dense factorisation / PCG on breakdown
+    int lin_iters;
+    int num_successful;
+    int num_unsuccessful;
+    int n_recorded;
+    int cg_done;             // PCG loop control
+    int cg_iter;
+    int pad;
+    double radius;
+    double decrease_factor;
+    double x_cost;
+    double x_norm;
+    double initial_cost;
+    // PCG scalars
+    double cg_rho, cg_last_rho, cg_alpha, cg_pq, cg_Q0, cg_norm_b;
+    ba_iteration it;         // summary being filled for the current iteration
+};
+
+struct Ctx {
+    // sizes
+    int Nc, Np, No, n;       // n = 6*Nc (reduced system order; inactive cameras are identity rows)
+    int n_chunks;
+    int rank, n_ranks;
+    // options
+    ba_options opt;
+    // parameters: two buffers each, state->cur selects x, the other is the candidate
+    double *cam[2];          // [Nc][6]
+    double *pt[2];           // [Np][3]
+    double *cam_init, *pt_init;
+    // constants
+    const int *cam_kind;     // [Nc] CAM_FREE / CAM_FIXED / CAM_INACTIVE
+    const float *cam_K;      // [Nc][9]
+    const float *cam_extr;   // [Nc][16]
+    // landmark-major observations (sorted by landmark, then camera)
+    const float2 *pm_uv;
+    const int *pm_cam;
+    const int *pm_pt;
+    const int *pt_ptr;       // [Np+1]
+    // camera-major copy
+    const float2 *cm_uv;
+    const int *cm_pt;
+    const int *chunk_cam, *chunk_beg, *chunk_end;   // [n_chunks] work units of <= CHUNK observations
+    const int *cam_chunk_ptr;                       // [Nc+1] chunk range per camera
+    // per-camera tables at x and at the candidate
+    CamEntry *tab_x, *tab_c;
+    // Jacobi scaling
+    double *scale_cam, *scale_pt;
+    // normal-equation blocks (scaled space)
+    double *U;               // [Nc][36]  (summed over ranks)
+    double *bc;              // [Nc][6]   (summed over ranks)
+    double *U_loc, *bc_loc;  // this rank's contribution (alias U / bc on a single GPU)
+    double *V;               // [Np][6] sym
+    double *bp;              // [Np][3]
+    double *W;               // [No][18] = Jc^T Jp
+    double *cam_part;        // [n_chunks][27]
+    double *Vinv;            // [Np][6]
+    double *wv;              // [Np][3] = Vinv * bp
+    // reduced system
+    double *S;               // [n][n] row-major, lower blocks
+    double *rhs;             // [n] (becomes y_c after the solve)
+    double *yc;              // [n]
+    // partial sums
+    double *part;            // [n_part][4]
+    int n_part;
+    double *sums;            // [SUM_COUNT]  (summed over ranks)
+    double *maxs;            // [MAX_COUNT]  (max over ranks)
+    double *sums_loc, *maxs_loc;   // this rank's contribution (alias sums / maxs on a single GPU)
+    double *camsums;         // [CS_COUNT]
+    // PCG work vectors (n each) and block-Jacobi preconditioner
+    double *cg_r, *cg_p, *cg_z, *cg_q, *cg_x, *Minv, *tp;
+    // control
+    LMState *state;
+    ba_iteration *iters;     // [max_num_iterations + 2]
+    volatile int *host_flags; // mapped pinned: [0] = done, [1] = cg_done
+};
+
+constexpr int CHUNK = 128;   // observations per camera-side reduction unit
+
+} // namespace ba

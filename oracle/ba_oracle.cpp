@@ -1293,28 +1293,41 @@ void orc_rotation_to_angle_axis(const double R[9], double aa[3]) {
     }
 }
 
-// General 4x4 inverse by cofactors in float32 (what Eigen's Matrix4f::inverse() computes up to rounding).
+// General 4x4 inverse in float32 (Eigen Matrix4f::inverse() stand-in).  Eigen's compute_inverse_size4 builds the
+// adjugate from the six 2x2 minors of rows (0,1) and the six of rows (2,3); same formulation here, row-major.
 void orc_inverse4x4_f32(const float m[16], float out[16]) {
-    float inv[16];
-    inv[0] = m[5] * m[10] * m[15] - m[5] * m[11] * m[14] - m[9] * m[6] * m[15] + m[9] * m[7] * m[14] + m[13] * m[6] * m[11] - m[13] * m[7] * m[10];
-    inv[4] = -m[4] * m[10] * m[15] + m[4] * m[11] * m[14] + m[8] * m[6] * m[15] - m[8] * m[7] * m[14] - m[12] * m[6] * m[11] + m[12] * m[7] * m[10];
-    inv[8] = m[4] * m[9] * m[15] - m[4] * m[11] * m[13] - m[8] * m[5] * m[15] + m[8] * m[7] * m[13] + m[12] * m[5] * m[11] - m[12] * m[7] * m[9];
-    inv[12] = -m[4] * m[9] * m[14] + m[4] * m[10] * m[13] + m[8] * m[5] * m[14] - m[8] * m[6] * m[13] - m[12] * m[5] * m[10] + m[12] * m[6] * m[9];
-    inv[1] = -m[1] * m[10] * m[15] + m[1] * m[11] * m[14] + m[9] * m[2] * m[15] - m[9] * m[3] * m[14] - m[13] * m[2] * m[11] + m[13] * m[3] * m[10];
-    inv[5] = m[0] * m[10] * m[15] - m[0] * m[11] * m[14] - m[8] * m[2] * m[15] + m[8] * m[3] * m[14] + m[12] * m[2] * m[11] - m[12] * m[3] * m[10];
-    inv[9] = -m[0] * m[9] * m[15] + m[0] * m[11] * m[13] + m[8] * m[1] * m[15] - m[8] * m[3] * m[13] - m[12] * m[1] * m[11] + m[12] * m[3] * m[9];
-    inv[13] = m[0] * m[9] * m[14] - m[0] * m[10] * m[13] - m[8] * m[1] * m[14] + m[8] * m[2] * m[13] + m[12] * m[1] * m[10] - m[12] * m[2] * m[9];
-    inv[2] = m[1] * m[6] * m[15] - m[1] * m[7] * m[14] - m[5] * m[2] * m[15] + m[5] * m[3] * m[14] + m[13] * m[2] * m[7] - m[13] * m[3] * m[6];
-    inv[6] = -m[0] * m[6] * m[15] + m[0] * m[7] * m[14] + m[4] * m[2] * m[15] - m[4] * m[3] * m[14] - m[12] * m[2] * m[7] + m[12] * m[3] * m[6];
-    inv[10] = m[0] * m[5] * m[15] - m[0] * m[7] * m[13] - m[4] * m[1] * m[15] + m[4] * m[3] * m[13] + m[12] * m[1] * m[7] - m[12] * m[3] * m[5];
-    inv[14] = -m[0] * m[5] * m[14] + m[0] * m[6] * m[13] + m[4] * m[1] * m[14] - m[4] * m[2] * m[13] - m[12] * m[1] * m[6] + m[12] * m[2] * m[5];
-    inv[3] = -m[1] * m[6] * m[11] + m[1] * m[7] * m[10] + m[5] * m[2] * m[11] - m[5] * m[3] * m[10] - m[9] * m[2] * m[7] + m[9] * m[3] * m[6];
-    inv[7] = m[0] * m[6] * m[11] - m[0] * m[7] * m[10] - m[4] * m[2] * m[11] + m[4] * m[3] * m[10] + m[8] * m[2] * m[7] - m[8] * m[3] * m[6];
-    inv[11] = -m[0] * m[5] * m[11] + m[0] * m[7] * m[9] + m[4] * m[1] * m[11] - m[4] * m[3] * m[9] - m[8] * m[1] * m[7] + m[8] * m[3] * m[5];
-    inv[15] = m[0] * m[5] * m[10] - m[0] * m[6] * m[9] - m[4] * m[1] * m[10] + m[4] * m[2] * m[9] + m[8] * m[1] * m[6] - m[8] * m[2] * m[5];
-    const float det = m[0] * inv[0] + m[1] * inv[4] + m[2] * inv[8] + m[3] * inv[12];
+    auto M = [&](int r, int c) { return m[4 * r + c]; };
+    // minors of the top two rows (columns i<j) and of the bottom two rows
+    const float t01 = M(0, 0) * M(1, 1) - M(1, 0) * M(0, 1);
+    const float t02 = M(0, 0) * M(1, 2) - M(1, 0) * M(0, 2);
+    const float t03 = M(0, 0) * M(1, 3) - M(1, 0) * M(0, 3);
+    const float t12 = M(0, 1) * M(1, 2) - M(1, 1) * M(0, 2);
+    const float t13 = M(0, 1) * M(1, 3) - M(1, 1) * M(0, 3);
+    const float t23 = M(0, 2) * M(1, 3) - M(1, 2) * M(0, 3);
+    const float b23 = M(2, 2) * M(3, 3) - M(3, 2) * M(2, 3);
+    const float b13 = M(2, 1) * M(3, 3) - M(3, 1) * M(2, 3);
+    const float b12 = M(2, 1) * M(3, 2) - M(3, 1) * M(2, 2);
+    const float b03 = M(2, 0) * M(3, 3) - M(3, 0) * M(2, 3);
+    const float b02 = M(2, 0) * M(3, 2) - M(3, 0) * M(2, 2);
+    const float b01 = M(2, 0) * M(3, 1) - M(3, 0) * M(2, 1);
+    const float det = t01 * b23 - t02 * b13 + t03 * b12 + t12 * b03 - t13 * b02 + t23 * b01;
     const float idet = 1.0f / det;
-    for (int i = 0; i < 16; ++i) out[i] = inv[i] * idet;
+    out[0] = (M(1, 1) * b23 - M(1, 2) * b13 + M(1, 3) * b12) * idet;
+    out[1] = (-M(0, 1) * b23 + M(0, 2) * b13 - M(0, 3) * b12) * idet;
+    out[2] = (M(3, 1) * t23 - M(3, 2) * t13 + M(3, 3) * t12) * idet;
+    out[3] = (-M(2, 1) * t23 + M(2, 2) * t13 - M(2, 3) * t12) * idet;
+    out[4] = (-M(1, 0) * b23 + M(1, 2) * b03 - M(1, 3) * b02) * idet;
+    out[5] = (M(0, 0) * b23 - M(0, 2) * b03 + M(0, 3) * b02) * idet;
+    out[6] = (-M(3, 0) * t23 + M(3, 2) * t03 - M(3, 3) * t02) * idet;
+    out[7] = (M(2, 0) * t23 - M(2, 2) * t03 + M(2, 3) * t02) * idet;
+    out[8] = (M(1, 0) * b13 - M(1, 1) * b03 + M(1, 3) * b01) * idet;
+    out[9] = (-M(0, 0) * b13 + M(0, 1) * b03 - M(0, 3) * b01) * idet;
+    out[10] = (M(3, 0) * t13 - M(3, 1) * t03 + M(3, 3) * t01) * idet;
+    out[11] = (-M(2, 0) * t13 + M(2, 1) * t03 - M(2, 3) * t01) * idet;
+    out[12] = (-M(1, 0) * b12 + M(1, 1) * b02 - M(1, 2) * b01) * idet;
+    out[13] = (M(0, 0) * b12 - M(0, 1) * b02 + M(0, 2) * b01) * idet;
+    out[14] = (-M(3, 0) * t12 + M(3, 1) * t02 - M(3, 2) * t01) * idet;
+    out[15] = (M(2, 0) * t12 - M(2, 1) * t02 + M(2, 2) * t01) * idet;
 }
 
 void orc_eval_cam_point(const double cam[6], const double pt[3], const float uv[2], const float K[9],
