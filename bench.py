@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""bench.py -- LM iterations/sec of the BA hot path on synthetic scenes of the named shapes.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload K1|K2|K4|K5] [--solver dense|pcg]
+
+A "step" = one ceres::Solve replacement (ba_solve, <= --lm-iters LM iterations, the reference's per-keyframe setting
+`setNbOfMaxItPerBA(10)`, BundleAdjustment.cpp:204-205) over the whole workload starting from the same initial
+parameters.  `value` = LM iterations per second with the problem resident in HBM (device time, CUDA events, max over
+ranks); `e2e` = the same through the C ABI with HOST buffers (ba_set_problem H2D + ba_solve + ba_get_* D2H inside the
+timed region).  N > 1: landmarks are sharded over ranks (strong scaling), NCCL all-reduces the reduced system.
+
+--impl reference: the reference's own CPU implementation of the path.  Real Ceres is not in this image, so this is the
+C++ CPU oracle (oracle/, "port") on all host threads, each step a bounded sample (max 1 LM iteration) of the same
+workload.  Only this leg and cpu_baseline execute anything under oracle/.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "lm_iters_per_sec"
+UNIT = "LM iterations/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def load_workload(name: str):
+    from bundleadjustment_b200 import synthetic as syn
+    t = time.time()
+    sc = syn.config(name)
+    pb = syn.flatten(sc)
+    log(f"[bench] workload {name}: cams={pb.shape[0]} landmarks={pb.shape[1]} obs={pb.shape[2]} (generated in {time.time() - t:.1f}s, seed {sc.seed})")
+    return sc, pb
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device = device
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.device)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cholesky_flops(n: int) -> float:
+    return n ** 3 / 3.0 + 2.0 * n * n
+
+
+def measure_fp64_peak(device: int) -> float:
+    """FP64 GEMM throughput of this GPU (TFLOP/s): torch.matmul f64 4096^3, best of 5.  MEASURED_PEAKS.json has no
+    FP64 figure, so the denominator of the tensor-pipe roofline is measured here, the same way the driver measures
+    bf16 (cuBLAS through torch, CUDA events)."""
+    import torch
+    n = 4096
+    a = torch.randn(n, n, dtype=torch.float64, device=f"cuda:{device}")
+    b = torch.randn(n, n, dtype=torch.float64, device=f"cuda:{device}")
+    torch.matmul(a, b)
+    best = 1e9
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, b); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    torch.cuda.empty_cache()
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm: the C++ oracle ("port" of the reference's Ceres path; real Ceres is not in this image)
+# ---------------------------------------------------------------------------------------------------------------
+def run_cpu(pb, solver: str, lm_iters: int, threads: int):
+    """One bounded CPU sample: orc_solve with max_num_iterations = lm_iters.  Returns (lm_iterations, seconds)."""
+    from oracle import ba_oracle as orc
+    orc.build()
+    kw = dict(max_num_iterations=lm_iters, num_threads=threads)
+    if solver == "pcg":
+        kw.update(linear_solver=orc.ITERATIVE_SCHUR)
+    opt = orc.default_options(**kw)
+    t = time.perf_counter()
+    _, _, sm, its = orc.solve(pb, opt)
+    dt = time.perf_counter() - t
+    return max(len(its) - 1, 1), dt, sm
+
+
+def cpu_baseline(pb, workload: str, solver: str) -> dict:
+    threads = os.cpu_count() or 1
+    n_it, dt, _ = run_cpu(pb, solver, 1, threads)
+    return {"value": n_it / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"1 LM iteration (iteration-0 evaluation + 1 step) of {workload}, {solver} Schur, oracle/ba_oracle.cpp "
+                      f"with OpenMP on {threads} threads: {dt:.2f} s"}
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    _, pb = load_workload(args.workload)
+    threads = os.cpu_count() or 1
+    for _ in range(min(args.warmup, 1)):           # one warm-up sample is enough to page the problem in
+        run_cpu(pb, args.solver, 1, threads)
+    tot_it, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        n_it, dt, _ = run_cpu(pb, args.solver, 1, threads)
+        tot_it += n_it; tot_t += dt
+    value = tot_it / tot_t
+    out = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": tot_t / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "cams": int(pb.shape[0]), "landmarks": int(pb.shape[1]), "observations": int(pb.shape[2]),
+                   "linear_solver": args.solver, "lm_iters_per_step": 1,
+                   "note": "restated Ceres-path CPU baseline (oracle port), not Ceres itself; each step = 1 LM iteration sample"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{args.steps} x 1 LM iteration of {args.workload}"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------
+def shard_problem(pb, cut, rank):
+    """Rank's landmark range + its observations (obs_pt rebased); cameras replicated."""
+    import dataclasses
+    a, b = int(cut[rank]), int(cut[rank + 1])
+    sel = (pb.obs_pt >= a) & (pb.obs_pt < b)
+    return dataclasses.replace(pb, pt=np.ascontiguousarray(pb.pt[a:b]), obs_cam=np.ascontiguousarray(pb.obs_cam[sel]),
+                               obs_pt=np.ascontiguousarray(pb.obs_pt[sel] - a), obs_uv=np.ascontiguousarray(pb.obs_uv[sel]))
+
+
+def pinned_copy(a: np.ndarray) -> np.ndarray:
+    """The same array in page-locked host memory (torch is plumbing: pinned allocator only)."""
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t.numpy()
+
+
+def main_ours(args):
+    import torch
+    import torch.distributed as dist
+    import bundleadjustment_b200 as bab
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log(f"[bench] WORLD_SIZE={world} but --gpus {args.gpus}; using WORLD_SIZE")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+
+    _, pb_full = load_workload(args.workload)
+    Nc, Np, No = pb_full.shape
+    kw = dict(max_num_iterations=args.lm_iters)
+    if args.solver == "pcg":
+        kw.update(linear_solver=bab.capi.ITERATIVE_SCHUR)
+        if args.cg_tight:
+            kw.update(eta=1e-14, cg_r_tolerance=1e-10, max_linear_solver_iterations=2000)
+    opt = bab.default_options(**kw)
+    solver = bab.Solver(opt, device=local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{local}")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(bab.capi.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        solver.comm_init(world, rank, bytes(uid.cpu().numpy().tobytes()))
+        cut = bab.capi.partition_landmarks(Np, pb_full.obs_pt, world, quadratic=(args.solver == "dense"))
+        pb = shard_problem(pb_full, cut, rank)
+    else:
+        pb = pb_full
+    # page-locked host copies of everything that crosses PCIe in the e2e leg
+    import dataclasses
+    pb = dataclasses.replace(pb, **{f: pinned_copy(getattr(pb, f)) for f in ("cam", "cam_fixed", "fixed_extr", "K", "pt", "obs_cam", "obs_pt", "obs_uv")})
+    h2d = sum(getattr(pb, f).nbytes for f in ("cam", "cam_fixed", "fixed_extr", "K", "pt", "obs_cam", "obs_pt", "obs_uv"))
+    d2h = pb.cam.nbytes + pb.pt.nbytes
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    solver.set_problem(pb)
+    solver.set_profiling(True)
+    # ---- device-resident leg: inputs already in HBM, each step re-starts from the stored initial parameters ----
+    for _ in range(args.warmup):
+        solver.reset_parameters()
+        solver.solve()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    t_dev, t_lin, t_eval, n_it, n_solves, launches, cg_its = 0.0, 0.0, 0.0, 0, 0, 0, 0
+    wall0 = time.perf_counter()
+    last = None
+    for _ in range(args.steps):
+        solver.reset_parameters()
+        sm = solver.solve()
+        t_dev += sm.seconds_total; t_lin += sm.seconds_linear_solver; t_eval += sm.seconds_evaluate
+        n_it += sm.num_iterations - 1
+        n_solves += sm.num_iterations - (1 if sm.termination_type == bab.capi.NO_CONVERGENCE else 0)
+        launches += solver.launch_count()
+        last = sm
+    barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop() if rank == 0 else None
+    t_dev = allmax(t_dev)
+    its = solver.iterations()
+    cg_its = sum(i["linear_solver_iterations"] for i in its) * args.steps if args.solver == "pcg" else 0
+    value = n_it / t_dev
+    # ---- end-to-end leg: host buffers in, host results out, through the C ABI ----
+    e2e_it, e2e_t = 0, 0.0
+    barrier()
+    for s in range(args.warmup_e2e + args.steps_e2e):
+        barrier()
+        t0 = time.perf_counter()
+        solver.set_problem(pb)
+        sm = solver.solve()
+        cam_out, pt_out = solver.cameras(), solver.points()
+        torch.cuda.synchronize()
+        dt = allmax(time.perf_counter() - t0)
+        if s >= args.warmup_e2e:
+            e2e_it += sm.num_iterations - 1; e2e_t += dt
+    e2e_value = e2e_it / e2e_t if e2e_t > 0 else None
+    # ---- second metric: materialised residual + Jacobian evaluation (176 B / observation written) ----
+    solver.set_problem(pb)
+    solver.evaluate_device_ms(3)
+    ev_ms = allmax(solver.evaluate_device_ms(20))
+    obs_per_s = No / (ev_ms * 1e-3)
+    if rank != 0:
+        return 0
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    eval_bytes = 176.0 * pb.shape[2] + 16.0 * pb.shape[2] + 48.0 * Nc + 24.0 * pb.shape[1]
+    roof_eval = {"bound": "hbm", "kernel": "evaluate_materialize_kernel", "achieved": eval_bytes / (ev_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                 "unit": "GB/s", "frac": eval_bytes / (ev_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                 "algorithmic_bytes_per_obs": 176 + 16}
+    if args.solver == "dense":
+        n = 6 * Nc
+        fp64_peak = measure_fp64_peak(local)
+        ach = n_solves * cholesky_flops(n) / t_lin / 1e12
+        roofline = {"bound": "tensor", "kernel": "dense Cholesky of S (gemm_nt_kernel DMMA m8n8k4 + potrf_diag) incl. Schur assembly",
+                    "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None,
+                    "peak_source": "FP64: torch.matmul f64 4096^3 measured in this run (MEASURED_PEAKS.json has no FP64 entry)",
+                    "flops_per_launch": cholesky_flops(n), "share_of_step": t_lin / t_dev}
+    else:
+        per_cg = 2 * 144.0 * pb.shape[2] + 48.0 * pb.shape[1] + 10 * 8.0 * 6 * Nc
+        ach = cg_its * per_cg / t_lin / 1e9 if t_lin > 0 else 0.0
+        roofline = {"bound": "hbm", "kernel": "pcg_matvec_points_kernel (2 passes over W per CG iteration)", "achieved": ach,
+                    "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                    "bytes_per_launch": per_cg, "share_of_step": t_lin / t_dev}
+    cpu = cpu_baseline(pb_full, args.workload, args.solver) if (world == 1 and not args.no_cpu) else None
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "cams": Nc, "landmarks": Np, "observations": No, "linear_solver": args.solver,
+                   "lm_iters_per_step": n_it / args.steps, "max_num_iterations": args.lm_iters, "huber": True,
+                   "parallelism": f"landmark-sharded x{world}" if world > 1 else "single GPU",
+                   "l2": "inputs larger than L2 (W + S >> 126 MB); no flush needed" if args.workload in ("K4", "K5") else "small problem: L2-resident by nature",
+                   "termination": last.message.decode(), "final_cost": last.final_cost, "seed": {"K1": 1, "K2": 2, "K4": 4, "K5": 5}.get(args.workload)},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "steps": args.steps_e2e, "note": "ba_set_problem (host sort + H2D) + ba_solve + ba_get_cameras/points per step, wall clock, max over ranks"},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "roofline_eval": roof_eval,
+        "obs_per_sec": obs_per_s,
+        "stage_seconds_per_step": {"linearize": t_eval / args.steps, "linear_solve": t_lin / args.steps, "total": t_dev / args.steps},
+        "wall_seconds_timed_region": wall,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="K4", choices=["K1", "K2", "K4", "K5"])
+    ap.add_argument("--solver", default="dense", choices=["dense", "pcg"])
+    ap.add_argument("--lm-iters", type=int, default=10)
+    ap.add_argument("--cg-tight", action="store_true", help="PCG run to |r| <= 1e-10 |b| (exact-step trajectory)")
+    ap.add_argument("--steps-e2e", type=int, default=3)
+    ap.add_argument("--warmup-e2e", type=int, default=1)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+    return main_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

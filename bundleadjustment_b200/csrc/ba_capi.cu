@@ -99,6 +99,13 @@ struct ba_handle {
     int n_ranks = 1, rank = 0;
     std::vector<int> cam_obs_count;  // global per-camera observation counts
     int launches = 0;                // kernels/collectives enqueued by the last solve (bench bookkeeping)
+    bool profile = false;            // record CUDA events around every linear solve / linearisation
+    std::vector<cudaEvent_t> prof_ev;   // [4 per body]: lin begin, lin end (= solve begin), solve end, body end
+    size_t prof_used = 0;
+    cudaEvent_t prof_event() {
+        if (prof_used == prof_ev.size()) { cudaEvent_t e; cudaEventCreate(&e); prof_ev.push_back(e); }
+        return prof_ev[prof_used++];
+    }
 
     void free_problem() {
         DevBuf *all[] = {&cam0, &cam1, &pt0, &pt1, &cam_init, &pt_init, &cam_kind, &cam_K, &cam_extr, &pm_uv, &pm_cam, &pm_pt,
@@ -517,6 +524,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
     }
     if (h->opt.linear_solver == BA_DENSE_SCHUR && (rc = ensure_dense(h))) return rc;
     h->launches = 0;
+    h->prof_used = 0;
     h->host_flags[0] = 0; h->host_flags[1] = 0;
     CU(cudaEventRecord(h->ev_start, s));
     launch_init_state(ctx, s);
@@ -529,8 +537,6 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         launch_compute_scale(ctx, s);
         h->launches += 1;
     }
-    cudaEvent_t ev_it[2];
-    ev_it[0] = h->ev_ring[0]; ev_it[1] = h->ev_ring[1];
     cudaEvent_t ev_lm[2];
     CU(cudaEventCreateWithFlags(&ev_lm[0], cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&ev_lm[1], cudaEventDisableTiming));
@@ -543,9 +549,12 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
             if (e != cudaSuccess) { status = fail(BA_ERR_CUDA, "LM loop: %s", cudaGetErrorString(e)); break; }
             if (h->host_flags[0]) break;
         }
+        if (h->profile) cudaEventRecord(h->prof_event(), s);
         if ((rc = enqueue_linearize(h, 0))) { status = rc; break; }
         launch_begin_iteration(ctx, s);
+        if (h->profile) cudaEventRecord(h->prof_event(), s);
         if ((rc = enqueue_linear_solve(h))) { status = rc; break; }
+        if (h->profile) cudaEventRecord(h->prof_event(), s);
         launch_backsub(ctx, s);
         launch_eval_candidate(ctx, h->cost_part.as<double>(), s);
         if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_STEP_BEGIN, ctx.sums + SUM_STEP_BEGIN, SUM_STEP_N))) { status = rc; break; }
@@ -578,12 +587,28 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         float ms = 0;
         cudaEventElapsedTime(&ms, h->ev_start, h->ev_stop);
         summary->seconds_total = ms * 1e-3;
+        if (h->profile) {
+            double t_lin = 0, t_solve = 0;
+            for (size_t i = 0; i + 2 < h->prof_used; i += 3) {
+                float a = 0, b = 0;
+                cudaEventElapsedTime(&a, h->prof_ev[i], h->prof_ev[i + 1]);
+                cudaEventElapsedTime(&b, h->prof_ev[i + 1], h->prof_ev[i + 2]);
+                t_lin += a; t_solve += b;
+            }
+            summary->seconds_evaluate = t_lin * 1e-3;
+            summary->seconds_linear_solver = t_solve * 1e-3;
+        }
         std::snprintf(summary->message, sizeof(summary->message), "%s", message_text(st.msg));
     }
     return BA_OK;
 }
 
 extern "C" int ba_get_launch_count(ba_handle *h) { return h ? h->launches : 0; }
+extern "C" int ba_set_profiling(ba_handle *h, int32_t on) {
+    if (!h) return fail(BA_ERR_INVALID, "handle is NULL");
+    h->profile = on != 0;
+    return BA_OK;
+}
 
 extern "C" int ba_get_cameras(ba_handle *h, double *cam) {
     if (!h || !h->has_problem || !cam) return fail(BA_ERR_STATE, "no problem / NULL output");

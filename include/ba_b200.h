@@ -162,6 +162,9 @@ int ba_comm_init(ba_handle *h, int32_t n_ranks, int32_t rank, const uint8_t id[1
 
 /* Number of kernels + collectives the last ba_solve enqueued (benchmark bookkeeping: "gpu_launches"). */
 int ba_get_launch_count(ba_handle *h);
+/* on != 0: ba_solve records CUDA events around each linearisation and each linear solve and reports the sums in
+ * ba_summary.seconds_evaluate / seconds_linear_solver (event recording does not synchronise the stream). */
+int ba_set_profiling(ba_handle *h, int32_t on);
 
 /* Dense SPD solve A x = b with the reduced-system Cholesky (DenseSchurComplementSolver's Eigen LLT stand-in) on
  * its own: tests and the FP64 tensor-pipe micro-benchmark.  A: n x n row-major, lower triangle read.
