@@ -150,16 +150,23 @@ gemm_nt_kernel(const double *A, int lda, const double *B, int ldb, double *C,
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// Diagonal block: Cholesky in shared memory + inverse of the factor.  One CTA, 256 threads.
-// T is NB x (NB+1); L in the lower triangle, (L^-1)^T accumulated in the strict upper triangle, 1/diag in dinv.
+// Diagonal block: Cholesky in shared memory + inverse of the factor, one CTA of 256 threads.
+// The inverse costs no extra sequential depth: the block is factored as the augmented panel [A_kk ; I], whose
+// bottom half turns into L^-T under the very same right-looking updates.  Both halves share one NB x (NB+1) tile:
+// L in the lower triangle, E = L^-T in the strict upper triangle (E[r][c], r < c), diag(E) = 1/diag(L) in dinv.
+// Blocked by SB = 16 columns: (A) one warp factors + inverts the 16x16 diagonal sub-block, (B) one thread per row
+// applies L_d^-T to the sub-panel, (C) all threads apply the rank-16 trailing update with 4x4 register tiles.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int TP = NB + 1;
+constexpr int SB = 16;
+constexpr int PVP = SB + 1;
 
 __global__ void __launch_bounds__(256, 1)
 potrf_diag_kernel(double *__restrict__ A, int ld, int k0, int nb, double *__restrict__ invL, LMState *state, int *fail_flag) {
     if (state && state->done) return;
-    extern __shared__ __align__(16) double T[];       // [NB][TP] + dinv[NB]
+    extern __shared__ __align__(16) double T[];       // [NB][TP] + dinv[NB] + Pv[NB][PVP]
     double *dinv = T + NB * TP;
+    double *Pv = dinv + NB;
     __shared__ int s_bad;
     const int tid = threadIdx.x;
     if (tid == 0) s_bad = 0;
@@ -170,20 +177,97 @@ potrf_diag_kernel(double *__restrict__ A, int ld, int k0, int nb, double *__rest
         T[i * TP + j] = v;
     }
     __syncthreads();
-    const int ti = tid >> 4, tj = tid & 15;
-    for (int j = 0; j < nb; ++j) {
-        double d = T[j * TP + j];
-        const bool bad = !(d > 0.0) || !isfinite(d);
-        if (bad) d = 1.0;
-        const double sd = sqrt(d), inv = 1.0 / sd;
-        __syncthreads();                                     // everyone has read T[j][j]
-        if (bad && tid == 0) s_bad = 1;
-        for (int i = j + 1 + tid; i < nb; i += 256) T[i * TP + j] *= inv;
-        if (tid == 0) T[j * TP + j] = sd;
+    for (int j0 = 0; j0 < NB; j0 += SB) {
+        // ---- (A) 16x16 diagonal sub-block: potrf + inverse, warp 0 ----
+        if (tid < 32) {
+            const int i = tid;
+            for (int j = 0; j < SB; ++j) {
+                double d = T[(j0 + j) * TP + j0 + j];
+                const bool bad = !(d > 0.0) || !isfinite(d);
+                if (bad) d = 1.0;
+                const double sd = sqrt(d), inv = 1.0 / sd;
+                __syncwarp();
+                if (bad && i == 0) s_bad = 1;
+                if (i < SB && i > j) T[(j0 + i) * TP + j0 + j] *= inv;
+                if (i == j) { T[(j0 + j) * TP + j0 + j] = sd; dinv[j0 + j] = inv; }
+                __syncwarp();
+                if (i < SB && i > j) {
+                    const double lij = T[(j0 + i) * TP + j0 + j];
+                    for (int c = j + 1; c <= i; ++c) T[(j0 + i) * TP + j0 + c] -= lij * T[(j0 + c) * TP + j0 + j];
+                }
+                __syncwarp();
+            }
+            if (i < SB) {
+                // lane c: column c of X = L_d^-1, stored transposed in the strict upper triangle
+                const int c = i;
+                const double xc = dinv[j0 + c];
+                for (int ii = 1; ii < SB; ++ii) {
+                    double acc = 0.0;
+                    for (int k = 0; k < ii; ++k) {
+                        const double lik = T[(j0 + ii) * TP + j0 + k];
+                        if (k >= c) acc += lik * ((k == c) ? xc : T[(j0 + c) * TP + j0 + k]);
+                    }
+                    if (ii > c) T[(j0 + c) * TP + j0 + ii] = -acc * dinv[j0 + ii];
+                }
+            }
+        }
         __syncthreads();
-        for (int i = j + 1 + ti; i < nb; i += 16) {
-            const double lij = T[i * TP + j];
-            for (int c = j + 1 + tj; c <= i; c += 16) T[i * TP + c] -= lij * T[c * TP + j];
+        // ---- (B) sub-panel rows: x <- x * L_d^-T ; x < j0: rows of E, x >= j0 + SB: rows of L ----
+        if (tid < NB) {
+            const int x = tid;
+            double w[SB];
+            if (x < j0 || x >= j0 + SB) {
+                double v[SB];
+#pragma unroll
+                for (int k = 0; k < SB; ++k) v[k] = T[x * TP + j0 + k];
+#pragma unroll
+                for (int k = 0; k < SB; ++k) {
+                    double acc = v[k] * dinv[j0 + k];
+#pragma unroll
+                    for (int m = 0; m < k; ++m) acc += v[m] * T[(j0 + m) * TP + j0 + k];
+                    w[k] = acc;
+                }
+#pragma unroll
+                for (int k = 0; k < SB; ++k) T[x * TP + j0 + k] = w[k];
+            } else {
+#pragma unroll
+                for (int k = 0; k < SB; ++k) w[k] = (x < j0 + k) ? T[x * TP + j0 + k] : ((x == j0 + k) ? dinv[x] : 0.0);
+            }
+#pragma unroll
+            for (int k = 0; k < SB; ++k) Pv[x * PVP + k] = w[k];
+        }
+        __syncthreads();
+        // ---- (C) trailing update of columns c >= j0 + SB: rows x < j0 + SB (E) and x >= c (L) ----
+        const int c_begin = j0 + SB;
+        const int ntask = 32 * ((NB - c_begin) / 4);
+        for (int t = tid; t < ntask; t += 256) {
+            const int tx = t & 31, c0 = c_begin + (t >> 5) * 4;
+            double acc[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[r][q] = 0.0;
+#pragma unroll 4
+            for (int k = 0; k < SB; ++k) {
+                double a[4], b[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) a[r] = Pv[(tx + 32 * r) * PVP + k];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) b[q] = Pv[(c0 + q) * PVP + k];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[r][q] += a[r] * b[q];
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int x = tx + 32 * r;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = c0 + q;
+                    if (x < c_begin || x >= c) T[x * TP + c] -= acc[r][q];
+                }
+            }
         }
         __syncthreads();
     }
@@ -192,26 +276,7 @@ potrf_diag_kernel(double *__restrict__ A, int ld, int k0, int nb, double *__rest
         const int i = idx / nb, j = idx % nb;
         if (j <= i) A[(size_t)(k0 + i) * ld + k0 + j] = T[i * TP + j];
     }
-    // inverse: thread c owns column c of X = L^-1, stored transposed in the strict upper triangle: X[i][c] -> T[c][i]
-    if (tid < NB) {
-        const int c = tid;
-        const double xc = 1.0 / T[c * TP + c];
-        dinv[c] = xc;
-        for (int i = 1; i < NB; ++i) {
-            // all lanes walk the same (i, k) sequence: L[i][k] is a broadcast, T[c][k] is conflict-free
-            double s = 0.0;
-            for (int k = 0; k < i; ++k) {
-                const double lik = T[i * TP + k];
-                if (k >= c) {
-                    const double xk = (k == c) ? xc : T[c * TP + k];
-                    s += lik * xk;
-                }
-            }
-            if (i > c) T[c * TP + i] = -s / T[i * TP + i];
-        }
-    }
-    __syncthreads();
-    // invL: full NB x NB row-major, zeros above the diagonal
+    // invL: full NB x NB row-major, zeros above the diagonal; X[i][c] = E[c][i]
     for (int idx = tid; idx < NB * NB; idx += 256) {
         const int i = idx / NB, c = idx % NB;
         double v = 0.0;
@@ -226,33 +291,45 @@ potrf_diag_kernel(double *__restrict__ A, int ld, int k0, int nb, double *__rest
 }
 
 // Backward substitution L^T y = z, one launch per block row k (descending).  z lives in row n of A.
+// Every CTA recomputes y_k = L_kk^-T z_k (128 x 128 GEMV from the stored inverse), then owns 64 columns of the
+// update z[col] -= sum_r L[k0 + r][col] y_k[r], rows split over 4 thread groups.
 __global__ void __launch_bounds__(256)
 back_solve_kernel(double *__restrict__ A, int ld, int n, int k0, int nb, const double *__restrict__ invL,
                   double *__restrict__ y, const LMState *state) {
     if (state && state->done) return;
     __shared__ double ys[NB];
+    __shared__ double part[4][64];
+    __shared__ double yp[2][NB];
     double *z = A + (size_t)n * ld;
     const int tid = threadIdx.x;
-    if (tid < NB) {
-        // y_k[c] = sum_{r >= c} invL[r][c] * z[k0 + r]
-        double s = 0.0;
-        if (tid < nb)
-            for (int r = tid; r < nb; ++r) s += invL[r * NB + tid] * z[k0 + r];
-        ys[tid] = s;
+    {
+        // y_k[c] = sum_{r >= c} invL[r][c] * z[k0 + r]; two threads per column (even / odd r)
+        const int c = tid & (NB - 1), half = tid >> 7;
+        double acc = 0.0;
+        if (c < nb)
+            for (int r = c + half; r < nb; r += 2) acc += invL[r * NB + c] * z[k0 + r];
+        yp[half][c] = acc;
     }
     __syncthreads();
+    if (tid < NB) ys[tid] = yp[0][tid] + yp[1][tid];
+    __syncthreads();
     if (blockIdx.x == 0 && tid < nb) y[k0 + tid] = ys[tid];
-    // z[col] -= sum_r L[k0 + r][col] * y_k[r] for col < k0
-    const int col = blockIdx.x * 256 + tid;
+    const int cl = tid & 63, rg = tid >> 6;
+    const int col = blockIdx.x * 64 + cl;
+    double acc = 0.0;
     if (col < k0) {
-        double s = 0.0;
-        for (int r = 0; r < nb; ++r) s += A[(size_t)(k0 + r) * ld + col] * ys[r];
-        z[col] -= s;
+        const int r_lo = rg * 32, r_hi = min(nb, r_lo + 32);
+        const double *src = A + (size_t)(k0 + r_lo) * ld + col;
+#pragma unroll 8
+        for (int r = r_lo; r < r_hi; ++r, src += ld) acc += (*src) * ys[r];
     }
+    part[rg][cl] = acc;
+    __syncthreads();
+    if (tid < 64 && col < k0) z[col] -= part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
 }
 
 static const int GEMM_SMEM = 2 * (BM + BN) * SPAD * (int)sizeof(double);     // 81920
-static const int POTRF_SMEM = (NB * TP + NB) * (int)sizeof(double);           // 133120
+static const int POTRF_SMEM = (NB * TP + NB + NB * PVP) * (int)sizeof(double);   // 150528
 
 int chol_init() {
     cudaError_t e;
@@ -292,7 +369,7 @@ void chol_factor_solve(double *A, int n, double *invL, double *y, LMState *state
     for (int kb = nblk - 1; kb >= 0; --kb) {
         const int k0 = kb * NB;
         const int nb = (n - k0 < NB) ? (n - k0) : NB;
-        const int blocks = (k0 + 255) / 256 > 0 ? (k0 + 255) / 256 : 1;
+        const int blocks = (k0 + 63) / 64 > 0 ? (k0 + 63) / 64 : 1;
         back_solve_kernel<<<blocks, 256, 0, s>>>(A, n, n, k0, nb, invL + (size_t)kb * NB * NB, y, state);
     }
 }
