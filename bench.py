@@ -174,15 +174,6 @@ def main_reference(args):
 # ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
-def shard_problem(pb, cut, rank):
-    """Rank's landmark range + its observations (obs_pt rebased); cameras replicated."""
-    import dataclasses
-    a, b = int(cut[rank]), int(cut[rank + 1])
-    sel = (pb.obs_pt >= a) & (pb.obs_pt < b)
-    return dataclasses.replace(pb, pt=np.ascontiguousarray(pb.pt[a:b]), obs_cam=np.ascontiguousarray(pb.obs_cam[sel]),
-                               obs_pt=np.ascontiguousarray(pb.obs_pt[sel] - a), obs_uv=np.ascontiguousarray(pb.obs_uv[sel]))
-
-
 def pinned_copy(a: np.ndarray) -> np.ndarray:
     """The same array in page-locked host memory (torch is plumbing: pinned allocator only)."""
     import torch
@@ -219,8 +210,9 @@ def main_ours(args):
             uid.copy_(torch.frombuffer(bytearray(bab.capi.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(uid, 0)
         solver.comm_init(world, rank, bytes(uid.cpu().numpy().tobytes()))
-        cut = bab.capi.partition_landmarks(Np, pb_full.obs_pt, world, quadratic=(args.solver == "dense"))
-        pb = shard_problem(pb_full, cut, rank)
+        pb_full = bab.sharding.landmark_major(pb_full)
+        cut = bab.sharding.partition(pb_full, world, quadratic=(args.solver == "dense"))
+        pb = bab.sharding.shard(pb_full, cut, rank)
     else:
         pb = pb_full
     # page-locked host copies of everything that crosses PCIe in the e2e leg

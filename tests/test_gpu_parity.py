@@ -20,6 +20,19 @@ def _traj_check(its, oits, rtol=1e-6):
         assert abs(a["trust_region_radius"] - b["trust_region_radius"]) <= 1e-5 * b["trust_region_radius"], (a, b)
 
 
+@pytest.mark.parametrize("name", ["tiny_huber", "tiny_l2", "small_huber"])
+def test_golden_fixtures(bab, name):
+    """The CUDA path against the committed golden vectors (tests/golden/make_golden.py)."""
+    import golden_util as G
+    pb, z, gits = G.load(name)
+    s = bab.Solver(bab.default_options(max_num_iterations=int(z["max_num_iterations"]), use_huber=int(z["use_huber"])))
+    s.set_problem(pb)
+    ev = s.evaluate()
+    sm = s.solve()
+    G.check_against_golden(z, gits, ev, s.iterations(), s.cameras(), s.points(), sm.final_cost, sm.termination_type)
+    s.close()
+
+
 @pytest.fixture(scope="module")
 def k1_small():
     return syn.flatten(syn.config("K1", scale=0.25))
