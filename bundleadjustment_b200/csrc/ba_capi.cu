@@ -226,13 +226,14 @@ int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
 }
 
 int ensure_dense(ba_handle *h) {
-    const size_t n = (size_t)h->ctx.n;
-    const size_t need = sizeof(double) * (n + 1) * n;
+    const int n = h->ctx.n;
+    const size_t need = sizeof(double) * chol_matrix_doubles(n);
     if (h->S.bytes < need) {
         CU(h->S.alloc(need));
-        CU(h->invL.alloc(sizeof(double) * std::max<size_t>(chol_work_doubles((int)n), 1)));
+        CU(h->invL.alloc(sizeof(double) * chol_work_doubles(n)));
     }
     h->ctx.S = h->S.as<double>();
+    h->ctx.ldS = chol_ld(n);
     return BA_OK;
 }
 
@@ -467,13 +468,14 @@ int enqueue_linear_solve(ba_handle *h) {
         // rhs row of the augmented matrix
         if (h->comm) {
             // lower triangle + rhs would do; the full buffer keeps the collective a single contiguous message
-            if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.n))) return rc;
+            if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.ldS))) return rc;     // the n real rows (padding excluded)
             if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
         }
-        CU(cudaMemcpyAsync(ctx.S + (size_t)ctx.n * ctx.n, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToDevice, s));
-        chol_factor_solve(ctx.S, ctx.n, h->invL.as<double>(), ctx.yc, ctx.state, nullptr, s);
-        const int nblk = (ctx.n + CHOL_NB - 1) / CHOL_NB;
-        h->launches += 4 * nblk;
+        // rhs^T becomes row ldS of the matrix: the forward substitution is then part of the factorisation's dataflow
+        CU(cudaMemcpyAsync(ctx.S + (size_t)ctx.ldS * ctx.ldS, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToDevice, s));
+        const int ce = chol_factor_solve(ctx.S, ctx.n, h->invL.as<double>(), ctx.yc, ctx.state, nullptr, s);
+        if (ce) return fail(BA_ERR_CUDA, "chol_factor_solve: %s", cudaGetErrorString((cudaError_t)ce));
+        h->launches += 2;
     } else {
         launch_pcg_setup(ctx, s);
         h->launches += 2;
@@ -751,12 +753,12 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
     launch_point_invert(ctx, radius, s);
     launch_schur_build(ctx, radius, s);
     if (h->comm) {
-        if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.n))) return rc;
+        if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.ldS))) return rc;
         if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
     }
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
-    if (S) CU(cudaMemcpy(S, ctx.S, 8 * (size_t)ctx.n * ctx.n, cudaMemcpyDeviceToHost));
+    if (S) CU(cudaMemcpy2D(S, 8 * (size_t)ctx.n, ctx.S, 8 * (size_t)ctx.ldS, 8 * (size_t)ctx.n, (size_t)ctx.n, cudaMemcpyDeviceToHost));
     if (rhs) CU(cudaMemcpy(rhs, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToHost));
     if (cost) CU(cudaMemcpy(cost, ctx.sums + SUM_LIN_COST, 8, cudaMemcpyDeviceToHost));
     return BA_OK;
@@ -770,14 +772,15 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     if (rc) return rc;
     int e0 = chol_init();
     if (e0) return fail(BA_ERR_CUDA, "chol_init: %s", cudaGetErrorString((cudaError_t)e0));
-    const int np = (n + 1) & ~1;          // even order keeps 16-byte row alignment
-    std::vector<double> Ah((size_t)(np + 1) * np, 0.0);
-    for (int i = 0; i < n; ++i) std::memcpy(&Ah[(size_t)i * np], A + (size_t)i * n, 8 * (size_t)n);
-    if (np > n) Ah[(size_t)n * np + n] = 1.0;
+    const int np = chol_ld(n);
+    const size_t rows = chol_rows(n);
+    std::vector<double> Ah(rows * (size_t)np, 0.0);
+    for (int i = 0; i < n; ++i) std::memcpy(&Ah[(size_t)i * np], A + (size_t)i * n, 8 * (size_t)(i + 1));
+    for (int i = n; i < np; ++i) Ah[(size_t)i * np + i] = 1.0;
     std::memcpy(&Ah[(size_t)np * np], b, 8 * (size_t)n);
     DevBuf dA, dA0, dInv, dY, dFail;
     CU(dA.alloc(8 * Ah.size())); CU(dA0.alloc(8 * Ah.size()));
-    CU(dInv.alloc(8 * chol_work_doubles(np))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
+    CU(dInv.alloc(8 * chol_work_doubles(n))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
     CU(cudaMemcpy(dA0.p, Ah.data(), 8 * Ah.size(), cudaMemcpyHostToDevice));
     CU(cudaMemset(dFail.p, 0, 4));
     cudaEvent_t e1, e2;
@@ -787,7 +790,8 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     for (int r = 0; r < repeats; ++r) {
         CU(cudaMemcpy(dA.p, dA0.p, 8 * Ah.size(), cudaMemcpyDeviceToDevice));
         CU(cudaEventRecord(e1, 0));
-        chol_factor_solve(dA.as<double>(), np, dInv.as<double>(), dY.as<double>(), nullptr, dFail.as<int>(), 0);
+        const int ce = chol_factor_solve(dA.as<double>(), n, dInv.as<double>(), dY.as<double>(), nullptr, dFail.as<int>(), 0);
+        if (ce) return fail(BA_ERR_CUDA, "chol_factor_solve: %s", cudaGetErrorString((cudaError_t)ce));
         CU(cudaEventRecord(e2, 0));
         CU(cudaDeviceSynchronize());
         float t = 0;

@@ -1,30 +1,61 @@
-// ba_cholesky.cu -- dense blocked Cholesky of the reduced camera system on the FP64 tensor pipe.
+// ba_cholesky.cu -- dense Cholesky solve of the reduced camera system on the FP64 tensor pipe.
 //
 // Replaces Ceres' DenseSchurComplementSolver::SolveReducedLinearSystem (Eigen LLT) that the reference selects with
 // options.linear_solver_type = ceres::DENSE_SCHUR (ba_project/src/ba/Optimizer.cpp:85).
 //
-// Layout: A is (n+1) x n row-major (ld = n).  Lower triangle holds S; the extra row n holds rhs^T, so the forward
-// substitution z = L^-1 rhs falls out of the factorisation itself (row n is just one more row of every panel).
-// Right-looking, block size NB = 128:
-//   potrf_diag : one CTA factors the NB x NB diagonal block in shared memory and inverts it (L_kk^-1)
-//   gemm_nt    : FP64 tensor-core (DMMA m8n8k4) C = A * B^T tiles, 128x128x16, cp.async double-buffered
-//                 - MODE_SET : panel TRSM as a GEMM with L_kk^-T     A_ik <- A_ik * L_kk^-T
-//                 - MODE_SUB : trailing SYRK update (lower tiles)     A_ij <- A_ij - A_ik * A_jk^T
-//   back_solve : one launch per block row for L^T y = z
-// FP64 on sm_100a has no tcgen05 kind; mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4) is the tensor-pipe instruction.
+// ONE persistent cooperative kernel (one CTA per SM) runs the whole factorisation + both substitutions as a tile
+// dataflow: 128 x 128 tiles, LEFT-looking, tasks handed out column-major round-robin, tile readiness published through
+// per-row progress counters (release/acquire), so there is no launch gap, no global barrier and the serial chain
+// potrf(j) -> trsm(j+1, j) -> last k-slice of (j+1, j+1) -> potrf(j+1) overlaps with the bulk updates of later columns.
+//
+//   task (i, j), i >= j:   C = A_ij - sum_{k<j} L_ik L_jk^T          one long-K DMMA GEMM (K = 128 j), accumulators in
+//                                                                     registers, A/B k-slices through a 4-stage cp.async ring
+//        i == j:           C = L_jj L_jj^T in shared memory (warp-register 32 x 32 base case + DMMA panel/trailing updates),
+//                          L_jj^-1 falls out of the same elimination ([A; I] trick) and is stored for the TRSMs
+//        i >  j:           L_ij = C L_jj^-T as a second DMMA GEMM (C staged in shared memory)
+//   rhs: the right-hand side is row n_pad of A (tile row T), so the forward substitution z = L^-1 rhs IS the tasks (T, j).
+//   back substitution:     block m's owner applies z_m -= L_km^T y_k as the y_k appear, then y_m = L_mm^-T z_m.
+//
+// Layout contract (see chol_rows / chol_ld): A is (n_pad + 128) x n_pad row-major with n_pad = ceil(n / 128) * 128; the
+// lower triangle of the leading n x n block holds S, rows/cols [n, n_pad) are identity padding, row n_pad holds rhs^T,
+// the remaining rows are zero.  FP64 has no tcgen05 kind on sm_100a: mma.sync.m8n8k4.f64 (SASS DMMA) is the tensor-pipe
+// instruction (measured 37.1 TFLOP/s register-only peak on B200, tools/dmma_bench.cu).
 #include "ba_launch.h"
+
+#include <cooperative_groups.h>
 
 namespace ba {
 
-constexpr int NB = CHOL_NB;        // 128
-constexpr int BM = 128, BN = 128, BK = 16;
-constexpr int SPAD = BK + 4;       // smem row stride in doubles: 160 B == 32 mod 128 -> conflict-free fragments
+constexpr int NB = CHOL_NB;            // 128: tile edge
+constexpr int BK = 16;                 // k-slice of the cp.async ring
+constexpr int SPAD = BK + 4;           // 20 doubles: row stride == 4 (mod 16) -> conflict-free DMMA fragment loads
+constexpr int NSTAGE = 4;
+constexpr int LDT = NB + 4;            // 132: stride of the staged C tile, same conflict-free property
+constexpr int PB = 32;                 // potrf panel width (warp-register base case)
+constexpr int LDP = PB + 4;            // 36
 
-size_t chol_work_doubles(int n) { return (size_t)((n + NB - 1) / NB) * NB * NB; }
+constexpr int STAGE_DOUBLES = 2 * NB * SPAD;                       // A slice + B slice
+constexpr int TILE_DOUBLES = NB * LDT;                             // 16896
+constexpr int RING_DOUBLES = NSTAGE * STAGE_DOUBLES;               // 20480
+// potrf scratch (Pv | invd | dinv) aliases the ring's tail; the ring itself may spill over the C tile during the main loop
+constexpr int SMEM_DOUBLES = TILE_DOUBLES + NB * LDP + PB * LDP + NB;   // 16896 + 4608 + 1152 + 128 = 22784
+static_assert(RING_DOUBLES <= SMEM_DOUBLES, "ring must fit");
+constexpr int CHOL_SMEM = SMEM_DOUBLES * (int)sizeof(double);      // 182272 B
 
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem, int src_bytes) {
+int chol_ld(int n) { return ((n + NB - 1) / NB) * NB; }
+size_t chol_rows(int n) { return (size_t)chol_ld(n) + NB; }
+size_t chol_matrix_doubles(int n) { return chol_rows(n) * (size_t)chol_ld(n); }
+// work area: L_jj^-1 blocks, then int flags [rowdone (T + 1) | diagdone (T) | ydone (T) | abort (1)]
+static inline int chol_flag_count(int T) { return 3 * T + 2; }
+size_t chol_work_doubles(int n) {
+    const int T = chol_ld(n) / NB;
+    return (size_t)T * NB * NB + (size_t)T * NB + (size_t)(chol_flag_count(T) + 1) / 2 + 1;
+}
+
+// ---- small PTX helpers -------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(src_bytes));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 template <int N>
@@ -35,343 +66,428 @@ __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double
                  : "+d"(c0), "+d"(c1)
                  : "d"(a), "d"(b));
 }
+__device__ __forceinline__ int ld_acquire(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int *p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
 
-enum { MODE_SET = 0, MODE_SUB = 1 };
+struct CholArgs {
+    double *A;            // (n_pad + 128) x n_pad
+    int ld;               // n_pad
+    int T;                // column tiles = n_pad / 128; row tiles = T + 1 (the last one is the rhs row)
+    int n;                // logical order (entries of y written)
+    double *invL;         // [T][128*128]
+    double *ypad;         // [T][128] solution blocks as they are produced (cross-CTA exchange)
+    int *rowdone;         // [T + 1] number of finished tiles in the row (columns 0 .. rowdone-1 are final)
+    int *diagdone;        // [T]
+    int *ydone;           // [T]
+    int *abort_flag;      // [1] set when a wait timed out (never expected; keeps a bug from hanging the GPU)
+    double *y;            // [n]
+    LMState *state;       // may be nullptr
+    int *fail_flag;       // may be nullptr
+};
 
-// C[m][n] (op)= sum_k A[m][k] * B[n][k];  A: M x K (lda), B: N x K (ldb), C: M x N (ldc); all row-major.
-// TRI: blockIdx.x enumerates lower-triangular tile pairs (ti >= tj) of a square tile grid whose tile rows start at
-// row_tile0 * 0 ... ; A and B are then the same panel (B tile = rows of the panel at tj).
-template <int MODE, bool TRI>
-__global__ void __launch_bounds__(256, 1)
-gemm_nt_kernel(const double *A, int lda, const double *B, int ldb, double *C,
-               int ldc, int M, int N, int K, int tiles_n, const LMState *state) {
-    if (state && state->done) return;
-    extern __shared__ __align__(16) double smem[];
-    double *sA = smem;                       // [2][BM][SPAD]
-    double *sB = smem + 2 * BM * SPAD;       // [2][BN][SPAD]
-    int tm, tn;
-    if (TRI) {
-        // linear index -> (tm >= tn)
-        const int t = blockIdx.x;
-        int r = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-        while ((r + 1) * (r + 2) / 2 <= t) ++r;
-        while (r * (r + 1) / 2 > t) --r;
-        tm = r; tn = t - r * (r + 1) / 2;
-    } else {
-        tm = blockIdx.x / tiles_n; tn = blockIdx.x % tiles_n;
+constexpr long long SPIN_TIMEOUT_NS = 4000000000LL;    // 4 s
+
+__device__ __forceinline__ long long global_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
+    return t;
+}
+
+// spin until *flag >= need; returns false if aborted (every thread polls for itself: its own cp.asyncs follow)
+__device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_flag) {
+    if (ld_acquire(flag) >= need) return true;
+    const long long t0 = global_ns();
+    unsigned spins = 0;
+    while (true) {
+        __nanosleep(64);
+        if (ld_acquire(flag) >= need) return true;
+        if ((++spins & 255u) == 0) {
+            if (ld_acquire(abort_flag)) return false;
+            if (global_ns() - t0 > SPIN_TIMEOUT_NS) { atomicExch(abort_flag, 1); return false; }
+        }
     }
-    const int m0 = tm * BM, n0 = tn * BN;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// Diagonal tile: Cholesky + inverse of the factor, in shared memory, one CTA (8 warps).
+// In-place augmented elimination of [A; I]: after the sweep the tile holds L in the lower triangle (diag included)
+// and E = L^-T in the STRICT upper triangle (E[r][c], r < c), with diag(E) = 1 / diag(L) in dinv.  Per 32-column panel:
+//   (A) warp 0 factors the 32 x 32 diagonal block in REGISTERS (lane = row, shuffles broadcast the pivot column) and
+//       forward-substitutes its inverse (lane = column of L_d^-1);
+//   (B) every other row x (L rows below, E rows above) gets  row <- row * L_d^-T  as DMMA tiles;
+//   (C) masked DMMA trailing update of the columns to the right:  T[x][c] -= Pv[x] . Pv[c]  for x >= c (L) or x < c0 + 32 (E).
+// Non-positive / non-finite pivots are replaced by 1 and reported (no hang, Ceres' LINEAR_SOLVER_FAILURE semantics
+// are applied by the LM controller).
+// -------------------------------------------------------------------------------------------------------------
+__device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double *__restrict__ Pv, double *__restrict__ invd,
+                                                double *__restrict__ dinv) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp >> 2, wn = warp & 3;          // 2 x 4 warps -> 64 x 32 per warp
     const int g = lane >> 2, tig = lane & 3;
-
-    double acc[8][4][2];
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-
-    auto load_stage = [&](int stage, int kk) {
-        // each operand tile: 128 rows x 16 doubles = 128 x 8 segments of 16 B; 256 threads x 4 each
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int idx = tid + 256 * r;          // 0..1023
-            const int row = idx >> 3, seg = idx & 7;
-            const int k = kk + seg * 2;
-            int kb = (K - k) * 8;
-            kb = kb < 0 ? 0 : (kb > 16 ? 16 : kb);
-            {
-                const int gr = m0 + row;
-                const int bytes = (gr < M) ? kb : 0;
-                const double *src = A + (size_t)(gr < M ? gr : 0) * lda + (bytes ? k : 0);
-                cp_async16(sA + ((size_t)stage * BM + row) * SPAD + seg * 2, src, bytes);
-            }
-            {
-                const int gr = n0 + row;
-                const int bytes = (gr < N) ? kb : 0;
-                const double *src = B + (size_t)(gr < N ? gr : 0) * ldb + (bytes ? k : 0);
-                cp_async16(sB + ((size_t)stage * BN + row) * SPAD + seg * 2, src, bytes);
-            }
-        }
-    };
-
-    const int nk = (K + BK - 1) / BK;
-    load_stage(0, 0);
-    cp_async_commit();
-    for (int kt = 0; kt < nk; ++kt) {
-        if (kt + 1 < nk) {
-            load_stage((kt + 1) & 1, (kt + 1) * BK);
-            cp_async_commit();
-            cp_async_wait<1>();
-        } else {
-            cp_async_wait<0>();
-        }
-        __syncthreads();
-        const double *a_s = sA + (size_t)(kt & 1) * BM * SPAD + (size_t)(wm * 64 + g) * SPAD + tig;
-        const double *b_s = sB + (size_t)(kt & 1) * BN * SPAD + (size_t)(wn * 32 + g) * SPAD + tig;
-#pragma unroll
-        for (int ks = 0; ks < BK / 4; ++ks) {
-            double a[8], b[4];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] = a_s[(size_t)i * 8 * SPAD + ks * 4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = b_s[(size_t)j * 8 * SPAD + ks * 4];
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-        }
-        __syncthreads();
-    }
-    // epilogue
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int row = m0 + wm * 64 + i * 8 + g;
-        if (row >= M) continue;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int col = n0 + wn * 32 + j * 8 + 2 * tig;
-            if (col >= N) continue;
-            double *dst = C + (size_t)row * ldc + col;
-            if (col + 1 < N) {
-                double2 v;
-                if (MODE == MODE_SUB) {
-                    v = *reinterpret_cast<double2 *>(dst);
-                    v.x -= acc[i][j][0]; v.y -= acc[i][j][1];
-                } else {
-                    v.x = acc[i][j][0]; v.y = acc[i][j][1];
-                }
-                *reinterpret_cast<double2 *>(dst) = v;
-            } else {
-                if (MODE == MODE_SUB) dst[0] -= acc[i][j][0]; else dst[0] = acc[i][j][0];
-            }
-        }
-    }
-}
-
-// -------------------------------------------------------------------------------------------------------------
-// Diagonal block: Cholesky in shared memory + inverse of the factor, one CTA of 256 threads.
-// The inverse costs no extra sequential depth: the block is factored as the augmented panel [A_kk ; I], whose
-// bottom half turns into L^-T under the very same right-looking updates.  Both halves share one NB x (NB+1) tile:
-// L in the lower triangle, E = L^-T in the strict upper triangle (E[r][c], r < c), diag(E) = 1/diag(L) in dinv.
-// Blocked by SB = 16 columns: (A) one warp factors + inverts the 16x16 diagonal sub-block, (B) one thread per row
-// applies L_d^-T to the sub-panel, (C) all threads apply the rank-16 trailing update with 4x4 register tiles.
-// -------------------------------------------------------------------------------------------------------------
-constexpr int TP = NB + 1;
-constexpr int SB = 16;
-constexpr int PVP = SB + 1;
-
-__global__ void __launch_bounds__(256, 1)
-potrf_diag_kernel(double *__restrict__ A, int ld, int k0, int nb, double *__restrict__ invL, LMState *state, int *fail_flag) {
-    if (state && state->done) return;
-    extern __shared__ __align__(16) double T[];       // [NB][TP] + dinv[NB] + Pv[NB][PVP]
-    double *dinv = T + NB * TP;
-    double *Pv = dinv + NB;
+    const unsigned FULL = 0xffffffffu;
     __shared__ int s_bad;
-    const int tid = threadIdx.x;
     if (tid == 0) s_bad = 0;
-    for (int idx = tid; idx < NB * NB; idx += 256) {
-        const int i = idx / NB, j = idx % NB;
-        double v = (i == j) ? 1.0 : 0.0;
-        if (i < nb && j < nb && j <= i) v = A[(size_t)(k0 + i) * ld + k0 + j];
-        T[i * TP + j] = v;
-    }
     __syncthreads();
-    for (int j0 = 0; j0 < NB; j0 += SB) {
-        // ---- (A) 16x16 diagonal sub-block: potrf + inverse, warp 0 ----
-        if (tid < 32) {
-            const int i = tid;
-            for (int j = 0; j < SB; ++j) {
-                double d = T[(j0 + j) * TP + j0 + j];
-                const bool bad = !(d > 0.0) || !isfinite(d);
-                if (bad) d = 1.0;
-                const double sd = sqrt(d), inv = 1.0 / sd;
-                __syncwarp();
-                if (bad && i == 0) s_bad = 1;
-                if (i < SB && i > j) T[(j0 + i) * TP + j0 + j] *= inv;
-                if (i == j) { T[(j0 + j) * TP + j0 + j] = sd; dinv[j0 + j] = inv; }
-                __syncwarp();
-                if (i < SB && i > j) {
-                    const double lij = T[(j0 + i) * TP + j0 + j];
-                    for (int c = j + 1; c <= i; ++c) T[(j0 + i) * TP + j0 + c] -= lij * T[(j0 + c) * TP + j0 + j];
+    for (int c0 = 0; c0 < NB; c0 += PB) {
+        // ---- (A) ----
+        if (warp == 0) {
+            double a[PB];
+            const double *row = Ts + (size_t)(c0 + lane) * LDT + c0;
+#pragma unroll
+            for (int k = 0; k < PB; ++k) a[k] = row[k];
+            bool bad = false;
+#pragma unroll
+            for (int j = 0; j < PB; ++j) {
+                double d = __shfl_sync(FULL, a[j], j);
+                if (!(d > 0.0) || isinf(d)) { d = 1.0; bad = true; }
+                const double s = sqrt(d), inv = 1.0 / s;
+                if (lane == 0) dinv[c0 + j] = inv;
+                a[j] = (lane == j) ? s : a[j] * inv;
+#pragma unroll
+                for (int c = j + 1; c < PB; ++c) {
+                    const double lc = __shfl_sync(FULL, a[j], c);
+                    a[c] = fma(-a[j], lc, a[c]);
                 }
-                __syncwarp();
             }
-            if (i < SB) {
-                // lane c: column c of X = L_d^-1, stored transposed in the strict upper triangle
-                const int c = i;
-                const double xc = dinv[j0 + c];
-                for (int ii = 1; ii < SB; ++ii) {
-                    double acc = 0.0;
-                    for (int k = 0; k < ii; ++k) {
-                        const double lik = T[(j0 + ii) * TP + j0 + k];
-                        if (k >= c) acc += lik * ((k == c) ? xc : T[(j0 + c) * TP + j0 + k]);
+            if (bad && lane == 0) s_bad = 1;
+            __syncwarp();
+            // lane = column c of X = L_d^-1 by forward substitution; x[i] = 0 for i < lane falls out of the recurrence
+            double x[PB];
+#pragma unroll
+            for (int i = 0; i < PB; ++i) {
+                double acc = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+                for (int k = 0; k < i; ++k) {
+                    const double lik = __shfl_sync(FULL, a[k], i);
+                    acc = fma(-lik, x[k], acc);
+                }
+                x[i] = acc * dinv[c0 + i];
+            }
+            double *trow = Ts + (size_t)(c0 + lane) * LDT + c0;
+            double *prow = Pv + (size_t)(c0 + lane) * LDP;
+#pragma unroll
+            for (int k = 0; k < PB; ++k) {
+                if (k <= lane) trow[k] = a[k];          // L_d (lower, diag)
+                else trow[k] = x[k];                    // E block = (L_d^-1)^T, strict upper: E[r][c] = X[c][r]
+                prow[k] = x[k];                         // E row incl. its diagonal (1 / l_rr) and zeros left of it
+                invd[(size_t)k * LDP + lane] = x[k];    // X row-major: X[k][lane]
+            }
+        }
+        __syncthreads();
+        // ---- (B) rows outside the diagonal block: 96 rows = 12 m-tiles of 8 ----
+        for (int mt = warp; mt < (NB - PB) / 8; mt += 8) {
+            const int r = mt * 8 + g;
+            const int xrow = r < c0 ? r : r + PB;
+            double af[PB / 4];
+#pragma unroll
+            for (int ks = 0; ks < PB / 4; ++ks) af[ks] = Ts[(size_t)xrow * LDT + c0 + ks * 4 + tig];
+            double o[PB / 8][2];
+#pragma unroll
+            for (int nt = 0; nt < PB / 8; ++nt) o[nt][0] = o[nt][1] = 0.0;
+#pragma unroll
+            for (int ks = 0; ks < PB / 4; ++ks)
+#pragma unroll
+                for (int nt = 0; nt < PB / 8; ++nt)
+                    dmma884(o[nt][0], o[nt][1], af[ks], invd[(size_t)(nt * 8 + g) * LDP + ks * 4 + tig]);
+            __syncwarp();
+#pragma unroll
+            for (int nt = 0; nt < PB / 8; ++nt) {
+                const int col = nt * 8 + 2 * tig;
+                Ts[(size_t)xrow * LDT + c0 + col] = o[nt][0];
+                Ts[(size_t)xrow * LDT + c0 + col + 1] = o[nt][1];
+                Pv[(size_t)xrow * LDP + col] = o[nt][0];
+                Pv[(size_t)xrow * LDP + col + 1] = o[nt][1];
+            }
+        }
+        __syncthreads();
+        // ---- (C) trailing columns c >= c0 + 32 ----
+        const int nb0 = (c0 + PB) / 8, nbn = NB / 8 - nb0;
+        for (int idx = warp; idx < (NB / 8) * nbn; idx += 8) {
+            const int am = idx / nbn, bn = nb0 + idx % nbn;
+            if (!(8 * am < c0 + PB || am >= bn)) continue;
+            double o0 = 0.0, o1 = 0.0;
+#pragma unroll
+            for (int ks = 0; ks < PB / 4; ++ks)
+                dmma884(o0, o1, Pv[(size_t)(am * 8 + g) * LDP + ks * 4 + tig], Pv[(size_t)(bn * 8 + g) * LDP + ks * 4 + tig]);
+            const int x = am * 8 + g, c = bn * 8 + 2 * tig;
+            if (x < c0 + PB || x >= c) Ts[(size_t)x * LDT + c] -= o0;
+            if (x < c0 + PB || x >= c + 1) Ts[(size_t)x * LDT + c + 1] -= o1;
+        }
+        __syncthreads();
+    }
+    return s_bad != 0;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// The dataflow kernel
+// -------------------------------------------------------------------------------------------------------------
+// one k-slice (16 columns) of a 128-row operand tile into shared memory: 128 x 8 16-byte segments, 4 per thread
+__device__ __forceinline__ void load_slice(double *__restrict__ dst, const double *__restrict__ src, int ld, int tid) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int idx = tid + 256 * r;
+        const int row = idx >> 3, seg = idx & 7;
+        cp_async16(dst + (size_t)row * SPAD + seg * 2, src + (size_t)row * ld + seg * 2);
+    }
+}
+
+// acc += A_s (128 x 16, stride lda_s) * B_s^T (128 x 16, stride SPAD): warp (wm, wn) owns a 64 x 32 sub-tile
+__device__ __forceinline__ void mma_slice(double (&acc)[8][4][2], const double *__restrict__ a_s, int lda_s,
+                                          const double *__restrict__ b_s) {
+#pragma unroll
+    for (int ks = 0; ks < BK / 4; ++ks) {
+        double a[8], b[4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = a_s[(size_t)i * 8 * lda_s + ks * 4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = b_s[(size_t)j * 8 * SPAD + ks * 4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    }
+}
+
+__global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
+    if (p.state && p.state->done) return;
+    extern __shared__ __align__(16) double smem[];
+    double *tileC = smem;                                  // [128][LDT]   (main loop: part of the ring)
+    double *scratch = smem + TILE_DOUBLES;                 // epilogue ring (2 stages of B) / potrf scratch
+    double *Pv = scratch, *invd = scratch + NB * LDP, *dinv = invd + PB * LDP;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp >> 2, wn = warp & 3;               // 2 x 4 warps -> 64 x 32 per warp
+    const int g = lane >> 2, tig = lane & 3;
+    const int T = p.T, TR = p.T + 1, ld = p.ld;
+    const int ntasks = T * (T + 1) / 2 + T;                // lower triangle of T x T + the rhs tile row
+    bool aborted = false;
+
+    // ================= phase 1: factorisation + forward substitution =================
+    int j = 0, colbase = 0;
+    for (int t = blockIdx.x; t < ntasks && !aborted; t += gridDim.x) {
+        while (t >= colbase + (TR - j)) { colbase += TR - j; ++j; }
+        const int i = j + (t - colbase);
+        const bool diag = (i == j);
+        double acc[8][4][2];
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+        const double *Arow = p.A + (size_t)i * NB * ld;    // row panel i
+        const double *Brow = p.A + (size_t)j * NB * ld;    // row panel j
+        const int nk = j * (NB / BK);                      // k-slices of the bulk update
+        int have = 0;                                      // k-blocks known to be final in both row panels
+        auto ensure = [&](int kb) -> bool {                // L_ik and L_jk final for k-block kb
+            if (kb < have) return true;
+            if (!wait_ge(p.rowdone + i, kb + 1, p.abort_flag)) return false;
+            if (!diag && !wait_ge(p.rowdone + j, kb + 1, p.abort_flag)) return false;
+            const int hi = ld_acquire(p.rowdone + i), hj = diag ? hi : ld_acquire(p.rowdone + j);
+            have = min(min(hi, hj), j);
+            return true;
+        };
+        auto issue = [&](int kt) {
+            double *st = smem + (size_t)(kt % NSTAGE) * STAGE_DOUBLES;
+            load_slice(st, Arow + (size_t)kt * BK, ld, tid);
+            if (!diag) load_slice(st + NB * SPAD, Brow + (size_t)kt * BK, ld, tid);
+        };
+        // prologue
+        for (int s = 0; s < NSTAGE - 1; ++s) {
+            if (s < nk) {
+                if ((s & 7) == 0 && !ensure(s >> 3)) { aborted = true; }
+                if (!aborted) issue(s);
+            }
+            cp_async_commit();
+        }
+        for (int kt = 0; kt < nk; ++kt) {
+            cp_async_wait<NSTAGE - 2>();
+            __syncthreads();
+            const int nx = kt + NSTAGE - 1;
+            if (nx < nk && !aborted) {
+                if ((nx & 7) == 0 && !ensure(nx >> 3)) aborted = true;
+                if (!aborted) issue(nx);
+            }
+            cp_async_commit();
+            const double *st = smem + (size_t)(kt % NSTAGE) * STAGE_DOUBLES;
+            const double *a_s = st + (size_t)(wm * 64 + g) * SPAD + tig;
+            const double *b_s = (diag ? st : st + NB * SPAD) + (size_t)(wn * 32 + g) * SPAD + tig;
+            mma_slice(acc, a_s, SPAD, b_s);
+        }
+        cp_async_wait<0>();
+        aborted = __syncthreads_or(aborted);
+        if (aborted) break;
+
+        // C = A_ij - acc  -> shared tile
+        {
+            const double *Cg = p.A + (size_t)(i * NB) * ld + (size_t)j * NB;
+#pragma unroll
+            for (int a = 0; a < 8; ++a) {
+                const int row = wm * 64 + a * 8 + g;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int col = wn * 32 + b * 8 + 2 * tig;
+                    double2 v = *reinterpret_cast<const double2 *>(Cg + (size_t)row * ld + col);
+                    v.x -= acc[a][b][0]; v.y -= acc[a][b][1];
+                    if (diag) {                            // strict upper starts as the zero part of [A; I]'s identity
+                        if (col > row) v.x = 0.0;
+                        if (col + 1 > row) v.y = 0.0;
                     }
-                    if (ii > c) T[(j0 + c) * TP + j0 + ii] = -acc * dinv[j0 + ii];
+                    *reinterpret_cast<double2 *>(tileC + (size_t)row * LDT + col) = v;
                 }
             }
         }
         __syncthreads();
-        // ---- (B) sub-panel rows: x <- x * L_d^-T ; x < j0: rows of E, x >= j0 + SB: rows of L ----
-        if (tid < NB) {
-            const int x = tid;
-            double w[SB];
-            if (x < j0 || x >= j0 + SB) {
-                double v[SB];
-#pragma unroll
-                for (int k = 0; k < SB; ++k) v[k] = T[x * TP + j0 + k];
-#pragma unroll
-                for (int k = 0; k < SB; ++k) {
-                    double acc = v[k] * dinv[j0 + k];
-#pragma unroll
-                    for (int m = 0; m < k; ++m) acc += v[m] * T[(j0 + m) * TP + j0 + k];
-                    w[k] = acc;
-                }
-#pragma unroll
-                for (int k = 0; k < SB; ++k) T[x * TP + j0 + k] = w[k];
-            } else {
-#pragma unroll
-                for (int k = 0; k < SB; ++k) w[k] = (x < j0 + k) ? T[x * TP + j0 + k] : ((x == j0 + k) ? dinv[x] : 0.0);
+        if (diag) {
+            const bool bad = potrf_inverse_tile(tileC, Pv, invd, dinv);
+            double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
+            double *Ig = p.invL + (size_t)j * NB * NB;
+            for (int idx = tid; idx < NB * NB; idx += 256) {
+                const int r = idx >> 7, c = idx & (NB - 1);
+                if (c <= r) Lg[(size_t)r * ld + c] = tileC[(size_t)r * LDT + c];
+                Ig[idx] = (c < r) ? tileC[(size_t)c * LDT + r] : (c == r ? dinv[r] : 0.0);
             }
-#pragma unroll
-            for (int k = 0; k < SB; ++k) Pv[x * PVP + k] = w[k];
-        }
-        __syncthreads();
-        // ---- (C) trailing update of columns c >= j0 + SB: rows x < j0 + SB (E) and x >= c (L) ----
-        const int c_begin = j0 + SB;
-        const int ntask = 32 * ((NB - c_begin) / 4);
-        for (int t = tid; t < ntask; t += 256) {
-            const int tx = t & 31, c0 = c_begin + (t >> 5) * 4;
-            double acc[4][4];
-#pragma unroll
-            for (int r = 0; r < 4; ++r)
-#pragma unroll
-                for (int q = 0; q < 4; ++q) acc[r][q] = 0.0;
-#pragma unroll 4
-            for (int k = 0; k < SB; ++k) {
-                double a[4], b[4];
-#pragma unroll
-                for (int r = 0; r < 4; ++r) a[r] = Pv[(tx + 32 * r) * PVP + k];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) b[q] = Pv[(c0 + q) * PVP + k];
-#pragma unroll
-                for (int r = 0; r < 4; ++r)
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) acc[r][q] += a[r] * b[q];
+            if (bad && tid == 0) {
+                if (p.state) p.state->chol_fail = 1;
+                if (p.fail_flag) *p.fail_flag = 1;
             }
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) { st_release(p.diagdone + j, 1); st_release(p.rowdone + j, j + 1); }
+        } else {
+            // L_ij = C * L_jj^-T : A operand = the staged tile, B operand = invL_j through a 2-stage ring
+            if (!wait_ge(p.diagdone + j, 1, p.abort_flag)) aborted = true;
+            aborted = __syncthreads_or(aborted);
+            if (aborted) break;
+            const double *Ig = p.invL + (size_t)j * NB * NB;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int x = tx + 32 * r;
+            for (int a = 0; a < 8; ++a)
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int c = c0 + q;
-                    if (x < c_begin || x >= c) T[x * TP + c] -= acc[r][q];
+                for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+            load_slice(scratch, Ig, NB, tid);
+            cp_async_commit();
+            for (int kt = 0; kt < NB / BK; ++kt) {
+                if (kt + 1 < NB / BK) load_slice(scratch + (size_t)((kt + 1) & 1) * NB * SPAD, Ig + (size_t)(kt + 1) * BK, NB, tid);
+                cp_async_commit();
+                cp_async_wait<1>();
+                __syncthreads();
+                const double *a_s = tileC + (size_t)(wm * 64 + g) * LDT + kt * BK + tig;
+                const double *b_s = scratch + (size_t)(kt & 1) * NB * SPAD + (size_t)(wn * 32 + g) * SPAD + tig;
+                mma_slice(acc, a_s, LDT, b_s);
+                __syncthreads();
+            }
+            double *Cg = p.A + (size_t)(i * NB) * ld + (size_t)j * NB;
+#pragma unroll
+            for (int a = 0; a < 8; ++a) {
+                const int row = wm * 64 + a * 8 + g;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int col = wn * 32 + b * 8 + 2 * tig;
+                    *reinterpret_cast<double2 *>(Cg + (size_t)row * ld + col) = make_double2(acc[a][b][0], acc[a][b][1]);
                 }
             }
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) st_release(p.rowdone + i, j + 1);
         }
-        __syncthreads();
     }
-    // write L back (lower triangle of the block)
-    for (int idx = tid; idx < nb * nb; idx += 256) {
-        const int i = idx / nb, j = idx % nb;
-        if (j <= i) A[(size_t)(k0 + i) * ld + k0 + j] = T[i * TP + j];
+    if (aborted) {
+        if (tid == 0) {
+            if (p.state) p.state->chol_fail = 1;
+            if (p.fail_flag) *p.fail_flag = 1;
+        }
+        return;
     }
-    // invL: full NB x NB row-major, zeros above the diagonal; X[i][c] = E[c][i]
-    for (int idx = tid; idx < NB * NB; idx += 256) {
-        const int i = idx / NB, c = idx % NB;
-        double v = 0.0;
-        if (i == c) v = dinv[c];
-        else if (i > c) v = T[c * TP + i];
-        invL[idx] = v;
-    }
-    if (tid == 0 && s_bad) {
-        if (state) state->chol_fail = 1;
-        if (fail_flag) *fail_flag = 1;
-    }
-}
 
-// Backward substitution L^T y = z, one launch per block row k (descending).  z lives in row n of A.
-// Every CTA recomputes y_k = L_kk^-T z_k (128 x 128 GEMV from the stored inverse), then owns 64 columns of the
-// update z[col] -= sum_r L[k0 + r][col] y_k[r], rows split over 4 thread groups.
-__global__ void __launch_bounds__(256)
-back_solve_kernel(double *__restrict__ A, int ld, int n, int k0, int nb, const double *__restrict__ invL,
-                  double *__restrict__ y, const LMState *state) {
-    if (state && state->done) return;
-    __shared__ double ys[NB];
-    __shared__ double part[4][64];
-    __shared__ double yp[2][NB];
-    double *z = A + (size_t)n * ld;
-    const int tid = threadIdx.x;
-    {
-        // y_k[c] = sum_{r >= c} invL[r][c] * z[k0 + r]; two threads per column (even / odd r)
+    // ================= phase 2: back substitution L^T y = z (z = row n_pad of A) =================
+    double *zs = smem;                 // [128] running z_m
+    double *ys = smem + NB;            // [128] y_k being applied
+    double *part = smem + 2 * NB;      // [2][128]
+    const double *z = p.A + (size_t)T * NB * ld;
+    for (int m = T - 1 - (int)blockIdx.x; m >= 0; m -= gridDim.x) {
+        // z_m is final once tile (T, m) is; L_km tiles are final once row k reached column m
+        if (!__syncthreads_and(wait_ge(p.rowdone + T, m + 1, p.abort_flag) && wait_ge(p.diagdone + m, 1, p.abort_flag))) break;
+        if (tid < NB) zs[tid] = __ldcg(z + (size_t)m * NB + tid);
         const int c = tid & (NB - 1), half = tid >> 7;
-        double acc = 0.0;
-        if (c < nb)
-            for (int r = c + half; r < nb; r += 2) acc += invL[r * NB + c] * z[k0 + r];
-        yp[half][c] = acc;
+        bool ok = true;
+        for (int k = T - 1; k > m; --k) {
+            ok = wait_ge(p.ydone + k, 1, p.abort_flag) && wait_ge(p.rowdone + k, m + 1, p.abort_flag);
+            if (!__syncthreads_and(ok)) { ok = false; break; }
+            if (tid < NB) ys[tid] = __ldcg(p.ypad + (size_t)k * NB + tid);
+            __syncthreads();
+            const double *Lkm = p.A + (size_t)(k * NB + half * 64) * ld + (size_t)m * NB + c;
+            double accv = 0.0;
+#pragma unroll 16
+            for (int r = 0; r < 64; ++r) accv = fma(__ldcg(Lkm + (size_t)r * ld), ys[half * 64 + r], accv);
+            part[half * NB + c] = accv;
+            __syncthreads();
+            if (tid < NB) zs[tid] -= part[tid] + part[NB + tid];
+        }
+        if (!ok) break;
+        __syncthreads();
+        // y_m[c] = sum_{r >= c} invL_m[r][c] z_m[r]
+        const double *Ig = p.invL + (size_t)m * NB * NB;
+        double accv = 0.0;
+        for (int r = max(c, half * 64); r < half * 64 + 64; ++r) accv = fma(__ldcg(Ig + (size_t)r * NB + c), zs[r], accv);
+        part[half * NB + c] = accv;
+        __syncthreads();
+        if (tid < NB) {
+            const double v = part[tid] + part[NB + tid];
+            p.ypad[(size_t)m * NB + tid] = v;
+            if (m * NB + tid < p.n) p.y[m * NB + tid] = v;
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) st_release(p.ydone + m, 1);
     }
-    __syncthreads();
-    if (tid < NB) ys[tid] = yp[0][tid] + yp[1][tid];
-    __syncthreads();
-    if (blockIdx.x == 0 && tid < nb) y[k0 + tid] = ys[tid];
-    const int cl = tid & 63, rg = tid >> 6;
-    const int col = blockIdx.x * 64 + cl;
-    double acc = 0.0;
-    if (col < k0) {
-        const int r_lo = rg * 32, r_hi = min(nb, r_lo + 32);
-        const double *src = A + (size_t)(k0 + r_lo) * ld + col;
-#pragma unroll 8
-        for (int r = r_lo; r < r_hi; ++r, src += ld) acc += (*src) * ys[r];
-    }
-    part[rg][cl] = acc;
-    __syncthreads();
-    if (tid < 64 && col < k0) z[col] -= part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
 }
 
-static const int GEMM_SMEM = 2 * (BM + BN) * SPAD * (int)sizeof(double);     // 81920
-static const int POTRF_SMEM = (NB * TP + NB + NB * PVP) * (int)sizeof(double);   // 150528
+// -------------------------------------------------------------------------------------------------------------
+// host side
+// -------------------------------------------------------------------------------------------------------------
+static int g_chol_grid[64];     // per device: co-resident CTAs (0 = not initialised)
 
 int chol_init() {
-    cudaError_t e;
-    e = cudaFuncSetAttribute(gemm_nt_kernel<MODE_SET, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(gemm_nt_kernel<MODE_SUB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    if (g_chol_grid[dev]) return 0;
+    e = cudaFuncSetAttribute(chol_dataflow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CHOL_SMEM);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, POTRF_SMEM);
-    return (int)e;
+    int coop = 0, sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (!coop) return (int)cudaErrorNotSupported;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_dataflow_kernel, 256, CHOL_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
+    g_chol_grid[dev] = sms;       // one CTA per SM (shared memory allows exactly one)
+    return 0;
 }
 
-void chol_factor_solve(double *A, int n, double *invL, double *y, LMState *state, int *fail_flag, cudaStream_t s) {
-    const int M = n + 1;                 // rows including the rhs row
-    const int nblk = (n + NB - 1) / NB;
-    for (int kb = 0; kb < nblk; ++kb) {
-        const int k0 = kb * NB;
-        const int nb = (n - k0 < NB) ? (n - k0) : NB;
-        double *inv = invL + (size_t)kb * NB * NB;
-        potrf_diag_kernel<<<1, 256, POTRF_SMEM, s>>>(A, n, k0, nb, inv, state, fail_flag);
-        const int r0 = k0 + nb;          // first row below the diagonal block
-        const int rows = M - r0;         // >= 1 (the rhs row)
-        // panel: A[r0.., k0..k0+nb) <- A * invL^T
-        {
-            const int tiles_m = (rows + BM - 1) / BM;
-            gemm_nt_kernel<MODE_SET, false><<<tiles_m, 256, GEMM_SMEM, s>>>(
-                A + (size_t)r0 * n + k0, n, inv, NB, A + (size_t)r0 * n + k0, n, rows, nb, nb, 1, state);
-        }
-        // trailing update: lower tiles of A[r0.., r0..n) -= P P^T with P = A[r0.., k0..k0+nb)
-        const int cols = n - r0;
-        if (cols > 0) {
-            const int t = (rows + BM - 1) / BM;            // tile rows (rows >= cols, same tile origin)
-            const int tiles = t * (t + 1) / 2;
-            gemm_nt_kernel<MODE_SUB, true><<<tiles, 256, GEMM_SMEM, s>>>(
-                A + (size_t)r0 * n + k0, n, A + (size_t)r0 * n + k0, n, A + (size_t)r0 * n + r0, n, rows, cols, nb, 0, state);
-        }
-    }
-    for (int kb = nblk - 1; kb >= 0; --kb) {
-        const int k0 = kb * NB;
-        const int nb = (n - k0 < NB) ? (n - k0) : NB;
-        const int blocks = (k0 + 63) / 64 > 0 ? (k0 + 63) / 64 : 1;
-        back_solve_kernel<<<blocks, 256, 0, s>>>(A, n, n, k0, nb, invL + (size_t)kb * NB * NB, y, state);
-    }
+int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, cudaStream_t s) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int ld = chol_ld(n), T = ld / NB;
+    CholArgs p;
+    p.A = A; p.ld = ld; p.T = T; p.n = n;
+    p.invL = work;
+    p.ypad = work + (size_t)T * NB * NB;
+    int *flags = reinterpret_cast<int *>(p.ypad + (size_t)T * NB);
+    p.rowdone = flags; p.diagdone = flags + (T + 1); p.ydone = p.diagdone + T; p.abort_flag = p.ydone + T;
+    p.y = y; p.state = state; p.fail_flag = fail_flag;
+    cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)chol_flag_count(T), s);
+    if (e != cudaSuccess) return (int)e;
+    const int ntasks = T * (T + 3) / 2;
+    int grid = g_chol_grid[dev] < ntasks ? g_chol_grid[dev] : ntasks;
+    if (grid < 1) return (int)cudaErrorInitializationError;
+    void *args[] = {&p};
+    e = cudaLaunchCooperativeKernel((const void *)chol_dataflow_kernel, dim3(grid), dim3(256), args, CHOL_SMEM, s);
+    return (int)e;
 }
 
 } // namespace ba

@@ -292,10 +292,11 @@ __global__ void schur_init_kernel(Ctx ctx, double radius_override) {
     const LMState *st = ctx.state;
     if (radius_override <= 0 && st->done) return;
     const double radius = radius_override > 0 ? radius_override : st->radius;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (camera, row a)
-    if (i >= 6 * ctx.Nc) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (camera, row a) + the padding rows
+    if (i >= ctx.ldS) return;
+    if (i >= 6 * ctx.Nc) { ctx.S[(size_t)i * ctx.ldS + i] = 1.0; return; }     // identity padding up to the tile edge
     const int c = i / 6, a = i % 6;
-    double *row = ctx.S + (size_t)i * ctx.n + 6 * (size_t)c;
+    double *row = ctx.S + (size_t)i * ctx.ldS + 6 * (size_t)c;
     const bool lead = ctx.rank == 0;
     if (ctx.cam_kind[c] == CAM_FREE) {
         const double *U = ctx.U + 36 * (size_t)c;
@@ -321,7 +322,7 @@ __global__ void __launch_bounds__(128) schur_accum_kernel(Ctx ctx, int force) {
     const double vi[6] = {Vi[0], Vi[1], Vi[2], Vi[3], Vi[4], Vi[5]};
     const double *wv = ctx.wv + 3 * (size_t)p;
     const double w3[3] = {wv[0], wv[1], wv[2]};
-    const int n = ctx.n;
+    const int n = ctx.ldS;
     for (int i = o0; i < o1; ++i) {
         const int ci = ctx.pm_cam[i];
         if (ctx.cam_kind[ci] != CAM_FREE) continue;
@@ -687,8 +688,8 @@ void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s)
 
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) {
     const int force = radius_override > 0;
-    cudaMemsetAsync(ctx.S, 0, sizeof(double) * (size_t)ctx.n * ctx.n, s);
-    schur_init_kernel<<<cdiv(6 * ctx.Nc, 128), 128, 0, s>>>(ctx, radius_override);
+    cudaMemsetAsync(ctx.S, 0, sizeof(double) * chol_matrix_doubles(ctx.n), s);
+    schur_init_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, radius_override);
     schur_accum_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, force);
 }
 

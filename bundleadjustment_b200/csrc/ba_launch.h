@@ -20,19 +20,18 @@ void launch_backsub(const Ctx &ctx, cudaStream_t s);
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
 void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s);
 
-// ba_cholesky.cu -- dense SPD factorisation + solve of the reduced camera system (C6)
-struct CholWork {
-    double *invL = nullptr;     // [nblk][NB*NB] inverses of the diagonal blocks
-    int n = 0;
-    size_t bytes() const;
-};
+// ba_cholesky.cu -- dense SPD factorisation + solve of the reduced camera system (C6), one cooperative kernel
 constexpr int CHOL_NB = 128;
-int chol_init();                                        // one-time kernel attribute setup; returns cudaError
+int chol_init();                                        // per-device kernel attribute setup; returns cudaError
+int chol_ld(int n);                                     // n_pad = ceil(n / 128) * 128 = leading dimension
+size_t chol_rows(int n);                                // n_pad + 128 rows
+size_t chol_matrix_doubles(int n);                      // rows * ld
 size_t chol_work_doubles(int n);
-// A: (n+1) x n row-major (ld = n), lower triangle valid, row n = rhs^T.  On exit y (n) holds the solution.
-// state may be nullptr (standalone use); otherwise kernels early-exit on state->done and report breakdown in
-// state->chol_fail.  fail_flag (device int, may be nullptr) is set on breakdown as well.
-void chol_factor_solve(double *A, int n, double *invL, double *y, LMState *state, int *fail_flag, cudaStream_t s);
+// A: chol_rows(n) x chol_ld(n) row-major: lower triangle of the leading n x n block = S, rows/cols [n, n_pad) identity
+// padding, row n_pad = rhs^T, all other rows zero.  On exit y (n) holds the solution and A's lower triangle holds L.
+// state may be nullptr (standalone use); otherwise the kernel early-exits on state->done and reports breakdown in
+// state->chol_fail.  fail_flag (device int, may be nullptr) is set on breakdown as well.  Returns a cudaError.
+int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, cudaStream_t s);
 
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s);       // local block-diag(S) + rhs (all-reduce Minv, rhs after)

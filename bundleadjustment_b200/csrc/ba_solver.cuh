@@ -97,7 +97,8 @@ struct Ctx {
     double *Vinv;            // [Np][6]
     double *wv;              // [Np][3] = Vinv * bp
     // reduced system
-    double *S;               // [n][n] row-major, lower blocks
+    double *S;               // [chol_rows(n)][ldS] row-major, lower blocks; row ldS = rhs^T (see ba_cholesky.cu)
+    int ldS;                 // leading dimension = n rounded up to the Cholesky tile (128)
     double *rhs;             // [n] (becomes y_c after the solve)
     double *yc;              // [n]
     // partial sums
