@@ -75,6 +75,16 @@ __device__ __forceinline__ void st_release(int *p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
 
+// 1 / d to ~1 ulp: MUFU seed (20+ bits) + two Newton steps; d must be a normal positive number
+__device__ __forceinline__ double fast_rcp(double d) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;\n" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-d, r, 1.0);
+    return fma(r, e, r);
+}
+
 struct CholArgs {
     double *A;            // (n_pad + 128) x n_pad
     int ld;               // n_pad
@@ -89,6 +99,7 @@ struct CholArgs {
     double *y;            // [n]
     LMState *state;       // may be nullptr
     int *fail_flag;       // may be nullptr
+    long long *prof;      // may be nullptr; [grid][8] ns: start, phase-1 end, end, waited (ph 1), waited (ph 2), potrf, tasks, trsm
 };
 
 constexpr long long SPIN_TIMEOUT_NS = 4000000000LL;    // 4 s
@@ -100,13 +111,13 @@ __device__ __forceinline__ long long global_ns() {
 }
 
 // spin until *flag >= need; returns false if aborted (every thread polls for itself: its own cp.asyncs follow)
-__device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_flag) {
+__device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_flag, long long &waited) {
     if (ld_acquire(flag) >= need) return true;
     const long long t0 = global_ns();
     unsigned spins = 0;
     while (true) {
         __nanosleep(64);
-        if (ld_acquire(flag) >= need) return true;
+        if (ld_acquire(flag) >= need) { waited += global_ns() - t0; return true; }
         if ((++spins & 255u) == 0) {
             if (ld_acquire(abort_flag)) return false;
             if (global_ns() - t0 > SPIN_TIMEOUT_NS) { atomicExch(abort_flag, 1); return false; }
@@ -125,15 +136,18 @@ __device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_fl
 // Non-positive / non-finite pivots are replaced by 1 and reported (no hang, Ceres' LINEAR_SOLVER_FAILURE semantics
 // are applied by the LM controller).
 // -------------------------------------------------------------------------------------------------------------
+__device__ long long g_potrf_phase[4];   // tools/chol_prof.cu: accumulated ns in (A), (B), (C), calls
+
 __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double *__restrict__ Pv, double *__restrict__ invd,
                                                 double *__restrict__ dinv) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tig = lane & 3;
-    const unsigned FULL = 0xffffffffu;
     __shared__ int s_bad;
     if (tid == 0) s_bad = 0;
     __syncthreads();
+    long long tA = 0, tB = 0, tC = 0;
     for (int c0 = 0; c0 < NB; c0 += PB) {
+        const long long t0 = global_ns();
         // ---- (A) ----
         if (warp == 0) {
             double a[PB];
@@ -141,44 +155,69 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 #pragma unroll
             for (int k = 0; k < PB; ++k) a[k] = row[k];
             bool bad = false;
+            // Square-root-free sweep (L D L^T): only a reciprocal sits on the serial pivot chain.  Column j of the
+            // current matrix is broadcast through shared memory (one store per lane, 16-byte broadcast loads) instead of
+            // 2 x (31 - j) shuffles; column j of the unit factor stays UNSCALED in a[j] (= l_ij d_j).
+            double *Lcol = invd;                             // [j][c], stride LDP (invd is rewritten at the end of (A))
+            double myd = 1.0;                                // d_lane
 #pragma unroll
             for (int j = 0; j < PB; ++j) {
-                double d = __shfl_sync(FULL, a[j], j);
-                if (!(d > 0.0) || isinf(d)) { d = 1.0; bad = true; }
-                const double s = sqrt(d), inv = 1.0 / s;
-                if (lane == 0) dinv[c0 + j] = inv;
-                a[j] = (lane == j) ? s : a[j] * inv;
+                Lcol[j * LDP + lane] = a[j];
+                __syncwarp();
+                double d = Lcol[j * LDP + j];
+                if (!(d > 1e-300) || isinf(d)) { d = 1.0; bad = true; }
+                const double rd = fast_rcp(d);
+                if (lane == j) myd = d;
+                const double ajs = a[j] * rd;
+                if (((j + 1) & 1) && j + 1 < PB) a[j + 1] = fma(-ajs, Lcol[j * LDP + j + 1], a[j + 1]);
 #pragma unroll
-                for (int c = j + 1; c < PB; ++c) {
-                    const double lc = __shfl_sync(FULL, a[j], c);
-                    a[c] = fma(-a[j], lc, a[c]);
+                for (int c = (j + 2) & ~1; c < PB; c += 2) {          // 16-byte broadcast loads of column pairs
+                    const double2 ac = *reinterpret_cast<const double2 *>(Lcol + j * LDP + c);
+                    a[c] = fma(-ajs, ac.x, a[c]);
+                    a[c + 1] = fma(-ajs, ac.y, a[c + 1]);
                 }
+            }
+            // L = (unit factor) * sqrt(D): l_ij = a_ij / sqrt(d_j)
+            const double mys = sqrt(myd), myis = 1.0 / mys;
+            dinv[c0 + lane] = myis;
+            __syncwarp();
+            double *trow = Ts + (size_t)(c0 + lane) * LDT + c0;
+            double *LT = invd;                               // [k][i] = l_ik: rows of L^T, contiguous in i
+#pragma unroll
+            for (int j = 0; j < PB; ++j) {
+                a[j] = (lane == j) ? mys : a[j] * dinv[c0 + j];
+                if (j <= lane) trow[j] = a[j];               // L_d (lower, diag) into the tile
+                LT[j * LDP + lane] = a[j];
             }
             if (bad && lane == 0) s_bad = 1;
             __syncwarp();
-            // lane = column c of X = L_d^-1 by forward substitution; x[i] = 0 for i < lane falls out of the recurrence
+            // lane = column of X = L_d^-1, right-looking forward substitution (independent FMAs per pivot);
+            // x[i] = 0 for i < lane falls out of the recurrence
             double x[PB];
 #pragma unroll
-            for (int i = 0; i < PB; ++i) {
-                double acc = (i == lane) ? 1.0 : 0.0;
+            for (int i = 0; i < PB; ++i) x[i] = (i == lane) ? 1.0 : 0.0;
 #pragma unroll
-                for (int k = 0; k < i; ++k) {
-                    const double lik = __shfl_sync(FULL, a[k], i);
-                    acc = fma(-lik, x[k], acc);
+            for (int k = 0; k < PB; ++k) {
+                x[k] *= dinv[c0 + k];
+                if (((k + 1) & 1) && k + 1 < PB) x[k + 1] = fma(-LT[k * LDP + k + 1], x[k], x[k + 1]);
+#pragma unroll
+                for (int i = (k + 2) & ~1; i < PB; i += 2) {
+                    const double2 l2 = *reinterpret_cast<const double2 *>(LT + k * LDP + i);
+                    x[i] = fma(-l2.x, x[k], x[i]);
+                    x[i + 1] = fma(-l2.y, x[k], x[i + 1]);
                 }
-                x[i] = acc * dinv[c0 + i];
             }
-            double *trow = Ts + (size_t)(c0 + lane) * LDT + c0;
+            __syncwarp();                                    // LT fully consumed before invd is rewritten
             double *prow = Pv + (size_t)(c0 + lane) * LDP;
 #pragma unroll
             for (int k = 0; k < PB; ++k) {
-                if (k <= lane) trow[k] = a[k];          // L_d (lower, diag)
-                else trow[k] = x[k];                    // E block = (L_d^-1)^T, strict upper: E[r][c] = X[c][r]
+                if (k > lane) trow[k] = x[k];           // E block = (L_d^-1)^T, strict upper: E[r][c] = X[c][r]
                 prow[k] = x[k];                         // E row incl. its diagonal (1 / l_rr) and zeros left of it
                 invd[(size_t)k * LDP + lane] = x[k];    // X row-major: X[k][lane]
             }
         }
         __syncthreads();
+        const long long t1 = global_ns();
         // ---- (B) rows outside the diagonal block: 96 rows = 12 m-tiles of 8 ----
         for (int mt = warp; mt < (NB - PB) / 8; mt += 8) {
             const int r = mt * 8 + g;
@@ -205,21 +244,49 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
             }
         }
         __syncthreads();
-        // ---- (C) trailing columns c >= c0 + 32 ----
+        const long long t2 = global_ns();
+        // ---- (C) trailing columns c >= c0 + 32: one m-tile x up to 4 n-tiles per pass (independent DMMA chains) ----
         const int nb0 = (c0 + PB) / 8, nbn = NB / 8 - nb0;
-        for (int idx = warp; idx < (NB / 8) * nbn; idx += 8) {
-            const int am = idx / nbn, bn = nb0 + idx % nbn;
-            if (!(8 * am < c0 + PB || am >= bn)) continue;
-            double o0 = 0.0, o1 = 0.0;
+        const int ngrp = (nbn + 3) / 4;
+        for (int idx = warp; idx < (NB / 8) * ngrp; idx += 8) {
+            const int am = idx / ngrp, bn0 = nb0 + (idx % ngrp) * 4;
+            const bool erow = 8 * am < c0 + PB;
+            if (!erow && am < bn0) continue;                 // every n-tile of the group lies right of the diagonal
+            double af[PB / 4];
+#pragma unroll
+            for (int ks = 0; ks < PB / 4; ++ks) af[ks] = Pv[(size_t)(am * 8 + g) * LDP + ks * 4 + tig];
+            double o[4][2];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) o[q][0] = o[q][1] = 0.0;
 #pragma unroll
             for (int ks = 0; ks < PB / 4; ++ks)
-                dmma884(o0, o1, Pv[(size_t)(am * 8 + g) * LDP + ks * 4 + tig], Pv[(size_t)(bn * 8 + g) * LDP + ks * 4 + tig]);
-            const int x = am * 8 + g, c = bn * 8 + 2 * tig;
-            if (x < c0 + PB || x >= c) Ts[(size_t)x * LDT + c] -= o0;
-            if (x < c0 + PB || x >= c + 1) Ts[(size_t)x * LDT + c + 1] -= o1;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int bn = min(bn0 + q, NB / 8 - 1);
+                    dmma884(o[q][0], o[q][1], af[ks], Pv[(size_t)(bn * 8 + g) * LDP + ks * 4 + tig]);
+                }
+            const int x = am * 8 + g;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int bn = bn0 + q;
+                if (bn >= NB / 8) break;
+                const int c = bn * 8 + 2 * tig;
+                if (erow || x >= c) Ts[(size_t)x * LDT + c] -= o[q][0];
+                if (erow || x >= c + 1) Ts[(size_t)x * LDT + c + 1] -= o[q][1];
+            }
         }
         __syncthreads();
+        const long long t3 = global_ns();
+        tA += t1 - t0; tB += t2 - t1; tC += t3 - t2;
     }
+#ifdef CHOL_PROFILE_PHASES
+    if (tid == 0) {
+        atomicAdd((unsigned long long *)&g_potrf_phase[0], (unsigned long long)tA);
+        atomicAdd((unsigned long long *)&g_potrf_phase[1], (unsigned long long)tB);
+        atomicAdd((unsigned long long *)&g_potrf_phase[2], (unsigned long long)tC);
+        atomicAdd((unsigned long long *)&g_potrf_phase[3], 1ull);
+    }
+#endif
     return s_bad != 0;
 }
 
@@ -265,6 +332,8 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     const int T = p.T, TR = p.T + 1, ld = p.ld;
     const int ntasks = T * (T + 1) / 2 + T;                // lower triangle of T x T + the rhs tile row
     bool aborted = false;
+    long long waited = 0, t_potrf = 0, t_trsm = 0, n_tasks = 0;
+    const long long t_start = global_ns();
 
     // ================= phase 1: factorisation + forward substitution =================
     int j = 0, colbase = 0;
@@ -284,8 +353,8 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         int have = 0;                                      // k-blocks known to be final in both row panels
         auto ensure = [&](int kb) -> bool {                // L_ik and L_jk final for k-block kb
             if (kb < have) return true;
-            if (!wait_ge(p.rowdone + i, kb + 1, p.abort_flag)) return false;
-            if (!diag && !wait_ge(p.rowdone + j, kb + 1, p.abort_flag)) return false;
+            if (!wait_ge(p.rowdone + i, kb + 1, p.abort_flag, waited)) return false;
+            if (!diag && !wait_ge(p.rowdone + j, kb + 1, p.abort_flag, waited)) return false;
             const int hi = ld_acquire(p.rowdone + i), hj = diag ? hi : ld_acquire(p.rowdone + j);
             have = min(min(hi, hj), j);
             return true;
@@ -342,7 +411,9 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         }
         __syncthreads();
         if (diag) {
+            const long long tp0 = global_ns();
             const bool bad = potrf_inverse_tile(tileC, Pv, invd, dinv);
+            t_potrf += global_ns() - tp0;
             double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
             double *Ig = p.invL + (size_t)j * NB * NB;
             for (int idx = tid; idx < NB * NB; idx += 256) {
@@ -359,9 +430,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (tid == 0) { st_release(p.diagdone + j, 1); st_release(p.rowdone + j, j + 1); }
         } else {
             // L_ij = C * L_jj^-T : A operand = the staged tile, B operand = invL_j through a 2-stage ring
-            if (!wait_ge(p.diagdone + j, 1, p.abort_flag)) aborted = true;
+            if (!wait_ge(p.diagdone + j, 1, p.abort_flag, waited)) aborted = true;
             aborted = __syncthreads_or(aborted);
             if (aborted) break;
+            const long long tt0 = global_ns();
             const double *Ig = p.invL + (size_t)j * NB * NB;
 #pragma unroll
             for (int a = 0; a < 8; ++a)
@@ -392,8 +464,11 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             __threadfence();
             __syncthreads();
             if (tid == 0) st_release(p.rowdone + i, j + 1);
+            t_trsm += global_ns() - tt0;
         }
+        ++n_tasks;
     }
+    const long long t_phase1 = global_ns(), waited1 = waited;
     if (aborted) {
         if (tid == 0) {
             if (p.state) p.state->chol_fail = 1;
@@ -409,20 +484,30 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     const double *z = p.A + (size_t)T * NB * ld;
     for (int m = T - 1 - (int)blockIdx.x; m >= 0; m -= gridDim.x) {
         // z_m is final once tile (T, m) is; L_km tiles are final once row k reached column m
-        if (!__syncthreads_and(wait_ge(p.rowdone + T, m + 1, p.abort_flag) && wait_ge(p.diagdone + m, 1, p.abort_flag))) break;
+        if (!__syncthreads_and(wait_ge(p.rowdone + T, m + 1, p.abort_flag, waited) && wait_ge(p.diagdone + m, 1, p.abort_flag, waited))) break;
         if (tid < NB) zs[tid] = __ldcg(z + (size_t)m * NB + tid);
         const int c = tid & (NB - 1), half = tid >> 7;
         bool ok = true;
         for (int k = T - 1; k > m; --k) {
-            ok = wait_ge(p.ydone + k, 1, p.abort_flag) && wait_ge(p.rowdone + k, m + 1, p.abort_flag);
+            ok = wait_ge(p.ydone + k, 1, p.abort_flag, waited) && wait_ge(p.rowdone + k, m + 1, p.abort_flag, waited);
             if (!__syncthreads_and(ok)) { ok = false; break; }
             if (tid < NB) ys[tid] = __ldcg(p.ypad + (size_t)k * NB + tid);
             __syncthreads();
             const double *Lkm = p.A + (size_t)(k * NB + half * 64) * ld + (size_t)m * NB + c;
-            double accv = 0.0;
-#pragma unroll 16
-            for (int r = 0; r < 64; ++r) accv = fma(__ldcg(Lkm + (size_t)r * ld), ys[half * 64 + r], accv);
-            part[half * NB + c] = accv;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+            for (int rb = 0; rb < 64; rb += 32) {
+                double lv[32];
+#pragma unroll
+                for (int r = 0; r < 32; ++r) lv[r] = __ldcg(Lkm + (size_t)(rb + r) * ld);    // 32 loads in flight per thread
+#pragma unroll
+                for (int r = 0; r < 32; r += 4) {
+                    const double *yy = ys + half * 64 + rb + r;
+                    a0 = fma(lv[r], yy[0], a0); a1 = fma(lv[r + 1], yy[1], a1);
+                    a2 = fma(lv[r + 2], yy[2], a2); a3 = fma(lv[r + 3], yy[3], a3);
+                }
+            }
+            part[half * NB + c] = (a0 + a1) + (a2 + a3);
             __syncthreads();
             if (tid < NB) zs[tid] -= part[tid] + part[NB + tid];
         }
@@ -430,9 +515,20 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         __syncthreads();
         // y_m[c] = sum_{r >= c} invL_m[r][c] z_m[r]
         const double *Ig = p.invL + (size_t)m * NB * NB;
-        double accv = 0.0;
-        for (int r = max(c, half * 64); r < half * 64 + 64; ++r) accv = fma(__ldcg(Ig + (size_t)r * NB + c), zs[r], accv);
-        part[half * NB + c] = accv;
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+        for (int rb = 0; rb < 64; rb += 32) {
+            double iv[32];
+#pragma unroll
+            for (int r = 0; r < 32; ++r) iv[r] = (half * 64 + rb + r >= c) ? __ldcg(Ig + (size_t)(half * 64 + rb + r) * NB + c) : 0.0;
+#pragma unroll
+            for (int r = 0; r < 32; r += 4) {
+                const double *zz = zs + half * 64 + rb + r;
+                a0 = fma(iv[r], zz[0], a0); a1 = fma(iv[r + 1], zz[1], a1);
+                a2 = fma(iv[r + 2], zz[2], a2); a3 = fma(iv[r + 3], zz[3], a3);
+            }
+        }
+        part[half * NB + c] = (a0 + a1) + (a2 + a3);
         __syncthreads();
         if (tid < NB) {
             const double v = part[tid] + part[NB + tid];
@@ -443,12 +539,18 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         __syncthreads();
         if (tid == 0) st_release(p.ydone + m, 1);
     }
+    if (p.prof && tid == 0) {
+        long long *o = p.prof + 8 * (size_t)blockIdx.x;
+        o[0] = t_start; o[1] = t_phase1; o[2] = global_ns(); o[3] = waited1; o[4] = waited - waited1; o[5] = t_potrf;
+        o[6] = n_tasks; o[7] = t_trsm;
+    }
 }
 
 // -------------------------------------------------------------------------------------------------------------
 // host side
 // -------------------------------------------------------------------------------------------------------------
 static int g_chol_grid[64];     // per device: co-resident CTAs (0 = not initialised)
+long long *g_chol_prof = nullptr;   // tools/chol_prof.cu only: device buffer [grid][8] of per-CTA timings
 
 int chol_init() {
     int dev = 0;
@@ -479,7 +581,7 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
     p.ypad = work + (size_t)T * NB * NB;
     int *flags = reinterpret_cast<int *>(p.ypad + (size_t)T * NB);
     p.rowdone = flags; p.diagdone = flags + (T + 1); p.ydone = p.diagdone + T; p.abort_flag = p.ydone + T;
-    p.y = y; p.state = state; p.fail_flag = fail_flag;
+    p.y = y; p.state = state; p.fail_flag = fail_flag; p.prof = g_chol_prof;
     cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)chol_flag_count(T), s);
     if (e != cudaSuccess) return (int)e;
     const int ntasks = T * (T + 3) / 2;

@@ -1,0 +1,67 @@
+// chol_prof.cu -- per-CTA timing breakdown of the dataflow Cholesky (tools only; includes the product source).
+// build: see tools/Makefile-less one-liner in profiles/README; run: tools/_build/chol_prof [n]
+#define CHOL_PROFILE_PHASES 1
+#include "../bundleadjustment_b200/csrc/ba_cholesky.cu"
+
+#include <algorithm>
+#include <cstdio>
+#include <vector>
+
+using namespace ba;
+
+__global__ void fill_spd(double *A, int n, int ld, size_t rows) {
+    const size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (idx >= rows * (size_t)ld) return;
+    const int r = (int)(idx / ld), c = (int)(idx % ld);
+    double v = 0.0;
+    if (r < n && c <= r) {
+        unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
+        h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
+        v = ((h & 0xffff) / 65536.0 - 0.5) * 0.01;
+        if (r == c) v = 1.0 + 0.04 * sqrt((double)n);
+    } else if (r < ld && r == c) v = 1.0;
+    else if (r == ld && c < n) v = 1.0;
+    A[idx] = v;
+}
+
+int main(int argc, char **argv) {
+    const int n = argc > 1 ? atoi(argv[1]) : 10200;
+    const int ld = chol_ld(n);
+    const size_t rows = chol_rows(n);
+    double *A, *work, *y;
+    cudaMalloc(&A, 8 * rows * ld); cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
+    cudaMalloc(&g_chol_prof, 8 * 8 * 256);
+    if (chol_init()) { printf("chol_init failed\n"); return 1; }
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int r = 0; r < 4; ++r) {
+        fill_spd<<<(unsigned)((rows * ld + 255) / 256), 256>>>(A, n, ld, rows);
+        cudaEventRecord(e0);
+        int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, 0);
+        cudaEventRecord(e1);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (ce || e) { printf("error %d %s\n", ce, cudaGetErrorString(e)); return 1; }
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        best = std::min(best, ms);
+    }
+    std::vector<long long> h(8 * 256);
+    cudaMemcpy(h.data(), g_chol_prof, 8 * 8 * 256, cudaMemcpyDeviceToHost);
+    int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    const int T = ld / NB, grid = std::min(sms, T * (T + 3) / 2);
+    long long t0 = h[0], tend = 0;
+    for (int b = 0; b < grid; ++b) { t0 = std::min(t0, h[8 * b]); tend = std::max(tend, h[8 * b + 2]); }
+    double s_p1 = 0, s_w1 = 0, s_w2 = 0, s_potrf = 0, s_trsm = 0, max_p1 = 0, s_tasks = 0, potrf_tiles = T;
+    for (int b = 0; b < grid; ++b) {
+        const long long *o = &h[8 * b];
+        s_p1 += (o[1] - o[0]); max_p1 = std::max(max_p1, (double)(o[1] - t0)); s_w1 += o[3]; s_w2 += o[4]; s_potrf += o[5]; s_trsm += o[7]; s_tasks += o[6];
+    }
+    printf("n=%d T=%d grid=%d: best %.3f ms  %.2f TFLOP/s\n", n, T, grid, best, ((double)n * n * n / 3 + 2.0 * n * n) / best / 1e9);
+    printf("  kernel span %.3f ms; phase 1 ends (max over CTAs) at %.3f ms; mean phase-1 busy %.3f ms of which waiting %.3f ms, trsm epilogues %.3f ms\n",
+           (tend - t0) * 1e-6, max_p1 * 1e-6, s_p1 / grid * 1e-6, s_w1 / grid * 1e-6, s_trsm / grid * 1e-6);
+    printf("  potrf: %.1f us per diagonal tile (%d tiles); phase 2 (back substitution) %.3f ms, mean wait there %.3f ms; tasks %.0f\n",
+           s_potrf / potrf_tiles * 1e-3, T, (tend - t0 - max_p1) * 1e-6, s_w2 / grid * 1e-6, s_tasks);
+    long long ph[4];
+    cudaMemcpyFromSymbol(ph, g_potrf_phase, sizeof(ph));
+    if (ph[3]) printf("  potrf phases per tile: (A) %.1f us  (B) %.1f us  (C) %.1f us  over %lld calls\n", ph[0] * 1e-3 / ph[3], ph[1] * 1e-3 / ph[3], ph[2] * 1e-3 / ph[3], ph[3]);
+    return 0;
+}
