@@ -27,20 +27,24 @@
 namespace ba {
 
 constexpr int NB = CHOL_NB;            // 128: tile edge
-constexpr int BK = 16;                 // k-slice of the cp.async ring
-constexpr int SPAD = BK + 4;           // 20 doubles: row stride == 4 (mod 16) -> conflict-free DMMA fragment loads
-constexpr int NSTAGE = 4;
+constexpr int BK = 32;                 // k-slice of the cp.async ring
+constexpr int SPAD = BK + 4;           // 36 doubles: row stride == 4 (mod 16) -> conflict-free DMMA fragment loads
+constexpr int NSTAGE = 3;
+constexpr int KSL = NB / BK;           // k-slices per 128-column block
 constexpr int LDT = NB + 4;            // 132: stride of the staged C tile, same conflict-free property
 constexpr int PB = 32;                 // potrf panel width (warp-register base case)
 constexpr int LDP = PB + 4;            // 36
 
 constexpr int STAGE_DOUBLES = 2 * NB * SPAD;                       // A slice + B slice
 constexpr int TILE_DOUBLES = NB * LDT;                             // 16896
-constexpr int RING_DOUBLES = NSTAGE * STAGE_DOUBLES;               // 20480
-// potrf scratch (Pv | invd | dinv) aliases the ring's tail; the ring itself may spill over the C tile during the main loop
-constexpr int SMEM_DOUBLES = TILE_DOUBLES + NB * LDP + PB * LDP + NB;   // 16896 + 4608 + 1152 + 128 = 22784
-static_assert(RING_DOUBLES <= SMEM_DOUBLES, "ring must fit");
-constexpr int CHOL_SMEM = SMEM_DOUBLES * (int)sizeof(double);      // 182272 B
+constexpr int RING_DOUBLES = NSTAGE * STAGE_DOUBLES;               // 27648
+// Shared memory: [C tile | scratch].  The main-loop ring overlays both; after it the scratch holds either the TRSM's
+// 2-stage ring of L_jj^-1 slices or the potrf work arrays (Pv | invd | dinv).
+constexpr int SCRATCH_DOUBLES = 2 * NB * SPAD;                     // 9216 >= 128*36 + 32*36 + 128
+constexpr int SMEM_DOUBLES = (TILE_DOUBLES + SCRATCH_DOUBLES > RING_DOUBLES) ? TILE_DOUBLES + SCRATCH_DOUBLES : RING_DOUBLES;
+static_assert(NB * LDP + PB * LDP + NB <= SCRATCH_DOUBLES, "potrf scratch must fit");
+constexpr int CHOL_SMEM = SMEM_DOUBLES * (int)sizeof(double);      // 221184 B
+static_assert(CHOL_SMEM <= 227 * 1024, "shared memory budget");
 
 int chol_ld(int n) { return ((n + NB - 1) / NB) * NB; }
 size_t chol_rows(int n) { return (size_t)chol_ld(n) + NB; }
@@ -110,13 +114,14 @@ __device__ __forceinline__ long long global_ns() {
     return t;
 }
 
-// spin until *flag >= need; returns false if aborted (every thread polls for itself: its own cp.asyncs follow)
+// spin until *flag >= need; returns false if aborted.  Called by ONE thread per CTA; the verdict reaches the others through
+// a CTA barrier, and everything they then read was written through L2 (cp.async.cg / __ldcg), never a stale L1 line.
 __device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_flag, long long &waited) {
     if (ld_acquire(flag) >= need) return true;
     const long long t0 = global_ns();
     unsigned spins = 0;
     while (true) {
-        __nanosleep(64);
+        __nanosleep(32);
         if (ld_acquire(flag) >= need) { waited += global_ns() - t0; return true; }
         if ((++spins & 255u) == 0) {
             if (ld_acquire(abort_flag)) return false;
@@ -145,9 +150,13 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
     __shared__ int s_bad;
     if (tid == 0) s_bad = 0;
     __syncthreads();
+#ifdef CHOL_PROFILE_PHASES
     long long tA = 0, tB = 0, tC = 0;
+#endif
     for (int c0 = 0; c0 < NB; c0 += PB) {
+#ifdef CHOL_PROFILE_PHASES
         const long long t0 = global_ns();
+#endif
         // ---- (A) ----
         if (warp == 0) {
             double a[PB];
@@ -217,7 +226,9 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
             }
         }
         __syncthreads();
+#ifdef CHOL_PROFILE_PHASES
         const long long t1 = global_ns();
+#endif
         // ---- (B) rows outside the diagonal block: 96 rows = 12 m-tiles of 8 ----
         for (int mt = warp; mt < (NB - PB) / 8; mt += 8) {
             const int r = mt * 8 + g;
@@ -244,7 +255,9 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
             }
         }
         __syncthreads();
+#ifdef CHOL_PROFILE_PHASES
         const long long t2 = global_ns();
+#endif
         // ---- (C) trailing columns c >= c0 + 32: one m-tile x up to 4 n-tiles per pass (independent DMMA chains) ----
         const int nb0 = (c0 + PB) / 8, nbn = NB / 8 - nb0;
         const int ngrp = (nbn + 3) / 4;
@@ -276,8 +289,10 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
             }
         }
         __syncthreads();
+#ifdef CHOL_PROFILE_PHASES
         const long long t3 = global_ns();
         tA += t1 - t0; tB += t2 - t1; tC += t3 - t2;
+#endif
     }
 #ifdef CHOL_PROFILE_PHASES
     if (tid == 0) {
@@ -293,12 +308,13 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 // -------------------------------------------------------------------------------------------------------------
 // The dataflow kernel
 // -------------------------------------------------------------------------------------------------------------
-// one k-slice (16 columns) of a 128-row operand tile into shared memory: 128 x 8 16-byte segments, 4 per thread
+// one k-slice (BK columns) of a 128-row operand tile into shared memory: 128 x BK/2 16-byte segments
 __device__ __forceinline__ void load_slice(double *__restrict__ dst, const double *__restrict__ src, int ld, int tid) {
+    constexpr int SEGS = BK / 2;
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
+    for (int r = 0; r < NB * SEGS / 256; ++r) {
         const int idx = tid + 256 * r;
-        const int row = idx >> 3, seg = idx & 7;
+        const int row = idx / SEGS, seg = idx % SEGS;
         cp_async16(dst + (size_t)row * SPAD + seg * 2, src + (size_t)row * ld + seg * 2);
     }
 }
@@ -331,9 +347,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     const int g = lane >> 2, tig = lane & 3;
     const int T = p.T, TR = p.T + 1, ld = p.ld;
     const int ntasks = T * (T + 1) / 2 + T;                // lower triangle of T x T + the rhs tile row
+    __shared__ int s_have;
     bool aborted = false;
     long long waited = 0, t_potrf = 0, t_trsm = 0, n_tasks = 0;
-    const long long t_start = global_ns();
+    const long long t_start = p.prof ? global_ns() : 0;
 
     // ================= phase 1: factorisation + forward substitution =================
     int j = 0, colbase = 0;
@@ -351,12 +368,23 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         const double *Brow = p.A + (size_t)j * NB * ld;    // row panel j
         const int nk = j * (NB / BK);                      // k-slices of the bulk update
         int have = 0;                                      // k-blocks known to be final in both row panels
-        auto ensure = [&](int kb) -> bool {                // L_ik and L_jk final for k-block kb
+        // L_ik and L_jk final for k-block kb.  Called at uniform points by ALL threads; only thread 0 touches the flags
+        // (an acquire costs an L1 invalidate), the verdict travels through shared memory + a barrier.  The operand
+        // loads that follow are cp.async.cg (L2), so the CTA barrier is enough to order them after the acquire.
+        auto ensure = [&](int kb) -> bool {
             if (kb < have) return true;
-            if (!wait_ge(p.rowdone + i, kb + 1, p.abort_flag, waited)) return false;
-            if (!diag && !wait_ge(p.rowdone + j, kb + 1, p.abort_flag, waited)) return false;
-            const int hi = ld_acquire(p.rowdone + i), hj = diag ? hi : ld_acquire(p.rowdone + j);
-            have = min(min(hi, hj), j);
+            if (tid == 0) {
+                int h = -1;
+                if (wait_ge(p.rowdone + i, kb + 1, p.abort_flag, waited) && (diag || wait_ge(p.rowdone + j, kb + 1, p.abort_flag, waited))) {
+                    const int hi = ld_acquire(p.rowdone + i), hj = diag ? hi : ld_acquire(p.rowdone + j);
+                    h = min(min(hi, hj), j);
+                }
+                s_have = h;
+            }
+            __syncthreads();
+            const int h = s_have;
+            if (h < 0) return false;
+            have = h;
             return true;
         };
         auto issue = [&](int kt) {
@@ -367,7 +395,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         // prologue
         for (int s = 0; s < NSTAGE - 1; ++s) {
             if (s < nk) {
-                if ((s & 7) == 0 && !ensure(s >> 3)) { aborted = true; }
+                if ((s % KSL) == 0 && !ensure(s / KSL)) { aborted = true; }
                 if (!aborted) issue(s);
             }
             cp_async_commit();
@@ -377,7 +405,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             __syncthreads();
             const int nx = kt + NSTAGE - 1;
             if (nx < nk && !aborted) {
-                if ((nx & 7) == 0 && !ensure(nx >> 3)) aborted = true;
+                if ((nx % KSL) == 0 && !ensure(nx / KSL)) aborted = true;
                 if (!aborted) issue(nx);
             }
             cp_async_commit();
@@ -411,9 +439,9 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         }
         __syncthreads();
         if (diag) {
-            const long long tp0 = global_ns();
+            const long long tp0 = p.prof ? global_ns() : 0;
             const bool bad = potrf_inverse_tile(tileC, Pv, invd, dinv);
-            t_potrf += global_ns() - tp0;
+            if (p.prof) t_potrf += global_ns() - tp0;
             double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
             double *Ig = p.invL + (size_t)j * NB * NB;
             for (int idx = tid; idx < NB * NB; idx += 256) {
@@ -430,10 +458,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (tid == 0) { st_release(p.diagdone + j, 1); st_release(p.rowdone + j, j + 1); }
         } else {
             // L_ij = C * L_jj^-T : A operand = the staged tile, B operand = invL_j through a 2-stage ring
-            if (!wait_ge(p.diagdone + j, 1, p.abort_flag, waited)) aborted = true;
+            if (tid == 0 && !wait_ge(p.diagdone + j, 1, p.abort_flag, waited)) aborted = true;
             aborted = __syncthreads_or(aborted);
             if (aborted) break;
-            const long long tt0 = global_ns();
+            const long long tt0 = p.prof ? global_ns() : 0;
             const double *Ig = p.invL + (size_t)j * NB * NB;
 #pragma unroll
             for (int a = 0; a < 8; ++a)
@@ -464,11 +492,11 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             __threadfence();
             __syncthreads();
             if (tid == 0) st_release(p.rowdone + i, j + 1);
-            t_trsm += global_ns() - tt0;
+            if (p.prof) t_trsm += global_ns() - tt0;
         }
         ++n_tasks;
     }
-    const long long t_phase1 = global_ns(), waited1 = waited;
+    const long long t_phase1 = p.prof ? global_ns() : 0, waited1 = waited;
     if (aborted) {
         if (tid == 0) {
             if (p.state) p.state->chol_fail = 1;
@@ -484,12 +512,12 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     const double *z = p.A + (size_t)T * NB * ld;
     for (int m = T - 1 - (int)blockIdx.x; m >= 0; m -= gridDim.x) {
         // z_m is final once tile (T, m) is; L_km tiles are final once row k reached column m
-        if (!__syncthreads_and(wait_ge(p.rowdone + T, m + 1, p.abort_flag, waited) && wait_ge(p.diagdone + m, 1, p.abort_flag, waited))) break;
+        if (!__syncthreads_and(tid != 0 || (wait_ge(p.rowdone + T, m + 1, p.abort_flag, waited) && wait_ge(p.diagdone + m, 1, p.abort_flag, waited)))) break;
         if (tid < NB) zs[tid] = __ldcg(z + (size_t)m * NB + tid);
         const int c = tid & (NB - 1), half = tid >> 7;
         bool ok = true;
         for (int k = T - 1; k > m; --k) {
-            ok = wait_ge(p.ydone + k, 1, p.abort_flag, waited) && wait_ge(p.rowdone + k, m + 1, p.abort_flag, waited);
+            ok = tid != 0 || (wait_ge(p.ydone + k, 1, p.abort_flag, waited) && wait_ge(p.rowdone + k, m + 1, p.abort_flag, waited));
             if (!__syncthreads_and(ok)) { ok = false; break; }
             if (tid < NB) ys[tid] = __ldcg(p.ypad + (size_t)k * NB + tid);
             __syncthreads();

@@ -10,7 +10,7 @@
 using namespace ba;
 
 template <int SHAPE>
-__global__ void __launch_bounds__(256) mma_peak_kernel(double *out, int iters) {
+__global__ void __launch_bounds__(512) mma_peak_kernel(double *out, int iters) {
     double c[16][4];
     for (int i = 0; i < 16; ++i) for (int j = 0; j < 4; ++j) c[i][j] = 0.0;
     double a[8], b[4];
@@ -46,62 +46,34 @@ __global__ void __launch_bounds__(256) mma_peak_kernel(double *out, int iters) {
 }
 
 template <int SHAPE>
-void run_peak(const char *name, double flops_per_inst_per_warp, double *out) {
-    const int blocks = 148 * 2, iters = 4000;
+void run_peak(const char *name, double flops_per_inst_per_warp, double *out, int blocks = 148 * 2, int threads = 256) {
+    const int iters = 4000;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
-    mma_peak_kernel<SHAPE><<<blocks, 256>>>(out, 10);
+    mma_peak_kernel<SHAPE><<<blocks, threads>>>(out, 10);
     cudaEventRecord(e0);
-    mma_peak_kernel<SHAPE><<<blocks, 256>>>(out, iters);
+    mma_peak_kernel<SHAPE><<<blocks, threads>>>(out, iters);
     cudaEventRecord(e1);
     cudaError_t e = cudaDeviceSynchronize();
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1);
-    const double fl = (double)blocks * 8 * iters * 16 * flops_per_inst_per_warp;
+    const double fl = (double)blocks * (threads / 32) * iters * 16 * flops_per_inst_per_warp;
     printf("%-14s %8.3f ms  %7.2f TFLOP/s  (%s)\n", name, ms, fl / ms / 1e9, cudaGetErrorString(e));
-}
-
-void run_gemm(int M, int N, int K, bool tri) {
-    double *A, *C;
-    cudaMalloc(&A, sizeof(double) * (size_t)M * K);
-    cudaMalloc(&C, sizeof(double) * (size_t)M * N);
-    cudaMemset(A, 0, sizeof(double) * (size_t)M * K);
-    cudaMemset(C, 0, sizeof(double) * (size_t)M * N);
-    chol_init();
-    const int tm = (M + BM - 1) / BM, tn = (N + BN - 1) / BN;
-    cudaEvent_t e0, e1;
-    cudaEventCreate(&e0); cudaEventCreate(&e1);
-    float best = 1e30f;
-    for (int r = 0; r < 4; ++r) {
-        cudaEventRecord(e0);
-        if (tri) gemm_nt_kernel<MODE_SUB, true><<<tm * (tm + 1) / 2, 256, GEMM_SMEM>>>(A, K, A, K, C, N, M, N, K, 0, nullptr);
-        else gemm_nt_kernel<MODE_SUB, false><<<tm * tn, 256, GEMM_SMEM>>>(A, K, A, K, C, N, M, N, K, tn, nullptr);
-        cudaEventRecord(e1);
-        cudaDeviceSynchronize();
-        float ms; cudaEventElapsedTime(&ms, e0, e1);
-        if (r) best = fminf(best, ms);
-    }
-    const double tiles = tri ? tm * (tm + 1) / 2.0 : (double)tm * tn;
-    const double fl = tiles * 2.0 * BM * BN * K;
-    printf("gemm_nt %s M=%d N=%d K=%d: %8.3f ms  %6.2f TFLOP/s  (%s)\n", tri ? "tri " : "full", M, N, K, best, fl / best / 1e9,
-           cudaGetErrorString(cudaGetLastError()));
-    cudaFree(A); cudaFree(C);
 }
 
 int main() {
     double *out;
-    cudaMalloc(&out, sizeof(double) * 148 * 2 * 256);
+    cudaMalloc(&out, sizeof(double) * 148 * 2 * 512);
     run_peak<0>("dmma m8n8k4", 2.0 * 8 * 8 * 4, out);
     run_peak<1>("dmma m16n8k4", 2.0 * 16 * 8 * 4, out);
     run_peak<2>("dmma m16n8k8", 2.0 * 16 * 8 * 8, out);
     run_peak<3>("dmma m16n8k16", 2.0 * 16 * 8 * 16, out);
     run_peak<4>("dfma", 2.0 * 4 * 32, out);
-    cudaFuncSetAttribute(gemm_nt_kernel<MODE_SUB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
-    run_gemm(8192, 8192, 128, false);
-    run_gemm(8192, 8192, 1024, false);
-    run_gemm(8192, 8192, 8192, false);
-    run_gemm(10112, 10112, 128, true);
-    run_gemm(5120, 5120, 128, true);
-    run_gemm(2560, 2560, 128, true);
+    run_peak<0>("m8n8k4 1w/sp", 2.0 * 8 * 8 * 4, out, 148, 128);
+    run_peak<0>("m8n8k4 2w/sp", 2.0 * 8 * 8 * 4, out, 148, 256);
+    run_peak<0>("m8n8k4 3w/sp", 2.0 * 8 * 8 * 4, out, 148, 384);
+    run_peak<0>("m8n8k4 4w/sp", 2.0 * 8 * 8 * 4, out, 148, 512);
+    run_peak<3>("m16n8k16 1w/sp", 2.0 * 16 * 8 * 16, out, 148, 128);
+    run_peak<3>("m16n8k16 2w/sp", 2.0 * 16 * 8 * 16, out, 148, 256);
     return 0;
 }
