@@ -56,19 +56,21 @@ const char *message_text(int msg) {
     }
 }
 
-struct DevBuf {
+struct DevBuf {                      // grow-only: re-solving a problem of the same shape never touches the allocator
     void *p = nullptr;
-    size_t bytes = 0;
+    size_t bytes = 0, cap = 0;
     cudaError_t alloc(size_t b) {
+        if (b <= cap && p) { bytes = b; return cudaSuccess; }
         free();
-        bytes = b;
         if (b == 0) return cudaSuccess;
-        return cudaMalloc(&p, b);
+        cudaError_t e = cudaMalloc(&p, b);
+        if (e == cudaSuccess) { bytes = b; cap = b; } else p = nullptr;
+        return e;
     }
     void free() {
         if (p) cudaFree(p);
         p = nullptr;
-        bytes = 0;
+        bytes = 0; cap = 0;
     }
     template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
 };
@@ -83,8 +85,16 @@ struct ba_handle {
     cudaEvent_t ev_ring[4] = {nullptr, nullptr, nullptr, nullptr};
     bool has_problem = false;
     Ctx ctx;
-    // caller order -> landmark-major position
+    // caller order -> landmark-major position (fetched from the device on first use)
     std::vector<int> perm;           // pm position of caller observation i
+    bool perm_valid = false;
+    DevBuf raw_cam, raw_pt, raw_uv, raw_fixed, perm_dev, cnt_cam, cnt_cam_global, cam_ptr, prep_flags;
+    DevBuf pair_obs, seg_beg, seg_cams, unit_ptr, unit_seg, unit_beg, unit_part;
+    PrepScratch scr, scr2;
+    PrepIn prep_in;
+    PrepOut prep_out;
+    bool pairs_built = false;
+    int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
@@ -111,8 +121,11 @@ struct ba_handle {
         DevBuf *all[] = {&cam0, &cam1, &pt0, &pt1, &cam_init, &pt_init, &cam_kind, &cam_K, &cam_extr, &pm_uv, &pm_cam, &pm_pt,
                          &pt_ptr, &cm_uv, &cm_pt, &chunk_cam, &chunk_beg, &chunk_end, &cam_chunk_ptr, &tab_x, &tab_c, &scale_cam,
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &sums, &maxs,
-                         &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &ev_res, &ev_jc, &ev_jp};
+                         &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &ev_res, &ev_jc, &ev_jp,
+                         &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part};
         for (DevBuf *b : all) b->free();
+        scr.release(); scr2.release();
         has_problem = false;
     }
 };
@@ -174,6 +187,7 @@ int ba_create(const ba_options *opt, int device, ba_handle **out) {
     CU(cudaEventCreate(&h->ev_start));
     CU(cudaEventCreate(&h->ev_stop));
     for (auto &e : h->ev_ring) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(cudaHostAlloc((void **)&h->h_prep, 64, cudaHostAllocDefault));
     CU(cudaHostAlloc((void **)&h->host_flags, 64, cudaHostAllocMapped));
     std::memset(h->host_flags, 0, 64);
     CU(cudaHostGetDevicePointer((void **)&h->host_flags_dev, h->host_flags, 0));
@@ -190,6 +204,7 @@ int ba_destroy(ba_handle *h) {
     h->free_problem();
     if (h->comm) ncclCommDestroy(h->comm);
     if (h->host_flags) cudaFreeHost(h->host_flags);
+    if (h->h_prep) cudaFreeHost(h->h_prep);
     for (auto &e : h->ev_ring) if (e) cudaEventDestroy(e);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->ev_stop) cudaEventDestroy(h->ev_stop);
@@ -234,6 +249,31 @@ int ensure_dense(ba_handle *h) {
     }
     h->ctx.S = h->S.as<double>();
     h->ctx.ldS = chol_ld(n);
+    if (!h->pairs_built) {
+        // camera-pair-major index for the deterministic Schur reduction (device-side, once per problem)
+        cudaStream_t s = h->stream;
+        long long *h_total = reinterpret_cast<long long *>(h->h_prep + 4);
+        int rc = prep_pairs_count(h->prep_in, h->prep_out, h->scr, h_total, s);
+        if (rc) return fail(BA_ERR_CUDA, "prep_pairs_count: %s", cudaGetErrorString((cudaError_t)rc));
+        PairIndex &pi = h->ctx.pairs;
+        std::memset(&pi, 0, sizeof(pi));
+        pi.P = *h_total;
+        const size_t P = (size_t)std::max<long long>(pi.P, 1);
+        const size_t Ncz = (size_t)h->ctx.Nc;
+        pi.seg_cap = std::min<size_t>(P, Ncz * (Ncz + 1) / 2);
+        CU(h->pair_obs.alloc(8 * P)); CU(h->seg_beg.alloc(8 * pi.seg_cap)); CU(h->seg_cams.alloc(8 * pi.seg_cap));
+        CU(h->unit_ptr.alloc(4 * (pi.seg_cap + 1)));
+        pi.pair_obs = h->pair_obs.as<int2>(); pi.seg_beg = h->seg_beg.as<long long>(); pi.seg_cams = h->seg_cams.as<int2>();
+        pi.unit_ptr = h->unit_ptr.as<int>();
+        rc = prep_pairs_build(h->prep_in, h->prep_out, pi, h->scr, h->scr2, h->h_prep + 6, s);
+        if (rc) return fail(BA_ERR_CUDA, "prep_pairs_build: %s", cudaGetErrorString((cudaError_t)rc));
+        const size_t nu = (size_t)std::max(pi.n_units, 1);
+        CU(h->unit_seg.alloc(4 * nu)); CU(h->unit_beg.alloc(8 * nu)); CU(h->unit_part.alloc(8 * 42 * nu));
+        pi.unit_seg = h->unit_seg.as<int>(); pi.unit_beg = h->unit_beg.as<long long>(); pi.unit_part = h->unit_part.as<double>();
+        if ((rc = prep_pairs_units(pi, s))) return fail(BA_ERR_CUDA, "prep_pairs_units: %s", cudaGetErrorString((cudaError_t)rc));
+        h->scr2.release();            // the sort scratch is the largest temporary: give it back
+        h->pairs_built = true;
+    }
     return BA_OK;
 }
 
@@ -248,103 +288,71 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
         return fail(BA_ERR_INVALID, "NULL array");
     CU(cudaSetDevice(h->device));
     const int Nc = n_cam, Np = n_pt, No = n_obs;
-    std::vector<int> pcount(Np, 0), ccount(Nc, 0);
-    for (int i = 0; i < No; ++i) {
-        const int c = obs_cam[i], p = obs_pt[i];
-        if (c < 0 || c >= Nc || p < 0 || p >= Np) return fail(BA_ERR_INVALID, "observation %d references camera %d / landmark %d out of range", i, c, p);
-        if (cam_fixed[c] && !fixed_extr) return fail(BA_ERR_INVALID, "fixed camera %d but fixed_extr is NULL", c);
-        pcount[p]++; ccount[c]++;
-    }
-    h->free_problem();
+    h->has_problem = false;
+    h->perm_valid = false;
+    h->pairs_built = false;
     cudaStream_t s = h->stream;
     Ctx &ctx = h->ctx;
     std::memset(&ctx, 0, sizeof(ctx));
     ctx.Nc = Nc; ctx.Np = Np; ctx.No = No; ctx.n = 6 * Nc;
     ctx.rank = h->rank; ctx.n_ranks = h->n_ranks;
     ctx.opt = h->opt;
-
-    // ---- landmark-major order: counting sort by landmark, then by camera inside the (short) track ----
-    std::vector<int> pt_ptr(Np + 1, 0);
-    for (int p = 0; p < Np; ++p) pt_ptr[p + 1] = pt_ptr[p] + pcount[p];
-    std::vector<int> order(No);          // pm position -> caller index
-    {
-        std::vector<int> fill(pt_ptr.begin(), pt_ptr.end() - 1);
-        for (int i = 0; i < No; ++i) order[fill[obs_pt[i]]++] = i;
-        for (int p = 0; p < Np; ++p)
-            std::stable_sort(order.begin() + pt_ptr[p], order.begin() + pt_ptr[p + 1],
-                             [&](int a, int b) { return obs_cam[a] < obs_cam[b]; });
-    }
-    h->perm.assign(No, 0);
-    std::vector<float2> pm_uv(No);
-    std::vector<int> pm_cam(No), pm_pt(No);
-    for (int e = 0; e < No; ++e) {
-        const int i = order[e];
-        h->perm[i] = e;
-        pm_uv[e] = make_float2(obs_uv[2 * (size_t)i], obs_uv[2 * (size_t)i + 1]);
-        pm_cam[e] = obs_cam[i];
-        pm_pt[e] = obs_pt[i];
-    }
-    // ---- global per-camera observation counts decide which cameras are part of the problem ----
-    h->cam_obs_count = ccount;
-    if (h->comm) {
-        DevBuf tmp;
-        CU(tmp.alloc(sizeof(int) * Nc));
-        CU(cudaMemcpyAsync(tmp.p, ccount.data(), sizeof(int) * Nc, cudaMemcpyHostToDevice, s));
-        NC(ncclAllReduce(tmp.p, tmp.p, Nc, ncclInt, ncclSum, h->comm, s));
-        CU(cudaMemcpyAsync(h->cam_obs_count.data(), tmp.p, sizeof(int) * Nc, cudaMemcpyDeviceToHost, s));
-        CU(cudaStreamSynchronize(s));
-        tmp.free();
-    }
-    std::vector<int> kind(Nc);
-    for (int c = 0; c < Nc; ++c) kind[c] = cam_fixed[c] ? CAM_FIXED : (h->cam_obs_count[c] > 0 ? CAM_FREE : CAM_INACTIVE);
-    // ---- camera-major copy (free cameras only) + reduction chunks ----
-    std::vector<int> cam_ptr(Nc + 1, 0);
-    for (int c = 0; c < Nc; ++c) cam_ptr[c + 1] = cam_ptr[c] + ((kind[c] == CAM_FREE) ? ccount[c] : 0);
-    const int Ncm = cam_ptr[Nc];
-    std::vector<float2> cm_uv(std::max(Ncm, 1));
-    std::vector<int> cm_pt(std::max(Ncm, 1));
-    {
-        std::vector<int> fill(cam_ptr.begin(), cam_ptr.end() - 1);
-        for (int e = 0; e < No; ++e) {
-            const int c = pm_cam[e];
-            if (kind[c] != CAM_FREE) continue;
-            const int d = fill[c]++;
-            cm_uv[d] = pm_uv[e];
-            cm_pt[d] = pm_pt[e];
-        }
-    }
-    std::vector<int> chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr(Nc + 1, 0);
-    for (int c = 0; c < Nc; ++c) {
-        for (int b = cam_ptr[c]; b < cam_ptr[c + 1]; b += CHUNK) {
-            chunk_cam.push_back(c);
-            chunk_beg.push_back(b);
-            chunk_end.push_back(std::min(b + CHUNK, cam_ptr[c + 1]));
-        }
-        cam_chunk_ptr[c + 1] = (int)chunk_cam.size();
-    }
-    ctx.n_chunks = (int)chunk_cam.size();
-    ctx.n_part = std::max((Np + 127) / 128, 1);
-
-    // ---- upload ----
     int rc;
 #define UP(buf, ptr, cnt) if ((rc = upload(h->buf, ptr, (size_t)(cnt), s))) return rc
+#define AL(buf, bytes) CU(h->buf.alloc(std::max<size_t>((size_t)(bytes), 8)))
+    // ---- raw observations to the device; all index building happens there (ba_prep.cu) ----
+    UP(raw_cam, obs_cam, No); UP(raw_pt, obs_pt, No); UP(raw_uv, obs_uv, 2 * (size_t)No); UP(raw_fixed, cam_fixed, Nc);
+    const size_t max_chunks = (size_t)No / CHUNK + (size_t)Nc + 1;
+    AL(pm_uv, 8 * (size_t)No); AL(pm_cam, 4 * (size_t)No); AL(pm_pt, 4 * (size_t)No); AL(pt_ptr, 4 * (size_t)(Np + 1));
+    AL(perm_dev, 4 * (size_t)No); AL(cnt_cam, 4 * (size_t)Nc); AL(cnt_cam_global, 4 * (size_t)Nc); AL(cam_kind, 4 * (size_t)Nc);
+    AL(cam_ptr, 4 * (size_t)(Nc + 1)); AL(cam_chunk_ptr, 4 * (size_t)(Nc + 1)); AL(cm_uv, 8 * (size_t)No); AL(cm_pt, 4 * (size_t)No);
+    AL(chunk_cam, 4 * max_chunks); AL(chunk_beg, 4 * max_chunks); AL(chunk_end, 4 * max_chunks); AL(prep_flags, 16);
+    PrepIn &pin = h->prep_in;
+    PrepOut &po = h->prep_out;
+    pin.Nc = Nc; pin.Np = Np; pin.No = No;
+    pin.obs_cam = h->raw_cam.as<int>(); pin.obs_pt = h->raw_pt.as<int>(); pin.obs_uv = h->raw_uv.as<float2>();
+    pin.cam_fixed = h->raw_fixed.as<unsigned char>();
+    po.pm_uv = h->pm_uv.as<float2>(); po.pm_cam = h->pm_cam.as<int>(); po.pm_pt = h->pm_pt.as<int>(); po.pt_ptr = h->pt_ptr.as<int>();
+    po.perm = h->perm_dev.as<int>(); po.cnt_cam = h->cnt_cam.as<int>(); po.cnt_cam_global = h->cnt_cam_global.as<int>();
+    po.cam_kind = h->cam_kind.as<int>(); po.cam_ptr = h->cam_ptr.as<int>(); po.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
+    po.cm_uv = h->cm_uv.as<float2>(); po.cm_pt = h->cm_pt.as<int>();
+    po.chunk_cam = h->chunk_cam.as<int>(); po.chunk_beg = h->chunk_beg.as<int>(); po.chunk_end = h->chunk_end.as<int>();
+    po.flags = h->prep_flags.as<int>(); po.h_flags = h->h_prep;
+    rc = prep_observations(pin, po, h->scr, s);
+    if (rc < 0) {
+        const int i = -rc - 1;
+        return fail(BA_ERR_INVALID, "observation %d references camera %d / landmark %d out of range", i, obs_cam[i], obs_pt[i]);
+    }
+    if (rc) return fail(BA_ERR_CUDA, "prep_observations: %s", cudaGetErrorString((cudaError_t)rc));
+    // ---- per-camera observation counts (summed over ranks) decide which cameras are part of the problem ----
+    h->cam_obs_count.resize(Nc);
+    if (h->comm) {
+        NC(ncclAllReduce(po.cnt_cam, po.cnt_cam_global, Nc, ncclInt, ncclSum, h->comm, s));
+    } else {
+        CU(cudaMemcpyAsync(po.cnt_cam_global, po.cnt_cam, 4 * (size_t)Nc, cudaMemcpyDeviceToDevice, s));
+    }
+    if (!fixed_extr) {      // legal only if no fixed camera is observed
+        CU(cudaMemcpyAsync(h->cam_obs_count.data(), po.cnt_cam_global, 4 * (size_t)Nc, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        for (int c = 0; c < Nc; ++c)
+            if (cam_fixed[c] && h->cam_obs_count[c] > 0) return fail(BA_ERR_INVALID, "fixed camera %d but fixed_extr is NULL", c);
+    }
+    if ((rc = prep_camera_major(pin, po, h->scr, s))) return fail(BA_ERR_CUDA, "prep_camera_major: %s", cudaGetErrorString((cudaError_t)rc));
+    if ((rc = prep_chunks(pin, po, s))) return fail(BA_ERR_CUDA, "prep_chunks: %s", cudaGetErrorString((cudaError_t)rc));
+    ctx.n_chunks = po.n_chunks;
+    ctx.n_part = std::max((Np + 127) / 128, 1);
+
+    // ---- parameters and constants ----
     UP(cam0, cam, 6 * (size_t)Nc); UP(cam1, cam, 6 * (size_t)Nc); UP(cam_init, cam, 6 * (size_t)Nc);
     UP(pt0, pt, 3 * (size_t)Np); UP(pt1, pt, 3 * (size_t)Np); UP(pt_init, pt, 3 * (size_t)Np);
-    UP(cam_kind, kind.data(), Nc);
     UP(cam_K, K, 9 * (size_t)Nc);
     if (fixed_extr) { UP(cam_extr, fixed_extr, 16 * (size_t)Nc); }
-    else { std::vector<float> z(16 * (size_t)Nc, 0.f); UP(cam_extr, z.data(), z.size()); CU(cudaStreamSynchronize(s)); }
-    UP(pm_uv, pm_uv.data(), No); UP(pm_cam, pm_cam.data(), No); UP(pm_pt, pm_pt.data(), No);
-    UP(pt_ptr, pt_ptr.data(), Np + 1);
-    UP(cm_uv, cm_uv.data(), Ncm); UP(cm_pt, cm_pt.data(), Ncm);
-    UP(chunk_cam, chunk_cam.data(), chunk_cam.size()); UP(chunk_beg, chunk_beg.data(), chunk_beg.size());
-    UP(chunk_end, chunk_end.data(), chunk_end.size()); UP(cam_chunk_ptr, cam_chunk_ptr.data(), Nc + 1);
+    else { AL(cam_extr, 64 * (size_t)Nc); CU(cudaMemsetAsync(h->cam_extr.p, 0, 64 * (size_t)Nc, s)); }
 #undef UP
-#define AL(buf, bytes) CU(h->buf.alloc(std::max<size_t>((size_t)(bytes), 8)))
     AL(tab_x, sizeof(CamEntry) * (size_t)Nc); AL(tab_c, sizeof(CamEntry) * (size_t)Nc);
     AL(scale_cam, 8 * 6 * (size_t)Nc); AL(scale_pt, 8 * 3 * (size_t)Np);
     AL(U, 8 * 36 * (size_t)Nc); AL(bc, 8 * 6 * (size_t)Nc); AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
-    AL(W, 8 * 18 * (size_t)No); AL(cam_part, 8 * 27 * (size_t)ctx.n_chunks);
+    AL(W, 8 * 18 * (size_t)No); AL(cam_part, 8 * 27 * (size_t)std::max(ctx.n_chunks, 1));
     AL(Vinv, 8 * 6 * (size_t)Np); AL(wv, 8 * 3 * (size_t)Np);
     AL(rhs, 8 * (size_t)ctx.n); AL(yc, 8 * (size_t)ctx.n);
     AL(part, 8 * 4 * (size_t)ctx.n_part); AL(cost_part, 8 * (size_t)((No + 127) / 128 + 1));
@@ -352,7 +360,6 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(state, sizeof(LMState)); AL(iters, sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2));
     AL(cg_r, 8 * (size_t)ctx.n); AL(cg_p, 8 * (size_t)ctx.n); AL(cg_z, 8 * (size_t)ctx.n); AL(cg_q, 8 * (size_t)ctx.n);
     AL(cg_x, 8 * (size_t)ctx.n); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np);
-#undef AL
     ctx.cam[0] = h->cam0.as<double>(); ctx.cam[1] = h->cam1.as<double>();
     ctx.pt[0] = h->pt0.as<double>(); ctx.pt[1] = h->pt1.as<double>();
     ctx.cam_init = h->cam_init.as<double>(); ctx.pt_init = h->pt_init.as<double>();
@@ -372,14 +379,15 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.state = h->state.as<LMState>(); ctx.iters = h->iters.as<ba_iteration>();
     ctx.host_flags = h->host_flags_dev;
     if (h->comm) {
-        CU(h->U_loc.alloc(8 * 36 * (size_t)Nc)); CU(h->bc_loc.alloc(8 * 6 * (size_t)Nc));
-        CU(h->sums_loc.alloc(8 * SUM_COUNT)); CU(h->maxs_loc.alloc(8 * MAX_COUNT));
+        AL(U_loc, 8 * 36 * (size_t)Nc); AL(bc_loc, 8 * 6 * (size_t)Nc);
+        AL(sums_loc, 8 * SUM_COUNT); AL(maxs_loc, 8 * MAX_COUNT);
         CU(cudaMemsetAsync(h->sums_loc.p, 0, 8 * SUM_COUNT, s)); CU(cudaMemsetAsync(h->maxs_loc.p, 0, 8 * MAX_COUNT, s));
         ctx.U_loc = h->U_loc.as<double>(); ctx.bc_loc = h->bc_loc.as<double>();
         ctx.sums_loc = h->sums_loc.as<double>(); ctx.maxs_loc = h->maxs_loc.as<double>();
     } else {
         ctx.U_loc = ctx.U; ctx.bc_loc = ctx.bc; ctx.sums_loc = ctx.sums; ctx.maxs_loc = ctx.maxs;
     }
+#undef AL
     CU(cudaMemsetAsync(h->sums.p, 0, 8 * SUM_COUNT, s));
     CU(cudaMemsetAsync(h->maxs.p, 0, 8 * MAX_COUNT, s));
     CU(cudaMemsetAsync(h->camsums.p, 0, 8 * CS_COUNT, s));
@@ -388,7 +396,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     launch_fill(ctx.scale_pt, 3 * (size_t)Np, 1.0, s);
     launch_cam_prep(ctx, 0, 1, s);      // K / fixed extrinsics of both tables are written once here
     launch_cam_prep(ctx, 1, 1, s);
-    CU(cudaStreamSynchronize(s));       // host staging vectors die at scope exit
+    CU(cudaStreamSynchronize(s));       // the caller may free / reuse its arrays after the call returns
     CU(cudaGetLastError());
     h->has_problem = true;
     return BA_OK;
@@ -690,6 +698,11 @@ extern "C" int ba_evaluate(ba_handle *h, double *cost, double *residuals, double
             CU(cudaMemcpy(&c, h->sums_loc.p, 8, cudaMemcpyDeviceToHost));
         }
         *cost = c;
+    }
+    if (!h->perm_valid && No && (residuals || jac_cam || jac_pt)) {
+        h->perm.resize(No);
+        CU(cudaMemcpy(h->perm.data(), h->perm_dev.p, 4 * (size_t)No, cudaMemcpyDeviceToHost));
+        h->perm_valid = true;
     }
     auto gather = [&](const DevBuf &src, double *dst, int width) -> int {
         std::vector<double> tmp((size_t)No * width);

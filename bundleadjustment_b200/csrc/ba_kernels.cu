@@ -310,47 +310,97 @@ __global__ void schur_init_kernel(Ctx ctx, double radius_override) {
     }
 }
 
-// one thread per landmark: all camera pairs of its track (lower blocks), fp64 atomics into S and rhs
-__global__ void __launch_bounds__(128) schur_accum_kernel(Ctx ctx, int force) {
+// C5 proper: S -= sum_p W_i V'^-1 W_j^T and rhs -= sum_p W_i V'^-1 b_p as DETERMINISTIC segmented reductions over the
+// camera-pair-major index (ba_prep.cu).  One warp per unit (<= PAIR_UNIT entries of ONE S block): each lane accumulates
+// the 6x6 block (and, on diagonal blocks, the 6 rhs entries) of its entries in registers, the 32 lane partials are
+// transposed through shared memory and summed in a fixed order.  No atomics anywhere: every S block has exactly one
+// writer (schur_segments_kernel), so the reduced system is bit-reproducible run to run.
+// Traffic per entry: 2 x 144 B of W + 48 B V'^-1 (+ 24 B on diagonal blocks); consecutive segments share cameras, so all
+// but the first touch of a W block come from L2.
+constexpr int SCHUR_WARPS = 4;
+__global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && st->done) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= ctx.Np) return;
-    const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
-    if (o1 <= o0) return;
-    const double *Vi = ctx.Vinv + 6 * (size_t)p;
-    const double vi[6] = {Vi[0], Vi[1], Vi[2], Vi[3], Vi[4], Vi[5]};
-    const double *wv = ctx.wv + 3 * (size_t)p;
-    const double w3[3] = {wv[0], wv[1], wv[2]};
-    const int n = ctx.ldS;
-    for (int i = o0; i < o1; ++i) {
-        const int ci = ctx.pm_cam[i];
-        if (ctx.cam_kind[ci] != CAM_FREE) continue;
-        const double *Wi = ctx.W + 18 * (size_t)i;
+    __shared__ double sred[SCHUR_WARPS][42][33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int u = blockIdx.x * SCHUR_WARPS + warp;
+    const PairIndex &pi = ctx.pairs;
+    if (u >= pi.n_units) return;
+    const int seg = pi.unit_seg[u];
+    const long long beg = pi.unit_beg[u];
+    const long long seg_end = (seg + 1 < pi.n_seg) ? pi.seg_beg[seg + 1] : pi.P;
+    const long long end = (beg + PAIR_UNIT < seg_end) ? beg + PAIR_UNIT : seg_end;
+    const int2 cams = pi.seg_cams[seg];
+    const bool diag = cams.x == cams.y;
+    double acc[36], racc[6];
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) racc[k] = 0.0;
+    for (long long e = beg + lane; e < end; e += 32) {
+        const int2 ob = pi.pair_obs[e];
+        const int p = ctx.pm_pt[ob.x];
+        const double2 *Vi2 = reinterpret_cast<const double2 *>(ctx.Vinv + 6 * (size_t)p);
+        const double2 v01 = Vi2[0], v23 = Vi2[1], v45 = Vi2[2];
+        const double vi[6] = {v01.x, v01.y, v23.x, v23.y, v45.x, v45.y};
+        const double2 *Wa = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)ob.x);
         double Y[18];
 #pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            const double w0 = Wi[a * 3], w1 = Wi[a * 3 + 1], w2 = Wi[a * 3 + 2];
-            Y[a * 3 + 0] = w0 * vi[0] + w1 * vi[1] + w2 * vi[2];
-            Y[a * 3 + 1] = w0 * vi[1] + w1 * vi[3] + w2 * vi[4];
-            Y[a * 3 + 2] = w0 * vi[2] + w1 * vi[4] + w2 * vi[5];
-            atomicAdd(ctx.rhs + 6 * (size_t)ci + a, -(w0 * w3[0] + w1 * w3[1] + w2 * w3[2]));
+        for (int h = 0; h < 3; ++h) {                 // rows 2h, 2h+1 of W_a: 6 doubles = 3 x 16 B
+            const double2 w0 = Wa[3 * h], w1 = Wa[3 * h + 1], w2 = Wa[3 * h + 2];
+            const double r0[3] = {w0.x, w0.y, w1.x}, r1[3] = {w1.y, w2.x, w2.y};
+            Y[6 * h + 0] = r0[0] * vi[0] + r0[1] * vi[1] + r0[2] * vi[2];
+            Y[6 * h + 1] = r0[0] * vi[1] + r0[1] * vi[3] + r0[2] * vi[4];
+            Y[6 * h + 2] = r0[0] * vi[2] + r0[1] * vi[4] + r0[2] * vi[5];
+            Y[6 * h + 3] = r1[0] * vi[0] + r1[1] * vi[1] + r1[2] * vi[2];
+            Y[6 * h + 4] = r1[0] * vi[1] + r1[1] * vi[3] + r1[2] * vi[4];
+            Y[6 * h + 5] = r1[0] * vi[2] + r1[1] * vi[4] + r1[2] * vi[5];
         }
-        for (int j = o0; j < o1; ++j) {
-            const int cj = ctx.pm_cam[j];
-            if (cj > ci || ctx.cam_kind[cj] != CAM_FREE) continue;     // lower blocks only (row ci >= col cj)
-            const double *Wj = ctx.W + 18 * (size_t)j;
-            double wj[18];
+        if (diag && ob.x == ob.y) {                   // the observation itself: its share of rhs_c -= W V'^-1 b_p
+            const double *bp = ctx.bp + 3 * (size_t)p;
+            const double b0 = bp[0], b1 = bp[1], b2 = bp[2];
 #pragma unroll
-            for (int k = 0; k < 18; ++k) wj[k] = Wj[k];
-            double *dst = ctx.S + (size_t)(6 * ci) * n + 6 * (size_t)cj;
+            for (int a = 0; a < 6; ++a) racc[a] += Y[a * 3] * b0 + Y[a * 3 + 1] * b1 + Y[a * 3 + 2] * b2;
+        }
+        const double2 *Wb = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)ob.y);
 #pragma unroll
-            for (int a = 0; a < 6; ++a)
+        for (int h = 0; h < 3; ++h) {                 // columns 2h, 2h+1 of the block = rows 2h, 2h+1 of W_b
+            const double2 w0 = Wb[3 * h], w1 = Wb[3 * h + 1], w2 = Wb[3 * h + 2];
 #pragma unroll
-                for (int b = 0; b < 6; ++b)
-                    atomicAdd(dst + (size_t)a * n + b, -(Y[a * 3] * wj[b * 3] + Y[a * 3 + 1] * wj[b * 3 + 1] + Y[a * 3 + 2] * wj[b * 3 + 2]));
+            for (int a = 0; a < 6; ++a) {
+                acc[a * 6 + 2 * h] += Y[a * 3] * w0.x + Y[a * 3 + 1] * w0.y + Y[a * 3 + 2] * w1.x;
+                acc[a * 6 + 2 * h + 1] += Y[a * 3] * w1.y + Y[a * 3 + 1] * w2.x + Y[a * 3 + 2] * w2.y;
+            }
         }
     }
+#pragma unroll
+    for (int k = 0; k < 36; ++k) sred[warp][k][lane] = acc[k];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) sred[warp][36 + k][lane] = racc[k];
+    __syncwarp();
+    double *dst = pi.unit_part + 42 * (size_t)u;
+    for (int k = lane; k < 42; k += 32) {
+        double t = 0.0;
+#pragma unroll
+        for (int l = 0; l < 32; ++l) t += sred[warp][k][l];
+        dst[k] = t;
+    }
+}
+
+// one thread per (segment, entry): ordered sum of the segment's unit partials, single writer per S element
+__global__ void schur_segments_kernel(Ctx ctx, int force) {
+    const LMState *st = ctx.state;
+    if (!force && st->done) return;
+    const PairIndex &pi = ctx.pairs;
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const int seg = (int)(idx / 42), k = (int)(idx % 42);
+    if (seg >= pi.n_seg) return;
+    const int2 cams = pi.seg_cams[seg];
+    if (k >= 36 && cams.x != cams.y) return;
+    double t = 0.0;
+    for (int u = pi.unit_ptr[seg]; u < pi.unit_ptr[seg + 1]; ++u) t += pi.unit_part[42 * (size_t)u + k];
+    if (k < 36) ctx.S[(size_t)(6 * cams.x + k / 6) * ctx.ldS + 6 * (size_t)cams.y + k % 6] -= t;
+    else ctx.rhs[6 * (size_t)cams.x + (k - 36)] -= t;
 }
 
 // -------------------------------------------------------------------------------------------------------------
@@ -690,7 +740,10 @@ void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) 
     const int force = radius_override > 0;
     cudaMemsetAsync(ctx.S, 0, sizeof(double) * chol_matrix_doubles(ctx.n), s);
     schur_init_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, radius_override);
-    schur_accum_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, force);
+    if (ctx.pairs.n_units > 0) {
+        schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, 0, s>>>(ctx, force);
+        schur_segments_kernel<<<(unsigned)(((long long)ctx.pairs.n_seg * 42 + 255) / 256), 256, 0, s>>>(ctx, force);
+    }
 }
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {

@@ -20,6 +20,37 @@ void launch_backsub(const Ctx &ctx, cudaStream_t s);
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
 void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s);
 
+// ba_prep.cu -- device-side index building (ba_set_problem)
+struct PrepScratch {              // grow-only temporary storage
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes);    // returns a cudaError
+    void release();
+};
+struct PrepIn {
+    int Nc, Np, No;
+    const int *obs_cam, *obs_pt;          // [No] caller order (device)
+    const float2 *obs_uv;                 // [No]
+    const unsigned char *cam_fixed;       // [Nc]
+};
+struct PrepOut {
+    // landmark-major
+    float2 *pm_uv; int *pm_cam, *pm_pt, *pt_ptr, *perm;
+    // cameras
+    int *cnt_cam, *cnt_cam_global, *cam_kind, *cam_ptr, *cam_chunk_ptr;
+    // camera-major
+    float2 *cm_uv; int *cm_pt, *chunk_cam, *chunk_beg, *chunk_end;
+    int *flags;                            // device [4]
+    int *h_flags;                          // pinned host [4]: bad index (1-based), unsorted, Ncm, n_chunks
+    int Ncm = 0, n_chunks = 0;
+};
+int prep_observations(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStream_t s);   // <0: -(1 + index of a bad observation)
+int prep_camera_major(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStream_t s);   // needs cnt_cam_global
+int prep_chunks(const PrepIn &in, PrepOut &out, cudaStream_t s);
+int prep_pairs_count(const PrepIn &in, const PrepOut &out, PrepScratch &scr, long long *h_total, cudaStream_t s);
+int prep_pairs_build(const PrepIn &in, const PrepOut &out, PairIndex &pi, PrepScratch &scr, PrepScratch &scr2, int *h_two, cudaStream_t s);
+int prep_pairs_units(PairIndex &pi, cudaStream_t s);
+
 // ba_cholesky.cu -- dense SPD factorisation + solve of the reduced camera system (C6), one cooperative kernel
 constexpr int CHOL_NB = 128;
 int chol_init();                                        // per-device kernel attribute setup; returns cudaError

@@ -57,6 +57,23 @@ struct LMState {
     ba_iteration it;         // summary being filled for the current iteration
 };
 
+// Camera-pair-major view of the observations (dense Schur): entry k = (observation a, observation b) of ONE landmark with
+// camera(a) >= camera(b), entries sorted by (camera a, camera b); a segment = all entries of one S block, cut into
+// units of <= PAIR_UNIT entries (one warp each).
+constexpr int PAIR_UNIT = 256;
+struct PairIndex {
+    long long P;             // entries
+    int n_seg, n_units;
+    size_t seg_cap;          // capacity of the seg_* arrays
+    int2 *pair_obs;          // [P]
+    long long *seg_beg;      // [n_seg]
+    int2 *seg_cams;          // [n_seg] (ci, cj), ci >= cj
+    int *unit_ptr;           // [n_seg + 1]
+    int *unit_seg;           // [n_units]
+    long long *unit_beg;     // [n_units]
+    double *unit_part;       // [n_units][42]: 36 block entries + 6 rhs entries
+};
+
 struct Ctx {
     // sizes
     int Nc, Np, No, n;       // n = 6*Nc (reduced system order; inactive cameras are identity rows)
@@ -82,6 +99,7 @@ struct Ctx {
     const int *cm_pt;
     const int *chunk_cam, *chunk_beg, *chunk_end;   // [n_chunks] work units of <= CHUNK observations
     const int *cam_chunk_ptr;                       // [Nc+1] chunk range per camera
+    PairIndex pairs;         // dense Schur only (built on first use)
     // per-camera tables at x and at the candidate
     CamEntry *tab_x, *tab_c;
     // Jacobi scaling
