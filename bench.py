@@ -36,10 +36,10 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
-def load_workload(name: str):
+def load_workload(name: str, scale: float = 1.0):
     from bundleadjustment_b200 import synthetic as syn
     t = time.time()
-    sc = syn.config(name)
+    sc = syn.config(name, scale=scale)
     pb = syn.flatten(sc)
     log(f"[bench] workload {name}: cams={pb.shape[0]} landmarks={pb.shape[1]} obs={pb.shape[2]} (generated in {time.time() - t:.1f}s, seed {sc.seed})")
     return sc, pb
@@ -146,7 +146,7 @@ def main_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    _, pb = load_workload(args.workload)
+    _, pb = load_workload(args.workload, args.scale)
     threads = os.cpu_count() or 1
     for _ in range(min(args.warmup, 1)):           # one warm-up sample is enough to page the problem in
         run_cpu(pb, args.solver, 1, threads)
@@ -195,7 +195,7 @@ def main_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
 
-    _, pb_full = load_workload(args.workload)
+    _, pb_full = load_workload(args.workload, args.scale)
     Nc, Np, No = pb_full.shape
     kw = dict(max_num_iterations=args.lm_iters)
     if args.solver == "pcg":
@@ -281,6 +281,15 @@ def main_ours(args):
     solver.evaluate_device_ms(3)
     ev_ms = allmax(solver.evaluate_device_ms(20))
     obs_per_s = No / (ev_ms * 1e-3)
+    # symmetric shutdown on every rank BEFORE anything rank-specific: the handle's NCCL communicator is destroyed
+    # collectively, then the control-plane group
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    solver.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return 0
     peaks = {}
@@ -313,7 +322,7 @@ def main_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "cams": Nc, "landmarks": Np, "observations": No, "linear_solver": args.solver,
+        "config": {"workload": args.workload if args.scale == 1.0 else f"{args.workload} x{args.scale}", "cams": Nc, "landmarks": Np, "observations": No, "linear_solver": args.solver,
                    "lm_iters_per_step": n_it / args.steps, "max_num_iterations": args.lm_iters, "huber": True,
                    "parallelism": f"landmark-sharded x{world}" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (W + S >> 126 MB); no flush needed" if args.workload in ("K4", "K5") else "small problem: L2-resident by nature",
@@ -330,8 +339,6 @@ def main_ours(args):
         "cpu_baseline": cpu,
     }
     print(json.dumps(out), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
     return 0
 
 
@@ -348,6 +355,7 @@ def main():
     ap.add_argument("--steps-e2e", type=int, default=3)
     ap.add_argument("--warmup-e2e", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (profiling runs only; recorded in config)")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)

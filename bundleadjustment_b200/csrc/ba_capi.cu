@@ -97,6 +97,7 @@ struct ba_handle {
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
+    DevBuf cm_obs, blk_first_pt;
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
     DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
     DevBuf part, cost_part, sums, maxs, camsums, state, iters, invL, U_loc, bc_loc, sums_loc, maxs_loc;
@@ -123,7 +124,7 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &sums, &maxs,
                          &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt};
         for (DevBuf *b : all) b->free();
         scr.release(); scr2.release();
         has_problem = false;
@@ -306,6 +307,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(pm_uv, 8 * (size_t)No); AL(pm_cam, 4 * (size_t)No); AL(pm_pt, 4 * (size_t)No); AL(pt_ptr, 4 * (size_t)(Np + 1));
     AL(perm_dev, 4 * (size_t)No); AL(cnt_cam, 4 * (size_t)Nc); AL(cnt_cam_global, 4 * (size_t)Nc); AL(cam_kind, 4 * (size_t)Nc);
     AL(cam_ptr, 4 * (size_t)(Nc + 1)); AL(cam_chunk_ptr, 4 * (size_t)(Nc + 1)); AL(cm_uv, 8 * (size_t)No); AL(cm_pt, 4 * (size_t)No);
+    AL(cm_obs, 4 * (size_t)No); AL(blk_first_pt, 4 * ((size_t)No / TILE_WIN + 2));
     AL(chunk_cam, 4 * max_chunks); AL(chunk_beg, 4 * max_chunks); AL(chunk_end, 4 * max_chunks); AL(prep_flags, 16);
     PrepIn &pin = h->prep_in;
     PrepOut &po = h->prep_out;
@@ -315,7 +317,8 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     po.pm_uv = h->pm_uv.as<float2>(); po.pm_cam = h->pm_cam.as<int>(); po.pm_pt = h->pm_pt.as<int>(); po.pt_ptr = h->pt_ptr.as<int>();
     po.perm = h->perm_dev.as<int>(); po.cnt_cam = h->cnt_cam.as<int>(); po.cnt_cam_global = h->cnt_cam_global.as<int>();
     po.cam_kind = h->cam_kind.as<int>(); po.cam_ptr = h->cam_ptr.as<int>(); po.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
-    po.cm_uv = h->cm_uv.as<float2>(); po.cm_pt = h->cm_pt.as<int>();
+    po.cm_uv = h->cm_uv.as<float2>(); po.cm_pt = h->cm_pt.as<int>(); po.cm_obs = h->cm_obs.as<int>();
+    po.blk_first_pt = h->blk_first_pt.as<int>();
     po.chunk_cam = h->chunk_cam.as<int>(); po.chunk_beg = h->chunk_beg.as<int>(); po.chunk_end = h->chunk_end.as<int>();
     po.flags = h->prep_flags.as<int>(); po.h_flags = h->h_prep;
     rc = prep_observations(pin, po, h->scr, s);
@@ -324,6 +327,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
         return fail(BA_ERR_INVALID, "observation %d references camera %d / landmark %d out of range", i, obs_cam[i], obs_pt[i]);
     }
     if (rc) return fail(BA_ERR_CUDA, "prep_observations: %s", cudaGetErrorString((cudaError_t)rc));
+    if ((rc = prep_blocks(pin, po, s))) return fail(BA_ERR_CUDA, "prep_blocks: %s", cudaGetErrorString((cudaError_t)rc));
     // ---- per-camera observation counts (summed over ranks) decide which cameras are part of the problem ----
     h->cam_obs_count.resize(Nc);
     if (h->comm) {
@@ -340,7 +344,9 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     if ((rc = prep_camera_major(pin, po, h->scr, s))) return fail(BA_ERR_CUDA, "prep_camera_major: %s", cudaGetErrorString((cudaError_t)rc));
     if ((rc = prep_chunks(pin, po, s))) return fail(BA_ERR_CUDA, "prep_chunks: %s", cudaGetErrorString((cudaError_t)rc));
     ctx.n_chunks = po.n_chunks;
-    ctx.n_part = std::max((Np + 127) / 128, 1);
+    ctx.n_blocks = po.n_blocks;
+    ctx.tile_cap = std::max(po.max_block_obs, 1);
+    ctx.n_part = ctx.n_blocks;
 
     // ---- parameters and constants ----
     UP(cam0, cam, 6 * (size_t)Nc); UP(cam1, cam, 6 * (size_t)Nc); UP(cam_init, cam, 6 * (size_t)Nc);
@@ -368,6 +374,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.pt_ptr = h->pt_ptr.as<int>(); ctx.cm_uv = h->cm_uv.as<float2>(); ctx.cm_pt = h->cm_pt.as<int>();
     ctx.chunk_cam = h->chunk_cam.as<int>(); ctx.chunk_beg = h->chunk_beg.as<int>(); ctx.chunk_end = h->chunk_end.as<int>();
     ctx.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
+    ctx.cm_obs = h->cm_obs.as<int>(); ctx.blk_first_pt = h->blk_first_pt.as<int>();
     ctx.tab_x = h->tab_x.as<CamEntry>(); ctx.tab_c = h->tab_c.as<CamEntry>();
     ctx.scale_cam = h->scale_cam.as<double>(); ctx.scale_pt = h->scale_pt.as<double>();
     ctx.U = h->U.as<double>(); ctx.bc = h->bc.as<double>(); ctx.V = h->V.as<double>(); ctx.bp = h->bp.as<double>();
@@ -388,6 +395,9 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
         ctx.U_loc = ctx.U; ctx.bc_loc = ctx.bc; ctx.sums_loc = ctx.sums; ctx.maxs_loc = ctx.maxs;
     }
 #undef AL
+    if ((rc = tiles_init(ctx)))
+        return fail(rc == (int)cudaErrorInvalidConfiguration ? BA_ERR_INVALID : BA_ERR_CUDA,
+                    "a landmark block of %d observations does not fit in shared memory (longest supported track: about 1000 observations)", ctx.tile_cap);
     CU(cudaMemsetAsync(h->sums.p, 0, 8 * SUM_COUNT, s));
     CU(cudaMemsetAsync(h->maxs.p, 0, 8 * MAX_COUNT, s));
     CU(cudaMemsetAsync(h->camsums.p, 0, 8 * CS_COUNT, s));

@@ -50,70 +50,108 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// C1+C2+C3 (landmark side): one thread per landmark walks its track: residual, analytic Jacobian, Huber
-// corrector, Jacobi scaling, V_p, b_p, W = Jc^T Jp per observation, cost and gradient-norm partials.
+// Tile kernels (landmark side).  A CTA owns one landmark block = whole landmarks, a CONTIGUOUS run of <= tile_cap
+// landmark-major observations (ba_prep.cu).  Work is split one THREAD PER OBSERVATION (no divergence over track
+// lengths), per-observation results meet in shared memory, and per-landmark sums are taken there in track order
+// (deterministic).  Everything that touches W moves through shared memory so that global traffic is 16-byte coalesced.
 // -------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) linearize_points_kernel(Ctx ctx, int force) {
+struct Tile { int p0, p1, o0, n; };
+__device__ __forceinline__ Tile tile_of(const Ctx &ctx, int b) {
+    Tile t;
+    t.p0 = ctx.blk_first_pt[b]; t.p1 = ctx.blk_first_pt[b + 1];
+    t.o0 = ctx.pt_ptr[t.p0]; t.n = ctx.pt_ptr[t.p1] - t.o0;
+    return t;
+}
+// coalesced copy of n records of 18 doubles between global W (at observation o0) and shared memory
+__device__ __forceinline__ void tile_store_W(double *__restrict__ W, int o0, int n, const double *__restrict__ sW) {
+    double2 *dst = reinterpret_cast<double2 *>(W + 18 * (size_t)o0);
+    const double2 *src = reinterpret_cast<const double2 *>(sW);
+    for (int i = threadIdx.x; i < 9 * n; i += blockDim.x) dst[i] = src[i];
+}
+__device__ __forceinline__ void tile_load_W(const double *__restrict__ W, int o0, int n, double *__restrict__ sW) {
+    const double2 *src = reinterpret_cast<const double2 *>(W + 18 * (size_t)o0);
+    double2 *dst = reinterpret_cast<double2 *>(sW);
+    for (int i = threadIdx.x; i < 9 * n; i += blockDim.x) dst[i] = __ldcs(src + i);     // streamed once per pass
+}
+
+// C1+C2+C3 (landmark side): residual, analytic Jacobian, Huber corrector, Jacobi scaling per observation;
+// W = Jc^T Jp per observation; V_p, b_p per landmark; cost and gradient-norm partials per block.
+__global__ void __launch_bounds__(TILE_THREADS) linearize_points_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
+    extern __shared__ __align__(16) double tsm[];
+    double *sW = tsm;                              // [cap][18]
+    double *sV = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][9]: Jp^T Jp (6) | Jp^T r (3)
     __shared__ double red[32];
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const Tile t = tile_of(ctx, blockIdx.x);
     const double *ptx = ctx.pt[st->cur];
     double cost = 0.0, gsq = 0.0, gmax = 0.0, xsq = 0.0;
-    if (p < ctx.Np) {
-        const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
-        double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-        if (o1 > o0) {
-            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
-            const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
-            for (int o = o0; o < o1; ++o) {
-                const int c = ctx.pm_cam[o];
-                const int kind = ctx.cam_kind[c];
-                const float2 uv = ctx.pm_uv[o];
-                double r[2], Jc[12], Jp[6];
-                obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
-                double rho0;
-                const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
-                const double sr = sqrt(rho1);
-                cost += 0.5 * rho0;
-                r[0] *= sr; r[1] *= sr;
+    for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
+        const int o = t.o0 + k;
+        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const int kind = ctx.cam_kind[c];
+        const float2 uv = ctx.pm_uv[o];
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
+        double r[2], Jc[12], Jp[6];
+        obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
+        double rho0;
+        const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+        const double sr = sqrt(rho1);
+        cost += 0.5 * rho0;
+        r[0] *= sr; r[1] *= sr;
 #pragma unroll
-                for (int j = 0; j < 3; ++j) { const double f = sr * sp[j]; Jp[j] *= f; Jp[3 + j] *= f; }
-                V[0] += Jp[0] * Jp[0] + Jp[3] * Jp[3];
-                V[1] += Jp[0] * Jp[1] + Jp[3] * Jp[4];
-                V[2] += Jp[0] * Jp[2] + Jp[3] * Jp[5];
-                V[3] += Jp[1] * Jp[1] + Jp[4] * Jp[4];
-                V[4] += Jp[1] * Jp[2] + Jp[4] * Jp[5];
-                V[5] += Jp[2] * Jp[2] + Jp[5] * Jp[5];
+        for (int j = 0; j < 3; ++j) { const double f = sr * sp[j]; Jp[j] *= f; Jp[3 + j] *= f; }
+        double *v = sV + 9 * (size_t)k;
+        v[0] = Jp[0] * Jp[0] + Jp[3] * Jp[3];
+        v[1] = Jp[0] * Jp[1] + Jp[3] * Jp[4];
+        v[2] = Jp[0] * Jp[2] + Jp[3] * Jp[5];
+        v[3] = Jp[1] * Jp[1] + Jp[4] * Jp[4];
+        v[4] = Jp[1] * Jp[2] + Jp[4] * Jp[5];
+        v[5] = Jp[2] * Jp[2] + Jp[5] * Jp[5];
 #pragma unroll
-                for (int j = 0; j < 3; ++j) b[j] += Jp[j] * r[0] + Jp[3 + j] * r[1];
-                double *Wo = ctx.W + 18 * (size_t)o;
-                if (kind == CAM_FREE) {
-                    const double *sc = ctx.scale_cam + 6 * (size_t)c;
+        for (int j = 0; j < 3; ++j) v[6 + j] = Jp[j] * r[0] + Jp[3 + j] * r[1];
+        double *Wo = sW + 18 * (size_t)k;
+        if (kind == CAM_FREE) {
+            const double *sc = ctx.scale_cam + 6 * (size_t)c;
 #pragma unroll
-                    for (int a = 0; a < 6; ++a) {
-                        const double f = sr * sc[a];
-                        const double j0 = Jc[a] * f, j1 = Jc[6 + a] * f;
+            for (int a = 0; a < 6; ++a) {
+                const double f = sr * sc[a];
+                const double j0 = Jc[a] * f, j1 = Jc[6 + a] * f;
 #pragma unroll
-                        for (int k = 0; k < 3; ++k) Wo[a * 3 + k] = j0 * Jp[k] + j1 * Jp[3 + k];
-                    }
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 18; ++k) Wo[k] = 0.0;
-                }
+                for (int q = 0; q < 3; ++q) Wo[a * 3 + q] = j0 * Jp[q] + j1 * Jp[3 + q];
             }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 18; ++q) Wo[q] = 0.0;
+        }
+    }
+    __syncthreads();
+    tile_store_W(ctx.W, t.o0, t.n, sW);
+    for (int p = t.p0 + threadIdx.x; p < t.p1; p += blockDim.x) {
+        const int lo = ctx.pt_ptr[p] - t.o0, hi = ctx.pt_ptr[p + 1] - t.o0;
+        double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
+        for (int k = lo; k < hi; ++k) {                     // track order: the same sum order as a serial walk
+            const double *v = sV + 9 * (size_t)k;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) V[j] += v[j];
+#pragma unroll
+            for (int j = 0; j < 3; ++j) b[j] += v[6 + j];
+        }
+        if (hi > lo) {
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
-                const double g = b[j] / sp[j];
-                const double d = X[j] - (X[j] + (-g));
+                const double x = ptx[3 * (size_t)p + j];
+                const double g = b[j] / ctx.scale_pt[3 * (size_t)p + j];
+                const double d = x - (x + (-g));
                 gsq += d * d;
                 gmax = fmax(gmax, fabs(d));
-                xsq += X[j] * X[j];
+                xsq += x * x;
             }
         }
         double *Vp = ctx.V + 6 * (size_t)p;
 #pragma unroll
-        for (int k = 0; k < 6; ++k) Vp[k] = V[k];
+        for (int j = 0; j < 6; ++j) Vp[j] = V[j];
         double *bp = ctx.bp + 3 * (size_t)p;
         bp[0] = b[0]; bp[1] = b[1]; bp[2] = b[2];
     }
@@ -406,30 +444,39 @@ __global__ void schur_segments_kernel(Ctx ctx, int force) {
 // -------------------------------------------------------------------------------------------------------------
 // C7: back-substitution y_p = V'^-1 (b_p - sum W^T y_c), candidate = x + (-y) * scale, model-cost pieces
 // -------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) backsub_kernel(Ctx ctx) {
+__global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     const LMState *st = ctx.state;
     if (st->done) return;
+    extern __shared__ __align__(16) double tsm[];
+    double *sW = tsm;                              // [cap][18]
+    double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]: W_o^T y_c
     __shared__ double red[32];
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const Tile t = tile_of(ctx, blockIdx.x);
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
-    double dxsq = 0, yb = 0, yhy = 0;
-    if (p < ctx.Np) {
-        const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
-        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
-        if (o1 > o0) {
-            double a3[3] = {0, 0, 0};
-            for (int o = o0; o < o1; ++o) {
-                const int c = ctx.pm_cam[o];
-                if (ctx.cam_kind[c] != CAM_FREE) continue;
-                const double *Wo = ctx.W + 18 * (size_t)o;
-                const double *y = ctx.yc + 6 * (size_t)c;
+    tile_load_W(ctx.W, t.o0, t.n, sW);
+    __syncthreads();
+    for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
+        const int c = ctx.pm_cam[t.o0 + k];
+        double a3[3] = {0, 0, 0};
+        if (ctx.cam_kind[c] == CAM_FREE) {
+            const double2 *y2 = reinterpret_cast<const double2 *>(ctx.yc + 6 * (size_t)c);
+            const double2 y01 = y2[0], y23 = y2[1], y45 = y2[2];
+            const double y[6] = {y01.x, y01.y, y23.x, y23.y, y45.x, y45.y};
+            const double *Wo = sW + 18 * (size_t)k;
 #pragma unroll
-                for (int a = 0; a < 6; ++a) {
-                    const double ya = y[a];
-                    a3[0] += Wo[a * 3] * ya; a3[1] += Wo[a * 3 + 1] * ya; a3[2] += Wo[a * 3 + 2] * ya;
-                }
-            }
+            for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * y[a]; a3[1] += Wo[a * 3 + 1] * y[a]; a3[2] += Wo[a * 3 + 2] * y[a]; }
+        }
+        sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
+    }
+    __syncthreads();
+    double dxsq = 0, yb = 0, yhy = 0;
+    for (int p = t.p0 + threadIdx.x; p < t.p1; p += blockDim.x) {
+        const int lo = ctx.pt_ptr[p] - t.o0, hi = ctx.pt_ptr[p + 1] - t.o0;
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        if (hi > lo) {
+            double a3[3] = {0, 0, 0};
+            for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
             const double *Vi = ctx.Vinv + 6 * (size_t)p;
             const double *b = ctx.bp + 3 * (size_t)p;
             const double e0 = b[0] - a3[0], e1 = b[1] - a3[1], e2 = b[2] - a3[2];
@@ -437,14 +484,14 @@ __global__ void __launch_bounds__(128) backsub_kernel(Ctx ctx) {
             const double y1 = Vi[1] * e0 + Vi[3] * e1 + Vi[4] * e2;
             const double y2 = Vi[2] * e0 + Vi[4] * e1 + Vi[5] * e2;
             const double *V = ctx.V + 6 * (size_t)p;
-            yb = y0 * b[0] + y1 * b[1] + y2 * b[2];
-            yhy = y0 * (V[0] * y0 + V[1] * y1 + V[2] * y2) + y1 * (V[1] * y0 + V[3] * y1 + V[4] * y2) +
-                  y2 * (V[2] * y0 + V[4] * y1 + V[5] * y2) + 2.0 * (a3[0] * y0 + a3[1] * y1 + a3[2] * y2);
+            yb += y0 * b[0] + y1 * b[1] + y2 * b[2];
+            yhy += y0 * (V[0] * y0 + V[1] * y1 + V[2] * y2) + y1 * (V[1] * y0 + V[3] * y1 + V[4] * y2) +
+                   y2 * (V[2] * y0 + V[4] * y1 + V[5] * y2) + 2.0 * (a3[0] * y0 + a3[1] * y1 + a3[2] * y2);
             const double *sp = ctx.scale_pt + 3 * (size_t)p;
             const double c0 = X[0] + (-y0) * sp[0], c1 = X[1] + (-y1) * sp[1], c2 = X[2] + (-y2) * sp[2];
             ptc[3 * (size_t)p] = c0; ptc[3 * (size_t)p + 1] = c1; ptc[3 * (size_t)p + 2] = c2;
             const double d0 = X[0] - c0, d1 = X[1] - c1, d2 = X[2] - c2;
-            dxsq = d0 * d0 + d1 * d1 + d2 * d2;
+            dxsq += d0 * d0 + d1 * d1 + d2 * d2;
         } else {
             ptc[3 * (size_t)p] = X[0]; ptc[3 * (size_t)p + 1] = X[1]; ptc[3 * (size_t)p + 2] = X[2];
         }
@@ -702,6 +749,18 @@ __global__ void __launch_bounds__(128) evaluate_materialize_kernel(Ctx ctx, doub
 // host-side launchers
 // =============================================================================================================
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+static inline size_t tile_smem(const Ctx &ctx, int doubles_per_obs) { return sizeof(double) * (size_t)doubles_per_obs * (size_t)ctx.tile_cap; }
+
+// dynamic shared memory of the tile kernels grows with the longest landmark block; returns a cudaError
+int tiles_init(const Ctx &ctx) {
+    const size_t need = tile_smem(ctx, 27);
+    if (need > 227 * 1024) return (int)cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(linearize_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem(ctx, 21));
+    if (e != cudaSuccess) return (int)e;
+    return pcg_tiles_init(ctx);
+}
 
 void launch_init_state(const Ctx &ctx, cudaStream_t s) { lm_init_state_kernel<<<1, 1, 0, s>>>(ctx); }
 
@@ -717,7 +776,7 @@ void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
 // landmark + camera side of one linearisation (local part; the caller all-reduces U/bc/sums when sharded)
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
-    linearize_points_kernel<<<ctx.n_part, 128, 0, s>>>(ctx, force);
+    linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
     if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx, force);
     cam_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<1, 256, 0, s>>>(ctx, force);
@@ -747,7 +806,7 @@ void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) 
 }
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {
-    backsub_kernel<<<ctx.n_part, 128, 0, s>>>(ctx);
+    backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);
     cam_update_kernel<<<1, 256, 0, s>>>(ctx);
 }
 

@@ -18,6 +18,8 @@ void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s)
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_backsub(const Ctx &ctx, cudaStream_t s);
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
+int tiles_init(const Ctx &ctx);                          // per-problem dynamic shared memory opt-in of the tile kernels
+int pcg_tiles_init(const Ctx &ctx);
 void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s);
 
 // ba_prep.cu -- device-side index building (ba_set_problem)
@@ -39,12 +41,15 @@ struct PrepOut {
     // cameras
     int *cnt_cam, *cnt_cam_global, *cam_kind, *cam_ptr, *cam_chunk_ptr;
     // camera-major
-    float2 *cm_uv; int *cm_pt, *chunk_cam, *chunk_beg, *chunk_end;
+    float2 *cm_uv; int *cm_pt, *cm_obs, *chunk_cam, *chunk_beg, *chunk_end;
+    // landmark blocks of the tile kernels
+    int *blk_first_pt; int n_blocks = 0, max_block_obs = 0;
     int *flags;                            // device [4]
-    int *h_flags;                          // pinned host [4]: bad index (1-based), unsorted, Ncm, n_chunks
+    int *h_flags;                          // pinned host [8]: bad index (1-based), unsorted, Ncm, n_chunks, max block obs
     int Ncm = 0, n_chunks = 0;
 };
 int prep_observations(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStream_t s);   // <0: -(1 + index of a bad observation)
+int prep_blocks(const PrepIn &in, PrepOut &out, cudaStream_t s);                            // needs pt_ptr
 int prep_camera_major(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStream_t s);   // needs cnt_cam_global
 int prep_chunks(const PrepIn &in, PrepOut &out, cudaStream_t s);
 int prep_pairs_count(const PrepIn &in, const PrepOut &out, PrepScratch &scr, long long *h_total, cudaStream_t s);

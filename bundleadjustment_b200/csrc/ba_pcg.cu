@@ -14,60 +14,89 @@ __device__ __forceinline__ double lm_diag_pcg(const Ctx &ctx, double jtj, double
 
 #define CG_GUARD(st) if ((st)->done || (st)->cg_done) return;
 
-// Sd_c = U_c + D_c^2 (into Minv as scratch), rhs = b_c   (replicated part)
-__global__ void pcg_init_blocks_kernel(Ctx ctx) {
+// landmark contributions to block-diag(S) and rhs, CAMERA-major and deterministic: one warp per chunk of <= CHUNK
+// observations of one camera gathers W_o (144 B), V'^-1 (48 B) and V'^-1 b_p (24 B) of its observations, accumulates the
+// 21 unique entries of W V'^-1 W^T plus the 6 rhs entries per lane, reduces them with a fixed shuffle tree; the chunk
+// partials are then summed per camera in chunk order (pcg_setup_reduce_kernel).  No atomics.
+__global__ void __launch_bounds__(128) pcg_setup_cams_kernel(Ctx ctx) {
     const LMState *st = ctx.state;
     if (st->done) return;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 6 * ctx.Nc) return;
-    const int c = i / 6, a = i % 6;
-    double *row = ctx.Minv + 36 * (size_t)c + 6 * a;
-    const bool lead = ctx.rank == 0;
-    if (ctx.cam_kind[c] == CAM_FREE) {
-        const double *U = ctx.U + 36 * (size_t)c;
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= ctx.n_chunks) return;
+    const int beg = ctx.chunk_beg[w], end = ctx.chunk_end[w];
+    double acc[27];
 #pragma unroll
-        for (int b = 0; b < 6; ++b) row[b] = lead ? U[a * 6 + b] + (a == b ? lm_diag_pcg(ctx, U[a * 6 + a], st->radius) : 0.0) : 0.0;
-        ctx.rhs[i] = lead ? ctx.bc[i] : 0.0;
-    } else {
+    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    for (int d = beg + lane; d < end; d += 32) {
+        const int e = ctx.cm_obs[d], p = ctx.cm_pt[d];
+        const double2 *W2 = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)e);
+        double wv[18];
 #pragma unroll
-        for (int b = 0; b < 6; ++b) row[b] = (lead && a == b) ? 1.0 : 0.0;
-        ctx.rhs[i] = 0.0;
-    }
-}
-
-// landmark contributions to block-diag(S) and rhs
-__global__ void __launch_bounds__(128) pcg_setup_points_kernel(Ctx ctx) {
-    const LMState *st = ctx.state;
-    if (st->done) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= ctx.Np) return;
-    const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
-    if (o1 <= o0) return;
-    const double *Vi = ctx.Vinv + 6 * (size_t)p;
-    const double vi[6] = {Vi[0], Vi[1], Vi[2], Vi[3], Vi[4], Vi[5]};
-    const double *wv = ctx.wv + 3 * (size_t)p;
-    const double w3[3] = {wv[0], wv[1], wv[2]};
-    for (int i = o0; i < o1; ++i) {
-        const int c = ctx.pm_cam[i];
-        if (ctx.cam_kind[c] != CAM_FREE) continue;
-        const double *Wi = ctx.W + 18 * (size_t)i;
-        double w[18], Y[18];
-#pragma unroll
-        for (int k = 0; k < 18; ++k) w[k] = Wi[k];
+        for (int k = 0; k < 9; ++k) { const double2 v = W2[k]; wv[2 * k] = v.x; wv[2 * k + 1] = v.y; }
+        const double2 *Vi2 = reinterpret_cast<const double2 *>(ctx.Vinv + 6 * (size_t)p);
+        const double2 v01 = Vi2[0], v23 = Vi2[1], v45 = Vi2[2];
+        const double vi[6] = {v01.x, v01.y, v23.x, v23.y, v45.x, v45.y};
+        const double *w3 = ctx.wv + 3 * (size_t)p;
+        const double t0 = w3[0], t1 = w3[1], t2 = w3[2];
+        double Y[18];
 #pragma unroll
         for (int a = 0; a < 6; ++a) {
-            Y[a * 3 + 0] = w[a * 3] * vi[0] + w[a * 3 + 1] * vi[1] + w[a * 3 + 2] * vi[2];
-            Y[a * 3 + 1] = w[a * 3] * vi[1] + w[a * 3 + 1] * vi[3] + w[a * 3 + 2] * vi[4];
-            Y[a * 3 + 2] = w[a * 3] * vi[2] + w[a * 3 + 1] * vi[4] + w[a * 3 + 2] * vi[5];
-            atomicAdd(ctx.rhs + 6 * (size_t)c + a, -(w[a * 3] * w3[0] + w[a * 3 + 1] * w3[1] + w[a * 3 + 2] * w3[2]));
+            Y[a * 3 + 0] = wv[a * 3] * vi[0] + wv[a * 3 + 1] * vi[1] + wv[a * 3 + 2] * vi[2];
+            Y[a * 3 + 1] = wv[a * 3] * vi[1] + wv[a * 3 + 1] * vi[3] + wv[a * 3 + 2] * vi[4];
+            Y[a * 3 + 2] = wv[a * 3] * vi[2] + wv[a * 3 + 1] * vi[4] + wv[a * 3 + 2] * vi[5];
+            acc[21 + a] += wv[a * 3] * t0 + wv[a * 3 + 1] * t1 + wv[a * 3 + 2] * t2;
         }
-        double *dst = ctx.Minv + 36 * (size_t)c;
+        int k = 0;
 #pragma unroll
         for (int a = 0; a < 6; ++a)
 #pragma unroll
-            for (int b = 0; b < 6; ++b)
-                atomicAdd(dst + a * 6 + b, -(Y[a * 3] * w[b * 3] + Y[a * 3 + 1] * w[b * 3 + 1] + Y[a * 3 + 2] * w[b * 3 + 2]));
+            for (int b = a; b < 6; ++b) { acc[k] += Y[a * 3] * wv[b * 3] + Y[a * 3 + 1] * wv[b * 3 + 1] + Y[a * 3 + 2] * wv[b * 3 + 2]; ++k; }
     }
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) {
+        double *dst = ctx.cam_part + 27 * (size_t)w;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) dst[k] = acc[k];
+    }
+}
+
+// per camera: Minv <- (U + D^2) - sum of chunk partials (symmetric), rhs <- b_c - sum; replicated terms from rank 0 only
+__global__ void pcg_setup_reduce_kernel(Ctx ctx) {
+    const LMState *st = ctx.state;
+    if (st->done) return;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ctx.Nc) return;
+    double *M = ctx.Minv + 36 * (size_t)c;
+    const bool lead = ctx.rank == 0;
+    if (ctx.cam_kind[c] != CAM_FREE) {
+#pragma unroll
+        for (int k = 0; k < 36; ++k) M[k] = (lead && (k % 7 == 0)) ? 1.0 : 0.0;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) ctx.rhs[6 * (size_t)c + a] = 0.0;
+        return;
+    }
+    double acc[27];
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    for (int w = ctx.cam_chunk_ptr[c]; w < ctx.cam_chunk_ptr[c + 1]; ++w) {
+        const double *src = ctx.cam_part + 27 * (size_t)w;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) acc[k] += src[k];
+    }
+    const double *U = ctx.U + 36 * (size_t)c;
+    int k = 0;
+#pragma unroll
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+        for (int b = a; b < 6; ++b) {
+            double v = lead ? U[a * 6 + b] + (a == b ? lm_diag_pcg(ctx, U[a * 6 + a], st->radius) : 0.0) : 0.0;
+            v -= acc[k++];
+            M[a * 6 + b] = v; M[b * 6 + a] = v;
+        }
+#pragma unroll
+    for (int a = 0; a < 6; ++a) ctx.rhs[6 * (size_t)c + a] = (lead ? ctx.bc[6 * (size_t)c + a] : 0.0) - acc[21 + a];
 }
 
 // invert the 6x6 diagonal blocks in place; start CG: x = 0, r = b
@@ -157,34 +186,57 @@ __global__ void __launch_bounds__(1024) pcg_precond_kernel(Ctx ctx) {
     }
 }
 
-// q -= sum_p W_p V'^-1 W_p^T v   (landmark-major; v = p or x)
-__global__ void __launch_bounds__(128) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ q) {
+// q -= sum_p W_p V'^-1 W_p^T v   (v = p or x).  Tile kernel: the block's W records are read from HBM ONCE (coalesced,
+// into shared memory) and serve both halves of the product: t_o = W_o^T v_c per observation, a_p = sum over the track
+// (in track order), s_p = V'^-1 a_p per landmark, then q_c -= W_o s_p per observation (fp64 reductions into the
+// L2-resident 6 Nc vector).
+__global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ q) {
     const LMState *st = ctx.state;
     CG_GUARD(st);
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= ctx.Np) return;
-    const int o0 = ctx.pt_ptr[p], o1 = ctx.pt_ptr[p + 1];
-    if (o1 <= o0) return;
-    double a3[3] = {0, 0, 0};
-    for (int o = o0; o < o1; ++o) {
-        const int c = ctx.pm_cam[o];
-        if (ctx.cam_kind[c] != CAM_FREE) continue;
-        const double *Wo = ctx.W + 18 * (size_t)o;
-        const double *x = v + 6 * (size_t)c;
-#pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            const double xa = x[a];
-            a3[0] += Wo[a * 3] * xa; a3[1] += Wo[a * 3 + 1] * xa; a3[2] += Wo[a * 3 + 2] * xa;
-        }
+    extern __shared__ __align__(16) double tsm[];
+    double *sW = tsm;                              // [cap][18]
+    double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]
+    const int b = blockIdx.x;
+    const int p0 = ctx.blk_first_pt[b], p1 = ctx.blk_first_pt[b + 1];
+    const int o0 = ctx.pt_ptr[p0], n = ctx.pt_ptr[p1] - o0;
+    if (n == 0) return;
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)o0);
+        double2 *dst = reinterpret_cast<double2 *>(sW);
+        for (int i = threadIdx.x; i < 9 * n; i += blockDim.x) dst[i] = __ldcs(src + i);
     }
-    const double *Vi = ctx.Vinv + 6 * (size_t)p;
-    const double t0 = Vi[0] * a3[0] + Vi[1] * a3[1] + Vi[2] * a3[2];
-    const double t1 = Vi[1] * a3[0] + Vi[3] * a3[1] + Vi[4] * a3[2];
-    const double t2 = Vi[2] * a3[0] + Vi[4] * a3[1] + Vi[5] * a3[2];
-    for (int o = o0; o < o1; ++o) {
-        const int c = ctx.pm_cam[o];
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+        const int c = ctx.pm_cam[o0 + k];
+        double a3[3] = {0, 0, 0};
+        if (ctx.cam_kind[c] == CAM_FREE) {
+            const double2 *x2 = reinterpret_cast<const double2 *>(v + 6 * (size_t)c);
+            const double2 x01 = x2[0], x23 = x2[1], x45 = x2[2];
+            const double x[6] = {x01.x, x01.y, x23.x, x23.y, x45.x, x45.y};
+            const double *Wo = sW + 18 * (size_t)k;
+#pragma unroll
+            for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
+        }
+        sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
+    }
+    __syncthreads();
+    for (int p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
+        const int lo = ctx.pt_ptr[p] - o0, hi = ctx.pt_ptr[p + 1] - o0;
+        if (hi <= lo) continue;
+        double a3[3] = {0, 0, 0};
+        for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
+        const double *Vi = ctx.Vinv + 6 * (size_t)p;
+        const double t0 = Vi[0] * a3[0] + Vi[1] * a3[1] + Vi[2] * a3[2];
+        const double t1 = Vi[1] * a3[0] + Vi[3] * a3[1] + Vi[4] * a3[2];
+        const double t2 = Vi[2] * a3[0] + Vi[4] * a3[1] + Vi[5] * a3[2];
+        for (int k = lo; k < hi; ++k) { sT[3 * (size_t)k] = t0; sT[3 * (size_t)k + 1] = t1; sT[3 * (size_t)k + 2] = t2; }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+        const int c = ctx.pm_cam[o0 + k];
         if (ctx.cam_kind[c] != CAM_FREE) continue;
-        const double *Wo = ctx.W + 18 * (size_t)o;
+        const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
+        const double *Wo = sW + 18 * (size_t)k;
 #pragma unroll
         for (int a = 0; a < 6; ++a)
             atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
@@ -286,19 +338,23 @@ static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 // local part of the setup; the caller all-reduces Minv (36 Nc) and rhs (6 Nc) when sharded, then calls
 // launch_pcg_iteration repeatedly (first call starts CG).
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
-    pcg_init_blocks_kernel<<<cdiv(6 * ctx.Nc, 128), 128, 0, s>>>(ctx);
-    pcg_setup_points_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx);
+    if (ctx.n_chunks > 0) pcg_setup_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx);
+    pcg_setup_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
+}
+static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 21 * (size_t)ctx.tile_cap; }
+int pcg_tiles_init(const Ctx &ctx) {
+    return (int)cudaFuncSetAttribute(pcg_matvec_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_tile_smem(ctx));
 }
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s) { pcg_start_kernel<<<1, 256, 0, s>>>(ctx); }
 
 void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s) {      // precondition + direction + local matvec
     pcg_precond_kernel<<<1, 1024, 0, s>>>(ctx);
-    pcg_matvec_points_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, ctx.cg_p, ctx.cg_q);
+    pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_q);
 }
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) { pcg_update_kernel<<<1, 1024, 0, s>>>(ctx); }
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part of S x into cg_z
     cudaMemsetAsync(ctx.cg_z, 0, sizeof(double) * ctx.n, s);
-    pcg_matvec_points_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, ctx.cg_x, ctx.cg_z);
+    pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_z);
 }
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<1, 1024, 0, s>>>(ctx); }
 void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<1, 1024, 0, s>>>(ctx); }

@@ -71,12 +71,34 @@ __global__ void prep_cam_keys_kernel(int No, int Nc, const int *__restrict__ pm_
 }
 
 __global__ void prep_gather_cm_kernel(int Ncm, const int *__restrict__ order, const float2 *__restrict__ pm_uv,
-                                      const int *__restrict__ pm_pt, float2 *__restrict__ cm_uv, int *__restrict__ cm_pt) {
+                                      const int *__restrict__ pm_pt, float2 *__restrict__ cm_uv, int *__restrict__ cm_pt,
+                                      int *__restrict__ cm_obs) {
     const int d = blockIdx.x * blockDim.x + threadIdx.x;
     if (d >= Ncm) return;
     const int e = order[d];
     cm_uv[d] = pm_uv[e];
     cm_pt[d] = pm_pt[e];
+    cm_obs[d] = e;
+}
+
+// landmark blocks of the tile kernels: block b = the landmarks whose first observation index lies in
+// [TILE_WIN b, TILE_WIN (b + 1)) -- whole landmarks, <= TILE_WIN + (longest track) - 1 observations, no prefix dependency
+__global__ void prep_blocks_kernel(int n_blocks, int Np, const int *__restrict__ pt_ptr, int *__restrict__ first_pt) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > n_blocks) return;
+    if (b == n_blocks) { first_pt[b] = Np; return; }
+    const long long target = (long long)TILE_WIN * b;
+    int lo = 0, hi = Np;                      // first p in [0, Np] with pt_ptr[p] >= target
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pt_ptr[mid] >= target) hi = mid; else lo = mid + 1;
+    }
+    first_pt[b] = lo;
+}
+__global__ void prep_blocks_max_kernel(int n_blocks, const int *__restrict__ pt_ptr, const int *__restrict__ first_pt, int *__restrict__ mx) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    atomicMax(mx, pt_ptr[first_pt[b + 1]] - pt_ptr[first_pt[b]]);
 }
 
 __global__ void prep_chunks_kernel(int Nc, const int *__restrict__ cam_ptr, const int *__restrict__ cam_chunk_ptr,
@@ -228,6 +250,17 @@ int prep_observations(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStre
     return (int)cudaGetLastError();
 }
 
+int prep_blocks(const PrepIn &in, PrepOut &out, cudaStream_t s) {
+    out.n_blocks = in.No / TILE_WIN + 1;
+    PCU(cudaMemsetAsync(out.flags + 2, 0, sizeof(int), s));
+    prep_blocks_kernel<<<cdivp(out.n_blocks + 1, 256), 256, 0, s>>>(out.n_blocks, in.Np, out.pt_ptr, out.blk_first_pt);
+    prep_blocks_max_kernel<<<cdivp(out.n_blocks, 256), 256, 0, s>>>(out.n_blocks, out.pt_ptr, out.blk_first_pt, out.flags + 2);
+    PCU(cudaMemcpyAsync(out.h_flags + 4, out.flags + 2, sizeof(int), cudaMemcpyDeviceToHost, s));
+    PCU(cudaStreamSynchronize(s));
+    out.max_block_obs = out.h_flags[4];
+    return (int)cudaGetLastError();
+}
+
 int prep_camera_major(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStream_t s) {
     const int No = in.No, Nc = in.Nc;
     int bits = 1;
@@ -259,7 +292,7 @@ int prep_camera_major(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStre
     PCU(cudaStreamSynchronize(s));
     out.Ncm = out.h_flags[2];
     out.n_chunks = out.h_flags[3];
-    if (out.Ncm > 0) prep_gather_cm_kernel<<<cdivp(out.Ncm, 256), 256, 0, s>>>(out.Ncm, idx1, out.pm_uv, out.pm_pt, out.cm_uv, out.cm_pt);
+    if (out.Ncm > 0) prep_gather_cm_kernel<<<cdivp(out.Ncm, 256), 256, 0, s>>>(out.Ncm, idx1, out.pm_uv, out.pm_pt, out.cm_uv, out.cm_pt, out.cm_obs);
     return (int)cudaGetLastError();
 }
 

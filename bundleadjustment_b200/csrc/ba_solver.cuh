@@ -94,9 +94,12 @@ struct Ctx {
     const int *pm_cam;
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
+    const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
+    int n_blocks, tile_cap;
     // camera-major copy
     const float2 *cm_uv;
     const int *cm_pt;
+    const int *cm_obs;       // landmark-major position of each camera-major entry
     const int *chunk_cam, *chunk_beg, *chunk_end;   // [n_chunks] work units of <= CHUNK observations
     const int *cam_chunk_ptr;                       // [Nc+1] chunk range per camera
     PairIndex pairs;         // dense Schur only (built on first use)
@@ -135,5 +138,7 @@ struct Ctx {
 };
 
 constexpr int CHUNK = 128;   // observations per camera-side reduction unit
+constexpr int TILE_WIN = 192;   // observation window defining a landmark block of the tile kernels (ba_prep.cu)
+constexpr int TILE_THREADS = 256;
 
 } // namespace ba

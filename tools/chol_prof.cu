@@ -9,12 +9,12 @@
 
 using namespace ba;
 
-__global__ void fill_spd(double *A, int n, int ld, size_t rows) {
+__global__ void fill_spd(double *A, int n, int ld, size_t rows, int band) {
     const size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (idx >= rows * (size_t)ld) return;
     const int r = (int)(idx / ld), c = (int)(idx % ld);
     double v = 0.0;
-    if (r < n && c <= r) {
+    if (r < n && c <= r && r - c <= band) {
         unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
         h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
         v = ((h & 0xffff) / 65536.0 - 0.5) * 0.01;
@@ -26,6 +26,7 @@ __global__ void fill_spd(double *A, int n, int ld, size_t rows) {
 
 int main(int argc, char **argv) {
     const int n = argc > 1 ? atoi(argv[1]) : 10200;
+    const int band = argc > 2 ? atoi(argv[2]) : n;
     const int ld = chol_ld(n);
     const size_t rows = chol_rows(n);
     double *A, *work, *y;
@@ -35,7 +36,7 @@ int main(int argc, char **argv) {
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
     for (int r = 0; r < 4; ++r) {
-        fill_spd<<<(unsigned)((rows * ld + 255) / 256), 256>>>(A, n, ld, rows);
+        fill_spd<<<(unsigned)((rows * ld + 255) / 256), 256>>>(A, n, ld, rows, band);
         cudaEventRecord(e0);
         int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, 0);
         cudaEventRecord(e1);
