@@ -19,6 +19,7 @@ EXPORTS = [
     "ba_set_problem", "ba_set_parameters", "ba_reset_parameters", "ba_solve", "ba_get_cameras", "ba_get_points",
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
     "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
+    "ba_get_reduced_system_stats", "ba_tile_elimination_order",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
     "ba_pose_to_cam", "ba_cam_to_pose",
 ]
@@ -67,6 +68,8 @@ if not os.path.exists(LIB_PATH):
 
 lib = C.CDLL(LIB_PATH)
 lib.ba_last_error.restype = C.c_char_p
+lib.ba_tile_elimination_order.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+lib.ba_get_reduced_system_stats.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_dense_spd_solve.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
 lib.ba_schur_system.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
 
@@ -154,6 +157,12 @@ class Solver:
     def launch_count(self) -> int:
         return int(lib.ba_get_launch_count(self._h))
 
+    def reduced_system_stats(self) -> dict:
+        """Order of the reduced camera system, filled / total 128x128 tiles of its Cholesky factor, flops per solve."""
+        out = np.zeros(4)
+        _check(lib.ba_get_reduced_system_stats(self._h, _ptr(out)), "ba_get_reduced_system_stats")
+        return {"n": int(out[0]), "filled_tiles": int(out[1]), "lower_tiles": int(out[2]), "flops": float(out[3])}
+
     def cameras(self) -> np.ndarray:
         out = np.zeros((self.shape[0], 6))
         _check(lib.ba_get_cameras(self._h, _ptr(out)), "ba_get_cameras")
@@ -240,6 +249,17 @@ def dense_spd_solve(A, b, device: int = 0, repeats: int = 1):
 
 
 # ---- host-only helpers -------------------------------------------------------------------------------------
+def tile_elimination_order(adj):
+    """Nested-dissection order of the Cholesky tiles + {depth, filled tiles} before/after (host only)."""
+    adj = np.ascontiguousarray(adj, np.uint8)
+    G = adj.shape[0]
+    order = np.zeros(G, np.int32)
+    stats = np.zeros(4)
+    _check(lib.ba_tile_elimination_order(G, _ptr(adj), _ptr(order), _ptr(stats)), "ba_tile_elimination_order")
+    return order, {"depth_natural": int(stats[0]), "depth_ordered": int(stats[1]),
+                   "filled_natural": int(stats[2]), "filled_ordered": int(stats[3])}
+
+
 def comm_unique_id() -> bytes:
     buf = (C.c_uint8 * 128)()
     _check(lib.ba_comm_unique_id(buf), "ba_comm_unique_id")

@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <string>
@@ -94,6 +95,8 @@ struct ba_handle {
     PrepIn prep_in;
     PrepOut prep_out;
     bool pairs_built = false;
+    CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
+    DevBuf tile_map, cam_row, row_src, yperm;
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
@@ -124,8 +127,9 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &sums, &maxs,
                          &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &tile_map, &cam_row, &row_src, &yperm};
         for (DevBuf *b : all) b->free();
+        chol_plan_destroy(&chol_plan);
         scr.release(); scr2.release();
         has_problem = false;
     }
@@ -242,14 +246,19 @@ int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
 }
 
 int ensure_dense(ba_handle *h) {
-    const int n = h->ctx.n;
+    // padded reduced system: one 128-row Cholesky tile per group of CAMS_PER_TILE consecutive cameras
+    const int G = (h->ctx.Nc + CAMS_PER_TILE - 1) / CAMS_PER_TILE;
+    const int n = G * CHOL_NB;
     const size_t need = sizeof(double) * chol_matrix_doubles(n);
     if (h->S.bytes < need) {
         CU(h->S.alloc(need));
         CU(h->invL.alloc(sizeof(double) * chol_work_doubles(n)));
+        CU(h->yperm.alloc(sizeof(double) * (size_t)n));
     }
     h->ctx.S = h->S.as<double>();
-    h->ctx.ldS = chol_ld(n);
+    h->ctx.ldS = n;
+    h->ctx.cam_row = h->cam_row.as<int>();
+    h->ctx.row_src = h->row_src.as<int>();
     if (!h->pairs_built) {
         // camera-pair-major index for the deterministic Schur reduction (device-side, once per problem)
         cudaStream_t s = h->stream;
@@ -273,6 +282,39 @@ int ensure_dense(ba_handle *h) {
         pi.unit_seg = h->unit_seg.as<int>(); pi.unit_beg = h->unit_beg.as<long long>(); pi.unit_part = h->unit_part.as<double>();
         if ((rc = prep_pairs_units(pi, s))) return fail(BA_ERR_CUDA, "prep_pairs_units: %s", cudaGetErrorString((cudaError_t)rc));
         h->scr2.release();            // the sort scratch is the largest temporary: give it back
+        // which camera groups share landmarks (union over ranks) -> elimination order of the tiles (nested dissection),
+        // row layout of S, tile-level symbolic factorisation
+        CU(h->tile_map.alloc((size_t)G * G));
+        if ((rc = prep_group_map(pi, G, h->tile_map.as<unsigned char>(), s)))
+            return fail(BA_ERR_CUDA, "prep_group_map: %s", cudaGetErrorString((cudaError_t)rc));
+        if (h->comm) NC(ncclAllReduce(h->tile_map.p, h->tile_map.p, (size_t)G * G, ncclUint8, ncclMax, h->comm, s));
+        std::vector<unsigned char> adj((size_t)G * G);
+        CU(cudaMemcpyAsync(adj.data(), h->tile_map.p, adj.size(), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        const auto env_on = [](const char *name) { const char *v = std::getenv(name); return v && v[0] == '1'; };
+        std::vector<int> order;
+        if (env_on("BA_B200_NATURAL_ORDER")) { order.resize(G); std::iota(order.begin(), order.end(), 0); }   // measurement aid
+        else chol_tile_order(G, adj.data(), order);
+        if ((int)order.size() != G) return fail(BA_ERR_STATE, "tile ordering lost nodes (internal error)");
+        std::vector<int> pos(G);
+        for (int p = 0; p < G; ++p) pos[order[p]] = p;
+        std::vector<int> cam_row(h->ctx.Nc), row_src((size_t)n, -1);
+        for (int c = 0; c < h->ctx.Nc; ++c) {
+            cam_row[c] = CHOL_NB * pos[c / CAMS_PER_TILE] + 6 * (c % CAMS_PER_TILE);
+            for (int a = 0; a < 6; ++a) row_src[(size_t)cam_row[c] + a] = 6 * c + a;
+        }
+        if ((rc = upload(h->cam_row, cam_row.data(), cam_row.size(), s))) return rc;
+        if ((rc = upload(h->row_src, row_src.data(), row_src.size(), s))) return rc;
+        h->ctx.cam_row = h->cam_row.as<int>();
+        h->ctx.row_src = h->row_src.as<int>();
+        std::vector<unsigned char> nz((size_t)G * G, 0);
+        for (int gi = 0; gi < G; ++gi)
+            for (int gj = 0; gj <= gi; ++gj)
+                if (gi == gj || adj[(size_t)gi * G + gj]) nz[(size_t)std::max(pos[gi], pos[gj]) * G + std::min(pos[gi], pos[gj])] = 1;
+        CU(cudaStreamSynchronize(s));                                    // the uploads read the host vectors above
+        // BA_B200_DENSE_TILES=1 (measurement aid): treat every tile as filled
+        if ((rc = chol_plan_create(n, env_on("BA_B200_DENSE_TILES") ? nullptr : nz.data(), &h->chol_plan, s)))
+            return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
         h->pairs_built = true;
     }
     return BA_OK;
@@ -486,14 +528,15 @@ int enqueue_linear_solve(ba_handle *h) {
         // rhs row of the augmented matrix
         if (h->comm) {
             // lower triangle + rhs would do; the full buffer keeps the collective a single contiguous message
-            if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.ldS))) return rc;     // the n real rows (padding excluded)
+            if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.ldS * ctx.ldS))) return rc;
             if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
         }
         // rhs^T becomes row ldS of the matrix: the forward substitution is then part of the factorisation's dataflow
-        CU(cudaMemcpyAsync(ctx.S + (size_t)ctx.ldS * ctx.ldS, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToDevice, s));
-        const int ce = chol_factor_solve(ctx.S, ctx.n, h->invL.as<double>(), ctx.yc, ctx.state, nullptr, s);
+        launch_chol_rhs(ctx, s);
+        const int ce = chol_factor_solve(ctx.S, ctx.ldS, h->invL.as<double>(), h->yperm.as<double>(), ctx.state, nullptr, &h->chol_plan, s);
         if (ce) return fail(BA_ERR_CUDA, "chol_factor_solve: %s", cudaGetErrorString((cudaError_t)ce));
-        h->launches += 2;
+        launch_chol_unpermute(ctx, h->yperm.as<double>(), s);
+        h->launches += 3;
     } else {
         launch_pcg_setup(ctx, s);
         h->launches += 2;
@@ -776,14 +819,70 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
     launch_point_invert(ctx, radius, s);
     launch_schur_build(ctx, radius, s);
     if (h->comm) {
-        if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.n * ctx.ldS))) return rc;
+        if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.ldS * ctx.ldS))) return rc;
         if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
     }
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
-    if (S) CU(cudaMemcpy2D(S, 8 * (size_t)ctx.n, ctx.S, 8 * (size_t)ctx.ldS, 8 * (size_t)ctx.n, (size_t)ctx.n, cudaMemcpyDeviceToHost));
+    if (S) {
+        // the device matrix is in elimination order (lower blocks): hand it back in camera order, lower blocks
+        const size_t ld = (size_t)ctx.ldS, n = (size_t)ctx.n;
+        std::vector<double> Sp(ld * ld);
+        std::vector<int> cam_row(ctx.Nc);
+        CU(cudaMemcpy(Sp.data(), ctx.S, 8 * ld * ld, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(cam_row.data(), ctx.cam_row, 4 * (size_t)ctx.Nc, cudaMemcpyDeviceToHost));
+        std::memset(S, 0, 8 * n * n);
+        for (int ci = 0; ci < ctx.Nc; ++ci)
+            for (int cj = 0; cj <= ci; ++cj) {
+                const size_t r = cam_row[ci], q = cam_row[cj];
+                for (int a = 0; a < 6; ++a)
+                    for (int b = 0; b < 6; ++b)
+                        S[(6 * (size_t)ci + a) * n + 6 * (size_t)cj + b] = (r >= q) ? Sp[(r + a) * ld + q + b] : Sp[(q + b) * ld + r + a];
+            }
+    }
     if (rhs) CU(cudaMemcpy(rhs, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToHost));
     if (cost) CU(cudaMemcpy(cost, ctx.sums + SUM_LIN_COST, 8, cudaMemcpyDeviceToHost));
+    return BA_OK;
+}
+
+// Reduced-system bookkeeping of the current problem (dense Schur): out = {order n, filled tiles of L, tiles in the lower
+// triangle, flops of one factorisation + solve over the filled tiles}.  Builds the pair index / plan on first use.
+extern "C" int ba_get_reduced_system_stats(ba_handle *h, double out[4]) {
+    if (!h || !out) return fail(BA_ERR_INVALID, "NULL argument");
+    if (!h->has_problem) return fail(BA_ERR_STATE, "no problem set");
+    CU(cudaSetDevice(h->device));
+    int rc;
+    if ((rc = ensure_dense(h))) return rc;
+    const double T = (double)h->chol_plan.T;
+    out[0] = (double)h->ctx.ldS; out[1] = (double)h->chol_plan.filled_tiles; out[2] = T * (T + 1) / 2; out[3] = h->chol_plan.flops;
+    return BA_OK;
+}
+
+// Host-only: elimination order of the Cholesky tiles for a tile adjacency (G x G bytes, lower triangle read), as used for
+// the reduced camera system.  order[pos] = tile.  stats (may be NULL) = {dependency depth in natural order, depth in the
+// returned order, filled tiles natural, filled tiles ordered}.
+extern "C" int ba_tile_elimination_order(int32_t G, const uint8_t *adj, int32_t *order, double stats[4]) {
+    if (G <= 0 || !adj || !order) return fail(BA_ERR_INVALID, "bad arguments");
+    std::vector<int> ord;
+    chol_tile_order(G, adj, ord);
+    if ((int)ord.size() != G) return fail(BA_ERR_STATE, "tile ordering lost nodes (internal error)");
+    for (int p = 0; p < G; ++p) order[p] = ord[p];
+    if (stats) {
+        std::vector<int> pos(G);
+        for (int p = 0; p < G; ++p) pos[ord[p]] = p;
+        std::vector<unsigned char> nat((size_t)G * G, 0), per((size_t)G * G, 0);
+        for (int i = 0; i < G; ++i)
+            for (int j = 0; j <= i; ++j)
+                if (i == j || adj[(size_t)i * G + j]) {
+                    nat[(size_t)i * G + j] = 1;
+                    per[(size_t)std::max(pos[i], pos[j]) * G + std::min(pos[i], pos[j])] = 1;
+                }
+        int d0 = 0, d1 = 0;
+        long long f0 = 0, f1 = 0;
+        chol_plan_stats(G * CHOL_NB, nat.data(), &d0, &f0, nullptr);
+        chol_plan_stats(G * CHOL_NB, per.data(), &d1, &f1, nullptr);
+        stats[0] = d0; stats[1] = d1; stats[2] = (double)f0; stats[3] = (double)f1;
+    }
     return BA_OK;
 }
 
@@ -806,6 +905,15 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     CU(dInv.alloc(8 * chol_work_doubles(n))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
     CU(cudaMemcpy(dA0.p, Ah.data(), 8 * Ah.size(), cudaMemcpyHostToDevice));
     CU(cudaMemset(dFail.p, 0, 4));
+    // tile pattern of the caller's matrix (exact zeros only) -> the same sparsity plan the LM loop uses
+    const int T = np / CHOL_NB;
+    std::vector<unsigned char> nz((size_t)T * T, 0);
+    for (int i = 0; i < n; ++i) {
+        const double *row = A + (size_t)i * n;
+        for (int j = 0; j <= i; ++j) if (row[j] != 0.0) nz[(size_t)(i / CHOL_NB) * T + j / CHOL_NB] = 1;
+    }
+    CholPlan plan;
+    if ((rc = chol_plan_create(n, nz.data(), &plan, 0))) return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
     cudaEvent_t e1, e2;
     CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
     if (repeats < 1) repeats = 1;
@@ -813,7 +921,7 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     for (int r = 0; r < repeats; ++r) {
         CU(cudaMemcpy(dA.p, dA0.p, 8 * Ah.size(), cudaMemcpyDeviceToDevice));
         CU(cudaEventRecord(e1, 0));
-        const int ce = chol_factor_solve(dA.as<double>(), n, dInv.as<double>(), dY.as<double>(), nullptr, dFail.as<int>(), 0);
+        const int ce = chol_factor_solve(dA.as<double>(), n, dInv.as<double>(), dY.as<double>(), nullptr, dFail.as<int>(), &plan, 0);
         if (ce) return fail(BA_ERR_CUDA, "chol_factor_solve: %s", cudaGetErrorString((cudaError_t)ce));
         CU(cudaEventRecord(e2, 0));
         CU(cudaDeviceSynchronize());
@@ -830,6 +938,7 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     if (ms) *ms = best;
     cudaEventDestroy(e1); cudaEventDestroy(e2);
     dA.free(); dA0.free(); dInv.free(); dY.free(); dFail.free();
+    chol_plan_destroy(&plan);
     if (failed) return fail(BA_ERR_INVALID, "matrix is not positive definite");
     return BA_OK;
 }

@@ -24,6 +24,10 @@
 
 #include <cooperative_groups.h>
 
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
 namespace ba {
 
 constexpr int NB = CHOL_NB;            // 128: tile edge
@@ -49,8 +53,8 @@ static_assert(CHOL_SMEM <= 227 * 1024, "shared memory budget");
 int chol_ld(int n) { return ((n + NB - 1) / NB) * NB; }
 size_t chol_rows(int n) { return (size_t)chol_ld(n) + NB; }
 size_t chol_matrix_doubles(int n) { return chol_rows(n) * (size_t)chol_ld(n); }
-// work area: L_jj^-1 blocks, then int flags [rowdone (T + 1) | diagdone (T) | ydone (T) | abort (1)]
-static inline int chol_flag_count(int T) { return 3 * T + 2; }
+// work area: L_jj^-1 blocks, then int flags [tiledone ((T + 1) x T) | ydone (T) | abort (1)]
+static inline int chol_flag_count(int T) { return (T + 1) * T + T + 1; }
 size_t chol_work_doubles(int n) {
     const int T = chol_ld(n) / NB;
     return (size_t)T * NB * NB + (size_t)T * NB + (size_t)(chol_flag_count(T) + 1) / 2 + 1;
@@ -75,6 +79,11 @@ __device__ __forceinline__ int ld_acquire(const int *p) {
     asm volatile("ld.acquire.gpu.global.s32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ int ld_relaxed(const int *p) {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void st_release(int *p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
@@ -96,14 +105,18 @@ struct CholArgs {
     int n;                // logical order (entries of y written)
     double *invL;         // [T][128*128]
     double *ypad;         // [T][128] solution blocks as they are produced (cross-CTA exchange)
-    int *rowdone;         // [T + 1] number of finished tiles in the row (columns 0 .. rowdone-1 are final)
-    int *diagdone;        // [T]
+    int *tiledone;        // [T + 1][T] tile (i, j) of L (row T: of z) is final
     int *ydone;           // [T]
     int *abort_flag;      // [1] set when a wait timed out (never expected; keeps a bug from hanging the GPU)
     double *y;            // [n]
     LMState *state;       // may be nullptr
     int *fail_flag;       // may be nullptr
     long long *prof;      // may be nullptr; [grid][8] ns: start, phase-1 end, end, waited (ph 1), waited (ph 2), potrf, tasks, trsm
+    // tile-sparsity plan (chol_plan_create): only filled tiles are tasks, only filled k-blocks are multiplied
+    const int4 *task;     // [ntasks + 1] (i, j, dependency level, first klist entry), sorted by level
+    const int *klist;     // k-blocks of each task's update, ascending
+    const unsigned char *fill;   // [(T + 1)][T] filled tiles of L (row T = rhs)
+    int ntasks;
 };
 
 constexpr long long SPIN_TIMEOUT_NS = 4000000000LL;    // 4 s
@@ -345,18 +358,17 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp >> 2, wn = warp & 3;               // 2 x 4 warps -> 64 x 32 per warp
     const int g = lane >> 2, tig = lane & 3;
-    const int T = p.T, TR = p.T + 1, ld = p.ld;
-    const int ntasks = T * (T + 1) / 2 + T;                // lower triangle of T x T + the rhs tile row
+    const int T = p.T, ld = p.ld;
     __shared__ int s_have;
     bool aborted = false;
     long long waited = 0, t_potrf = 0, t_trsm = 0, n_tasks = 0;
     const long long t_start = p.prof ? global_ns() : 0;
 
     // ================= phase 1: factorisation + forward substitution =================
-    int j = 0, colbase = 0;
-    for (int t = blockIdx.x; t < ntasks && !aborted; t += gridDim.x) {
-        while (t >= colbase + (TR - j)) { colbase += TR - j; ++j; }
-        const int i = j + (t - colbase);
+    for (int t = blockIdx.x; t < p.ntasks && !aborted; t += gridDim.x) {
+        const int4 tk = __ldg(p.task + t);
+        const int i = tk.x, j = tk.y, kbeg = tk.w;       // klist[kbeg ..): k-blocks with L_ik and L_jk both filled
+        const int nkb = __ldg(&p.task[t + 1].w) - tk.w;
         const bool diag = (i == j);
         double acc[8][4][2];
 #pragma unroll
@@ -366,20 +378,36 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 
         const double *Arow = p.A + (size_t)i * NB * ld;    // row panel i
         const double *Brow = p.A + (size_t)j * NB * ld;    // row panel j
-        const int nk = j * (NB / BK);                      // k-slices of the bulk update
-        int have = 0;                                      // k-blocks known to be final in both row panels
-        // L_ik and L_jk final for k-block kb.  Called at uniform points by ALL threads; only thread 0 touches the flags
-        // (an acquire costs an L1 invalidate), the verdict travels through shared memory + a barrier.  The operand
-        // loads that follow are cp.async.cg (L2), so the CTA barrier is enough to order them after the acquire.
-        auto ensure = [&](int kb) -> bool {
-            if (kb < have) return true;
-            if (tid == 0) {
-                int h = -1;
-                if (wait_ge(p.rowdone + i, kb + 1, p.abort_flag, waited) && (diag || wait_ge(p.rowdone + j, kb + 1, p.abort_flag, waited))) {
-                    const int hi = ld_acquire(p.rowdone + i), hj = diag ? hi : ld_acquire(p.rowdone + j);
-                    h = min(min(hi, hj), j);
+        const int nk = nkb * KSL;                          // k-slices of the bulk update
+        int have = 0;                                      // leading klist entries known to be final in both row panels
+        // L_ik and L_jk final for klist entry q.  Called at uniform points by ALL threads; only warp 0 touches the flags:
+        // lane l probes the flag of entry q + l / 2 (row panel i or j) with a relaxed load, one ballot finds how many
+        // leading entries are complete, one fence turns the relaxed loads into acquires.  Only if entry q itself is not
+        // there yet does lane 0 spin.  The verdict travels through shared memory + a barrier; the operand loads that follow
+        // are cp.async.cg (L2), so the CTA barrier is enough to order them after the acquire.
+        auto ensure = [&](int q) -> bool {
+            if (q < have) return true;
+            if (warp == 0) {
+                const int e = q + (lane >> 1);
+                int ok = 1;
+                if (e < nkb && !(diag && (lane & 1))) {
+                    const int kb = __ldg(p.klist + kbeg + e);
+                    ok = ld_relaxed(p.tiledone + (size_t)((lane & 1) ? j : i) * T + kb);
                 }
-                s_have = h;
+                const unsigned m = __ballot_sync(0xffffffffu, ok == 0);
+                int h = m ? (__ffs(m) - 1) >> 1 : 16;      // leading complete entries
+                h = min(q + h, nkb);
+                if (h == q) {                              // entry q itself is pending: wait for it
+                    if (lane == 0) {
+                        const int kb = __ldg(p.klist + kbeg + q);
+                        const bool fine = wait_ge(p.tiledone + (size_t)i * T + kb, 1, p.abort_flag, waited) &&
+                                          (diag || wait_ge(p.tiledone + (size_t)j * T + kb, 1, p.abort_flag, waited));
+                        s_have = fine ? q + 1 : -1;
+                    }
+                } else {
+                    __threadfence();                       // relaxed loads above + fence = acquire
+                    if (lane == 0) s_have = h;
+                }
             }
             __syncthreads();
             const int h = s_have;
@@ -389,8 +417,9 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         };
         auto issue = [&](int kt) {
             double *st = smem + (size_t)(kt % NSTAGE) * STAGE_DOUBLES;
-            load_slice(st, Arow + (size_t)kt * BK, ld, tid);
-            if (!diag) load_slice(st + NB * SPAD, Brow + (size_t)kt * BK, ld, tid);
+            const size_t col = (size_t)__ldg(p.klist + kbeg + kt / KSL) * NB + (size_t)(kt % KSL) * BK;
+            load_slice(st, Arow + col, ld, tid);
+            if (!diag) load_slice(st + NB * SPAD, Brow + col, ld, tid);
         };
         // prologue
         for (int s = 0; s < NSTAGE - 1; ++s) {
@@ -455,10 +484,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             }
             __threadfence();
             __syncthreads();
-            if (tid == 0) { st_release(p.diagdone + j, 1); st_release(p.rowdone + j, j + 1); }
+            if (tid == 0) st_release(p.tiledone + (size_t)j * T + j, 1);
         } else {
             // L_ij = C * L_jj^-T : A operand = the staged tile, B operand = invL_j through a 2-stage ring
-            if (tid == 0 && !wait_ge(p.diagdone + j, 1, p.abort_flag, waited)) aborted = true;
+            if (tid == 0 && !wait_ge(p.tiledone + (size_t)j * T + j, 1, p.abort_flag, waited)) aborted = true;
             aborted = __syncthreads_or(aborted);
             if (aborted) break;
             const long long tt0 = p.prof ? global_ns() : 0;
@@ -491,7 +520,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             }
             __threadfence();
             __syncthreads();
-            if (tid == 0) st_release(p.rowdone + i, j + 1);
+            if (tid == 0) st_release(p.tiledone + (size_t)i * T + j, 1);
             if (p.prof) t_trsm += global_ns() - tt0;
         }
         ++n_tasks;
@@ -511,13 +540,14 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     double *part = smem + 2 * NB;      // [2][128]
     const double *z = p.A + (size_t)T * NB * ld;
     for (int m = T - 1 - (int)blockIdx.x; m >= 0; m -= gridDim.x) {
-        // z_m is final once tile (T, m) is; L_km tiles are final once row k reached column m
-        if (!__syncthreads_and(tid != 0 || (wait_ge(p.rowdone + T, m + 1, p.abort_flag, waited) && wait_ge(p.diagdone + m, 1, p.abort_flag, waited)))) break;
+        // z_m is final once tile (T, m) is
+        if (!__syncthreads_and(tid != 0 || (wait_ge(p.tiledone + (size_t)T * T + m, 1, p.abort_flag, waited) && wait_ge(p.tiledone + (size_t)m * T + m, 1, p.abort_flag, waited)))) break;
         if (tid < NB) zs[tid] = __ldcg(z + (size_t)m * NB + tid);
         const int c = tid & (NB - 1), half = tid >> 7;
         bool ok = true;
         for (int k = T - 1; k > m; --k) {
-            ok = tid != 0 || (wait_ge(p.ydone + k, 1, p.abort_flag, waited) && wait_ge(p.rowdone + k, m + 1, p.abort_flag, waited));
+            if (!__ldg(p.fill + (size_t)k * T + m)) continue;          // L_km is structurally zero
+            ok = tid != 0 || (wait_ge(p.ydone + k, 1, p.abort_flag, waited) && wait_ge(p.tiledone + (size_t)k * T + m, 1, p.abort_flag, waited));
             if (!__syncthreads_and(ok)) { ok = false; break; }
             if (tid < NB) ys[tid] = __ldcg(p.ypad + (size_t)k * NB + tid);
             __syncthreads();
@@ -599,21 +629,236 @@ int chol_init() {
     return 0;
 }
 
-int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, cudaStream_t s) {
+// ---- elimination order of the tiles -----------------------------------------------------------------------------
+// Nested dissection on the tile graph (George's automatic scheme: the middle level of a BFS level structure rooted at a
+// pseudo-peripheral node is a separator).  Parts on the two sides of a separator share no tile, so their columns
+// factorise concurrently and the dependency chain shrinks from T tiles to roughly leaf + sum of the separators above
+// it.  Graphs without a usable level structure (dense co-visibility) come back in BFS order, which is harmless.
+namespace {
+struct TileGraph {
+    int G;
+    const unsigned char *adj;
+    bool edge(int a, int b) const { return a != b && adj[(size_t)std::max(a, b) * G + std::min(a, b)] != 0; }
+};
+
+// BFS over the nodes with in[v] == tag; fills lvl (levels) and out (visit order); returns the number of levels
+int bfs(const TileGraph &g, const std::vector<int> &in, int tag, int root, std::vector<int> &lvl, std::vector<int> &out) {
+    out.clear();
+    out.push_back(root);
+    lvl[root] = 0;
+    int nlev = 1;
+    for (size_t h = 0; h < out.size(); ++h) {
+        const int v = out[h];
+        for (int w = 0; w < g.G; ++w)
+            if (in[w] == tag && lvl[w] < 0 && g.edge(v, w)) { lvl[w] = lvl[v] + 1; nlev = std::max(nlev, lvl[w] + 1); out.push_back(w); }
+    }
+    return nlev;
+}
+
+void dissect(const TileGraph &g, std::vector<int> nodes, std::vector<int> &in, int &next_tag, std::vector<int> &order) {
+    const int tag = next_tag++;
+    for (int v : nodes) in[v] = tag;
+    std::vector<int> lvl(g.G, -1), comp, tmp;
+    for (int seed : nodes) {
+        if (lvl[seed] >= 0 || in[seed] != tag) continue;
+        // connected component of seed, then a pseudo-peripheral root (two sweeps towards a far, low-degree node)
+        int nlev = bfs(g, in, tag, seed, lvl, comp);
+        for (int sweep = 0; sweep < 3; ++sweep) {
+            int best = -1, bestdeg = 1 << 30;
+            for (int v : comp) {
+                if (lvl[v] != nlev - 1) continue;
+                int deg = 0;
+                for (int w : comp) deg += g.edge(v, w);
+                if (deg < bestdeg) { bestdeg = deg; best = v; }
+            }
+            for (int v : comp) lvl[v] = -1;
+            const int nl2 = bfs(g, in, tag, best, lvl, tmp);
+            const bool deeper = nl2 > nlev;
+            nlev = nl2; comp = tmp;
+            if (!deeper) break;
+        }
+        // separator = the level that balances the two sides best
+        std::vector<int> cnt(nlev, 0);
+        for (int v : comp) cnt[lvl[v]]++;
+        int m = -1, best_cost = 1 << 30, before = 0;
+        const int total = (int)comp.size();
+        for (int l = 0; l < nlev; ++l) {
+            if (l >= 1 && l <= nlev - 2) {
+                const int after = total - before - cnt[l];
+                const int cost = std::max(before, after) * 4 + cnt[l];
+                if (cost < best_cost) { best_cost = cost; m = l; }
+            }
+            before += cnt[l];
+        }
+        const bool leaf = m < 0 || total <= 2 * cnt[m] + 2 || 3 * cnt[m] > total;
+        if (leaf) {
+            for (int v : comp) { order.push_back(v); in[v] = -1; }     // BFS order keeps the leaf banded
+            continue;
+        }
+        std::vector<int> rest, sep;
+        for (int v : comp) (lvl[v] == m ? sep : rest).push_back(v);
+        for (int v : comp) in[v] = -1;                                  // leave this level's tag (lvl stays set: visited)
+        dissect(g, rest, in, next_tag, order);
+        for (int v : sep) order.push_back(v);
+    }
+}
+} // namespace
+
+void chol_tile_order(int G, const unsigned char *adj, std::vector<int> &order) {
+    order.clear();
+    order.reserve(G);
+    TileGraph g{G, adj};
+    std::vector<int> nodes(G), in(G, -1);
+    for (int v = 0; v < G; ++v) nodes[v] = v;
+    int next_tag = 0;
+    dissect(g, nodes, in, next_tag, order);
+}
+
+// ---- tile-sparsity plan ------------------------------------------------------------------------------------------
+// The reduced camera matrix of a SLAM / SfM map is block-banded when cameras only share landmarks with their
+// neighbours.  A tile of L can only be nonzero if it is nonzero in S or filled by the elimination of an earlier column
+// (tile-level symbolic factorisation); everything else is skipped.  The arithmetic on the filled tiles is exactly the
+// dense one (the skipped terms are exact zeros), so results do not depend on the plan.
+namespace {
+struct HostPlan {
+    std::vector<unsigned char> blob;
+    size_t o_task = 0, o_kl = 0, o_fill = 0;
+    int T = 0, ntasks = 0, depth = 0;
+    long long filled = 0;
+    double flops = 0.0;
+};
+
+void plan_analyse(int n, const unsigned char *nz, HostPlan &hp) {
+    const int T = chol_ld(n) / NB;
+    std::vector<unsigned char> f((size_t)(T + 1) * T, 0);
+    for (int i = 0; i < T; ++i)
+        for (int j = 0; j <= i; ++j) f[(size_t)i * T + j] = (i == j) || !nz || nz[(size_t)i * T + j] || nz[(size_t)j * T + i];
+    std::vector<int> rows;
+    for (int j = 0; j < T; ++j) {                       // eliminating column j couples all its rows pairwise
+        rows.clear();
+        for (int i = j + 1; i < T; ++i) if (f[(size_t)i * T + j]) rows.push_back(i);
+        for (size_t a = 0; a < rows.size(); ++a)
+            for (size_t b = a + 1; b < rows.size(); ++b) f[(size_t)rows[b] * T + rows[a]] = 1;
+    }
+    for (int j = 0; j < T; ++j) f[(size_t)T * T + j] = 1;   // the rhs row
+    // tasks = filled tiles; dependency level = longest chain of tasks below it.  Tasks are handed out in level order
+    // (a topological order, so the round-robin dataflow cannot deadlock): independent sub-chains of a sparse pattern
+    // run side by side.  For a dense matrix this is exactly the column-major order.
+    struct HostTask { int i, j, level, kbeg, kend; };
+    std::vector<HostTask> ht;
+    std::vector<int> kl_tmp, level((size_t)(T + 1) * T, 0);
+    double flops = 0.0;
+    long long filled = 0;
+    const double t3 = (double)NB * NB * NB;
+    for (int j = 0; j < T; ++j)
+        for (int i = j; i <= T; ++i) {
+            if (!f[(size_t)i * T + j]) continue;
+            const int kbeg = (int)kl_tmp.size();
+            int lv = 0;
+            for (int k = 0; k < j; ++k)
+                if (f[(size_t)i * T + k] && f[(size_t)j * T + k]) {
+                    kl_tmp.push_back(k);
+                    lv = std::max(lv, 1 + std::max(level[(size_t)i * T + k], level[(size_t)j * T + k]));
+                }
+            if (i != j) lv = std::max(lv, 1 + level[(size_t)j * T + j]);
+            level[(size_t)i * T + j] = lv;
+            const double nkb = (double)((int)kl_tmp.size() - kbeg);
+            if (i == T) flops += 2.0 * NB * NB * nkb + (double)NB * NB;             // one rhs row block
+            else if (i == j) { flops += t3 * nkb + t3 / 3.0; ++filled; }
+            else { flops += 2.0 * t3 * nkb + t3; ++filled; }
+            ht.push_back({i, j, lv, kbeg, (int)kl_tmp.size()});
+        }
+    std::stable_sort(ht.begin(), ht.end(), [](const HostTask &a, const HostTask &b) { return a.level < b.level; });
+    std::vector<int4> task;
+    std::vector<int> klist;
+    klist.reserve(kl_tmp.size());
+    int depth = 0;
+    for (const HostTask &h : ht) {
+        task.push_back(make_int4(h.i, h.j, h.level, (int)klist.size()));
+        klist.insert(klist.end(), kl_tmp.begin() + h.kbeg, kl_tmp.begin() + h.kend);
+        depth = std::max(depth, h.level + 1);
+    }
+    task.push_back(make_int4(0, 0, 0, (int)klist.size()));
+    flops += 2.0 * (double)filled * NB * NB;                                        // back substitution
+    const size_t o_task = 0, o_kl = o_task + sizeof(int4) * task.size();
+    const size_t o_fill = o_kl + sizeof(int) * std::max<size_t>(klist.size(), 1);
+    const size_t bytes = o_fill + f.size();
+    std::vector<unsigned char> &blob = hp.blob;
+    blob.assign(bytes, 0);
+    std::memcpy(blob.data() + o_task, task.data(), sizeof(int4) * task.size());
+    if (!klist.empty()) std::memcpy(blob.data() + o_kl, klist.data(), sizeof(int) * klist.size());
+    std::memcpy(blob.data() + o_fill, f.data(), f.size());
+    hp.o_task = o_task; hp.o_kl = o_kl; hp.o_fill = o_fill;
+    hp.T = T; hp.ntasks = (int)task.size() - 1; hp.depth = depth; hp.filled = filled; hp.flops = flops;
+}
+} // namespace
+
+// host-only: dependency depth (tasks) and filled tiles of the plan for a tile pattern
+void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *filled, double *flops) {
+    HostPlan hp;
+    plan_analyse(n, nz, hp);
+    if (depth) *depth = hp.depth;
+    if (filled) *filled = hp.filled;
+    if (flops) *flops = hp.flops;
+}
+
+int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t s) {
+    HostPlan hp;
+    plan_analyse(n, nz, hp);
+    const size_t bytes = hp.blob.size();
+    if (pl->cap < bytes) {
+        if (pl->blob) cudaFree(pl->blob);
+        pl->blob = nullptr; pl->cap = 0;
+        cudaError_t e = cudaMalloc(&pl->blob, bytes);
+        if (e != cudaSuccess) return (int)e;
+        pl->cap = bytes;
+    }
+    cudaError_t e = cudaMemcpyAsync(pl->blob, hp.blob.data(), bytes, cudaMemcpyHostToDevice, s);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return (int)e;
+    unsigned char *b = static_cast<unsigned char *>(pl->blob);
+    pl->n = n; pl->T = hp.T; pl->ntasks = hp.ntasks;
+    pl->task = reinterpret_cast<const int4 *>(b + hp.o_task);
+    pl->klist = reinterpret_cast<const int *>(b + hp.o_kl);
+    pl->fill = b + hp.o_fill;
+    pl->filled_tiles = hp.filled;
+    pl->depth = hp.depth;
+    pl->flops = hp.flops;
+    return 0;
+}
+
+void chol_plan_destroy(CholPlan *pl) {
+    if (pl->blob) cudaFree(pl->blob);
+    *pl = CholPlan();
+}
+
+static CholPlan g_dense_plan[64];   // per device: fully dense plan of the last order asked for (standalone use)
+
+int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s) {
     int dev = 0;
     cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
     const int ld = chol_ld(n), T = ld / NB;
+    if (!plan) {
+        if (g_dense_plan[dev].n != n) {
+            int rc = chol_plan_create(n, nullptr, &g_dense_plan[dev], s);
+            if (rc) return rc;
+        }
+        plan = &g_dense_plan[dev];
+    }
+    if (plan->n != n || plan->T != T) return (int)cudaErrorInvalidValue;
     CholArgs p;
     p.A = A; p.ld = ld; p.T = T; p.n = n;
     p.invL = work;
     p.ypad = work + (size_t)T * NB * NB;
     int *flags = reinterpret_cast<int *>(p.ypad + (size_t)T * NB);
-    p.rowdone = flags; p.diagdone = flags + (T + 1); p.ydone = p.diagdone + T; p.abort_flag = p.ydone + T;
+    p.tiledone = flags; p.ydone = flags + (size_t)(T + 1) * T; p.abort_flag = p.ydone + T;
     p.y = y; p.state = state; p.fail_flag = fail_flag; p.prof = g_chol_prof;
+    p.task = plan->task; p.klist = plan->klist; p.fill = plan->fill; p.ntasks = plan->ntasks;
     cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)chol_flag_count(T), s);
     if (e != cudaSuccess) return (int)e;
-    const int ntasks = T * (T + 3) / 2;
-    int grid = g_chol_grid[dev] < ntasks ? g_chol_grid[dev] : ntasks;
+    int grid = g_chol_grid[dev] < plan->ntasks ? g_chol_grid[dev] : plan->ntasks;
     if (grid < 1) return (int)cudaErrorInitializationError;
     void *args[] = {&p};
     e = cudaLaunchCooperativeKernel((const void *)chol_dataflow_kernel, dim3(grid), dim3(256), args, CHOL_SMEM, s);

@@ -330,22 +330,39 @@ __global__ void schur_init_kernel(Ctx ctx, double radius_override) {
     const LMState *st = ctx.state;
     if (radius_override <= 0 && st->done) return;
     const double radius = radius_override > 0 ? radius_override : st->radius;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (camera, row a) + the padding rows
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per row of S
     if (i >= ctx.ldS) return;
-    if (i >= 6 * ctx.Nc) { ctx.S[(size_t)i * ctx.ldS + i] = 1.0; return; }     // identity padding up to the tile edge
-    const int c = i / 6, a = i % 6;
-    double *row = ctx.S + (size_t)i * ctx.ldS + 6 * (size_t)c;
     const bool lead = ctx.rank == 0;
+    const int src = ctx.row_src[i];
+    if (src < 0) { ctx.S[(size_t)i * ctx.ldS + i] = lead ? 1.0 : 0.0; return; }     // identity padding
+    const int c = src / 6, a = src % 6;
+    double *row = ctx.S + (size_t)i * ctx.ldS + ctx.cam_row[c];
     if (ctx.cam_kind[c] == CAM_FREE) {
         const double *U = ctx.U + 36 * (size_t)c;
 #pragma unroll
         for (int b = 0; b < 6; ++b) row[b] = lead ? U[a * 6 + b] + (a == b ? lm_diag(ctx, U[a * 6 + a], radius) : 0.0) : 0.0;
-        ctx.rhs[i] = lead ? ctx.bc[i] : 0.0;
+        ctx.rhs[src] = lead ? ctx.bc[src] : 0.0;
     } else {
 #pragma unroll
         for (int b = 0; b < 6; ++b) row[b] = (lead && a == b) ? 1.0 : 0.0;
-        ctx.rhs[i] = 0.0;
+        ctx.rhs[src] = 0.0;
     }
+}
+
+// rhs (camera order) -> row ldS of S (elimination order); solution y (elimination order) -> yc (camera order)
+__global__ void chol_rhs_kernel(Ctx ctx) {
+    if (ctx.state->done) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ctx.ldS) return;
+    const int src = ctx.row_src[i];
+    ctx.S[(size_t)ctx.ldS * ctx.ldS + i] = src >= 0 ? ctx.rhs[src] : 0.0;
+}
+__global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
+    if (ctx.state->done) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ctx.ldS) return;
+    const int src = ctx.row_src[i];
+    if (src >= 0) ctx.yc[src] = y[i];
 }
 
 // C5 proper: S -= sum_p W_i V'^-1 W_j^T and rhs -= sum_p W_i V'^-1 b_p as DETERMINISTIC segmented reductions over the
@@ -437,7 +454,12 @@ __global__ void schur_segments_kernel(Ctx ctx, int force) {
     if (k >= 36 && cams.x != cams.y) return;
     double t = 0.0;
     for (int u = pi.unit_ptr[seg]; u < pi.unit_ptr[seg + 1]; ++u) t += pi.unit_part[42 * (size_t)u + k];
-    if (k < 36) ctx.S[(size_t)(6 * cams.x + k / 6) * ctx.ldS + 6 * (size_t)cams.y + k % 6] -= t;
+    if (k < 36) {
+        // block (camera x, camera y) of the lower triangle IN ELIMINATION ORDER: transposed if y comes later than x
+        const int r = ctx.cam_row[cams.x] + k / 6, q = ctx.cam_row[cams.y] + k % 6;
+        if (ctx.cam_row[cams.x] >= ctx.cam_row[cams.y]) ctx.S[(size_t)r * ctx.ldS + q] -= t;
+        else ctx.S[(size_t)q * ctx.ldS + r] -= t;
+    }
     else ctx.rhs[6 * (size_t)cams.x + (k - 36)] -= t;
 }
 
@@ -797,13 +819,16 @@ void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s)
 
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) {
     const int force = radius_override > 0;
-    cudaMemsetAsync(ctx.S, 0, sizeof(double) * chol_matrix_doubles(ctx.n), s);
+    cudaMemsetAsync(ctx.S, 0, sizeof(double) * chol_matrix_doubles(ctx.ldS), s);
     schur_init_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, radius_override);
     if (ctx.pairs.n_units > 0) {
         schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, 0, s>>>(ctx, force);
         schur_segments_kernel<<<(unsigned)(((long long)ctx.pairs.n_seg * 42 + 255) / 256), 256, 0, s>>>(ctx, force);
     }
 }
+
+void launch_chol_rhs(const Ctx &ctx, cudaStream_t s) { chol_rhs_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx); }
+void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s) { chol_unpermute_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, y); }
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {
     backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);

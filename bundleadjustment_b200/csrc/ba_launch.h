@@ -3,6 +3,8 @@
 
 #include "ba_solver.cuh"
 
+#include <vector>
+
 namespace ba {
 
 // ba_kernels.cu
@@ -16,6 +18,8 @@ void launch_begin_iteration(const Ctx &ctx, cudaStream_t s);
 void launch_decide(const Ctx &ctx, cudaStream_t s);
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
+void launch_chol_rhs(const Ctx &ctx, cudaStream_t s);                       // rhs -> row ldS of S, in elimination order
+void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s);  // y (elimination order) -> yc
 void launch_backsub(const Ctx &ctx, cudaStream_t s);
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
 int tiles_init(const Ctx &ctx);                          // per-problem dynamic shared memory opt-in of the tile kernels
@@ -55,6 +59,8 @@ int prep_chunks(const PrepIn &in, PrepOut &out, cudaStream_t s);
 int prep_pairs_count(const PrepIn &in, const PrepOut &out, PrepScratch &scr, long long *h_total, cudaStream_t s);
 int prep_pairs_build(const PrepIn &in, const PrepOut &out, PairIndex &pi, PrepScratch &scr, PrepScratch &scr2, int *h_two, cudaStream_t s);
 int prep_pairs_units(PairIndex &pi, cudaStream_t s);
+// map[G x G] bytes (lower triangle): camera groups (CAMS_PER_TILE consecutive cameras = one Cholesky tile) that share a landmark
+int prep_group_map(const PairIndex &pi, int G, unsigned char *map, cudaStream_t s);
 
 // ba_cholesky.cu -- dense SPD factorisation + solve of the reduced camera system (C6), one cooperative kernel
 constexpr int CHOL_NB = 128;
@@ -67,7 +73,22 @@ size_t chol_work_doubles(int n);
 // padding, row n_pad = rhs^T, all other rows zero.  On exit y (n) holds the solution and A's lower triangle holds L.
 // state may be nullptr (standalone use); otherwise the kernel early-exits on state->done and reports breakdown in
 // state->chol_fail.  fail_flag (device int, may be nullptr) is set on breakdown as well.  Returns a cudaError.
-int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, cudaStream_t s);
+// plan: tile-level sparsity plan of this matrix (nullptr = dense).
+struct CholPlan {
+    int n = 0, T = 0, ntasks = 0;
+    const int4 *task = nullptr; const int *klist = nullptr; const unsigned char *fill = nullptr;
+    long long filled_tiles = 0;      // tiles of L (T x T lower triangle) that can be nonzero
+    double flops = 0.0;              // factorisation + both substitutions over the filled tiles
+    int depth = 0;                   // longest dependency chain, in tasks
+    void *blob = nullptr; size_t cap = 0;   // device storage (grow-only)
+};
+// nz: host T x T bytes, (i, j) != 0 where tile (i, j) or (j, i) of S can be nonzero (nullptr = dense); synchronises s.
+// Elimination order of the tiles from their adjacency (G x G bytes, lower triangle read): order[pos] = tile.
+void chol_tile_order(int G, const unsigned char *adj, std::vector<int> &order);
+int chol_plan_create(int n, const unsigned char *nz, CholPlan *plan, cudaStream_t s);
+void chol_plan_destroy(CholPlan *plan);
+void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *filled, double *flops);   // host only
+int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
 
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s);       // local block-diag(S) + rhs (all-reduce Minv, rhs after)

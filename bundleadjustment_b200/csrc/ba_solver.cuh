@@ -118,8 +118,12 @@ struct Ctx {
     double *Vinv;            // [Np][6]
     double *wv;              // [Np][3] = Vinv * bp
     // reduced system
-    double *S;               // [chol_rows(n)][ldS] row-major, lower blocks; row ldS = rhs^T (see ba_cholesky.cu)
-    int ldS;                 // leading dimension = n rounded up to the Cholesky tile (128)
+    // One Cholesky tile (128 rows) holds CAMS_PER_TILE consecutive cameras (126 rows + 2 identity rows); the tiles are laid
+    // out in elimination order (nested dissection of the camera-group graph), so camera c's block starts at row cam_row[c].
+    double *S;               // [ldS + 128][ldS] row-major, lower blocks; row ldS = rhs^T (see ba_cholesky.cu)
+    int ldS;                 // order of the padded system = 128 * number of camera groups
+    const int *cam_row;      // [Nc]
+    const int *row_src;      // [ldS] 6 c + a of the camera parameter in that row, -1 for padding rows
     double *rhs;             // [n] (becomes y_c after the solve)
     double *yc;              // [n]
     // partial sums
@@ -137,6 +141,7 @@ struct Ctx {
     volatile int *host_flags; // mapped pinned: [0] = done, [1] = cg_done
 };
 
+constexpr int CAMS_PER_TILE = 21;   // 6 * 21 = 126 <= 128 (CHOL_NB)
 constexpr int CHUNK = 128;   // observations per camera-side reduction unit
 constexpr int TILE_WIN = 192;   // observation window defining a landmark block of the tile kernels (ba_prep.cu)
 constexpr int TILE_THREADS = 256;

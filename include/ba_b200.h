@@ -171,11 +171,21 @@ int ba_set_profiling(ba_handle *h, int32_t on);
  * ms (may be NULL): best device time of factor + solve over `repeats` runs. */
 int ba_dense_spd_solve(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats);
 
+/* Reduced camera system of the current problem (dense Schur): out = {padded order (one 128-row tile per 21 cameras), 128 x 128 tiles of the Cholesky factor that
+ * can be nonzero, tiles in the lower triangle, flops of one factorisation + solve over those tiles}.  Cameras that share
+ * no landmark leave exact-zero tiles in S (DenseSchurComplementSolver fills them with zeros, ceres
+ * schur_complement_solver.cc); the factorisation skips tiles that stay zero, which changes no result. */
+int ba_get_reduced_system_stats(ba_handle *h, double out[4]);
+
 /* ---- host-only helpers (no GPU needed) ---------------------------------------------------------------- */
 /* Balanced contiguous landmark partition: cut[r]..cut[r+1] for r in [0,n_ranks); weight = sum over the
  * landmark's track length t of t (iterative) or t*(t+1)/2 (dense Schur).  obs_pt must be sorted ascending. */
 int ba_partition_landmarks(int32_t n_pt, int32_t n_obs, const int32_t *obs_pt, int32_t n_ranks,
                            int32_t quadratic, int32_t *cut /* n_ranks+1 */);
+/* Elimination order of the 128 x 128 Cholesky tiles for a tile adjacency (G x G bytes, lower triangle read): nested
+ * dissection, so that independent parts of the reduced camera system factorise concurrently.  order[pos] = tile.
+ * stats (may be NULL) = {dependency depth natural order, depth in the returned order, filled tiles natural, ordered}. */
+int ba_tile_elimination_order(int32_t G, const uint8_t *adj, int32_t *order, double stats[4]);
 /* Matrix4f::inverse() stand-in (float32 adjugate), ceres::AngleAxisToRotationMatrix / RotationMatrixToAngleAxis
  * (column-major 3x3) */
 void ba_inverse4x4_f32(const float m[16], float out[16]);

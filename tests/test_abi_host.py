@@ -105,3 +105,35 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "ba_oracle" not in text and "import oracle" not in text and "from oracle" not in text, os.path.join(dirpath, f)
+
+
+def test_tile_elimination_order_band_and_dense():
+    """Nested dissection of the Cholesky tile graph (host only): a permutation; shortens the dependency chain of banded
+    co-visibility by a large factor; leaves a dense graph alone."""
+    from bundleadjustment_b200 import capi
+    for G, band in [(81, 2), (40, 1), (7, 1), (1, 0)]:
+        adj = np.zeros((G, G), np.uint8)
+        for i in range(G):
+            adj[i, max(0, i - band):i + 1] = 1
+        order, st = capi.tile_elimination_order(adj)
+        assert sorted(order.tolist()) == list(range(G))
+        assert st["depth_natural"] == 2 * G
+        assert st["depth_ordered"] <= st["depth_natural"]
+        if G >= 40:
+            assert st["depth_ordered"] * 4 <= st["depth_natural"]
+            assert st["filled_ordered"] <= 2 * st["filled_natural"]
+    G = 30
+    adj = np.tril(np.ones((G, G), np.uint8))
+    order, st = capi.tile_elimination_order(adj)
+    assert sorted(order.tolist()) == list(range(G))
+    assert st["depth_ordered"] == st["depth_natural"] == 2 * G
+    assert st["filled_ordered"] == st["filled_natural"] == G * (G + 1) // 2
+    # two disconnected halves: independent chains
+    adj = np.zeros((20, 20), np.uint8)
+    for i in range(20):
+        adj[i, i] = 1
+        if i % 10:
+            adj[i, i - 1] = 1
+    order, st = capi.tile_elimination_order(adj)
+    assert sorted(order.tolist()) == list(range(20))
+    assert st["depth_ordered"] <= 20

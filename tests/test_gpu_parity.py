@@ -105,6 +105,26 @@ def test_schur_system_matches_oracle(bab, orc):
     s.close()
 
 
+def test_schur_system_elimination_order(bab, orc):
+    """Many camera groups with banded co-visibility: the device matrix lives in nested-dissection order (blocks of later-
+    eliminated cameras are stored transposed); ba_schur_system must hand back the same S as the oracle."""
+    pb = syn.flatten(syn.make_scene("t", 6, 150, 4000, 4.0, 16, arc_deg=120.0))
+    s = bab.Solver(bab.default_options())
+    s.set_problem(pb)
+    st = s.reduced_system_stats()
+    assert st["filled_tiles"] < st["lower_tiles"]
+    S, rhs, cost = s.schur_system(1e4)
+    So, rhso, costo = orc.schur_system(pb, 1e4, 0, pb.pt.shape[0])
+    L = np.tril(S)
+    Lo = np.tril(So.T)
+    for c in range(pb.cam.shape[0]):
+        if pb.cam_fixed[c]:
+            L[6 * c:6 * c + 6, 6 * c:6 * c + 6] = 0.0
+    assert np.abs(L - Lo).max() <= 1e-10 * np.abs(Lo).max()
+    assert np.abs(rhs - rhso).max() <= 1e-10 * np.abs(rhso).max()
+    s.close()
+
+
 @pytest.mark.parametrize("n", [6, 64, 130, 174, 500, 1194])
 def test_dense_spd_solve(bab, n):
     rng = np.random.default_rng(n)
@@ -114,6 +134,59 @@ def test_dense_spd_solve(bab, n):
     x, ms = bab.capi.dense_spd_solve(A, b)
     ref = np.linalg.solve(A, b)
     assert np.abs(x - ref).max() <= 1e-10 * np.abs(ref).max()
+
+
+def _tile_pattern_matrix(n, pattern, seed):
+    """SPD matrix whose 128x128 tile pattern follows pattern(i, j) (i >= j); diagonally dominant."""
+    rng = np.random.default_rng(seed)
+    T = (n + 127) // 128
+    A = np.zeros((n, n))
+    for i in range(T):
+        for j in range(i + 1):
+            if i == j or pattern(i, j, T):
+                r0, r1, c0, c1 = i * 128, min(n, i * 128 + 128), j * 128, min(n, j * 128 + 128)
+                A[r0:r1, c0:c1] = rng.normal(size=(r1 - r0, c1 - c0))
+    A = np.tril(A)
+    A = A + A.T
+    A += np.diag(np.abs(A).sum(1) + 1.0)
+    return A
+
+
+@pytest.mark.parametrize("name,n,pattern", [
+    ("band1", 1000, lambda i, j, T: i - j <= 1),
+    ("band2", 1300, lambda i, j, T: i - j <= 2),
+    ("arrow", 1100, lambda i, j, T: i == T - 1),                    # dense last block row: no fill
+    ("arrow_first", 900, lambda i, j, T: j == 0),                   # dense first block column: fills everything
+    ("blockdiag", 700, lambda i, j, T: False),
+    ("scattered", 1500, lambda i, j, T: (7 * i + 3 * j) % 5 == 0),
+])
+def test_dense_spd_solve_tile_patterns(bab, name, n, pattern):
+    """The factorisation skips tiles that are structurally zero (tile-level symbolic fill); results must equal a
+    dense solve for any pattern, including ones that fill in."""
+    A = _tile_pattern_matrix(n, pattern, seed=len(name) + n)
+    b = np.random.default_rng(n).normal(size=n)
+    x, ms = bab.capi.dense_spd_solve(A, b)
+    ref = np.linalg.solve(A, b)
+    assert np.abs(x - ref).max() <= 1e-11 * np.abs(ref).max()
+
+
+def test_tile_skipping_changes_nothing(bab, monkeypatch):
+    """Banded co-visibility (K4-shaped, scaled down): the LM trajectory with the tile-sparsity plan is bit-identical to the
+    one with every tile treated as filled."""
+    pb = syn.flatten(syn.make_scene("band", 11, 260, 9000, 4.0, 16))
+    opt = bab.default_options(max_num_iterations=6)
+    runs = []
+    for dense in ("0", "1"):
+        monkeypatch.setenv("BA_B200_DENSE_TILES", dense)
+        s = bab.Solver(opt)
+        s.set_problem(pb)
+        sm = s.solve()
+        st = s.reduced_system_stats()
+        runs.append((np.array([it["cost"] for it in s.iterations()]), s.cameras(), s.points(), st))
+        s.close()
+    assert runs[0][3]["filled_tiles"] < runs[1][3]["filled_tiles"] == runs[1][3]["lower_tiles"]
+    assert np.array_equal(runs[0][0], runs[1][0])
+    assert np.array_equal(runs[0][1], runs[1][1]) and np.array_equal(runs[0][2], runs[1][2])
 
 
 def test_dense_spd_not_positive_definite(bab):

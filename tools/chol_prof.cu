@@ -33,12 +33,21 @@ int main(int argc, char **argv) {
     cudaMalloc(&A, 8 * rows * ld); cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
     cudaMalloc(&g_chol_prof, 8 * 8 * 256);
     if (chol_init()) { printf("chol_init failed\n"); return 1; }
+    // tile plan of the band (exact tile pattern of fill_spd)
+    const int Tp = ld / CHOL_NB;
+    std::vector<unsigned char> nz((size_t)Tp * Tp, 0);
+    for (int i = 0; i < Tp; ++i)
+        for (int j = 0; j <= i; ++j) nz[(size_t)i * Tp + j] = (i * CHOL_NB - (j * CHOL_NB + CHOL_NB - 1)) <= band;
+    CholPlan plan;
+    const CholPlan *plan_ptr = nullptr;
+    if (band < n) { if (chol_plan_create(n, nz.data(), &plan, 0)) { printf("plan failed\n"); return 1; } plan_ptr = &plan;
+        printf("band %d: %lld filled tiles, %d tasks, %.3f GFLOP\n", band, plan.filled_tiles, plan.ntasks, plan.flops * 1e-9); }
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
     for (int r = 0; r < 4; ++r) {
         fill_spd<<<(unsigned)((rows * ld + 255) / 256), 256>>>(A, n, ld, rows, band);
         cudaEventRecord(e0);
-        int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, 0);
+        int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, plan_ptr, 0);
         cudaEventRecord(e1);
         cudaError_t e = cudaDeviceSynchronize();
         if (ce || e) { printf("error %d %s\n", ce, cudaGetErrorString(e)); return 1; }
