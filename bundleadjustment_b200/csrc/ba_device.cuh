@@ -5,6 +5,8 @@
 // semantics.
 #pragma once
 
+#include <cstddef>
+
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <float.h>
@@ -14,17 +16,33 @@ namespace ba {
 
 // ---------------------------------------------------------------------------------------------------------
 // Per-camera table entry, rebuilt once per linearisation point by cam_prep_kernel so that the per-observation
-// kernels never evaluate sincos.  48 doubles = 384 B, 128-bit aligned.
-//   free camera : R (col-major 3x3), dR[3] = dR/dw_k (col-major), t, K (row-major, promoted from f32)
-//   fixed camera: P = 4x4 row-major world->camera extrinsics (promoted from f32) in R[0..8]+dR[0..6], K
+// kernels never evaluate sincos.  52 doubles = 416 B in three 32-byte-aligned groups, so that a thread gathers its camera
+// with 256-bit loads (LDG.E.ENL2.256: one L1 wavefront per 32 B instead of one per double; the landmark-major kernels
+// gather a different camera in every lane, which made the 64-bit version L1-bound).
+//   free camera : R (col-major 3x3) | t,  K (row-major, promoted from f32),  dR[3] = dR/dw_k (col-major)
+//   fixed camera: P = 4x4 row-major world->camera extrinsics (promoted from f32) in dR[0..15], K
 // ---------------------------------------------------------------------------------------------------------
-struct __align__(16) CamEntry {
+struct __align__(32) CamEntry {
     double R[9];
-    double dR[27];
     double t[3];
     double K[9];
+    double pad0[3];
+    double dR[27];
+    double pad1;
 };
-static_assert(sizeof(CamEntry) == 48 * 8, "CamEntry layout");
+static_assert(sizeof(CamEntry) == 52 * 8, "CamEntry layout");
+static_assert(offsetof(CamEntry, K) % 32 == 0 && offsetof(CamEntry, dR) % 32 == 0, "CamEntry groups must be 32-byte aligned");
+
+struct __align__(32) Double4 { double x, y, z, w; };
+// N4 x 256-bit loads of 32-byte-aligned doubles into registers
+template <int N4>
+__device__ __forceinline__ void load_vec4(const double *__restrict__ src, double *dst) {
+#pragma unroll
+    for (int i = 0; i < N4; ++i) {
+        const Double4 v = *reinterpret_cast<const Double4 *>(src + 4 * i);
+        dst[4 * i] = v.x; dst[4 * i + 1] = v.y; dst[4 * i + 2] = v.z; dst[4 * i + 3] = v.w;
+    }
+}
 
 enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
 
@@ -114,17 +132,21 @@ __device__ __forceinline__ void project(const double *__restrict__ K, const doub
 __device__ __forceinline__ void obs_residual(const CamEntry *__restrict__ ce, int kind, const double X[3], float2 uv, double r[2]) {
     double p[3];
     if (kind == CAM_FREE) {
+        double Rt[12];
+        load_vec4<3>(ce->R, Rt);
 #pragma unroll
-        for (int i = 0; i < 3; ++i) p[i] = ce->R[i] * X[0] + ce->R[i + 3] * X[1] + ce->R[i + 6] * X[2] + ce->t[i];
+        for (int i = 0; i < 3; ++i) p[i] = Rt[i] * X[0] + Rt[i + 3] * X[1] + Rt[i + 6] * X[2] + Rt[9 + i];
     } else {
-        const double *P = ce->R; // 16 contiguous doubles (R[9] then dR[0..6])
+        double P[16];
+        load_vec4<4>(ce->dR, P);
         double ph[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
         p[0] = ph[0] / ph[3]; p[1] = ph[1] / ph[3]; p[2] = ph[2] / ph[3];
     }
-    double pix[2];
-    project(ce->K, p, pix, nullptr, false);
+    double pix[2], K[12];
+    load_vec4<3>(ce->K, K);
+    project(K, p, pix, nullptr, false);
     r[0] = pix[0] - (double)uv.x;
     r[1] = pix[1] - (double)uv.y;
 }
@@ -133,22 +155,27 @@ __device__ __forceinline__ void obs_residual(const CamEntry *__restrict__ ce, in
 template <bool WANT_JC, bool WANT_JP>
 __device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, int kind, const double X[3], float2 uv,
                                               double r[2], double Jc[12], double Jp[6]) {
-    double p[3], pix[2], G[6];
+    double p[3], pix[2], G[6], K[12];
+    load_vec4<3>(ce->K, K);
     if (kind == CAM_FREE) {
+        double Rt[12];
+        load_vec4<3>(ce->R, Rt);
 #pragma unroll
-        for (int i = 0; i < 3; ++i) p[i] = ce->R[i] * X[0] + ce->R[i + 3] * X[1] + ce->R[i + 6] * X[2] + ce->t[i];
-        project(ce->K, p, pix, G, true);
+        for (int i = 0; i < 3; ++i) p[i] = Rt[i] * X[0] + Rt[i + 3] * X[1] + Rt[i + 6] * X[2] + Rt[9 + i];
+        project(K, p, pix, G, true);
         if (WANT_JP) {
 #pragma unroll
             for (int rr = 0; rr < 2; ++rr)
 #pragma unroll
                 for (int j = 0; j < 3; ++j)
-                    Jp[rr * 3 + j] = G[rr * 3 + 0] * ce->R[0 + 3 * j] + G[rr * 3 + 1] * ce->R[1 + 3 * j] + G[rr * 3 + 2] * ce->R[2 + 3 * j];
+                    Jp[rr * 3 + j] = G[rr * 3 + 0] * Rt[0 + 3 * j] + G[rr * 3 + 1] * Rt[1 + 3 * j] + G[rr * 3 + 2] * Rt[2 + 3 * j];
         }
         if (WANT_JC) {
+            double dRr[28];
+            load_vec4<7>(ce->dR, dRr);
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
-                const double *D = ce->dR + 9 * j;
+                const double *D = dRr + 9 * j;
                 double d[3];
 #pragma unroll
                 for (int i = 0; i < 3; ++i) d[i] = D[i] * X[0] + D[i + 3] * X[1] + D[i + 6] * X[2];
@@ -159,13 +186,14 @@ __device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, i
             for (int j = 0; j < 3; ++j) { Jc[3 + j] = G[j]; Jc[9 + j] = G[3 + j]; }
         }
     } else {
-        const double *P = ce->R;
+        double P[16];
+        load_vec4<4>(ce->dR, P);
         double ph[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
         const double ih = 1.0 / ph[3];
         p[0] = ph[0] / ph[3]; p[1] = ph[1] / ph[3]; p[2] = ph[2] / ph[3];
-        project(ce->K, p, pix, G, true);
+        project(K, p, pix, G, true);
         if (WANT_JP) {
             double dp[9];
 #pragma unroll

@@ -31,7 +31,7 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
     for (int i = 0; i < 9; ++i) ce->K[i] = (double)K[i];
     if (kind == CAM_FIXED) {
         const float *E = ctx.cam_extr + 16 * (size_t)c;
-        double *P = ce->R;
+        double *P = ce->dR;
 #pragma unroll
         for (int i = 0; i < 16; ++i) P[i] = (double)E[i];
         return;
