@@ -19,7 +19,7 @@ EXPORTS = [
     "ba_set_problem", "ba_set_parameters", "ba_reset_parameters", "ba_solve", "ba_get_cameras", "ba_get_points",
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
     "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
-    "ba_get_reduced_system_stats", "ba_tile_elimination_order",
+    "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
     "ba_pose_to_cam", "ba_cam_to_pose",
 ]
@@ -69,6 +69,7 @@ if not os.path.exists(LIB_PATH):
 lib = C.CDLL(LIB_PATH)
 lib.ba_last_error.restype = C.c_char_p
 lib.ba_tile_elimination_order.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+lib.ba_get_kernel_profile.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_get_reduced_system_stats.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_dense_spd_solve.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
 lib.ba_schur_system.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -156,6 +157,11 @@ class Solver:
 
     def launch_count(self) -> int:
         return int(lib.ba_get_launch_count(self._h))
+
+    def kernel_profile(self) -> dict:
+        out = np.zeros(4)
+        _check(lib.ba_get_kernel_profile(self._h, _ptr(out)), "ba_get_kernel_profile")
+        return {"cholesky_seconds": float(out[0]), "cholesky_launches": int(out[1])}
 
     def reduced_system_stats(self) -> dict:
         """Order of the reduced camera system, filled / total 128x128 tiles of its Cholesky factor, flops per solve."""

@@ -96,7 +96,8 @@ struct ba_handle {
     PrepOut prep_out;
     bool pairs_built = false;
     CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
-    DevBuf tile_map, cam_row, row_src, yperm;
+    DevBuf tile_map, cam_row, row_src, yperm, nz_tiles, s_packed;
+    int n_nz_tiles = 0;
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
@@ -116,6 +117,14 @@ struct ba_handle {
     bool profile = false;            // record CUDA events around every linear solve / linearisation
     std::vector<cudaEvent_t> prof_ev;   // [4 per body]: lin begin, lin end (= solve begin), solve end, body end
     size_t prof_used = 0;
+    std::vector<cudaEvent_t> dom_ev;    // event pairs around the dominant linear-solver kernel (the Cholesky dataflow kernel)
+    size_t dom_used = 0;
+    double dom_seconds = 0.0;
+    int dom_launches = 0;
+    cudaEvent_t dom_event() {
+        if (dom_used == dom_ev.size()) { cudaEvent_t e; cudaEventCreate(&e); dom_ev.push_back(e); }
+        return dom_ev[dom_used++];
+    }
     cudaEvent_t prof_event() {
         if (prof_used == prof_ev.size()) { cudaEvent_t e; cudaEventCreate(&e); prof_ev.push_back(e); }
         return prof_ev[prof_used++];
@@ -127,7 +136,7 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &sums, &maxs,
                          &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &tile_map, &cam_row, &row_src, &yperm};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
         for (DevBuf *b : all) b->free();
         chol_plan_destroy(&chol_plan);
         scr.release(); scr2.release();
@@ -211,6 +220,8 @@ int ba_destroy(ba_handle *h) {
     if (h->host_flags) cudaFreeHost(h->host_flags);
     if (h->h_prep) cudaFreeHost(h->h_prep);
     for (auto &e : h->ev_ring) if (e) cudaEventDestroy(e);
+    for (auto &e : h->prof_ev) cudaEventDestroy(e);
+    for (auto &e : h->dom_ev) cudaEventDestroy(e);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
     if (h->ev_stop) cudaEventDestroy(h->ev_stop);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -311,6 +322,15 @@ int ensure_dense(ba_handle *h) {
         for (int gi = 0; gi < G; ++gi)
             for (int gj = 0; gj <= gi; ++gj)
                 if (gi == gj || adj[(size_t)gi * G + gj]) nz[(size_t)std::max(pos[gi], pos[gj]) * G + std::min(pos[gi], pos[gj])] = 1;
+        if (h->comm) {
+            std::vector<int2> tl;
+            for (int i = 0; i < G; ++i)
+                for (int j = 0; j <= i; ++j) if (nz[(size_t)i * G + j]) tl.push_back(make_int2(i, j));
+            h->n_nz_tiles = (int)tl.size();
+            if ((rc = upload(h->nz_tiles, tl.data(), tl.size(), s))) return rc;
+            CU(h->s_packed.alloc(sizeof(double) * CHOL_NB * CHOL_NB * std::max<size_t>(tl.size(), 1)));
+            CU(cudaStreamSynchronize(s));
+        }
         CU(cudaStreamSynchronize(s));                                    // the uploads read the host vectors above
         // BA_B200_DENSE_TILES=1 (measurement aid): treat every tile as filled
         if ((rc = chol_plan_create(n, env_on("BA_B200_DENSE_TILES") ? nullptr : nz.data(), &h->chol_plan, s)))
@@ -499,6 +519,18 @@ int allreduce_max(ba_handle *h, const double *src, double *dst, size_t count) {
     return BA_OK;
 }
 
+// sum of the ranks' contributions to S: pack the tiles a camera pair can touch, one all-reduce, unpack
+int allreduce_S(ba_handle *h) {
+    if (!h->comm) return BA_OK;
+    Ctx &ctx = h->ctx;
+    launch_tiles_copy(ctx.S, ctx.ldS, h->nz_tiles.as<int2>(), h->n_nz_tiles, h->s_packed.as<double>(), 0, h->stream);
+    int rc = allreduce_sum(h, h->s_packed.as<double>(), (size_t)h->n_nz_tiles * CHOL_NB * CHOL_NB);
+    if (rc) return rc;
+    launch_tiles_copy(ctx.S, ctx.ldS, h->nz_tiles.as<int2>(), h->n_nz_tiles, h->s_packed.as<double>(), 1, h->stream);
+    h->launches += 2;
+    return BA_OK;
+}
+
 // one linearisation at x: local blocks, then the replicated camera blocks are summed over ranks
 int enqueue_linearize(ba_handle *h, int force) {
     const Ctx &ctx = h->ctx;
@@ -527,14 +559,15 @@ int enqueue_linear_solve(ba_handle *h) {
         h->launches += 3;
         // rhs row of the augmented matrix
         if (h->comm) {
-            // lower triangle + rhs would do; the full buffer keeps the collective a single contiguous message
-            if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.ldS * ctx.ldS))) return rc;
+            if ((rc = allreduce_S(h))) return rc;
             if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
         }
         // rhs^T becomes row ldS of the matrix: the forward substitution is then part of the factorisation's dataflow
         launch_chol_rhs(ctx, s);
+        if (h->profile) cudaEventRecord(h->dom_event(), s);
         const int ce = chol_factor_solve(ctx.S, ctx.ldS, h->invL.as<double>(), h->yperm.as<double>(), ctx.state, nullptr, &h->chol_plan, s);
         if (ce) return fail(BA_ERR_CUDA, "chol_factor_solve: %s", cudaGetErrorString((cudaError_t)ce));
+        if (h->profile) cudaEventRecord(h->dom_event(), s);
         launch_chol_unpermute(ctx, h->yperm.as<double>(), s);
         h->launches += 3;
     } else {
@@ -588,6 +621,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
     if (h->opt.linear_solver == BA_DENSE_SCHUR && (rc = ensure_dense(h))) return rc;
     h->launches = 0;
     h->prof_used = 0;
+    h->dom_used = 0; h->dom_seconds = 0.0; h->dom_launches = 0;
     h->host_flags[0] = 0; h->host_flags[1] = 0;
     CU(cudaEventRecord(h->ev_start, s));
     launch_init_state(ctx, s);
@@ -660,6 +694,12 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
             }
             summary->seconds_evaluate = t_lin * 1e-3;
             summary->seconds_linear_solver = t_solve * 1e-3;
+            for (size_t i = 0; i + 1 < h->dom_used; i += 2) {
+                float a = 0;
+                cudaEventElapsedTime(&a, h->dom_ev[i], h->dom_ev[i + 1]);
+                h->dom_seconds += a * 1e-3;
+                h->dom_launches++;
+            }
         }
         std::snprintf(summary->message, sizeof(summary->message), "%s", message_text(st.msg));
     }
@@ -819,7 +859,7 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
     launch_point_invert(ctx, radius, s);
     launch_schur_build(ctx, radius, s);
     if (h->comm) {
-        if ((rc = allreduce_sum(h, ctx.S, (size_t)ctx.ldS * ctx.ldS))) return rc;
+        if ((rc = allreduce_S(h))) return rc;
         if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
     }
     CU(cudaStreamSynchronize(s));
@@ -842,6 +882,14 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
     }
     if (rhs) CU(cudaMemcpy(rhs, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToHost));
     if (cost) CU(cudaMemcpy(cost, ctx.sums + SUM_LIN_COST, 8, cudaMemcpyDeviceToHost));
+    return BA_OK;
+}
+
+// Profiling detail of the last ba_solve (ba_set_profiling on): out = {seconds inside the dense-Cholesky kernel (CUDA events on
+// the solver's stream around each launch, memset of its flags included), number of such launches, 0, 0}.
+extern "C" int ba_get_kernel_profile(ba_handle *h, double out[4]) {
+    if (!h || !out) return fail(BA_ERR_INVALID, "NULL argument");
+    out[0] = h->dom_seconds; out[1] = (double)h->dom_launches; out[2] = 0.0; out[3] = 0.0;
     return BA_OK;
 }
 

@@ -827,6 +827,23 @@ void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) 
     }
 }
 
+// multi-GPU: only the tiles of S that a camera pair can touch travel through the all-reduce (packed contiguously)
+__global__ void __launch_bounds__(256) tiles_copy_kernel(double *__restrict__ S, int ld, const int2 *__restrict__ tiles,
+                                                          double *__restrict__ packed, int unpack) {
+    const int2 t = tiles[blockIdx.x];
+    double *src = S + (size_t)t.x * CHOL_NB * ld + (size_t)t.y * CHOL_NB;
+    double *pk = packed + (size_t)blockIdx.x * CHOL_NB * CHOL_NB;
+    for (int idx = threadIdx.x; idx < CHOL_NB * CHOL_NB / 2; idx += blockDim.x) {
+        const int r = idx / (CHOL_NB / 2), c2 = idx % (CHOL_NB / 2);
+        double2 *a = reinterpret_cast<double2 *>(src + (size_t)r * ld) + c2;
+        double2 *b = reinterpret_cast<double2 *>(pk + (size_t)r * CHOL_NB) + c2;
+        if (unpack) *a = *b; else *b = *a;
+    }
+}
+void launch_tiles_copy(double *S, int ld, const int2 *tiles, int n_tiles, double *packed, int unpack, cudaStream_t s) {
+    if (n_tiles > 0) tiles_copy_kernel<<<n_tiles, 256, 0, s>>>(S, ld, tiles, packed, unpack);
+}
+
 void launch_chol_rhs(const Ctx &ctx, cudaStream_t s) { chol_rhs_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx); }
 void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s) { chol_unpermute_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, y); }
 

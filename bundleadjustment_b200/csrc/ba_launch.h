@@ -18,6 +18,7 @@ void launch_begin_iteration(const Ctx &ctx, cudaStream_t s);
 void launch_decide(const Ctx &ctx, cudaStream_t s);
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
+void launch_tiles_copy(double *S, int ld, const int2 *tiles, int n_tiles, double *packed, int unpack, cudaStream_t s);
 void launch_chol_rhs(const Ctx &ctx, cudaStream_t s);                       // rhs -> row ldS of S, in elimination order
 void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s);  // y (elimination order) -> yc
 void launch_backsub(const Ctx &ctx, cudaStream_t s);
