@@ -292,7 +292,7 @@ int ensure_dense(ba_handle *h) {
         CU(h->unit_seg.alloc(4 * nu)); CU(h->unit_beg.alloc(8 * nu)); CU(h->unit_part.alloc(8 * 42 * nu));
         pi.unit_seg = h->unit_seg.as<int>(); pi.unit_beg = h->unit_beg.as<long long>(); pi.unit_part = h->unit_part.as<double>();
         if ((rc = prep_pairs_units(pi, s))) return fail(BA_ERR_CUDA, "prep_pairs_units: %s", cudaGetErrorString((cudaError_t)rc));
-        h->scr2.release();            // the sort scratch is the largest temporary: give it back
+        // (the sort scratch stays allocated: cudaFree + cudaMalloc of it cost up to 100 ms per ba_set_problem)
         // which camera groups share landmarks (union over ranks) -> elimination order of the tiles (nested dissection),
         // row layout of S, tile-level symbolic factorisation
         CU(h->tile_map.alloc((size_t)G * G));

@@ -111,10 +111,11 @@ struct CholArgs {
     double *y;            // [n]
     LMState *state;       // may be nullptr
     int *fail_flag;       // may be nullptr
+    long long *task_prof; // may be nullptr (tools only): [ntasks][4] ns: picked, operands consumed, factor/diag ready, published; then [T][2] phase 2
     long long *prof;      // may be nullptr; [grid][8] ns: start, phase-1 end, end, waited (ph 1), waited (ph 2), potrf, tasks, trsm
     // tile-sparsity plan (chol_plan_create): only filled tiles are tasks, only filled k-blocks are multiplied
     const int4 *task;     // [ntasks + 1] (i, j, dependency level, first klist entry), sorted by level
-    const int *klist;     // k-blocks of each task's update, ascending
+    const int *klist;     // k-blocks of each task's update, in the order their operands become ready
     const unsigned char *fill;   // [(T + 1)][T] filled tiles of L (row T = rhs)
     int ntasks;
 };
@@ -370,6 +371,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         const int i = tk.x, j = tk.y, kbeg = tk.w;       // klist[kbeg ..): k-blocks with L_ik and L_jk both filled
         const int nkb = __ldg(&p.task[t + 1].w) - tk.w;
         const bool diag = (i == j);
+        if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t] = global_ns();
         double acc[8][4][2];
 #pragma unroll
         for (int a = 0; a < 8; ++a)
@@ -446,6 +448,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         cp_async_wait<0>();
         aborted = __syncthreads_or(aborted);
         if (aborted) break;
+        if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 1] = global_ns();
 
         // C = A_ij - acc  -> shared tile
         {
@@ -471,6 +474,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             const long long tp0 = p.prof ? global_ns() : 0;
             const bool bad = potrf_inverse_tile(tileC, Pv, invd, dinv);
             if (p.prof) t_potrf += global_ns() - tp0;
+            if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
             double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
             double *Ig = p.invL + (size_t)j * NB * NB;
             for (int idx = tid; idx < NB * NB; idx += 256) {
@@ -491,6 +495,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             aborted = __syncthreads_or(aborted);
             if (aborted) break;
             const long long tt0 = p.prof ? global_ns() : 0;
+            if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
             const double *Ig = p.invL + (size_t)j * NB * NB;
 #pragma unroll
             for (int a = 0; a < 8; ++a)
@@ -523,6 +528,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (tid == 0) st_release(p.tiledone + (size_t)i * T + j, 1);
             if (p.prof) t_trsm += global_ns() - tt0;
         }
+        if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 3] = global_ns();
         ++n_tasks;
     }
     const long long t_phase1 = p.prof ? global_ns() : 0, waited1 = waited;
@@ -596,6 +602,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         __threadfence();
         __syncthreads();
         if (tid == 0) st_release(p.ydone + m, 1);
+        if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)p.ntasks + m] = global_ns();
     }
     if (p.prof && tid == 0) {
         long long *o = p.prof + 8 * (size_t)blockIdx.x;
@@ -608,7 +615,8 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 // host side
 // -------------------------------------------------------------------------------------------------------------
 static int g_chol_grid[64];     // per device: co-resident CTAs (0 = not initialised)
-long long *g_chol_prof = nullptr;   // tools/chol_prof.cu only: device buffer [grid][8] of per-CTA timings
+long long *g_chol_prof = nullptr;
+long long *g_chol_task_prof = nullptr;   // tools/chol_prof.cu only: [ntasks][4] + [T]   // tools/chol_prof.cu only: device buffer [grid][8] of per-CTA timings
 
 int chol_init() {
     int dev = 0;
@@ -762,6 +770,11 @@ void plan_analyse(int n, const unsigned char *nz, HostPlan &hp) {
                 }
             if (i != j) lv = std::max(lv, 1 + level[(size_t)j * T + j]);
             level[(size_t)i * T + j] = lv;
+            // consume the k-blocks in the order their operands become available (dependency level, then k): a separator
+            // tile with many contributions then only waits for the last ones.  Fixed per plan, so sums stay reproducible.
+            std::stable_sort(kl_tmp.begin() + kbeg, kl_tmp.end(), [&](int a, int b) {
+                return std::max(level[(size_t)i * T + a], level[(size_t)j * T + a]) < std::max(level[(size_t)i * T + b], level[(size_t)j * T + b]);
+            });
             const double nkb = (double)((int)kl_tmp.size() - kbeg);
             if (i == T) flops += 2.0 * NB * NB * nkb + (double)NB * NB;             // one rhs row block
             else if (i == j) { flops += t3 * nkb + t3 / 3.0; ++filled; }
@@ -854,7 +867,7 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
     p.ypad = work + (size_t)T * NB * NB;
     int *flags = reinterpret_cast<int *>(p.ypad + (size_t)T * NB);
     p.tiledone = flags; p.ydone = flags + (size_t)(T + 1) * T; p.abort_flag = p.ydone + T;
-    p.y = y; p.state = state; p.fail_flag = fail_flag; p.prof = g_chol_prof;
+    p.y = y; p.state = state; p.fail_flag = fail_flag; p.prof = g_chol_prof; p.task_prof = g_chol_task_prof;
     p.task = plan->task; p.klist = plan->klist; p.fill = plan->fill; p.ntasks = plan->ntasks;
     cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)chol_flag_count(T), s);
     if (e != cudaSuccess) return (int)e;

@@ -373,7 +373,7 @@ __global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
 // Traffic per entry: 2 x 144 B of W + 48 B V'^-1 (+ 24 B on diagonal blocks); consecutive segments share cameras, so all
 // but the first touch of a W block come from L2.
 constexpr int SCHUR_WARPS = 4;
-__global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, int force) {
+__global__ void __launch_bounds__(SCHUR_WARPS * 32, 3) schur_units_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && st->done) return;
     __shared__ double sred[SCHUR_WARPS][42][33];
@@ -392,9 +392,16 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
     for (int k = 0; k < 36; ++k) acc[k] = 0.0;
 #pragma unroll
     for (int k = 0; k < 6; ++k) racc[k] = 0.0;
-    for (long long e = beg + lane; e < end; e += 32) {
-        const int2 ob = pi.pair_obs[e];
-        const int p = ctx.pm_pt[ob.x];
+    // software pipeline: the next entry's (obs a, obs b) and landmark index are fetched while the current one is processed,
+    // so an iteration costs one dependent gather (W, V'^-1) instead of three
+    long long e = beg + lane;
+    int2 ob_n = make_int2(0, 0);
+    int p_n = 0;
+    if (e < end) { ob_n = pi.pair_obs[e]; p_n = ctx.pm_pt[ob_n.x]; }
+    for (; e < end; e += 32) {
+        const int2 ob = ob_n;
+        const int p = p_n;
+        if (e + 32 < end) { ob_n = pi.pair_obs[e + 32]; p_n = ctx.pm_pt[ob_n.x]; }
         const double2 *Vi2 = reinterpret_cast<const double2 *>(ctx.Vinv + 6 * (size_t)p);
         const double2 v01 = Vi2[0], v23 = Vi2[1], v45 = Vi2[2];
         const double vi[6] = {v01.x, v01.y, v23.x, v23.y, v45.x, v45.y};
