@@ -96,6 +96,7 @@ struct ba_handle {
     PrepOut prep_out;
     bool pairs_built = false;
     CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
+    bool S_dirty = true;             // S may hold values outside the plan's tiles (new buffer / new plan): clear all of it once
     DevBuf tile_map, cam_row, row_src, yperm, nz_tiles, s_packed;
     int n_nz_tiles = 0;
     int *h_prep = nullptr;           // pinned [8]
@@ -335,6 +336,7 @@ int ensure_dense(ba_handle *h) {
         // BA_B200_DENSE_TILES=1 (measurement aid): treat every tile as filled
         if ((rc = chol_plan_create(n, env_on("BA_B200_DENSE_TILES") ? nullptr : nz.data(), &h->chol_plan, s)))
             return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
+        h->S_dirty = true;
         h->pairs_built = true;
     }
     return BA_OK;
@@ -555,8 +557,10 @@ int enqueue_linear_solve(ba_handle *h) {
     launch_point_invert(ctx, -1.0, s);
     h->launches += 1;
     if (h->opt.linear_solver == BA_DENSE_SCHUR) {
+        if ((rc = chol_clear(ctx.S, &h->chol_plan, h->S_dirty, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
+        h->S_dirty = false;
         launch_schur_build(ctx, -1.0, s);
-        h->launches += 3;
+        h->launches += 4;
         // rhs row of the augmented matrix
         if (h->comm) {
             if ((rc = allreduce_S(h))) return rc;
@@ -857,6 +861,8 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
         if ((rc = enqueue_linearize(h, 1))) return rc;
     }
     launch_point_invert(ctx, radius, s);
+    if ((rc = chol_clear(ctx.S, &h->chol_plan, true, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
+    h->S_dirty = false;
     launch_schur_build(ctx, radius, s);
     if (h->comm) {
         if ((rc = allreduce_S(h))) return rc;

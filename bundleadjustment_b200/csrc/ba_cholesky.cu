@@ -841,6 +841,27 @@ int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t 
     return 0;
 }
 
+// zero the tiles the factorisation will touch (S tiles + fill-in); everything else is zero already and stays zero
+__global__ void __launch_bounds__(256) chol_clear_kernel(double *__restrict__ A, int ld, int T, const unsigned char *__restrict__ fill) {
+    int i = (int)((sqrtf(8.0f * blockIdx.x + 1.0f) - 1.0f) * 0.5f);          // blockIdx = i (i + 1) / 2 + j, j <= i
+    while ((i + 1) * (i + 2) / 2 <= (int)blockIdx.x) ++i;
+    while (i * (i + 1) / 2 > (int)blockIdx.x) --i;
+    const int j = blockIdx.x - i * (i + 1) / 2;
+    if (!fill[(size_t)i * T + j]) return;
+    double *dst = A + (size_t)i * NB * ld + (size_t)j * NB;
+    for (int idx = threadIdx.x; idx < NB * NB / 2; idx += blockDim.x) {
+        const int r = idx / (NB / 2), c2 = idx % (NB / 2);
+        reinterpret_cast<double2 *>(dst + (size_t)r * ld)[c2] = make_double2(0.0, 0.0);
+    }
+}
+
+int chol_clear(double *A, const CholPlan *plan, bool everything, cudaStream_t s) {
+    if (everything) return (int)cudaMemsetAsync(A, 0, sizeof(double) * chol_matrix_doubles(plan->n), s);
+    const int T = plan->T;
+    chol_clear_kernel<<<T * (T + 1) / 2, 256, 0, s>>>(A, chol_ld(plan->n), T, plan->fill);
+    return (int)cudaGetLastError();
+}
+
 void chol_plan_destroy(CholPlan *pl) {
     if (pl->blob) cudaFree(pl->blob);
     *pl = CholPlan();

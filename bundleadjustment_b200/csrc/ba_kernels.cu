@@ -826,7 +826,6 @@ void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s)
 
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) {
     const int force = radius_override > 0;
-    cudaMemsetAsync(ctx.S, 0, sizeof(double) * chol_matrix_doubles(ctx.ldS), s);
     schur_init_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, radius_override);
     if (ctx.pairs.n_units > 0) {
         schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, 0, s>>>(ctx, force);

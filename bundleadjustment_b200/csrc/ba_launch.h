@@ -88,6 +88,8 @@ struct CholPlan {
 void chol_tile_order(int G, const unsigned char *adj, std::vector<int> &order);
 int chol_plan_create(int n, const unsigned char *nz, CholPlan *plan, cudaStream_t s);
 void chol_plan_destroy(CholPlan *plan);
+// zero A before S is assembled: the whole buffer, or only the tiles of the plan (the rest must already be zero)
+int chol_clear(double *A, const CholPlan *plan, bool everything, cudaStream_t s);
 void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *filled, double *flops);   // host only
 int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
 
