@@ -333,7 +333,7 @@ __device__ __forceinline__ void load_slice(double *__restrict__ dst, const doubl
     }
 }
 
-// acc += A_s (128 x 16, stride lda_s) * B_s^T (128 x 16, stride SPAD): warp (wm, wn) owns a 64 x 32 sub-tile
+// acc += A_s (128 x BK, stride lda_s) * B_s^T (128 x BK, stride SPAD): warp (wm, wn) owns a 64 x 32 sub-tile
 __device__ __forceinline__ void mma_slice(double (&acc)[8][4][2], const double *__restrict__ a_s, int lda_s,
                                           const double *__restrict__ b_s) {
 #pragma unroll
@@ -357,7 +357,9 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     double *scratch = smem + TILE_DOUBLES;                 // epilogue ring (2 stages of B) / potrf scratch
     double *Pv = scratch, *invd = scratch + NB * LDP, *dinv = invd + PB * LDP;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp >> 2, wn = warp & 3;               // 2 x 4 warps -> 64 x 32 per warp
+    // 2 x 4 warps -> 64 x 32 per warp.  Warps w and w + 4 share an SM sub-partition (and its DMMA pipe): the column blocks are
+    // mirrored in the lower warp row so that triangular work (TRSM against the lower-triangular L_jj^-1) is balanced.
+    const int wm = warp >> 2, wn = wm ? 3 - (warp & 3) : (warp & 3);
     const int g = lane >> 2, tig = lane & 3;
     const int T = p.T, ld = p.ld;
     __shared__ int s_have;
@@ -475,11 +477,11 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             const bool bad = potrf_inverse_tile(tileC, Pv, invd, dinv);
             if (p.prof) t_potrf += global_ns() - tp0;
             if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
-            double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
+            // L_jj^-1 first: it is all the TRSMs (and the back substitution) wait for; L_jj itself is only stored for the
+            // caller and leaves after the flag is up
             double *Ig = p.invL + (size_t)j * NB * NB;
             for (int idx = tid; idx < NB * NB; idx += 256) {
                 const int r = idx >> 7, c = idx & (NB - 1);
-                if (c <= r) Lg[(size_t)r * ld + c] = tileC[(size_t)r * LDT + c];
                 Ig[idx] = (c < r) ? tileC[(size_t)c * LDT + r] : (c == r ? dinv[r] : 0.0);
             }
             if (bad && tid == 0) {
@@ -489,6 +491,12 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             __threadfence();
             __syncthreads();
             if (tid == 0) st_release(p.tiledone + (size_t)j * T + j, 1);
+            double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
+            for (int idx = tid; idx < NB * NB; idx += 256) {
+                const int r = idx >> 7, c = idx & (NB - 1);
+                if (c <= r) Lg[(size_t)r * ld + c] = tileC[(size_t)r * LDT + c];
+            }
+            __syncthreads();                               // tileC is reused by the next task
         } else {
             // L_ij = C * L_jj^-T : A operand = the staged tile, B operand = invL_j through a 2-stage ring
             if (tid == 0 && !wait_ge(p.tiledone + (size_t)j * T + j, 1, p.abort_flag, waited)) aborted = true;
@@ -510,7 +518,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
                 __syncthreads();
                 const double *a_s = tileC + (size_t)(wm * 64 + g) * LDT + kt * BK + tig;
                 const double *b_s = scratch + (size_t)(kt & 1) * NB * SPAD + (size_t)(wn * 32 + g) * SPAD + tig;
-                mma_slice(acc, a_s, LDT, b_s);
+                if (kt <= wn) mma_slice(acc, a_s, LDT, b_s);   // L_jj^-1 is lower triangular: k-slices right of this warp's columns are zero
                 __syncthreads();
             }
             double *Cg = p.A + (size_t)(i * NB) * ld + (size_t)j * NB;
