@@ -422,8 +422,8 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(tab_x, sizeof(CamEntry) * (size_t)Nc); AL(tab_c, sizeof(CamEntry) * (size_t)Nc);
     AL(scale_cam, 8 * 6 * (size_t)Nc); AL(scale_pt, 8 * 3 * (size_t)Np);
     AL(U, 8 * 36 * (size_t)Nc); AL(bc, 8 * 6 * (size_t)Nc); AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
-    AL(W, 8 * 18 * (size_t)No); AL(cam_part, 8 * 27 * (size_t)std::max(ctx.n_chunks, 1));
-    AL(Vinv, 8 * 6 * (size_t)Np); AL(wv, 8 * 3 * (size_t)Np);
+    AL(W, 8 * 18 * (size_t)No + 64);     /* + slack: rows are fetched as aligned 32-byte windows (load_row18) */ AL(cam_part, 8 * 27 * (size_t)std::max(ctx.n_chunks, 1));
+    AL(Vinv, 8 * 6 * (size_t)Np + 64); AL(wv, 8 * 3 * (size_t)Np);
     AL(rhs, 8 * (size_t)ctx.n); AL(yc, 8 * (size_t)ctx.n);
     AL(part, 8 * 4 * (size_t)ctx.n_part); AL(cost_part, 8 * (size_t)((No + 127) / 128 + 1));
     AL(sums, 8 * SUM_COUNT); AL(maxs, 8 * MAX_COUNT); AL(camsums, 8 * CS_COUNT);

@@ -44,6 +44,25 @@ __device__ __forceinline__ void load_vec4(const double *__restrict__ src, double
     }
 }
 
+// Row `row` of a [.][18]-double array (W: 144-byte rows, so odd rows start 16 bytes off a 32-byte boundary) as five 256-bit
+// loads of the enclosing 32-byte-aligned window + a parity select.  A per-lane gather costs one L1 sector request per load
+// instruction and lane, whatever the width: 5 requests instead of 9 (128-bit) or 18 (64-bit).  The array needs 16 bytes of
+// slack behind its last row.  load_row6: the same for [.][6] arrays (48-byte rows, two loads).
+__device__ __forceinline__ void load_row18(const double *__restrict__ base, size_t row, double (&w)[18]) {
+    const bool odd = row & 1;
+    double raw[20];
+    load_vec4<5>(base + 18 * row - (odd ? 2 : 0), raw);
+#pragma unroll
+    for (int k = 0; k < 18; ++k) w[k] = odd ? raw[k + 2] : raw[k];
+}
+__device__ __forceinline__ void load_row6(const double *__restrict__ base, size_t row, double (&v)[6]) {
+    const bool odd = row & 1;
+    double raw[8];
+    load_vec4<2>(base + 6 * row - (odd ? 2 : 0), raw);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) v[k] = odd ? raw[k + 2] : raw[k];
+}
+
 enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
 
 // ceres::AngleAxisToRotationMatrix + closed-form derivative of the branch taken (autodiff-equivalent)

@@ -373,11 +373,25 @@ __global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
 // Traffic per entry: 2 x 144 B of W + 48 B V'^-1 (+ 24 B on diagonal blocks); consecutive segments share cameras, so all
 // but the first touch of a W block come from L2.
 constexpr int SCHUR_WARPS = 4;
-__global__ void __launch_bounds__(SCHUR_WARPS * 32, 3) schur_units_kernel(Ctx ctx, int force) {
+constexpr int SCHUR_K = 96;                  // stacked reduction index of one batch: 32 entries x 3 landmark coordinates
+constexpr int SCHUR_LD = SCHUR_K + 4;        // row stride 100 doubles: 100 mod 16 == 4 -> conflict-free DMMA fragment loads
+__device__ __forceinline__ void dmma884_acc(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+// The block of one camera pair is  sum_e Y_e W_b,e^T  with Y_e = W_a,e V'^-1 (6 x 3): stacked over the entries this is ONE
+// small GEMM  [Y_1 .. Y_E] (6 x 3E) * [W_b,1 .. W_b,E]^T (3E x 6), so the reduction over entries runs on the FP64 tensor
+// pipe (DMMA m8n8k4, 6 of 8 rows/columns used; column 6 carries the stacked b_p, which makes rhs_c -= W V'^-1 b_p fall out
+// of the same product).  Per batch of 32 entries each lane gathers its entry's rows, forms Y in registers and parks Y and
+// W_b k-major in shared memory; the warp then issues <= 24 DMMAs.  Two accumulator registers per lane instead of 42.
+__global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && st->done) return;
-    __shared__ double sred[SCHUR_WARPS][42][33];
+    __shared__ __align__(16) double sY[SCHUR_WARPS][6 * SCHUR_LD];      // [a][k]: Y_e[a][q] at k = 3 e + q
+    __shared__ __align__(16) double sB[SCHUR_WARPS][7 * SCHUR_LD];      // [b][k]: W_b,e[b][q]; row 6: b_p of self entries
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, tig = lane & 3;
     const int u = blockIdx.x * SCHUR_WARPS + warp;
     const PairIndex &pi = ctx.pairs;
     if (u >= pi.n_units) return;
@@ -387,65 +401,67 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32, 3) schur_units_kernel(Ctx ct
     const long long end = (beg + PAIR_UNIT < seg_end) ? beg + PAIR_UNIT : seg_end;
     const int2 cams = pi.seg_cams[seg];
     const bool diag = cams.x == cams.y;
-    double acc[36], racc[6];
-#pragma unroll
-    for (int k = 0; k < 36; ++k) acc[k] = 0.0;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) racc[k] = 0.0;
-    // software pipeline: the next entry's (obs a, obs b) and landmark index are fetched while the current one is processed,
-    // so an iteration costs one dependent gather (W, V'^-1) instead of three
+    double *Ys = sY[warp], *Bs = sB[warp];
+    double c0 = 0.0, c1 = 0.0;                                          // C[g][2 tig], C[g][2 tig + 1] of the 8 x 8 product
     long long e = beg + lane;
     int2 ob_n = make_int2(0, 0);
     int p_n = 0;
     if (e < end) { ob_n = pi.pair_obs[e]; p_n = ctx.pm_pt[ob_n.x]; }
-    for (; e < end; e += 32) {
-        const int2 ob = ob_n;
-        const int p = p_n;
+    for (long long base = beg; base < end; base += 32, e += 32) {
+        const bool live = e < end;
+        const int2 ob = live ? ob_n : make_int2(0, 0);                  // dead lanes read row 0 (finite data) and contribute Y = 0
+        const int p = live ? p_n : 0;
         if (e + 32 < end) { ob_n = pi.pair_obs[e + 32]; p_n = ctx.pm_pt[ob_n.x]; }
-        const double2 *Vi2 = reinterpret_cast<const double2 *>(ctx.Vinv + 6 * (size_t)p);
-        const double2 v01 = Vi2[0], v23 = Vi2[1], v45 = Vi2[2];
-        const double vi[6] = {v01.x, v01.y, v23.x, v23.y, v45.x, v45.y};
-        const double2 *Wa = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)ob.x);
-        double Y[18];
+        // gathers as aligned 256-bit windows (12 sector requests per entry instead of 21); W_b is W_a on self entries
+        double vi[6], wa[18], wb[18];
+        load_row6(ctx.Vinv, (size_t)p, vi);
+        load_row18(ctx.W, (size_t)ob.x, wa);
+        if (ob.x != ob.y) load_row18(ctx.W, (size_t)ob.y, wb);
+        else {
 #pragma unroll
-        for (int h = 0; h < 3; ++h) {                 // rows 2h, 2h+1 of W_a: 6 doubles = 3 x 16 B
-            const double2 w0 = Wa[3 * h], w1 = Wa[3 * h + 1], w2 = Wa[3 * h + 2];
-            const double r0[3] = {w0.x, w0.y, w1.x}, r1[3] = {w1.y, w2.x, w2.y};
-            Y[6 * h + 0] = r0[0] * vi[0] + r0[1] * vi[1] + r0[2] * vi[2];
-            Y[6 * h + 1] = r0[0] * vi[1] + r0[1] * vi[3] + r0[2] * vi[4];
-            Y[6 * h + 2] = r0[0] * vi[2] + r0[1] * vi[4] + r0[2] * vi[5];
-            Y[6 * h + 3] = r1[0] * vi[0] + r1[1] * vi[1] + r1[2] * vi[2];
-            Y[6 * h + 4] = r1[0] * vi[1] + r1[1] * vi[3] + r1[2] * vi[4];
-            Y[6 * h + 5] = r1[0] * vi[2] + r1[1] * vi[4] + r1[2] * vi[5];
+            for (int k = 0; k < 18; ++k) wb[k] = wa[k];
         }
-        if (diag && ob.x == ob.y) {                   // the observation itself: its share of rhs_c -= W V'^-1 b_p
+        double b3[3] = {0.0, 0.0, 0.0};
+        if (diag && live && ob.x == ob.y) {                             // the observation itself: its share of the rhs
             const double *bp = ctx.bp + 3 * (size_t)p;
-            const double b0 = bp[0], b1 = bp[1], b2 = bp[2];
-#pragma unroll
-            for (int a = 0; a < 6; ++a) racc[a] += Y[a * 3] * b0 + Y[a * 3 + 1] * b1 + Y[a * 3 + 2] * b2;
+            b3[0] = bp[0]; b3[1] = bp[1]; b3[2] = bp[2];
         }
-        const double2 *Wb = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)ob.y);
+        __syncwarp();                                                   // previous batch's DMMAs have consumed the buffers
+        const double lv = live ? 1.0 : 0.0;
 #pragma unroll
-        for (int h = 0; h < 3; ++h) {                 // columns 2h, 2h+1 of the block = rows 2h, 2h+1 of W_b
-            const double2 w0 = Wb[3 * h], w1 = Wb[3 * h + 1], w2 = Wb[3 * h + 2];
-#pragma unroll
-            for (int a = 0; a < 6; ++a) {
-                acc[a * 6 + 2 * h] += Y[a * 3] * w0.x + Y[a * 3 + 1] * w0.y + Y[a * 3 + 2] * w1.x;
-                acc[a * 6 + 2 * h + 1] += Y[a * 3] * w1.y + Y[a * 3 + 1] * w2.x + Y[a * 3 + 2] * w2.y;
-            }
+        for (int h = 0; h < 3; ++h) {                                   // rows 2h, 2h+1 of W_a
+            const double r0[3] = {wa[6 * h] * lv, wa[6 * h + 1] * lv, wa[6 * h + 2] * lv};
+            const double r1[3] = {wa[6 * h + 3] * lv, wa[6 * h + 4] * lv, wa[6 * h + 5] * lv};
+            double *y0 = Ys + (2 * h) * SCHUR_LD + 3 * lane, *y1 = y0 + SCHUR_LD;
+            y0[0] = r0[0] * vi[0] + r0[1] * vi[1] + r0[2] * vi[2];
+            y0[1] = r0[0] * vi[1] + r0[1] * vi[3] + r0[2] * vi[4];
+            y0[2] = r0[0] * vi[2] + r0[1] * vi[4] + r0[2] * vi[5];
+            y1[0] = r1[0] * vi[0] + r1[1] * vi[1] + r1[2] * vi[2];
+            y1[1] = r1[0] * vi[1] + r1[1] * vi[3] + r1[2] * vi[4];
+            y1[2] = r1[0] * vi[2] + r1[1] * vi[4] + r1[2] * vi[5];
+            double *w0 = Bs + (2 * h) * SCHUR_LD + 3 * lane, *w1 = w0 + SCHUR_LD;
+            w0[0] = wb[6 * h]; w0[1] = wb[6 * h + 1]; w0[2] = wb[6 * h + 2];
+            w1[0] = wb[6 * h + 3]; w1[1] = wb[6 * h + 4]; w1[2] = wb[6 * h + 5];
+        }
+        if (diag) {
+            double *w6 = Bs + 6 * SCHUR_LD + 3 * lane;
+            w6[0] = b3[0]; w6[1] = b3[1]; w6[2] = b3[2];
+        }
+        __syncwarp();
+        const long long left = end - base;
+        const int ksteps = left >= 32 ? SCHUR_K / 4 : (int)((3 * left + 3) / 4);
+        const bool arow = g < 6, brow = g < 6 || (diag && g == 6);
+        for (int s4 = 0; s4 < ksteps; ++s4) {
+            const double av = arow ? Ys[g * SCHUR_LD + 4 * s4 + tig] : 0.0;
+            const double bv = brow ? Bs[g * SCHUR_LD + 4 * s4 + tig] : 0.0;
+            dmma884_acc(c0, c1, av, bv);
         }
     }
-#pragma unroll
-    for (int k = 0; k < 36; ++k) sred[warp][k][lane] = acc[k];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) sred[warp][36 + k][lane] = racc[k];
-    __syncwarp();
     double *dst = pi.unit_part + 42 * (size_t)u;
-    for (int k = lane; k < 42; k += 32) {
-        double t = 0.0;
-#pragma unroll
-        for (int l = 0; l < 32; ++l) t += sred[warp][k][l];
-        dst[k] = t;
+    if (g < 6) {
+        const int c = 2 * tig;
+        if (c < 6) { dst[g * 6 + c] = c0; dst[g * 6 + c + 1] = c1; }
+        else dst[36 + g] = c0;                                          // column 6: the rhs share (zero on off-diagonal blocks)
     }
 }
 
