@@ -214,32 +214,26 @@ __global__ void __launch_bounds__(128) linearize_cams_kernel(Ctx ctx, int force)
     }
 }
 
-// per camera: ordered sum of its chunk partials -> U (full 6x6 row-major), b_c
+// per camera: ordered sum of its chunk partials -> U (full 6x6 row-major), b_c.  One warp per camera, lane k owns entry k
+// of the 27 (21 upper-triangle entries of U + 6 of b_c): coalesced reads, the same chunk order as a serial walk.
 __global__ void cam_reduce_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ctx.Nc) return;
-    double acc[27];
-#pragma unroll
-    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
-    for (int w = ctx.cam_chunk_ptr[c]; w < ctx.cam_chunk_ptr[c + 1]; ++w) {
-        const double *src = ctx.cam_part + 27 * (size_t)w;
-#pragma unroll
-        for (int k = 0; k < 27; ++k) acc[k] += src[k];
-    }
-    double *U = ctx.U_loc + 36 * (size_t)c;
-    int k = 0;
-#pragma unroll
-    for (int a = 0; a < 6; ++a)
-#pragma unroll
-        for (int b = a; b < 6; ++b) { U[a * 6 + b] = acc[k]; U[b * 6 + a] = acc[k]; ++k; }
-#pragma unroll
-    for (int a = 0; a < 6; ++a) ctx.bc_loc[6 * (size_t)c + a] = acc[21 + a];
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, k = threadIdx.x & 31;
+    if (c >= ctx.Nc || k >= 27) return;
+    double acc = 0.0;
+    for (int w = ctx.cam_chunk_ptr[c]; w < ctx.cam_chunk_ptr[c + 1]; ++w) acc += ctx.cam_part[27 * (size_t)w + k];
+    if (k < 21) {
+        int a = 0, rem = k;                                   // k-th entry of the row-major upper triangle
+        while (rem >= 6 - a) { rem -= 6 - a; ++a; }
+        const int b = a + rem;
+        double *U = ctx.U_loc + 36 * (size_t)c;
+        U[a * 6 + b] = acc; U[b * 6 + a] = acc;
+    } else ctx.bc_loc[6 * (size_t)c + (k - 21)] = acc;
 }
 
 // landmark-side partials -> sums / maxs (single block, fixed order)
-__global__ void reduce_lin_partials_kernel(Ctx ctx, int force) {
+__global__ void __launch_bounds__(1024) reduce_lin_partials_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
     __shared__ double red[32];
@@ -256,7 +250,7 @@ __global__ void reduce_lin_partials_kernel(Ctx ctx, int force) {
 }
 
 // camera-side gradient / parameter norms from the (all-reduced) b_c; single block
-__global__ void cam_norms_kernel(Ctx ctx, int force) {
+__global__ void __launch_bounds__(1024) cam_norms_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
     __shared__ double red[32];
@@ -549,7 +543,7 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
 }
 
 // cameras: candidate = x + (-y_c) * scale, camera-side model-cost pieces, candidate R table.  Single block.
-__global__ void cam_update_kernel(Ctx ctx) {
+__global__ void __launch_bounds__(512) cam_update_kernel(Ctx ctx) {
     const LMState *st = ctx.state;
     if (st->done) return;
     __shared__ double red[32];
@@ -619,7 +613,7 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
 }
 
 // step partials -> sums (single block)
-__global__ void reduce_step_partials_kernel(Ctx ctx, const double *cost_part, int n_cost_part) {
+__global__ void __launch_bounds__(1024) reduce_step_partials_kernel(Ctx ctx, const double *cost_part, int n_cost_part) {
     const LMState *st = ctx.state;
     if (st->done) return;
     __shared__ double red[32];
@@ -823,10 +817,10 @@ void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
     linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
     if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx, force);
-    cam_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx, force);
-    reduce_lin_partials_kernel<<<1, 256, 0, s>>>(ctx, force);
+    cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
+    reduce_lin_partials_kernel<<<1, 1024, 0, s>>>(ctx, force);
 }
-void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s) { cam_norms_kernel<<<1, 256, 0, s>>>(ctx, force); }
+void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s) { cam_norms_kernel<<<1, 1024, 0, s>>>(ctx, force); }
 
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s) {
     const int n = max(6 * ctx.Nc, 3 * ctx.Np);
@@ -871,13 +865,13 @@ void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s) { ch
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {
     backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);
-    cam_update_kernel<<<1, 256, 0, s>>>(ctx);
+    cam_update_kernel<<<1, 512, 0, s>>>(ctx);
 }
 
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s) {
     const int nb = cdiv(ctx.No, 256);
     eval_candidate_kernel<<<nb, 256, 0, s>>>(ctx, cost_part);
-    reduce_step_partials_kernel<<<1, 256, 0, s>>>(ctx, cost_part, nb);
+    reduce_step_partials_kernel<<<1, 1024, 0, s>>>(ctx, cost_part, nb);
 }
 
 void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s) {
