@@ -337,9 +337,10 @@ def main_ours(args):
                                                 "frac": fl / (ms * 1e-3) / 1e12 / fp64_peak, "traffic": None, "peak_source": peak_src,
                                                 "flops_per_launch": fl, "launch_ms": ms}
     else:
-        per_cg = 2 * 144.0 * pb.shape[2] + 48.0 * pb.shape[1] + 10 * 8.0 * 6 * Nc
+        # one pass over W per CG iteration (144 B/obs) + V'^-1 (48 B/landmark) + the camera-side vectors
+        per_cg = 144.0 * pb.shape[2] + 48.0 * pb.shape[1] + 10 * 8.0 * 6 * Nc
         ach = cg_its * per_cg / t_lin / 1e9 if t_lin > 0 else 0.0
-        roofline = {"bound": "hbm", "kernel": "pcg_matvec_points_kernel (2 passes over W per CG iteration)", "achieved": ach,
+        roofline = {"bound": "hbm", "kernel": "pcg_matvec_points_kernel (one pass over W per CG iteration; achieved = bytes x CG iterations / linear-solve stage time, which also holds the preconditioner setup)", "achieved": ach,
                     "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None, "peak_source": hbm_src,
                     "bytes_per_launch": per_cg, "share_of_step": t_lin / t_dev}
     cpu = cpu_baseline(pb_full, args.workload, args.solver) if (world == 1 and not args.no_cpu) else None

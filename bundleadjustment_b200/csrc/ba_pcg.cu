@@ -6,6 +6,10 @@
 // every 10 iterations, optional relative-residual stop.
 #include "ba_launch.h"
 
+#include <cooperative_groups.h>
+
+#include <algorithm>
+
 namespace ba {
 
 __device__ __forceinline__ double lm_diag_pcg(const Ctx &ctx, double jtj, double radius) {
@@ -99,54 +103,78 @@ __global__ void pcg_setup_reduce_kernel(Ctx ctx) {
     for (int a = 0; a < 6; ++a) ctx.rhs[6 * (size_t)c + a] = (lead ? ctx.bc[6 * (size_t)c + a] : 0.0) - acc[21 + a];
 }
 
-// invert the 6x6 diagonal blocks in place; start CG: x = 0, r = b
-__global__ void pcg_start_kernel(Ctx ctx) {
+// The camera-side vector kernels of one CG iteration are COOPERATIVE launches (one CTA per SM at most): a dot product is
+// reduced per CTA, published, and after grid.sync() EVERY CTA sums the published partials in the same fixed order, so all
+// of them hold the identical scalar and go on to the dependent vector update -- one launch instead of a single-CTA kernel
+// (which left 147 SMs idle for ~120 us per call, the dominant replicated cost on 8 GPUs).
+constexpr int CG_THREADS = 256;
+constexpr int CG_MAX_GRID = 1024;              // partial slots (grid is capped by co-residency, far below this)
+
+// identical in every CTA: fixed-order sum of the per-CTA partials
+__device__ __forceinline__ double grid_total(const double *part, int nblocks, double *red) {
+    double v = 0.0;
+    for (int i = threadIdx.x; i < nblocks; i += blockDim.x) v += part[i];
+    v = block_sum(v, red);
+    __shared__ double s_total;
+    __syncthreads();
+    if (threadIdx.x == 0) s_total = v;
+    __syncthreads();
+    return s_total;
+}
+
+// invert the 6x6 diagonal blocks in place (one thread per camera)
+__global__ void __launch_bounds__(128) pcg_invert_blocks_kernel(Ctx ctx) {
+    LMState *st = ctx.state;
+    if (st->done) return;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ctx.Nc) return;
+    double *M = ctx.Minv + 36 * (size_t)c;
+    double A[36], inv[36];
+#pragma unroll
+    for (int k = 0; k < 36; ++k) A[k] = M[k];
+    if (!inv_spd6(A, inv)) {
+        atomicExch(&st->cg_bad_block, 1);
+#pragma unroll
+        for (int k = 0; k < 36; ++k) inv[k] = 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < 36; ++k) M[k] = inv[k];
+}
+
+// start CG: x = 0, r = b, |b|
+__global__ void __launch_bounds__(1024) pcg_start_kernel(Ctx ctx) {
     LMState *st = ctx.state;
     if (st->done) return;
     __shared__ double red[32];
     double nb = 0.0;
-    int bad = 0;
-    for (int c = threadIdx.x; c < ctx.Nc; c += blockDim.x) {
-        double *M = ctx.Minv + 36 * (size_t)c;
-        double A[36], inv[36];
-#pragma unroll
-        for (int k = 0; k < 36; ++k) A[k] = M[k];
-        if (!inv_spd6(A, inv)) {
-            bad = 1;
-#pragma unroll
-            for (int k = 0; k < 36; ++k) inv[k] = 0.0;
-        }
-#pragma unroll
-        for (int k = 0; k < 36; ++k) M[k] = inv[k];
-#pragma unroll
-        for (int a = 0; a < 6; ++a) {
-            const double b = ctx.rhs[6 * (size_t)c + a];
-            ctx.cg_x[6 * (size_t)c + a] = 0.0;
-            ctx.cg_r[6 * (size_t)c + a] = b;
-            nb += b * b;
-        }
+    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+        const double b = ctx.rhs[i];
+        ctx.cg_x[i] = 0.0;
+        ctx.cg_r[i] = b;
+        nb += b * b;
     }
     nb = block_sum(nb, red);
-    bad = __syncthreads_or(bad);
     if (threadIdx.x == 0) {
         st->cg_norm_b = sqrt(nb);
         st->cg_rho = 1.0; st->cg_last_rho = 1.0; st->cg_Q0 = 0.0; st->cg_iter = 0; st->cg_done = 0;
-        if (bad || !isfinite(nb)) { st->chol_fail = 1; st->cg_done = 1; }
+        if (st->cg_bad_block || !isfinite(nb)) { st->chol_fail = 1; st->cg_done = 1; }
+        st->cg_bad_block = 0;
         // |r| <= r_tolerance * |b| at x = 0 (only when the relative-residual rule is enabled)
         if (ctx.opt.cg_r_tolerance > 0 && sqrt(nb) <= ctx.opt.cg_r_tolerance * sqrt(nb)) st->cg_done = 1;
         ctx.host_flags[1] = st->cg_done;
     }
 }
 
-// z = M^-1 r ; rho = r.z ; p = z + beta p.   Single CTA (n <= ~80k).
-__global__ void __launch_bounds__(1024) pcg_precond_kernel(Ctx ctx) {
+// z = M^-1 r ; rho = r.z ; p = z + beta p ; q = 0.   Cooperative, grid-stride over cameras.
+__global__ void __launch_bounds__(CG_THREADS) pcg_precond_kernel(Ctx ctx, double *part) {
     LMState *st = ctx.state;
     CG_GUARD(st);
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     __shared__ double red[32];
-    __shared__ double s_beta;
-    __shared__ int s_stop;
+    const int it = st->cg_iter + 1;                 // read before anyone advances it (block 0 writes after the grid barrier)
+    const double last_rho = st->cg_rho;
     double rho = 0.0;
-    for (int c = threadIdx.x; c < ctx.Nc; c += blockDim.x) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ctx.Nc; c += gridDim.x * blockDim.x) {
         const double *M = ctx.Minv + 36 * (size_t)c;
         double r[6];
 #pragma unroll
@@ -161,25 +189,25 @@ __global__ void __launch_bounds__(1024) pcg_precond_kernel(Ctx ctx) {
         }
     }
     rho = block_sum(rho, red);
-    if (threadIdx.x == 0) {
-        const int it = st->cg_iter + 1;
-        st->cg_iter = it;
-        st->cg_last_rho = st->cg_rho;
-        st->cg_rho = rho;
-        s_stop = 0;
-        s_beta = 0.0;
-        if (rho == 0.0 || !isfinite(rho)) { s_stop = 1; }
-        else if (it > 1) {
-            s_beta = rho / st->cg_last_rho;
-            if (s_beta == 0.0 || !isfinite(s_beta)) s_stop = 1;
-        }
-        if (s_stop) { st->chol_fail = 1; st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+    if (threadIdx.x == 0) part[blockIdx.x] = rho;
+    grid.sync();
+    rho = grid_total(part, gridDim.x, red);
+    bool stop = false;
+    double beta = 0.0;
+    if (rho == 0.0 || !isfinite(rho)) stop = true;
+    else if (it > 1) {
+        beta = rho / last_rho;
+        if (beta == 0.0 || !isfinite(beta)) stop = true;
     }
-    __syncthreads();
-    if (s_stop) return;
-    const double beta = s_beta;
-    const bool first = st->cg_iter == 1;
-    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->cg_iter = it;
+        st->cg_last_rho = last_rho;
+        st->cg_rho = rho;
+        if (stop) { st->chol_fail = 1; st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+    }
+    if (stop) return;
+    const bool first = it == 1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
         const double z = ctx.cg_z[i];
         ctx.cg_p[i] = first ? z : z + beta * ctx.cg_p[i];
         ctx.cg_q[i] = 0.0;
@@ -254,36 +282,39 @@ __device__ __forceinline__ double cam_block_row(const Ctx &ctx, const LMState *s
     return s;
 }
 
-// q += (U + D^2) p ; alpha = rho / p.q ; x += alpha p ; r -= alpha q ; stop rules.   Single CTA.
-__global__ void __launch_bounds__(1024) pcg_update_kernel(Ctx ctx) {
+// q += (U + D^2) p ; alpha = rho / p.q ; x += alpha p ; r -= alpha q ; stop rules.   Cooperative.
+__global__ void __launch_bounds__(CG_THREADS) pcg_update_kernel(Ctx ctx, double *part) {
     LMState *st = ctx.state;
     CG_GUARD(st);
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     __shared__ double red[32];
-    __shared__ double s_alpha;
-    __shared__ int s_stop;
+    const double rho = st->cg_rho;
     double pq = 0.0;
-    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
         const double q = ctx.cg_q[i] + cam_block_row(ctx, st, i / 6, i % 6, ctx.cg_p);
         ctx.cg_q[i] = q;
         pq += ctx.cg_p[i] * q;
     }
     pq = block_sum(pq, red);
-    if (threadIdx.x == 0) {
-        s_stop = 0;
-        s_alpha = 0.0;
-        if (pq <= 0.0 || isinf(pq) || isnan(pq)) {
-            // "Matrix is indefinite, no more progress can be made": keep the current x
-            s_stop = 1;
-        } else {
-            s_alpha = st->cg_rho / pq;
-            if (isinf(s_alpha)) { s_stop = 1; st->chol_fail = 1; }
-        }
-        if (s_stop) { st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+    if (threadIdx.x == 0) part[blockIdx.x] = pq;
+    grid.sync();
+    pq = grid_total(part, gridDim.x, red);
+    bool stop = false, fail = false;
+    double alpha = 0.0;
+    if (pq <= 0.0 || isinf(pq) || isnan(pq)) {
+        stop = true;                                  // "Matrix is indefinite, no more progress can be made": keep the current x
+    } else {
+        alpha = rho / pq;
+        if (isinf(alpha)) { stop = true; fail = true; }
     }
-    __syncthreads();
-    if (s_stop) return;
-    const double alpha = s_alpha;
-    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+    if (stop) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            if (fail) st->chol_fail = 1;
+            st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1;
+        }
+        return;
+    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
         ctx.cg_x[i] += alpha * ctx.cg_p[i];
         ctx.cg_r[i] -= alpha * ctx.cg_q[i];
     }
@@ -345,13 +376,39 @@ static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 21 
 int pcg_tiles_init(const Ctx &ctx) {
     return (int)cudaFuncSetAttribute(pcg_matvec_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_tile_smem(ctx));
 }
-void launch_pcg_start(const Ctx &ctx, cudaStream_t s) { pcg_start_kernel<<<1, 256, 0, s>>>(ctx); }
+void launch_pcg_start(const Ctx &ctx, cudaStream_t s) {
+    pcg_invert_blocks_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
+    pcg_start_kernel<<<1, 1024, 0, s>>>(ctx);
+}
+
+// grid of the cooperative camera-vector kernels: enough CTAs for the vector, never more than are co-resident
+static int cg_grid(const Ctx &ctx, const void *kernel) {
+    static int per_dev[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!per_dev[dev]) {
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, CG_THREADS, 0);
+        per_dev[dev] = std::max(1, std::min(sms * std::max(per_sm, 1), sms));      // one CTA per SM is plenty
+    }
+    return std::max(1, std::min(std::min(per_dev[dev], CG_MAX_GRID), cdiv(ctx.n, CG_THREADS)));
+}
 
 void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s) {      // precondition + direction + local matvec
-    pcg_precond_kernel<<<1, 1024, 0, s>>>(ctx);
+    Ctx c = ctx;
+    double *part = ctx.cg_part;
+    void *args[] = {&c, &part};
+    cudaLaunchCooperativeKernel((const void *)pcg_precond_kernel, dim3(cg_grid(ctx, (const void *)pcg_precond_kernel)), dim3(CG_THREADS), args, 0, s);
     pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_q);
 }
-void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) { pcg_update_kernel<<<1, 1024, 0, s>>>(ctx); }
+void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
+    Ctx c = ctx;
+    double *part = ctx.cg_part;
+    void *args[] = {&c, &part};
+    cudaLaunchCooperativeKernel((const void *)pcg_update_kernel, dim3(cg_grid(ctx, (const void *)pcg_update_kernel)), dim3(CG_THREADS), args, 0, s);
+}
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part of S x into cg_z
     cudaMemsetAsync(ctx.cg_z, 0, sizeof(double) * ctx.n, s);
     pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_z);

@@ -46,7 +46,7 @@ struct LMState {
     int n_recorded;
     int cg_done;             // PCG loop control
     int cg_iter;
-    int pad;
+    int cg_bad_block;        // a 6x6 preconditioner block was not positive definite
     double radius;
     double decrease_factor;
     double x_cost;
@@ -135,6 +135,7 @@ struct Ctx {
     double *camsums;         // [CS_COUNT]
     // PCG work vectors (n each) and block-Jacobi preconditioner
     double *cg_r, *cg_p, *cg_z, *cg_q, *cg_x, *Minv, *tp;
+    double *cg_part;         // [1024] per-CTA partials of the cooperative CG kernels
     // control
     LMState *state;
     ba_iteration *iters;     // [max_num_iterations + 2]
