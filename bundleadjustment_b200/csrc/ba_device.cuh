@@ -63,6 +63,34 @@ __device__ __forceinline__ void load_row6(const double *__restrict__ base, size_
     for (int k = 0; k < 6; ++k) v[k] = odd ? raw[k + 2] : raw[k];
 }
 
+// ---- TMA 1-D bulk copies (cp.async.bulk, SASS UBLKCP): a landmark block's W records are ONE contiguous, 16-byte
+// aligned run of 144 n bytes, so a single thread moves the whole tile between HBM and shared memory; the copy engine
+// does not occupy the LSU / L1 data pipe that the per-observation gathers and reductions need.
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_addr(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+}
+// one thread: arm the barrier with the byte count and start global -> shared
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gsrc, unsigned bytes, unsigned long long *bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+                 ::"r"(smem_addr(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile("{\n.reg .pred p;\nWAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+// one thread, after a CTA barrier that ordered the generic-proxy writes of the tile: shared -> global, then wait until the
+// source has been read (the CTA may exit / reuse the buffer afterwards)
+__device__ __forceinline__ void bulk_store(void *gdst, const void *smem_src, unsigned bytes) {
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(smem_addr(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+}
+
 enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
 
 // ceres::AngleAxisToRotationMatrix + closed-form derivative of the branch taken (autodiff-equivalent)

@@ -62,17 +62,19 @@ __device__ __forceinline__ Tile tile_of(const Ctx &ctx, int b) {
     t.o0 = ctx.pt_ptr[t.p0]; t.n = ctx.pt_ptr[t.p1] - t.o0;
     return t;
 }
-// coalesced copy of n records of 18 doubles between global W (at observation o0) and shared memory
+// n records of 18 doubles between global W (at observation o0) and shared memory: one TMA bulk copy each way.
+// tile_store_W: call after a CTA barrier that follows the last write of sW; only thread 0 does anything.
 __device__ __forceinline__ void tile_store_W(double *__restrict__ W, int o0, int n, const double *__restrict__ sW) {
-    double2 *dst = reinterpret_cast<double2 *>(W + 18 * (size_t)o0);
-    const double2 *src = reinterpret_cast<const double2 *>(sW);
-    for (int i = threadIdx.x; i < 9 * n; i += blockDim.x) dst[i] = src[i];
+    if (threadIdx.x == 0 && n > 0) bulk_store(W + 18 * (size_t)o0, sW, 144u * (unsigned)n);
 }
-__device__ __forceinline__ void tile_load_W(const double *__restrict__ W, int o0, int n, double *__restrict__ sW) {
-    const double2 *src = reinterpret_cast<const double2 *>(W + 18 * (size_t)o0);
-    double2 *dst = reinterpret_cast<double2 *>(sW);
-    for (int i = threadIdx.x; i < 9 * n; i += blockDim.x) dst[i] = __ldcs(src + i);     // streamed once per pass
+// tile_load_W: starts the copy (thread 0) and returns; every thread calls tile_wait_W before touching sW.  bar is a shared
+// 8-byte word used for this one transfer.
+__device__ __forceinline__ void tile_load_W(const double *__restrict__ W, int o0, int n, double *__restrict__ sW, unsigned long long *bar) {
+    if (threadIdx.x == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0 && n > 0) bulk_load(sW, W + 18 * (size_t)o0, 144u * (unsigned)n, bar);
 }
+__device__ __forceinline__ void tile_wait_W(unsigned long long *bar) { mbar_wait(bar, 0); }
 
 // C1+C2+C3 (landmark side): residual, analytic Jacobian, Huber corrector, Jacobi scaling per observation;
 // W = Jc^T Jp per observation; V_p, b_p per landmark; cost and gradient-norm partials per block.
@@ -127,7 +129,7 @@ __global__ void __launch_bounds__(TILE_THREADS) linearize_points_kernel(Ctx ctx,
         }
     }
     __syncthreads();
-    tile_store_W(ctx.W, t.o0, t.n, sW);
+    tile_store_W(ctx.W, t.o0, t.n, sW);            // TMA store by thread 0; the others go on with the per-landmark sums
     for (int p = t.p0 + threadIdx.x; p < t.p1; p += blockDim.x) {
         const int lo = ctx.pt_ptr[p] - t.o0, hi = ctx.pt_ptr[p + 1] - t.o0;
         double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
@@ -493,8 +495,8 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     const Tile t = tile_of(ctx, blockIdx.x);
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
-    tile_load_W(ctx.W, t.o0, t.n, sW);
-    __syncthreads();
+    __shared__ unsigned long long wbar;
+    tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
     for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
         const int c = ctx.pm_cam[t.o0 + k];
         double a3[3] = {0, 0, 0};
@@ -502,6 +504,7 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
             const double2 *y2 = reinterpret_cast<const double2 *>(ctx.yc + 6 * (size_t)c);
             const double2 y01 = y2[0], y23 = y2[1], y45 = y2[2];
             const double y[6] = {y01.x, y01.y, y23.x, y23.y, y45.x, y45.y};
+            tile_wait_W(&wbar);
             const double *Wo = sW + 18 * (size_t)k;
 #pragma unroll
             for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * y[a]; a3[1] += Wo[a * 3 + 1] * y[a]; a3[2] += Wo[a * 3 + 2] * y[a]; }

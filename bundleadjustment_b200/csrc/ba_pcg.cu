@@ -228,12 +228,11 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     const int p0 = ctx.blk_first_pt[b], p1 = ctx.blk_first_pt[b + 1];
     const int o0 = ctx.pt_ptr[p0], n = ctx.pt_ptr[p1] - o0;
     if (n == 0) return;
-    {
-        const double2 *src = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)o0);
-        double2 *dst = reinterpret_cast<double2 *>(sW);
-        for (int i = threadIdx.x; i < 9 * n; i += blockDim.x) dst[i] = __ldcs(src + i);
-    }
+    // the block's W records: one TMA bulk copy (thread 0) that streams in while the threads gather their camera entries of v
+    __shared__ unsigned long long wbar;
+    if (threadIdx.x == 0) mbar_init(&wbar, 1);
     __syncthreads();
+    if (threadIdx.x == 0) bulk_load(sW, ctx.W + 18 * (size_t)o0, 144u * (unsigned)n, &wbar);
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
         const int c = ctx.pm_cam[o0 + k];
         double a3[3] = {0, 0, 0};
@@ -241,6 +240,7 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
             const double2 *x2 = reinterpret_cast<const double2 *>(v + 6 * (size_t)c);
             const double2 x01 = x2[0], x23 = x2[1], x45 = x2[2];
             const double x[6] = {x01.x, x01.y, x23.x, x23.y, x45.x, x45.y};
+            mbar_wait(&wbar, 0);
             const double *Wo = sW + 18 * (size_t)k;
 #pragma unroll
             for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
@@ -264,6 +264,7 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         const int c = ctx.pm_cam[o0 + k];
         if (ctx.cam_kind[c] != CAM_FREE) continue;
         const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
+        mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
         const double *Wo = sW + 18 * (size_t)k;
 #pragma unroll
         for (int a = 0; a < 6; ++a)
