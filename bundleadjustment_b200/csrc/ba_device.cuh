@@ -91,6 +91,13 @@ __device__ __forceinline__ void bulk_store(void *gdst, const void *smem_src, uns
     asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
 }
 
+// record k of a shared-memory tile of 18-double records as nine 16-byte loads (conflict free at the 144-byte stride)
+__device__ __forceinline__ void load_record18(const double *__restrict__ sW, int k, double (&w)[18]) {
+    const double2 *src = reinterpret_cast<const double2 *>(sW + 18 * (size_t)k);
+#pragma unroll
+    for (int q = 0; q < 9; ++q) { const double2 v = src[q]; w[2 * q] = v.x; w[2 * q + 1] = v.y; }
+}
+
 enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
 
 // ceres::AngleAxisToRotationMatrix + closed-form derivative of the branch taken (autodiff-equivalent)

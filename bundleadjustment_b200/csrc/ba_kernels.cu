@@ -78,7 +78,7 @@ __device__ __forceinline__ void tile_wait_W(unsigned long long *bar) { mbar_wait
 
 // C1+C2+C3 (landmark side): residual, analytic Jacobian, Huber corrector, Jacobi scaling per observation;
 // W = Jc^T Jp per observation; V_p, b_p per landmark; cost and gradient-norm partials per block.
-__global__ void __launch_bounds__(TILE_THREADS) linearize_points_kernel(Ctx ctx, int force) {
+__global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
     extern __shared__ __align__(16) double tsm[];
@@ -113,7 +113,9 @@ __global__ void __launch_bounds__(TILE_THREADS) linearize_points_kernel(Ctx ctx,
         v[5] = Jp[2] * Jp[2] + Jp[5] * Jp[5];
 #pragma unroll
         for (int j = 0; j < 3; ++j) v[6 + j] = Jp[j] * r[0] + Jp[3 + j] * r[1];
-        double *Wo = sW + 18 * (size_t)k;
+        // the record leaves as nine 16-byte shared stores: at the 144-byte record stride those are bank-conflict free,
+        // eighteen 8-byte stores are 4-way conflicted
+        double wr[18];
         if (kind == CAM_FREE) {
             const double *sc = ctx.scale_cam + 6 * (size_t)c;
 #pragma unroll
@@ -121,12 +123,15 @@ __global__ void __launch_bounds__(TILE_THREADS) linearize_points_kernel(Ctx ctx,
                 const double f = sr * sc[a];
                 const double j0 = Jc[a] * f, j1 = Jc[6 + a] * f;
 #pragma unroll
-                for (int q = 0; q < 3; ++q) Wo[a * 3 + q] = j0 * Jp[q] + j1 * Jp[3 + q];
+                for (int q = 0; q < 3; ++q) wr[a * 3 + q] = j0 * Jp[q] + j1 * Jp[3 + q];
             }
         } else {
 #pragma unroll
-            for (int q = 0; q < 18; ++q) Wo[q] = 0.0;
+            for (int q = 0; q < 18; ++q) wr[q] = 0.0;
         }
+        double2 *Wo2 = reinterpret_cast<double2 *>(sW + 18 * (size_t)k);
+#pragma unroll
+        for (int q = 0; q < 9; ++q) Wo2[q] = make_double2(wr[2 * q], wr[2 * q + 1]);
     }
     __syncthreads();
     tile_store_W(ctx.W, t.o0, t.n, sW);            // TMA store by thread 0; the others go on with the per-landmark sums
@@ -505,7 +510,8 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
             const double2 y01 = y2[0], y23 = y2[1], y45 = y2[2];
             const double y[6] = {y01.x, y01.y, y23.x, y23.y, y45.x, y45.y};
             tile_wait_W(&wbar);
-            const double *Wo = sW + 18 * (size_t)k;
+            double Wo[18];
+            load_record18(sW, k, Wo);
 #pragma unroll
             for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * y[a]; a3[1] += Wo[a * 3 + 1] * y[a]; a3[2] += Wo[a * 3 + 2] * y[a]; }
         }

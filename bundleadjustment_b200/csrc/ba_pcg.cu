@@ -241,7 +241,8 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
             const double2 x01 = x2[0], x23 = x2[1], x45 = x2[2];
             const double x[6] = {x01.x, x01.y, x23.x, x23.y, x45.x, x45.y};
             mbar_wait(&wbar, 0);
-            const double *Wo = sW + 18 * (size_t)k;
+            double Wo[18];
+            load_record18(sW, k, Wo);
 #pragma unroll
             for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
         }
@@ -265,7 +266,8 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         if (ctx.cam_kind[c] != CAM_FREE) continue;
         const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
         mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
-        const double *Wo = sW + 18 * (size_t)k;
+        double Wo[18];
+        load_record18(sW, k, Wo);
 #pragma unroll
         for (int a = 0; a < 6; ++a)
             atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
