@@ -16,22 +16,26 @@ namespace ba {
 
 // ---------------------------------------------------------------------------------------------------------
 // Per-camera table entry, rebuilt once per linearisation point by cam_prep_kernel so that the per-observation
-// kernels never evaluate sincos.  52 doubles = 416 B in three 32-byte-aligned groups, so that a thread gathers its camera
-// with 256-bit loads (LDG.E.ENL2.256: one L1 wavefront per 32 B instead of one per double; the landmark-major kernels
-// gather a different camera in every lane, which made the 64-bit version L1-bound).
-//   free camera : R (col-major 3x3) | t,  K (row-major, promoted from f32),  dR[3] = dR/dw_k (col-major)
-//   fixed camera: P = 4x4 row-major world->camera extrinsics (promoted from f32) in dR[0..15], K
+// kernels never evaluate sincos.  40 doubles = 320 B in three 32-byte-aligned groups, so that a thread gathers its camera
+// with 256-bit loads (LDG.E.ENL2.256; the landmark-major kernels gather a different camera in every lane, and a gather
+// costs L1 data-pipe passes per load instruction and lane, not per byte).
+//   free camera : R (col-major 3x3) | t,   K (row-major, promoted from f32),   Jr | sc
+//                 Jr = right Jacobian of the rotation, stored as its three columns: d(R X)/dw_j = R (Jr_j x X).  It is
+//                 derived in cam_prep from the exact dR/dw_j (Jr_j = vee(R^T dR_j)), 9 doubles instead of 27.
+//                 sc = Jacobi scale of the six camera parameters (travels with the entry instead of a second gather).
+//   fixed camera: P = 4x4 row-major world->camera extrinsics (promoted from f32) in Jr[0..8] | sc[0..5] | pad, K
 // ---------------------------------------------------------------------------------------------------------
 struct __align__(32) CamEntry {
     double R[9];
     double t[3];
     double K[9];
     double pad0[3];
-    double dR[27];
+    double Jr[9];
+    double sc[6];
     double pad1;
 };
-static_assert(sizeof(CamEntry) == 52 * 8, "CamEntry layout");
-static_assert(offsetof(CamEntry, K) % 32 == 0 && offsetof(CamEntry, dR) % 32 == 0, "CamEntry groups must be 32-byte aligned");
+static_assert(sizeof(CamEntry) == 40 * 8, "CamEntry layout");
+static_assert(offsetof(CamEntry, K) % 32 == 0 && offsetof(CamEntry, Jr) % 32 == 0, "CamEntry groups must be 32-byte aligned");
 
 struct __align__(32) Double4 { double x, y, z, w; };
 // N4 x 256-bit loads of 32-byte-aligned doubles into registers
@@ -192,7 +196,7 @@ __device__ __forceinline__ void obs_residual(const CamEntry *__restrict__ ce, in
         for (int i = 0; i < 3; ++i) p[i] = Rt[i] * X[0] + Rt[i + 3] * X[1] + Rt[i + 6] * X[2] + Rt[9 + i];
     } else {
         double P[16];
-        load_vec4<4>(ce->dR, P);
+        load_vec4<4>(ce->Jr, P);
         double ph[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
@@ -206,9 +210,10 @@ __device__ __forceinline__ void obs_residual(const CamEntry *__restrict__ ce, in
 }
 
 // residual + Jacobians (unrobustified, unscaled).  Jc 2x6 row-major (zero for fixed), Jp 2x3 row-major.
+// sc (may be nullptr): receives the camera's six Jacobi scales from the table entry (1 for fixed cameras).
 template <bool WANT_JC, bool WANT_JP>
 __device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, int kind, const double X[3], float2 uv,
-                                              double r[2], double Jc[12], double Jp[6]) {
+                                              double r[2], double Jc[12], double Jp[6], double *sc = nullptr) {
     double p[3], pix[2], G[6], K[12];
     load_vec4<3>(ce->K, K);
     if (kind == CAM_FREE) {
@@ -217,31 +222,37 @@ __device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, i
 #pragma unroll
         for (int i = 0; i < 3; ++i) p[i] = Rt[i] * X[0] + Rt[i + 3] * X[1] + Rt[i + 6] * X[2] + Rt[9 + i];
         project(K, p, pix, G, true);
+        double GR[6];                                     // d pix / d X = G R (2 x 3)
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                GR[rr * 3 + j] = G[rr * 3 + 0] * Rt[0 + 3 * j] + G[rr * 3 + 1] * Rt[1 + 3 * j] + G[rr * 3 + 2] * Rt[2 + 3 * j];
         if (WANT_JP) {
 #pragma unroll
-            for (int rr = 0; rr < 2; ++rr)
-#pragma unroll
-                for (int j = 0; j < 3; ++j)
-                    Jp[rr * 3 + j] = G[rr * 3 + 0] * Rt[0 + 3 * j] + G[rr * 3 + 1] * Rt[1 + 3 * j] + G[rr * 3 + 2] * Rt[2 + 3 * j];
+            for (int k = 0; k < 6; ++k) Jp[k] = GR[k];
         }
         if (WANT_JC) {
-            double dRr[28];
-            load_vec4<7>(ce->dR, dRr);
+            double Js[16];
+            load_vec4<4>(ce->Jr, Js);
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
-                const double *D = dRr + 9 * j;
-                double d[3];
-#pragma unroll
-                for (int i = 0; i < 3; ++i) d[i] = D[i] * X[0] + D[i + 3] * X[1] + D[i + 6] * X[2];
-                Jc[j] = G[0] * d[0] + G[1] * d[1] + G[2] * d[2];
-                Jc[6 + j] = G[3] * d[0] + G[4] * d[1] + G[5] * d[2];
+                // d(R X)/dw_j = R (Jr_j x X)  ->  d pix / dw_j = (G R) (Jr_j x X)
+                const double a0 = Js[3 * j], a1 = Js[3 * j + 1], a2 = Js[3 * j + 2];
+                const double c0 = a1 * X[2] - a2 * X[1], c1 = a2 * X[0] - a0 * X[2], c2 = a0 * X[1] - a1 * X[0];
+                Jc[j] = GR[0] * c0 + GR[1] * c1 + GR[2] * c2;
+                Jc[6 + j] = GR[3] * c0 + GR[4] * c1 + GR[5] * c2;
             }
 #pragma unroll
             for (int j = 0; j < 3; ++j) { Jc[3 + j] = G[j]; Jc[9 + j] = G[3 + j]; }
+            if (sc) {
+#pragma unroll
+                for (int a = 0; a < 6; ++a) sc[a] = Js[9 + a];
+            }
         }
     } else {
         double P[16];
-        load_vec4<4>(ce->dR, P);
+        load_vec4<4>(ce->Jr, P);
         double ph[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
@@ -263,6 +274,10 @@ __device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, i
         if (WANT_JC) {
 #pragma unroll
             for (int j = 0; j < 12; ++j) Jc[j] = 0.0;
+            if (sc) {
+#pragma unroll
+                for (int a = 0; a < 6; ++a) sc[a] = 1.0;
+            }
         }
     }
     r[0] = pix[0] - (double)uv.x;

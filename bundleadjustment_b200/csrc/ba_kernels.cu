@@ -31,7 +31,7 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
     for (int i = 0; i < 9; ++i) ce->K[i] = (double)K[i];
     if (kind == CAM_FIXED) {
         const float *E = ctx.cam_extr + 16 * (size_t)c;
-        double *P = ce->dR;
+        double *P = ce->Jr;                       // 16 contiguous doubles: Jr[9] | sc[6] | pad1
 #pragma unroll
         for (int i = 0; i < 16; ++i) P[i] = (double)E[i];
         return;
@@ -43,8 +43,21 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
 #pragma unroll
     for (int i = 0; i < 9; ++i) ce->R[i] = R[i];
     if (which == 0) {
+        // right Jacobian from the exact derivative: R^T dR_j is the skew matrix [Jr_j]x
 #pragma unroll
-        for (int i = 0; i < 27; ++i) ce->dR[i] = dR[i];
+        for (int j = 0; j < 3; ++j) {
+            const double *D = dR + 9 * j;
+            double S[9];                          // S[a][b] = sum_i R[i][a] D[i][b]   (R, D column-major)
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+#pragma unroll
+                for (int b = 0; b < 3; ++b) S[a * 3 + b] = R[0 + 3 * a] * D[0 + 3 * b] + R[1 + 3 * a] * D[1 + 3 * b] + R[2 + 3 * a] * D[2 + 3 * b];
+            ce->Jr[3 * j + 0] = 0.5 * (S[2 * 3 + 1] - S[1 * 3 + 2]);
+            ce->Jr[3 * j + 1] = 0.5 * (S[0 * 3 + 2] - S[2 * 3 + 0]);
+            ce->Jr[3 * j + 2] = 0.5 * (S[1 * 3 + 0] - S[0 * 3 + 1]);
+        }
+#pragma unroll
+        for (int a = 0; a < 6; ++a) ce->sc[a] = ctx.scale_cam[6 * (size_t)c + a];
     }
     ce->t[0] = x[3]; ce->t[1] = x[4]; ce->t[2] = x[5];
 }
@@ -95,8 +108,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
         const float2 uv = ctx.pm_uv[o];
         const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
-        double r[2], Jc[12], Jp[6];
-        obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
+        double r[2], Jc[12], Jp[6], sc[6];
+        obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp, sc);
         double rho0;
         const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
         const double sr = sqrt(rho1);
@@ -117,7 +130,6 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
         // eighteen 8-byte stores are 4-way conflicted
         double wr[18];
         if (kind == CAM_FREE) {
-            const double *sc = ctx.scale_cam + 6 * (size_t)c;
 #pragma unroll
             for (int a = 0; a < 6; ++a) {
                 const double f = sr * sc[a];

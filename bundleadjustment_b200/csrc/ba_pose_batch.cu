@@ -11,8 +11,16 @@ namespace ba {
 
 constexpr int PB_THREADS = 128;
 
+// camera record of one pose problem (shared memory, read uniformly by the CTA): R and dR/dw_k column-major, t, K
+struct PoseCam {
+    double R[9];
+    double dR[27];
+    double t[3];
+    double K[9];
+};
+
 struct PoseShared {
-    CamEntry ce;              // R, dR, t, K at the point being evaluated
+    PoseCam ce;               // R, dR, t, K at the point being evaluated
     double x[6], cand[6], scale[6];
     double H[36];             // J^T J (unscaled, robustified)
     double g[6];              // J^T r (unscaled)
@@ -25,7 +33,7 @@ struct PoseShared {
 
 // residual (+ 2x6 Jacobian) of PoseOnlyAngleReprojectionError: p = [R t] * Xh
 template <bool WANT_J>
-__device__ __forceinline__ void pose_obs(const CamEntry &ce, float4 Xh, float2 uv, double r[2], double Jc[12]) {
+__device__ __forceinline__ void pose_obs(const PoseCam &ce, float4 Xh, float2 uv, double r[2], double Jc[12]) {
     const double X[3] = {(double)Xh.x, (double)Xh.y, (double)Xh.z};
     const double w = (double)Xh.w;
     double p[3];
