@@ -706,7 +706,7 @@ void dissect(const TileGraph &g, std::vector<int> nodes, std::vector<int> &in, i
             }
             before += cnt[l];
         }
-        const bool leaf = m < 0 || total <= 2 * cnt[m] + 2 || 3 * cnt[m] > total;
+        const bool leaf = m < 0 || total <= cnt[m] + 1 || 2 * cnt[m] > total;
         if (leaf) {
             for (int v : comp) { order.push_back(v); in[v] = -1; }     // BFS order keeps the leaf banded
             continue;
