@@ -413,8 +413,15 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.n_part = ctx.n_blocks;
 
     // ---- parameters and constants ----
-    UP(cam0, cam, 6 * (size_t)Nc); UP(cam1, cam, 6 * (size_t)Nc); UP(cam_init, cam, 6 * (size_t)Nc);
-    UP(pt0, pt, 3 * (size_t)Np); UP(pt1, pt, 3 * (size_t)Np); UP(pt_init, pt, 3 * (size_t)Np);
+    // one H2D copy each; the two working buffers are filled device-to-device
+    UP(cam_init, cam, 6 * (size_t)Nc); UP(pt_init, pt, 3 * (size_t)Np);
+    AL(cam0, 8 * 6 * (size_t)Nc); AL(cam1, 8 * 6 * (size_t)Nc); AL(pt0, 8 * 3 * (size_t)Np); AL(pt1, 8 * 3 * (size_t)Np);
+    CU(cudaMemcpyAsync(h->cam0.p, h->cam_init.p, 8 * 6 * (size_t)Nc, cudaMemcpyDeviceToDevice, s));
+    CU(cudaMemcpyAsync(h->cam1.p, h->cam_init.p, 8 * 6 * (size_t)Nc, cudaMemcpyDeviceToDevice, s));
+    if (Np) {
+        CU(cudaMemcpyAsync(h->pt0.p, h->pt_init.p, 8 * 3 * (size_t)Np, cudaMemcpyDeviceToDevice, s));
+        CU(cudaMemcpyAsync(h->pt1.p, h->pt_init.p, 8 * 3 * (size_t)Np, cudaMemcpyDeviceToDevice, s));
+    }
     UP(cam_K, K, 9 * (size_t)Nc);
     if (fixed_extr) { UP(cam_extr, fixed_extr, 16 * (size_t)Nc); }
     else { AL(cam_extr, 64 * (size_t)Nc); CU(cudaMemsetAsync(h->cam_extr.p, 0, 64 * (size_t)Nc, s)); }
