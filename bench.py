@@ -308,6 +308,13 @@ def main_ours(args):
                  "unit": "GB/s", "frac": eval_bytes / (ev_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": hbm_src,
                  "algorithmic_bytes_per_obs": 176 + 16}
     extra = {}
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the committed ncu --set full
+    # captures (profiles/): only valid for the full-size named workloads on one GPU
+    traffic = None
+    if world == 1 and args.scale == 1.0:
+        traffic = {("K4", "dense"): 65.548e6 + 19.983e6,        # profiles/r01_K4_cholesky_sparse_ncu_full_v9.txt
+                   ("K5", "pcg"): 4.685456e9 + 0.003992e9,      # profiles/r01_K5_pcg_kernels_ncu_full_v7.txt
+                   }.get((args.workload, args.solver))
     if args.solver == "dense":
         fp64_peak = measure_fp64_peak(local)
         peak_src = ("FP64: torch.matmul f64 4096^3 measured in this run (MEASURED_PEAKS.json has no FP64 entry; the register-only "
@@ -315,7 +322,7 @@ def main_ours(args):
         ach = n_solves * rs["flops"] / t_chol / 1e12 if t_chol > 0 else 0.0
         roofline = {"bound": "tensor", "kernel": "chol_dataflow_kernel (tile-sparse left-looking Cholesky + both substitutions of the reduced camera "
                                                  "system, one cooperative launch, DMMA m8n8k4)",
-                    "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None, "peak_source": peak_src,
+                    "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": traffic, "peak_source": peak_src,
                     "flops_per_launch": rs["flops"], "avg_launch_ms": t_chol / max(n_solves, 1) * 1e3, "share_of_step": t_chol / t_dev,
                     "padded_order": rs["n"], "filled_tiles": rs["filled_tiles"], "lower_tiles": rs["lower_tiles"],
                     "dense_equivalent_flops": cholesky_flops(rs["n"]),
@@ -341,7 +348,7 @@ def main_ours(args):
         per_cg = 144.0 * pb.shape[2] + 48.0 * pb.shape[1] + 10 * 8.0 * 6 * Nc
         ach = cg_its * per_cg / t_lin / 1e9 if t_lin > 0 else 0.0
         roofline = {"bound": "hbm", "kernel": "pcg_matvec_points_kernel (one pass over W per CG iteration; achieved = bytes x CG iterations / linear-solve stage time, which also holds the preconditioner setup)", "achieved": ach,
-                    "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                    "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": traffic, "peak_source": hbm_src,
                     "bytes_per_launch": per_cg, "share_of_step": t_lin / t_dev}
     cpu = cpu_baseline(pb_full, args.workload, args.solver) if (world == 1 and not args.no_cpu) else None
     out = {
