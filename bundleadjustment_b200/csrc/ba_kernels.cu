@@ -408,12 +408,10 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
     const int u = blockIdx.x * SCHUR_WARPS + warp;
     const PairIndex &pi = ctx.pairs;
     if (u >= pi.n_units) return;
-    const int seg = pi.unit_seg[u];
+    const int info = pi.unit_seg[u];
     const long long beg = pi.unit_beg[u];
-    const long long seg_end = (seg + 1 < pi.n_seg) ? pi.seg_beg[seg + 1] : pi.P;
-    const long long end = (beg + PAIR_UNIT < seg_end) ? beg + PAIR_UNIT : seg_end;
-    const int2 cams = pi.seg_cams[seg];
-    const bool diag = cams.x == cams.y;
+    const long long end = beg + (info >> 1);
+    const bool diag = info & 1;
     double *Ys = sY[warp], *Bs = sB[warp];
     double c0 = 0.0, c1 = 0.0;                                          // C[g][2 tig], C[g][2 tig + 1] of the 8 x 8 product
     long long e = beg + lane;

@@ -185,13 +185,20 @@ __global__ void pair_unit_count_kernel(int n_seg, long long P, const long long *
     unit_cnt[s] = (int)((e - seg_beg[s] + PAIR_UNIT - 1) / PAIR_UNIT);
 }
 
-__global__ void pair_unit_fill_kernel(int n_seg, long long P, const long long *__restrict__ seg_beg, const int *__restrict__ unit_ptr,
-                                      int *__restrict__ unit_seg, long long *__restrict__ unit_beg) {
+// unit record: first entry + (entry count << 1 | diagonal block), so that a unit starts with ONE round of loads
+__global__ void pair_unit_fill_kernel(int n_seg, long long P, const long long *__restrict__ seg_beg, const int2 *__restrict__ seg_cams,
+                                      const int *__restrict__ unit_ptr, int *__restrict__ unit_info, long long *__restrict__ unit_beg) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_seg) return;
     const long long e = (s + 1 < n_seg) ? seg_beg[s + 1] : P;
+    const int2 c = seg_cams[s];
+    const int diag = c.x == c.y;
     int u = unit_ptr[s];
-    for (long long b = seg_beg[s]; b < e; b += PAIR_UNIT, ++u) { unit_seg[u] = s; unit_beg[u] = b; }
+    for (long long b = seg_beg[s]; b < e; b += PAIR_UNIT, ++u) {
+        const long long cnt = (e - b < PAIR_UNIT) ? e - b : PAIR_UNIT;
+        unit_info[u] = ((int)cnt << 1) | diag;
+        unit_beg[u] = b;
+    }
 }
 
 // ---- host drivers ------------------------------------------------------------------------------------------------
@@ -384,7 +391,7 @@ int prep_group_map(const PairIndex &pi, int G, unsigned char *map, cudaStream_t 
 
 int prep_pairs_units(PairIndex &pi, cudaStream_t s) {
     if (pi.n_seg > 0)
-        pair_unit_fill_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.P, pi.seg_beg, pi.unit_ptr, pi.unit_seg, pi.unit_beg);
+        pair_unit_fill_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.P, pi.seg_beg, pi.seg_cams, pi.unit_ptr, pi.unit_seg, pi.unit_beg);
     return (int)cudaGetLastError();
 }
 

@@ -69,7 +69,7 @@ struct PairIndex {
     long long *seg_beg;      // [n_seg]
     int2 *seg_cams;          // [n_seg] (ci, cj), ci >= cj
     int *unit_ptr;           // [n_seg + 1]
-    int *unit_seg;           // [n_units]
+    int *unit_seg;           // [n_units] entry count << 1 | (diagonal block)
     long long *unit_beg;     // [n_units]
     double *unit_part;       // [n_units][42]: 36 block entries + 6 rhs entries
 };
