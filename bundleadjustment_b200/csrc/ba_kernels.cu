@@ -834,7 +834,7 @@ void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
 // landmark + camera side of one linearisation (local part; the caller all-reduces U/bc/sums when sharded)
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
-    linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+    if (ctx.n_blocks > 0) linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
     if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx, force);
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<1, 1024, 0, s>>>(ctx, force);
@@ -883,18 +883,18 @@ void launch_chol_rhs(const Ctx &ctx, cudaStream_t s) { chol_rhs_kernel<<<cdiv(ct
 void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s) { chol_unpermute_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, y); }
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {
-    backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);
+    if (ctx.n_blocks > 0) backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);
     cam_update_kernel<<<1, 512, 0, s>>>(ctx);
 }
 
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s) {
     const int nb = cdiv(ctx.No, 256);
-    eval_candidate_kernel<<<nb, 256, 0, s>>>(ctx, cost_part);
+    if (nb > 0) eval_candidate_kernel<<<nb, 256, 0, s>>>(ctx, cost_part);
     reduce_step_partials_kernel<<<1, 1024, 0, s>>>(ctx, cost_part, nb);
 }
 
 void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s) {
-    evaluate_materialize_kernel<<<cdiv(ctx.No, 128), 128, 0, s>>>(ctx, res, jc, jp, cost_part);
+    if (ctx.No > 0) evaluate_materialize_kernel<<<cdiv(ctx.No, 128), 128, 0, s>>>(ctx, res, jc, jp, cost_part);
 }
 
 } // namespace ba

@@ -404,7 +404,7 @@ void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s) {      // precondition + 
     double *part = ctx.cg_part;
     void *args[] = {&c, &part};
     cudaLaunchCooperativeKernel((const void *)pcg_precond_kernel, dim3(cg_grid(ctx, (const void *)pcg_precond_kernel)), dim3(CG_THREADS), args, 0, s);
-    pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_q);
+    if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_q);
 }
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
     Ctx c = ctx;
@@ -414,7 +414,7 @@ void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
 }
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part of S x into cg_z
     cudaMemsetAsync(ctx.cg_z, 0, sizeof(double) * ctx.n, s);
-    pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_z);
+    if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_z);
 }
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<1, 1024, 0, s>>>(ctx); }
 void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<1, 1024, 0, s>>>(ctx); }
