@@ -431,12 +431,12 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(U, 8 * 36 * (size_t)Nc); AL(bc, 8 * 6 * (size_t)Nc); AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
     AL(W, 8 * 18 * (size_t)No + 64);     /* + slack: rows are fetched as aligned 32-byte windows (load_row18) */ AL(cam_part, 8 * 27 * (size_t)std::max(ctx.n_chunks, 1));
     AL(Vinv, 8 * 6 * (size_t)Np + 64); AL(wv, 8 * 3 * (size_t)Np);
-    AL(rhs, 8 * (size_t)ctx.n); AL(yc, 8 * (size_t)ctx.n);
+    AL(rhs, 8 * (size_t)ctx.n); AL(yc, 8 * (size_t)ctx.n + 64);      /* + slack: 6-double rows are gathered as 32-byte windows */
     AL(part, 8 * 4 * (size_t)ctx.n_part); AL(cost_part, 8 * (size_t)((No + 127) / 128 + 1));
     AL(sums, 8 * SUM_COUNT); AL(maxs, 8 * MAX_COUNT); AL(camsums, 8 * CS_COUNT);
     AL(state, sizeof(LMState)); AL(iters, sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2));
-    AL(cg_r, 8 * (size_t)ctx.n); AL(cg_p, 8 * (size_t)ctx.n); AL(cg_z, 8 * (size_t)ctx.n); AL(cg_q, 8 * (size_t)ctx.n);
-    AL(cg_x, 8 * (size_t)ctx.n); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np); AL(cg_part, 8 * 1024);
+    AL(cg_r, 8 * (size_t)ctx.n); AL(cg_p, 8 * (size_t)ctx.n + 64); AL(cg_z, 8 * (size_t)ctx.n); AL(cg_q, 8 * (size_t)ctx.n);
+    AL(cg_x, 8 * (size_t)ctx.n + 64); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np); AL(cg_part, 8 * 1024);
     ctx.cam[0] = h->cam0.as<double>(); ctx.cam[1] = h->cam1.as<double>();
     ctx.pt[0] = h->pt0.as<double>(); ctx.pt[1] = h->pt1.as<double>();
     ctx.cam_init = h->cam_init.as<double>(); ctx.pt_init = h->pt_init.as<double>();

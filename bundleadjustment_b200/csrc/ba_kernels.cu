@@ -516,9 +516,8 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
         const int c = ctx.pm_cam[t.o0 + k];
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
-            const double2 *y2 = reinterpret_cast<const double2 *>(ctx.yc + 6 * (size_t)c);
-            const double2 y01 = y2[0], y23 = y2[1], y45 = y2[2];
-            const double y[6] = {y01.x, y01.y, y23.x, y23.y, y45.x, y45.y};
+            double y[6];
+            load_row6(ctx.yc, (size_t)c, y);
             tile_wait_W(&wbar);
             double Wo[18];
             load_record18(sW, k, Wo);

@@ -34,13 +34,9 @@ __global__ void __launch_bounds__(128) pcg_setup_cams_kernel(Ctx ctx) {
     for (int k = 0; k < 27; ++k) acc[k] = 0.0;
     for (int d = beg + lane; d < end; d += 32) {
         const int e = ctx.cm_obs[d], p = ctx.cm_pt[d];
-        const double2 *W2 = reinterpret_cast<const double2 *>(ctx.W + 18 * (size_t)e);
-        double wv[18];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) { const double2 v = W2[k]; wv[2 * k] = v.x; wv[2 * k + 1] = v.y; }
-        const double2 *Vi2 = reinterpret_cast<const double2 *>(ctx.Vinv + 6 * (size_t)p);
-        const double2 v01 = Vi2[0], v23 = Vi2[1], v45 = Vi2[2];
-        const double vi[6] = {v01.x, v01.y, v23.x, v23.y, v45.x, v45.y};
+        double wv[18], vi[6];                              // gathers as aligned 256-bit windows (7 requests instead of 12)
+        load_row18(ctx.W, (size_t)e, wv);
+        load_row6(ctx.Vinv, (size_t)p, vi);
         const double *w3 = ctx.wv + 3 * (size_t)p;
         const double t0 = w3[0], t1 = w3[1], t2 = w3[2];
         double Y[18];
@@ -237,9 +233,8 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         const int c = ctx.pm_cam[o0 + k];
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
-            const double2 *x2 = reinterpret_cast<const double2 *>(v + 6 * (size_t)c);
-            const double2 x01 = x2[0], x23 = x2[1], x45 = x2[2];
-            const double x[6] = {x01.x, x01.y, x23.x, x23.y, x45.x, x45.y};
+            double x[6];
+            load_row6(v, (size_t)c, x);
             mbar_wait(&wbar, 0);
             double Wo[18];
             load_record18(sW, k, Wo);
