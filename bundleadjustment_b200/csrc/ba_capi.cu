@@ -106,7 +106,7 @@ struct ba_handle {
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
     DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
     DevBuf part, cost_part, sums, maxs, camsums, state, iters, invL, U_loc, bc_loc, sums_loc, maxs_loc;
-    DevBuf cg_r, cg_p, cg_z, cg_q, cg_x, Minv, tp, cg_part;
+    DevBuf cg_r, cg_p, cg_z, cg_q, cg_x, Minv, tp, cg_part, cg_qp;
     DevBuf ev_res, ev_jc, ev_jp;     // materialised evaluation outputs
     int *host_flags = nullptr;       // mapped pinned
     int *host_flags_dev = nullptr;
@@ -135,7 +135,7 @@ struct ba_handle {
         DevBuf *all[] = {&cam0, &cam1, &pt0, &pt1, &cam_init, &pt_init, &cam_kind, &cam_K, &cam_extr, &pm_uv, &pm_cam, &pm_pt,
                          &pt_ptr, &cm_uv, &cm_pt, &chunk_cam, &chunk_beg, &chunk_end, &cam_chunk_ptr, &tab_x, &tab_c, &scale_cam,
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &sums, &maxs,
-                         &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &ev_res, &ev_jc, &ev_jp,
+                         &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
                          &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
         for (DevBuf *b : all) b->free();
@@ -436,7 +436,8 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(sums, 8 * SUM_COUNT); AL(maxs, 8 * MAX_COUNT); AL(camsums, 8 * CS_COUNT);
     AL(state, sizeof(LMState)); AL(iters, sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2));
     AL(cg_r, 8 * (size_t)ctx.n); AL(cg_p, 8 * (size_t)ctx.n + 64); AL(cg_z, 8 * (size_t)ctx.n); AL(cg_q, 8 * (size_t)ctx.n);
-    AL(cg_x, 8 * (size_t)ctx.n + 64); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np); AL(cg_part, 8 * 1024);
+    AL(cg_x, 8 * (size_t)ctx.n + 64); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np); AL(cg_part, 8 * 1024); AL(cg_qp, 8 * 32 * (size_t)ctx.n);
+    CU(cudaMemsetAsync(h->cg_qp.p, 0, 8 * 32 * (size_t)ctx.n, s));
     ctx.cam[0] = h->cam0.as<double>(); ctx.cam[1] = h->cam1.as<double>();
     ctx.pt[0] = h->pt0.as<double>(); ctx.pt[1] = h->pt1.as<double>();
     ctx.cam_init = h->cam_init.as<double>(); ctx.pt_init = h->pt_init.as<double>();
@@ -453,7 +454,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.rhs = h->rhs.as<double>(); ctx.yc = h->yc.as<double>();
     ctx.part = h->part.as<double>(); ctx.sums = h->sums.as<double>(); ctx.maxs = h->maxs.as<double>(); ctx.camsums = h->camsums.as<double>();
     ctx.cg_r = h->cg_r.as<double>(); ctx.cg_p = h->cg_p.as<double>(); ctx.cg_z = h->cg_z.as<double>(); ctx.cg_q = h->cg_q.as<double>();
-    ctx.cg_x = h->cg_x.as<double>(); ctx.Minv = h->Minv.as<double>(); ctx.tp = h->tp.as<double>(); ctx.cg_part = h->cg_part.as<double>();
+    ctx.cg_x = h->cg_x.as<double>(); ctx.Minv = h->Minv.as<double>(); ctx.tp = h->tp.as<double>(); ctx.cg_part = h->cg_part.as<double>(); ctx.cg_qp = h->cg_qp.as<double>();
     ctx.state = h->state.as<LMState>(); ctx.iters = h->iters.as<ba_iteration>();
     ctx.host_flags = h->host_flags_dev;
     if (h->comm) {
@@ -598,12 +599,12 @@ int enqueue_linear_solve(ba_handle *h) {
             launch_pcg_iter_a(ctx, s);
             if ((rc = allreduce_sum(h, ctx.cg_q, (size_t)ctx.n))) return rc;
             launch_pcg_iter_b(ctx, s);
-            h->launches += 3;
+            h->launches += 4;
             if (it % 10 == 0) {   // residual_reset_period
                 launch_pcg_reset_a(ctx, s);
                 if ((rc = allreduce_sum(h, ctx.cg_z, (size_t)ctx.n))) return rc;
                 launch_pcg_reset_b(ctx, s);
-                h->launches += 3;
+                h->launches += 3;   // matvec, fold, reset
             }
             launch_pcg_check(ctx, s);
             h->launches += 1;

@@ -103,6 +103,7 @@ __global__ void pcg_setup_reduce_kernel(Ctx ctx) {
 // reduced per CTA, published, and after grid.sync() EVERY CTA sums the published partials in the same fixed order, so all
 // of them hold the identical scalar and go on to the dependent vector update -- one launch instead of a single-CTA kernel
 // (which left 147 SMs idle for ~120 us per call, the dominant replicated cost on 8 GPUs).
+constexpr int CG_QCOPIES = 32;                 // private accumulation copies of the matvec result (power of two)
 constexpr int CG_THREADS = 256;
 constexpr int CG_MAX_GRID = 1024;              // partial slots (grid is capped by co-residency, far below this)
 
@@ -214,9 +215,12 @@ __global__ void __launch_bounds__(CG_THREADS) pcg_precond_kernel(Ctx ctx, double
 // into shared memory) and serve both halves of the product: t_o = W_o^T v_c per observation, a_p = sum over the track
 // (in track order), s_p = V'^-1 a_p per landmark, then q_c -= W_o s_p per observation (fp64 reductions into the
 // L2-resident 6 Nc vector).
-__global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ q) {
+__global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp) {
     const LMState *st = ctx.state;
     CG_GUARD(st);
+    // the reductions go to one of CG_QCOPIES private copies of the vector (by CTA): when landmarks that are neighbours in
+    // index share cameras, concurrent CTAs would otherwise serialise on the same few addresses
+    double *__restrict__ q = qp + (size_t)(blockIdx.x & (CG_QCOPIES - 1)) * ctx.n;
     extern __shared__ __align__(16) double tsm[];
     double *sW = tsm;                              // [cap][18]
     double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]
@@ -267,6 +271,18 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         for (int a = 0; a < 6; ++a)
             atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
     }
+}
+
+// out = sum of the private copies (fixed order), copies zeroed for the next product
+__global__ void pcg_fold_kernel(Ctx ctx, double *__restrict__ qp, double *__restrict__ out) {
+    const LMState *st = ctx.state;
+    CG_GUARD(st);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ctx.n) return;
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < CG_QCOPIES; ++k) { t += qp[(size_t)k * ctx.n + i]; qp[(size_t)k * ctx.n + i] = 0.0; }
+    out[i] = t;
 }
 
 // out[i] = in[i] + ((U + D^2) v)[i]  helper (per camera row)
@@ -399,7 +415,8 @@ void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s) {      // precondition + 
     double *part = ctx.cg_part;
     void *args[] = {&c, &part};
     cudaLaunchCooperativeKernel((const void *)pcg_precond_kernel, dim3(cg_grid(ctx, (const void *)pcg_precond_kernel)), dim3(CG_THREADS), args, 0, s);
-    if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_q);
+    if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_qp);
+    pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_q);
 }
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
     Ctx c = ctx;
@@ -408,8 +425,8 @@ void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
     cudaLaunchCooperativeKernel((const void *)pcg_update_kernel, dim3(cg_grid(ctx, (const void *)pcg_update_kernel)), dim3(CG_THREADS), args, 0, s);
 }
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part of S x into cg_z
-    cudaMemsetAsync(ctx.cg_z, 0, sizeof(double) * ctx.n, s);
-    if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_z);
+    if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_qp);
+    pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_z);
 }
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<1, 1024, 0, s>>>(ctx); }
 void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<1, 1024, 0, s>>>(ctx); }

@@ -136,6 +136,7 @@ struct Ctx {
     // PCG work vectors (n each) and block-Jacobi preconditioner
     double *cg_r, *cg_p, *cg_z, *cg_q, *cg_x, *Minv, *tp;
     double *cg_part;         // [1024] per-CTA partials of the cooperative CG kernels
+    double *cg_qp;           // [32][n] private accumulation copies of the matvec (all zero between products)
     // control
     LMState *state;
     ba_iteration *iters;     // [max_num_iterations + 2]
