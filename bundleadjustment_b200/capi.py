@@ -169,13 +169,18 @@ class Solver:
         _check(lib.ba_get_reduced_system_stats(self._h, _ptr(out)), "ba_get_reduced_system_stats")
         return {"n": int(out[0]), "filled_tiles": int(out[1]), "lower_tiles": int(out[2]), "flops": float(out[3])}
 
-    def cameras(self) -> np.ndarray:
-        out = np.zeros((self.shape[0], 6))
+    def cameras(self, out: np.ndarray | None = None) -> np.ndarray:
+        """out (optional): a C-contiguous float64 [Nc, 6] destination, e.g. page-locked memory."""
+        if out is None:
+            out = np.zeros((self.shape[0], 6))
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape == (self.shape[0], 6)
         _check(lib.ba_get_cameras(self._h, _ptr(out)), "ba_get_cameras")
         return out
 
-    def points(self) -> np.ndarray:
-        out = np.zeros((self.shape[1], 3))
+    def points(self, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.zeros((self.shape[1], 3))
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape == (self.shape[1], 3)
         _check(lib.ba_get_points(self._h, _ptr(out)), "ba_get_points")
         return out
 
