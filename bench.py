@@ -36,9 +36,14 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
-def load_workload(name: str, scale: float = 1.0):
+def load_workload(name: str, scale: float = 1.0, path: str | None = None):
     from bundleadjustment_b200 import synthetic as syn
     t = time.time()
+    if path:                                  # a BAL text file (*.txt) or a flat binary dump (bundleadjustment_b200/problem_io.py)
+        from bundleadjustment_b200 import problem_io as pio
+        pb = (pio.read_bal(path) if path.endswith(".txt") else pio.read_binary(path))[0]
+        log(f"[bench] problem {path}: cams={pb.shape[0]} landmarks={pb.shape[1]} obs={pb.shape[2]} (read in {time.time() - t:.1f}s)")
+        return None, pb
     sc = syn.config(name, scale=scale)
     pb = syn.flatten(sc)
     log(f"[bench] workload {name}: cams={pb.shape[0]} landmarks={pb.shape[1]} obs={pb.shape[2]} (generated in {time.time() - t:.1f}s, seed {sc.seed})")
@@ -146,7 +151,7 @@ def main_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    _, pb = load_workload(args.workload, args.scale)
+    _, pb = load_workload(args.workload, args.scale, args.problem)
     threads = os.cpu_count() or 1
     for _ in range(min(args.warmup, 1)):           # one warm-up sample is enough to page the problem in
         run_cpu(pb, args.solver, 1, threads)
@@ -158,7 +163,7 @@ def main_reference(args):
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": tot_t / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f64", "data": "file" if args.problem else "synthetic",
         "config": {"workload": args.workload, "cams": int(pb.shape[0]), "landmarks": int(pb.shape[1]), "observations": int(pb.shape[2]),
                    "linear_solver": args.solver, "lm_iters_per_step": 1,
                    "note": "restated Ceres-path CPU baseline (oracle port), not Ceres itself; each step = 1 LM iteration sample"},
@@ -195,7 +200,7 @@ def main_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
 
-    _, pb_full = load_workload(args.workload, args.scale)
+    _, pb_full = load_workload(args.workload, args.scale, args.problem)
     Nc, Np, No = pb_full.shape
     kw = dict(max_num_iterations=args.lm_iters)
     if args.solver == "pcg":
@@ -355,7 +360,7 @@ def main_ours(args):
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
+        "dtype": "f64", "data": "file" if args.problem else "synthetic",
         "config": {"workload": args.workload if args.scale == 1.0 else f"{args.workload} x{args.scale}", "cams": Nc, "landmarks": Np, "observations": No, "linear_solver": args.solver,
                    "lm_iters_per_step": n_it / args.steps, "max_num_iterations": args.lm_iters, "huber": True,
                    "parallelism": f"landmark-sharded x{world}" if world > 1 else "single GPU",
@@ -384,6 +389,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="K4", choices=["K1", "K2", "K4", "K5"])
+    ap.add_argument("--problem", default=None, help="read the problem from a BAL text file (*.txt) or a flat binary dump instead of generating --workload")
     ap.add_argument("--solver", default="dense", choices=["dense", "pcg"])
     ap.add_argument("--lm-iters", type=int, default=10)
     ap.add_argument("--cg-tight", action="store_true", help="PCG run to |r| <= 1e-10 |b| (exact-step trajectory)")
@@ -393,6 +399,8 @@ def main():
     ap.add_argument("--no-dense-chol", action="store_true", help="skip the dense-matrix run of the Cholesky kernel (roofline_dense_cholesky)")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (profiling runs only; recorded in config)")
     args = ap.parse_args()
+    if args.problem:
+        args.workload = "file:" + os.path.basename(args.problem)
     if args.impl == "reference":
         return main_reference(args)
     return main_ours(args)

@@ -89,7 +89,9 @@ private:
 
 class Frame : public std::enable_shared_from_this<Frame> {
 public:
-    Frame(Matrix4f pose, Matrix3f intrinsics, int frameID) : m_frameID(frameID), m_intrinsics(intrinsics), m_pose(pose) {}
+    Frame(Matrix4f pose, Matrix3f intrinsics, int frameID, double timeStamp = 0.0)
+        : m_frameID(frameID), m_intrinsics(intrinsics), m_pose(pose), m_timeStamp(timeStamp) {}
+    double getTimeStamp() { return m_timeStamp; }                                   // Frame.cpp:197-201
     void setPose(Matrix4f pose) { std::lock_guard<std::mutex> l(m_frameMutex); m_pose = pose; m_validPose = true; }
     Matrix4f getPose() { std::lock_guard<std::mutex> l(m_frameMutex); return m_pose; }
     Matrix3f getIntrinsics() { std::lock_guard<std::mutex> l(m_frameMutex); return m_intrinsics; }
@@ -130,6 +132,7 @@ private:
     std::vector<std::shared_ptr<MapPoint>> m_mapPoints;
     std::vector<bool> m_outlier;
     Matrix4f m_pose;
+    double m_timeStamp = 0.0;
     bool m_validPose = false;
     std::vector<std::shared_ptr<Frame>> m_orderedCovisibilityFrames;
     std::mutex m_frameMutex;

@@ -116,3 +116,63 @@ extern "C" int ba_host_shim_run(int mode, int Nc, const float *pose, const float
     dump(g, kp_ptr, pose_out, pt_out, outlier_out, kp_point_out, pt_alive);
     return status;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// ProblemIO: format conversions, the trajectory writer through the SceneMap template, and the
+// load -> solve -> checkpoint flow.  `err` receives a NUL-terminated message (cap bytes).
+// ---------------------------------------------------------------------------------------------------------------
+#include "../../bundleadjustment_b200/host/ProblemIO.h"
+#include "../../include/ba_b200.h"
+
+namespace {
+int report(bool ok, const std::string &msg, char *err, int cap) {
+    if (err && cap > 0) { std::strncpy(err, ok ? "" : msg.c_str(), (size_t)cap - 1); err[cap - 1] = '\0'; }
+    return ok ? 0 : 1;
+}
+}  // namespace
+
+// kind: 0 = BAL text, 1 = flat binary
+extern "C" int ba_host_shim_convert(const char *src, int src_kind, const char *dst, int dst_kind, int fix_first, int32_t *shape /*[4]*/,
+                                    char *err, int cap) {
+    ba_io::FlatProblem p;
+    std::string msg;
+    int distorted = 0;
+    bool ok = src_kind == 0 ? ba_io::readBAL(src, p, &msg, fix_first != 0, &distorted) : ba_io::readBinary(src, p, &msg);
+    if (ok) ok = dst_kind == 0 ? ba_io::writeBAL(dst, p, &msg) : ba_io::writeBinary(dst, p, &msg);
+    if (ok && shape) { shape[0] = p.numCameras(); shape[1] = p.numPoints(); shape[2] = p.numObservations(); shape[3] = distorted; }
+    return report(ok, msg, err, cap);
+}
+
+extern "C" int ba_host_shim_trajectory(const char *prefix, int n, const int32_t *frame_id, const double *ts, const float *pose,
+                                       char *err, int cap) {
+    SceneMap map;
+    for (int f = 0; f < n; ++f) {
+        Matrix4f P;
+        for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) P(r, c) = pose[16 * f + 4 * r + c];
+        map.addKeyFrame(std::make_shared<Frame>(P, Matrix3f::Identity(), frame_id[f], ts[f]));
+    }
+    std::string msg;
+    return report(ba_io::writeTrajectoryTUM(prefix, &map, &msg), msg, err, cap);
+}
+
+// readBinary -> ba_set_problem -> ba_solve -> fetch -> writeBinary (checkpoint).  info = {initial, final cost, iterations, termination}
+extern "C" int ba_host_shim_solve_file(const char *src, const char *dst, int max_it, int linear_solver, double *info, char *err, int cap) {
+    ba_io::FlatProblem p;
+    std::string msg;
+    if (!ba_io::readBinary(src, p, &msg)) return report(false, msg, err, cap);
+    ba_options opt;
+    ba_default_options(&opt);
+    opt.max_num_iterations = max_it;
+    opt.linear_solver = linear_solver;
+    ba_handle *h = nullptr;
+    ba_summary sm;
+    int rc = ba_create(&opt, 0, &h);
+    if (rc == BA_OK) rc = ba_io::setProblem(h, p);
+    if (rc == BA_OK) rc = ba_solve(h, &sm);
+    if (rc == BA_OK) rc = ba_io::fetchParameters(h, p);
+    if (rc != BA_OK) msg = ba_last_error();
+    if (h) ba_destroy(h);
+    if (rc != BA_OK) return report(false, msg, err, cap);
+    info[0] = sm.initial_cost; info[1] = sm.final_cost; info[2] = sm.num_iterations; info[3] = sm.termination_type;
+    return report(ba_io::writeBinary(dst, p, &msg), msg, err, cap);
+}
