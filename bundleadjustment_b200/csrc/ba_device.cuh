@@ -95,6 +95,11 @@ __device__ __forceinline__ void bulk_store(void *gdst, const void *smem_src, uns
     asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
 }
 
+// the copy alone (no fence / commit / wait): for callers that batch several copies into one group and double buffer
+__device__ __forceinline__ void bulk_store_issue(void *gdst, const void *smem_src, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(smem_addr(smem_src)), "r"(bytes) : "memory");
+}
+
 // record k of a shared-memory tile of 18-double records as nine 16-byte loads (conflict free at the 144-byte stride)
 __device__ __forceinline__ void load_record18(const double *__restrict__ sW, int k, double (&w)[18]) {
     const double2 *src = reinterpret_cast<const double2 *>(sW + 18 * (size_t)k);
@@ -284,6 +289,10 @@ __device__ __forceinline__ void obs_linearize(const CamEntry *__restrict__ ce, i
     r[1] = pix[1] - (double)uv.y;
 }
 
+// L2 prefetch of a line the thread will read a few microseconds later (per-landmark rows of the tile kernels' second phase):
+// costs no registers, turns a DRAM round trip on the critical path of the CTA into an L2 hit
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];\n" ::"l"(p)); }
+
 // ---- reductions --------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -317,6 +326,21 @@ __device__ __forceinline__ double block_max(double v, double *smem) {
     v = (threadIdx.x < nw) ? smem[threadIdx.x] : 0.0;
     if (wid == 0) v = warp_max(v);
     return v;
+}
+
+// three sums and one max in ONE pass (fixed trees; results valid in thread 0).  smem: >= 4 * 32 doubles, not in use by
+// anyone else; one CTA barrier instead of eight.
+__device__ __forceinline__ void block_sum3_max(double &a, double &b, double &c, double &m, double *smem) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c); m = warp_max(m);
+    if (lane == 0) { smem[wid] = a; smem[32 + wid] = b; smem[64 + wid] = c; smem[96 + wid] = m; }
+    __syncthreads();
+    if (wid == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        a = lane < nw ? smem[lane] : 0.0; b = lane < nw ? smem[32 + lane] : 0.0;
+        c = lane < nw ? smem[64 + lane] : 0.0; m = lane < nw ? smem[96 + lane] : 0.0;
+        a = warp_sum(a); b = warp_sum(b); c = warp_sum(c); m = warp_max(m);
+    }
 }
 
 // symmetric 3x3 SPD inverse via Cholesky (InvertPSDMatrix).  m = {00,01,02,11,12,22}; returns false if not PD.

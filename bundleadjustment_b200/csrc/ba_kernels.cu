@@ -6,6 +6,8 @@
 // everything ceres::Solve (Optimizer.cpp:242) does with them per LM iteration.
 #include "ba_launch.h"
 
+#include <algorithm>
+
 namespace ba {
 
 #define DEV_STATE_GUARD(ctx)                 \
@@ -70,9 +72,9 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
 // -------------------------------------------------------------------------------------------------------------
 struct Tile { int p0, p1, o0, n; };
 __device__ __forceinline__ Tile tile_of(const Ctx &ctx, int b) {
+    const int4 v = ctx.blk_info[b];
     Tile t;
-    t.p0 = ctx.blk_first_pt[b]; t.p1 = ctx.blk_first_pt[b + 1];
-    t.o0 = ctx.pt_ptr[t.p0]; t.n = ctx.pt_ptr[t.p1] - t.o0;
+    t.p0 = v.x; t.p1 = v.y; t.o0 = v.z; t.n = v.w;
     return t;
 }
 // n records of 18 doubles between global W (at observation o0) and shared memory: one TMA bulk copy each way.
@@ -97,10 +99,14 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
     extern __shared__ __align__(16) double tsm[];
     double *sW = tsm;                              // [cap][18]
     double *sV = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][9]: Jp^T Jp (6) | Jp^T r (3)
-    __shared__ double red[32];
+    __shared__ double red[128];
     const Tile t = tile_of(ctx, blockIdx.x);
     const double *ptx = ctx.pt[st->cur];
     double cost = 0.0, gsq = 0.0, gmax = 0.0, xsq = 0.0;
+    // second phase (thread per landmark): its track bounds are fetched now, off the critical path
+    const int p_mine = t.p0 + threadIdx.x;
+    int lo_mine = 0, hi_mine = 0;
+    if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0; }
     for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
         const int o = t.o0 + k;
         const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
@@ -147,8 +153,8 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
     }
     __syncthreads();
     tile_store_W(ctx.W, t.o0, t.n, sW);            // TMA store by thread 0; the others go on with the per-landmark sums
-    for (int p = t.p0 + threadIdx.x; p < t.p1; p += blockDim.x) {
-        const int lo = ctx.pt_ptr[p] - t.o0, hi = ctx.pt_ptr[p + 1] - t.o0;
+    for (int p = p_mine; p < t.p1; p += blockDim.x) {
+        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - t.o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - t.o0;
         double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
         for (int k = lo; k < hi; ++k) {                     // track order: the same sum order as a serial walk
             const double *v = sV + 9 * (size_t)k;
@@ -174,13 +180,10 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
         double *bp = ctx.bp + 3 * (size_t)p;
         bp[0] = b[0]; bp[1] = b[1]; bp[2] = b[2];
     }
-    cost = block_sum(cost, red);
-    gsq = block_sum(gsq, red);
-    xsq = block_sum(xsq, red);
-    gmax = block_max(gmax, red);
+    block_sum3_max(cost, gsq, xsq, gmax, red);
     if (threadIdx.x == 0) {
-        double *pp = ctx.part + 4 * (size_t)blockIdx.x;
-        pp[0] = cost; pp[1] = gsq; pp[2] = xsq; pp[3] = gmax;
+        double4 *pp = reinterpret_cast<double4 *>(ctx.part + 4 * (size_t)blockIdx.x);
+        *pp = make_double4(cost, gsq, xsq, gmax);
     }
 }
 
@@ -506,14 +509,23 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     extern __shared__ __align__(16) double tsm[];
     double *sW = tsm;                              // [cap][18]
     double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]: W_o^T y_c
-    __shared__ double red[32];
+    __shared__ double red[128];
     const Tile t = tile_of(ctx, blockIdx.x);
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
     __shared__ unsigned long long wbar;
+    const int c_first = threadIdx.x < t.n ? ctx.pm_cam[t.o0 + threadIdx.x] : 0;   // in flight across the barrier below
+    // second phase (thread per landmark): track bounds now, the landmark's rows on their way into L2
+    const int p_mine = t.p0 + threadIdx.x;
+    int lo_mine = 0, hi_mine = 0;
+    if (p_mine < t.p1) {
+        lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0;
+        prefetch_l2(ctx.Vinv + 6 * (size_t)p_mine); prefetch_l2(ctx.V + 6 * (size_t)p_mine);
+        prefetch_l2(ctx.bp + 3 * (size_t)p_mine); prefetch_l2(ptx + 3 * (size_t)p_mine); prefetch_l2(ctx.scale_pt + 3 * (size_t)p_mine);
+    }
     tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
     for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
-        const int c = ctx.pm_cam[t.o0 + k];
+        const int c = k == (int)threadIdx.x ? c_first : ctx.pm_cam[t.o0 + k];
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
             double y[6];
@@ -528,8 +540,8 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     }
     __syncthreads();
     double dxsq = 0, yb = 0, yhy = 0;
-    for (int p = t.p0 + threadIdx.x; p < t.p1; p += blockDim.x) {
-        const int lo = ctx.pt_ptr[p] - t.o0, hi = ctx.pt_ptr[p + 1] - t.o0;
+    for (int p = p_mine; p < t.p1; p += blockDim.x) {
+        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - t.o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - t.o0;
         const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         if (hi > lo) {
             double a3[3] = {0, 0, 0};
@@ -553,10 +565,11 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
             ptc[3 * (size_t)p] = X[0]; ptc[3 * (size_t)p + 1] = X[1]; ptc[3 * (size_t)p + 2] = X[2];
         }
     }
-    dxsq = block_sum(dxsq, red); yb = block_sum(yb, red); yhy = block_sum(yhy, red);
+    double unused = 0.0;
+    block_sum3_max(dxsq, yb, yhy, unused, red);
     if (threadIdx.x == 0) {
-        double *pp = ctx.part + 4 * (size_t)blockIdx.x;
-        pp[0] = dxsq; pp[1] = yb; pp[2] = yhy; pp[3] = 0.0;
+        double4 *pp = reinterpret_cast<double4 *>(ctx.part + 4 * (size_t)blockIdx.x);
+        *pp = make_double4(dxsq, yb, yhy, 0.0);
     }
 }
 
@@ -772,34 +785,72 @@ __global__ void lm_init_state_kernel(Ctx ctx) {
 // -------------------------------------------------------------------------------------------------------------
 // Materialised evaluation (ba_evaluate): residual + both Jacobian blocks per observation, robustified, unscaled.
 // 176 B / observation of output; this is the "residual+Jacobian obs/sec" kernel.
+//
+// Persistent, WARP-granular: a warp owns runs of 32 consecutive observations.  Every lane evaluates one observation and
+// parks its record in the warp's shared-memory stage (16-byte stores); the three output runs of the warp (res 512 B,
+// J_cam 3072 B, J_pt 1536 B, each contiguous in global memory) then leave as TMA bulk stores issued by lane 0.  The stage
+// is double buffered (wait_group.read 1 before a buffer is rewritten), so the stores of run i drain while the warp gathers
+// and computes run i + 1, whose indices were prefetched one run ahead.  No CTA barrier anywhere: warps drift freely.
 // -------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) evaluate_materialize_kernel(Ctx ctx, double *res, double *jc, double *jp, double *cost_part) {
-    __shared__ double red[32];
+constexpr int EV_WARPS = 4;
+struct __align__(128) EvStage { double jc[32 * 12]; double jp[32 * 6]; double res[32 * 2]; };   // 5120 B
+static_assert(sizeof(EvStage) == 5120, "EvStage layout");
+
+__global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(Ctx ctx, double *res, double *jc, double *jp, double *cost_part) {
+    __shared__ EvStage stage[EV_WARPS][2];
     const LMState *st = ctx.state;
     const double *ptx = ctx.pt[st->cur];
-    const int o = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int gw = blockIdx.x * EV_WARPS + warp, nw = gridDim.x * EV_WARPS;
+    const int n_runs = (ctx.No + 31) >> 5;
     double cost = 0.0;
-    if (o < ctx.No) {
-        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
-        const int kind = ctx.cam_kind[c];
-        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
-        double r[2], Jc[12], Jp[6];
-        obs_linearize<true, true>(ctx.tab_x + c, kind, X, ctx.pm_uv[o], r, Jc, Jp);
-        double rho0;
-        const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
-        const double sr = sqrt(rho1);
-        cost = 0.5 * rho0;
-        double2 *r2 = reinterpret_cast<double2 *>(res) + o;
-        *r2 = make_double2(r[0] * sr, r[1] * sr);
-        double2 *c2 = reinterpret_cast<double2 *>(jc + 12 * (size_t)o);
+    int c_n = 0, p_n = 0;
+    float2 uv_n = make_float2(0.f, 0.f);
+    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = ctx.pm_cam[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
+    int it = 0;
+    for (int run = gw; run < n_runs; run += nw, ++it) {
+        const int o0 = run * 32, o = o0 + lane;
+        const int n = min(32, ctx.No - o0);
+        const int c = c_n, p = p_n;
+        const float2 uv = uv_n;
+        {   // indices of the warp's next run: in flight during this run's gathers and arithmetic
+            const int on = o + nw * 32;
+            if (run + nw < n_runs && on < ctx.No) { c_n = ctx.pm_cam[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
+        }
+        double r[2] = {0, 0}, Jc[12], Jp[6], sr = 0.0;
+        if (lane < n) {
+            const int kind = ctx.cam_kind[c];
+            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+            obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
+            double rho0;
+            const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+            sr = sqrt(rho1);
+            cost += 0.5 * rho0;
+        }
+        EvStage &sg = stage[warp][it & 1];
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");    // the stores of run it - 2 have read sg
+        __syncwarp();
+        if (lane < n) {
+            double2 *c2 = reinterpret_cast<double2 *>(sg.jc + 12 * lane);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) c2[k] = make_double2(Jc[2 * k] * sr, Jc[2 * k + 1] * sr);
-        double2 *p2 = reinterpret_cast<double2 *>(jp + 6 * (size_t)o);
+            for (int k = 0; k < 6; ++k) c2[k] = make_double2(Jc[2 * k] * sr, Jc[2 * k + 1] * sr);
+            double2 *p2 = reinterpret_cast<double2 *>(sg.jp + 6 * lane);
 #pragma unroll
-        for (int k = 0; k < 3; ++k) p2[k] = make_double2(Jp[2 * k] * sr, Jp[2 * k + 1] * sr);
+            for (int k = 0; k < 3; ++k) p2[k] = make_double2(Jp[2 * k] * sr, Jp[2 * k + 1] * sr);
+            reinterpret_cast<double2 *>(sg.res)[lane] = make_double2(r[0] * sr, r[1] * sr);
+        }
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");                     // writers: generic -> async proxy
+        __syncwarp();
+        if (lane == 0) {
+            bulk_store_issue(jc + 12 * (size_t)o0, sg.jc, 96u * (unsigned)n);
+            bulk_store_issue(jp + 6 * (size_t)o0, sg.jp, 48u * (unsigned)n);
+            bulk_store_issue(res + 2 * (size_t)o0, sg.res, 16u * (unsigned)n);
+            asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+        }
     }
-    cost = block_sum(cost, red);
-    if (threadIdx.x == 0) cost_part[blockIdx.x] = cost;
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");        // shared memory stays valid until read
+    cost = warp_sum(cost);
+    if (lane == 0) cost_part[gw] = cost;
 }
 
 // =============================================================================================================
@@ -892,8 +943,21 @@ void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s) {
     reduce_step_partials_kernel<<<1, 1024, 0, s>>>(ctx, cost_part, nb);
 }
 
-void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s) {
-    if (ctx.No > 0) evaluate_materialize_kernel<<<cdiv(ctx.No, 128), 128, 0, s>>>(ctx, res, jc, jp, cost_part);
+// returns the number of cost partials written (one per warp)
+int launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s) {
+    if (ctx.No <= 0) return 0;
+    const int n_runs = cdiv(ctx.No, 32);
+    static int ctas_per_sm = 0, sms = 0;
+    if (!ctas_per_sm) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, evaluate_materialize_kernel, EV_WARPS * 32, 0);
+        if (ctas_per_sm < 1) ctas_per_sm = 1;
+    }
+    const int grid = std::min(cdiv(n_runs, EV_WARPS), sms * ctas_per_sm);
+    evaluate_materialize_kernel<<<grid, EV_WARPS * 32, 0, s>>>(ctx, res, jc, jp, cost_part);
+    return grid * EV_WARPS;
 }
 
 } // namespace ba

@@ -25,7 +25,8 @@ void launch_backsub(const Ctx &ctx, cudaStream_t s);
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
 int tiles_init(const Ctx &ctx);                          // per-problem dynamic shared memory opt-in of the tile kernels
 int pcg_tiles_init(const Ctx &ctx);
-void launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s);
+int launch_materialize(const Ctx &ctx, double *res, double *jc, double *jp, double *cost_part, cudaStream_t s);   // returns the number of cost partials
+
 
 // ba_prep.cu -- device-side index building (ba_set_problem)
 struct PrepScratch {              // grow-only temporary storage
@@ -48,7 +49,7 @@ struct PrepOut {
     // camera-major
     float2 *cm_uv; int *cm_pt, *cm_obs, *chunk_cam, *chunk_beg, *chunk_end;
     // landmark blocks of the tile kernels
-    int *blk_first_pt; int n_blocks = 0, max_block_obs = 0;
+    int *blk_first_pt; int4 *blk_info; int n_blocks = 0, max_block_obs = 0;
     int *flags;                            // device [4]
     int *h_flags;                          // pinned host [8]: bad index (1-based), unsorted, Ncm, n_chunks, max block obs
     int Ncm = 0, n_chunks = 0;

@@ -224,17 +224,21 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     extern __shared__ __align__(16) double tsm[];
     double *sW = tsm;                              // [cap][18]
     double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]
-    const int b = blockIdx.x;
-    const int p0 = ctx.blk_first_pt[b], p1 = ctx.blk_first_pt[b + 1];
-    const int o0 = ctx.pt_ptr[p0], n = ctx.pt_ptr[p1] - o0;
+    const int4 bi = ctx.blk_info[blockIdx.x];
+    const int p0 = bi.x, p1 = bi.y, o0 = bi.z, n = bi.w;
     if (n == 0) return;
+    const int c_first = threadIdx.x < n ? ctx.pm_cam[o0 + threadIdx.x] : 0;      // in flight across the barrier below
+    // second phase (thread per landmark): track bounds now, V'^-1 on its way into L2
+    const int p_mine = p0 + threadIdx.x;
+    int lo_mine = 0, hi_mine = 0;
+    if (p_mine < p1) { lo_mine = ctx.pt_ptr[p_mine] - o0; hi_mine = ctx.pt_ptr[p_mine + 1] - o0; prefetch_l2(ctx.Vinv + 6 * (size_t)p_mine); }
     // the block's W records: one TMA bulk copy (thread 0) that streams in while the threads gather their camera entries of v
     __shared__ unsigned long long wbar;
     if (threadIdx.x == 0) mbar_init(&wbar, 1);
     __syncthreads();
     if (threadIdx.x == 0) bulk_load(sW, ctx.W + 18 * (size_t)o0, 144u * (unsigned)n, &wbar);
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        const int c = ctx.pm_cam[o0 + k];
+        const int c = k == (int)threadIdx.x ? c_first : ctx.pm_cam[o0 + k];
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
             double x[6];
@@ -248,8 +252,8 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
     }
     __syncthreads();
-    for (int p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
-        const int lo = ctx.pt_ptr[p] - o0, hi = ctx.pt_ptr[p + 1] - o0;
+    for (int p = p_mine; p < p1; p += blockDim.x) {
+        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - o0;
         if (hi <= lo) continue;
         double a3[3] = {0, 0, 0};
         for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     }
     __syncthreads();
     for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        const int c = ctx.pm_cam[o0 + k];
+        const int c = k == (int)threadIdx.x ? c_first : ctx.pm_cam[o0 + k];
         if (ctx.cam_kind[c] != CAM_FREE) continue;
         const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
         mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)

@@ -95,10 +95,16 @@ __global__ void prep_blocks_kernel(int n_blocks, int Np, const int *__restrict__
     }
     first_pt[b] = lo;
 }
-__global__ void prep_blocks_max_kernel(int n_blocks, const int *__restrict__ pt_ptr, const int *__restrict__ first_pt, int *__restrict__ mx) {
+// + the block's record {first landmark, end landmark, first observation, observation count}: ONE 16-byte load at the top of a
+// tile kernel instead of two dependent pairs of loads
+__global__ void prep_blocks_max_kernel(int n_blocks, const int *__restrict__ pt_ptr, const int *__restrict__ first_pt, int *__restrict__ mx,
+                                       int4 *__restrict__ info) {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_blocks) return;
-    atomicMax(mx, pt_ptr[first_pt[b + 1]] - pt_ptr[first_pt[b]]);
+    const int p0 = first_pt[b], p1 = first_pt[b + 1];
+    const int o0 = pt_ptr[p0], n = pt_ptr[p1] - o0;
+    info[b] = make_int4(p0, p1, o0, n);
+    atomicMax(mx, n);
 }
 
 __global__ void prep_chunks_kernel(int Nc, const int *__restrict__ cam_ptr, const int *__restrict__ cam_chunk_ptr,
@@ -261,7 +267,7 @@ int prep_blocks(const PrepIn &in, PrepOut &out, cudaStream_t s) {
     out.n_blocks = in.No / TILE_WIN + 1;
     PCU(cudaMemsetAsync(out.flags + 2, 0, sizeof(int), s));
     prep_blocks_kernel<<<cdivp(out.n_blocks + 1, 256), 256, 0, s>>>(out.n_blocks, in.Np, out.pt_ptr, out.blk_first_pt);
-    prep_blocks_max_kernel<<<cdivp(out.n_blocks, 256), 256, 0, s>>>(out.n_blocks, out.pt_ptr, out.blk_first_pt, out.flags + 2);
+    prep_blocks_max_kernel<<<cdivp(out.n_blocks, 256), 256, 0, s>>>(out.n_blocks, out.pt_ptr, out.blk_first_pt, out.flags + 2, out.blk_info);
     PCU(cudaMemcpyAsync(out.h_flags + 4, out.flags + 2, sizeof(int), cudaMemcpyDeviceToHost, s));
     PCU(cudaStreamSynchronize(s));
     out.max_block_obs = out.h_flags[4];

@@ -95,6 +95,7 @@ struct Ctx {
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
+    const int4 *blk_info;    // [n_blocks] {first landmark, end landmark, first observation, observation count}
     int n_blocks, tile_cap;
     // camera-major copy
     const float2 *cm_uv;
