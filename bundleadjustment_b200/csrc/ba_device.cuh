@@ -330,17 +330,55 @@ __device__ __forceinline__ double block_max(double v, double *smem) {
 
 // three sums and one max in ONE pass (fixed trees; results valid in thread 0).  smem: >= 4 * 32 doubles, not in use by
 // anyone else; one CTA barrier instead of eight.
-__device__ __forceinline__ void block_sum3_max(double &a, double &b, double &c, double &m, double *smem) {
+// MAX4: the fourth value is a maximum of non-negative numbers (else a fourth sum).
+template <bool MAX4>
+__device__ __forceinline__ void block_red4(double &a, double &b, double &c, double &m, double *smem) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c); m = warp_max(m);
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c); m = MAX4 ? warp_max(m) : warp_sum(m);
     if (lane == 0) { smem[wid] = a; smem[32 + wid] = b; smem[64 + wid] = c; smem[96 + wid] = m; }
     __syncthreads();
     if (wid == 0) {
         const int nw = (blockDim.x + 31) >> 5;
         a = lane < nw ? smem[lane] : 0.0; b = lane < nw ? smem[32 + lane] : 0.0;
         c = lane < nw ? smem[64 + lane] : 0.0; m = lane < nw ? smem[96 + lane] : 0.0;
-        a = warp_sum(a); b = warp_sum(b); c = warp_sum(c); m = warp_max(m);
+        a = warp_sum(a); b = warp_sum(b); c = warp_sum(c); m = MAX4 ? warp_max(m) : warp_sum(m);
     }
+}
+__device__ __forceinline__ void block_sum3_max(double &a, double &b, double &c, double &m, double *smem) { block_red4<true>(a, b, c, m, smem); }
+
+// ---- multi-CTA reductions with a "last CTA sums" tail (no second launch, no cooperative launch) ---------------------------
+// Every CTA publishes its four block-reduced values, the last one to arrive (atomic ticket) adds the published partials in
+// CTA order with the same fixed tree and returns true with the totals valid in thread 0.  Deterministic for a given grid.
+// part: [gridDim.x] double4 slots owned by this kernel; count: zero before the launch, reset by the last CTA.
+constexpr int RED_MAX_GRID = 1024;
+template <bool MAX4>
+__device__ __forceinline__ bool grid_red4(double &a, double &b, double &c, double &m, double *part, unsigned *count, double *smem) {
+    block_red4<MAX4>(a, b, c, m, smem);
+    if (gridDim.x == 1) return true;
+    __shared__ int s_last;
+    if (threadIdx.x == 0) {
+        reinterpret_cast<double4 *>(part)[blockIdx.x] = make_double4(a, b, c, m);
+        __threadfence();
+        const unsigned t = atomicAdd(count, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return false;
+    __threadfence();
+    a = b = c = m = 0.0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) {
+        const double2 v0 = __ldcg(reinterpret_cast<const double2 *>(part) + 2 * i), v1 = __ldcg(reinterpret_cast<const double2 *>(part) + 2 * i + 1);
+        a += v0.x; b += v0.y; c += v1.x; m = MAX4 ? fmax(m, v1.y) : m + v1.y;
+    }
+    block_red4<MAX4>(a, b, c, m, smem);
+    if (threadIdx.x == 0) *count = 0;
+    return true;
+}
+__device__ __forceinline__ bool grid_sum3_max(double &a, double &b, double &c, double &m, double *part, unsigned *count, double *smem) {
+    return grid_red4<true>(a, b, c, m, part, count, smem);
+}
+__device__ __forceinline__ bool grid_sum4(double &a, double &b, double &c, double &d, double *part, unsigned *count, double *smem) {
+    return grid_red4<false>(a, b, c, d, part, count, smem);
 }
 
 // symmetric 3x3 SPD inverse via Cholesky (InvertPSDMatrix).  m = {00,01,02,11,12,22}; returns false if not PD.

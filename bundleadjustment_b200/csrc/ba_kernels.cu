@@ -107,11 +107,13 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
     const int p_mine = t.p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
     if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0; }
-    for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
-        const int o = t.o0 + k;
-        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+    for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
+        const int o = t.o0 + i;
+        int c, p, k;                               // k = the observation's landmark-major slot in the tile
+        float2 uv;
+        if (ctx.order_mask & ORDER_LINEARIZE) { c = ctx.pr_cam[o]; p = ctx.pr_pt[o]; uv = ctx.pr_uv[o]; k = ctx.pr_k[o]; }   // neighbouring lanes share cameras
+        else { c = ctx.pm_cam[o]; p = ctx.pm_pt[o]; uv = ctx.pm_uv[o]; k = i; }
         const int kind = ctx.cam_kind[c];
-        const float2 uv = ctx.pm_uv[o];
         const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
         double r[2], Jc[12], Jp[6], sc[6];
@@ -254,37 +256,38 @@ __global__ void cam_reduce_kernel(Ctx ctx, int force) {
     } else ctx.bc_loc[6 * (size_t)c + (k - 21)] = acc;
 }
 
-// landmark-side partials -> sums / maxs (single block, fixed order)
-__global__ void __launch_bounds__(1024) reduce_lin_partials_kernel(Ctx ctx, int force) {
+// landmark-side partials -> sums / maxs (multi-CTA, fixed order)
+__global__ void __launch_bounds__(RED_THREADS) reduce_lin_partials_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
-    __shared__ double red[32];
+    __shared__ double red[128];
     double cost = 0, gsq = 0, xsq = 0, gmax = 0;
-    for (int i = threadIdx.x; i < ctx.n_part; i += blockDim.x) {
-        const double *pp = ctx.part + 4 * (size_t)i;
-        cost += pp[0]; gsq += pp[1]; xsq += pp[2]; gmax = fmax(gmax, pp[3]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n_part; i += gridDim.x * blockDim.x) {
+        const double4 pp = reinterpret_cast<const double4 *>(ctx.part)[i];
+        cost += pp.x; gsq += pp.y; xsq += pp.z; gmax = fmax(gmax, pp.w);
     }
-    cost = block_sum(cost, red); gsq = block_sum(gsq, red); xsq = block_sum(xsq, red); gmax = block_max(gmax, red);
+    if (!grid_sum3_max(cost, gsq, xsq, gmax, red_slot(ctx, RED_LIN), ctx.red_count + RED_LIN, red)) return;
     if (threadIdx.x == 0) {
         ctx.sums_loc[SUM_LIN_COST] = cost; ctx.sums_loc[SUM_LIN_GSQ] = gsq; ctx.sums_loc[SUM_LIN_XSQ] = xsq;
         ctx.maxs_loc[MAX_LIN_G] = gmax;
     }
 }
 
-// camera-side gradient / parameter norms from the (all-reduced) b_c; single block
-__global__ void __launch_bounds__(1024) cam_norms_kernel(Ctx ctx, int force) {
+// camera-side gradient / parameter norms from the (all-reduced) b_c; multi-CTA
+__global__ void __launch_bounds__(RED_THREADS) cam_norms_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
-    __shared__ double red[32];
+    __shared__ double red[128];
     const double *x = ctx.cam[st->cur];
     double gsq = 0, xsq = 0, gmax = 0;
-    for (int i = threadIdx.x; i < 6 * ctx.Nc; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 6 * ctx.Nc; i += gridDim.x * blockDim.x) {
         if (ctx.cam_kind[i / 6] != CAM_FREE) continue;
         const double g = ctx.bc[i] / ctx.scale_cam[i];
         const double d = x[i] - (x[i] + (-g));
         gsq += d * d; gmax = fmax(gmax, fabs(d)); xsq += x[i] * x[i];
     }
-    gsq = block_sum(gsq, red); xsq = block_sum(xsq, red); gmax = block_max(gmax, red);
+    double unused = 0.0;
+    if (!grid_sum3_max(gsq, xsq, unused, gmax, red_slot(ctx, RED_CAM_NORMS), ctx.red_count + RED_CAM_NORMS, red)) return;
     if (threadIdx.x == 0) { ctx.camsums[CS_GSQ] = gsq; ctx.camsums[CS_GMAX] = gmax; ctx.camsums[CS_XSQ] = xsq; }
 }
 
@@ -514,7 +517,11 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
     __shared__ unsigned long long wbar;
-    const int c_first = threadIdx.x < t.n ? ctx.pm_cam[t.o0 + threadIdx.x] : 0;   // in flight across the barrier below
+    // processing order (neighbouring lanes share cameras); the first pass' entry is in flight across the barrier below
+    const bool ordered = ctx.order_mask & ORDER_BACKSUB;
+    const int *obs_cam = ordered ? ctx.pr_cam : ctx.pm_cam;
+    int c_first = 0, k_first = threadIdx.x;
+    if (threadIdx.x < t.n) { c_first = obs_cam[t.o0 + threadIdx.x]; if (ordered) k_first = ctx.pr_k[t.o0 + threadIdx.x]; }
     // second phase (thread per landmark): track bounds now, the landmark's rows on their way into L2
     const int p_mine = t.p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
@@ -524,8 +531,9 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
         prefetch_l2(ctx.bp + 3 * (size_t)p_mine); prefetch_l2(ptx + 3 * (size_t)p_mine); prefetch_l2(ctx.scale_pt + 3 * (size_t)p_mine);
     }
     tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
-    for (int k = threadIdx.x; k < t.n; k += blockDim.x) {
-        const int c = k == (int)threadIdx.x ? c_first : ctx.pm_cam[t.o0 + k];
+    for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
+        const int c = i == (int)threadIdx.x ? c_first : obs_cam[t.o0 + i];
+        const int k = i == (int)threadIdx.x ? k_first : (ordered ? (int)ctx.pr_k[t.o0 + i] : i);
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
             double y[6];
@@ -573,15 +581,15 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     }
 }
 
-// cameras: candidate = x + (-y_c) * scale, camera-side model-cost pieces, candidate R table.  Single block.
-__global__ void __launch_bounds__(512) cam_update_kernel(Ctx ctx) {
+// cameras: candidate = x + (-y_c) * scale, camera-side model-cost pieces, candidate R table.  Multi-CTA, thread per camera.
+__global__ void __launch_bounds__(128) cam_update_kernel(Ctx ctx) {
     const LMState *st = ctx.state;
     if (st->done) return;
-    __shared__ double red[32];
+    __shared__ double red[128];
     const double *x = ctx.cam[st->cur];
     double *xc = ctx.cam[st->cur ^ 1];
     double dxsq = 0, yb = 0, yhy = 0;
-    for (int c = threadIdx.x; c < ctx.Nc; c += blockDim.x) {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ctx.Nc; c += gridDim.x * blockDim.x) {
         const int kind = ctx.cam_kind[c];
         CamEntry *ce = ctx.tab_c + c;
         double cand[6];
@@ -616,7 +624,8 @@ __global__ void __launch_bounds__(512) cam_update_kernel(Ctx ctx) {
         }
         // K (and P for fixed cameras) of tab_c were written once at set_problem time
     }
-    dxsq = block_sum(dxsq, red); yb = block_sum(yb, red); yhy = block_sum(yhy, red);
+    double unused = 0.0;
+    if (!grid_sum3_max(dxsq, yb, yhy, unused, red_slot(ctx, RED_CAM_UPDATE), ctx.red_count + RED_CAM_UPDATE, red)) return;
     if (threadIdx.x == 0) { ctx.camsums[CS_DXSQ] = dxsq; ctx.camsums[CS_YB] = yb; ctx.camsums[CS_YHY] = yhy; }
 }
 
@@ -631,10 +640,12 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
     double cost = 0.0;
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o < ctx.No) {
-        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const bool ordered = ctx.order_mask & ORDER_EVAL_CANDIDATE;      // the cost is a sum: any order serves
+        const int c = ordered ? ctx.pr_cam[o] : ctx.pm_cam[o], p = ordered ? ctx.pr_pt[o] : ctx.pm_pt[o];
+        const float2 uv = ordered ? ctx.pr_uv[o] : ctx.pm_uv[o];
         const double X[3] = {ptc[3 * (size_t)p], ptc[3 * (size_t)p + 1], ptc[3 * (size_t)p + 2]};
         double r[2];
-        obs_residual(ctx.tab_c + c, ctx.cam_kind[c], X, ctx.pm_uv[o], r);
+        obs_residual(ctx.tab_c + c, ctx.cam_kind[c], X, uv, r);
         double rho0;
         huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
         cost = 0.5 * rho0;
@@ -643,18 +654,18 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
     if (threadIdx.x == 0) part_out[blockIdx.x] = cost;
 }
 
-// step partials -> sums (single block)
-__global__ void __launch_bounds__(1024) reduce_step_partials_kernel(Ctx ctx, const double *cost_part, int n_cost_part) {
+// step partials -> sums (multi-CTA, fixed order)
+__global__ void __launch_bounds__(RED_THREADS) reduce_step_partials_kernel(Ctx ctx, const double *cost_part, int n_cost_part) {
     const LMState *st = ctx.state;
     if (st->done) return;
-    __shared__ double red[32];
+    __shared__ double red[128];
     double dxsq = 0, yb = 0, yhy = 0, cc = 0;
-    for (int i = threadIdx.x; i < ctx.n_part; i += blockDim.x) {
-        const double *pp = ctx.part + 4 * (size_t)i;
-        dxsq += pp[0]; yb += pp[1]; yhy += pp[2];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n_part; i += gridDim.x * blockDim.x) {
+        const double4 pp = reinterpret_cast<const double4 *>(ctx.part)[i];
+        dxsq += pp.x; yb += pp.y; yhy += pp.z;
     }
-    for (int i = threadIdx.x; i < n_cost_part; i += blockDim.x) cc += cost_part[i];
-    dxsq = block_sum(dxsq, red); yb = block_sum(yb, red); yhy = block_sum(yhy, red); cc = block_sum(cc, red);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_cost_part; i += gridDim.x * blockDim.x) cc += cost_part[i];
+    if (!grid_sum4(dxsq, yb, yhy, cc, red_slot(ctx, RED_STEP), ctx.red_count + RED_STEP, red)) return;
     if (threadIdx.x == 0) {
         ctx.sums_loc[SUM_STEP_DXSQ] = dxsq; ctx.sums_loc[SUM_STEP_YB] = yb; ctx.sums_loc[SUM_STEP_YHY] = yhy;
         ctx.sums_loc[SUM_CAND_COST] = cc;
@@ -803,10 +814,14 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int gw = blockIdx.x * EV_WARPS + warp, nw = gridDim.x * EV_WARPS;
     const int n_runs = (ctx.No + 31) >> 5;
+    // processing order (ba_prep.cu): the lanes of a run share cameras; the outputs are then in processing order as well
+    const bool ordered = ctx.order_mask & ORDER_MATERIALIZE;
+    const int *obs_cam = ordered ? ctx.pr_cam : ctx.pm_cam, *obs_pt = ordered ? ctx.pr_pt : ctx.pm_pt;
+    const float2 *obs_uv = ordered ? ctx.pr_uv : ctx.pm_uv;
     double cost = 0.0;
     int c_n = 0, p_n = 0;
     float2 uv_n = make_float2(0.f, 0.f);
-    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = ctx.pm_cam[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
+    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = obs_cam[o]; p_n = obs_pt[o]; uv_n = obs_uv[o]; }
     int it = 0;
     for (int run = gw; run < n_runs; run += nw, ++it) {
         const int o0 = run * 32, o = o0 + lane;
@@ -815,7 +830,7 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
         const float2 uv = uv_n;
         {   // indices of the warp's next run: in flight during this run's gathers and arithmetic
             const int on = o + nw * 32;
-            if (run + nw < n_runs && on < ctx.No) { c_n = ctx.pm_cam[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
+            if (run + nw < n_runs && on < ctx.No) { c_n = obs_cam[on]; p_n = obs_pt[on]; uv_n = obs_uv[on]; }
         }
         double r[2] = {0, 0}, Jc[12], Jp[6], sr = 0.0;
         if (lane < n) {
@@ -857,6 +872,8 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
 // host-side launchers
 // =============================================================================================================
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+// grid of a multi-CTA reduction over n items: enough CTAs to spread the reads, never more than the partial slots
+static inline int red_grid(int n, int per_cta) { return std::max(1, std::min(cdiv(n, per_cta), 256)); }
 static inline size_t tile_smem(const Ctx &ctx, int doubles_per_obs) { return sizeof(double) * (size_t)doubles_per_obs * (size_t)ctx.tile_cap; }
 
 // dynamic shared memory of the tile kernels grows with the longest landmark block; returns a cudaError
@@ -887,9 +904,9 @@ void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     if (ctx.n_blocks > 0) linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
     if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx, force);
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
-    reduce_lin_partials_kernel<<<1, 1024, 0, s>>>(ctx, force);
+    reduce_lin_partials_kernel<<<red_grid(ctx.n_part, 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force);
 }
-void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s) { cam_norms_kernel<<<1, 1024, 0, s>>>(ctx, force); }
+void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s) { cam_norms_kernel<<<red_grid(6 * ctx.Nc, 2 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force); }
 
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s) {
     const int n = max(6 * ctx.Nc, 3 * ctx.Np);
@@ -934,13 +951,13 @@ void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s) { ch
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {
     if (ctx.n_blocks > 0) backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);
-    cam_update_kernel<<<1, 512, 0, s>>>(ctx);
+    cam_update_kernel<<<red_grid(ctx.Nc, 128), 128, 0, s>>>(ctx);
 }
 
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s) {
     const int nb = cdiv(ctx.No, 256);
     if (nb > 0) eval_candidate_kernel<<<nb, 256, 0, s>>>(ctx, cost_part);
-    reduce_step_partials_kernel<<<1, 1024, 0, s>>>(ctx, cost_part, nb);
+    reduce_step_partials_kernel<<<red_grid(std::max(ctx.n_part, nb), 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, cost_part, nb);
 }
 
 // returns the number of cost partials written (one per warp)

@@ -138,19 +138,20 @@ __global__ void __launch_bounds__(128) pcg_invert_blocks_kernel(Ctx ctx) {
     for (int k = 0; k < 36; ++k) M[k] = inv[k];
 }
 
-// start CG: x = 0, r = b, |b|
-__global__ void __launch_bounds__(1024) pcg_start_kernel(Ctx ctx) {
+// start CG: x = 0, r = b, |b|.   Multi-CTA; the last CTA to arrive holds the total and sets up the CG scalars.
+__global__ void __launch_bounds__(RED_THREADS) pcg_start_kernel(Ctx ctx) {
     LMState *st = ctx.state;
     if (st->done) return;
-    __shared__ double red[32];
+    __shared__ double red[128];
     double nb = 0.0;
-    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
         const double b = ctx.rhs[i];
         ctx.cg_x[i] = 0.0;
         ctx.cg_r[i] = b;
         nb += b * b;
     }
-    nb = block_sum(nb, red);
+    double u0 = 0.0, u1 = 0.0, u2 = 0.0;
+    if (!grid_sum4(nb, u0, u1, u2, red_slot(ctx, RED_CG_START), ctx.red_count + RED_CG_START, red)) return;
     if (threadIdx.x == 0) {
         st->cg_norm_b = sqrt(nb);
         st->cg_rho = 1.0; st->cg_last_rho = 1.0; st->cg_Q0 = 0.0; st->cg_iter = 0; st->cg_done = 0;
@@ -227,7 +228,11 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     const int4 bi = ctx.blk_info[blockIdx.x];
     const int p0 = bi.x, p1 = bi.y, o0 = bi.z, n = bi.w;
     if (n == 0) return;
-    const int c_first = threadIdx.x < n ? ctx.pm_cam[o0 + threadIdx.x] : 0;      // in flight across the barrier below
+    // processing order (neighbouring lanes share cameras, ba_prep.cu); the first pass' entry is in flight across the barrier
+    const bool ordered = ctx.order_mask & ORDER_MATVEC;
+    const int *obs_cam = ordered ? ctx.pr_cam : ctx.pm_cam;
+    int c_first = 0, k_first = threadIdx.x;
+    if (threadIdx.x < n) { c_first = obs_cam[o0 + threadIdx.x]; if (ordered) k_first = ctx.pr_k[o0 + threadIdx.x]; }
     // second phase (thread per landmark): track bounds now, V'^-1 on its way into L2
     const int p_mine = p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
@@ -237,8 +242,9 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     if (threadIdx.x == 0) mbar_init(&wbar, 1);
     __syncthreads();
     if (threadIdx.x == 0) bulk_load(sW, ctx.W + 18 * (size_t)o0, 144u * (unsigned)n, &wbar);
-    for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        const int c = k == (int)threadIdx.x ? c_first : ctx.pm_cam[o0 + k];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int c = i == (int)threadIdx.x ? c_first : obs_cam[o0 + i];
+        const int k = i == (int)threadIdx.x ? k_first : (ordered ? (int)ctx.pr_k[o0 + i] : i);
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
             double x[6];
@@ -264,8 +270,9 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         for (int k = lo; k < hi; ++k) { sT[3 * (size_t)k] = t0; sT[3 * (size_t)k + 1] = t1; sT[3 * (size_t)k + 2] = t2; }
     }
     __syncthreads();
-    for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        const int c = k == (int)threadIdx.x ? c_first : ctx.pm_cam[o0 + k];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int c = i == (int)threadIdx.x ? c_first : obs_cam[o0 + i];
+        const int k = i == (int)threadIdx.x ? k_first : (ordered ? (int)ctx.pr_k[o0 + i] : i);
         if (ctx.cam_kind[c] != CAM_FREE) continue;
         const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
         mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
@@ -338,29 +345,29 @@ __global__ void __launch_bounds__(CG_THREADS) pcg_update_kernel(Ctx ctx, double 
     }
 }
 
-// residual reset: r = b - (q + (U + D^2) x), with q holding the landmark part of S x.   Single CTA.
-__global__ void __launch_bounds__(1024) pcg_residual_reset_kernel(Ctx ctx) {
+// residual reset: r = b - (q + (U + D^2) x), with q holding the landmark part of S x.
+__global__ void __launch_bounds__(256) pcg_residual_reset_kernel(Ctx ctx) {
     LMState *st = ctx.state;
     CG_GUARD(st);
-    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
         const double ax = ctx.cg_z[i] + cam_block_row(ctx, st, i / 6, i % 6, ctx.cg_x);
         ctx.cg_r[i] = ctx.rhs[i] - ax;
     }
 }
 
 // Q1 = -x.(b + r); zeta = it (Q1 - Q0) / Q1 < eta -> stop; |r| <= r_tol |b| -> stop; it >= max -> stop
-__global__ void __launch_bounds__(1024) pcg_check_kernel(Ctx ctx) {
+__global__ void __launch_bounds__(RED_THREADS) pcg_check_kernel(Ctx ctx) {
     LMState *st = ctx.state;
     CG_GUARD(st);
-    __shared__ double red[32];
+    __shared__ double red[128];
     double s = 0.0, rr = 0.0;
-    for (int i = threadIdx.x; i < ctx.n; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
         const double r = ctx.cg_r[i];
         s += ctx.cg_x[i] * (ctx.rhs[i] + r);
         rr += r * r;
     }
-    s = block_sum(s, red);
-    rr = block_sum(rr, red);
+    double u0 = 0.0, u1 = 0.0;
+    if (!grid_sum4(s, rr, u0, u1, red_slot(ctx, RED_CG_CHECK), ctx.red_count + RED_CG_CHECK, red)) return;
     if (threadIdx.x == 0) {
         const int it = st->cg_iter;
         const double Q1 = -1.0 * s;
@@ -396,7 +403,7 @@ int pcg_tiles_init(const Ctx &ctx) {
 }
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s) {
     pcg_invert_blocks_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
-    pcg_start_kernel<<<1, 1024, 0, s>>>(ctx);
+    pcg_start_kernel<<<std::max(1, std::min(cdiv(ctx.n, 2 * RED_THREADS), 256)), RED_THREADS, 0, s>>>(ctx);
 }
 
 // grid of the cooperative camera-vector kernels: enough CTAs for the vector, never more than are co-resident
@@ -432,8 +439,8 @@ void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part o
     if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_x, ctx.cg_qp);
     pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_z);
 }
-void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<1, 1024, 0, s>>>(ctx); }
-void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<1, 1024, 0, s>>>(ctx); }
+void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
+void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<std::max(1, std::min(cdiv(ctx.n, 2 * RED_THREADS), 256)), RED_THREADS, 0, s>>>(ctx); }
 void launch_pcg_finish(const Ctx &ctx, cudaStream_t s) { pcg_finish_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
 
 } // namespace ba

@@ -94,6 +94,13 @@ struct Ctx {
     const int *pm_cam;
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
+    // processing order of the tile kernels: inside each landmark block the observations sorted by camera (ba_prep.cu);
+    // entry o0 + t = what thread t of the block's CTA works on, pr_k = its landmark-major slot in the block
+    const float2 *pr_uv;
+    const int *pr_cam;
+    const int *pr_pt;
+    const unsigned short *pr_k;
+    int order_mask;          // which kernels walk the processing order (ORDER_* bits; the others walk landmark-major order)
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
     const int4 *blk_info;    // [n_blocks] {first landmark, end landmark, first observation, observation count}
     int n_blocks, tile_cap;
@@ -134,6 +141,8 @@ struct Ctx {
     double *maxs;            // [MAX_COUNT]  (max over ranks)
     double *sums_loc, *maxs_loc;   // this rank's contribution (alias sums / maxs on a single GPU)
     double *camsums;         // [CS_COUNT]
+    double *red_part;        // [RED_SLOTS][RED_MAX_GRID][4] per-CTA partials of the multi-CTA reductions (grid_sum3_max)
+    unsigned *red_count;     // [RED_SLOTS] arrival tickets (zero between launches)
     // PCG work vectors (n each) and block-Jacobi preconditioner
     double *cg_r, *cg_p, *cg_z, *cg_q, *cg_x, *Minv, *tp;
     double *cg_part;         // [1024] per-CTA partials of the cooperative CG kernels
@@ -144,9 +153,18 @@ struct Ctx {
     volatile int *host_flags; // mapped pinned: [0] = done, [1] = cg_done
 };
 
+// kernels that can walk a landmark block in processing order (Ctx::order_mask)
+enum : int { ORDER_LINEARIZE = 1, ORDER_BACKSUB = 2, ORDER_MATVEC = 4, ORDER_EVAL_CANDIDATE = 8, ORDER_MATERIALIZE = 16,
+             ORDER_DEFAULT = ORDER_EVAL_CANDIDATE | ORDER_MATERIALIZE };
+
+// slots of red_part / red_count
+enum : int { RED_LIN = 0, RED_CAM_NORMS, RED_CAM_UPDATE, RED_STEP, RED_CG_CHECK, RED_CG_START, RED_SLOTS = 8 };
+__host__ __device__ inline double *red_slot(const Ctx &ctx, int slot) { return ctx.red_part + (size_t)slot * RED_MAX_GRID * 4; }
+
 constexpr int CAMS_PER_TILE = 21;   // 6 * 21 = 126 <= 128 (CHOL_NB)
 constexpr int CHUNK = 128;   // observations per camera-side reduction unit
 constexpr int TILE_WIN = 192;   // observation window defining a landmark block of the tile kernels (ba_prep.cu)
 constexpr int TILE_THREADS = 256;
+constexpr int RED_THREADS = 256;   // CTA size of the multi-CTA reductions (grid_red4)
 
 } // namespace ba
