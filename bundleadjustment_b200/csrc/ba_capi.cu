@@ -102,7 +102,7 @@ struct ba_handle {
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
-    DevBuf cm_obs, blk_first_pt, blk_info, pr_uv, pr_cam, pr_pt, pr_k;
+    DevBuf cm_obs, blk_first_pt, blk_info;
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
     DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
     DevBuf part, cost_part, red_part, red_count, sums, maxs, camsums, state, iters, invL, U_loc, bc_loc, sums_loc, maxs_loc;
@@ -137,7 +137,7 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &red_part, &red_count, &sums, &maxs,
                          &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pr_uv, &pr_cam, &pr_pt, &pr_k, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
         for (DevBuf *b : all) b->free();
         chol_plan_destroy(&chol_plan);
         scr.release(); scr2.release();
@@ -372,7 +372,6 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(perm_dev, 4 * (size_t)No); AL(cnt_cam, 4 * (size_t)Nc); AL(cnt_cam_global, 4 * (size_t)Nc); AL(cam_kind, 4 * (size_t)Nc);
     AL(cam_ptr, 4 * (size_t)(Nc + 1)); AL(cam_chunk_ptr, 4 * (size_t)(Nc + 1)); AL(cm_uv, 8 * (size_t)No); AL(cm_pt, 4 * (size_t)No);
     AL(cm_obs, 4 * (size_t)No); AL(blk_first_pt, 4 * ((size_t)No / TILE_WIN + 2)); AL(blk_info, 16 * ((size_t)No / TILE_WIN + 2));
-    AL(pr_uv, 8 * (size_t)No); AL(pr_cam, 4 * (size_t)No); AL(pr_pt, 4 * (size_t)No); AL(pr_k, 2 * (size_t)No);
     AL(chunk_cam, 4 * max_chunks); AL(chunk_beg, 4 * max_chunks); AL(chunk_end, 4 * max_chunks); AL(prep_flags, 16);
     PrepIn &pin = h->prep_in;
     PrepOut &po = h->prep_out;
@@ -384,7 +383,6 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     po.cam_kind = h->cam_kind.as<int>(); po.cam_ptr = h->cam_ptr.as<int>(); po.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
     po.cm_uv = h->cm_uv.as<float2>(); po.cm_pt = h->cm_pt.as<int>(); po.cm_obs = h->cm_obs.as<int>();
     po.blk_first_pt = h->blk_first_pt.as<int>(); po.blk_info = h->blk_info.as<int4>();
-    po.pr_uv = h->pr_uv.as<float2>(); po.pr_cam = h->pr_cam.as<int>(); po.pr_pt = h->pr_pt.as<int>(); po.pr_k = h->pr_k.as<unsigned short>();
     po.chunk_cam = h->chunk_cam.as<int>(); po.chunk_beg = h->chunk_beg.as<int>(); po.chunk_end = h->chunk_end.as<int>();
     po.flags = h->prep_flags.as<int>(); po.h_flags = h->h_prep;
     rc = prep_observations(pin, po, h->scr, s);
@@ -410,10 +408,6 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     if ((rc = prep_camera_major(pin, po, h->scr, s))) return fail(BA_ERR_CUDA, "prep_camera_major: %s", cudaGetErrorString((cudaError_t)rc));
     if ((rc = prep_chunks(pin, po, s))) return fail(BA_ERR_CUDA, "prep_chunks: %s", cudaGetErrorString((cudaError_t)rc));
     ctx.n_chunks = po.n_chunks;
-    {   // BA_B200_ORDER_MASK (measurement aid): which kernels walk the landmark blocks in processing order (ORDER_* bits)
-        const char *v = std::getenv("BA_B200_ORDER_MASK");
-        ctx.order_mask = v ? std::atoi(v) : ORDER_DEFAULT;
-    }
     ctx.n_blocks = po.n_blocks;
     ctx.tile_cap = std::max(po.max_block_obs, 1);
     ctx.n_part = ctx.n_blocks;
@@ -455,7 +449,6 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.chunk_cam = h->chunk_cam.as<int>(); ctx.chunk_beg = h->chunk_beg.as<int>(); ctx.chunk_end = h->chunk_end.as<int>();
     ctx.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
     ctx.cm_obs = h->cm_obs.as<int>(); ctx.blk_first_pt = h->blk_first_pt.as<int>(); ctx.blk_info = h->blk_info.as<int4>();
-    ctx.pr_uv = h->pr_uv.as<float2>(); ctx.pr_cam = h->pr_cam.as<int>(); ctx.pr_pt = h->pr_pt.as<int>(); ctx.pr_k = h->pr_k.as<unsigned short>();
     ctx.tab_x = h->tab_x.as<CamEntry>(); ctx.tab_c = h->tab_c.as<CamEntry>();
     ctx.scale_cam = h->scale_cam.as<double>(); ctx.scale_pt = h->scale_pt.as<double>();
     ctx.U = h->U.as<double>(); ctx.bc = h->bc.as<double>(); ctx.V = h->V.as<double>(); ctx.bp = h->bp.as<double>();
@@ -816,17 +809,6 @@ extern "C" int ba_evaluate(ba_handle *h, double *cost, double *residuals, double
     if (!h->perm_valid && No && (residuals || jac_cam || jac_pt)) {
         h->perm.resize(No);
         CU(cudaMemcpy(h->perm.data(), h->perm_dev.p, 4 * (size_t)No, cudaMemcpyDeviceToHost));
-        if (ctx.order_mask & ORDER_MATERIALIZE) {
-            // the kernel wrote its rows in processing order: row o0 + r of a landmark block holds landmark-major slot pr_k[o0 + r]
-            std::vector<unsigned short> slot(No);
-            std::vector<int4> info(ctx.n_blocks);
-            CU(cudaMemcpy(slot.data(), ctx.pr_k, 2 * (size_t)No, cudaMemcpyDeviceToHost));
-            CU(cudaMemcpy(info.data(), ctx.blk_info, sizeof(int4) * (size_t)ctx.n_blocks, cudaMemcpyDeviceToHost));
-            std::vector<int> row_of(No);
-            for (const int4 &bi : info)
-                for (int r = 0; r < bi.w; ++r) row_of[(size_t)bi.z + slot[(size_t)bi.z + r]] = bi.z + r;
-            for (int i = 0; i < No; ++i) h->perm[i] = row_of[h->perm[i]];
-        }
         h->perm_valid = true;
     }
     auto gather = [&](const DevBuf &src, double *dst, int width) -> int {

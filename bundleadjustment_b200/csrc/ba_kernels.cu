@@ -108,11 +108,9 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
     int lo_mine = 0, hi_mine = 0;
     if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0; }
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
-        const int o = t.o0 + i;
-        int c, p, k;                               // k = the observation's landmark-major slot in the tile
-        float2 uv;
-        if (ctx.order_mask & ORDER_LINEARIZE) { c = ctx.pr_cam[o]; p = ctx.pr_pt[o]; uv = ctx.pr_uv[o]; k = ctx.pr_k[o]; }   // neighbouring lanes share cameras
-        else { c = ctx.pm_cam[o]; p = ctx.pm_pt[o]; uv = ctx.pm_uv[o]; k = i; }
+        const int o = t.o0 + i, k = i;
+        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const float2 uv = ctx.pm_uv[o];
         const int kind = ctx.cam_kind[c];
         const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
@@ -190,51 +188,71 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// C3 (camera side): camera-major pass, one warp per chunk of <= CHUNK observations of ONE camera: U_c, b_c
-// partials by warp-level reduction (deterministic: fixed lane assignment + fixed shuffle tree).
+// C3 (camera side): camera-major pass, one warp per chunk of <= CHUNK observations of ONE camera: U_c, b_c partials.
+// U_c = sum_o Jc_o^T Jc_o and b_c = sum_o Jc_o^T r_o are ONE small product  A^T A  with A = the stacked rows [Jc | r] of
+// the chunk (2 rows per observation, 7 columns): per batch of 32 observations every lane evaluates its observation, parks its
+// two rows k-major in shared memory and the warp issues 16 DMMAs (m8n8k4; both operands are the same fragment).  Two
+// accumulator registers per lane instead of 27 doubles and no 27-fold shuffle reduction; deterministic (fixed order).
 // -------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) linearize_cams_kernel(Ctx ctx, int force) {
+constexpr int CAMS_WARPS = 4;
+constexpr int CAMS_LD = 64 + 4;              // 2 rows x 32 observations per batch; 68 mod 16 == 4 -> conflict-free fragment loads
+__device__ __forceinline__ void dmma884_acc(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+__global__ void __launch_bounds__(CAMS_WARPS * 32) linearize_cams_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
-    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+    __shared__ __align__(16) double sJ[CAMS_WARPS][7 * CAMS_LD];       // [column a of [Jc | r]][k = 2 lane + row]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, tig = lane & 3;
+    const int w = blockIdx.x * CAMS_WARPS + warp;
     if (w >= ctx.n_chunks) return;
     const int c = ctx.chunk_cam[w];
     const int beg = ctx.chunk_beg[w], end = ctx.chunk_end[w];
     const CamEntry *ce = ctx.tab_x + c;
     const double *ptx = ctx.pt[st->cur];
-    double sc[6];
+    double *Js = sJ[warp];
+    double c0 = 0.0, c1 = 0.0;                                          // C[g][2 tig], C[g][2 tig + 1] of the 8 x 8 product
+    for (int base = beg; base < end; base += 32) {
+        const int e = base + lane;
+        double r[2] = {0.0, 0.0}, Jc[12];
 #pragma unroll
-    for (int a = 0; a < 6; ++a) sc[a] = ctx.scale_cam[6 * (size_t)c + a];
-    double acc[27];
+        for (int a = 0; a < 12; ++a) Jc[a] = 0.0;
+        if (e < end) {
+            const int p = ctx.cm_pt[e];
+            const float2 uv = ctx.cm_uv[e];
+            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+            double Jp[6], sc[6];
+            obs_linearize<true, false>(ce, CAM_FREE, X, uv, r, Jc, Jp, sc);
+            double rho0;
+            const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+            const double sr = sqrt(rho1);
+            r[0] *= sr; r[1] *= sr;
 #pragma unroll
-    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
-    for (int e = beg + lane; e < end; e += 32) {
-        const int p = ctx.cm_pt[e];
-        const float2 uv = ctx.cm_uv[e];
-        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
-        double r[2], Jc[12], Jp[6];
-        obs_linearize<true, false>(ce, CAM_FREE, X, uv, r, Jc, Jp);
-        double rho0;
-        const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
-        const double sr = sqrt(rho1);
-        r[0] *= sr; r[1] *= sr;
+            for (int a = 0; a < 6; ++a) { const double f = sr * sc[a]; Jc[a] *= f; Jc[6 + a] *= f; }
+        }
+        __syncwarp();                                                   // the previous batch's DMMAs have consumed the buffer
 #pragma unroll
-        for (int a = 0; a < 6; ++a) { const double f = sr * sc[a]; Jc[a] *= f; Jc[6 + a] *= f; }
-        int k = 0;
-#pragma unroll
-        for (int a = 0; a < 6; ++a)
-#pragma unroll
-            for (int b = a; b < 6; ++b) acc[k++] += Jc[a] * Jc[b] + Jc[6 + a] * Jc[6 + b];
-#pragma unroll
-        for (int a = 0; a < 6; ++a) acc[21 + a] += Jc[a] * r[0] + Jc[6 + a] * r[1];
+        for (int a = 0; a < 6; ++a) *reinterpret_cast<double2 *>(Js + a * CAMS_LD + 2 * lane) = make_double2(Jc[a], Jc[6 + a]);
+        *reinterpret_cast<double2 *>(Js + 6 * CAMS_LD + 2 * lane) = make_double2(r[0], r[1]);
+        __syncwarp();
+        const int left = end - base;
+        const int ksteps = left >= 32 ? 16 : (2 * left + 3) / 4;        // dead lanes of the last batch wrote zeros
+        for (int s4 = 0; s4 < ksteps; ++s4) {
+            const double v = g < 7 ? Js[g * CAMS_LD + 4 * s4 + tig] : 0.0;   // A[g][k] and B[k][g] are the same number
+            dmma884_acc(c0, c1, v, v);
+        }
     }
-#pragma unroll
-    for (int k = 0; k < 27; ++k) acc[k] = warp_sum(acc[k]);
-    if (lane == 0) {
+    // upper triangle of U (row-major, 21 entries) | b_c (6): the layout cam_reduce_kernel sums
+    if (g < 6) {
         double *dst = ctx.cam_part + 27 * (size_t)w;
-#pragma unroll
-        for (int k = 0; k < 27; ++k) dst[k] = acc[k];
+        const int base_k = g * 6 - (g * (g - 1)) / 2 - g;               // + column = index of (g, column), column >= g
+        const int col = 2 * tig;
+        if (col >= g && col < 6) dst[base_k + col] = c0;
+        if (col + 1 >= g && col + 1 < 6) dst[base_k + col + 1] = c1;
+        if (col == 6) dst[21 + g] = c0;
     }
 }
 
@@ -394,11 +412,6 @@ __global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
 constexpr int SCHUR_WARPS = 4;
 constexpr int SCHUR_K = 96;                  // stacked reduction index of one batch: 32 entries x 3 landmark coordinates
 constexpr int SCHUR_LD = SCHUR_K + 4;        // row stride 100 doubles: 100 mod 16 == 4 -> conflict-free DMMA fragment loads
-__device__ __forceinline__ void dmma884_acc(double &c0, double &c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                 : "+d"(c0), "+d"(c1)
-                 : "d"(a), "d"(b));
-}
 // The block of one camera pair is  sum_e Y_e W_b,e^T  with Y_e = W_a,e V'^-1 (6 x 3): stacked over the entries this is ONE
 // small GEMM  [Y_1 .. Y_E] (6 x 3E) * [W_b,1 .. W_b,E]^T (3E x 6), so the reduction over entries runs on the FP64 tensor
 // pipe (DMMA m8n8k4, 6 of 8 rows/columns used; column 6 carries the stacked b_p, which makes rhs_c -= W V'^-1 b_p fall out
@@ -517,11 +530,7 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
     __shared__ unsigned long long wbar;
-    // processing order (neighbouring lanes share cameras); the first pass' entry is in flight across the barrier below
-    const bool ordered = ctx.order_mask & ORDER_BACKSUB;
-    const int *obs_cam = ordered ? ctx.pr_cam : ctx.pm_cam;
-    int c_first = 0, k_first = threadIdx.x;
-    if (threadIdx.x < t.n) { c_first = obs_cam[t.o0 + threadIdx.x]; if (ordered) k_first = ctx.pr_k[t.o0 + threadIdx.x]; }
+    const int c_first = threadIdx.x < t.n ? ctx.pm_cam[t.o0 + threadIdx.x] : 0;   // in flight across the barrier below
     // second phase (thread per landmark): track bounds now, the landmark's rows on their way into L2
     const int p_mine = t.p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
@@ -532,8 +541,8 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     }
     tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
-        const int c = i == (int)threadIdx.x ? c_first : obs_cam[t.o0 + i];
-        const int k = i == (int)threadIdx.x ? k_first : (ordered ? (int)ctx.pr_k[t.o0 + i] : i);
+        const int k = i;
+        const int c = i == (int)threadIdx.x ? c_first : ctx.pm_cam[t.o0 + i];
         double a3[3] = {0, 0, 0};
         if (ctx.cam_kind[c] == CAM_FREE) {
             double y[6];
@@ -640,12 +649,10 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
     double cost = 0.0;
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o < ctx.No) {
-        const bool ordered = ctx.order_mask & ORDER_EVAL_CANDIDATE;      // the cost is a sum: any order serves
-        const int c = ordered ? ctx.pr_cam[o] : ctx.pm_cam[o], p = ordered ? ctx.pr_pt[o] : ctx.pm_pt[o];
-        const float2 uv = ordered ? ctx.pr_uv[o] : ctx.pm_uv[o];
+        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
         const double X[3] = {ptc[3 * (size_t)p], ptc[3 * (size_t)p + 1], ptc[3 * (size_t)p + 2]};
         double r[2];
-        obs_residual(ctx.tab_c + c, ctx.cam_kind[c], X, uv, r);
+        obs_residual(ctx.tab_c + c, ctx.cam_kind[c], X, ctx.pm_uv[o], r);
         double rho0;
         huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
         cost = 0.5 * rho0;
@@ -814,14 +821,10 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int gw = blockIdx.x * EV_WARPS + warp, nw = gridDim.x * EV_WARPS;
     const int n_runs = (ctx.No + 31) >> 5;
-    // processing order (ba_prep.cu): the lanes of a run share cameras; the outputs are then in processing order as well
-    const bool ordered = ctx.order_mask & ORDER_MATERIALIZE;
-    const int *obs_cam = ordered ? ctx.pr_cam : ctx.pm_cam, *obs_pt = ordered ? ctx.pr_pt : ctx.pm_pt;
-    const float2 *obs_uv = ordered ? ctx.pr_uv : ctx.pm_uv;
     double cost = 0.0;
     int c_n = 0, p_n = 0;
     float2 uv_n = make_float2(0.f, 0.f);
-    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = obs_cam[o]; p_n = obs_pt[o]; uv_n = obs_uv[o]; }
+    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = ctx.pm_cam[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
     int it = 0;
     for (int run = gw; run < n_runs; run += nw, ++it) {
         const int o0 = run * 32, o = o0 + lane;
@@ -830,7 +833,7 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
         const float2 uv = uv_n;
         {   // indices of the warp's next run: in flight during this run's gathers and arithmetic
             const int on = o + nw * 32;
-            if (run + nw < n_runs && on < ctx.No) { c_n = obs_cam[on]; p_n = obs_pt[on]; uv_n = obs_uv[on]; }
+            if (run + nw < n_runs && on < ctx.No) { c_n = ctx.pm_cam[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
         }
         double r[2] = {0, 0}, Jc[12], Jp[6], sr = 0.0;
         if (lane < n) {
@@ -902,7 +905,7 @@ void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
     if (ctx.n_blocks > 0) linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
-    if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx, force);
+    if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<red_grid(ctx.n_part, 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force);
 }

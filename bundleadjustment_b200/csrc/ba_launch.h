@@ -44,8 +44,6 @@ struct PrepIn {
 struct PrepOut {
     // landmark-major
     float2 *pm_uv; int *pm_cam, *pm_pt, *pt_ptr, *perm;
-    // the same triplets in the tile kernels' processing order (camera-sorted inside each landmark block) + landmark-major slot
-    float2 *pr_uv; int *pr_cam, *pr_pt; unsigned short *pr_k;
     // cameras
     int *cnt_cam, *cnt_cam_global, *cam_kind, *cam_ptr, *cam_chunk_ptr;
     // camera-major

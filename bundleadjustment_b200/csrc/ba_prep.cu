@@ -107,32 +107,6 @@ __global__ void prep_blocks_max_kernel(int n_blocks, const int *__restrict__ pt_
     atomicMax(mx, n);
 }
 
-// Processing order inside a landmark block: its observations sorted by camera.  The tile kernels assign THREAD t of the CTA
-// to the t-th observation of that order, so the 32 lanes of a warp gather a handful of distinct cameras instead of ~20: a
-// per-lane 256-bit gather costs one L1 wavefront per DISTINCT address, and those wavefronts are what bounds the landmark-major
-// kernels (L1/TEX 60-95 % busy).  Results still land at the observation's landmark-major slot k of the tile, so the W layout,
-// the per-landmark sums in track order and every index into W are unchanged.  pr_* = the index triplet in processing order
-// (no extra dependent load), pr_k = the slot.  One CTA per block; rank by counting (n is a few hundred).
-__global__ void __launch_bounds__(256) prep_tile_order_kernel(const int4 *__restrict__ info, const int *__restrict__ pm_cam,
-                                                              const int *__restrict__ pm_pt, const float2 *__restrict__ pm_uv,
-                                                              int *__restrict__ pr_cam, int *__restrict__ pr_pt, float2 *__restrict__ pr_uv,
-                                                              unsigned short *__restrict__ pr_k) {
-    extern __shared__ int s_cam[];
-    const int4 bi = info[blockIdx.x];
-    const int o0 = bi.z, n = bi.w;
-    for (int k = threadIdx.x; k < n; k += blockDim.x) s_cam[k] = pm_cam[o0 + k];
-    __syncthreads();
-    for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        const int c = s_cam[k];
-        int rank = 0;
-        for (int j = 0; j < n; ++j) { const int cj = s_cam[j]; rank += (cj < c) || (cj == c && j < k); }
-        pr_cam[o0 + rank] = c;
-        pr_pt[o0 + rank] = pm_pt[o0 + k];
-        pr_uv[o0 + rank] = pm_uv[o0 + k];
-        pr_k[o0 + rank] = (unsigned short)k;
-    }
-}
-
 __global__ void prep_chunks_kernel(int Nc, const int *__restrict__ cam_ptr, const int *__restrict__ cam_chunk_ptr,
                                    int *__restrict__ chunk_cam, int *__restrict__ chunk_beg, int *__restrict__ chunk_end) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -297,10 +271,6 @@ int prep_blocks(const PrepIn &in, PrepOut &out, cudaStream_t s) {
     PCU(cudaMemcpyAsync(out.h_flags + 4, out.flags + 2, sizeof(int), cudaMemcpyDeviceToHost, s));
     PCU(cudaStreamSynchronize(s));
     out.max_block_obs = out.h_flags[4];
-    if (out.max_block_obs > 65535) return (int)cudaErrorInvalidConfiguration;     // slots are 16 bit (shared memory runs out long before)
-    if (in.No > 0)
-        prep_tile_order_kernel<<<out.n_blocks, 256, sizeof(int) * (size_t)std::max(out.max_block_obs, 1), s>>>(
-            out.blk_info, out.pm_cam, out.pm_pt, out.pm_uv, out.pr_cam, out.pr_pt, out.pr_uv, out.pr_k);
     return (int)cudaGetLastError();
 }
 

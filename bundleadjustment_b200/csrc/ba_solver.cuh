@@ -94,13 +94,6 @@ struct Ctx {
     const int *pm_cam;
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
-    // processing order of the tile kernels: inside each landmark block the observations sorted by camera (ba_prep.cu);
-    // entry o0 + t = what thread t of the block's CTA works on, pr_k = its landmark-major slot in the block
-    const float2 *pr_uv;
-    const int *pr_cam;
-    const int *pr_pt;
-    const unsigned short *pr_k;
-    int order_mask;          // which kernels walk the processing order (ORDER_* bits; the others walk landmark-major order)
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
     const int4 *blk_info;    // [n_blocks] {first landmark, end landmark, first observation, observation count}
     int n_blocks, tile_cap;
@@ -152,10 +145,6 @@ struct Ctx {
     ba_iteration *iters;     // [max_num_iterations + 2]
     volatile int *host_flags; // mapped pinned: [0] = done, [1] = cg_done
 };
-
-// kernels that can walk a landmark block in processing order (Ctx::order_mask)
-enum : int { ORDER_LINEARIZE = 1, ORDER_BACKSUB = 2, ORDER_MATVEC = 4, ORDER_EVAL_CANDIDATE = 8, ORDER_MATERIALIZE = 16,
-             ORDER_DEFAULT = ORDER_EVAL_CANDIDATE | ORDER_MATERIALIZE };
 
 // slots of red_part / red_count
 enum : int { RED_LIN = 0, RED_CAM_NORMS, RED_CAM_UPDATE, RED_STEP, RED_CG_CHECK, RED_CG_START, RED_SLOTS = 8 };
