@@ -201,7 +201,7 @@ __device__ __forceinline__ void dmma884_acc(double &c0, double &c1, double a, do
                  : "+d"(c0), "+d"(c1)
                  : "d"(a), "d"(b));
 }
-__global__ void __launch_bounds__(CAMS_WARPS * 32) linearize_cams_kernel(Ctx ctx, int force) {
+__global__ void __launch_bounds__(CAMS_WARPS * 32, 5) linearize_cams_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
     __shared__ __align__(16) double sJ[CAMS_WARPS][7 * CAMS_LD];       // [column a of [Jc | r]][k = 2 lane + row]
@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(CAMS_WARPS * 32) linearize_cams_kernel(Ctx ctx
     const CamEntry *ce = ctx.tab_x + c;
     const double *ptx = ctx.pt[st->cur];
     double *Js = sJ[warp];
-    double c0 = 0.0, c1 = 0.0;                                          // C[g][2 tig], C[g][2 tig + 1] of the 8 x 8 product
+    double acc[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};                // C[g][2 tig], C[g][2 tig + 1]: four independent DMMA chains
     for (int base = beg; base < end; base += 32) {
         const int e = base + lane;
         double r[2] = {0.0, 0.0}, Jc[12];
@@ -240,11 +240,16 @@ __global__ void __launch_bounds__(CAMS_WARPS * 32) linearize_cams_kernel(Ctx ctx
         __syncwarp();
         const int left = end - base;
         const int ksteps = left >= 32 ? 16 : (2 * left + 3) / 4;        // dead lanes of the last batch wrote zeros
-        for (int s4 = 0; s4 < ksteps; ++s4) {
-            const double v = g < 7 ? Js[g * CAMS_LD + 4 * s4 + tig] : 0.0;   // A[g][k] and B[k][g] are the same number
-            dmma884_acc(c0, c1, v, v);
+        const double *frag = Js + (g < 7 ? g : 0) * CAMS_LD + tig;          // A[g][k] and B[k][g] are the same number
+        const double keep = g < 7 ? 1.0 : 0.0;
+        int s4 = 0;
+        for (; s4 + 4 <= ksteps; s4 += 4) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const double v = frag[4 * (s4 + q)] * keep; dmma884_acc(acc[q][0], acc[q][1], v, v); }
         }
+        for (; s4 < ksteps; ++s4) { const double v = frag[4 * s4] * keep; dmma884_acc(acc[0][0], acc[0][1], v, v); }
     }
+    const double c0 = (acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]), c1 = (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]);
     // upper triangle of U (row-major, 21 entries) | b_c (6): the layout cam_reduce_kernel sums
     if (g < 6) {
         double *dst = ctx.cam_part + 27 * (size_t)w;
@@ -432,7 +437,7 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
     const long long end = beg + (info >> 1);
     const bool diag = info & 1;
     double *Ys = sY[warp], *Bs = sB[warp];
-    double c0 = 0.0, c1 = 0.0;                                          // C[g][2 tig], C[g][2 tig + 1] of the 8 x 8 product
+    double acc[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};                // C[g][2 tig], C[g][2 tig + 1]: four independent DMMA chains
     long long e = beg + lane;
     int2 ob_n = make_int2(0, 0);
     int p_n = 0;
@@ -481,12 +486,22 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
         const long long left = end - base;
         const int ksteps = left >= 32 ? SCHUR_K / 4 : (int)((3 * left + 3) / 4);
         const bool arow = g < 6, brow = g < 6 || (diag && g == 6);
-        for (int s4 = 0; s4 < ksteps; ++s4) {
+        int s4 = 0;
+        for (; s4 + 4 <= ksteps; s4 += 4) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const double av = arow ? Ys[g * SCHUR_LD + 4 * (s4 + q) + tig] : 0.0;
+                const double bv = brow ? Bs[g * SCHUR_LD + 4 * (s4 + q) + tig] : 0.0;
+                dmma884_acc(acc[q][0], acc[q][1], av, bv);
+            }
+        }
+        for (; s4 < ksteps; ++s4) {
             const double av = arow ? Ys[g * SCHUR_LD + 4 * s4 + tig] : 0.0;
             const double bv = brow ? Bs[g * SCHUR_LD + 4 * s4 + tig] : 0.0;
-            dmma884_acc(c0, c1, av, bv);
+            dmma884_acc(acc[0][0], acc[0][1], av, bv);
         }
     }
+    const double c0 = (acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]), c1 = (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]);
     double *dst = pi.unit_part + 42 * (size_t)u;
     if (g < 6) {
         const int c = 2 * tig;

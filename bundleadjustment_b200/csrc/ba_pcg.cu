@@ -19,72 +19,46 @@ __device__ __forceinline__ double lm_diag_pcg(const Ctx &ctx, double jtj, double
 #define CG_GUARD(st) if ((st)->done || (st)->cg_done) return;
 
 // landmark contributions to block-diag(S) and rhs, CAMERA-major and deterministic: one warp per chunk of <= CHUNK
-// observations of one camera.  sum_o W_o V'^-1 W_o^T and sum_o W_o V'^-1 b_p are ONE small product  Y B^T  with Y = the stacked
-// Y_o = W_o V'^-1 (6 x 3 per observation) and B = the stacked [W_o ; b_p^T] (7 x 3): per batch of 32 observations every lane
-// gathers W_o (144 B), V'^-1 (48 B) and b_p (24 B) of its observation, parks Y and B k-major in shared memory and the warp
-// issues 24 DMMAs (m8n8k4) -- the construction of schur_units_kernel on the diagonal blocks.  The chunk partials are then
-// summed per camera in chunk order (pcg_setup_reduce_kernel).  No atomics, no 27-fold shuffle reduction.
-constexpr int SETUP_WARPS = 4;
-constexpr int SETUP_LD = 96 + 4;             // 3 columns x 32 observations per batch; 100 mod 16 == 4
-__device__ __forceinline__ void dmma884_acc_pcg(double &c0, double &c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                 : "+d"(c0), "+d"(c1)
-                 : "d"(a), "d"(b));
-}
-__global__ void __launch_bounds__(SETUP_WARPS * 32) pcg_setup_cams_kernel(Ctx ctx) {
+// observations of one camera gathers W_o (144 B), V'^-1 (48 B) and V'^-1 b_p (24 B) of its observations, accumulates the
+// 21 unique entries of W V'^-1 W^T plus the 6 rhs entries per lane, reduces them with a fixed shuffle tree; the chunk
+// partials are then summed per camera in chunk order (pcg_setup_reduce_kernel).  No atomics.
+__global__ void __launch_bounds__(128) pcg_setup_cams_kernel(Ctx ctx) {
     const LMState *st = ctx.state;
     if (st->done) return;
-    __shared__ __align__(16) double sY[SETUP_WARPS][6 * SETUP_LD];     // [a][k]: Y_o[a][q] at k = 3 lane + q
-    __shared__ __align__(16) double sB[SETUP_WARPS][7 * SETUP_LD];     // [b][k]: W_o[b][q]; row 6: b_p[q]
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int g = lane >> 2, tig = lane & 3;
-    const int w = blockIdx.x * SETUP_WARPS + warp;
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (w >= ctx.n_chunks) return;
     const int beg = ctx.chunk_beg[w], end = ctx.chunk_end[w];
-    double *Ys = sY[warp], *Bs = sB[warp];
-    double c0 = 0.0, c1 = 0.0;
-    for (int base = beg; base < end; base += 32) {
-        const int d = base + lane;
-        const bool live = d < end;
-        const int e = live ? ctx.cm_obs[d] : 0, p = live ? ctx.cm_pt[d] : 0;     // dead lanes read row 0 (finite) and contribute zeros
+    double acc[27];
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    for (int d = beg + lane; d < end; d += 32) {
+        const int e = ctx.cm_obs[d], p = ctx.cm_pt[d];
         double wv[18], vi[6];                              // gathers as aligned 256-bit windows (7 requests instead of 12)
         load_row18(ctx.W, (size_t)e, wv);
         load_row6(ctx.Vinv, (size_t)p, vi);
-        const double *b3 = ctx.bp + 3 * (size_t)p;
-        const double lv = live ? 1.0 : 0.0;
-        const double bq[3] = {b3[0] * lv, b3[1] * lv, b3[2] * lv};
-        __syncwarp();                                      // the previous batch's DMMAs have consumed the buffers
+        const double *w3 = ctx.wv + 3 * (size_t)p;
+        const double t0 = w3[0], t1 = w3[1], t2 = w3[2];
+        double Y[18];
 #pragma unroll
         for (int a = 0; a < 6; ++a) {
-            const double w0 = wv[a * 3] * lv, w1 = wv[a * 3 + 1] * lv, w2 = wv[a * 3 + 2] * lv;
-            double *y = Ys + a * SETUP_LD + 3 * lane;
-            y[0] = w0 * vi[0] + w1 * vi[1] + w2 * vi[2];
-            y[1] = w0 * vi[1] + w1 * vi[3] + w2 * vi[4];
-            y[2] = w0 * vi[2] + w1 * vi[4] + w2 * vi[5];
-            double *bb = Bs + a * SETUP_LD + 3 * lane;
-            bb[0] = w0; bb[1] = w1; bb[2] = w2;
+            Y[a * 3 + 0] = wv[a * 3] * vi[0] + wv[a * 3 + 1] * vi[1] + wv[a * 3 + 2] * vi[2];
+            Y[a * 3 + 1] = wv[a * 3] * vi[1] + wv[a * 3 + 1] * vi[3] + wv[a * 3 + 2] * vi[4];
+            Y[a * 3 + 2] = wv[a * 3] * vi[2] + wv[a * 3 + 1] * vi[4] + wv[a * 3 + 2] * vi[5];
+            acc[21 + a] += wv[a * 3] * t0 + wv[a * 3 + 1] * t1 + wv[a * 3 + 2] * t2;
         }
-        {
-            double *bb = Bs + 6 * SETUP_LD + 3 * lane;
-            bb[0] = bq[0]; bb[1] = bq[1]; bb[2] = bq[2];
-        }
-        __syncwarp();
-        const int left = end - base;
-        const int ksteps = left >= 32 ? 24 : (3 * left + 3) / 4;
-        for (int s4 = 0; s4 < ksteps; ++s4) {
-            const double av = g < 6 ? Ys[g * SETUP_LD + 4 * s4 + tig] : 0.0;
-            const double bv = g < 7 ? Bs[g * SETUP_LD + 4 * s4 + tig] : 0.0;
-            dmma884_acc_pcg(c0, c1, av, bv);
-        }
+        int k = 0;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = a; b < 6; ++b) { acc[k] += Y[a * 3] * wv[b * 3] + Y[a * 3 + 1] * wv[b * 3 + 1] + Y[a * 3 + 2] * wv[b * 3 + 2]; ++k; }
     }
-    // upper triangle of the block (row-major, 21 entries) | rhs share (6): the layout pcg_setup_reduce_kernel sums
-    if (g < 6) {
+#pragma unroll
+    for (int k = 0; k < 27; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) {
         double *dst = ctx.cam_part + 27 * (size_t)w;
-        const int base_k = g * 6 - (g * (g - 1)) / 2 - g;
-        const int col = 2 * tig;
-        if (col >= g && col < 6) dst[base_k + col] = c0;
-        if (col + 1 >= g && col + 1 < 6) dst[base_k + col + 1] = c1;
-        if (col == 6) dst[21 + g] = c0;
+#pragma unroll
+        for (int k = 0; k < 27; ++k) dst[k] = acc[k];
     }
 }
 
@@ -416,7 +390,7 @@ static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 // local part of the setup; the caller all-reduces Minv (36 Nc) and rhs (6 Nc) when sharded, then calls
 // launch_pcg_iteration repeatedly (first call starts CG).
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
-    if (ctx.n_chunks > 0) pcg_setup_cams_kernel<<<cdiv(ctx.n_chunks, SETUP_WARPS), SETUP_WARPS * 32, 0, s>>>(ctx);
+    if (ctx.n_chunks > 0) pcg_setup_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx);
     pcg_setup_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
 }
 static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 21 * (size_t)ctx.tile_cap; }
