@@ -37,6 +37,12 @@ struct __align__(32) CamEntry {
 static_assert(sizeof(CamEntry) == 40 * 8, "CamEntry layout");
 static_assert(offsetof(CamEntry, K) % 32 == 0 && offsetof(CamEntry, Jr) % 32 == 0, "CamEntry groups must be 32-byte aligned");
 
+// Candidate-point table (cost-only evaluation): the 3 x 4 projection P = K [R | t] (free camera) or K E[0:3, :] (fixed camera;
+// the homogeneous divide of the reference's (E X).hnormalized() cancels in the pixel ratio), row-major.  Three 256-bit loads per
+// observation instead of six plus a kind test; the pixel differs from the two-stage product by rounding only (~1e-16 relative).
+struct __align__(32) CamProj { double P[12]; };
+static_assert(sizeof(CamProj) == 96, "CamProj layout");
+
 struct __align__(32) Double4 { double x, y, z, w; };
 // N4 x 256-bit loads of 32-byte-aligned doubles into registers
 template <int N4>
@@ -108,6 +114,9 @@ __device__ __forceinline__ void load_record18(const double *__restrict__ sW, int
 }
 
 enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
+// pm_camk word: camera index | kind << 30
+__device__ __forceinline__ int camk_cam(unsigned v) { return (int)(v & 0x3fffffffu); }
+__device__ __forceinline__ int camk_kind(unsigned v) { return (int)(v >> 30); }
 
 // ceres::AngleAxisToRotationMatrix + closed-form derivative of the branch taken (autodiff-equivalent)
 __device__ __forceinline__ void rodrigues(const double w[3], double R[9], double *dR /*27 or nullptr*/) {
@@ -191,27 +200,25 @@ __device__ __forceinline__ void project(const double *__restrict__ K, const doub
     }
 }
 
-// residual only (cost evaluation at a candidate point).  kind: CAM_FREE / CAM_FIXED.
-__device__ __forceinline__ void obs_residual(const CamEntry *__restrict__ ce, int kind, const double X[3], float2 uv, double r[2]) {
-    double p[3];
-    if (kind == CAM_FREE) {
-        double Rt[12];
-        load_vec4<3>(ce->R, Rt);
+// residual only (cost evaluation at a candidate point) from the camera's 3 x 4 projection
+__device__ __forceinline__ void obs_residual(const CamProj *__restrict__ cp, const double X[3], float2 uv, double r[2]) {
+    double P[12];
+    load_vec4<3>(cp->P, P);
+    const double q0 = P[0] * X[0] + P[1] * X[1] + P[2] * X[2] + P[3];
+    const double q1 = P[4] * X[0] + P[5] * X[1] + P[6] * X[2] + P[7];
+    const double q2 = P[8] * X[0] + P[9] * X[1] + P[10] * X[2] + P[11];
+    r[0] = q0 / q2 - (double)uv.x;
+    r[1] = q1 / q2 - (double)uv.y;
+}
+// P = K [R | t] with R column-major; K row-major promoted from f32
+__device__ __forceinline__ void cam_projection(const float *__restrict__ K, const double R[9], const double t[3], double P[12]) {
 #pragma unroll
-        for (int i = 0; i < 3; ++i) p[i] = Rt[i] * X[0] + Rt[i + 3] * X[1] + Rt[i + 6] * X[2] + Rt[9 + i];
-    } else {
-        double P[16];
-        load_vec4<4>(ce->Jr, P);
-        double ph[4];
+    for (int i = 0; i < 3; ++i) {
+        const double k0 = (double)K[3 * i], k1 = (double)K[3 * i + 1], k2 = (double)K[3 * i + 2];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) ph[i] = P[4 * i] * X[0] + P[4 * i + 1] * X[1] + P[4 * i + 2] * X[2] + P[4 * i + 3];
-        p[0] = ph[0] / ph[3]; p[1] = ph[1] / ph[3]; p[2] = ph[2] / ph[3];
+        for (int j = 0; j < 3; ++j) P[4 * i + j] = k0 * R[3 * j] + k1 * R[3 * j + 1] + k2 * R[3 * j + 2];
+        P[4 * i + 3] = k0 * t[0] + k1 * t[1] + k2 * t[2];
     }
-    double pix[2], K[12];
-    load_vec4<3>(ce->K, K);
-    project(K, p, pix, nullptr, false);
-    r[0] = pix[0] - (double)uv.x;
-    r[1] = pix[1] - (double)uv.y;
 }
 
 // residual + Jacobians (unrobustified, unscaled).  Jc 2x6 row-major (zero for fixed), Jp 2x3 row-major.

@@ -26,9 +26,31 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ctx.Nc) return;
     const int buf = which == 0 ? st->cur : (st->cur ^ 1);
-    CamEntry *ce = (which == 0 ? ctx.tab_x : ctx.tab_c) + c;
     const int kind = ctx.cam_kind[c];
     const float *K = ctx.cam_K + 9 * (size_t)c;
+    if (which == 1) {
+        // candidate table: the 3 x 4 projection only.  Fixed cameras: K E[0:3, :] (written once, at set_problem time).
+        double P[12];
+        if (kind == CAM_FIXED) {
+            const float *E = ctx.cam_extr + 16 * (size_t)c;
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    P[4 * i + j] = (double)K[3 * i] * (double)E[j] + (double)K[3 * i + 1] * (double)E[4 + j] + (double)K[3 * i + 2] * (double)E[8 + j];
+        } else {
+            const double *x = ctx.cam[buf] + 6 * (size_t)c;
+            const double w[3] = {x[0], x[1], x[2]}, t[3] = {x[3], x[4], x[5]};
+            double R[9];
+            rodrigues(w, R, nullptr);
+            cam_projection(K, R, t, P);
+        }
+        double *dst = ctx.tab_c[c].P;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) dst[i] = P[i];
+        return;
+    }
+    CamEntry *ce = ctx.tab_x + c;
 #pragma unroll
     for (int i = 0; i < 9; ++i) ce->K[i] = (double)K[i];
     if (kind == CAM_FIXED) {
@@ -41,26 +63,24 @@ __global__ void cam_prep_kernel(Ctx ctx, int which /*0: x (with derivs, needs ne
     const double *x = ctx.cam[buf] + 6 * (size_t)c;
     double w[3] = {x[0], x[1], x[2]};
     double R[9], dR[27];
-    rodrigues(w, R, which == 0 ? dR : nullptr);
+    rodrigues(w, R, dR);
 #pragma unroll
     for (int i = 0; i < 9; ++i) ce->R[i] = R[i];
-    if (which == 0) {
-        // right Jacobian from the exact derivative: R^T dR_j is the skew matrix [Jr_j]x
+    // right Jacobian from the exact derivative: R^T dR_j is the skew matrix [Jr_j]x
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const double *D = dR + 9 * j;
-            double S[9];                          // S[a][b] = sum_i R[i][a] D[i][b]   (R, D column-major)
+    for (int j = 0; j < 3; ++j) {
+        const double *D = dR + 9 * j;
+        double S[9];                          // S[a][b] = sum_i R[i][a] D[i][b]   (R, D column-major)
 #pragma unroll
-            for (int a = 0; a < 3; ++a)
+        for (int a = 0; a < 3; ++a)
 #pragma unroll
-                for (int b = 0; b < 3; ++b) S[a * 3 + b] = R[0 + 3 * a] * D[0 + 3 * b] + R[1 + 3 * a] * D[1 + 3 * b] + R[2 + 3 * a] * D[2 + 3 * b];
-            ce->Jr[3 * j + 0] = 0.5 * (S[2 * 3 + 1] - S[1 * 3 + 2]);
-            ce->Jr[3 * j + 1] = 0.5 * (S[0 * 3 + 2] - S[2 * 3 + 0]);
-            ce->Jr[3 * j + 2] = 0.5 * (S[1 * 3 + 0] - S[0 * 3 + 1]);
-        }
-#pragma unroll
-        for (int a = 0; a < 6; ++a) ce->sc[a] = ctx.scale_cam[6 * (size_t)c + a];
+            for (int b = 0; b < 3; ++b) S[a * 3 + b] = R[0 + 3 * a] * D[0 + 3 * b] + R[1 + 3 * a] * D[1 + 3 * b] + R[2 + 3 * a] * D[2 + 3 * b];
+        ce->Jr[3 * j + 0] = 0.5 * (S[2 * 3 + 1] - S[1 * 3 + 2]);
+        ce->Jr[3 * j + 1] = 0.5 * (S[0 * 3 + 2] - S[2 * 3 + 0]);
+        ce->Jr[3 * j + 2] = 0.5 * (S[1 * 3 + 0] - S[0 * 3 + 1]);
     }
+#pragma unroll
+    for (int a = 0; a < 6; ++a) ce->sc[a] = ctx.scale_cam[6 * (size_t)c + a];
     ce->t[0] = x[3]; ce->t[1] = x[4]; ce->t[2] = x[5];
 }
 
@@ -109,9 +129,9 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
     if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0; }
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
         const int o = t.o0 + i, k = i;
-        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const unsigned ck = ctx.pm_camk[o];
+        const int c = camk_cam(ck), kind = camk_kind(ck), p = ctx.pm_pt[o];
         const float2 uv = ctx.pm_uv[o];
-        const int kind = ctx.cam_kind[c];
         const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
         double r[2], Jc[12], Jp[6], sc[6];
@@ -545,7 +565,7 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
     __shared__ unsigned long long wbar;
-    const int c_first = threadIdx.x < t.n ? ctx.pm_cam[t.o0 + threadIdx.x] : 0;   // in flight across the barrier below
+    const unsigned ck_first = threadIdx.x < t.n ? ctx.pm_camk[t.o0 + threadIdx.x] : 0u;   // in flight across the barrier below
     // second phase (thread per landmark): track bounds now, the landmark's rows on their way into L2
     const int p_mine = t.p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
@@ -557,9 +577,10 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
         const int k = i;
-        const int c = i == (int)threadIdx.x ? c_first : ctx.pm_cam[t.o0 + i];
+        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[t.o0 + i];
+        const int c = camk_cam(ck);
         double a3[3] = {0, 0, 0};
-        if (ctx.cam_kind[c] == CAM_FREE) {
+        if (camk_kind(ck) == CAM_FREE) {
             double y[6];
             load_row6(ctx.yc, (size_t)c, y);
             tile_wait_W(&wbar);
@@ -615,7 +636,7 @@ __global__ void __launch_bounds__(128) cam_update_kernel(Ctx ctx) {
     double dxsq = 0, yb = 0, yhy = 0;
     for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ctx.Nc; c += gridDim.x * blockDim.x) {
         const int kind = ctx.cam_kind[c];
-        CamEntry *ce = ctx.tab_c + c;
+        CamProj *cp = ctx.tab_c + c;
         double cand[6];
         if (kind == CAM_FREE) {
             const double *y = ctx.yc + 6 * (size_t)c;
@@ -640,13 +661,14 @@ __global__ void __launch_bounds__(128) cam_update_kernel(Ctx ctx) {
 #pragma unroll
         for (int a = 0; a < 6; ++a) xc[6 * (size_t)c + a] = cand[a];
         if (kind == CAM_FREE) {
-            double R[9];
+            double R[9], P[12];
             rodrigues(cand, R, nullptr);
+            const double tc[3] = {cand[3], cand[4], cand[5]};
+            cam_projection(ctx.cam_K + 9 * (size_t)c, R, tc, P);
 #pragma unroll
-            for (int i = 0; i < 9; ++i) ce->R[i] = R[i];
-            ce->t[0] = cand[3]; ce->t[1] = cand[4]; ce->t[2] = cand[5];
+            for (int i = 0; i < 12; ++i) cp->P[i] = P[i];
         }
-        // K (and P for fixed cameras) of tab_c were written once at set_problem time
+        // the projections of fixed cameras were written once, at set_problem time
     }
     double unused = 0.0;
     if (!grid_sum3_max(dxsq, yb, yhy, unused, red_slot(ctx, RED_CAM_UPDATE), ctx.red_count + RED_CAM_UPDATE, red)) return;
@@ -664,10 +686,10 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
     double cost = 0.0;
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o < ctx.No) {
-        const int c = ctx.pm_cam[o], p = ctx.pm_pt[o];
+        const int c = camk_cam(ctx.pm_camk[o]), p = ctx.pm_pt[o];
         const double X[3] = {ptc[3 * (size_t)p], ptc[3 * (size_t)p + 1], ptc[3 * (size_t)p + 2]};
         double r[2];
-        obs_residual(ctx.tab_c + c, ctx.cam_kind[c], X, ctx.pm_uv[o], r);
+        obs_residual(ctx.tab_c + c, X, ctx.pm_uv[o], r);
         double rho0;
         huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
         cost = 0.5 * rho0;
@@ -837,22 +859,22 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
     const int gw = blockIdx.x * EV_WARPS + warp, nw = gridDim.x * EV_WARPS;
     const int n_runs = (ctx.No + 31) >> 5;
     double cost = 0.0;
-    int c_n = 0, p_n = 0;
+    unsigned c_n = 0u;
+    int p_n = 0;
     float2 uv_n = make_float2(0.f, 0.f);
-    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = ctx.pm_cam[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
+    if (gw < n_runs && gw * 32 + lane < ctx.No) { const int o = gw * 32 + lane; c_n = ctx.pm_camk[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
     int it = 0;
     for (int run = gw; run < n_runs; run += nw, ++it) {
         const int o0 = run * 32, o = o0 + lane;
         const int n = min(32, ctx.No - o0);
-        const int c = c_n, p = p_n;
+        const int c = camk_cam(c_n), kind = camk_kind(c_n), p = p_n;
         const float2 uv = uv_n;
         {   // indices of the warp's next run: in flight during this run's gathers and arithmetic
             const int on = o + nw * 32;
-            if (run + nw < n_runs && on < ctx.No) { c_n = ctx.pm_cam[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
+            if (run + nw < n_runs && on < ctx.No) { c_n = ctx.pm_camk[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
         }
         double r[2] = {0, 0}, Jc[12], Jp[6], sr = 0.0;
         if (lane < n) {
-            const int kind = ctx.cam_kind[c];
             const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
             obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
             double rho0;

@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     const int4 bi = ctx.blk_info[blockIdx.x];
     const int p0 = bi.x, p1 = bi.y, o0 = bi.z, n = bi.w;
     if (n == 0) return;
-    const int c_first = threadIdx.x < n ? ctx.pm_cam[o0 + threadIdx.x] : 0;      // in flight across the barrier below
+    const unsigned ck_first = threadIdx.x < n ? ctx.pm_camk[o0 + threadIdx.x] : 0u;      // in flight across the barrier below
     // second phase (thread per landmark): track bounds now, V'^-1 on its way into L2
     const int p_mine = p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
@@ -240,9 +240,10 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     if (threadIdx.x == 0) bulk_load(sW, ctx.W + 18 * (size_t)o0, 144u * (unsigned)n, &wbar);
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         const int k = i;
-        const int c = i == (int)threadIdx.x ? c_first : ctx.pm_cam[o0 + i];
+        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+        const int c = camk_cam(ck);
         double a3[3] = {0, 0, 0};
-        if (ctx.cam_kind[c] == CAM_FREE) {
+        if (camk_kind(ck) == CAM_FREE) {
             double x[6];
             load_row6(v, (size_t)c, x);
             mbar_wait(&wbar, 0);
@@ -268,8 +269,9 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     __syncthreads();
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         const int k = i;
-        const int c = i == (int)threadIdx.x ? c_first : ctx.pm_cam[o0 + i];
-        if (ctx.cam_kind[c] != CAM_FREE) continue;
+        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+        const int c = camk_cam(ck);
+        if (camk_kind(ck) != CAM_FREE) continue;
         const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
         mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
         double Wo[18];

@@ -107,6 +107,15 @@ __global__ void prep_blocks_max_kernel(int n_blocks, const int *__restrict__ pt_
     atomicMax(mx, n);
 }
 
+// camera index and camera kind of every landmark-major observation in ONE word (kind << 30 | camera): the per-observation
+// kernels then need no dependent gather of cam_kind[camera] (a per-lane gather costs an L1 pass per instruction)
+__global__ void prep_camk_kernel(int No, const int *__restrict__ pm_cam, const int *__restrict__ kind, unsigned *__restrict__ pm_camk) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= No) return;
+    const int c = pm_cam[e];
+    pm_camk[e] = (unsigned)c | ((unsigned)kind[c] << 30);
+}
+
 __global__ void prep_chunks_kernel(int Nc, const int *__restrict__ cam_ptr, const int *__restrict__ cam_chunk_ptr,
                                    int *__restrict__ chunk_cam, int *__restrict__ chunk_beg, int *__restrict__ chunk_end) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -299,6 +308,8 @@ int prep_camera_major(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStre
     PCU(cudaMemcpyAsync(out.h_flags + 2, out.cam_ptr + Nc, sizeof(int), cudaMemcpyDeviceToHost, s));
     PCU(cudaMemcpyAsync(out.h_flags + 3, out.cam_chunk_ptr + Nc, sizeof(int), cudaMemcpyDeviceToHost, s));
     if (No > 0) {
+        if (Nc >= (1 << 30)) return (int)cudaErrorInvalidValue;
+        prep_camk_kernel<<<cdivp(No, 256), 256, 0, s>>>(No, out.pm_cam, out.cam_kind, out.pm_camk);
         prep_cam_keys_kernel<<<cdivp(No, 256), 256, 0, s>>>(No, Nc, out.pm_cam, out.cam_kind, key0, idx0);
         PCU(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, key0, key1, idx0, idx1, No, 0, bits, s));
     }

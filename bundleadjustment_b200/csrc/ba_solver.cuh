@@ -92,6 +92,7 @@ struct Ctx {
     // landmark-major observations (sorted by landmark, then camera)
     const float2 *pm_uv;
     const int *pm_cam;
+    const unsigned *pm_camk; // [No] camera | kind << 30 (CAM_* of that camera): what the per-observation kernels read
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
@@ -105,7 +106,8 @@ struct Ctx {
     const int *cam_chunk_ptr;                       // [Nc+1] chunk range per camera
     PairIndex pairs;         // dense Schur only (built on first use)
     // per-camera tables at x and at the candidate
-    CamEntry *tab_x, *tab_c;
+    CamEntry *tab_x;         // linearisation point
+    CamProj *tab_c;          // candidate point (cost only)
     // Jacobi scaling
     double *scale_cam, *scale_pt;
     // normal-equation blocks (scaled space)
