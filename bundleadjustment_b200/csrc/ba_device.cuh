@@ -113,6 +113,15 @@ __device__ __forceinline__ void bulk_store(void *gdst, const void *smem_src, uns
     asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
 }
 
+// split form: bulk_store_begin after the CTA barrier that ordered the writes of the tile, bulk_store_end (same thread) before
+// the CTA exits or reuses the buffer -- whatever lies between overlaps with the drain of the tile
+__device__ __forceinline__ void bulk_store_begin(void *gdst, const void *smem_src, unsigned bytes) {
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(smem_addr(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store_end() { asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory"); }
+
 // the copy alone (no fence / commit / wait): for callers that batch several copies into one group and double buffer
 __device__ __forceinline__ void bulk_store_issue(void *gdst, const void *smem_src, unsigned bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gdst), "r"(smem_addr(smem_src)), "r"(bytes) : "memory");

@@ -7,6 +7,7 @@
 #include "ba_launch.h"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace ba {
 
@@ -98,9 +99,15 @@ __device__ __forceinline__ Tile tile_of(const Ctx &ctx, int b) {
     return t;
 }
 // n records of 18 doubles between global W (at observation o0) and shared memory: one TMA bulk copy each way.
-// tile_store_W: call after a CTA barrier that follows the last write of sW; only thread 0 does anything.
-__device__ __forceinline__ void tile_store_W(double *__restrict__ W, int o0, int n, const double *__restrict__ sW) {
-    if (threadIdx.x == 0 && n > 0) bulk_store(W + 18 * (size_t)o0, sW, 144u * (unsigned)n);
+// tile_store_W_begin: call after a CTA barrier that follows the last write of sW; tile_store_W_end: before the CTA exits.
+// Only thread 0 does anything; the wait sits at the very end so that the per-landmark sums and the block reduction overlap
+// with the drain of the tile (thread 0 waiting right after the issue held the whole CTA at its last barrier: 27 % of the
+// kernel's stall samples).
+__device__ __forceinline__ void tile_store_W_begin(double *__restrict__ W, int o0, int n, const double *__restrict__ sW) {
+    if (threadIdx.x == 0 && n > 0) bulk_store_begin(W + 18 * (size_t)o0, sW, 144u * (unsigned)n);
+}
+__device__ __forceinline__ void tile_store_W_end() {
+    if (threadIdx.x == 0) bulk_store_end();
 }
 // tile_load_W: starts the copy (thread 0) and returns; every thread calls tile_wait_W before touching sW.  bar is a shared
 // 8-byte word used for this one transfer.
@@ -113,7 +120,8 @@ __device__ __forceinline__ void tile_wait_W(unsigned long long *bar) { mbar_wait
 
 // C1+C2+C3 (landmark side): residual, analytic Jacobian, Huber corrector, Jacobi scaling per observation;
 // W = Jc^T Jp per observation; V_p, b_p per landmark; cost and gradient-norm partials per block.
-__global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx ctx, int force) {
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
     extern __shared__ __align__(16) double tsm[];
@@ -174,7 +182,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
         for (int q = 0; q < 9; ++q) Wo2[q] = make_double2(wr[2 * q], wr[2 * q + 1]);
     }
     __syncthreads();
-    tile_store_W(ctx.W, t.o0, t.n, sW);            // TMA store by thread 0; the others go on with the per-landmark sums
+    tile_store_W_begin(ctx.W, t.o0, t.n, sW);      // TMA store issued by thread 0; everybody goes on with the per-landmark sums
     for (int p = p_mine; p < t.p1; p += blockDim.x) {
         const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - t.o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - t.o0;
         double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
@@ -207,6 +215,7 @@ __global__ void __launch_bounds__(TILE_THREADS, 3) linearize_points_kernel(Ctx c
         double4 *pp = reinterpret_cast<double4 *>(ctx.part + 4 * (size_t)blockIdx.x);
         *pp = make_double4(cost, gsq, xsq, gmax);
     }
+    tile_store_W_end();                            // shared memory must stay intact until the copy engine has read the tile
 }
 
 // -------------------------------------------------------------------------------------------------------------
@@ -935,7 +944,9 @@ static inline size_t tile_smem(const Ctx &ctx, int doubles_per_obs) { return siz
 int tiles_init(const Ctx &ctx) {
     const size_t need = tile_smem(ctx, 27);
     if (need > 227 * 1024) return (int)cudaErrorInvalidConfiguration;
-    cudaError_t e = cudaFuncSetAttribute(linearize_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    cudaError_t e = cudaFuncSetAttribute(linearize_points_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(linearize_points_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem(ctx, 21));
     if (e != cudaSuccess) return (int)e;
@@ -963,7 +974,11 @@ void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
 // landmark + camera side of one linearisation (local part; the caller all-reduces U/bc/sums when sharded)
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
-    if (ctx.n_blocks > 0) linearize_points_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+    if (ctx.n_blocks > 0) {
+        static const int min_ctas = [] { const char *v = std::getenv("BA_B200_LIN_CTAS"); return v ? std::atoi(v) : 3; }();   // measurement aid
+        if (min_ctas == 2) linearize_points_kernel<2><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+        else linearize_points_kernel<3><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+    }
     if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<red_grid(ctx.n_part, 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force);
