@@ -415,21 +415,19 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     // ---- parameters and constants ----
     // one H2D copy each; the two working buffers are filled device-to-device
     UP(cam_init, cam, 6 * (size_t)Nc); UP(pt_init, pt, 3 * (size_t)Np);
-    AL(cam0, 8 * 6 * (size_t)Nc); AL(cam1, 8 * 6 * (size_t)Nc); AL(pt0, 8 * PT_LD * (size_t)Np); AL(pt1, 8 * PT_LD * (size_t)Np);   // rows padded to PT_LD doubles
+    AL(cam0, 8 * 6 * (size_t)Nc); AL(cam1, 8 * 6 * (size_t)Nc); AL(pt0, 8 * 3 * (size_t)Np); AL(pt1, 8 * 3 * (size_t)Np);
     CU(cudaMemcpyAsync(h->cam0.p, h->cam_init.p, 8 * 6 * (size_t)Nc, cudaMemcpyDeviceToDevice, s));
     CU(cudaMemcpyAsync(h->cam1.p, h->cam_init.p, 8 * 6 * (size_t)Nc, cudaMemcpyDeviceToDevice, s));
     if (Np) {
-        CU(cudaMemsetAsync(h->pt0.p, 0, 8 * PT_LD * (size_t)Np, s));
-        CU(cudaMemsetAsync(h->pt1.p, 0, 8 * PT_LD * (size_t)Np, s));
-        launch_pt_unpack(h->pt0.as<double>(), h->pt_init.as<double>(), Np, s);
-        launch_pt_unpack(h->pt1.as<double>(), h->pt_init.as<double>(), Np, s);
+        CU(cudaMemcpyAsync(h->pt0.p, h->pt_init.p, 8 * 3 * (size_t)Np, cudaMemcpyDeviceToDevice, s));
+        CU(cudaMemcpyAsync(h->pt1.p, h->pt_init.p, 8 * 3 * (size_t)Np, cudaMemcpyDeviceToDevice, s));
     }
     UP(cam_K, K, 9 * (size_t)Nc);
     if (fixed_extr) { UP(cam_extr, fixed_extr, 16 * (size_t)Nc); }
     else { AL(cam_extr, 64 * (size_t)Nc); CU(cudaMemsetAsync(h->cam_extr.p, 0, 64 * (size_t)Nc, s)); }
 #undef UP
     AL(tab_x, sizeof(CamEntry) * (size_t)Nc); AL(tab_c, sizeof(CamProj) * (size_t)Nc);
-    AL(scale_cam, 8 * 6 * (size_t)Nc); AL(scale_pt, 8 * PT_LD * (size_t)Np);
+    AL(scale_cam, 8 * 6 * (size_t)Nc); AL(scale_pt, 8 * 3 * (size_t)Np);
     AL(U, 8 * 36 * (size_t)Nc); AL(bc, 8 * 6 * (size_t)Nc); AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
     AL(W, 8 * 18 * (size_t)No + 64);     /* + slack: rows are fetched as aligned 32-byte windows (load_row18) */ AL(cam_part, 8 * 27 * (size_t)std::max(ctx.n_chunks, 1));
     AL(Vinv, 8 * 6 * (size_t)Np + 64); AL(wv, 8 * 3 * (size_t)Np);
@@ -480,7 +478,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     CU(cudaMemsetAsync(h->camsums.p, 0, 8 * CS_COUNT, s));
     launch_init_state(ctx, s);
     launch_fill(ctx.scale_cam, 6 * (size_t)Nc, 1.0, s);
-    launch_fill(ctx.scale_pt, PT_LD * (size_t)Np, 1.0, s);
+    launch_fill(ctx.scale_pt, 3 * (size_t)Np, 1.0, s);
     launch_cam_prep(ctx, 0, 1, s);      // K / fixed extrinsics of both tables are written once here
     launch_cam_prep(ctx, 1, 1, s);
     CU(cudaStreamSynchronize(s));       // the caller may free / reuse its arrays after the call returns
@@ -508,7 +506,7 @@ extern "C" int ba_reset_parameters(ba_handle *h) {
     cudaStream_t s = h->stream;
     for (int b = 0; b < 2; ++b) {
         CU(cudaMemcpyAsync(ctx.cam[b], ctx.cam_init, 8 * 6 * (size_t)ctx.Nc, cudaMemcpyDeviceToDevice, s));
-        launch_pt_unpack(ctx.pt[b], ctx.pt_init, ctx.Np, s);
+        if (ctx.Np) CU(cudaMemcpyAsync(ctx.pt[b], ctx.pt_init, 8 * 3 * (size_t)ctx.Np, cudaMemcpyDeviceToDevice, s));
     }
     launch_init_state(ctx, s);
     return BA_OK;
@@ -595,10 +593,7 @@ int enqueue_linear_solve(ba_handle *h) {
         launch_pcg_start(ctx, s);
         h->launches += 2;
         const int max_it = std::max(1, h->opt.max_linear_solver_iterations);
-        // The host runs R CG iterations ahead of the verdict it polls; whatever it enqueues past convergence early-exits on the
-        // device but still costs full-grid launches (~0.1 ms per iteration on K5).  One iteration of a large problem takes far
-        // longer than enqueueing the next, so two ahead keeps the stream fed there; small problems keep the deeper queue.
-        const int R = ctx.No >= (1 << 20) ? 2 : 4;
+        const int R = 4;
         for (int it = 1; it <= max_it; ++it) {
             if (it > R) {
                 CU(cudaEventSynchronize(h->ev_ring[it % R]));
@@ -646,7 +641,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
     CU(cudaEventRecord(h->ev_start, s));
     launch_init_state(ctx, s);
     launch_fill(ctx.scale_cam, 6 * (size_t)ctx.Nc, 1.0, s);
-    launch_fill(ctx.scale_pt, PT_LD * (size_t)ctx.Np, 1.0, s);
+    launch_fill(ctx.scale_pt, 3 * (size_t)ctx.Np, 1.0, s);
     h->launches += 3;
     if (h->opt.jacobi_scaling) {
         // iteration 0: column norms of the unscaled (robustified) Jacobian -> Jacobi scaling, fixed thereafter
@@ -747,11 +742,7 @@ extern "C" int ba_get_points(ba_handle *h, double *pt) {
     CU(cudaSetDevice(h->device));
     LMState st;
     CU(cudaMemcpy(&st, h->ctx.state, sizeof(st), cudaMemcpyDeviceToHost));
-    if (h->ctx.Np) {     // tight copy on the device, then one flat transfer
-        launch_pt_pack(h->ctx.tp, h->ctx.pt[st.cur], h->ctx.Np, h->stream);
-        CU(cudaMemcpyAsync(pt, h->ctx.tp, 8 * 3 * (size_t)h->ctx.Np, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-    }
+    if (h->ctx.Np) CU(cudaMemcpy(pt, h->ctx.pt[st.cur], 8 * 3 * (size_t)h->ctx.Np, cudaMemcpyDeviceToHost));
     return BA_OK;
 }
 
@@ -796,7 +787,7 @@ extern "C" int ba_evaluate(ba_handle *h, double *cost, double *residuals, double
     // gradient: unscaled blocks b_c, b_p of a forced linearisation with unit scale
     if (grad_cam || grad_pt) {
         launch_fill(ctx.scale_cam, 6 * (size_t)Nc, 1.0, s);
-        launch_fill(ctx.scale_pt, PT_LD * (size_t)Np, 1.0, s);
+        launch_fill(ctx.scale_pt, 3 * (size_t)Np, 1.0, s);
         if ((rc = enqueue_linearize(h, 1))) return rc;
     }
     CU(cudaStreamSynchronize(s));
@@ -873,7 +864,7 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
     int rc;
     if ((rc = ensure_dense(h))) return rc;
     launch_fill(ctx.scale_cam, 6 * (size_t)ctx.Nc, 1.0, s);
-    launch_fill(ctx.scale_pt, PT_LD * (size_t)ctx.Np, 1.0, s);
+    launch_fill(ctx.scale_pt, 3 * (size_t)ctx.Np, 1.0, s);
     if ((rc = enqueue_linearize(h, 1))) return rc;
     if (h->opt.jacobi_scaling) {
         launch_compute_scale(ctx, s);

@@ -54,18 +54,6 @@ __device__ __forceinline__ void load_vec4(const double *__restrict__ src, double
     }
 }
 
-// Landmark rows (the two parameter buffers pt[2] and the Jacobi scales scale_pt) are PADDED to 4 doubles = one aligned 32-byte
-// sector: a per-lane gather of a landmark is one 256-bit load instead of three 64-bit ones (an L1 pass per instruction and lane).
-constexpr int PT_LD = 4;
-__device__ __forceinline__ void load_pt(const double *__restrict__ base, size_t p, double (&X)[3]) {
-    const Double4 v = *reinterpret_cast<const Double4 *>(base + PT_LD * p);
-    X[0] = v.x; X[1] = v.y; X[2] = v.z;
-}
-__device__ __forceinline__ void store_pt(double *__restrict__ base, size_t p, double x0, double x1, double x2) {
-    Double4 v; v.x = x0; v.y = x1; v.z = x2; v.w = 0.0;
-    *reinterpret_cast<Double4 *>(base + PT_LD * p) = v;
-}
-
 // Row `row` of a [.][18]-double array (W: 144-byte rows, so odd rows start 16 bytes off a 32-byte boundary) as five 256-bit
 // loads of the enclosing 32-byte-aligned window + a parity select.  A per-lane gather costs one L1 sector request per load
 // instruction and lane, whatever the width: 5 requests instead of 9 (128-bit) or 18 (64-bit).  The array needs 16 bytes of

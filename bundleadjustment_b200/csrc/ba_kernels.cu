@@ -140,10 +140,8 @@ __global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kerne
         const unsigned ck = ctx.pm_camk[o];
         const int c = camk_cam(ck), kind = camk_kind(ck), p = ctx.pm_pt[o];
         const float2 uv = ctx.pm_uv[o];
-        double X[3];
-        load_pt(ptx, (size_t)p, X);
-        double sp[3];
-        load_pt(ctx.scale_pt, (size_t)p, sp);
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
         double r[2], Jc[12], Jp[6], sc[6];
         obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp, sc);
         double rho0;
@@ -196,8 +194,8 @@ __global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kerne
         if (hi > lo) {
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
-                const double x = ptx[PT_LD * (size_t)p + j];
-                const double g = b[j] / ctx.scale_pt[PT_LD * (size_t)p + j];
+                const double x = ptx[3 * (size_t)p + j];
+                const double g = b[j] / ctx.scale_pt[3 * (size_t)p + j];
                 const double d = x - (x + (-g));
                 gsq += d * d;
                 gmax = fmax(gmax, fabs(d));
@@ -254,8 +252,7 @@ __global__ void __launch_bounds__(CAMS_WARPS * 32, 5) linearize_cams_kernel(Ctx 
         if (e < end) {
             const int p = ctx.cm_pt[e];
             const float2 uv = ctx.cm_uv[e];
-            double X[3];
-        load_pt(ptx, (size_t)p, X);
+            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
             double Jp[6], sc[6];
             obs_linearize<true, false>(ce, CAM_FREE, X, uv, r, Jc, Jp, sc);
             double rho0;
@@ -354,19 +351,11 @@ __global__ void compute_scale_kernel(Ctx ctx) {
         ctx.scale_cam[i] = (ctx.cam_kind[c] == CAM_FREE) ? 1.0 / (1.0 + sqrt(ctx.U[36 * (size_t)c + a * 6 + a])) : 1.0;
     }
     if (i < 3 * ctx.Np) {
-        const int p = i / 3, a = i % 3;       // (rows of scale_pt are padded to PT_LD)
+        const int p = i / 3, a = i % 3;
         const int idx = (a == 0) ? 0 : (a == 1 ? 3 : 5);
         const bool active = ctx.pt_ptr[p + 1] > ctx.pt_ptr[p];
-        ctx.scale_pt[PT_LD * (size_t)p + a] = active ? 1.0 / (1.0 + sqrt(ctx.V[6 * (size_t)p + idx])) : 1.0;
+        ctx.scale_pt[i] = active ? 1.0 / (1.0 + sqrt(ctx.V[6 * (size_t)p + idx])) : 1.0;
     }
-}
-
-// landmark rows between the caller's tight [Np][3] layout and the padded [Np][PT_LD] working layout
-__global__ void pt_repack_kernel(double *__restrict__ dst, const double *__restrict__ src, int Np, int dst_ld, int src_ld) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 3 * Np) return;
-    const int p = i / 3, a = i % 3;
-    dst[(size_t)dst_ld * p + a] = src[(size_t)src_ld * p + a];
 }
 
 __global__ void fill_kernel(double *p, size_t n, double v) {
@@ -592,7 +581,7 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     if (p_mine < t.p1) {
         lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0;
         prefetch_l2(ctx.Vinv + 6 * (size_t)p_mine); prefetch_l2(ctx.V + 6 * (size_t)p_mine);
-        prefetch_l2(ctx.bp + 3 * (size_t)p_mine); prefetch_l2(ptx + PT_LD * (size_t)p_mine); prefetch_l2(ctx.scale_pt + PT_LD * (size_t)p_mine);
+        prefetch_l2(ctx.bp + 3 * (size_t)p_mine); prefetch_l2(ptx + 3 * (size_t)p_mine); prefetch_l2(ctx.scale_pt + 3 * (size_t)p_mine);
     }
     tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
@@ -615,8 +604,7 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     double dxsq = 0, yb = 0, yhy = 0;
     for (int p = p_mine; p < t.p1; p += blockDim.x) {
         const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - t.o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - t.o0;
-        double X[3];
-        load_pt(ptx, (size_t)p, X);
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         if (hi > lo) {
             double a3[3] = {0, 0, 0};
             for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
@@ -630,14 +618,13 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
             yb += y0 * b[0] + y1 * b[1] + y2 * b[2];
             yhy += y0 * (V[0] * y0 + V[1] * y1 + V[2] * y2) + y1 * (V[1] * y0 + V[3] * y1 + V[4] * y2) +
                    y2 * (V[2] * y0 + V[4] * y1 + V[5] * y2) + 2.0 * (a3[0] * y0 + a3[1] * y1 + a3[2] * y2);
-            double sp[3];
-            load_pt(ctx.scale_pt, (size_t)p, sp);
+            const double *sp = ctx.scale_pt + 3 * (size_t)p;
             const double c0 = X[0] + (-y0) * sp[0], c1 = X[1] + (-y1) * sp[1], c2 = X[2] + (-y2) * sp[2];
-            store_pt(ptc, (size_t)p, c0, c1, c2);
+            ptc[3 * (size_t)p] = c0; ptc[3 * (size_t)p + 1] = c1; ptc[3 * (size_t)p + 2] = c2;
             const double d0 = X[0] - c0, d1 = X[1] - c1, d2 = X[2] - c2;
             dxsq += d0 * d0 + d1 * d1 + d2 * d2;
         } else {
-            store_pt(ptc, (size_t)p, X[0], X[1], X[2]);
+            ptc[3 * (size_t)p] = X[0]; ptc[3 * (size_t)p + 1] = X[1]; ptc[3 * (size_t)p + 2] = X[2];
         }
     }
     double unused = 0.0;
@@ -709,8 +696,7 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
     const int o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o < ctx.No) {
         const int c = camk_cam(ctx.pm_camk[o]), p = ctx.pm_pt[o];
-        double X[3];
-        load_pt(ptc, (size_t)p, X);
+        const double X[3] = {ptc[3 * (size_t)p], ptc[3 * (size_t)p + 1], ptc[3 * (size_t)p + 2]};
         double r[2];
         obs_residual(ctx.tab_c + c, X, ctx.pm_uv[o], r);
         double rho0;
@@ -898,8 +884,7 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
         }
         double r[2] = {0, 0}, Jc[12], Jp[6], sr = 0.0;
         if (lane < n) {
-            double X[3];
-        load_pt(ptx, (size_t)p, X);
+            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
             obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
             double rho0;
             const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
@@ -958,13 +943,6 @@ void launch_init_state(const Ctx &ctx, cudaStream_t s) { lm_init_state_kernel<<<
 void launch_fill(double *p, size_t n, double v, cudaStream_t s) {
     if (n == 0) return;
     fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
-}
-
-void launch_pt_unpack(double *padded, const double *tight, int Np, cudaStream_t s) {     // pad column stays as it is (zero)
-    if (Np > 0) pt_repack_kernel<<<cdiv(3 * Np, 256), 256, 0, s>>>(padded, tight, Np, PT_LD, 3);
-}
-void launch_pt_pack(double *tight, const double *padded, int Np, cudaStream_t s) {
-    if (Np > 0) pt_repack_kernel<<<cdiv(3 * Np, 256), 256, 0, s>>>(tight, padded, Np, 3, PT_LD);
 }
 
 void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {

@@ -11,8 +11,6 @@ namespace ba {
 void launch_init_state(const Ctx &ctx, cudaStream_t s);
 void launch_fill(double *p, size_t n, double v, cudaStream_t s);
 void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s);
-void launch_pt_unpack(double *padded, const double *tight, int Np, cudaStream_t s);   // [Np][3] -> [Np][PT_LD]
-void launch_pt_pack(double *tight, const double *padded, int Np, cudaStream_t s);     // [Np][PT_LD] -> [Np][3]
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s);
 void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s);
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s);
