@@ -593,7 +593,10 @@ int enqueue_linear_solve(ba_handle *h) {
         launch_pcg_start(ctx, s);
         h->launches += 2;
         const int max_it = std::max(1, h->opt.max_linear_solver_iterations);
-        const int R = 4;
+        // The host runs R CG iterations ahead of the verdict it polls; whatever it enqueues past convergence early-exits on the
+        // device but still costs full-grid launches (~0.1 ms per iteration on K5).  One iteration of a large problem takes far
+        // longer than enqueueing the next, so two ahead keeps the stream fed there; small problems keep the deeper queue.
+        const int R = ctx.No >= (1 << 20) ? 2 : 4;
         for (int it = 1; it <= max_it; ++it) {
             if (it > R) {
                 CU(cudaEventSynchronize(h->ev_ring[it % R]));

@@ -54,6 +54,11 @@ __device__ __forceinline__ void load_vec4(const double *__restrict__ src, double
     }
 }
 
+// landmark p of a tight [.][3] parameter array
+__device__ __forceinline__ void load_pt(const double *__restrict__ base, size_t p, double (&X)[3]) {
+    X[0] = base[3 * p]; X[1] = base[3 * p + 1]; X[2] = base[3 * p + 2];
+}
+
 // Row `row` of a [.][18]-double array (W: 144-byte rows, so odd rows start 16 bytes off a 32-byte boundary) as five 256-bit
 // loads of the enclosing 32-byte-aligned window + a parity select.  A per-lane gather costs one L1 sector request per load
 // instruction and lane, whatever the width: 5 requests instead of 9 (128-bit) or 18 (64-bit).  The array needs 16 bytes of

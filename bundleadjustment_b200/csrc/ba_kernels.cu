@@ -230,7 +230,8 @@ __device__ __forceinline__ void dmma884_acc(double &c0, double &c1, double a, do
                  : "+d"(c0), "+d"(c1)
                  : "d"(a), "d"(b));
 }
-__global__ void __launch_bounds__(CAMS_WARPS * 32, 5) linearize_cams_kernel(Ctx ctx, int force) {
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(CAMS_WARPS * 32, MIN_CTAS) linearize_cams_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && (st->done || !st->need_linearize)) return;
     __shared__ __align__(16) double sJ[CAMS_WARPS][7 * CAMS_LD];       // [column a of [Jc | r]][k = 2 lane + row]
@@ -244,15 +245,19 @@ __global__ void __launch_bounds__(CAMS_WARPS * 32, 5) linearize_cams_kernel(Ctx 
     const double *ptx = ctx.pt[st->cur];
     double *Js = sJ[warp];
     double acc[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};                // C[g][2 tig], C[g][2 tig + 1]: four independent DMMA chains
+    // the next batch's pixel and landmark are fetched while this batch is evaluated (index -> landmark is a dependent chain)
+    float2 uv_n = make_float2(0.f, 0.f);
+    double Xn[3] = {0.0, 0.0, 0.0};
+    if (beg + lane < end) { uv_n = ctx.cm_uv[beg + lane]; load_pt(ptx, (size_t)ctx.cm_pt[beg + lane], Xn); }
     for (int base = beg; base < end; base += 32) {
         const int e = base + lane;
         double r[2] = {0.0, 0.0}, Jc[12];
 #pragma unroll
         for (int a = 0; a < 12; ++a) Jc[a] = 0.0;
+        const float2 uv = uv_n;
+        const double X[3] = {Xn[0], Xn[1], Xn[2]};
+        if (e + 32 < end) { uv_n = ctx.cm_uv[e + 32]; load_pt(ptx, (size_t)ctx.cm_pt[e + 32], Xn); }
         if (e < end) {
-            const int p = ctx.cm_pt[e];
-            const float2 uv = ctx.cm_uv[e];
-            const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
             double Jp[6], sc[6];
             obs_linearize<true, false>(ce, CAM_FREE, X, uv, r, Jc, Jp, sc);
             double rho0;
@@ -687,21 +692,32 @@ __global__ void __launch_bounds__(128) cam_update_kernel(Ctx ctx) {
 // -------------------------------------------------------------------------------------------------------------
 // C8 (ii): cost-only evaluation at the candidate, one thread per observation (landmark-major order)
 // -------------------------------------------------------------------------------------------------------------
+// Persistent (grid-stride) with the next observation's index triplet prefetched: the chain  index -> gathers -> arithmetic
+// of one observation overlaps with the index load of the next instead of being paid per CTA.
 __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *part_out) {
     const LMState *st = ctx.state;
     if (st->done) return;
     __shared__ double red[32];
     const double *ptc = ctx.pt[st->cur ^ 1];
     double cost = 0.0;
-    const int o = blockIdx.x * blockDim.x + threadIdx.x;
-    if (o < ctx.No) {
-        const int c = camk_cam(ctx.pm_camk[o]), p = ctx.pm_pt[o];
-        const double X[3] = {ptc[3 * (size_t)p], ptc[3 * (size_t)p + 1], ptc[3 * (size_t)p + 2]};
+    const int stride = gridDim.x * blockDim.x;
+    int o = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned ck_n = 0u;
+    int p_n = 0;
+    float2 uv_n = make_float2(0.f, 0.f);
+    if (o < ctx.No) { ck_n = ctx.pm_camk[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
+    for (; o < ctx.No; o += stride) {
+        const int c = camk_cam(ck_n), p = p_n;
+        const float2 uv = uv_n;
+        const int on = o + stride;
+        if (on < ctx.No) { ck_n = ctx.pm_camk[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
+        double X[3];
+        load_pt(ptc, (size_t)p, X);
         double r[2];
-        obs_residual(ctx.tab_c + c, X, ctx.pm_uv[o], r);
+        obs_residual(ctx.tab_c + c, X, uv, r);
         double rho0;
         huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
-        cost = 0.5 * rho0;
+        cost += 0.5 * rho0;
     }
     cost = block_sum(cost, red);
     if (threadIdx.x == 0) part_out[blockIdx.x] = cost;
@@ -953,11 +969,17 @@ void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
     if (ctx.n_blocks > 0) {
-        static const int min_ctas = [] { const char *v = std::getenv("BA_B200_LIN_CTAS"); return v ? std::atoi(v) : 3; }();   // measurement aid
-        if (min_ctas == 2) linearize_points_kernel<2><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
-        else linearize_points_kernel<3><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+        // 2 CTAs/SM at 128 registers (no spills) beat 3 CTAs/SM at 80 registers + 128 B of spills by 4-5 % (K4 and K5);
+        // BA_B200_LIN_CTAS=3 selects the other instantiation (measurement aid)
+        static const int min_ctas = [] { const char *v = std::getenv("BA_B200_LIN_CTAS"); return v ? std::atoi(v) : 2; }();
+        if (min_ctas == 3) linearize_points_kernel<3><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+        else linearize_points_kernel<2><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
     }
-    if (ctx.n_chunks > 0) linearize_cams_kernel<<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
+    if (ctx.n_chunks > 0) {
+        static const int min_ctas = [] { const char *v = std::getenv("BA_B200_CAMS_CTAS"); return v ? std::atoi(v) : 4; }();   // measurement aid
+        if (min_ctas == 5) linearize_cams_kernel<5><<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
+        else linearize_cams_kernel<4><<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
+    }
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<red_grid(ctx.n_part, 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force);
 }
@@ -1010,7 +1032,15 @@ void launch_backsub(const Ctx &ctx, cudaStream_t s) {
 }
 
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s) {
-    const int nb = cdiv(ctx.No, 256);
+    static int resident = 0;                      // CTAs of the persistent grid: every SM full
+    if (!resident) {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, eval_candidate_kernel, 256, 0);
+        resident = std::max(1, sms * std::max(per_sm, 1));
+    }
+    const int nb = std::min(cdiv(ctx.No, 256), resident);
     if (nb > 0) eval_candidate_kernel<<<nb, 256, 0, s>>>(ctx, cost_part);
     reduce_step_partials_kernel<<<red_grid(std::max(ctx.n_part, nb), 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, cost_part, nb);
 }

@@ -32,8 +32,11 @@ __global__ void __launch_bounds__(128) pcg_setup_cams_kernel(Ctx ctx) {
     double acc[27];
 #pragma unroll
     for (int k = 0; k < 27; ++k) acc[k] = 0.0;
+    int e_n = 0, p_n = 0;                                  // indices one iteration ahead: they head a dependent chain
+    if (beg + lane < end) { e_n = ctx.cm_obs[beg + lane]; p_n = ctx.cm_pt[beg + lane]; }
     for (int d = beg + lane; d < end; d += 32) {
-        const int e = ctx.cm_obs[d], p = ctx.cm_pt[d];
+        const int e = e_n, p = p_n;
+        if (d + 32 < end) { e_n = ctx.cm_obs[d + 32]; p_n = ctx.cm_pt[d + 32]; }
         double wv[18], vi[6];                              // gathers as aligned 256-bit windows (7 requests instead of 12)
         load_row18(ctx.W, (size_t)e, wv);
         load_row6(ctx.Vinv, (size_t)p, vi);
