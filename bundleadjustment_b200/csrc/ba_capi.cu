@@ -102,7 +102,7 @@ struct ba_handle {
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
-    DevBuf cm_obs, blk_first_pt, blk_info, pm_camk;
+    DevBuf cm_obs, blk_first_pt, blk_info, pm_camk, pm_trk;
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
     DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
     DevBuf part, cost_part, red_part, red_count, sums, maxs, camsums, state, iters, invL, U_loc, bc_loc, sums_loc, maxs_loc;
@@ -137,7 +137,7 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &red_part, &red_count, &sums, &maxs,
                          &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
         for (DevBuf *b : all) b->free();
         chol_plan_destroy(&chol_plan);
         scr.release(); scr2.release();
@@ -371,7 +371,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(pm_uv, 8 * (size_t)No); AL(pm_cam, 4 * (size_t)No); AL(pm_pt, 4 * (size_t)No); AL(pt_ptr, 4 * (size_t)(Np + 1));
     AL(perm_dev, 4 * (size_t)No); AL(cnt_cam, 4 * (size_t)Nc); AL(cnt_cam_global, 4 * (size_t)Nc); AL(cam_kind, 4 * (size_t)Nc);
     AL(cam_ptr, 4 * (size_t)(Nc + 1)); AL(cam_chunk_ptr, 4 * (size_t)(Nc + 1)); AL(cm_uv, 8 * (size_t)No); AL(cm_pt, 4 * (size_t)No);
-    AL(cm_obs, 4 * (size_t)No); AL(blk_first_pt, 4 * ((size_t)No / TILE_WIN + 2)); AL(blk_info, 16 * ((size_t)No / TILE_WIN + 2)); AL(pm_camk, 4 * (size_t)No);
+    AL(cm_obs, 4 * (size_t)No); AL(blk_first_pt, 4 * ((size_t)No / TILE_WIN + 2)); AL(blk_info, 16 * ((size_t)No / TILE_WIN + 2)); AL(pm_camk, 4 * (size_t)No); AL(pm_trk, 4 * (size_t)No);
     AL(chunk_cam, 4 * max_chunks); AL(chunk_beg, 4 * max_chunks); AL(chunk_end, 4 * max_chunks); AL(prep_flags, 16);
     PrepIn &pin = h->prep_in;
     PrepOut &po = h->prep_out;
@@ -382,7 +382,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     po.perm = h->perm_dev.as<int>(); po.cnt_cam = h->cnt_cam.as<int>(); po.cnt_cam_global = h->cnt_cam_global.as<int>();
     po.cam_kind = h->cam_kind.as<int>(); po.cam_ptr = h->cam_ptr.as<int>(); po.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
     po.cm_uv = h->cm_uv.as<float2>(); po.cm_pt = h->cm_pt.as<int>(); po.cm_obs = h->cm_obs.as<int>();
-    po.blk_first_pt = h->blk_first_pt.as<int>(); po.blk_info = h->blk_info.as<int4>(); po.pm_camk = h->pm_camk.as<unsigned>();
+    po.blk_first_pt = h->blk_first_pt.as<int>(); po.blk_info = h->blk_info.as<int4>(); po.pm_camk = h->pm_camk.as<unsigned>(); po.pm_trk = h->pm_trk.as<unsigned>();
     po.chunk_cam = h->chunk_cam.as<int>(); po.chunk_beg = h->chunk_beg.as<int>(); po.chunk_end = h->chunk_end.as<int>();
     po.flags = h->prep_flags.as<int>(); po.h_flags = h->h_prep;
     rc = prep_observations(pin, po, h->scr, s);
@@ -448,7 +448,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.pt_ptr = h->pt_ptr.as<int>(); ctx.cm_uv = h->cm_uv.as<float2>(); ctx.cm_pt = h->cm_pt.as<int>();
     ctx.chunk_cam = h->chunk_cam.as<int>(); ctx.chunk_beg = h->chunk_beg.as<int>(); ctx.chunk_end = h->chunk_end.as<int>();
     ctx.cam_chunk_ptr = h->cam_chunk_ptr.as<int>();
-    ctx.cm_obs = h->cm_obs.as<int>(); ctx.blk_first_pt = h->blk_first_pt.as<int>(); ctx.blk_info = h->blk_info.as<int4>(); ctx.pm_camk = h->pm_camk.as<unsigned>();
+    ctx.cm_obs = h->cm_obs.as<int>(); ctx.blk_first_pt = h->blk_first_pt.as<int>(); ctx.blk_info = h->blk_info.as<int4>(); ctx.pm_camk = h->pm_camk.as<unsigned>(); ctx.pm_trk = h->pm_trk.as<unsigned>();
     ctx.tab_x = h->tab_x.as<CamEntry>(); ctx.tab_c = h->tab_c.as<CamProj>();
     ctx.scale_cam = h->scale_cam.as<double>(); ctx.scale_pt = h->scale_pt.as<double>();
     ctx.U = h->U.as<double>(); ctx.bc = h->bc.as<double>(); ctx.V = h->V.as<double>(); ctx.bp = h->bp.as<double>();

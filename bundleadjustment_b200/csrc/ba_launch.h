@@ -43,7 +43,7 @@ struct PrepIn {
 };
 struct PrepOut {
     // landmark-major
-    float2 *pm_uv; int *pm_cam, *pm_pt, *pt_ptr, *perm; unsigned *pm_camk;
+    float2 *pm_uv; int *pm_cam, *pm_pt, *pt_ptr, *perm; unsigned *pm_camk, *pm_trk;
     // cameras
     int *cnt_cam, *cnt_cam_global, *cam_kind, *cam_ptr, *cam_chunk_ptr;
     // camera-major

@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(CG_THREADS) pcg_precond_kernel(Ctx ctx, double
 // into shared memory) and serve both halves of the product: t_o = W_o^T v_c per observation, a_p = sum over the track
 // (in track order), s_p = V'^-1 a_p per landmark, then q_c -= W_o s_p per observation (fp64 reductions into the
 // L2-resident 6 Nc vector).
-__global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp) {
+__global__ void __launch_bounds__(TILE_THREADS, 5) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp) {
     const LMState *st = ctx.state;
     CG_GUARD(st);
     // the reductions go to one of CG_QCOPIES private copies of the vector (by CTA): when landmarks that are neighbours in
@@ -229,13 +229,15 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
     double *sW = tsm;                              // [cap][18]
     double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]
     const int4 bi = ctx.blk_info[blockIdx.x];
-    const int p0 = bi.x, p1 = bi.y, o0 = bi.z, n = bi.w;
+    const int o0 = bi.z, n = bi.w;
     if (n == 0) return;
-    const unsigned ck_first = threadIdx.x < n ? ctx.pm_camk[o0 + threadIdx.x] : 0u;      // in flight across the barrier below
-    // second phase (thread per landmark): track bounds now, V'^-1 on its way into L2
-    const int p_mine = p0 + threadIdx.x;
-    int lo_mine = 0, hi_mine = 0;
-    if (p_mine < p1) { lo_mine = ctx.pt_ptr[p_mine] - o0; hi_mine = ctx.pt_ptr[p_mine + 1] - o0; prefetch_l2(ctx.Vinv + 6 * (size_t)p_mine); }
+    // in flight across the barrier below: the thread's camera word, track word and landmark (V'^-1 on its way into L2)
+    unsigned ck_first = 0u, trk_first = 0u;
+    int p_first = 0;
+    if (threadIdx.x < n) {
+        ck_first = ctx.pm_camk[o0 + threadIdx.x]; trk_first = ctx.pm_trk[o0 + threadIdx.x]; p_first = ctx.pm_pt[o0 + threadIdx.x];
+        prefetch_l2(ctx.Vinv + 6 * (size_t)p_first);
+    }
     // the block's W records: one TMA bulk copy (thread 0) that streams in while the threads gather their camera entries of v
     __shared__ unsigned long long wbar;
     if (threadIdx.x == 0) mbar_init(&wbar, 1);
@@ -258,27 +260,27 @@ __global__ void __launch_bounds__(TILE_THREADS) pcg_matvec_points_kernel(Ctx ctx
         sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
     }
     __syncthreads();
-    for (int p = p_mine; p < p1; p += blockDim.x) {
-        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - o0;
-        if (hi <= lo) continue;
+    // Second half, still one thread per OBSERVATION and no further barrier: every thread sums its landmark's track in track
+    // order (the position/length word says where it starts: t shared-memory reads, the same for all observations of the
+    // landmark), applies V'^-1 and scatters W_o s_p.  Redundant per observation, but all eight warps work; the former
+    // thread-per-landmark pass kept two warps busy while six waited at a second barrier (33 % of the stall samples).
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+        if (camk_kind(ck) != CAM_FREE) continue;
+        const int c = camk_cam(ck);
+        const unsigned trk = i == (int)threadIdx.x ? trk_first : ctx.pm_trk[o0 + i];
+        const int p = i == (int)threadIdx.x ? p_first : ctx.pm_pt[o0 + i];
+        const int lo = i - (int)(trk & 0xffffu), hi = lo + (int)(trk >> 16);
+        double vi[6];
+        load_row6(ctx.Vinv, (size_t)p, vi);
         double a3[3] = {0, 0, 0};
         for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
-        const double *Vi = ctx.Vinv + 6 * (size_t)p;
-        const double t0 = Vi[0] * a3[0] + Vi[1] * a3[1] + Vi[2] * a3[2];
-        const double t1 = Vi[1] * a3[0] + Vi[3] * a3[1] + Vi[4] * a3[2];
-        const double t2 = Vi[2] * a3[0] + Vi[4] * a3[1] + Vi[5] * a3[2];
-        for (int k = lo; k < hi; ++k) { sT[3 * (size_t)k] = t0; sT[3 * (size_t)k + 1] = t1; sT[3 * (size_t)k + 2] = t2; }
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const int k = i;
-        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
-        const int c = camk_cam(ck);
-        if (camk_kind(ck) != CAM_FREE) continue;
-        const double t0 = sT[3 * (size_t)k], t1 = sT[3 * (size_t)k + 1], t2 = sT[3 * (size_t)k + 2];
+        const double t0 = vi[0] * a3[0] + vi[1] * a3[1] + vi[2] * a3[2];
+        const double t1 = vi[1] * a3[0] + vi[3] * a3[1] + vi[4] * a3[2];
+        const double t2 = vi[2] * a3[0] + vi[4] * a3[1] + vi[5] * a3[2];
         mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
         double Wo[18];
-        load_record18(sW, k, Wo);
+        load_record18(sW, i, Wo);
 #pragma unroll
         for (int a = 0; a < 6; ++a)
             atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));

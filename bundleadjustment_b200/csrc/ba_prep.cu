@@ -107,6 +107,17 @@ __global__ void prep_blocks_max_kernel(int n_blocks, const int *__restrict__ pt_
     atomicMax(mx, n);
 }
 
+// position of every landmark-major observation inside its track | track length << 16: the tile kernels' per-landmark work
+// is done by the thread of the track's FIRST observation (spread over all warps of the CTA) instead of a thread-per-landmark
+// pass that kept two warps busy while six waited at the next barrier
+__global__ void prep_trk_kernel(int No, const int *__restrict__ pm_pt, const int *__restrict__ pt_ptr, unsigned *__restrict__ pm_trk) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= No) return;
+    const int p = pm_pt[e];
+    const int lo = pt_ptr[p], len = pt_ptr[p + 1] - lo;
+    pm_trk[e] = (unsigned)min(e - lo, 0xffff) | ((unsigned)min(len, 0xffff) << 16);
+}
+
 // camera index and camera kind of every landmark-major observation in ONE word (kind << 30 | camera): the per-observation
 // kernels then need no dependent gather of cam_kind[camera] (a per-lane gather costs an L1 pass per instruction)
 __global__ void prep_camk_kernel(int No, const int *__restrict__ pm_cam, const int *__restrict__ kind, unsigned *__restrict__ pm_camk) {
@@ -276,6 +287,7 @@ int prep_blocks(const PrepIn &in, PrepOut &out, cudaStream_t s) {
     out.n_blocks = in.No / TILE_WIN + 1;
     PCU(cudaMemsetAsync(out.flags + 2, 0, sizeof(int), s));
     prep_blocks_kernel<<<cdivp(out.n_blocks + 1, 256), 256, 0, s>>>(out.n_blocks, in.Np, out.pt_ptr, out.blk_first_pt);
+    if (in.No > 0) prep_trk_kernel<<<cdivp(in.No, 256), 256, 0, s>>>(in.No, out.pm_pt, out.pt_ptr, out.pm_trk);
     prep_blocks_max_kernel<<<cdivp(out.n_blocks, 256), 256, 0, s>>>(out.n_blocks, out.pt_ptr, out.blk_first_pt, out.flags + 2, out.blk_info);
     PCU(cudaMemcpyAsync(out.h_flags + 4, out.flags + 2, sizeof(int), cudaMemcpyDeviceToHost, s));
     PCU(cudaStreamSynchronize(s));

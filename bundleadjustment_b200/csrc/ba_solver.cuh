@@ -93,6 +93,7 @@ struct Ctx {
     const float2 *pm_uv;
     const int *pm_cam;
     const unsigned *pm_camk; // [No] camera | kind << 30 (CAM_* of that camera): what the per-observation kernels read
+    const unsigned *pm_trk;  // [No] position inside the landmark's track | track length << 16
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
