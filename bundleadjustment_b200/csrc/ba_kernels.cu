@@ -131,10 +131,10 @@ __global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kerne
     const Tile t = tile_of(ctx, blockIdx.x);
     const double *ptx = ctx.pt[st->cur];
     double cost = 0.0, gsq = 0.0, gmax = 0.0, xsq = 0.0;
-    // (landmarks without observations get zero blocks from a thread-per-landmark pass; its bounds are fetched now)
+    // second phase (thread per landmark): its track bounds are fetched now, off the critical path
     const int p_mine = t.p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
-    if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine]; hi_mine = ctx.pt_ptr[p_mine + 1]; }
+    if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0; }
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
         const int o = t.o0 + i, k = i;
         const unsigned ck = ctx.pm_camk[o];
@@ -181,43 +181,32 @@ __global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kerne
     }
     __syncthreads();
     tile_store_W_begin(ctx.W, t.o0, t.n, sW);      // TMA store issued by thread 0; everybody goes on with the per-landmark sums
-    // per-landmark sums by the thread of the track's FIRST observation (heads are spread over all warps), in track order
-    for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
-        const unsigned trk = ctx.pm_trk[t.o0 + i];
-        if (trk & 0xffffu) continue;
-        const int hi = i + (int)(trk >> 16), p = ctx.pm_pt[t.o0 + i];
+    for (int p = p_mine; p < t.p1; p += blockDim.x) {
+        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - t.o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - t.o0;
         double V[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-        for (int k = i; k < hi; ++k) {                      // the same sum order as a serial walk
+        for (int k = lo; k < hi; ++k) {                     // track order: the same sum order as a serial walk
             const double *v = sV + 9 * (size_t)k;
 #pragma unroll
             for (int j = 0; j < 6; ++j) V[j] += v[j];
 #pragma unroll
             for (int j = 0; j < 3; ++j) b[j] += v[6 + j];
         }
+        if (hi > lo) {
 #pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            const double x = ptx[3 * (size_t)p + j];
-            const double g = b[j] / ctx.scale_pt[3 * (size_t)p + j];
-            const double d = x - (x + (-g));
-            gsq += d * d;
-            gmax = fmax(gmax, fabs(d));
-            xsq += x * x;
+            for (int j = 0; j < 3; ++j) {
+                const double x = ptx[3 * (size_t)p + j];
+                const double g = b[j] / ctx.scale_pt[3 * (size_t)p + j];
+                const double d = x - (x + (-g));
+                gsq += d * d;
+                gmax = fmax(gmax, fabs(d));
+                xsq += x * x;
+            }
         }
         double *Vp = ctx.V + 6 * (size_t)p;
 #pragma unroll
         for (int j = 0; j < 6; ++j) Vp[j] = V[j];
         double *bp = ctx.bp + 3 * (size_t)p;
         bp[0] = b[0]; bp[1] = b[1]; bp[2] = b[2];
-    }
-    // landmarks without observations: zero blocks
-    for (int p = p_mine; p < t.p1; p += blockDim.x) {
-        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p], hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1];
-        if (hi > lo) continue;
-        double *Vp = ctx.V + 6 * (size_t)p;
-#pragma unroll
-        for (int j = 0; j < 6; ++j) Vp[j] = 0.0;
-        double *bp = ctx.bp + 3 * (size_t)p;
-        bp[0] = 0.0; bp[1] = 0.0; bp[2] = 0.0;
     }
     block_sum3_max(cost, gsq, xsq, gmax, red);
     if (threadIdx.x == 0) {
@@ -590,21 +579,15 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     const double *ptx = ctx.pt[st->cur];
     double *ptc = ctx.pt[st->cur ^ 1];
     __shared__ unsigned long long wbar;
-    // in flight across the barrier below: the thread's camera word, track word and landmark; a track HEAD (first observation of
-    // its landmark) does the landmark's share of the second phase and starts its rows on their way into L2 now
-    unsigned ck_first = 0u, trk_first = 1u;
-    int p_first = 0;
-    if (threadIdx.x < t.n) {
-        ck_first = ctx.pm_camk[t.o0 + threadIdx.x]; trk_first = ctx.pm_trk[t.o0 + threadIdx.x]; p_first = ctx.pm_pt[t.o0 + threadIdx.x];
-        if (!(trk_first & 0xffffu)) {
-            prefetch_l2(ctx.Vinv + 6 * (size_t)p_first); prefetch_l2(ctx.V + 6 * (size_t)p_first);
-            prefetch_l2(ctx.bp + 3 * (size_t)p_first); prefetch_l2(ptx + 3 * (size_t)p_first); prefetch_l2(ctx.scale_pt + 3 * (size_t)p_first);
-        }
-    }
-    // (landmarks without observations only carry their parameters over: thread-per-landmark pass at the end)
+    const unsigned ck_first = threadIdx.x < t.n ? ctx.pm_camk[t.o0 + threadIdx.x] : 0u;   // in flight across the barrier below
+    // second phase (thread per landmark): track bounds now, the landmark's rows on their way into L2
     const int p_mine = t.p0 + threadIdx.x;
     int lo_mine = 0, hi_mine = 0;
-    if (p_mine < t.p1) { lo_mine = ctx.pt_ptr[p_mine]; hi_mine = ctx.pt_ptr[p_mine + 1]; }
+    if (p_mine < t.p1) {
+        lo_mine = ctx.pt_ptr[p_mine] - t.o0; hi_mine = ctx.pt_ptr[p_mine + 1] - t.o0;
+        prefetch_l2(ctx.Vinv + 6 * (size_t)p_mine); prefetch_l2(ctx.V + 6 * (size_t)p_mine);
+        prefetch_l2(ctx.bp + 3 * (size_t)p_mine); prefetch_l2(ptx + 3 * (size_t)p_mine); prefetch_l2(ctx.scale_pt + 3 * (size_t)p_mine);
+    }
     tile_load_W(ctx.W, t.o0, t.n, sW, &wbar);      // TMA: the tile streams in while the threads gather their camera steps
     for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
         const int k = i;
@@ -624,34 +607,30 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
     }
     __syncthreads();
     double dxsq = 0, yb = 0, yhy = 0;
-    // per-landmark step by the thread of the track's first observation (heads are spread over all warps), sums in track order
-    for (int i = threadIdx.x; i < t.n; i += blockDim.x) {
-        const unsigned trk = i == (int)threadIdx.x ? trk_first : ctx.pm_trk[t.o0 + i];
-        if (trk & 0xffffu) continue;
-        const int hi = i + (int)(trk >> 16), p = i == (int)threadIdx.x ? p_first : ctx.pm_pt[t.o0 + i];
-        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
-        double a3[3] = {0, 0, 0};
-        for (int k = i; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
-        const double *Vi = ctx.Vinv + 6 * (size_t)p;
-        const double *b = ctx.bp + 3 * (size_t)p;
-        const double e0 = b[0] - a3[0], e1 = b[1] - a3[1], e2 = b[2] - a3[2];
-        const double y0 = Vi[0] * e0 + Vi[1] * e1 + Vi[2] * e2;
-        const double y1 = Vi[1] * e0 + Vi[3] * e1 + Vi[4] * e2;
-        const double y2 = Vi[2] * e0 + Vi[4] * e1 + Vi[5] * e2;
-        const double *V = ctx.V + 6 * (size_t)p;
-        yb += y0 * b[0] + y1 * b[1] + y2 * b[2];
-        yhy += y0 * (V[0] * y0 + V[1] * y1 + V[2] * y2) + y1 * (V[1] * y0 + V[3] * y1 + V[4] * y2) +
-               y2 * (V[2] * y0 + V[4] * y1 + V[5] * y2) + 2.0 * (a3[0] * y0 + a3[1] * y1 + a3[2] * y2);
-        const double *sp = ctx.scale_pt + 3 * (size_t)p;
-        const double c0 = X[0] + (-y0) * sp[0], c1 = X[1] + (-y1) * sp[1], c2 = X[2] + (-y2) * sp[2];
-        ptc[3 * (size_t)p] = c0; ptc[3 * (size_t)p + 1] = c1; ptc[3 * (size_t)p + 2] = c2;
-        const double d0 = X[0] - c0, d1 = X[1] - c1, d2 = X[2] - c2;
-        dxsq += d0 * d0 + d1 * d1 + d2 * d2;
-    }
     for (int p = p_mine; p < t.p1; p += blockDim.x) {
-        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p], hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1];
-        if (hi > lo) continue;
-        ptc[3 * (size_t)p] = ptx[3 * (size_t)p]; ptc[3 * (size_t)p + 1] = ptx[3 * (size_t)p + 1]; ptc[3 * (size_t)p + 2] = ptx[3 * (size_t)p + 2];
+        const int lo = p == p_mine ? lo_mine : ctx.pt_ptr[p] - t.o0, hi = p == p_mine ? hi_mine : ctx.pt_ptr[p + 1] - t.o0;
+        const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
+        if (hi > lo) {
+            double a3[3] = {0, 0, 0};
+            for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
+            const double *Vi = ctx.Vinv + 6 * (size_t)p;
+            const double *b = ctx.bp + 3 * (size_t)p;
+            const double e0 = b[0] - a3[0], e1 = b[1] - a3[1], e2 = b[2] - a3[2];
+            const double y0 = Vi[0] * e0 + Vi[1] * e1 + Vi[2] * e2;
+            const double y1 = Vi[1] * e0 + Vi[3] * e1 + Vi[4] * e2;
+            const double y2 = Vi[2] * e0 + Vi[4] * e1 + Vi[5] * e2;
+            const double *V = ctx.V + 6 * (size_t)p;
+            yb += y0 * b[0] + y1 * b[1] + y2 * b[2];
+            yhy += y0 * (V[0] * y0 + V[1] * y1 + V[2] * y2) + y1 * (V[1] * y0 + V[3] * y1 + V[4] * y2) +
+                   y2 * (V[2] * y0 + V[4] * y1 + V[5] * y2) + 2.0 * (a3[0] * y0 + a3[1] * y1 + a3[2] * y2);
+            const double *sp = ctx.scale_pt + 3 * (size_t)p;
+            const double c0 = X[0] + (-y0) * sp[0], c1 = X[1] + (-y1) * sp[1], c2 = X[2] + (-y2) * sp[2];
+            ptc[3 * (size_t)p] = c0; ptc[3 * (size_t)p + 1] = c1; ptc[3 * (size_t)p + 2] = c2;
+            const double d0 = X[0] - c0, d1 = X[1] - c1, d2 = X[2] - c2;
+            dxsq += d0 * d0 + d1 * d1 + d2 * d2;
+        } else {
+            ptc[3 * (size_t)p] = X[0]; ptc[3 * (size_t)p + 1] = X[1]; ptc[3 * (size_t)p + 2] = X[2];
+        }
     }
     double unused = 0.0;
     block_sum3_max(dxsq, yb, yhy, unused, red);
