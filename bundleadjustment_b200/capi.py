@@ -161,7 +161,8 @@ class Solver:
     def kernel_profile(self) -> dict:
         out = np.zeros(4)
         _check(lib.ba_get_kernel_profile(self._h, _ptr(out)), "ba_get_kernel_profile")
-        return {"cholesky_seconds": float(out[0]), "cholesky_launches": int(out[1])}
+        return {"cholesky_seconds": float(out[0]), "cholesky_launches": int(out[1]),      # dense Schur: the Cholesky kernel
+                "seconds": float(out[0]), "launches": int(out[1])}                        # (PCG: the matvec launches that did work)
 
     def reduced_system_stats(self) -> dict:
         """Order of the reduced camera system, filled / total 128x128 tiles of its Cholesky factor, flops per solve."""

@@ -97,7 +97,7 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s);       // local block-diag(S) + rhs (all-reduce Minv, rhs after)
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s);       // invert blocks, x = 0, r = b
-void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s);      // z = M^-1 r, p, local landmark part of q = S p
+void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s, cudaEvent_t ev_before_matvec = nullptr, cudaEvent_t ev_after_matvec = nullptr);      // z = M^-1 r, p, local landmark part of q = S p
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s);      // q += (U+D^2) p, alpha, x, r   (after all-reduce of q)
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s);     // local landmark part of S x into cg_z
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s);     // r = b - S x                   (after all-reduce of cg_z)

@@ -424,12 +424,14 @@ static int cg_grid(const Ctx &ctx, const void *kernel) {
     return std::max(1, std::min(std::min(per_dev[dev], CG_MAX_GRID), cdiv(ctx.n, CG_THREADS)));
 }
 
-void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s) {      // precondition + direction + local matvec
+void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s, cudaEvent_t ev0, cudaEvent_t ev1) {      // precondition + direction + local matvec
     Ctx c = ctx;
     double *part = ctx.cg_part;
     void *args[] = {&c, &part};
     cudaLaunchCooperativeKernel((const void *)pcg_precond_kernel, dim3(cg_grid(ctx, (const void *)pcg_precond_kernel)), dim3(CG_THREADS), args, 0, s);
+    if (ev0) cudaEventRecord(ev0, s);
     if (ctx.n_blocks > 0) pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, ctx.cg_p, ctx.cg_qp);
+    if (ev1) cudaEventRecord(ev1, s);
     pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_q);
 }
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {

@@ -166,8 +166,9 @@ int ba_get_launch_count(ba_handle *h);
  * ba_summary.seconds_evaluate / seconds_linear_solver (event recording does not synchronise the stream). */
 int ba_set_profiling(ba_handle *h, int32_t on);
 
-/* Profiling detail of the last ba_solve (profiling on): out = {seconds inside the dense-Cholesky kernel, measured with CUDA
- * events on the solver's stream around each launch; number of launches; 0; 0}.  Benchmark bookkeeping ("roofline"). */
+/* Profiling detail of the last ba_solve (profiling on): out = {seconds inside the dominant linear-solver kernel -- the dense
+ * Cholesky kernel, or the PCG matvec launches that did work -- measured with CUDA events on the solver's stream around each
+ * launch; number of launches; 0; 0}.  Benchmark bookkeeping ("roofline"). */
 int ba_get_kernel_profile(ba_handle *h, double out[4]);
 
 /* Dense SPD solve A x = b with the reduced-system Cholesky (DenseSchurComplementSolver's Eigen LLT stand-in) on

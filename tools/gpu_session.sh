@@ -30,7 +30,7 @@ if [ $RC4 -eq 0 ]; then
       --launch-skip 10 -c 5 -f -o $OUT/prof_K4_lm_$TAG python bench.py $SHORT > /dev/null 2>> $OUT/ncu_K4_$TAG.err
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"evaluate_materialize" --launch-skip 4 -c 1 -f -o $OUT/prof_K4_eval_$TAG \
       python bench.py $SHORT > /dev/null 2>> $OUT/ncu_K4_$TAG.err
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"chol_dataflow" --launch-skip 3 -c 1 -f -o $OUT/prof_K4_chol_$TAG \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"chol_dataflow" --launch-skip 4 -c 1 -f -o $OUT/prof_K4_chol_$TAG \
       python bench.py $SHORT > /dev/null 2>> $OUT/ncu_K4_$TAG.err
 fi
 if [ $RC5 -eq 0 ]; then
