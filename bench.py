@@ -36,6 +36,16 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (torch prints "NCCL version ..." from C++ when the first
+# communicator comes up), so file descriptor 1 is pointed at stderr for the whole run and the line goes to the saved one.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
 def load_workload(name: str, scale: float = 1.0, path: str | None = None):
     from bundleadjustment_b200 import synthetic as syn
     t = time.time()
@@ -172,7 +182,7 @@ def main_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out), flush=True)
+    emit(out)
     return 0
 
 
@@ -380,7 +390,7 @@ def main_ours(args):
         "wall_seconds_timed_region": wall,
         "cpu_baseline": cpu,
     }
-    print(json.dumps(out), flush=True)
+    emit(out)
     return 0
 
 
