@@ -599,8 +599,8 @@ int enqueue_linear_solve(ba_handle *h) {
         const int R = ctx.No >= (1 << 20) ? 2 : 4;
         for (int it = 1; it <= max_it; ++it) {
             if (it > R) {
-                CU(cudaEventSynchronize(h->ev_ring[it % R]));
-                if (h->host_flags[1] || h->host_flags[0]) break;
+                CU(cudaEventSynchronize(h->ev_ring[it % R]));                       // iteration it - R has finished:
+                if (h->host_flags[HF_CG_RING + (it - R) % HF_CG_SLOTS]) break;      // ITS verdict (the same on every rank)
             }
             if (h->profile) { cudaEvent_t e0 = h->dom_event(), e1 = h->dom_event(); launch_pcg_iter_a(ctx, s, e0, e1); }
             else launch_pcg_iter_a(ctx, s);
@@ -614,7 +614,8 @@ int enqueue_linear_solve(ba_handle *h) {
                 h->launches += 3;   // matvec, fold, reset
             }
             launch_pcg_check(ctx, s);
-            h->launches += 1;
+            launch_pcg_publish(ctx, it, s);
+            h->launches += 2;
             CU(cudaEventRecord(h->ev_ring[it % R], s));
         }
         launch_pcg_finish(ctx, s);
@@ -641,7 +642,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
     h->launches = 0;
     h->prof_used = 0;
     h->dom_used = 0; h->dom_seconds = 0.0; h->dom_launches = 0;
-    h->host_flags[0] = 0; h->host_flags[1] = 0;
+    for (int i = 0; i < 16; ++i) h->host_flags[i] = 0;
     CU(cudaEventRecord(h->ev_start, s));
     launch_init_state(ctx, s);
     launch_fill(ctx.scale_cam, 6 * (size_t)ctx.Nc, 1.0, s);
@@ -663,7 +664,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         if (k >= 2) {
             cudaError_t e = cudaEventSynchronize(ev_lm[k & 1]);    // body k-2 finished: safe to look at its verdict
             if (e != cudaSuccess) { status = fail(BA_ERR_CUDA, "LM loop: %s", cudaGetErrorString(e)); break; }
-            if (h->host_flags[0]) break;
+            if (h->host_flags[HF_LM_RING + (k - 2) % HF_LM_SLOTS]) break;           // the verdict of body k - 2 (the same on every rank)
         }
         if (h->profile) cudaEventRecord(h->prof_event(), s);
         if ((rc = enqueue_linearize(h, 0))) { status = rc; break; }
@@ -675,7 +676,8 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         launch_eval_candidate(ctx, h->cost_part.as<double>(), s);
         if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_STEP_BEGIN, ctx.sums + SUM_STEP_BEGIN, SUM_STEP_N))) { status = rc; break; }
         launch_decide(ctx, s);
-        h->launches += 6;
+        launch_lm_publish(ctx, k, s);
+        h->launches += 7;
         cudaEventRecord(ev_lm[k & 1], s);
     }
     cudaEventRecord(h->ev_stop, s);

@@ -851,6 +851,9 @@ __global__ void lm_decide_kernel(Ctx ctx) {
     }
 }
 
+// verdict as of the end of an LM body, for the host's enqueue loop (see HF_LM_RING)
+__global__ void lm_publish_kernel(Ctx ctx, int slot) { ctx.host_flags[HF_LM_RING + slot] = ctx.state->done; }
+
 __global__ void lm_init_state_kernel(Ctx ctx) {
     LMState *st = ctx.state;
     memset(st, 0, sizeof(LMState));
@@ -992,6 +995,7 @@ void launch_compute_scale(const Ctx &ctx, cudaStream_t s) {
 
 void launch_begin_iteration(const Ctx &ctx, cudaStream_t s) { lm_begin_iteration_kernel<<<1, 1, 0, s>>>(ctx); }
 void launch_decide(const Ctx &ctx, cudaStream_t s) { lm_decide_kernel<<<1, 1, 0, s>>>(ctx); }
+void launch_lm_publish(const Ctx &ctx, int body, cudaStream_t s) { lm_publish_kernel<<<1, 1, 0, s>>>(ctx, body % HF_LM_SLOTS); }
 
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s) {
     point_invert_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, radius_override);

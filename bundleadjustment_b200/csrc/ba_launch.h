@@ -16,6 +16,8 @@ void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s);
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s);
 void launch_begin_iteration(const Ctx &ctx, cudaStream_t s);
 void launch_decide(const Ctx &ctx, cudaStream_t s);
+void launch_lm_publish(const Ctx &ctx, int body, cudaStream_t s);        // verdict as of the end of LM body `body` -> host ring
+void launch_pcg_publish(const Ctx &ctx, int iteration, cudaStream_t s);  // verdict as of the end of CG iteration -> host ring
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_tiles_copy(double *S, int ld, const int2 *tiles, int n_tiles, double *packed, int unpack, cudaStream_t s);

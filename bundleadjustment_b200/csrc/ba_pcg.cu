@@ -384,6 +384,12 @@ __global__ void __launch_bounds__(RED_THREADS) pcg_check_kernel(Ctx ctx) {
     }
 }
 
+// verdict as of the end of a CG iteration, for the host's enqueue loop (see HF_CG_RING)
+__global__ void pcg_publish_kernel(Ctx ctx, int slot) {
+    const LMState *st = ctx.state;
+    ctx.host_flags[HF_CG_RING + slot] = (st->done || st->cg_done) ? 1 : 0;
+}
+
 __global__ void pcg_finish_kernel(Ctx ctx) {
     LMState *st = ctx.state;
     if (st->done) return;
@@ -446,6 +452,7 @@ void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part o
 }
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
 void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<std::max(1, std::min(cdiv(ctx.n, 2 * RED_THREADS), 256)), RED_THREADS, 0, s>>>(ctx); }
+void launch_pcg_publish(const Ctx &ctx, int iteration, cudaStream_t s) { pcg_publish_kernel<<<1, 1, 0, s>>>(ctx, iteration % HF_CG_SLOTS); }
 void launch_pcg_finish(const Ctx &ctx, cudaStream_t s) { pcg_finish_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
 
 } // namespace ba

@@ -146,8 +146,15 @@ struct Ctx {
     // control
     LMState *state;
     ba_iteration *iters;     // [max_num_iterations + 2]
-    volatile int *host_flags; // mapped pinned: [0] = done, [1] = cg_done
+    volatile int *host_flags; // mapped pinned [16]: [0] = done, [1] = cg_done (latest state), [HF_LM_RING ..] / [HF_CG_RING ..] = the
+                              // verdict AS OF THE END of LM body / CG iteration number (slot), written by the publish kernels
 };
+
+// The host stops enqueueing LM bodies / CG iterations when it sees the verdict of the body / iteration it last waited for.  It
+// must read the verdict AS OF THAT body, not the latest one: every rank of a sharded solve has to stop at the same body, or the
+// ranks' NCCL calls no longer pair up (a faster rank could already see the flag of the following body and leave one all-reduce
+// early).  Hence a ring of snapshots in the mapped flag words instead of the two "latest state" words.
+constexpr int HF_LM_RING = 2, HF_LM_SLOTS = 4, HF_CG_RING = 8, HF_CG_SLOTS = 8;
 
 // slots of red_part / red_count
 enum : int { RED_LIN = 0, RED_CAM_NORMS, RED_CAM_UPDATE, RED_STEP, RED_CG_CHECK, RED_CG_START, RED_SLOTS = 8 };
