@@ -328,7 +328,7 @@ def main_ours(args):
     traffic = None
     if world == 1 and args.scale == 1.0:
         traffic = {("K4", "dense"): 65.548e6 + 19.983e6,        # profiles/r01_K4_cholesky_sparse_ncu_full_v9.txt
-                   ("K5", "pcg"): 4.685456e9 + 0.003992e9,      # profiles/r01_K5_pcg_kernels_ncu_full_v7.txt
+                   ("K5", "pcg"): 5.075608e9 + 0.225956e9,      # profiles/r01_K5_lm_kernels_ncu_full_v12.txt (pcg_matvec_points_kernel)
                    }.get((args.workload, args.solver))
     if args.solver == "dense":
         fp64_peak = measure_fp64_peak(local)
