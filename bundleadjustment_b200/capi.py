@@ -19,7 +19,7 @@ EXPORTS = [
     "ba_set_problem", "ba_set_parameters", "ba_reset_parameters", "ba_solve", "ba_get_cameras", "ba_get_points",
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
     "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
-    "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile",
+    "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile", "ba_set_reduced_system_mode",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
     "ba_pose_to_cam", "ba_cam_to_pose",
 ]
@@ -151,6 +151,10 @@ class Solver:
         sm = Summary()
         _check(lib.ba_solve(self._h, C.byref(sm)), "ba_solve")
         return sm
+
+    def set_reduced_system_mode(self, natural_order: bool = False, dense_tiles: bool = False):
+        """Explicit (never environment-driven) switches of the reduced-system factorisation; call before set_problem."""
+        _check(lib.ba_set_reduced_system_mode(self._h, int(natural_order), int(dense_tiles)), "ba_set_reduced_system_mode")
 
     def set_profiling(self, on: bool = True):
         _check(lib.ba_set_profiling(self._h, int(on)), "ba_set_profiling")

@@ -95,6 +95,7 @@ struct ba_handle {
     PrepIn prep_in;
     PrepOut prep_out;
     bool pairs_built = false;
+    bool natural_tile_order = false, dense_tiles = false;   // ba_set_reduced_system_mode (explicit API, never the environment)
     CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
     bool S_dirty = true;             // S may hold values outside the plan's tiles (new buffer / new plan): clear all of it once
     DevBuf tile_map, cam_row, row_src, yperm, nz_tiles, s_packed;
@@ -303,9 +304,8 @@ int ensure_dense(ba_handle *h) {
         std::vector<unsigned char> adj((size_t)G * G);
         CU(cudaMemcpyAsync(adj.data(), h->tile_map.p, adj.size(), cudaMemcpyDeviceToHost, s));
         CU(cudaStreamSynchronize(s));
-        const auto env_on = [](const char *name) { const char *v = std::getenv(name); return v && v[0] == '1'; };
         std::vector<int> order;
-        if (env_on("BA_B200_NATURAL_ORDER")) { order.resize(G); std::iota(order.begin(), order.end(), 0); }   // measurement aid
+        if (h->natural_tile_order) { order.resize(G); std::iota(order.begin(), order.end(), 0); }   // ba_set_reduced_system_mode
         else chol_tile_order(G, adj.data(), order);
         if ((int)order.size() != G) return fail(BA_ERR_STATE, "tile ordering lost nodes (internal error)");
         std::vector<int> pos(G);
@@ -333,8 +333,8 @@ int ensure_dense(ba_handle *h) {
             CU(cudaStreamSynchronize(s));
         }
         CU(cudaStreamSynchronize(s));                                    // the uploads read the host vectors above
-        // BA_B200_DENSE_TILES=1 (measurement aid): treat every tile as filled
-        if ((rc = chol_plan_create(n, env_on("BA_B200_DENSE_TILES") ? nullptr : nz.data(), &h->chol_plan, s)))
+        // ba_set_reduced_system_mode(dense_tiles): treat every tile as filled (what Ceres' DENSE_SCHUR does)
+        if ((rc = chol_plan_create(n, h->dense_tiles ? nullptr : nz.data(), &h->chol_plan, s)))
             return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
         h->S_dirty = true;
         h->pairs_built = true;
@@ -731,6 +731,18 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         }
         std::snprintf(summary->message, sizeof(summary->message), "%s", message_text(st.msg));
     }
+    return BA_OK;
+}
+
+// Explicit switches of the reduced-system factorisation (tests, measurements; defaults 0 / 0): natural_order != 0 keeps the
+// Cholesky tiles in camera order instead of nested dissection; dense_tiles != 0 treats every tile as filled, i.e. factorises S
+// as the dense matrix Ceres' DENSE_SCHUR would.  Neither changes a result beyond summation order.  Takes effect at the next
+// ba_set_problem (the plan is built once per problem).
+extern "C" int ba_set_reduced_system_mode(ba_handle *h, int32_t natural_order, int32_t dense_tiles) {
+    if (!h) return fail(BA_ERR_INVALID, "handle is NULL");
+    h->natural_tile_order = natural_order != 0;
+    h->dense_tiles = dense_tiles != 0;
+    h->pairs_built = false;
     return BA_OK;
 }
 

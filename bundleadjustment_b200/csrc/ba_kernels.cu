@@ -605,6 +605,9 @@ __global__ void __launch_bounds__(TILE_THREADS) backsub_kernel(Ctx ctx) {
         }
         sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
     }
+    // the issuing thread always sees the bulk copy complete (a block seen only by fixed cameras has no other waiter;
+    // the CTA must not exit with the copy still writing into its shared memory)
+    if (threadIdx.x == 0 && t.n > 0) tile_wait_W(&wbar);
     __syncthreads();
     double dxsq = 0, yb = 0, yhy = 0;
     for (int p = p_mine; p < t.p1; p += blockDim.x) {
@@ -948,9 +951,7 @@ static inline size_t tile_smem(const Ctx &ctx, int doubles_per_obs) { return siz
 int tiles_init(const Ctx &ctx) {
     const size_t need = tile_smem(ctx, 27);
     if (need > 227 * 1024) return (int)cudaErrorInvalidConfiguration;
-    cudaError_t e = cudaFuncSetAttribute(linearize_points_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(linearize_points_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
+    cudaError_t e = cudaFuncSetAttribute(linearize_points_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem(ctx, 21));
     if (e != cudaSuccess) return (int)e;
@@ -972,17 +973,10 @@ void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s) {
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     launch_cam_prep(ctx, 0, force, s);
     if (ctx.n_blocks > 0) {
-        // 2 CTAs/SM at 128 registers (no spills) beat 3 CTAs/SM at 80 registers + 128 B of spills by 4-5 % (K4 and K5);
-        // BA_B200_LIN_CTAS=3 selects the other instantiation (measurement aid)
-        static const int min_ctas = [] { const char *v = std::getenv("BA_B200_LIN_CTAS"); return v ? std::atoi(v) : 2; }();
-        if (min_ctas == 3) linearize_points_kernel<3><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
-        else linearize_points_kernel<2><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
+        // 2 CTAs/SM at 128 registers (no spills) beat 3 CTAs/SM at 80 registers + 128 B of spills by 4-5 % (K4 and K5)
+        linearize_points_kernel<2><<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 27), s>>>(ctx, force);
     }
-    if (ctx.n_chunks > 0) {
-        static const int min_ctas = [] { const char *v = std::getenv("BA_B200_CAMS_CTAS"); return v ? std::atoi(v) : 4; }();   // measurement aid
-        if (min_ctas == 5) linearize_cams_kernel<5><<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
-        else linearize_cams_kernel<4><<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
-    }
+    if (ctx.n_chunks > 0) linearize_cams_kernel<4><<<cdiv(ctx.n_chunks, CAMS_WARPS), CAMS_WARPS * 32, 0, s>>>(ctx, force);
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<red_grid(ctx.n_part, 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force);
 }

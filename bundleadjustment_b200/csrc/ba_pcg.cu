@@ -161,6 +161,8 @@ __global__ void __launch_bounds__(RED_THREADS) pcg_start_kernel(Ctx ctx) {
         st->cg_rho = 1.0; st->cg_last_rho = 1.0; st->cg_Q0 = 0.0; st->cg_iter = 0; st->cg_done = 0;
         if (st->cg_bad_block || !isfinite(nb)) { st->chol_fail = 1; st->cg_done = 1; }
         st->cg_bad_block = 0;
+        // ConjugateGradientsSolver::Solve: |b| = 0 -> x = 0, success, no iterations (all cameras fixed, or a converged point)
+        if (nb == 0.0) st->cg_done = 1;
         // |r| <= r_tolerance * |b| at x = 0 (only when the relative-residual rule is enabled)
         if (ctx.opt.cg_r_tolerance > 0 && sqrt(nb) <= ctx.opt.cg_r_tolerance * sqrt(nb)) st->cg_done = 1;
         ctx.host_flags[1] = st->cg_done;
@@ -260,6 +262,9 @@ __global__ void __launch_bounds__(TILE_THREADS, 5) pcg_matvec_points_kernel(Ctx 
         }
         sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
     }
+    // The thread that started the bulk copy always sees it complete before the CTA can leave the tile: a block whose
+    // observations all belong to fixed cameras has no other waiter, and a CTA must not exit with a copy in flight.
+    if (threadIdx.x == 0) mbar_wait(&wbar, 0);
     __syncthreads();
     // Second half, still one thread per OBSERVATION and no further barrier: every thread sums its landmark's track in track
     // order (the position/length word says where it starts: t shared-memory reads, the same for all observations of the
@@ -285,103 +290,6 @@ __global__ void __launch_bounds__(TILE_THREADS, 5) pcg_matvec_points_kernel(Ctx 
 #pragma unroll
         for (int a = 0; a < 6; ++a)
             atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
-    }
-}
-
-// ---------------------------------------------------------------------------------------------------------------------------
-// EXPERIMENTAL, OFF BY DEFAULT (BA_B200_MATVEC_RING=1), NEVER RUN ON A GPU YET: written after the round's GPU budget was spent,
-// as the starting point of DESIGN.md section 9 item 1.  Same arithmetic as pcg_matvec_points_kernel, but persistent CTAs walk
-// the landmark blocks with a 2-stage TMA ring: while block j is computed, the W tile of block j + gridDim.x is on its way into
-// the other stage and its index triplets into registers, so a tile buffer is being filled for (nearly) the whole life of the
-// CTA instead of about half of it.  2 CTAs/SM (2 x 18 + 3 doubles per observation of shared memory each).
-// Stage s is re-armed only after the CTA barrier that ends the iteration which read it; its mbarrier parity flips once per
-// non-empty block that used it (tracked identically by every thread).
-// ---------------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TILE_THREADS, 2) pcg_matvec_ring_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp) {
-    const LMState *st = ctx.state;
-    CG_GUARD(st);
-    if ((int)blockIdx.x >= ctx.n_blocks) return;
-    double *__restrict__ q = qp + (size_t)(blockIdx.x & (CG_QCOPIES - 1)) * ctx.n;
-    extern __shared__ __align__(16) double tsm[];
-    const size_t cap = (size_t)ctx.tile_cap;
-    double *sT = tsm + 36 * cap;                   // [cap][3]
-    __shared__ unsigned long long bars[2];
-    if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
-    __syncthreads();
-    int b = blockIdx.x;
-    int4 bi = ctx.blk_info[b];
-    if (threadIdx.x == 0 && bi.w > 0) bulk_load(tsm, ctx.W + 18 * (size_t)bi.z, 144u * (unsigned)bi.w, &bars[0]);
-    unsigned ck_n = 0u, trk_n = 0u;
-    int p_n = 0;
-    if ((int)threadIdx.x < bi.w) {
-        ck_n = ctx.pm_camk[bi.z + threadIdx.x]; trk_n = ctx.pm_trk[bi.z + threadIdx.x]; p_n = ctx.pm_pt[bi.z + threadIdx.x];
-        prefetch_l2(ctx.Vinv + 6 * (size_t)p_n);
-    }
-    unsigned parity[2] = {0u, 0u};
-    for (int j = 0;; ++j) {
-        const int stage = j & 1;
-        const int o0 = bi.z, n = bi.w;
-        const unsigned ck_first = ck_n, trk_first = trk_n;
-        const int p_first = p_n;
-        // the next block of this CTA: W into the other stage (free since the barrier that ended the previous iteration), indices
-        // into registers
-        const int bn = b + (int)gridDim.x;
-        int4 bin = make_int4(0, 0, 0, 0);
-        if (bn < ctx.n_blocks) {
-            bin = ctx.blk_info[bn];
-            if (threadIdx.x == 0 && bin.w > 0)
-                bulk_load(tsm + 18 * cap * (size_t)(stage ^ 1), ctx.W + 18 * (size_t)bin.z, 144u * (unsigned)bin.w, &bars[stage ^ 1]);
-            if ((int)threadIdx.x < bin.w) {
-                ck_n = ctx.pm_camk[bin.z + threadIdx.x]; trk_n = ctx.pm_trk[bin.z + threadIdx.x]; p_n = ctx.pm_pt[bin.z + threadIdx.x];
-                prefetch_l2(ctx.Vinv + 6 * (size_t)p_n);
-            }
-        }
-        if (n > 0) {
-            const double *sW = tsm + 18 * cap * (size_t)stage;
-            unsigned long long *bar = &bars[stage];
-            const unsigned par = stage ? parity[1] : parity[0];
-            for (int i = threadIdx.x; i < n; i += blockDim.x) {
-                const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
-                const int c = camk_cam(ck);
-                double a3[3] = {0, 0, 0};
-                if (camk_kind(ck) == CAM_FREE) {
-                    double x[6];
-                    load_row6(v, (size_t)c, x);
-                    mbar_wait(bar, par);
-                    double Wo[18];
-                    load_record18(sW, i, Wo);
-#pragma unroll
-                    for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
-                }
-                sT[3 * (size_t)i] = a3[0]; sT[3 * (size_t)i + 1] = a3[1]; sT[3 * (size_t)i + 2] = a3[2];
-            }
-            __syncthreads();
-            for (int i = threadIdx.x; i < n; i += blockDim.x) {
-                const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
-                if (camk_kind(ck) != CAM_FREE) continue;
-                const int c = camk_cam(ck);
-                const unsigned trk = i == (int)threadIdx.x ? trk_first : ctx.pm_trk[o0 + i];
-                const int p = i == (int)threadIdx.x ? p_first : ctx.pm_pt[o0 + i];
-                const int lo = i - (int)(trk & 0xffffu), hi = lo + (int)(trk >> 16);
-                double vi[6];
-                load_row6(ctx.Vinv, (size_t)p, vi);
-                double a3[3] = {0, 0, 0};
-                for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
-                const double t0 = vi[0] * a3[0] + vi[1] * a3[1] + vi[2] * a3[2];
-                const double t1 = vi[1] * a3[0] + vi[3] * a3[1] + vi[4] * a3[2];
-                const double t2 = vi[2] * a3[0] + vi[4] * a3[1] + vi[5] * a3[2];
-                mbar_wait(bar, par);
-                double Wo[18];
-                load_record18(sW, i, Wo);
-#pragma unroll
-                for (int a = 0; a < 6; ++a)
-                    atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
-            }
-            if (stage) parity[1] ^= 1u; else parity[0] ^= 1u;
-        }
-        __syncthreads();                           // sT and this stage's W tile are free again
-        if (bn >= ctx.n_blocks) break;
-        b = bn; bi = bin;
     }
 }
 
@@ -505,30 +413,13 @@ void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
     pcg_setup_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
 }
 static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 21 * (size_t)ctx.tile_cap; }
-static inline size_t pcg_ring_smem(const Ctx &ctx) { return sizeof(double) * 39 * (size_t)ctx.tile_cap; }
-// BA_B200_MATVEC_RING=1 selects the experimental ring kernel (see its header); anything else, and blocks too long for two
-// stages, use the measured kernel
-static bool matvec_ring_wanted() {
-    static const bool on = [] { const char *e = std::getenv("BA_B200_MATVEC_RING"); return e && e[0] == '1'; }();
-    return on;
-}
 int pcg_tiles_init(const Ctx &ctx) {
-    if (matvec_ring_wanted() && pcg_ring_smem(ctx) <= 113 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(pcg_matvec_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_ring_smem(ctx));
-        if (e != cudaSuccess) return (int)e;
-    }
     return (int)cudaFuncSetAttribute(pcg_matvec_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_tile_smem(ctx));
 }
 // local landmark part of  qp -= W V'^-1 W^T v
 static void launch_matvec(const Ctx &ctx, const double *v, cudaStream_t s) {
     if (ctx.n_blocks <= 0) return;
-    if (matvec_ring_wanted() && pcg_ring_smem(ctx) <= 113 * 1024) {
-        static int sms = 0;
-        if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-        pcg_matvec_ring_kernel<<<std::min(ctx.n_blocks, 2 * std::max(sms, 1)), TILE_THREADS, pcg_ring_smem(ctx), s>>>(ctx, v, ctx.cg_qp);
-    } else {
-        pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, v, ctx.cg_qp);
-    }
+    pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, v, ctx.cg_qp);
 }
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s) {
     pcg_invert_blocks_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);

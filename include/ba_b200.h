@@ -182,6 +182,12 @@ int ba_dense_spd_solve(int device, int32_t n, const double *A, const double *b, 
  * schur_complement_solver.cc); the factorisation skips tiles that stay zero, which changes no result. */
 int ba_get_reduced_system_stats(ba_handle *h, double out[4]);
 
+/* Explicit switches of the reduced-system factorisation (tests and measurements; both default to 0): natural_order != 0
+ * keeps the Cholesky tiles in camera order instead of nested dissection; dense_tiles != 0 factorises S as a fully dense
+ * matrix, as Ceres' DENSE_SCHUR (Optimizer.cpp:85) does.  Results change by summation order only.  The library reads NO
+ * environment variables.  Call before ba_set_problem. */
+int ba_set_reduced_system_mode(ba_handle *h, int32_t natural_order, int32_t dense_tiles);
+
 /* ---- host-only helpers (no GPU needed) ---------------------------------------------------------------- */
 /* Balanced contiguous landmark partition: cut[r]..cut[r+1] for r in [0,n_ranks); weight = sum over the
  * landmark's track length t of t (iterative) or t*(t+1)/2 (dense Schur).  obs_pt must be sorted ascending. */

@@ -7,7 +7,32 @@ import numpy as np
 from bundleadjustment_b200.synthetic import Problem
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+CASES = sorted(n for n in (os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+               if not n.startswith("scipy_"))
+# optimum pins produced by scipy.optimize.least_squares (tests/golden/make_scipy_pin.py): code neither restatement shares
+SCIPY_CASES = sorted(os.path.splitext(os.path.basename(p))[0][len("scipy_"):] for p in glob.glob(os.path.join(GOLDEN_DIR, "scipy_*.npz")))
+
+
+def load_scipy_pin(name):
+    z = np.load(os.path.join(GOLDEN_DIR, "scipy_" + name + ".npz"))
+    pb = Problem(cam=z["cam"], cam_fixed=z["cam_fixed"], fixed_extr=z["fixed_extr"], K=z["K"], pt=z["pt"],
+                 obs_cam=z["obs_cam"], obs_pt=z["obs_pt"], obs_uv=z["obs_uv"])
+    return pb, z
+
+
+# options that let the LM loop run to the optimum instead of stopping at Ceres' default function tolerance
+CONVERGE = dict(max_num_iterations=800, function_tolerance=1e-16, parameter_tolerance=1e-16, gradient_tolerance=1e-14)
+
+
+def check_against_scipy_pin(z, cam, pt, final_cost):
+    """cost 1e-8 relative everywhere (held to 1e-10: both sides sit at the same minimum); parameters 1e-6 where the
+    optimum is unique (two fixed cameras; with one fixed camera monocular BA keeps a scale gauge freedom)."""
+    c = float(z["opt_cost"])
+    assert abs(final_cost - c) <= 1e-10 * c, (final_cost, c)
+    if int(z["gauge_fixed"]):
+        assert np.abs(cam - z["opt_cam"]).max() <= 1e-6, np.abs(cam - z["opt_cam"]).max()
+        assert np.abs(pt - z["opt_pt"]).max() <= 1e-6, np.abs(pt - z["opt_pt"]).max()
+
 FIELDS = ("iteration", "step_is_valid", "step_is_successful", "cost", "cost_change", "gradient_max_norm", "step_norm",
           "relative_decrease", "trust_region_radius")
 

@@ -170,16 +170,16 @@ def test_dense_spd_solve_tile_patterns(bab, name, n, pattern):
     assert np.abs(x - ref).max() <= 1e-11 * np.abs(ref).max()
 
 
-def test_tile_skipping_changes_nothing(bab, monkeypatch):
+def test_tile_skipping_changes_nothing(bab):
     """Banded co-visibility (K4-shaped, scaled down): the LM trajectory with the tile-sparsity plan equals the one with
     every tile treated as filled up to summation order (the skipped terms are exact zeros; the plan only decides in which
     order a tile's contributions are added)."""
     pb = syn.flatten(syn.make_scene("band", 11, 260, 9000, 4.0, 16))
     opt = bab.default_options(max_num_iterations=6)
     runs = []
-    for dense in ("0", "1"):
-        monkeypatch.setenv("BA_B200_DENSE_TILES", dense)
+    for dense in (False, True):
         s = bab.Solver(opt)
+        s.set_reduced_system_mode(dense_tiles=dense)
         s.set_problem(pb)
         sm = s.solve()
         st = s.reduced_system_stats()
