@@ -20,6 +20,7 @@ EXPORTS = [
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
     "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
     "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile", "ba_set_reduced_system_mode",
+    "ba_solve_pose_only_outer", "ba_release_workspace", "ba_workspace_launch_count",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
     "ba_pose_to_cam", "ba_cam_to_pose",
 ]
@@ -254,6 +255,36 @@ def prune_frames(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max, h
                                _ptr(kp_octave), _ptr(pt_xyz), _ptr(pt_min), _ptr(pt_max), _ptr(has_point), _ptr(out),
                                int(consider_outlier)), "ba_prune_frames")
     return out
+
+
+def solve_pose_only_outer(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max, has_point, outlier, n_outer=4,
+                          options: Options | None = None, device: int = 0, pose_out=None, outlier_out=None):
+    """ba_solve_pose_only_outer: returns (pose [F,4,4] f32, outlier u8, summaries of the last outer iteration, device ms).
+    pose_out / outlier_out (optional): caller-owned (e.g. page-locked) result buffers."""
+    F = int(np.asarray(frame_ptr).shape[0]) - 1
+    P = np.ascontiguousarray(pose, np.float32).reshape(F, 16)
+    if pose_out is None:
+        pose_out = P.copy()
+    else:
+        pose_out.reshape(F, 16)[...] = P
+    o = np.ascontiguousarray(outlier, np.uint8)
+    if outlier_out is None:
+        outlier_out = o.copy()
+    else:
+        outlier_out[...] = o
+    args = [np.ascontiguousarray(K, np.float32), np.ascontiguousarray(frame_ptr, np.int32), np.ascontiguousarray(kp_xy, np.float32),
+            np.ascontiguousarray(kp_octave, np.int32), np.ascontiguousarray(pt_xyz, np.float32), np.ascontiguousarray(pt_min, np.float32),
+            np.ascontiguousarray(pt_max, np.float32), np.ascontiguousarray(has_point, np.uint8)]
+    sms = (Summary * max(F, 1))()
+    ms = C.c_float(0)
+    opt = options or default_options(max_num_iterations=20)
+    _check(lib.ba_solve_pose_only_outer(C.byref(opt), int(device), F, _ptr(pose_out), *[_ptr(a) for a in args], _ptr(outlier_out),
+                                        int(n_outer), sms, C.byref(ms)), "ba_solve_pose_only_outer")
+    return pose_out.reshape(F, 4, 4), outlier_out, list(sms)[:F], float(ms.value)
+
+
+def workspace_launch_count(device: int = 0) -> int:
+    return int(lib.ba_workspace_launch_count(int(device)))
 
 
 def dense_spd_solve(A, b, device: int = 0, repeats: int = 1):

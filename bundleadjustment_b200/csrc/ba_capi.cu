@@ -1036,13 +1036,64 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
 // =============================================================================================================
 // batched frame-to-frame pose estimation, pruning
 // =============================================================================================================
-extern "C" void ba_inverse4x4_f32(const float m[16], float out[16]);   // ba_host.cpp
+namespace {
+
+// Persistent per-thread, per-device workspace of the handle-less entry points (pose batch, prune, pose outer loop): one stream,
+// two events and grow-only device buffers, created on first use and reused by every later call of the thread -- no cudaMalloc,
+// stream or event creation on the steady-state path (the tracker calls these once per frame).  Released by
+// ba_release_workspace() or with the process.
+struct Workspace {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t e1 = nullptr, e2 = nullptr;
+    DevBuf cam, K, ptr, Xh, uv, mask, sum, it, pose, extr, xy, oct, xyz, mn, mx, has, out;
+    int launches = 0;
+    void release() {
+        if (device < 0) return;
+        cudaSetDevice(device);
+        DevBuf *all[] = {&cam, &K, &ptr, &Xh, &uv, &mask, &sum, &it, &pose, &extr, &xy, &oct, &xyz, &mn, &mx, &has, &out};
+        for (DevBuf *b : all) b->free();
+        if (e1) cudaEventDestroy(e1);
+        if (e2) cudaEventDestroy(e2);
+        if (stream) cudaStreamDestroy(stream);
+        stream = nullptr; e1 = e2 = nullptr; device = -1;
+    }
+};
+thread_local Workspace *g_ws[64];
+
+int workspace(int device, Workspace **out) {
+    int rc = check_device(device);
+    if (rc) return rc;
+    if (device >= 64) return fail(BA_ERR_INVALID, "device %d: at most 64 devices", device);
+    Workspace *&w = g_ws[device];
+    if (!w) w = new Workspace();
+    if (w->device < 0) {
+        CU(cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking));
+        CU(cudaEventCreate(&w->e1));
+        CU(cudaEventCreate(&w->e2));
+        w->device = device;
+    }
+    *out = w;
+    return BA_OK;
+}
+
+template <typename T>
+int ws_upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) { return upload(b, src, count, s); }
+
+} // namespace
+
+extern "C" int ba_release_workspace(void) {
+    for (Workspace *&w : g_ws)
+        if (w) { w->release(); delete w; w = nullptr; }
+    return BA_OK;
+}
 
 extern "C" int ba_solve_pose_only_batch(const ba_options *opt_in, int device, int32_t B, double *cam, const float *K,
                                         const int32_t *prob_ptr, const float *Xh, const float *uv, const uint8_t *obs_mask,
                                         ba_summary *summaries, ba_iteration *iters, int32_t iters_cap) {
     if (B < 0 || (B && (!cam || !K || !prob_ptr))) return fail(BA_ERR_INVALID, "bad arguments");
-    int rc = check_device(device);
+    Workspace *w;
+    int rc = workspace(device, &w);
     if (rc) return rc;
     if (B == 0) return BA_OK;
     ba_options opt;
@@ -1052,38 +1103,32 @@ extern "C" int ba_solve_pose_only_batch(const ba_options *opt_in, int device, in
         if (prob_ptr[b + 1] < prob_ptr[b]) return fail(BA_ERR_INVALID, "prob_ptr not monotone at %d", b);
     if (No && (!Xh || !uv)) return fail(BA_ERR_INVALID, "NULL observation arrays");
     if (iters && iters_cap <= 0) return fail(BA_ERR_INVALID, "iters given but iters_cap <= 0");
-    cudaStream_t s;
-    CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-    DevBuf dcam, dK, dptr, dX, duv, dmask, dsum, dit;
-    CU(dcam.alloc(48 * (size_t)B)); CU(dK.alloc(36 * (size_t)B)); CU(dptr.alloc(4 * (size_t)(B + 1)));
-    CU(dX.alloc(16 * std::max<size_t>(No, 1))); CU(duv.alloc(8 * std::max<size_t>(No, 1)));
-    CU(dsum.alloc(sizeof(ba_summary) * (size_t)B));
-    if (obs_mask) CU(dmask.alloc(std::max<size_t>(No, 1)));
-    if (iters) CU(dit.alloc(sizeof(ba_iteration) * (size_t)B * iters_cap));
-    cudaEvent_t e1, e2;
-    CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
-    CU(cudaMemcpyAsync(dcam.p, cam, 48 * (size_t)B, cudaMemcpyHostToDevice, s));
-    CU(cudaMemcpyAsync(dK.p, K, 36 * (size_t)B, cudaMemcpyHostToDevice, s));
-    CU(cudaMemcpyAsync(dptr.p, prob_ptr, 4 * (size_t)(B + 1), cudaMemcpyHostToDevice, s));
-    if (No) {
-        CU(cudaMemcpyAsync(dX.p, Xh, 16 * (size_t)No, cudaMemcpyHostToDevice, s));
-        CU(cudaMemcpyAsync(duv.p, uv, 8 * (size_t)No, cudaMemcpyHostToDevice, s));
-        if (obs_mask) CU(cudaMemcpyAsync(dmask.p, obs_mask, (size_t)No, cudaMemcpyHostToDevice, s));
+    cudaStream_t s = w->stream;
+    if ((rc = ws_upload(w->cam, cam, 6 * (size_t)B, s))) return rc;
+    if ((rc = ws_upload(w->K, K, 9 * (size_t)B, s))) return rc;
+    if ((rc = ws_upload(w->ptr, prob_ptr, (size_t)B + 1, s))) return rc;
+    if ((rc = ws_upload(w->Xh, Xh, 4 * (size_t)No, s))) return rc;
+    if ((rc = ws_upload(w->uv, uv, 2 * (size_t)No, s))) return rc;
+    if (obs_mask && (rc = ws_upload(w->mask, obs_mask, (size_t)No, s))) return rc;
+    CU(w->sum.alloc(sizeof(ba_summary) * (size_t)B));
+    if (iters) {
+        CU(w->it.alloc(sizeof(ba_iteration) * (size_t)B * iters_cap));
+        CU(cudaMemsetAsync(w->it.p, 0, w->it.bytes, s));
     }
-    if (iters) CU(cudaMemsetAsync(dit.p, 0, dit.bytes, s));
-    CU(cudaEventRecord(e1, s));
-    launch_pose_batch(opt, B, dcam.as<double>(), dK.as<float>(), dptr.as<int>(), dX.as<float4>(), duv.as<float2>(),
-                      obs_mask ? dmask.as<uint8_t>() : nullptr, dsum.as<ba_summary>(), iters ? dit.as<ba_iteration>() : nullptr,
+    CU(cudaEventRecord(w->e1, s));
+    launch_pose_batch(opt, B, w->cam.as<double>(), w->K.as<float>(), w->ptr.as<int>(), w->Xh.as<float4>(), w->uv.as<float2>(),
+                      obs_mask ? w->mask.as<uint8_t>() : nullptr, w->sum.as<ba_summary>(), iters ? w->it.as<ba_iteration>() : nullptr,
                       iters_cap, s);
-    CU(cudaEventRecord(e2, s));
-    CU(cudaMemcpyAsync(cam, dcam.p, 48 * (size_t)B, cudaMemcpyDeviceToHost, s));
+    w->launches = 1;
+    CU(cudaEventRecord(w->e2, s));
+    CU(cudaMemcpyAsync(cam, w->cam.p, 48 * (size_t)B, cudaMemcpyDeviceToHost, s));
     std::vector<ba_summary> sm(B);
-    CU(cudaMemcpyAsync(sm.data(), dsum.p, sizeof(ba_summary) * (size_t)B, cudaMemcpyDeviceToHost, s));
-    if (iters) CU(cudaMemcpyAsync(iters, dit.p, dit.bytes, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(sm.data(), w->sum.p, sizeof(ba_summary) * (size_t)B, cudaMemcpyDeviceToHost, s));
+    if (iters) CU(cudaMemcpyAsync(iters, w->it.p, w->it.bytes, cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
     float ms = 0;
-    cudaEventElapsedTime(&ms, e1, e2);
+    cudaEventElapsedTime(&ms, w->e1, w->e2);
     if (summaries) {
         for (int b = 0; b < B; ++b) {
             ba_summary &o = summaries[b];
@@ -1099,49 +1144,117 @@ extern "C" int ba_solve_pose_only_batch(const ba_options *opt_in, int device, in
             }
         }
     }
-    cudaEventDestroy(e1); cudaEventDestroy(e2);
-    dcam.free(); dK.free(); dptr.free(); dX.free(); duv.free(); dmask.free(); dsum.free(); dit.free();
-    cudaStreamDestroy(s);
     return BA_OK;
 }
+
+namespace {
+// keypoint arrays of a set of frames -> workspace (shared by ba_prune_frames and ba_solve_pose_only_outer)
+int upload_keypoints(Workspace *w, int F, const float *pose, const float *K, const int32_t *frame_ptr, const float *kp_xy,
+                     const int32_t *kp_octave, const float *pt_xyz, const float *pt_min_dist, const float *pt_max_dist,
+                     const uint8_t *has_point, const uint8_t *outlier) {
+    cudaStream_t s = w->stream;
+    const size_t n = (size_t)frame_ptr[F];
+    int rc;
+    if ((rc = ws_upload(w->pose, pose, 16 * (size_t)F, s))) return rc;
+    if ((rc = ws_upload(w->K, K, 9 * (size_t)F, s))) return rc;
+    if ((rc = ws_upload(w->ptr, frame_ptr, (size_t)F + 1, s))) return rc;
+    if ((rc = ws_upload(w->xy, kp_xy, 2 * n, s))) return rc;
+    if ((rc = ws_upload(w->oct, kp_octave, n, s))) return rc;
+    if ((rc = ws_upload(w->xyz, pt_xyz, 3 * n, s))) return rc;
+    if ((rc = ws_upload(w->mn, pt_min_dist, n, s))) return rc;
+    if ((rc = ws_upload(w->mx, pt_max_dist, n, s))) return rc;
+    if ((rc = ws_upload(w->has, has_point, n, s))) return rc;
+    if ((rc = ws_upload(w->out, outlier, n, s))) return rc;
+    CU(w->extr.alloc(64 * (size_t)F));
+    return BA_OK;
+}
+} // namespace
 
 extern "C" int ba_prune_frames(int device, int32_t n_frames, const float *pose, const float *K, const int32_t *frame_ptr,
                                const float *kp_xy, const int32_t *kp_octave, const float *pt_xyz, const float *pt_min_dist,
                                const float *pt_max_dist, const uint8_t *has_point, uint8_t *outlier, int32_t consider_outlier) {
     if (n_frames < 0 || (n_frames && (!pose || !K || !frame_ptr))) return fail(BA_ERR_INVALID, "bad arguments");
-    int rc = check_device(device);
+    Workspace *w;
+    int rc = workspace(device, &w);
     if (rc) return rc;
     if (n_frames == 0) return BA_OK;
     const int n_kp = frame_ptr[n_frames];
     if (n_kp == 0) return BA_OK;
     if (!kp_xy || !kp_octave || !pt_xyz || !pt_min_dist || !pt_max_dist || !has_point || !outlier) return fail(BA_ERR_INVALID, "NULL keypoint arrays");
-    // extr = pose.inverse() in float32, once per frame (Optimizer.cpp:10)
-    std::vector<float> extr(16 * (size_t)n_frames);
-    for (int f = 0; f < n_frames; ++f) ba_inverse4x4_f32(pose + 16 * (size_t)f, extr.data() + 16 * (size_t)f);
-    DevBuf dpose, dextr, dK, dptr, dxy, doct, dpt, dmin, dmax, dhas, dout;
-    CU(dpose.alloc(64 * (size_t)n_frames)); CU(dextr.alloc(64 * (size_t)n_frames)); CU(dK.alloc(36 * (size_t)n_frames));
-    CU(dptr.alloc(4 * (size_t)(n_frames + 1)));
-    CU(dxy.alloc(8 * (size_t)n_kp)); CU(doct.alloc(4 * (size_t)n_kp)); CU(dpt.alloc(12 * (size_t)n_kp));
-    CU(dmin.alloc(4 * (size_t)n_kp)); CU(dmax.alloc(4 * (size_t)n_kp)); CU(dhas.alloc((size_t)n_kp)); CU(dout.alloc((size_t)n_kp));
-    CU(cudaMemcpy(dpose.p, pose, dpose.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dextr.p, extr.data(), dextr.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dK.p, K, dK.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dptr.p, frame_ptr, dptr.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dxy.p, kp_xy, dxy.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(doct.p, kp_octave, doct.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dpt.p, pt_xyz, dpt.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dmin.p, pt_min_dist, dmin.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dmax.p, pt_max_dist, dmax.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dhas.p, has_point, dhas.bytes, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(dout.p, outlier, dout.bytes, cudaMemcpyHostToDevice));
-    launch_prune(n_frames, dpose.as<float>(), dextr.as<float>(), dK.as<float>(), dptr.as<int>(), dxy.as<float2>(), doct.as<int>(),
-                 dpt.as<float>(), dmin.as<float>(), dmax.as<float>(), dhas.as<uint8_t>(), dout.as<uint8_t>(), consider_outlier, n_kp, 0);
-    CU(cudaDeviceSynchronize());
+    cudaStream_t s = w->stream;
+    if ((rc = upload_keypoints(w, n_frames, pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min_dist, pt_max_dist, has_point, outlier))) return rc;
+    launch_pose_inverse(n_frames, w->pose.as<float>(), w->extr.as<float>(), s);       // extr = pose.inverse() in float32 (Optimizer.cpp:10)
+    launch_prune(n_frames, w->pose.as<float>(), w->extr.as<float>(), w->K.as<float>(), w->ptr.as<int>(), w->xy.as<float2>(), w->oct.as<int>(),
+                 w->xyz.as<float>(), w->mn.as<float>(), w->mx.as<float>(), w->has.as<uint8_t>(), w->out.as<uint8_t>(), consider_outlier, n_kp, s);
+    w->launches = 2;
+    CU(cudaMemcpyAsync(outlier, w->out.p, (size_t)n_kp, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
-    CU(cudaMemcpy(outlier, dout.p, dout.bytes, cudaMemcpyDeviceToHost));
-    DevBuf *all[] = {&dpose, &dextr, &dK, &dptr, &dxy, &doct, &dpt, &dmin, &dmax, &dhas, &dout};
-    for (DevBuf *b : all) b->free();
     return BA_OK;
+}
+
+// SfMHelper::estimatePoseUsingBA's loop (SfMHelper.cpp:106-117: setNbOfIterations(4), setNbOfMaxItPerBA(20)) over a batch of
+// frames, device-resident: per outer iteration  pose -> (angle-axis, t)  |  observation mask = has point && !outlier  |  one
+// ceres::Solve replacement per frame (pose_batch_kernel)  |  write-back pose = inverse(f32 extrinsics)  |
+// pruneCorrespondences(frame, considerOutlier = true) -- five launches, nothing crosses PCIe between them.
+extern "C" int ba_solve_pose_only_outer(const ba_options *opt_in, int device, int32_t n_frames, float *pose, const float *K,
+                                        const int32_t *frame_ptr, const float *kp_xy, const int32_t *kp_octave,
+                                        const float *pt_xyz, const float *pt_min_dist, const float *pt_max_dist,
+                                        const uint8_t *has_point, uint8_t *outlier, int32_t n_outer, ba_summary *summaries,
+                                        float *device_ms) {
+    if (n_frames < 0 || n_outer < 0 || (n_frames && (!pose || !K || !frame_ptr))) return fail(BA_ERR_INVALID, "bad arguments");
+    Workspace *w;
+    int rc = workspace(device, &w);
+    if (rc) return rc;
+    if (device_ms) *device_ms = 0.f;
+    if (n_frames == 0) return BA_OK;
+    const int F = n_frames, n_kp = frame_ptr[F];
+    for (int f = 0; f < F; ++f)
+        if (frame_ptr[f + 1] < frame_ptr[f]) return fail(BA_ERR_INVALID, "frame_ptr not monotone at %d", f);
+    if (n_kp && (!kp_xy || !kp_octave || !pt_xyz || !pt_min_dist || !pt_max_dist || !has_point || !outlier)) return fail(BA_ERR_INVALID, "NULL keypoint arrays");
+    ba_options opt;
+    if (opt_in) opt = *opt_in; else { ba_default_options(&opt); opt.max_num_iterations = 20; }
+    cudaStream_t s = w->stream;
+    if ((rc = upload_keypoints(w, F, pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min_dist, pt_max_dist, has_point, outlier))) return rc;
+    CU(w->cam.alloc(48 * (size_t)F));
+    CU(w->sum.alloc(sizeof(ba_summary) * (size_t)F));
+    CU(w->mask.alloc(std::max<size_t>(n_kp, 1)));
+    CU(w->Xh.alloc(16 * std::max<size_t>(n_kp, 1)));
+    CU(cudaEventRecord(w->e1, s));
+    w->launches = 0;
+    for (int it = 0; it < n_outer; ++it) {
+        launch_pose_to_cam(F, w->pose.as<float>(), w->cam.as<double>(), s);
+        launch_pose_mask(n_kp, w->has.as<uint8_t>(), w->out.as<uint8_t>(), w->mask.as<uint8_t>(), w->xyz.as<float>(), it == 0 ? w->Xh.as<float4>() : nullptr, s);
+        launch_pose_batch(opt, F, w->cam.as<double>(), w->K.as<float>(), w->ptr.as<int>(), w->Xh.as<float4>(), w->xy.as<float2>(),
+                          w->mask.as<uint8_t>(), w->sum.as<ba_summary>(), nullptr, 0, s);
+        launch_cam_to_pose(F, w->cam.as<double>(), w->pose.as<float>(), w->extr.as<float>(), s);
+        launch_prune(F, w->pose.as<float>(), w->extr.as<float>(), w->K.as<float>(), w->ptr.as<int>(), w->xy.as<float2>(), w->oct.as<int>(),
+                     w->xyz.as<float>(), w->mn.as<float>(), w->mx.as<float>(), w->has.as<uint8_t>(), w->out.as<uint8_t>(), 1, n_kp, s);
+        w->launches += n_kp ? 5 : 3;
+    }
+    CU(cudaEventRecord(w->e2, s));
+    CU(cudaMemcpyAsync(pose, w->pose.p, 64 * (size_t)F, cudaMemcpyDeviceToHost, s));
+    if (n_kp) CU(cudaMemcpyAsync(outlier, w->out.p, (size_t)n_kp, cudaMemcpyDeviceToHost, s));
+    std::vector<ba_summary> sm(summaries && n_outer ? F : 0);
+    if (!sm.empty()) CU(cudaMemcpyAsync(sm.data(), w->sum.p, sizeof(ba_summary) * (size_t)F, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    float ms = 0;
+    cudaEventElapsedTime(&ms, w->e1, w->e2);
+    if (device_ms) *device_ms = ms;
+    for (size_t b = 0; b < sm.size(); ++b) {
+        ba_summary &o = summaries[b];
+        o = sm[b];
+        const int msg = (int)(unsigned char)o.message[0];
+        std::snprintf(o.message, sizeof(o.message), "%s", message_text(msg));
+        o.seconds_total = ms * 1e-3;         // whole batch, all outer iterations
+    }
+    return BA_OK;
+}
+
+// kernels the last handle-less call of this thread launched on `device` (benchmark bookkeeping)
+extern "C" int ba_workspace_launch_count(int device) {
+    return (device >= 0 && device < 64 && g_ws[device]) ? g_ws[device]->launches : 0;
 }
 
 // =============================================================================================================

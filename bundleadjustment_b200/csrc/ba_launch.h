@@ -110,6 +110,10 @@ void launch_pcg_finish(const Ctx &ctx, cudaStream_t s);      // copies x -> yc, 
 void launch_pose_batch(const ba_options &opt, int B, double *cam, const float *K, const int *prob_ptr,
                        const float4 *Xh, const float2 *uv, const uint8_t *mask, ba_summary *summaries,
                        ba_iteration *iters, int iters_cap, cudaStream_t s);
+void launch_pose_to_cam(int F, const float *pose, double *cam, cudaStream_t s);                       // Optimizer.cpp:462-465 per frame
+void launch_cam_to_pose(int F, const double *cam, float *pose, float *extr, cudaStream_t s);          // write-back + extr = pose^-1
+void launch_pose_inverse(int F, const float *pose, float *extr, cudaStream_t s);                      // extr = pose^-1 (f32)
+void launch_pose_mask(int n_kp, const uint8_t *has_point, const uint8_t *outlier, uint8_t *mask, const float *xyz, float4 *Xh, cudaStream_t s);
 void launch_prune(int n_frames, const float *pose, const float *extr, const float *K, const int *frame_ptr, const float2 *kp_xy,
                   const int *kp_octave, const float *pt_xyz, const float *pt_min, const float *pt_max,
                   const uint8_t *has_point, uint8_t *outlier, int consider_outlier, int n_kp, cudaStream_t s);

@@ -6,6 +6,7 @@
 // Ceres' Schur ordering eliminates it as the only e-block, i.e. each LM step is the damped 6x6 normal-equation
 // solve ("degenerate case for R3/K3").  One CTA per problem runs the WHOLE trust-region loop.
 #include "ba_launch.h"
+#include "ba_pose_math.cuh"
 
 namespace ba {
 
@@ -314,6 +315,63 @@ __global__ void prune_kernel(int n_frames, const float *__restrict__ pose, const
     const float chi = __fmul_rn(dist, invSigmaP);
     if (chi > chiThresh) { outlier[i] = 1; return; }
     outlier[i] = 0;
+}
+
+// ---- device-resident outer loop of SfMHelper::estimatePoseUsingBA (SfMHelper.cpp:106-117 -> Optimizer.cpp:417-457) ----
+// per frame: pose (f32, camera->world) -> extrinsics (f32 inverse) -> angle-axis + translation (f64)   [Optimizer.cpp:462-465]
+__global__ void pose_to_cam_kernel(int F, const float *__restrict__ pose, double *__restrict__ cam) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    float extr[16];
+    double c[6];
+    dev_pose_to_cam(pose + 16 * (size_t)f, c, extr);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cam[6 * (size_t)f + k] = c[k];
+}
+// per frame: write-back (Optimizer.cpp:448-453) pose = inverse(f32(R(cam), t)), and the extrinsics pruneCorrespondences
+// derives from that pose (Optimizer.cpp:10: extr = pose.inverse())
+__global__ void cam_to_pose_kernel(int F, const double *__restrict__ cam, float *__restrict__ pose, float *__restrict__ extr) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    float P[16], E[16];
+    double c[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) c[k] = cam[6 * (size_t)f + k];
+    dev_cam_to_pose(c, P);
+    dev_inverse4x4_f32(P, E);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { pose[16 * (size_t)f + k] = P[k]; extr[16 * (size_t)f + k] = E[k]; }
+}
+// extr = pose.inverse() alone (ba_prune_frames)
+__global__ void pose_inverse_kernel(int F, const float *__restrict__ pose, float *__restrict__ extr) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    float E[16];
+    dev_inverse4x4_f32(pose + 16 * (size_t)f, E);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) extr[16 * (size_t)f + k] = E[k];
+}
+// per keypoint: the observation list of the next solve = keypoints with a map point that are not outliers (Optimizer.cpp:472);
+// Xh = MapPoint::getPosition().homogeneous() (Optimizer.cpp:482), written once
+__global__ void pose_mask_kernel(int n_kp, const uint8_t *__restrict__ has_point, const uint8_t *__restrict__ outlier, uint8_t *__restrict__ mask,
+                                 const float *__restrict__ xyz, float4 *__restrict__ Xh) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_kp) return;
+    mask[i] = (has_point[i] && !outlier[i]) ? 1 : 0;
+    if (Xh) Xh[i] = make_float4(xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2], 1.0f);
+}
+
+void launch_pose_to_cam(int F, const float *pose, double *cam, cudaStream_t s) {
+    if (F > 0) pose_to_cam_kernel<<<(F + 127) / 128, 128, 0, s>>>(F, pose, cam);
+}
+void launch_cam_to_pose(int F, const double *cam, float *pose, float *extr, cudaStream_t s) {
+    if (F > 0) cam_to_pose_kernel<<<(F + 127) / 128, 128, 0, s>>>(F, cam, pose, extr);
+}
+void launch_pose_inverse(int F, const float *pose, float *extr, cudaStream_t s) {
+    if (F > 0) pose_inverse_kernel<<<(F + 127) / 128, 128, 0, s>>>(F, pose, extr);
+}
+void launch_pose_mask(int n_kp, const uint8_t *has_point, const uint8_t *outlier, uint8_t *mask, const float *xyz, float4 *Xh, cudaStream_t s) {
+    if (n_kp > 0) pose_mask_kernel<<<(n_kp + 255) / 256, 256, 0, s>>>(n_kp, has_point, outlier, mask, xyz, Xh);
 }
 
 void launch_pose_batch(const ba_options &opt, int B, double *cam, const float *K, const int *prob_ptr,

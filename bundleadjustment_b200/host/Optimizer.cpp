@@ -253,6 +253,60 @@ void MotionOnlyBAOptimizerAngles::optimizeCameraPoses(const std::vector<std::sha
     ba_options opt;
     ba_default_options(&opt);
     opt.max_num_iterations = (int32_t)m_nMaxItPerBA;
+    // The whole outer loop (Optimizer.cpp:422-456: build, Solve, write-back, pruneCorrespondences(frame, true)) runs on the
+    // device: the object graph is walked ONCE into per-keypoint arrays, ba_solve_pose_only_outer iterates, and poses and outlier
+    // bits are written back through the setters at the end.  A map point whose registered keypoint position differs from the
+    // frame's own keypoint (two keypoints matched to one map point) cannot be expressed per keypoint: such batches take the
+    // per-iteration host loop below, which calls the same kernels one outer iteration at a time.
+    std::vector<int32_t> ptr(B + 1, 0);
+    for (int b = 0; b < B; ++b) ptr[b + 1] = ptr[b] + frames[b]->getKeypointCount();
+    const size_t n = (size_t)ptr[B];
+    std::vector<float> pose(16 * (size_t)B), K(9 * (size_t)B), xy(2 * n), xyz(3 * n, 0.f), mn(n, 0.f), mx(n, 0.f);
+    std::vector<int32_t> octave(n, 0);
+    std::vector<uint8_t> has(n, 0), out(n, 0);
+    bool perKeypoint = true;
+    for (int b = 0; b < B && perKeypoint; ++b) {
+        const std::shared_ptr<Frame> &frame = frames[b];
+        toRowMajor4(frame->getPose(), &pose[16 * (size_t)b]);
+        toRowMajor3(frame->getIntrinsics(), &K[9 * (size_t)b]);
+        const auto points = frame->getMapPoints();
+        for (int j = 0, cnt = ptr[b + 1] - ptr[b]; j < cnt; ++j) {
+            const size_t k = (size_t)ptr[b] + j;
+            const cv::KeyPoint *kp = frame->getKeypoint(j);
+            xy[2 * k] = kp->pt.x; xy[2 * k + 1] = kp->pt.y;
+            octave[k] = kp->octave;
+            out[k] = frame->isOutlier(j) ? 1 : 0;
+            const std::shared_ptr<MapPoint> mp = j < (int)points.size() ? points[j] : nullptr;
+            if (!mp) continue;
+            has[k] = 1;
+            const Vector3f p = mp->getPosition();
+            xyz[3 * k] = p(0); xyz[3 * k + 1] = p(1); xyz[3 * k + 2] = p(2);
+            mn[k] = mp->getMinDistance(); mx[k] = mp->getMaxDistance();
+            const Vector2f reg = mp->getCorresponding2DKeyPointPosition(frame);
+            if (reg(0) != kp->pt.x || reg(1) != kp->pt.y) { perKeypoint = false; break; }
+        }
+    }
+    if (perKeypoint) {
+        std::vector<uint8_t> before(out);
+        std::vector<ba_summary> sms(B);
+        if (fail(ba_solve_pose_only_outer(&opt, m_device, B, pose.data(), K.data(), ptr.data(), xy.data(), octave.data(), xyz.data(),
+                                          mn.data(), mx.data(), has.data(), out.data(), (int32_t)m_nIterations, sms.data(), nullptr)))
+            return;
+        if (m_nIterations > 0) {
+            m_lastTermination = sms[0].termination_type;
+            m_lastInitialCost = sms[0].initial_cost;
+            m_lastFinalCost = sms[0].final_cost;
+            m_lastNumIterations = sms[0].num_iterations;
+            for (int b = 0; b < B; ++b) frames[b]->setPose(fromRowMajor4(&pose[16 * (size_t)b]));   // Optimizer.cpp:448-453
+        }
+        for (int b = 0; b < B; ++b)
+            for (int j = 0, cnt = ptr[b + 1] - ptr[b]; j < cnt; ++j) {
+                const size_t k = (size_t)ptr[b] + j;
+                if (out[k] == before[k]) continue;
+                if (out[k]) frames[b]->setOutlier(j); else frames[b]->setInlier(j);
+            }
+        return;
+    }
     for (unsigned it = 0; it < m_nIterations; ++it) {
         std::vector<double> cam(6 * (size_t)B);
         std::vector<float> K(9 * (size_t)B), Xh, uv;

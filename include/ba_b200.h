@@ -153,6 +153,26 @@ int ba_prune_frames(int device, int32_t n_frames, const float *pose /*16F*/, con
                     const float *pt_xyz, const float *pt_min_dist, const float *pt_max_dist,
                     const uint8_t *has_point, uint8_t *outlier /*in/out*/, int32_t consider_outlier);
 
+/* ---- SfMHelper::estimatePoseUsingBA's whole loop (SfMHelper.cpp:106-117: 4 outer iterations x <= 20 LM iterations,
+ * Optimizer.cpp:417-457), batched over frames and DEVICE-RESIDENT: per outer iteration the pose -> parameter conversion
+ * (Optimizer.cpp:462-465), the observation list (keypoints with a map point that are not outliers, :472), one ceres::Solve
+ * replacement per frame, the float32 write-back (:448-453) and pruneCorrespondences(frame, considerOutlier = true) (:455)
+ * run as five kernel launches; nothing crosses PCIe between outer iterations.  Keypoint arrays as in ba_prune_frames
+ * (pt_xyz = the keypoint's map point position, float32, constant).  pose and outlier are updated in place.
+ * summaries (may be NULL): the LAST outer iteration's ba_summary per frame.  device_ms (may be NULL): device time. */
+int ba_solve_pose_only_outer(const ba_options *opt, int device, int32_t n_frames, float *pose /*16F in/out*/,
+                             const float *K /*9F*/, const int32_t *frame_ptr, const float *kp_xy,
+                             const int32_t *kp_octave, const float *pt_xyz, const float *pt_min_dist,
+                             const float *pt_max_dist, const uint8_t *has_point, uint8_t *outlier /*in/out*/,
+                             int32_t n_outer, ba_summary *summaries, float *device_ms);
+
+/* The handle-less entry points (ba_solve_pose_only_batch, ba_prune_frames, ba_solve_pose_only_outer) keep one stream, two
+ * events and grow-only device buffers per calling thread and device, so that the per-frame calls of the tracker never
+ * allocate.  ba_release_workspace frees the calling thread's workspaces; ba_workspace_launch_count = kernels the thread's
+ * last such call launched on `device` (benchmark bookkeeping). */
+int ba_release_workspace(void);
+int ba_workspace_launch_count(int device);
+
 /* ---- multi-GPU: landmark-sharded, one process per GPU, NCCL over NVLink ------------------------------- *
  * Rank r owns a contiguous landmark range and all of its observations; cameras are replicated.  Every rank
  * passes the FULL camera arrays and its LOCAL landmarks/observations (obs_pt local) to ba_set_problem after

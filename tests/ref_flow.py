@@ -132,21 +132,57 @@ def local_ba(orc, g: Graph, current, cov, n_outer=1, max_it=10) -> Graph:
     return g
 
 
-def motion_only(orc, g: Graph, n_outer=4, max_it=20) -> Graph:
+def pose_graph_from_batch(batch: PoseBatch, seed=0) -> Graph:
+    """K3's 1 000 independent frame-to-frame problems as an object graph: frame b observes its own private landmarks
+    (no sharing between frames), the initial pose is the float32 camera->world matrix of batch.cam, a few keypoints start as
+    outliers (they can become inliers again: considerOutlier = true) and a few have no map point."""
+    rng = np.random.default_rng(seed)
+    from oracle import ba_oracle as orc
+    B = batch.cam.shape[0]
+    n = int(batch.prob_ptr[-1])
+    pose = np.stack([orc.cam_to_pose(batch.cam[b]) for b in range(B)]).astype(np.float32)
+    pt = np.ascontiguousarray(batch.Xh[:, :3], np.float32)
+    kp_frame = np.repeat(np.arange(B), np.diff(batch.prob_ptr))
+    centre = pose[kp_frame, :3, 3]
+    d = np.linalg.norm(pt - centre, axis=1)
+    kp_point = np.arange(n, dtype=np.int32)
+    kp_point[rng.random(n) < 0.01] = -1
+    return Graph(pose=pose, K=np.ascontiguousarray(batch.K.reshape(B, 3, 3)), frame_id=np.arange(1, B + 1, dtype=np.int32),
+                 kp_ptr=batch.prob_ptr.astype(np.int32), kp_xy=batch.uv.copy(), kp_octave=rng.integers(0, 4, n).astype(np.int32),
+                 kp_point=kp_point, kp_outlier=(rng.random(n) < 0.03).astype(np.uint8), pt=pt,
+                 pt_min=(0.2 * d).astype(np.float32), pt_max=(3.0 * d).astype(np.float32))
+
+
+def keypoint_arrays(g: Graph):
+    """per-keypoint map point data as ba_prune_frames / ba_solve_pose_only_outer take it"""
+    has = (g.kp_point >= 0).astype(np.uint8)
+    pi = np.where(g.kp_point >= 0, g.kp_point, 0)
+    return g.pt[pi], g.pt_min[pi], g.pt_max[pi], has
+
+
+def run_pose_outer(bab, g: Graph, n_outer=4, max_it=20) -> Graph:
+    """the device-resident outer loop (ba_solve_pose_only_outer) on the same graph"""
+    xyz, mn, mx, has = keypoint_arrays(g)
+    pose, out, sms, ms = bab.capi.solve_pose_only_outer(g.pose, g.K.reshape(-1, 9), g.kp_ptr, g.kp_xy, g.kp_octave, xyz, mn, mx, has,
+                                                        g.kp_outlier, n_outer=n_outer, options=bab.default_options(max_num_iterations=max_it))
+    res = dataclasses.replace(g, pose=pose.copy(), kp_outlier=out.copy())
+    res.sms, res.device_ms = sms, ms
+    return res
+
+
+def motion_only(orc, g: Graph, n_outer=4, max_it=20, threads=8) -> Graph:
     g = dataclasses.replace(g, pose=g.pose.copy(), pt=g.pt.copy(), kp_outlier=g.kp_outlier.copy())
     Nc = g.pose.shape[0]
     for _ in range(n_outer):
-        cam = np.zeros((Nc, 6)); ptr = [0]; Xh, uv = [], []
-        for f in range(Nc):
-            cam[f], _ = orc.pose_to_cam(g.pose[f])
-            for k in range(g.kp_ptr[f], g.kp_ptr[f + 1]):
-                p = int(g.kp_point[k])
-                if p >= 0 and not g.kp_outlier[k]:
-                    Xh.append([*g.pt[p], 1.0]); uv.append(g.kp_xy[k])
-            ptr.append(len(uv))
-        batch = PoseBatch(cam=cam, K=np.ascontiguousarray(g.K.reshape(-1, 9)), prob_ptr=np.array(ptr, np.int32),
-                          Xh=np.array(Xh, np.float32).reshape(-1, 4), uv=np.array(uv, np.float32).reshape(-1, 2), gt_cam=cam)
-        out, sms, _ = orc.solve_pose_only_batch(batch, orc.default_options(max_num_iterations=max_it, num_threads=8))
+        cam = np.stack([orc.pose_to_cam(g.pose[f])[0] for f in range(Nc)])
+        keep = (g.kp_point >= 0) & (g.kp_outlier == 0)                      # Optimizer.cpp:472, keypoint order kept
+        kp_frame = np.repeat(np.arange(Nc), np.diff(g.kp_ptr))
+        ptr = np.zeros(Nc + 1, np.int32)
+        ptr[1:] = np.cumsum(np.bincount(kp_frame[keep], minlength=Nc))
+        Xh = np.concatenate([g.pt[g.kp_point[keep]], np.ones((int(keep.sum()), 1), np.float32)], 1).astype(np.float32)
+        batch = PoseBatch(cam=cam, K=np.ascontiguousarray(g.K.reshape(-1, 9)), prob_ptr=ptr,
+                          Xh=np.ascontiguousarray(Xh), uv=np.ascontiguousarray(g.kp_xy[keep], np.float32), gt_cam=cam)
+        out, sms, _ = orc.solve_pose_only_batch(batch, orc.default_options(max_num_iterations=max_it, num_threads=threads))
         for f in range(Nc):
             g.pose[f] = orc.cam_to_pose(out[f])
         _prune(orc, g, range(Nc), True)
