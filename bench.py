@@ -1,21 +1,36 @@
 #!/usr/bin/env python
 """bench.py -- LM iterations/sec of the BA hot path on synthetic scenes of the named shapes.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload K1|K2|K4|K5] [--solver dense|pcg]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload K1|K2|K3|K4|K5] [--solver dense|pcg]
 
-A "step" = one ceres::Solve replacement (ba_solve, <= --lm-iters LM iterations, the reference's per-keyframe setting
-`setNbOfMaxItPerBA(10)`, BundleAdjustment.cpp:204-205) over the whole workload starting from the same initial
-parameters.  `value` = LM iterations per second with the problem resident in HBM (device time, CUDA events, max over
-ranks); `e2e` = the same through the C ABI with HOST buffers (ba_set_problem H2D + ba_solve + ba_get_* D2H inside the
-timed region).  N > 1: landmarks are sharded over ranks (strong scaling), NCCL all-reduces the reduced system.
+Headline (`value`, `e2e`, `roofline`, `parity`): BASELINE.json configs[3] = K4 (1 700 cameras / 500 k landmarks / ~2 M
+observations, dense Schur, Huber).  A "step" = one ceres::Solve replacement (ba_solve, <= --lm-iters LM iterations, the
+reference's per-keyframe setting `setNbOfMaxItPerBA(10)`, BundleAdjustment.cpp:204-205) over the whole workload from the
+same initial parameters.  `value` = LM iterations per second with the problem resident in HBM (device time, CUDA events,
+max over ranks); `e2e` = the same through the C ABI with page-locked HOST buffers (ba_set_problem H2D + ba_solve + ba_get_*
+D2H inside the timed region).  N > 1: landmarks are sharded over ranks (strong scaling), NCCL all-reduces the reduced system.
+
+Parity gate BEFORE the timed region: at N > 1 the sharded solve is compared with a single-GPU solve
+of the same problem on rank 0; at N = 1 the CUDA solution is compared with the solution of the CPU baseline sample (the
+oracle port running the SAME configuration).  The JSON line carries `parity: {..., ok}`.
+
+The line ends with two compact objects measured in the same process at every N: `k3` (BASELINE configs[2]: 1 000
+frame-to-frame pose problems x 500 landmarks, 4 outer x <= 20 LM iterations with prune, then a K1-shaped keyframe BA,
+rank 0 only -- the path does not shard) and, as the LAST key, `k5` (BASELINE configs[4]: 13 k cameras / 4.5 M landmarks /
+30 M observations, Schur-Jacobi PCG, landmark-sharded like K4).
 
 --impl reference: the reference's own CPU implementation of the path.  Real Ceres is not in this image, so this is the
-C++ CPU oracle (oracle/, "port") on all host threads, each step a bounded sample (max 1 LM iteration) of the same
-workload.  Only this leg and cpu_baseline execute anything under oracle/.
+C++ CPU oracle (oracle/, "port") on all host threads, each step one solve of the SAME configuration (same workload, same
+--lm-iters).  The oracle's factorisation skips the structurally zero part of S like the CUDA tile plan does
+(exploit_sparsity: bit-identical results); the dense-factorisation figure, which is what Ceres' DENSE_SCHUR would do, is
+reported beside it.  Only this leg and cpu_baseline execute anything under oracle/; the reference arm does not import the
+product package.
 """
 from __future__ import annotations
 
 import argparse
+import dataclasses
+import importlib.util
 import json
 import os
 import subprocess
@@ -46,18 +61,38 @@ def emit(obj) -> None:
     os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
 
 
+def _load_by_path(name: str, rel: str):
+    """Import one numpy-only module of the package WITHOUT importing the package (whose __init__ dlopens libba_b200.so): the
+    reference arm must not load the product library."""
+    spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, rel))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+_SYN = None
+
+
+def synthetic():
+    global _SYN
+    if _SYN is None:
+        _SYN = sys.modules.get("bundleadjustment_b200.synthetic") or _load_by_path("_ba_synthetic", "bundleadjustment_b200/synthetic.py")
+    return _SYN
+
+
 def load_workload(name: str, scale: float = 1.0, path: str | None = None):
-    from bundleadjustment_b200 import synthetic as syn
+    syn = synthetic()
     t = time.time()
     if path:                                  # a BAL text file (*.txt) or a flat binary dump (bundleadjustment_b200/problem_io.py)
-        from bundleadjustment_b200 import problem_io as pio
+        pio = sys.modules.get("bundleadjustment_b200.problem_io") or _load_by_path("_ba_problem_io", "bundleadjustment_b200/problem_io.py")
         pb = (pio.read_bal(path) if path.endswith(".txt") else pio.read_binary(path))[0]
         log(f"[bench] problem {path}: cams={pb.shape[0]} landmarks={pb.shape[1]} obs={pb.shape[2]} (read in {time.time() - t:.1f}s)")
-        return None, pb
+        return pb
     sc = syn.config(name, scale=scale)
     pb = syn.flatten(sc)
     log(f"[bench] workload {name}: cams={pb.shape[0]} landmarks={pb.shape[1]} obs={pb.shape[2]} (generated in {time.time() - t:.1f}s, seed {sc.seed})")
-    return sc, pb
+    return pb
 
 
 class ClockSampler:
@@ -132,53 +167,103 @@ def measure_fp64_peak(device: int) -> float:
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+def hbm_peak():
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        if "hbm_gbs" in peaks:
+            return float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        pass
+    return 6650.0, "fallback 6650 GB/s (B200_PROFILING.md)"
+
+
+def committed_traffic(workload: str, solver: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the committed ncu --set full
+    capture named in profiles/traffic.json (full-size named workloads on one GPU only)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        e = t.get(f"{workload}/{solver}")
+        return (float(e["dram_bytes_per_launch"]), e["source"]) if e else (None, None)
+    except Exception:
+        return None, None
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # CPU arm: the C++ oracle ("port" of the reference's Ceres path; real Ceres is not in this image)
 # ---------------------------------------------------------------------------------------------------------------
-def run_cpu(pb, solver: str, lm_iters: int, threads: int):
-    """One bounded CPU sample: orc_solve with max_num_iterations = lm_iters.  Returns (lm_iterations, seconds)."""
+def run_cpu(pb, solver: str, lm_iters: int, threads: int, exploit_sparsity: bool = True):
+    """One CPU solve: orc_solve with max_num_iterations = lm_iters.  Returns (LM iterations, seconds, solution dict)."""
     from oracle import ba_oracle as orc
     orc.build()
-    kw = dict(max_num_iterations=lm_iters, num_threads=threads)
+    kw = dict(max_num_iterations=lm_iters, num_threads=threads, exploit_sparsity=int(exploit_sparsity))
     if solver == "pcg":
         kw.update(linear_solver=orc.ITERATIVE_SCHUR)
     opt = orc.default_options(**kw)
     t = time.perf_counter()
-    _, _, sm, its = orc.solve(pb, opt)
+    cam, pt, sm, its = orc.solve(pb, opt)
     dt = time.perf_counter() - t
-    return max(len(its) - 1, 1), dt, sm
+    sol = {"costs": [i["cost"] for i in its], "final_cost": sm.final_cost, "cam": cam, "pt": pt,
+           "radius": its[-1]["trust_region_radius"], "cg": [i["linear_solver_iterations"] for i in its]}
+    return max(len(its) - 1, 1), dt, sol
 
 
-def cpu_baseline(pb, workload: str, solver: str) -> dict:
+def cpu_baseline(pb, workload: str, solver: str, lm_iters: int):
+    """The bounded CPU sample of the default run (rank 0, N = 1): the SAME configuration as the GPU arm on all host threads
+    (sparsity-aware factorisation), plus -- dense Schur only -- a 4-thread run (the reference's num_threads = 4,
+    Optimizer.cpp:88) and a dense-factorisation run (what Ceres' DENSE_SCHUR does), each a few LM iterations."""
     threads = os.cpu_count() or 1
-    n_it, dt, _ = run_cpu(pb, solver, 1, threads)
-    return {"value": n_it / dt, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"1 LM iteration (iteration-0 evaluation + 1 step) of {workload}, {solver} Schur, oracle/ba_oracle.cpp "
-                      f"with OpenMP on {threads} threads: {dt:.2f} s"}
+    n_it, dt, sol = run_cpu(pb, solver, lm_iters, threads)
+    out = {"value": n_it / dt, "unit": UNIT, "cores": threads, "kind": "port", "same_config_as_gpu_arm": True,
+           "sample": f"one solve of {workload}, {solver} Schur, {n_it} LM iterations (iteration-0 evaluation included, as in the GPU "
+                     f"arm), oracle/ba_oracle.cpp with OpenMP on {threads} threads: {dt:.2f} s"}
+    if solver == "dense":
+        out["sample"] += "; factorisation skips the structurally zero part of S (bit-identical to the dense one)"
+        k = min(3, lm_iters)
+        n4, dt4, _ = run_cpu(pb, solver, k, min(4, threads))
+        out["value_4_threads"] = n4 / dt4
+        out["sample_4_threads"] = f"{n4} LM iterations on {min(4, threads)} threads (Optimizer.cpp:88 num_threads = 4): {dt4:.2f} s"
+        k = min(2, lm_iters)
+        nd, dtd, _ = run_cpu(pb, solver, k, threads, exploit_sparsity=False)
+        out["value_dense_factorisation"] = nd / dtd
+        out["sample_dense_factorisation"] = (f"{nd} LM iterations with S factorised as a dense {6 * pb.shape[0]}^2 matrix, as Ceres' "
+                                             f"DENSE_SCHUR would, {threads} threads: {dtd:.2f} s")
+    return out, sol
 
 
 def main_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    _, pb = load_workload(args.workload, args.scale, args.problem)
+    if args.workload == "K3":
+        return main_reference_k3(args)
+    pb = load_workload(args.workload, args.scale, args.problem)
     threads = os.cpu_count() or 1
-    for _ in range(min(args.warmup, 1)):           # one warm-up sample is enough to page the problem in
-        run_cpu(pb, args.solver, 1, threads)
+    n_it, dt, _ = run_cpu(pb, args.solver, args.lm_iters, threads)              # warm-up sample (pages the problem in) + estimate
+    lm_iters = args.lm_iters
+    budget = 240.0
+    if dt * args.steps > budget:                                                 # keep the whole run within a few minutes
+        lm_iters = max(1, int(args.lm_iters * budget / (dt * args.steps)))
     tot_it, tot_t = 0, 0.0
     for _ in range(args.steps):
-        n_it, dt, _ = run_cpu(pb, args.solver, 1, threads)
+        n_it, dt, _ = run_cpu(pb, args.solver, lm_iters, threads)
         tot_it += n_it; tot_t += dt
     value = tot_it / tot_t
+    cpu = {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+           "sample": f"{args.steps} solves of {args.workload} x {lm_iters} LM iterations each (sparsity-aware factorisation)"}
+    if args.solver == "dense":
+        nd, dtd, _ = run_cpu(pb, args.solver, min(2, lm_iters), threads, exploit_sparsity=False)
+        cpu["value_dense_factorisation"] = nd / dtd
+        cpu["sample_dense_factorisation"] = f"{nd} LM iterations with S factorised densely, as Ceres' DENSE_SCHUR would: {dtd:.2f} s"
     out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": tot_t / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "file" if args.problem else "synthetic",
         "config": {"workload": args.workload, "cams": int(pb.shape[0]), "landmarks": int(pb.shape[1]), "observations": int(pb.shape[2]),
-                   "linear_solver": args.solver, "lm_iters_per_step": 1,
-                   "note": "restated Ceres-path CPU baseline (oracle port), not Ceres itself; each step = 1 LM iteration sample"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{args.steps} x 1 LM iteration of {args.workload}"},
+                   "linear_solver": args.solver, "lm_iters_per_step": tot_it / args.steps, "max_num_iterations": lm_iters, "huber": True,
+                   "same_config_as_gpu_arm": lm_iters == args.lm_iters,
+                   "note": "restated Ceres-path CPU baseline (oracle port), not Ceres itself; each step = one solve of the same "
+                           "workload with the same max_num_iterations as the GPU arm"},
+        "cpu_baseline": cpu,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -196,73 +281,140 @@ def pinned_copy(a: np.ndarray) -> np.ndarray:
     return t.numpy()
 
 
-def main_ours(args):
-    import torch
-    import torch.distributed as dist
-    import bundleadjustment_b200 as bab
+class Dist:
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            import torch.distributed as dist
+            self.dist = dist
+            dist.init_process_group("nccl", device_id=torch.device(f"cuda:{self.local}"))
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        log(f"[bench] WORLD_SIZE={world} but --gpus {args.gpus}; using WORLD_SIZE")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    _, pb_full = load_workload(args.workload, args.scale, args.problem)
+    def allmax(self, x: float) -> float:
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=f"cuda:{self.local}")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather_rows(self, a: np.ndarray) -> np.ndarray:
+        """concatenate the ranks' row blocks (landmark shards) on every rank"""
+        if self.world == 1:
+            return a
+        parts = [None] * self.world
+        self.dist.all_gather_object(parts, np.ascontiguousarray(a))
+        return np.concatenate(parts, 0)
+
+    def new_solver(self, bab, opt, sharded=True):
+        s = bab.Solver(opt, device=self.local)
+        if sharded and self.world > 1:
+            uid = self.torch.zeros(128, dtype=self.torch.uint8, device=f"cuda:{self.local}")
+            if self.rank == 0:
+                uid.copy_(self.torch.frombuffer(bytearray(bab.capi.comm_unique_id()), dtype=self.torch.uint8))
+            self.dist.broadcast(uid, 0)
+            s.comm_init(self.world, self.rank, bytes(uid.cpu().numpy().tobytes()))
+        return s
+
+    def close(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def solution_of(solver, sm, D: Dist | None = None) -> dict:
+    its = solver.iterations()
+    pt = solver.points()
+    if D is not None:
+        pt = D.gather_rows(pt)
+    return {"costs": [i["cost"] for i in its], "final_cost": sm.final_cost, "cam": solver.cameras(), "pt": pt,
+            "radius": its[-1]["trust_region_radius"], "cg": [i["linear_solver_iterations"] for i in its]}
+
+
+def run_workload(D: Dist, bab, args, workload: str, solver_name: str, steps: int, warmup: int, steps_e2e: int, warmup_e2e: int,
+                 with_cpu: bool, full: bool):
+    """One workload at D.world ranks: parity gate, device-resident leg, end-to-end leg, rooflines.  `full`: the headline
+    workload (adds the materialised-evaluation metric, the dense-matrix Cholesky figure and the all-tiles-filled run)."""
+    torch = D.torch
+    world, rank, local = D.world, D.rank, D.local
+    pb_full = load_workload(workload, args.scale, args.problem if full else None)
     Nc, Np, No = pb_full.shape
     kw = dict(max_num_iterations=args.lm_iters)
-    if args.solver == "pcg":
+    if solver_name == "pcg":
         kw.update(linear_solver=bab.capi.ITERATIVE_SCHUR)
         if args.cg_tight:
-            kw.update(eta=1e-14, cg_r_tolerance=1e-10, max_linear_solver_iterations=2000)
+            kw.update(eta=1e-300, cg_r_tolerance=1e-10, max_linear_solver_iterations=2000)
     opt = bab.default_options(**kw)
-    solver = bab.Solver(opt, device=local)
+    cut = None
     if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{local}")
-        if rank == 0:
-            uid.copy_(torch.frombuffer(bytearray(bab.capi.comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(uid, 0)
-        solver.comm_init(world, rank, bytes(uid.cpu().numpy().tobytes()))
         pb_full = bab.sharding.landmark_major(pb_full)
-        cut = bab.sharding.partition(pb_full, world, quadratic=(args.solver == "dense"))
+        cut = bab.sharding.partition(pb_full, world, quadratic=(solver_name == "dense"))
         pb = bab.sharding.shard(pb_full, cut, rank)
     else:
         pb = pb_full
-    # page-locked host copies of everything that crosses PCIe in the e2e leg
-    import dataclasses
-    pb = dataclasses.replace(pb, **{f: pinned_copy(getattr(pb, f)) for f in ("cam", "cam_fixed", "fixed_extr", "K", "pt", "obs_cam", "obs_pt", "obs_uv")})
-    h2d = sum(getattr(pb, f).nbytes for f in ("cam", "cam_fixed", "fixed_extr", "K", "pt", "obs_cam", "obs_pt", "obs_uv"))
+    fields = ("cam", "cam_fixed", "fixed_extr", "K", "pt", "obs_cam", "obs_pt", "obs_uv")
+    pb = dataclasses.replace(pb, **{f: pinned_copy(getattr(pb, f)) for f in fields})      # page-locked: the e2e leg's H2D source
+    h2d = sum(getattr(pb, f).nbytes for f in fields)
     d2h = pb.cam.nbytes + pb.pt.nbytes
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def allmax(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
+    # ---- parity gate (before anything is timed) ----
+    parity = None
+    ref_sol = None
+    if world > 1:
+        if rank == 0:                                # the same problem on ONE GPU, no communicator
+            s1 = bab.Solver(opt, device=local)
+            s1.set_problem(pb_full)
+            ref_sol = solution_of(s1, s1.solve())
+            s1.close()
+            torch.cuda.empty_cache()
+        D.barrier()
+    solver = D.new_solver(bab, opt)
     solver.set_problem(pb)
-    solver.set_profiling(True)
+    sm0 = solver.solve()
+    got_sol = solution_of(solver, sm0, D)
+    cpu = None
+    if world > 1:
+        if rank == 0:
+            parity = bab.parity.compare(pb_full, got_sol, ref_sol)
+            parity["against"] = "single-GPU solve of the same problem (rank 0, no communicator)"
+    elif with_cpu:
+        cpu, cpu_sol = cpu_baseline(pb_full, workload, solver_name, args.lm_iters)       # the oracle as the CHECKER and the CPU baseline
+        if solver_name == "pcg" and got_sol["cg"] != cpu_sol["cg"]:
+            # Ceres' inexact rule stops on a threshold (zeta < eta): two correct implementations can stop one CG iteration apart,
+            # after which the trajectories are different inexact-Newton sequences.  Compare up to the first such LM iteration.
+            k = next(i for i, (a, b) in enumerate(zip(got_sol["cg"], cpu_sol["cg"])) if a != b)
+            parity = {"ok": bool(k >= 1 and all(abs(a - b) <= 1e-6 * abs(b) for a, b in zip(got_sol["costs"][:k], cpu_sol["costs"][:k]))
+                                 and abs(got_sol["cg"][k] - cpu_sol["cg"][k]) <= 1),
+                      "note": f"CG iteration counts differ at LM iteration {k} ({got_sol['cg'][k]} vs {cpu_sol['cg'][k]}: threshold rule); "
+                              f"cost trajectory compared up to there at 1e-6", "cg_gpu": got_sol["cg"], "cg_cpu": cpu_sol["cg"]}
+        else:
+            parity = bab.parity.compare(pb_full, got_sol, cpu_sol)
+        parity["against"] = "CPU baseline sample (oracle port, same configuration)"
+    if parity is not None and not parity["ok"]:
+        log(f"[bench] PARITY GATE FAILED for {workload}: {parity}")
+
     # ---- device-resident leg: inputs already in HBM, each step re-starts from the stored initial parameters ----
-    for _ in range(args.warmup):
+    solver.set_profiling(True)
+    for _ in range(warmup):
         solver.reset_parameters()
         solver.solve()
-    barrier()
+    D.barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    t_dev, t_lin, t_eval, t_chol, n_it, n_solves, launches, cg_its, n_dom = 0.0, 0.0, 0.0, 0.0, 0, 0, 0, 0, 0
+    t_dev, t_lin, t_eval, t_dom, n_it, n_solves, launches, n_dom = 0.0, 0.0, 0.0, 0.0, 0, 0, 0, 0
     wall0 = time.perf_counter()
     last = None
-    for _ in range(args.steps):
+    for _ in range(steps):
         solver.reset_parameters()
         sm = solver.solve()
         t_dev += sm.seconds_total; t_lin += sm.seconds_linear_solver; t_eval += sm.seconds_evaluate
@@ -270,81 +422,58 @@ def main_ours(args):
         n_solves += sm.num_iterations - (1 if sm.termination_type == bab.capi.NO_CONVERGENCE else 0)
         launches += solver.launch_count()
         kp = solver.kernel_profile()
-        t_chol += kp["seconds"]; n_dom += kp["launches"]
+        t_dom += kp["seconds"]; n_dom += kp["launches"]
         last = sm
-    barrier()
+    D.barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop() if rank == 0 else None
-    t_dev = allmax(t_dev)
+    t_dev = D.allmax(t_dev)
     its = solver.iterations()
-    cg_its = sum(i["linear_solver_iterations"] for i in its) * args.steps if args.solver == "pcg" else 0
+    cg_its = sum(i["linear_solver_iterations"] for i in its) * steps if solver_name == "pcg" else 0
     value = n_it / t_dev
     # ---- end-to-end leg: host buffers in, host results out, through the C ABI ----
     e2e_it, e2e_t = 0, 0.0
     cam_out, pt_out = pinned_copy(np.zeros_like(pb.cam)), pinned_copy(np.zeros_like(pb.pt))     # page-locked result buffers
-    barrier()
-    for s in range(args.warmup_e2e + args.steps_e2e):
-        barrier()
+    D.barrier()
+    for s in range(warmup_e2e + steps_e2e):
+        D.barrier()
         t0 = time.perf_counter()
         solver.set_problem(pb)
         sm = solver.solve()
         solver.cameras(cam_out); solver.points(pt_out)
         torch.cuda.synchronize()
-        dt = allmax(time.perf_counter() - t0)
-        if s >= args.warmup_e2e:
+        dt = D.allmax(time.perf_counter() - t0)
+        if s >= warmup_e2e:
             e2e_it += sm.num_iterations - 1; e2e_t += dt
     e2e_value = e2e_it / e2e_t if e2e_t > 0 else None
-    # ---- second metric: materialised residual + Jacobian evaluation (176 B / observation written) ----
-    solver.set_problem(pb)
-    solver.evaluate_device_ms(3)
-    ev_ms = allmax(solver.evaluate_device_ms(20))
-    obs_per_s = No / (ev_ms * 1e-3)
-    rs = solver.reduced_system_stats() if args.solver == "dense" else None
-    # symmetric shutdown on every rank BEFORE anything rank-specific: the handle's NCCL communicator is destroyed
-    # collectively, then the control-plane group
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    solver.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    if rank != 0:
-        return 0
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    eval_bytes = 176.0 * pb.shape[2] + 16.0 * pb.shape[2] + 48.0 * Nc + 24.0 * pb.shape[1]
-    roof_eval = {"bound": "hbm", "kernel": "evaluate_materialize_kernel", "achieved": eval_bytes / (ev_ms * 1e-3) / 1e9, "peak": hbm_peak,
-                 "unit": "GB/s", "frac": eval_bytes / (ev_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": hbm_src,
-                 "algorithmic_bytes_per_obs": 176 + 16}
+    hbm, hbm_src = hbm_peak()
+    res = {"value": value, "ms_per_step": t_dev / steps * 1e3, "steps": steps, "warmup": warmup, "lm_iters_per_step": n_it / steps,
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": steps_e2e,
+                   "note": "ba_set_problem (H2D of the raw problem + device-side index build) + ba_solve + ba_get_cameras/points (D2H) per "
+                           "step, wall clock, max over ranks"},
+           "gpu_launches": launches, "clocks": clocks, "parity": parity, "cpu_baseline": cpu, "wall_seconds_timed_region": wall,
+           "shape": {"cams": Nc, "landmarks": Np, "observations": No},
+           "termination": last.message.decode(), "final_cost": last.final_cost,
+           "stage_seconds_per_step": {"linearize": t_eval / steps, "linear_solve": t_lin / steps, "total": t_dev / steps}}
+    traffic, traffic_src = committed_traffic(workload, solver_name) if (world == 1 and args.scale == 1.0) else (None, None)
     extra = {}
-    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel, from the committed ncu --set full
-    # captures (profiles/): only valid for the full-size named workloads on one GPU
-    traffic = None
-    if world == 1 and args.scale == 1.0:
-        traffic = {("K4", "dense"): 65.548e6 + 19.983e6,        # profiles/r01_K4_cholesky_sparse_ncu_full_v9.txt
-                   ("K5", "pcg"): 5.075608e9 + 0.225956e9,      # profiles/r01_K5_lm_kernels_ncu_full_v12.txt (pcg_matvec_points_kernel)
-                   }.get((args.workload, args.solver))
-    if args.solver == "dense":
-        fp64_peak = measure_fp64_peak(local)
+    if solver_name == "dense":
+        rs = solver.reduced_system_stats()
+        fp64_peak = measure_fp64_peak(local) if rank == 0 else 1.0
         peak_src = ("FP64: torch.matmul f64 4096^3 measured in this run (MEASURED_PEAKS.json has no FP64 entry; the register-only "
                     "DMMA m8n8k4 peak measured by tools/dmma_bench.cu is 37.1 TFLOP/s)")
-        ach = n_solves * rs["flops"] / t_chol / 1e12 if t_chol > 0 else 0.0
-        roofline = {"bound": "tensor", "kernel": "chol_dataflow_kernel (tile-sparse left-looking Cholesky + both substitutions of the reduced camera "
-                                                 "system, one cooperative launch, DMMA m8n8k4)",
-                    "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": traffic, "peak_source": peak_src,
-                    "flops_per_launch": rs["flops"], "avg_launch_ms": t_chol / max(n_solves, 1) * 1e3, "share_of_step": t_chol / t_dev,
-                    "padded_order": rs["n"], "filled_tiles": rs["filled_tiles"], "lower_tiles": rs["lower_tiles"],
-                    "dense_equivalent_flops": cholesky_flops(rs["n"]),
-                    "note": "banded co-visibility: the factorisation skips structurally zero tiles and runs in nested-dissection order; what "
-                            "remains is a dependency chain of 128x128 potrf/trsm/update tasks (latency-bound, not flop-bound). "
-                            "roofline_dense_cholesky is the same kernel on a dense matrix of the same order."}
-        if not args.no_dense_chol:
+        ach = n_solves * rs["flops"] / t_dom / 1e12 if t_dom > 0 else 0.0
+        res["roofline"] = {"bound": "tensor", "kernel": "chol_dataflow_kernel (tile-sparse left-looking Cholesky + both substitutions of the "
+                                                        "reduced camera system, one cooperative launch, DMMA m8n8k4)",
+                           "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": traffic,
+                           "traffic_source": traffic_src, "peak_source": peak_src,
+                           "flops_per_launch": rs["flops"], "avg_launch_ms": t_dom / max(n_solves, 1) * 1e3, "share_of_step": t_dom / t_dev,
+                           "padded_order": rs["n"], "filled_tiles": rs["filled_tiles"], "lower_tiles": rs["lower_tiles"],
+                           "dense_equivalent_flops": cholesky_flops(rs["n"]),
+                           "note": "banded co-visibility: the factorisation skips structurally zero tiles and runs in nested-dissection order; "
+                                   "what remains is a dependency chain of 128x128 potrf/trsm/update tasks (latency-bound, not flop-bound). "
+                                   "roofline_dense_cholesky is the same kernel on a dense matrix of the same order."}
+        if full and world == 1 and not args.no_dense_chol:
             # the same kernel with every tile filled: dense random SPD matrix of the padded order through ba_dense_spd_solve
             n = rs["n"]
             rng = np.random.default_rng(0)
@@ -358,38 +487,232 @@ def main_ours(args):
                                                 "achieved": fl / (ms * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
                                                 "frac": fl / (ms * 1e-3) / 1e12 / fp64_peak, "traffic": None, "peak_source": peak_src,
                                                 "flops_per_launch": fl, "launch_ms": ms}
+            # the same WORKLOAD with every tile of S treated as filled (what a scene with loop closures everywhere, or Ceres'
+            # DENSE_SCHUR, pays): the honest companion of the headline, which exploits K4's 32-camera co-visibility window
+            sd = bab.Solver(opt, device=local)
+            sd.set_reduced_system_mode(dense_tiles=True)
+            sd.set_problem(pb)
+            sd.solve()
+            td, nd = 0.0, 0
+            for _ in range(2):
+                sd.reset_parameters()
+                smd = sd.solve()
+                td += smd.seconds_total; nd += smd.num_iterations - 1
+            sd.close()
+            torch.cuda.empty_cache()
+            extra["all_tiles_filled"] = {"value": nd / td, "unit": UNIT, "ms_per_step": td / 2 * 1e3,
+                                         "note": "same workload, ba_set_reduced_system_mode(dense_tiles=1): S factorised as a dense matrix"}
     else:
         # one pass over W per CG iteration (144 B/obs) + V'^-1 (48 B/landmark) + the camera-side vectors
         per_cg = 144.0 * pb.shape[2] + 48.0 * pb.shape[1] + 10 * 8.0 * 6 * Nc
         # per-launch duration from CUDA events around every matvec launch that did work (ba_get_kernel_profile)
-        ach = per_cg * n_dom / t_chol / 1e9 if t_chol > 0 else 0.0
-        roofline = {"bound": "hbm", "kernel": "pcg_matvec_points_kernel (one pass over W per CG iteration)", "achieved": ach,
-                    "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": traffic, "peak_source": hbm_src,
-                    "bytes_per_launch": per_cg, "avg_launch_ms": t_chol / max(n_dom, 1) * 1e3, "launches_timed": n_dom,
-                    "share_of_step": t_chol / t_dev, "cg_iterations_per_step": cg_its / args.steps,
-                    "linear_solve_stage_gbs": cg_its * per_cg / t_lin / 1e9 if t_lin > 0 else 0.0}
-    cpu = cpu_baseline(pb_full, args.workload, args.solver) if (world == 1 and not args.no_cpu) else None
+        ach = per_cg * n_dom / t_dom / 1e9 if t_dom > 0 else 0.0
+        res["roofline"] = {"bound": "hbm", "kernel": "pcg_matvec_points_kernel (one pass over W per CG iteration)", "achieved": ach,
+                           "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": traffic, "traffic_source": traffic_src,
+                           "peak_source": hbm_src, "bytes_per_launch": per_cg, "avg_launch_ms": t_dom / max(n_dom, 1) * 1e3,
+                           "launches_timed": n_dom, "share_of_step": t_dom / t_dev, "cg_iterations_per_step": cg_its / steps,
+                           "linear_solve_stage_gbs": cg_its * per_cg / t_lin / 1e9 if t_lin > 0 else 0.0,
+                           "timing": "CUDA events on the solver's stream around each matvec launch inside the timed solves (warm L2, "
+                                     "back to back); ncu's per-launch figure (profiles/) is cold-cache and serialised"}
+    if full:
+        # ---- second metric: materialised residual + Jacobian evaluation (176 B / observation) ----
+        solver.set_problem(pb)
+        solver.evaluate_device_ms(3)
+        ev_ms = D.allmax(solver.evaluate_device_ms(20))
+        eval_bytes = 176.0 * pb.shape[2] + 48.0 * Nc + 24.0 * pb.shape[1]
+        extra["roofline_eval"] = {"bound": "hbm", "kernel": "evaluate_materialize_kernel", "achieved": eval_bytes / (ev_ms * 1e-3) / 1e9, "peak": hbm,
+                                  "unit": "GB/s", "frac": eval_bytes / (ev_ms * 1e-3) / 1e9 / hbm, "traffic": None, "peak_source": hbm_src,
+                                  "algorithmic_bytes_per_obs": 176}
+        extra["obs_per_sec"] = No / (ev_ms * 1e-3)
+    # symmetric shutdown of this workload's handle on every rank (the NCCL communicator is destroyed collectively)
+    torch.cuda.synchronize()
+    D.barrier()
+    solver.close()
+    torch.cuda.empty_cache()
+    D.barrier()
+    res.update(extra)
+    return res
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# K3: frame-to-frame pose estimation (motion-only + structure refinement), BASELINE configs[2]
+# ---------------------------------------------------------------------------------------------------------------
+def k3_inputs():
+    """1 000 independent frames x 500 landmarks as per-keypoint arrays (what the tracker's frames hold), seed 3."""
+    syn = synthetic()
+    batch = syn.make_pose_batch(seed=3, n_prob=1000, n_pts=500)
+    rng = np.random.default_rng(7)
+    B, n = batch.cam.shape[0], int(batch.prob_ptr[-1])
+    # camera->world float32 poses of the initial guesses: the numpy twin of ba_cam_to_pose (synthetic.py has the rotation helpers)
+    R = syn._rodrigues(batch.cam[:, :3])
+    extr = np.tile(np.eye(4, dtype=np.float32), (B, 1, 1))
+    extr[:, :3, :3] = R.astype(np.float32); extr[:, :3, 3] = batch.cam[:, 3:].astype(np.float32)
+    pose = np.linalg.inv(extr).astype(np.float32)
+    xyz = np.ascontiguousarray(batch.Xh[:, :3], np.float32)
+    kp_frame = np.repeat(np.arange(B), np.diff(batch.prob_ptr))
+    d = np.linalg.norm(xyz - pose[kp_frame, :3, 3], axis=1)
+    return dict(pose=pose, K=batch.K, frame_ptr=batch.prob_ptr.astype(np.int32), kp_xy=batch.uv, kp_octave=rng.integers(0, 4, n).astype(np.int32),
+                pt_xyz=xyz, pt_min=(0.2 * d).astype(np.float32), pt_max=(3.0 * d).astype(np.float32), has_point=np.ones(n, np.uint8),
+                outlier=(rng.random(n) < 0.03).astype(np.uint8)), batch
+
+
+def run_k3(D: Dist, bab, args, steps: int, warmup: int, with_cpu: bool):
+    """SfMHelper::estimatePoseUsingBA at K3's shape (4 outer x <= 20 LM iterations + prune, SfMHelper.cpp:106-117) for 1 000
+    frames in one call, then the keyframe BA that follows a keyframe decision (BundleAdjustment.cpp:204-205: 1 outer x <= 10
+    LM iterations) on a K1-shaped map.  `value` = LM iterations of all problems / device time of the call (pose problems are
+    independent: the path does not shard, rank 0 runs it)."""
+    torch = D.torch
+    kin, batch = k3_inputs()
+    kin = {k: pinned_copy(v) for k, v in kin.items()}
+    B = kin["pose"].shape[0]
+    n_obs = int(kin["frame_ptr"][-1])
+    opt = bab.default_options(max_num_iterations=20)
+    pose_out, out_out = pinned_copy(np.zeros((B, 16), np.float32)), pinned_copy(np.zeros(n_obs, np.uint8))
+    call = lambda: bab.capi.solve_pose_only_outer(kin["pose"], kin["K"], kin["frame_ptr"], kin["kp_xy"], kin["kp_octave"], kin["pt_xyz"],
+                                                  kin["pt_min"], kin["pt_max"], kin["has_point"], kin["outlier"], n_outer=4, options=opt,
+                                                  device=D.local, pose_out=pose_out, outlier_out=out_out)
+    for _ in range(warmup):
+        call()
+    pose, outl, sms, ms, lm_total = call()
+    t_dev, t_e2e = 0.0, 0.0
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        _, _, _, ms, _ = call()
+        t_e2e += time.perf_counter() - t0
+        t_dev += ms * 1e-3
+    launches = bab.capi.workspace_launch_count(D.local) * steps
+    hbm, hbm_src = hbm_peak()
+    # pose_batch_kernel reads 16 B (Xh) + 8 B (uv) + 1 B (mask) per observation per pass over the problem: one pass per linearisation
+    # and one per candidate evaluation; everything is L2-resident (12 MB), so the bound is latency / FP64 issue, not HBM
+    h2d = sum(kin[k].nbytes for k in kin)
+    res = {"value": lm_total / (t_dev / steps), "unit": UNIT, "ms_per_step": t_dev / steps * 1e3, "steps": steps,
+           "problems": B, "observations": n_obs, "lm_iterations_per_step": lm_total, "frames_per_sec": B / (t_dev / steps),
+           "e2e": {"value": lm_total / (t_e2e / steps), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(pose_out.nbytes + out_out.nbytes),
+                   "frames_per_sec": B / (t_e2e / steps)},
+           "gpu_launches": launches, "outliers_after": int(outl.sum()),
+           "workload": "K3: 1000 frames x 500 landmarks, 4 outer x <= 20 LM iterations + prune, one ba_solve_pose_only_outer call"}
+    # structure refinement: the keyframe BA that follows (1 outer x <= 10 LM iterations on a K1-shaped map)
+    pb = load_workload("K1")
+    s = bab.Solver(bab.default_options(max_num_iterations=10), device=D.local)
+    s.set_problem(pb)
+    s.solve()
+    td, nd = 0.0, 0
+    for _ in range(steps):
+        s.reset_parameters()
+        sm = s.solve()
+        td += sm.seconds_total; nd += sm.num_iterations - 1
+    t0 = time.perf_counter()
+    s.set_problem(pb); sm = s.solve(); s.cameras(); s.points()
+    te = time.perf_counter() - t0
+    s.close()
+    res["keyframe_ba"] = {"value": nd / td, "unit": UNIT, "ms_per_step": td / steps * 1e3, "e2e_ms": te * 1e3,
+                          "workload": "K1 (30 cameras / 10 k landmarks / ~60 k observations), 1 outer x <= 10 LM iterations"}
+    if with_cpu:
+        from oracle import ba_oracle as orc
+        orc.build()
+        threads = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        _, osms, oit = orc.solve_pose_only_batch(dataclasses.replace(batch, cam=np.stack([bab.capi.pose_to_cam(kin["pose"][b].reshape(4, 4))[0] for b in range(B)])),
+                                                 orc.default_options(max_num_iterations=20, num_threads=threads),
+                                                 mask=(kin["has_point"] & (1 - kin["outlier"])).astype(np.uint8))
+        dt = time.perf_counter() - t0
+        n = sum(len(x) - 1 for x in oit)
+        res["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": f"first outer pass only (1000 problems, {n} LM iterations), oracle port on {threads} threads: {dt:.2f} s"}
+    return res
+
+
+def main_reference_k3(args):
+    syn = synthetic()
+    from oracle import ba_oracle as orc
+    orc.build()
+    batch = syn.make_pose_batch(seed=3, n_prob=1000, n_pts=500)
+    threads = os.cpu_count() or 1
+    opt = orc.default_options(max_num_iterations=20, num_threads=threads)
+    orc.solve_pose_only_batch(batch, opt)
+    tot_it, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        _, _, oit = orc.solve_pose_only_batch(batch, opt)
+        tot_t += time.perf_counter() - t0
+        tot_it += sum(len(x) - 1 for x in oit)
+    value = tot_it / tot_t
+    emit({"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+          "ms_per_step": tot_t / args.steps * 1e3, "higher_is_better": True, "scaling": "replicas only", "vs_baseline": None, "dtype": "f64",
+          "data": "synthetic", "config": {"workload": "K3", "problems": 1000, "note": "one pass of <= 20 LM iterations per problem (oracle port)"},
+          "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": f"{args.steps} x 1000 pose problems"},
+          "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
+    return 0
+
+
+def compact(r: dict) -> dict:
+    """the short form of a workload result that rides at the end of the JSON line"""
+    out = {"value": r["value"], "unit": UNIT, "ms_per_step": r["ms_per_step"], "steps": r["steps"], "lm_iters_per_step": r["lm_iters_per_step"],
+           "e2e": r["e2e"]["value"], "h2d_bytes_per_step": r["e2e"]["h2d_bytes_per_step"], "d2h_bytes_per_step": r["e2e"]["d2h_bytes_per_step"],
+           "roofline_frac": r["roofline"]["frac"], "roofline_kernel_ms": r["roofline"]["avg_launch_ms"], "roofline_share_of_step": r["roofline"]["share_of_step"],
+           "cg_iterations_per_step": r["roofline"].get("cg_iterations_per_step"), "gpu_launches": r["gpu_launches"],
+           "parity": ({k: r["parity"][k] for k in ("ok", "max_cost_rel_diff", "final_cost_rel_diff", "max_cam_diff", "max_pt_diff", "pt_outside_cond_bound", "against", "note")
+                       if k in r["parity"]} if r["parity"] else None),
+           "cpu_baseline": ({k: r["cpu_baseline"][k] for k in ("value", "cores", "kind", "sample")} if r.get("cpu_baseline") else None),
+           "shape": r["shape"], "final_cost": r["final_cost"]}
+    return out
+
+
+def main_ours(args):
+    import bundleadjustment_b200 as bab
+    D = Dist()
+    if D.world != args.gpus:
+        log(f"[bench] WORLD_SIZE={D.world} but --gpus {args.gpus}; using WORLD_SIZE")
+    with_cpu = D.world == 1 and not args.no_cpu
+    if args.workload == "K3":
+        r = run_k3(D, bab, args, args.steps, args.warmup, with_cpu) if D.rank == 0 else None
+        D.barrier(); D.close()
+        if D.rank == 0:
+            emit({"metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": D.world, "steps": args.steps, "warmup": args.warmup,
+                  "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "replicas only", "vs_baseline": None, "dtype": "f64",
+                  "data": "synthetic", "config": {"workload": r["workload"]}, "e2e": r["e2e"], "gpu_launches": r["gpu_launches"],
+                  "cpu_baseline": r.get("cpu_baseline"), "k3": r})
+        return 0
+    head = run_workload(D, bab, args, args.workload, args.solver, args.steps, args.warmup, args.steps_e2e, args.warmup_e2e, with_cpu, full=True)
+    k3 = None
+    if not args.no_k3 and not args.problem and D.rank == 0:
+        try:
+            k3 = run_k3(D, bab, args, max(5, args.steps), 3, with_cpu)
+        except Exception as e:                                   # the headline line must survive a failure of a side leg
+            k3 = {"error": repr(e)}
+    D.barrier()
+    k5 = None
+    if not args.no_k5 and not args.problem and not (args.workload == "K5"):
+        try:
+            k5 = compact(run_workload(D, bab, args, "K5", "pcg", max(5, min(args.steps, 10)), 3, 2, 1, with_cpu, full=False))
+        except Exception as e:
+            k5 = {"error": repr(e)}
+    D.close()
+    if D.rank != 0:
+        return 0
+    world = D.world
+    sh = head["shape"]
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "file" if args.problem else "synthetic",
-        "config": {"workload": args.workload if args.scale == 1.0 else f"{args.workload} x{args.scale}", "cams": Nc, "landmarks": Np, "observations": No, "linear_solver": args.solver,
-                   "lm_iters_per_step": n_it / args.steps, "max_num_iterations": args.lm_iters, "huber": True,
+        "config": {"workload": args.workload if args.scale == 1.0 else f"{args.workload} x{args.scale}", "cams": sh["cams"], "landmarks": sh["landmarks"],
+                   "observations": sh["observations"], "linear_solver": args.solver,
+                   "lm_iters_per_step": head["lm_iters_per_step"], "max_num_iterations": args.lm_iters, "huber": True,
                    "parallelism": f"landmark-sharded x{world}" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (W + S >> 126 MB); no flush needed" if args.workload in ("K4", "K5") else "small problem: L2-resident by nature",
-                   "termination": last.message.decode(), "final_cost": last.final_cost, "seed": {"K1": 1, "K2": 2, "K4": 4, "K5": 5}.get(args.workload)},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "steps": args.steps_e2e, "note": "ba_set_problem (H2D of the raw problem + device-side index build) + ba_solve + ba_get_cameras/points (D2H) per step, wall clock, max over ranks"},
-        "gpu_launches": launches,
-        "clocks": clocks,
-        "roofline": roofline,
-        "roofline_eval": roof_eval,
-        **extra,
-        "obs_per_sec": obs_per_s,
-        "stage_seconds_per_step": {"linearize": t_eval / args.steps, "linear_solve": t_lin / args.steps, "total": t_dev / args.steps},
-        "wall_seconds_timed_region": wall,
-        "cpu_baseline": cpu,
+                   "termination": head["termination"], "final_cost": head["final_cost"], "seed": {"K1": 1, "K2": 2, "K4": 4, "K5": 5}.get(args.workload)},
+        "e2e": head["e2e"], "gpu_launches": head["gpu_launches"], "clocks": head["clocks"], "parity": head["parity"],
+        "roofline": head["roofline"],
     }
+    for k in ("roofline_eval", "roofline_dense_cholesky", "all_tiles_filled", "obs_per_sec"):
+        if k in head:
+            out[k] = head[k]
+    out["stage_seconds_per_step"] = head["stage_seconds_per_step"]
+    out["wall_seconds_timed_region"] = head["wall_seconds_timed_region"]
+    out["cpu_baseline"] = head["cpu_baseline"]
+    out["k3"] = k3
+    out["k5"] = k5                      # LAST key: survives tail truncation of the line
     emit(out)
     return 0
 
@@ -400,17 +723,21 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="K4", choices=["K1", "K2", "K4", "K5"])
+    ap.add_argument("--workload", default="K4", choices=["K1", "K2", "K3", "K4", "K5"])
     ap.add_argument("--problem", default=None, help="read the problem from a BAL text file (*.txt) or a flat binary dump instead of generating --workload")
-    ap.add_argument("--solver", default="dense", choices=["dense", "pcg"])
+    ap.add_argument("--solver", default=None, choices=["dense", "pcg"])
     ap.add_argument("--lm-iters", type=int, default=10)
     ap.add_argument("--cg-tight", action="store_true", help="PCG run to |r| <= 1e-10 |b| (exact-step trajectory)")
     ap.add_argument("--steps-e2e", type=int, default=3)
     ap.add_argument("--warmup-e2e", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-k5", action="store_true", help="skip the K5 (PCG, 30 M observations) leg appended as the last key")
+    ap.add_argument("--no-k3", action="store_true", help="skip the K3 (pose batch) leg")
     ap.add_argument("--no-dense-chol", action="store_true", help="skip the dense-matrix run of the Cholesky kernel (roofline_dense_cholesky)")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (profiling runs only; recorded in config)")
     args = ap.parse_args()
+    if args.solver is None:
+        args.solver = "pcg" if args.workload == "K5" else "dense"
     if args.problem:
         args.workload = "file:" + os.path.basename(args.problem)
     if args.impl == "reference":

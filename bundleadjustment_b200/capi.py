@@ -259,7 +259,8 @@ def prune_frames(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max, h
 
 def solve_pose_only_outer(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max, has_point, outlier, n_outer=4,
                           options: Options | None = None, device: int = 0, pose_out=None, outlier_out=None):
-    """ba_solve_pose_only_outer: returns (pose [F,4,4] f32, outlier u8, summaries of the last outer iteration, device ms).
+    """ba_solve_pose_only_outer: returns (pose [F,4,4] f32, outlier u8, summaries of the last outer iteration, device ms,
+    LM iterations of all frames and outer iterations).
     pose_out / outlier_out (optional): caller-owned (e.g. page-locked) result buffers."""
     F = int(np.asarray(frame_ptr).shape[0]) - 1
     P = np.ascontiguousarray(pose, np.float32).reshape(F, 16)
@@ -277,10 +278,11 @@ def solve_pose_only_outer(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, 
             np.ascontiguousarray(pt_max, np.float32), np.ascontiguousarray(has_point, np.uint8)]
     sms = (Summary * max(F, 1))()
     ms = C.c_float(0)
+    lm = C.c_int64(0)
     opt = options or default_options(max_num_iterations=20)
     _check(lib.ba_solve_pose_only_outer(C.byref(opt), int(device), F, _ptr(pose_out), *[_ptr(a) for a in args], _ptr(outlier_out),
-                                        int(n_outer), sms, C.byref(ms)), "ba_solve_pose_only_outer")
-    return pose_out.reshape(F, 4, 4), outlier_out, list(sms)[:F], float(ms.value)
+                                        int(n_outer), sms, C.byref(ms), C.byref(lm)), "ba_solve_pose_only_outer")
+    return pose_out.reshape(F, 4, 4), outlier_out, list(sms)[:F], float(ms.value), int(lm.value)
 
 
 def workspace_launch_count(device: int = 0) -> int:

@@ -1201,12 +1201,13 @@ extern "C" int ba_solve_pose_only_outer(const ba_options *opt_in, int device, in
                                         const int32_t *frame_ptr, const float *kp_xy, const int32_t *kp_octave,
                                         const float *pt_xyz, const float *pt_min_dist, const float *pt_max_dist,
                                         const uint8_t *has_point, uint8_t *outlier, int32_t n_outer, ba_summary *summaries,
-                                        float *device_ms) {
+                                        float *device_ms, int64_t *lm_iterations) {
     if (n_frames < 0 || n_outer < 0 || (n_frames && (!pose || !K || !frame_ptr))) return fail(BA_ERR_INVALID, "bad arguments");
     Workspace *w;
     int rc = workspace(device, &w);
     if (rc) return rc;
     if (device_ms) *device_ms = 0.f;
+    if (lm_iterations) *lm_iterations = 0;
     if (n_frames == 0) return BA_OK;
     const int F = n_frames, n_kp = frame_ptr[F];
     for (int f = 0; f < F; ++f)
@@ -1217,7 +1218,7 @@ extern "C" int ba_solve_pose_only_outer(const ba_options *opt_in, int device, in
     cudaStream_t s = w->stream;
     if ((rc = upload_keypoints(w, F, pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min_dist, pt_max_dist, has_point, outlier))) return rc;
     CU(w->cam.alloc(48 * (size_t)F));
-    CU(w->sum.alloc(sizeof(ba_summary) * (size_t)F));
+    CU(w->sum.alloc(sizeof(ba_summary) * (size_t)F * std::max(n_outer, 1)));      // one slice per outer iteration
     CU(w->mask.alloc(std::max<size_t>(n_kp, 1)));
     CU(w->Xh.alloc(16 * std::max<size_t>(n_kp, 1)));
     CU(cudaEventRecord(w->e1, s));
@@ -1226,7 +1227,7 @@ extern "C" int ba_solve_pose_only_outer(const ba_options *opt_in, int device, in
         launch_pose_to_cam(F, w->pose.as<float>(), w->cam.as<double>(), s);
         launch_pose_mask(n_kp, w->has.as<uint8_t>(), w->out.as<uint8_t>(), w->mask.as<uint8_t>(), w->xyz.as<float>(), it == 0 ? w->Xh.as<float4>() : nullptr, s);
         launch_pose_batch(opt, F, w->cam.as<double>(), w->K.as<float>(), w->ptr.as<int>(), w->Xh.as<float4>(), w->xy.as<float2>(),
-                          w->mask.as<uint8_t>(), w->sum.as<ba_summary>(), nullptr, 0, s);
+                          w->mask.as<uint8_t>(), w->sum.as<ba_summary>() + (size_t)it * F, nullptr, 0, s);
         launch_cam_to_pose(F, w->cam.as<double>(), w->pose.as<float>(), w->extr.as<float>(), s);
         launch_prune(F, w->pose.as<float>(), w->extr.as<float>(), w->K.as<float>(), w->ptr.as<int>(), w->xy.as<float2>(), w->oct.as<int>(),
                      w->xyz.as<float>(), w->mn.as<float>(), w->mx.as<float>(), w->has.as<uint8_t>(), w->out.as<uint8_t>(), 1, n_kp, s);
@@ -1235,16 +1236,18 @@ extern "C" int ba_solve_pose_only_outer(const ba_options *opt_in, int device, in
     CU(cudaEventRecord(w->e2, s));
     CU(cudaMemcpyAsync(pose, w->pose.p, 64 * (size_t)F, cudaMemcpyDeviceToHost, s));
     if (n_kp) CU(cudaMemcpyAsync(outlier, w->out.p, (size_t)n_kp, cudaMemcpyDeviceToHost, s));
-    std::vector<ba_summary> sm(summaries && n_outer ? F : 0);
-    if (!sm.empty()) CU(cudaMemcpyAsync(sm.data(), w->sum.p, sizeof(ba_summary) * (size_t)F, cudaMemcpyDeviceToHost, s));
+    std::vector<ba_summary> sm((summaries || lm_iterations) ? (size_t)F * n_outer : 0);
+    if (!sm.empty()) CU(cudaMemcpyAsync(sm.data(), w->sum.p, sizeof(ba_summary) * sm.size(), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
     float ms = 0;
     cudaEventElapsedTime(&ms, w->e1, w->e2);
     if (device_ms) *device_ms = ms;
-    for (size_t b = 0; b < sm.size(); ++b) {
+    if (lm_iterations)
+        for (const ba_summary &x : sm) *lm_iterations += std::max(x.num_iterations - 1, 0);
+    for (size_t b = 0; summaries && n_outer && b < (size_t)F; ++b) {
         ba_summary &o = summaries[b];
-        o = sm[b];
+        o = sm[(size_t)(n_outer - 1) * F + b];
         const int msg = (int)(unsigned char)o.message[0];
         std::snprintf(o.message, sizeof(o.message), "%s", message_text(msg));
         o.seconds_total = ms * 1e-3;         // whole batch, all outer iterations

@@ -290,7 +290,7 @@ void MotionOnlyBAOptimizerAngles::optimizeCameraPoses(const std::vector<std::sha
         std::vector<uint8_t> before(out);
         std::vector<ba_summary> sms(B);
         if (fail(ba_solve_pose_only_outer(&opt, m_device, B, pose.data(), K.data(), ptr.data(), xy.data(), octave.data(), xyz.data(),
-                                          mn.data(), mx.data(), has.data(), out.data(), (int32_t)m_nIterations, sms.data(), nullptr)))
+                                          mn.data(), mx.data(), has.data(), out.data(), (int32_t)m_nIterations, sms.data(), nullptr, nullptr)))
             return;
         if (m_nIterations > 0) {
             m_lastTermination = sms[0].termination_type;

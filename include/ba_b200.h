@@ -159,12 +159,13 @@ int ba_prune_frames(int device, int32_t n_frames, const float *pose /*16F*/, con
  * replacement per frame, the float32 write-back (:448-453) and pruneCorrespondences(frame, considerOutlier = true) (:455)
  * run as five kernel launches; nothing crosses PCIe between outer iterations.  Keypoint arrays as in ba_prune_frames
  * (pt_xyz = the keypoint's map point position, float32, constant).  pose and outlier are updated in place.
- * summaries (may be NULL): the LAST outer iteration's ba_summary per frame.  device_ms (may be NULL): device time. */
+ * summaries (may be NULL): the LAST outer iteration's ba_summary per frame.  device_ms (may be NULL): device time of the
+ * whole loop.  lm_iterations (may be NULL): LM iterations of all frames and all outer iterations (iteration 0 excluded). */
 int ba_solve_pose_only_outer(const ba_options *opt, int device, int32_t n_frames, float *pose /*16F in/out*/,
                              const float *K /*9F*/, const int32_t *frame_ptr, const float *kp_xy,
                              const int32_t *kp_octave, const float *pt_xyz, const float *pt_min_dist,
                              const float *pt_max_dist, const uint8_t *has_point, uint8_t *outlier /*in/out*/,
-                             int32_t n_outer, ba_summary *summaries, float *device_ms);
+                             int32_t n_outer, ba_summary *summaries, float *device_ms, int64_t *lm_iterations);
 
 /* The handle-less entry points (ba_solve_pose_only_batch, ba_prune_frames, ba_solve_pose_only_outer) keep one stream, two
  * events and grow-only device buffers per calling thread and device, so that the per-frame calls of the tracker never

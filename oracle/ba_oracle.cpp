@@ -318,7 +318,11 @@ int potrf_unblocked(int n0, int nb, double *A, int n) {
     return 0;
 }
 
-int cholesky_inplace(int n, double *A, int num_threads) {
+// last (may be nullptr = dense): last[j] = index of the last row of column j of L that can be nonzero (monotone
+// non-decreasing, >= j: the column envelope after symbolic elimination).  Rows below the panel's envelope are exact zeros
+// before and after the panel's TRSM / SYRK, so skipping them changes no bit of the result.  orc_options.exploit_sparsity
+// selects it: the CPU baseline is then given the same structural-zero skipping the CUDA path's tile plan has.
+int cholesky_inplace(int n, double *A, int num_threads, const int *last = nullptr) {
     const int NB = 64;
     (void)num_threads;
     for (int k0 = 0; k0 < n; k0 += NB) {
@@ -326,10 +330,12 @@ int cholesky_inplace(int n, double *A, int num_threads) {
         if (potrf_unblocked(k0, nb, A, n)) return 1;
         const int r0 = k0 + nb;
         if (r0 >= n) break;
-        // TRSM: rows r0..n of columns k0..k0+nb:  L21 = A21 * L11^{-T}
+        const int nr = last ? std::min(n, last[k0 + nb - 1] + 1) : n;    // rows [r0, nr) of the panel can be nonzero
+        if (r0 >= nr) continue;
+        // TRSM: rows r0..nr of columns k0..k0+nb:  L21 = A21 * L11^{-T}
 #pragma omp parallel for schedule(static) num_threads(num_threads)
-        for (int ib = r0; ib < n; ib += 256) {
-            const int ie = std::min(n, ib + 256);
+        for (int ib = r0; ib < nr; ib += 256) {
+            const int ie = std::min(nr, ib + 256);
             for (int j = k0; j < k0 + nb; ++j) {
                 const double inv = 1.0 / CM(j, j);
                 for (int k = k0; k < j; ++k) {
@@ -345,11 +351,11 @@ int cholesky_inplace(int n, double *A, int num_threads) {
         // SYRK: A22 -= L21 L21^T (lower part), column tiles in parallel
         const int TJ = 32;
 #pragma omp parallel for schedule(dynamic, 1) num_threads(num_threads)
-        for (int jb = r0; jb < n; jb += TJ) {
-            const int je = std::min(n, jb + TJ);
+        for (int jb = r0; jb < nr; jb += TJ) {
+            const int je = std::min(nr, jb + TJ);
             for (int j = jb; j < je; ++j) {
-                double *dst = &CM(j, j); // rows j..n of column j
-                const int len = n - j;
+                double *dst = &CM(j, j); // rows j..nr of column j
+                const int len = nr - j;
                 int k = k0;
                 for (; k + 4 <= k0 + nb; k += 4) {
                     const double l0 = CM(j, k), l1 = CM(j, k + 1), l2 = CM(j, k + 2), l3 = CM(j, k + 3);
@@ -367,19 +373,21 @@ int cholesky_inplace(int n, double *A, int num_threads) {
     return 0;
 }
 
-void cholesky_solve_inplace(int n, const double *A, double *b) {
+void cholesky_solve_inplace(int n, const double *A, double *b, const int *last = nullptr) {
     // L y = b
     for (int j = 0; j < n; ++j) {
         const double y = b[j] / CM(j, j);
         b[j] = y;
         const double *col = &CM(j, j);
-        for (int i = 1; i < n - j; ++i) b[j + i] -= col[i] * y;
+        const int len = (last ? last[j] + 1 : n) - j;
+        for (int i = 1; i < len; ++i) b[j + i] -= col[i] * y;
     }
     // L^T x = y
     for (int j = n - 1; j >= 0; --j) {
         const double *col = &CM(j, j);
         double v = b[j];
-        for (int i = 1; i < n - j; ++i) v -= col[i] * b[j + i];
+        const int len = (last ? last[j] + 1 : n) - j;
+        for (int i = 1; i < len; ++i) v -= col[i] * b[j + i];
         b[j] = v / col[0];
     }
 }
@@ -1096,12 +1104,59 @@ struct BAModel : Model {
         return 0;
     }
 
+    // column envelope of the reduced camera matrix in slot order (row-major upper == column-major lower): row 6 sc + a
+    // reaches column 6 * (largest slot sharing a landmark with sc) + 5, then the monotone closure that covers all fill
+    std::vector<int> env_last;
+    std::vector<double> S_env;
+    void envelope_init(int n) {
+        if ((int)env_last.size() == n) return;
+        std::vector<int> far(n_cam_active);
+        for (int s = 0; s < n_cam_active; ++s) far[s] = s;
+        for (int p = 0; p < Np; ++p) {
+            int lo = 1 << 30, hi = -1;
+            for (int e = pt_ptr[p]; e < pt_ptr[p + 1]; ++e) {
+                const int sc = cam_slot[obs_cam[pt_obs[e]]];
+                if (sc >= 0) { lo = std::min(lo, sc); hi = std::max(hi, sc); }
+            }
+            if (hi >= 0) far[lo] = std::max(far[lo], hi);       // every camera of the track reaches hi; lo's row is the longest
+            for (int e = pt_ptr[p]; e < pt_ptr[p + 1]; ++e) {
+                const int sc = cam_slot[obs_cam[pt_obs[e]]];
+                if (sc >= 0) far[sc] = std::max(far[sc], hi);
+            }
+        }
+        env_last.assign(n, 0);
+        int run = 0;
+        for (int s = 0; s < n_cam_active; ++s) {
+            run = std::max(run, 6 * far[s] + 5);
+            for (int a = 0; a < 6; ++a) env_last[6 * s + a] = run;
+        }
+        S_env.assign((size_t)n * n, 0.0);
+    }
+
     int solve(const double *D, double *y, int *lin_iters) override {
         const int n = 6 * n_cam_active;
         std::vector<double> yc(std::max(n, 1), 0.0);
         *lin_iters = 0;
         if (n > 0) {
-            if (o.linear_solver == ORC_DENSE_SCHUR) {
+            if (o.linear_solver == ORC_DENSE_SCHUR && o.exploit_sparsity) {
+                // Same arithmetic as the dense branch below on the entries that can be nonzero: the column envelope of S
+                // (from camera co-visibility, closed under elimination) bounds every row range, S lives in a persistent
+                // buffer of which only the envelope is cleared.  Bit-identical results (the skipped terms are exact zeros).
+                envelope_init(n);
+                std::vector<double> rhs(n, 0.0);
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+                for (int j = 0; j < n; ++j) std::memset(&S_env[(size_t)j * n + j], 0, sizeof(double) * (size_t)(env_last[j] + 1 - j));
+                schur_build(D, 0, Np, true, S_env.data(), rhs.data());
+                *lin_iters = 1;
+                int bad = 0;
+#pragma omp parallel for schedule(static) reduction(| : bad) num_threads(nthreads)
+                for (int j = 0; j < n; ++j)
+                    for (int i = j; i <= env_last[j]; ++i) bad |= std::isnan(S_env[(size_t)j * n + i]) ? 1 : 0;
+                if (bad) return 1;
+                if (cholesky_inplace(n, S_env.data(), nthreads, env_last.data())) return 1;
+                cholesky_solve_inplace(n, S_env.data(), rhs.data(), env_last.data());
+                yc = rhs;
+            } else if (o.linear_solver == ORC_DENSE_SCHUR) {
                 std::vector<double> S((size_t)n * n, 0.0), rhs(n, 0.0);
                 schur_build(D, 0, Np, true, S.data(), rhs.data());
                 *lin_iters = 1;

@@ -44,7 +44,8 @@ typedef struct orc_options {
     int32_t max_num_consecutive_invalid_steps; /* 5 */
     int32_t max_linear_solver_iterations;      /* 500 (CG) */
     int32_t use_huber;                 /* 1: HuberLoss(sqrt(5.991)), Optimizer.cpp:312 */
-    int32_t pad0;
+    int32_t exploit_sparsity;          /* 0 = factorise S densely, as Ceres' DENSE_SCHUR does; 1 = skip the structurally zero
+                                          part of S (column envelope): same bits, the sparsity the CUDA tile plan exploits */
     double function_tolerance;         /* 1e-6 */
     double gradient_tolerance;         /* 1e-10 */
     double parameter_tolerance;        /* 1e-8 */

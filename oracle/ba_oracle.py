@@ -21,7 +21,7 @@ class Options(C.Structure):
     _fields_ = [
         ("max_num_iterations", C.c_int32), ("num_threads", C.c_int32), ("linear_solver", C.c_int32),
         ("jacobi_scaling", C.c_int32), ("max_num_consecutive_invalid_steps", C.c_int32),
-        ("max_linear_solver_iterations", C.c_int32), ("use_huber", C.c_int32), ("pad0", C.c_int32),
+        ("max_linear_solver_iterations", C.c_int32), ("use_huber", C.c_int32), ("exploit_sparsity", C.c_int32),
         ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
         ("parameter_tolerance", C.c_double), ("initial_trust_region_radius", C.c_double),
         ("max_trust_region_radius", C.c_double), ("min_trust_region_radius", C.c_double),

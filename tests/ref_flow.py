@@ -163,10 +163,10 @@ def keypoint_arrays(g: Graph):
 def run_pose_outer(bab, g: Graph, n_outer=4, max_it=20) -> Graph:
     """the device-resident outer loop (ba_solve_pose_only_outer) on the same graph"""
     xyz, mn, mx, has = keypoint_arrays(g)
-    pose, out, sms, ms = bab.capi.solve_pose_only_outer(g.pose, g.K.reshape(-1, 9), g.kp_ptr, g.kp_xy, g.kp_octave, xyz, mn, mx, has,
+    pose, out, sms, ms, lm = bab.capi.solve_pose_only_outer(g.pose, g.K.reshape(-1, 9), g.kp_ptr, g.kp_xy, g.kp_octave, xyz, mn, mx, has,
                                                         g.kp_outlier, n_outer=n_outer, options=bab.default_options(max_num_iterations=max_it))
     res = dataclasses.replace(g, pose=pose.copy(), kp_outlier=out.copy())
-    res.sms, res.device_ms = sms, ms
+    res.sms, res.device_ms, res.lm_iterations = sms, ms, lm
     return res
 
 

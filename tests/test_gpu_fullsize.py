@@ -6,11 +6,22 @@ Landmarks are the one place where 1e-6 ABSOLUTE is not always attainable in floa
 cameras has a nearly singular 3x3 block V_p + D_p^2, and the two sides add the same terms in different orders.  The bound
 used here is stated instead of waived: every landmark must satisfy
 
-    |x_gpu - x_oracle|  <=  1e-6  +  C_COND * eps * cond(V_p') * |x_final - x_initial|        (C_COND below)
+    |x_gpu - x_oracle|  <=  1e-6 * max(1, |x_oracle|)  +  C_COND * eps * cond(V_p') * |x_final - x_initial|     (C_COND below)
 
 where V_p' = V_p + D_p^2 is the oracle's own damped block at the last linearisation and |x_final - x_initial| is the distance
-the landmark travelled (the quantity the accumulated relative errors of the back-substitution multiply).  A landmark that
-violates it is a bug, not conditioning; the test prints the worst offenders with their condition numbers."""
+the landmark travelled (the quantity the accumulated relative errors of the back-substitution multiply).  The first term is
+north_star's 1e-6, relative for coordinates above 1 m: K4's 1 % gross-outlier tracks send a few 3-view landmarks tens of
+kilometres away (depth unobservable), where 1e-6 absolute would be 3e-11 relative -- below what any two summation orders
+can agree on.  A landmark that violates the bound is a bug, not conditioning; the test prints the worst offenders with
+their condition numbers, and how many landmarks needed the conditioning term at all.
+
+PCG with Ceres' inexact rule (eta = 0.1) stops on a THRESHOLD test (zeta < eta); two correct implementations that differ in
+the last bits can stop one CG iteration apart, after which the two LM trajectories are different inexact-Newton sequences.
+The comparison is therefore made three ways: (a) PCG driven to |r| <= 1e-13 |b| against the DENSE oracle (exact steps, full
+tolerances); (b) PCG with a FIXED number of CG iterations per LM iteration (eta tiny, max_linear_solver_iterations = 25: no
+threshold decisions, steps as inexact as Ceres') against the oracle's PCG under the same setting, full tolerances;
+(c) Ceres' own rule against the oracle's PCG: CG iteration counts may differ by at most one, the trajectories must agree to
+1e-6 up to the first LM iteration where they do, and to 1e-3 afterwards."""
 import dataclasses
 import time
 
@@ -59,15 +70,17 @@ def check_landmarks(orc, pb, pt, opt_, ocam, radius, label, use_huber=1):
         return
     cond = landmark_condition(orc, pb, ocam, opt_, radius, use_huber)
     travel = np.linalg.norm(opt_ - pb.pt, axis=1)
-    bound = 1e-6 + C_COND * EPS * cond * travel
+    rel = 1e-6 * np.maximum(1.0, np.abs(opt_).max(axis=1))
+    bound = rel + C_COND * EPS * cond * travel
     bad = over[diff[over] > bound[over]]
+    print(f"   {int((diff[over] > rel[over]).sum())} landmarks need the conditioning term (|x| up to {np.abs(opt_[over]).max():.3e})")
     for p in over[np.argsort(-diff[over])][:8]:
         print(f"   landmark {p}: diff {diff[p]:.3e} cond {cond[p]:.3e} travel {travel[p]:.3e} bound {bound[p]:.3e} "
               f"track {int((pb.obs_pt == p).sum())}")
-    assert bad.size == 0, f"{bad.size} landmarks exceed 1e-6 + {C_COND} eps cond travel; worst {diff[bad].max():.3e}"
+    assert bad.size == 0, f"{bad.size} landmarks exceed 1e-6 max(1,|x|) + {C_COND} eps cond travel; worst {diff[bad].max():.3e}"
 
 
-def _solve_both(bab, orc, pb, max_it, label, threads=None, **kw):
+def _solve_both(bab, orc, pb, max_it, label, threads=None, oracle_kw=None, **kw):
     opt = bab.default_options(max_num_iterations=max_it, **kw)
     s = bab.Solver(opt)
     s.set_problem(pb)
@@ -75,7 +88,7 @@ def _solve_both(bab, orc, pb, max_it, label, threads=None, **kw):
     its, cam, pt = s.iterations(), s.cameras(), s.points()
     s.close()
     t = time.time()
-    okw = dict(kw)
+    okw = dict(kw, **(oracle_kw or {}))
     if threads:
         okw["num_threads"] = threads
     ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(max_num_iterations=max_it, **okw))
@@ -95,26 +108,63 @@ def _full_check(orc, pb, g, o, label):
     check_landmarks(orc, pb, pt, opt_, ocam, oits[-1]["trust_region_radius"], label)
 
 
+FIXED_CG = dict(linear_solver=1, eta=1e-300, max_linear_solver_iterations=25)      # (b): exactly 25 CG iterations per LM iteration
+
+
+def _pcg_checks(bab, orc, pb, max_it, label):
+    """(b) and (c) of the module docstring."""
+    import os
+    g, o = _solve_both(bab, orc, pb, max_it, label + " fixed-CG", threads=os.cpu_count(), **FIXED_CG)
+    assert [i["linear_solver_iterations"] for i in g[1]] == [i["linear_solver_iterations"] for i in o[1]]
+    _full_check(orc, pb, g, o, label + " fixed-CG")
+    g, o = _solve_both(bab, orc, pb, max_it, label + " ceres-rule", threads=os.cpu_count(), linear_solver=1)
+    (sm, its, cam, pt), (osm, oits, ocam, opt_) = g, o
+    assert len(its) == len(oits)
+    na, nb = [i["linear_solver_iterations"] for i in its], [i["linear_solver_iterations"] for i in oits]
+    print(f"[{label} ceres-rule] CG iterations gpu {na} oracle {nb}")
+    split = next((k for k, (a, b) in enumerate(zip(na, nb)) if a != b), len(its))
+    for k, (a, b) in enumerate(zip(its, oits)):
+        assert abs(na[k] - nb[k]) <= 1 or k > split, (k, na, nb)
+        assert a["step_is_successful"] == b["step_is_successful"]
+        tol = 1e-6 if k <= split - 1 or split == len(its) else 1e-3
+        if k == split:
+            tol = 1e-3                      # the step computed with one CG iteration more / fewer
+        assert abs(a["cost"] - b["cost"]) <= tol * abs(b["cost"]), (k, split, a, b)
+    if split == len(its):
+        assert abs(sm.final_cost - osm.final_cost) <= 1e-8 * osm.final_cost
+        assert np.abs(cam - ocam).max() <= 1e-6
+        check_landmarks(orc, pb, pt, opt_, ocam, oits[-1]["trust_region_radius"], label + " ceres-rule")
+
+
 def test_k4_full_size_vs_oracle(bab, orc):
     """BASELINE configs[3] exactly as bench.py runs it: 1 700 cameras / 500 k landmarks / ~2 M observations, dense Schur,
     Huber, 10 LM iterations.  The oracle factorises the 10 200^2 reduced system densely (about 3 s per iteration)."""
     import os
     pb = syn.flatten(syn.config("K4"))
-    g, o = _solve_both(bab, orc, pb, 10, "K4", threads=os.cpu_count())
+    g, o = _solve_both(bab, orc, pb, 10, "K4", threads=os.cpu_count(), oracle_kw=dict(exploit_sparsity=1))
     _full_check(orc, pb, g, o, "K4")
 
 
 def test_k4_full_size_pcg_vs_oracle_pcg(bab, orc):
-    """K4 with Ceres' ITERATIVE_SCHUR rule (eta = 0.1) against the oracle's own PCG: same CG iteration counts, same
-    trajectory; and the tight PCG against the dense oracle with the stated landmark bound."""
+    """K4 through the Schur-Jacobi PCG against the oracle's own PCG: fixed CG iteration count (full tolerances) and Ceres'
+    rule (counts within one); the tight PCG against the dense oracle is test_k4_full_size_tight_pcg_vs_dense_oracle."""
+    pb = syn.flatten(syn.config("K4"))
+    _pcg_checks(bab, orc, pb, 6, "K4/pcg")
+
+
+def test_k4_full_size_tight_pcg_vs_dense_oracle(bab, orc):
+    """(a): K4, PCG run to |r| <= 1e-13 |b|, against the DENSE oracle at the full tolerances (replaces round 1's 5e-4)."""
     import os
     pb = syn.flatten(syn.config("K4"))
-    g, o = _solve_both(bab, orc, pb, 6, "K4/pcg", threads=os.cpu_count(), linear_solver=1)
-    _traj_check(g[1], o[1])
-    assert [i["linear_solver_iterations"] for i in g[1]] == [i["linear_solver_iterations"] for i in o[1]]
-    assert abs(g[0].final_cost - o[0].final_cost) <= 1e-8 * o[0].final_cost
-    assert np.abs(g[2] - o[2]).max() <= 1e-6
-    check_landmarks(orc, pb, g[3], o[3], o[2], o[1][-1]["trust_region_radius"], "K4/pcg")
+    tight = dict(linear_solver=1, eta=1e-300, cg_r_tolerance=1e-13, max_linear_solver_iterations=5000)
+    s = bab.Solver(bab.default_options(max_num_iterations=10, **tight))
+    s.set_problem(pb)
+    sm = s.solve()
+    its, cam, pt = s.iterations(), s.cameras(), s.points()
+    print("[K4 tight PCG] CG iterations", [i["linear_solver_iterations"] for i in its])
+    s.close()
+    ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(max_num_iterations=10, num_threads=os.cpu_count(), exploit_sparsity=1))
+    _full_check(orc, pb, (sm, its, cam, pt), (osm, oits, ocam, opt_), "K4 tight PCG vs dense oracle")
 
 
 def test_k2_full_size_vs_oracle(bab, orc):
@@ -164,35 +214,24 @@ def test_k5_tenth_dense_oracle_vs_tight_pcg_and_pcg_vs_pcg(bab, orc):
     equal CG iteration counts."""
     import os
     pb = syn.flatten(syn.config("K5", scale=0.1))
-    tight = dict(linear_solver=1, eta=1e-14, cg_r_tolerance=1e-13, max_linear_solver_iterations=5000)
+    tight = dict(linear_solver=1, eta=1e-300, cg_r_tolerance=1e-13, max_linear_solver_iterations=5000)
     s = bab.Solver(bab.default_options(max_num_iterations=5, **tight))
     s.set_problem(pb)
     sm = s.solve()
     its, cam, pt = s.iterations(), s.cameras(), s.points()
     s.close()
     t = time.time()
-    ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(max_num_iterations=5, num_threads=os.cpu_count()))
+    ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(max_num_iterations=5, num_threads=os.cpu_count(), exploit_sparsity=1))
     print(f"[K5x0.1] dense oracle: 5 LM iterations in {time.time() - t:.1f}s")
     _full_check(orc, pb, (sm, its, cam, pt), (osm, oits, ocam, opt_), "K5x0.1 tight PCG vs dense oracle")
-    g, o = _solve_both(bab, orc, pb, 5, "K5x0.1 pcg", threads=os.cpu_count(), linear_solver=1)
-    _traj_check(g[1], o[1])
-    assert [i["linear_solver_iterations"] for i in g[1]] == [i["linear_solver_iterations"] for i in o[1]]
-    assert abs(g[0].final_cost - o[0].final_cost) <= 1e-8 * o[0].final_cost
-    assert np.abs(g[2] - o[2]).max() <= 1e-6
-    check_landmarks(orc, pb, g[3], o[3], o[2], o[1][-1]["trust_region_radius"], "K5x0.1 pcg")
+    _pcg_checks(bab, orc, pb, 5, "K5x0.1 pcg")
 
 
 def test_k5_full_size_pcg_vs_oracle_pcg(bab, orc):
     """BASELINE configs[4] at full size (13 k cameras / 4.5 M landmarks / 30 M observations), Schur-Jacobi PCG with Ceres'
     rule, 2 LM iterations against the oracle's PCG (host memory: about 12 GB)."""
-    import os
     pb = syn.flatten(syn.config("K5"))
-    g, o = _solve_both(bab, orc, pb, 2, "K5", threads=os.cpu_count(), linear_solver=1)
-    _traj_check(g[1], o[1])
-    assert [i["linear_solver_iterations"] for i in g[1]] == [i["linear_solver_iterations"] for i in o[1]]
-    assert abs(g[0].final_cost - o[0].final_cost) <= 1e-8 * o[0].final_cost
-    assert np.abs(g[2] - o[2]).max() <= 1e-6
-    check_landmarks(orc, pb, g[3], o[3], o[2], o[1][-1]["trust_region_radius"], "K5")
+    _pcg_checks(bab, orc, pb, 2, "K5")
 
 
 def test_all_cameras_fixed_and_fixed_only_block(bab, orc):
