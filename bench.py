@@ -352,7 +352,7 @@ def run_workload(D: Dist, bab, args, workload: str, solver_name: str, steps: int
     if solver_name == "pcg":
         kw.update(linear_solver=bab.capi.ITERATIVE_SCHUR)
         if args.cg_tight:
-            kw.update(eta=1e-300, cg_r_tolerance=1e-10, max_linear_solver_iterations=2000)
+            kw.update(eta=-1.0, cg_r_tolerance=1e-10, max_linear_solver_iterations=2000)
     opt = bab.default_options(**kw)
     cut = None
     if world > 1:

@@ -97,16 +97,14 @@ struct ba_handle {
     bool pairs_built = false;
     bool natural_tile_order = false, dense_tiles = false;   // ba_set_reduced_system_mode (explicit API, never the environment)
     CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
-    bool S_dirty = true;             // S may hold values outside the plan's tiles (new buffer / new plan): clear all of it once
-    DevBuf tile_map, cam_row, row_src, yperm, nz_tiles, s_packed;
-    int n_nz_tiles = 0;
+    DevBuf tile_map, cam_row, row_src, yperm;
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
     DevBuf cm_obs, blk_first_pt, blk_info, pm_camk, pm_trk;
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
     DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
-    DevBuf part, cost_part, red_part, red_count, sums, maxs, camsums, state, iters, invL, U_loc, bc_loc, sums_loc, maxs_loc;
+    DevBuf part, cost_part, red_part, red_count, lin_red, lin_loc, camsums, state, iters, invL;   // lin_*: [U | b_c | sums | max slots], one all-reduce
     DevBuf cg_r, cg_p, cg_z, cg_q, cg_x, Minv, tp, cg_part, cg_qp;
     DevBuf ev_res, ev_jc, ev_jp;     // materialised evaluation outputs
     int *host_flags = nullptr;       // mapped pinned
@@ -115,6 +113,7 @@ struct ba_handle {
     ncclComm_t comm = nullptr;
     int n_ranks = 1, rank = 0;
     std::vector<int> cam_obs_count;  // global per-camera observation counts
+    size_t lin_count = 0;            // doubles in the packed linearisation message
     int launches = 0;                // kernels/collectives enqueued by the last solve (bench bookkeeping)
     bool profile = false;            // record CUDA events around every linear solve / linearisation
     std::vector<cudaEvent_t> prof_ev;   // [4 per body]: lin begin, lin end (= solve begin), solve end, body end
@@ -135,10 +134,10 @@ struct ba_handle {
     void free_problem() {
         DevBuf *all[] = {&cam0, &cam1, &pt0, &pt1, &cam_init, &pt_init, &cam_kind, &cam_K, &cam_extr, &pm_uv, &pm_cam, &pm_pt,
                          &pt_ptr, &cm_uv, &cm_pt, &chunk_cam, &chunk_beg, &chunk_end, &cam_chunk_ptr, &tab_x, &tab_c, &scale_cam,
-                         &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &red_part, &red_count, &sums, &maxs,
-                         &camsums, &state, &iters, &invL, &U_loc, &bc_loc, &sums_loc, &maxs_loc, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
+                         &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &red_part, &red_count, &lin_red, &lin_loc,
+                         &camsums, &state, &iters, &invL, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &tile_map, &cam_row, &row_src, &yperm, &nz_tiles, &s_packed};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &tile_map, &cam_row, &row_src, &yperm};
         for (DevBuf *b : all) b->free();
         chol_plan_destroy(&chol_plan);
         scr.release(); scr2.release();
@@ -262,16 +261,8 @@ int ensure_dense(ba_handle *h) {
     // padded reduced system: one 128-row Cholesky tile per group of CAMS_PER_TILE consecutive cameras
     const int G = (h->ctx.Nc + CAMS_PER_TILE - 1) / CAMS_PER_TILE;
     const int n = G * CHOL_NB;
-    const size_t need = sizeof(double) * chol_matrix_doubles(n);
-    if (h->S.bytes < need) {
-        CU(h->S.alloc(need));
-        CU(h->invL.alloc(sizeof(double) * chol_work_doubles(n)));
-        CU(h->yperm.alloc(sizeof(double) * (size_t)n));
-    }
-    h->ctx.S = h->S.as<double>();
     h->ctx.ldS = n;
-    h->ctx.cam_row = h->cam_row.as<int>();
-    h->ctx.row_src = h->row_src.as<int>();
+    h->ctx.S_T = G;
     if (!h->pairs_built) {
         // camera-pair-major index for the deterministic Schur reduction (device-side, once per problem)
         cudaStream_t s = h->stream;
@@ -317,28 +308,28 @@ int ensure_dense(ba_handle *h) {
         }
         if ((rc = upload(h->cam_row, cam_row.data(), cam_row.size(), s))) return rc;
         if ((rc = upload(h->row_src, row_src.data(), row_src.size(), s))) return rc;
-        h->ctx.cam_row = h->cam_row.as<int>();
-        h->ctx.row_src = h->row_src.as<int>();
         std::vector<unsigned char> nz((size_t)G * G, 0);
         for (int gi = 0; gi < G; ++gi)
             for (int gj = 0; gj <= gi; ++gj)
                 if (gi == gj || adj[(size_t)gi * G + gj]) nz[(size_t)std::max(pos[gi], pos[gj]) * G + std::min(pos[gi], pos[gj])] = 1;
-        if (h->comm) {
-            std::vector<int2> tl;
-            for (int i = 0; i < G; ++i)
-                for (int j = 0; j <= i; ++j) if (nz[(size_t)i * G + j]) tl.push_back(make_int2(i, j));
-            h->n_nz_tiles = (int)tl.size();
-            if ((rc = upload(h->nz_tiles, tl.data(), tl.size(), s))) return rc;
-            CU(h->s_packed.alloc(sizeof(double) * CHOL_NB * CHOL_NB * std::max<size_t>(tl.size(), 1)));
-            CU(cudaStreamSynchronize(s));
-        }
         CU(cudaStreamSynchronize(s));                                    // the uploads read the host vectors above
-        // ba_set_reduced_system_mode(dense_tiles): treat every tile as filled (what Ceres' DENSE_SCHUR does)
-        if ((rc = chol_plan_create(n, h->dense_tiles ? nullptr : nz.data(), &h->chol_plan, s)))
+        // ba_set_reduced_system_mode(dense_tiles): treat every tile as filled (what Ceres' DENSE_SCHUR does).  The plan also fixes
+        // the STORAGE of S: [tiles a camera pair can touch | reduced rhs (6 Nc, camera order) | fill-in tiles | rhs tiles].
+        if ((rc = chol_plan_create(n, h->dense_tiles ? nullptr : nz.data(), &h->chol_plan, s, (size_t)h->ctx.n)))
             return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
-        h->S_dirty = true;
+        CU(h->S.alloc(sizeof(double) * (size_t)h->chol_plan.total_doubles));
+        CU(h->invL.alloc(sizeof(double) * chol_work_doubles(n)));
+        CU(cudaMemsetAsync(h->invL.p, 0, sizeof(double) * chol_work_doubles(n), s));    // the kernel only ever writes the lower triangles of L_jj^-1
+        CU(h->yperm.alloc(sizeof(double) * (size_t)n));
         h->pairs_built = true;
     }
+    h->ctx.S = h->S.as<double>();
+    h->ctx.S_toff = h->chol_plan.tile_off;
+    h->ctx.cam_row = h->cam_row.as<int>();
+    h->ctx.row_src = h->row_src.as<int>();
+    // the reduced right-hand side lives inside the S buffer, right behind the tiles the Schur kernels write: a sharded solve
+    // all-reduces [S tiles | rhs] as ONE message out of the buffer the kernels wrote (no pack / unpack pass)
+    h->ctx.rhs = h->ctx.S + h->chol_plan.front_doubles;
     return BA_OK;
 }
 
@@ -372,7 +363,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     AL(perm_dev, 4 * (size_t)No); AL(cnt_cam, 4 * (size_t)Nc); AL(cnt_cam_global, 4 * (size_t)Nc); AL(cam_kind, 4 * (size_t)Nc);
     AL(cam_ptr, 4 * (size_t)(Nc + 1)); AL(cam_chunk_ptr, 4 * (size_t)(Nc + 1)); AL(cm_uv, 8 * (size_t)No); AL(cm_pt, 4 * (size_t)No);
     AL(cm_obs, 4 * (size_t)No); AL(blk_first_pt, 4 * ((size_t)No / TILE_WIN + 2)); AL(blk_info, 16 * ((size_t)No / TILE_WIN + 2)); AL(pm_camk, 4 * (size_t)No); AL(pm_trk, 4 * (size_t)No);
-    AL(chunk_cam, 4 * max_chunks); AL(chunk_beg, 4 * max_chunks); AL(chunk_end, 4 * max_chunks); AL(prep_flags, 16);
+    AL(chunk_cam, 4 * max_chunks); AL(chunk_beg, 4 * max_chunks); AL(chunk_end, 4 * max_chunks); AL(prep_flags, 32);
     PrepIn &pin = h->prep_in;
     PrepOut &po = h->prep_out;
     pin.Nc = Nc; pin.Np = Np; pin.No = No;
@@ -386,6 +377,15 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     po.chunk_cam = h->chunk_cam.as<int>(); po.chunk_beg = h->chunk_beg.as<int>(); po.chunk_end = h->chunk_end.as<int>();
     po.flags = h->prep_flags.as<int>(); po.h_flags = h->h_prep;
     rc = prep_observations(pin, po, h->scr, s);
+    if (h->comm) {
+        // a rank that rejects its shard must not leave its peers blocked in the first data collective: agree on the verdict first
+        int bad = rc != 0 ? 1 : 0, *flag = h->prep_flags.as<int>() + 7;
+        CU(cudaMemcpyAsync(flag, &bad, 4, cudaMemcpyHostToDevice, s));
+        NC(ncclAllReduce(flag, flag, 1, ncclInt, ncclMax, h->comm, s));
+        CU(cudaMemcpyAsync(&bad, flag, 4, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        if (bad && rc == 0) return fail(BA_ERR_INVALID, "another rank rejected its shard of the problem (see that rank's error)");
+    }
     if (rc < 0) {
         const int i = -rc - 1;
         return fail(BA_ERR_INVALID, "observation %d references camera %d / landmark %d out of range", i, obs_cam[i], obs_pt[i]);
@@ -428,12 +428,20 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
 #undef UP
     AL(tab_x, sizeof(CamEntry) * (size_t)Nc); AL(tab_c, sizeof(CamProj) * (size_t)Nc);
     AL(scale_cam, 8 * 6 * (size_t)Nc); AL(scale_pt, 8 * 3 * (size_t)Np);
-    AL(U, 8 * 36 * (size_t)Nc); AL(bc, 8 * 6 * (size_t)Nc); AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
+    AL(V, 8 * 6 * (size_t)Np); AL(bp, 8 * 3 * (size_t)Np);
     AL(W, 8 * 18 * (size_t)No + 64);     /* + slack: rows are fetched as aligned 32-byte windows (load_row18) */ AL(cam_part, 8 * 27 * (size_t)std::max(ctx.n_chunks, 1));
     AL(Vinv, 8 * 6 * (size_t)Np + 64); AL(wv, 8 * 3 * (size_t)Np);
     AL(rhs, 8 * (size_t)ctx.n); AL(yc, 8 * (size_t)ctx.n + 64);      /* + slack: 6-double rows are gathered as 32-byte windows */
     AL(part, 8 * 4 * (size_t)ctx.n_part); AL(cost_part, 8 * (size_t)((No + 31) / 32 + 8));
-    AL(sums, 8 * SUM_COUNT); AL(maxs, 8 * MAX_COUNT); AL(camsums, 8 * CS_COUNT);
+    AL(camsums, 8 * CS_COUNT);
+    // One contiguous message per linearisation: [U (36 Nc) | b_c (6 Nc) | sums (SUM_COUNT) | max slots (one per rank)].  A sharded
+    // solve all-reduces (sum) the rank's lin_loc into lin_red in ONE call; the max over ranks of the gradient norm rides along
+    // exactly: rank r writes its value into slot r (zeros elsewhere), the sum hands every rank all of them.
+    const size_t lin_count = 42 * (size_t)Nc + SUM_COUNT + (size_t)std::max(h->n_ranks, 1);
+    AL(lin_red, 8 * lin_count);
+    CU(cudaMemsetAsync(h->lin_red.p, 0, 8 * lin_count, s));
+    if (h->comm) { AL(lin_loc, 8 * lin_count); CU(cudaMemsetAsync(h->lin_loc.p, 0, 8 * lin_count, s)); }
+    h->lin_count = lin_count;
     AL(red_part, 8 * 4 * (size_t)RED_MAX_GRID * RED_SLOTS); AL(red_count, 4 * RED_SLOTS);
     CU(cudaMemsetAsync(h->red_count.p, 0, 4 * RED_SLOTS, s));
     AL(state, sizeof(LMState)); AL(iters, sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2));
@@ -451,30 +459,25 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.cm_obs = h->cm_obs.as<int>(); ctx.blk_first_pt = h->blk_first_pt.as<int>(); ctx.blk_info = h->blk_info.as<int4>(); ctx.pm_camk = h->pm_camk.as<unsigned>(); ctx.pm_trk = h->pm_trk.as<unsigned>();
     ctx.tab_x = h->tab_x.as<CamEntry>(); ctx.tab_c = h->tab_c.as<CamProj>();
     ctx.scale_cam = h->scale_cam.as<double>(); ctx.scale_pt = h->scale_pt.as<double>();
-    ctx.U = h->U.as<double>(); ctx.bc = h->bc.as<double>(); ctx.V = h->V.as<double>(); ctx.bp = h->bp.as<double>();
+    {
+        double *red = h->lin_red.as<double>(), *loc = h->comm ? h->lin_loc.as<double>() : red;
+        ctx.U = red; ctx.bc = red + 36 * (size_t)Nc; ctx.sums = red + 42 * (size_t)Nc; ctx.maxs = ctx.sums + SUM_COUNT;
+        ctx.U_loc = loc; ctx.bc_loc = loc + 36 * (size_t)Nc; ctx.sums_loc = loc + 42 * (size_t)Nc;
+        ctx.maxs_loc = ctx.sums_loc + SUM_COUNT + (h->comm ? h->rank : 0);
+    }
+    ctx.V = h->V.as<double>(); ctx.bp = h->bp.as<double>();
     ctx.W = h->W.as<double>(); ctx.cam_part = h->cam_part.as<double>(); ctx.Vinv = h->Vinv.as<double>(); ctx.wv = h->wv.as<double>();
     ctx.rhs = h->rhs.as<double>(); ctx.yc = h->yc.as<double>();
-    ctx.part = h->part.as<double>(); ctx.sums = h->sums.as<double>(); ctx.maxs = h->maxs.as<double>(); ctx.camsums = h->camsums.as<double>();
+    ctx.part = h->part.as<double>(); ctx.camsums = h->camsums.as<double>();
     ctx.red_part = h->red_part.as<double>(); ctx.red_count = h->red_count.as<unsigned>();
     ctx.cg_r = h->cg_r.as<double>(); ctx.cg_p = h->cg_p.as<double>(); ctx.cg_z = h->cg_z.as<double>(); ctx.cg_q = h->cg_q.as<double>();
     ctx.cg_x = h->cg_x.as<double>(); ctx.Minv = h->Minv.as<double>(); ctx.tp = h->tp.as<double>(); ctx.cg_part = h->cg_part.as<double>(); ctx.cg_qp = h->cg_qp.as<double>();
     ctx.state = h->state.as<LMState>(); ctx.iters = h->iters.as<ba_iteration>();
     ctx.host_flags = h->host_flags_dev;
-    if (h->comm) {
-        AL(U_loc, 8 * 36 * (size_t)Nc); AL(bc_loc, 8 * 6 * (size_t)Nc);
-        AL(sums_loc, 8 * SUM_COUNT); AL(maxs_loc, 8 * MAX_COUNT);
-        CU(cudaMemsetAsync(h->sums_loc.p, 0, 8 * SUM_COUNT, s)); CU(cudaMemsetAsync(h->maxs_loc.p, 0, 8 * MAX_COUNT, s));
-        ctx.U_loc = h->U_loc.as<double>(); ctx.bc_loc = h->bc_loc.as<double>();
-        ctx.sums_loc = h->sums_loc.as<double>(); ctx.maxs_loc = h->maxs_loc.as<double>();
-    } else {
-        ctx.U_loc = ctx.U; ctx.bc_loc = ctx.bc; ctx.sums_loc = ctx.sums; ctx.maxs_loc = ctx.maxs;
-    }
 #undef AL
     if ((rc = tiles_init(ctx)))
         return fail(rc == (int)cudaErrorInvalidConfiguration ? BA_ERR_INVALID : BA_ERR_CUDA,
                     "a landmark block of %d observations does not fit in shared memory (longest supported track: about 1000 observations)", ctx.tile_cap);
-    CU(cudaMemsetAsync(h->sums.p, 0, 8 * SUM_COUNT, s));
-    CU(cudaMemsetAsync(h->maxs.p, 0, 8 * MAX_COUNT, s));
     CU(cudaMemsetAsync(h->camsums.p, 0, 8 * CS_COUNT, s));
     launch_init_state(ctx, s);
     launch_fill(ctx.scale_cam, 6 * (size_t)Nc, 1.0, s);
@@ -525,23 +528,12 @@ int allreduce_sum(ba_handle *h, const double *src, double *dst, size_t count) {
     return BA_OK;
 }
 int allreduce_sum(ba_handle *h, double *buf, size_t count) { return allreduce_sum(h, buf, buf, count); }
-int allreduce_max(ba_handle *h, const double *src, double *dst, size_t count) {
-    if (!h->comm) return BA_OK;
-    NC(ncclAllReduce(src, dst, count, ncclDouble, ncclMax, h->comm, h->stream));
-    h->launches++;
-    return BA_OK;
-}
 
-// sum of the ranks' contributions to S: pack the tiles a camera pair can touch, one all-reduce, unpack
+// sum of the ranks' contributions to the reduced system: ONE all-reduce over [tiles a camera pair can touch | rhs], in place,
+// straight out of the buffer the Schur kernels wrote
 int allreduce_S(ba_handle *h) {
     if (!h->comm) return BA_OK;
-    Ctx &ctx = h->ctx;
-    launch_tiles_copy(ctx.S, ctx.ldS, h->nz_tiles.as<int2>(), h->n_nz_tiles, h->s_packed.as<double>(), 0, h->stream);
-    int rc = allreduce_sum(h, h->s_packed.as<double>(), (size_t)h->n_nz_tiles * CHOL_NB * CHOL_NB);
-    if (rc) return rc;
-    launch_tiles_copy(ctx.S, ctx.ldS, h->nz_tiles.as<int2>(), h->n_nz_tiles, h->s_packed.as<double>(), 1, h->stream);
-    h->launches += 2;
-    return BA_OK;
+    return allreduce_sum(h, h->ctx.S, (size_t)(h->chol_plan.front_doubles + h->ctx.n));
 }
 
 // one linearisation at x: local blocks, then the replicated camera blocks are summed over ranks
@@ -550,11 +542,9 @@ int enqueue_linearize(ba_handle *h, int force) {
     launch_linearize_local(ctx, force, h->stream);
     h->launches += 5;
     int rc;
-    // out-of-place so that a body that does not re-linearise reproduces the same reduced blocks
-    if ((rc = allreduce_sum(h, ctx.U_loc, ctx.U, 36 * (size_t)ctx.Nc))) return rc;
-    if ((rc = allreduce_sum(h, ctx.bc_loc, ctx.bc, 6 * (size_t)ctx.Nc))) return rc;
-    if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_LIN_BEGIN, ctx.sums + SUM_LIN_BEGIN, SUM_LIN_N))) return rc;
-    if ((rc = allreduce_max(h, ctx.maxs_loc, ctx.maxs, MAX_COUNT))) return rc;
+    // ONE message [U | b_c | sums | max slots]; out-of-place so that a body that does not re-linearise reproduces the same
+    // reduced blocks (the step slots of `sums` ride along and are overwritten by the step all-reduce before anyone reads them)
+    if ((rc = allreduce_sum(h, h->lin_loc.as<double>(), h->lin_red.as<double>(), h->lin_count))) return rc;
     launch_cam_norms(ctx, force, h->stream);
     h->launches += 1;
     return BA_OK;
@@ -568,15 +558,10 @@ int enqueue_linear_solve(ba_handle *h) {
     launch_point_invert(ctx, -1.0, s);
     h->launches += 1;
     if (h->opt.linear_solver == BA_DENSE_SCHUR) {
-        if ((rc = chol_clear(ctx.S, &h->chol_plan, h->S_dirty, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
-        h->S_dirty = false;
+        if ((rc = chol_clear(ctx.S, &h->chol_plan, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
         launch_schur_build(ctx, -1.0, s);
         h->launches += 4;
-        // rhs row of the augmented matrix
-        if (h->comm) {
-            if ((rc = allreduce_S(h))) return rc;
-            if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
-        }
+        if ((rc = allreduce_S(h))) return rc;
         // rhs^T becomes row ldS of the matrix: the forward substitution is then part of the factorisation's dataflow
         launch_chol_rhs(ctx, s);
         if (h->profile) cudaEventRecord(h->dom_event(), s);
@@ -638,6 +623,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         CU(h->iters.alloc(sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2)));
         ctx.iters = h->iters.as<ba_iteration>();
     }
+    ctx.rhs = h->rhs.as<double>();                  // (ensure_dense moves it into the S buffer: one message [S | rhs])
     if (h->opt.linear_solver == BA_DENSE_SCHUR && (rc = ensure_dense(h))) return rc;
     h->launches = 0;
     h->prof_used = 0;
@@ -824,10 +810,11 @@ extern "C" int ba_evaluate(ba_handle *h, double *cost, double *residuals, double
         for (int i = 0; i < nb; ++i) c += part[i];
         if (h->comm) {
             // sum over ranks through the device
-            CU(cudaMemcpy(h->sums_loc.p, &c, 8, cudaMemcpyHostToDevice));
-            NC(ncclAllReduce(h->sums_loc.p, h->sums_loc.p, 1, ncclDouble, ncclSum, h->comm, s));
+            double *tmp = h->camsums.as<double>() + CS_COUNT - 1;      // spare slot (rewritten by every linearisation)
+            CU(cudaMemcpy(tmp, &c, 8, cudaMemcpyHostToDevice));
+            NC(ncclAllReduce(tmp, tmp, 1, ncclDouble, ncclSum, h->comm, s));
             CU(cudaStreamSynchronize(s));
-            CU(cudaMemcpy(&c, h->sums_loc.p, 8, cudaMemcpyDeviceToHost));
+            CU(cudaMemcpy(&c, tmp, 8, cudaMemcpyDeviceToHost));
         }
         *cost = c;
     }
@@ -896,29 +883,30 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
         if ((rc = enqueue_linearize(h, 1))) return rc;
     }
     launch_point_invert(ctx, radius, s);
-    if ((rc = chol_clear(ctx.S, &h->chol_plan, true, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
-    h->S_dirty = false;
+    if ((rc = chol_clear(ctx.S, &h->chol_plan, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
     launch_schur_build(ctx, radius, s);
-    if (h->comm) {
-        if ((rc = allreduce_S(h))) return rc;
-        if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
-    }
+    if ((rc = allreduce_S(h))) return rc;
     CU(cudaStreamSynchronize(s));
     CU(cudaGetLastError());
     if (S) {
         // the device matrix is in elimination order (lower blocks): hand it back in camera order, lower blocks
-        const size_t ld = (size_t)ctx.ldS, n = (size_t)ctx.n;
-        std::vector<double> Sp(ld * ld);
+        const size_t n = (size_t)ctx.n;
+        const CholPlan &pl = h->chol_plan;
+        std::vector<double> Sp((size_t)pl.total_doubles);
         std::vector<int> cam_row(ctx.Nc);
-        CU(cudaMemcpy(Sp.data(), ctx.S, 8 * ld * ld, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(Sp.data(), ctx.S, 8 * Sp.size(), cudaMemcpyDeviceToHost));
         CU(cudaMemcpy(cam_row.data(), ctx.cam_row, 4 * (size_t)ctx.Nc, cudaMemcpyDeviceToHost));
+        const auto at = [&](size_t r, size_t q) -> double {                  // element (r, q) of the tile-packed lower triangle
+            const long long o = pl.h_tile_off[(r / CHOL_NB) * (size_t)pl.T + q / CHOL_NB];
+            return o < 0 ? 0.0 : Sp[(size_t)o + (r % CHOL_NB) * CHOL_NB + q % CHOL_NB];
+        };
         std::memset(S, 0, 8 * n * n);
         for (int ci = 0; ci < ctx.Nc; ++ci)
             for (int cj = 0; cj <= ci; ++cj) {
                 const size_t r = cam_row[ci], q = cam_row[cj];
                 for (int a = 0; a < 6; ++a)
                     for (int b = 0; b < 6; ++b)
-                        S[(6 * (size_t)ci + a) * n + 6 * (size_t)cj + b] = (r >= q) ? Sp[(r + a) * ld + q + b] : Sp[(q + b) * ld + r + a];
+                        S[(6 * (size_t)ci + a) * n + 6 * (size_t)cj + b] = (r >= q) ? at(r + a, q + b) : at(q + b, r + a);
             }
     }
     if (rhs) CU(cudaMemcpy(rhs, ctx.rhs, 8 * (size_t)ctx.n, cudaMemcpyDeviceToHost));
@@ -985,17 +973,7 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     int e0 = chol_init();
     if (e0) return fail(BA_ERR_CUDA, "chol_init: %s", cudaGetErrorString((cudaError_t)e0));
     const int np = chol_ld(n);
-    const size_t rows = chol_rows(n);
-    std::vector<double> Ah(rows * (size_t)np, 0.0);
-    for (int i = 0; i < n; ++i) std::memcpy(&Ah[(size_t)i * np], A + (size_t)i * n, 8 * (size_t)(i + 1));
-    for (int i = n; i < np; ++i) Ah[(size_t)i * np + i] = 1.0;
-    std::memcpy(&Ah[(size_t)np * np], b, 8 * (size_t)n);
-    DevBuf dA, dA0, dInv, dY, dFail;
-    CU(dA.alloc(8 * Ah.size())); CU(dA0.alloc(8 * Ah.size()));
-    CU(dInv.alloc(8 * chol_work_doubles(n))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
-    CU(cudaMemcpy(dA0.p, Ah.data(), 8 * Ah.size(), cudaMemcpyHostToDevice));
-    CU(cudaMemset(dFail.p, 0, 4));
-    // tile pattern of the caller's matrix (exact zeros only) -> the same sparsity plan the LM loop uses
+    // tile pattern of the caller's matrix (exact zeros only) -> the same sparsity plan (and tile-packed storage) the LM loop uses
     const int T = np / CHOL_NB;
     std::vector<unsigned char> nz((size_t)T * T, 0);
     for (int i = 0; i < n; ++i) {
@@ -1004,6 +982,14 @@ extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const 
     }
     CholPlan plan;
     if ((rc = chol_plan_create(n, nz.data(), &plan, 0))) return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
+    std::vector<double> Ah;
+    chol_pack_host(&plan, A, b, Ah);
+    DevBuf dA, dA0, dInv, dY, dFail;
+    CU(dA.alloc(8 * Ah.size())); CU(dA0.alloc(8 * Ah.size()));
+    CU(dInv.alloc(8 * chol_work_doubles(n))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
+    CU(cudaMemcpy(dA0.p, Ah.data(), 8 * Ah.size(), cudaMemcpyHostToDevice));
+    CU(cudaMemset(dFail.p, 0, 4));
+    CU(cudaMemset(dInv.p, 0, 8 * chol_work_doubles(n)));
     cudaEvent_t e1, e2;
     CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
     if (repeats < 1) repeats = 1;

@@ -16,9 +16,13 @@
 //   rhs: the right-hand side is row n_pad of A (tile row T), so the forward substitution z = L^-1 rhs IS the tasks (T, j).
 //   back substitution:     block m's owner applies z_m -= L_km^T y_k as the y_k appear, then y_m = L_mm^-T z_m.
 //
-// Layout contract (see chol_rows / chol_ld): A is (n_pad + 128) x n_pad row-major with n_pad = ceil(n / 128) * 128; the
-// lower triangle of the leading n x n block holds S, rows/cols [n, n_pad) are identity padding, row n_pad holds rhs^T,
-// the remaining rows are zero.  FP64 has no tcgen05 kind on sm_100a: mma.sync.m8n8k4.f64 (SASS DMMA) is the tensor-pipe
+// Layout contract: the matrix is stored TILE-PACKED -- only the 128 x 128 tiles of the plan exist, each contiguous and
+// row-major (row stride 128), at offset plan->tile_off[i * T + j] (doubles) of one buffer of plan->total_doubles.  Logical
+// matrix: n_pad = ceil(n / 128) * 128 rows/columns, lower triangle of the leading n x n block = S, rows/cols [n, n_pad)
+// identity padding; tile row T (i = T) is the right-hand side: row 0 of tile (T, j) holds rhs[128 j ..], its other rows are
+// zero.  The tiles S itself can touch come FIRST (plan->front_doubles), followed by plan->extra_doubles caller-owned doubles
+// (the reduced right-hand side in camera order), then the fill-in tiles and the rhs tiles: a sharded solve all-reduces the
+// prefix [S tiles | rhs] in ONE call straight out of the buffer the Schur kernels wrote (no staging copy).  FP64 has no tcgen05 kind on sm_100a: mma.sync.m8n8k4.f64 (SASS DMMA) is the tensor-pipe
 // instruction (measured 37.1 TFLOP/s register-only peak on B200, tools/dmma_bench.cu).
 #include "ba_launch.h"
 
@@ -51,8 +55,6 @@ constexpr int CHOL_SMEM = SMEM_DOUBLES * (int)sizeof(double);      // 221184 B
 static_assert(CHOL_SMEM <= 227 * 1024, "shared memory budget");
 
 int chol_ld(int n) { return ((n + NB - 1) / NB) * NB; }
-size_t chol_rows(int n) { return (size_t)chol_ld(n) + NB; }
-size_t chol_matrix_doubles(int n) { return chol_rows(n) * (size_t)chol_ld(n); }
 // work area: L_jj^-1 blocks, then int flags [tiledone ((T + 1) x T) | ydone (T) | abort (1)]
 static inline int chol_flag_count(int T) { return (T + 1) * T + T + 1; }
 size_t chol_work_doubles(int n) {
@@ -99,8 +101,8 @@ __device__ __forceinline__ double fast_rcp(double d) {
 }
 
 struct CholArgs {
-    double *A;            // (n_pad + 128) x n_pad
-    int ld;               // n_pad
+    double *A;            // tile-packed matrix (see the layout contract)
+    const long long *toff;   // [(T + 1) * T] offset of tile (i, j) in doubles, -1 = not part of the plan
     int T;                // column tiles = n_pad / 128; row tiles = T + 1 (the last one is the rhs row)
     int n;                // logical order (entries of y written)
     double *invL;         // [T][128*128]
@@ -361,7 +363,9 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     // mirrored in the lower warp row so that triangular work (TRSM against the lower-triangular L_jj^-1) is balanced.
     const int wm = warp >> 2, wn = wm ? 3 - (warp & 3) : (warp & 3);
     const int g = lane >> 2, tig = lane & 3;
-    const int T = p.T, ld = p.ld;
+    const int T = p.T;
+    constexpr int ld = NB;                                 // row stride inside a packed tile
+    auto tile_ptr = [&](int ti, int tj) -> double * { return p.A + __ldg(p.toff + (size_t)ti * T + tj); };
     __shared__ int s_have;
     bool aborted = false;
     long long waited = 0, t_potrf = 0, t_trsm = 0, n_tasks = 0;
@@ -380,8 +384,6 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 #pragma unroll
             for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
 
-        const double *Arow = p.A + (size_t)i * NB * ld;    // row panel i
-        const double *Brow = p.A + (size_t)j * NB * ld;    // row panel j
         const int nk = nkb * KSL;                          // k-slices of the bulk update
         int have = 0;                                      // leading klist entries known to be final in both row panels
         // L_ik and L_jk final for klist entry q.  Called at uniform points by ALL threads; only warp 0 touches the flags:
@@ -421,9 +423,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         };
         auto issue = [&](int kt) {
             double *st = smem + (size_t)(kt % NSTAGE) * STAGE_DOUBLES;
-            const size_t col = (size_t)__ldg(p.klist + kbeg + kt / KSL) * NB + (size_t)(kt % KSL) * BK;
-            load_slice(st, Arow + col, ld, tid);
-            if (!diag) load_slice(st + NB * SPAD, Brow + col, ld, tid);
+            const int kb = __ldg(p.klist + kbeg + kt / KSL);
+            const int col = (kt % KSL) * BK;
+            load_slice(st, tile_ptr(i, kb) + col, ld, tid);
+            if (!diag) load_slice(st + NB * SPAD, tile_ptr(j, kb) + col, ld, tid);
         };
         // prologue
         for (int s = 0; s < NSTAGE - 1; ++s) {
@@ -454,7 +457,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 
         // C = A_ij - acc  -> shared tile
         {
-            const double *Cg = p.A + (size_t)(i * NB) * ld + (size_t)j * NB;
+            const double *Cg = tile_ptr(i, j);
 #pragma unroll
             for (int a = 0; a < 8; ++a) {
                 const int row = wm * 64 + a * 8 + g;
@@ -480,9 +483,11 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             // L_jj^-1 first: it is all the TRSMs (and the back substitution) wait for; L_jj itself is only stored for the
             // caller and leaves after the flag is up
             double *Ig = p.invL + (size_t)j * NB * NB;
+            // (only the lower triangle is written: the work area is zeroed when it is allocated and nothing else ever writes
+            // the strict upper part, so half of the 128 KB leaves the SM before the flag can go up)
             for (int idx = tid; idx < NB * NB; idx += 256) {
                 const int r = idx >> 7, c = idx & (NB - 1);
-                Ig[idx] = (c < r) ? tileC[(size_t)c * LDT + r] : (c == r ? dinv[r] : 0.0);
+                if (c <= r) Ig[idx] = (c < r) ? tileC[(size_t)c * LDT + r] : dinv[r];
             }
             if (bad && tid == 0) {
                 if (p.state) p.state->chol_fail = 1;
@@ -491,7 +496,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             __threadfence();
             __syncthreads();
             if (tid == 0) st_release(p.tiledone + (size_t)j * T + j, 1);
-            double *Lg = p.A + (size_t)(j * NB) * ld + (size_t)j * NB;
+            double *Lg = tile_ptr(j, j);
             for (int idx = tid; idx < NB * NB; idx += 256) {
                 const int r = idx >> 7, c = idx & (NB - 1);
                 if (c <= r) Lg[(size_t)r * ld + c] = tileC[(size_t)r * LDT + c];
@@ -521,7 +526,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
                 if (kt <= wn) mma_slice(acc, a_s, LDT, b_s);   // L_jj^-1 is lower triangular: k-slices right of this warp's columns are zero
                 __syncthreads();
             }
-            double *Cg = p.A + (size_t)(i * NB) * ld + (size_t)j * NB;
+            double *Cg = tile_ptr(i, j);
 #pragma unroll
             for (int a = 0; a < 8; ++a) {
                 const int row = wm * 64 + a * 8 + g;
@@ -552,11 +557,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     double *zs = smem;                 // [128] running z_m
     double *ys = smem + NB;            // [128] y_k being applied
     double *part = smem + 2 * NB;      // [2][128]
-    const double *z = p.A + (size_t)T * NB * ld;
     for (int m = T - 1 - (int)blockIdx.x; m >= 0; m -= gridDim.x) {
         // z_m is final once tile (T, m) is
         if (!__syncthreads_and(tid != 0 || (wait_ge(p.tiledone + (size_t)T * T + m, 1, p.abort_flag, waited) && wait_ge(p.tiledone + (size_t)m * T + m, 1, p.abort_flag, waited)))) break;
-        if (tid < NB) zs[tid] = __ldcg(z + (size_t)m * NB + tid);
+        if (tid < NB) zs[tid] = __ldcg(tile_ptr(T, m) + tid);      // row 0 of the rhs tile
         const int c = tid & (NB - 1), half = tid >> 7;
         bool ok = true;
         for (int k = T - 1; k > m; --k) {
@@ -565,7 +569,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (!__syncthreads_and(ok)) { ok = false; break; }
             if (tid < NB) ys[tid] = __ldcg(p.ypad + (size_t)k * NB + tid);
             __syncthreads();
-            const double *Lkm = p.A + (size_t)(k * NB + half * 64) * ld + (size_t)m * NB + c;
+            const double *Lkm = tile_ptr(k, m) + (size_t)(half * 64) * ld + c;
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
             for (int rb = 0; rb < 64; rb += 32) {
@@ -738,17 +742,27 @@ void chol_tile_order(int G, const unsigned char *adj, std::vector<int> &order) {
 namespace {
 struct HostPlan {
     std::vector<unsigned char> blob;
-    size_t o_task = 0, o_kl = 0, o_fill = 0;
+    std::vector<long long> toff;          // [(T + 1) * T]
+    long long front_doubles = 0, extra_doubles = 0, total_doubles = 0;
+    size_t o_task = 0, o_kl = 0, o_fill = 0, o_toff = 0;
     int T = 0, ntasks = 0, depth = 0;
     long long filled = 0;
     double flops = 0.0;
 };
 
-void plan_analyse(int n, const unsigned char *nz, HostPlan &hp) {
+void plan_analyse(int n, const unsigned char *nz, HostPlan &hp, size_t extra_doubles = 0) {
     const int T = chol_ld(n) / NB;
     std::vector<unsigned char> f((size_t)(T + 1) * T, 0);
     for (int i = 0; i < T; ++i)
         for (int j = 0; j <= i; ++j) f[(size_t)i * T + j] = (i == j) || !nz || nz[(size_t)i * T + j] || nz[(size_t)j * T + i];
+    // storage: [tiles S can touch | extra (caller's rhs) | fill-in tiles | rhs tiles]
+    hp.toff.assign((size_t)(T + 1) * T, -1);
+    long long off = 0;
+    for (int i = 0; i < T; ++i)
+        for (int j = 0; j <= i; ++j) if (f[(size_t)i * T + j]) { hp.toff[(size_t)i * T + j] = off; off += (long long)NB * NB; }
+    hp.front_doubles = off;
+    hp.extra_doubles = (long long)((extra_doubles + 1) & ~(size_t)1);     // keeps every tile 16-byte aligned
+    off += hp.extra_doubles;
     std::vector<int> rows;
     for (int j = 0; j < T; ++j) {                       // eliminating column j couples all its rows pairwise
         rows.clear();
@@ -757,6 +771,10 @@ void plan_analyse(int n, const unsigned char *nz, HostPlan &hp) {
             for (size_t b = a + 1; b < rows.size(); ++b) f[(size_t)rows[b] * T + rows[a]] = 1;
     }
     for (int j = 0; j < T; ++j) f[(size_t)T * T + j] = 1;   // the rhs row
+    for (int i = 0; i <= T; ++i)
+        for (int j = 0; j < T && j <= i; ++j)
+            if (f[(size_t)i * T + j] && hp.toff[(size_t)i * T + j] < 0) { hp.toff[(size_t)i * T + j] = off; off += (long long)NB * NB; }
+    hp.total_doubles = off;
     // tasks = filled tiles; dependency level = longest chain of tasks below it.  Tasks are handed out in level order
     // (a topological order, so the round-robin dataflow cannot deadlock): independent sub-chains of a sparse pattern
     // run side by side.  For a dense matrix this is exactly the column-major order.
@@ -803,9 +821,12 @@ void plan_analyse(int n, const unsigned char *nz, HostPlan &hp) {
     flops += 2.0 * (double)filled * NB * NB;                                        // back substitution
     const size_t o_task = 0, o_kl = o_task + sizeof(int4) * task.size();
     const size_t o_fill = o_kl + sizeof(int) * std::max<size_t>(klist.size(), 1);
-    const size_t bytes = o_fill + f.size();
+    const size_t o_toff = (o_fill + f.size() + 15) & ~(size_t)15;
+    const size_t bytes = o_toff + sizeof(long long) * hp.toff.size();
     std::vector<unsigned char> &blob = hp.blob;
     blob.assign(bytes, 0);
+    std::memcpy(blob.data() + o_toff, hp.toff.data(), sizeof(long long) * hp.toff.size());
+    hp.o_toff = o_toff;
     std::memcpy(blob.data() + o_task, task.data(), sizeof(int4) * task.size());
     if (!klist.empty()) std::memcpy(blob.data() + o_kl, klist.data(), sizeof(int) * klist.size());
     std::memcpy(blob.data() + o_fill, f.data(), f.size());
@@ -823,9 +844,9 @@ void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *fill
     if (flops) *flops = hp.flops;
 }
 
-int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t s) {
+int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t s, size_t extra_doubles) {
     HostPlan hp;
-    plan_analyse(n, nz, hp);
+    plan_analyse(n, nz, hp, extra_doubles);
     const size_t bytes = hp.blob.size();
     if (pl->cap < bytes) {
         if (pl->blob) cudaFree(pl->blob);
@@ -843,31 +864,18 @@ int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t 
     pl->task = reinterpret_cast<const int4 *>(b + hp.o_task);
     pl->klist = reinterpret_cast<const int *>(b + hp.o_kl);
     pl->fill = b + hp.o_fill;
+    pl->tile_off = reinterpret_cast<const long long *>(b + hp.o_toff);
+    pl->h_tile_off = hp.toff;
+    pl->front_doubles = hp.front_doubles; pl->extra_doubles = hp.extra_doubles; pl->total_doubles = hp.total_doubles;
     pl->filled_tiles = hp.filled;
     pl->depth = hp.depth;
     pl->flops = hp.flops;
     return 0;
 }
 
-// zero the tiles the factorisation will touch (S tiles + fill-in); everything else is zero already and stays zero
-__global__ void __launch_bounds__(256) chol_clear_kernel(double *__restrict__ A, int ld, int T, const unsigned char *__restrict__ fill) {
-    int i = (int)((sqrtf(8.0f * blockIdx.x + 1.0f) - 1.0f) * 0.5f);          // blockIdx = i (i + 1) / 2 + j, j <= i
-    while ((i + 1) * (i + 2) / 2 <= (int)blockIdx.x) ++i;
-    while (i * (i + 1) / 2 > (int)blockIdx.x) --i;
-    const int j = blockIdx.x - i * (i + 1) / 2;
-    if (!fill[(size_t)i * T + j]) return;
-    double *dst = A + (size_t)i * NB * ld + (size_t)j * NB;
-    for (int idx = threadIdx.x; idx < NB * NB / 2; idx += blockDim.x) {
-        const int r = idx / (NB / 2), c2 = idx % (NB / 2);
-        reinterpret_cast<double2 *>(dst + (size_t)r * ld)[c2] = make_double2(0.0, 0.0);
-    }
-}
-
-int chol_clear(double *A, const CholPlan *plan, bool everything, cudaStream_t s) {
-    if (everything) return (int)cudaMemsetAsync(A, 0, sizeof(double) * chol_matrix_doubles(plan->n), s);
-    const int T = plan->T;
-    chol_clear_kernel<<<T * (T + 1) / 2, 256, 0, s>>>(A, chol_ld(plan->n), T, plan->fill);
-    return (int)cudaGetLastError();
+// zero the whole packed matrix (every tile of the plan + the caller's extra region) before S is assembled
+int chol_clear(double *A, const CholPlan *plan, cudaStream_t s) {
+    return (int)cudaMemsetAsync(A, 0, sizeof(double) * (size_t)plan->total_doubles, s);
 }
 
 void chol_plan_destroy(CholPlan *pl) {
@@ -875,23 +883,38 @@ void chol_plan_destroy(CholPlan *pl) {
     *pl = CholPlan();
 }
 
-static CholPlan g_dense_plan[64];   // per device: fully dense plan of the last order asked for (standalone use)
+// host matrix (n x n row-major, lower triangle read) + rhs -> the plan's tile-packed storage (host vector of total_doubles)
+void chol_pack_host(const CholPlan *pl, const double *A, const double *b, std::vector<double> &out) {
+    const int n = pl->n, T = pl->T;
+    out.assign((size_t)pl->total_doubles, 0.0);
+    for (int ti = 0; ti < T; ++ti)
+        for (int tj = 0; tj <= ti; ++tj) {
+            const long long o = pl->h_tile_off[(size_t)ti * T + tj];
+            if (o < 0) continue;
+            double *t = out.data() + o;
+            for (int r = 0; r < NB; ++r) {
+                const int gi = ti * NB + r;
+                for (int c = 0; c < NB; ++c) {
+                    const int gj = tj * NB + c;
+                    if (gj > gi) continue;
+                    t[(size_t)r * NB + c] = (gi < n && gj < n) ? A[(size_t)gi * n + gj] : (gi == gj ? 1.0 : 0.0);
+                }
+            }
+        }
+    for (int tj = 0; tj < T; ++tj) {
+        double *t = out.data() + pl->h_tile_off[(size_t)T * T + tj];
+        for (int c = 0; c < NB; ++c) { const int gj = tj * NB + c; t[c] = gj < n ? b[gj] : 0.0; }
+    }
+}
 
 int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s) {
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
     const int ld = chol_ld(n), T = ld / NB;
-    if (!plan) {
-        if (g_dense_plan[dev].n != n) {
-            int rc = chol_plan_create(n, nullptr, &g_dense_plan[dev], s);
-            if (rc) return rc;
-        }
-        plan = &g_dense_plan[dev];
-    }
-    if (plan->n != n || plan->T != T) return (int)cudaErrorInvalidValue;
+    if (!plan || plan->n != n || plan->T != T) return (int)cudaErrorInvalidValue;       // the plan defines the storage
     CholArgs p;
-    p.A = A; p.ld = ld; p.T = T; p.n = n;
+    p.A = A; p.toff = plan->tile_off; p.T = T; p.n = n;
     p.invL = work;
     p.ypad = work + (size_t)T * NB * NB;
     int *flags = reinterpret_cast<int *>(p.ypad + (size_t)T * NB);

@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_lin_partials_kernel(Ctx ct
     if (!grid_sum3_max(cost, gsq, xsq, gmax, red_slot(ctx, RED_LIN), ctx.red_count + RED_LIN, red)) return;
     if (threadIdx.x == 0) {
         ctx.sums_loc[SUM_LIN_COST] = cost; ctx.sums_loc[SUM_LIN_GSQ] = gsq; ctx.sums_loc[SUM_LIN_XSQ] = xsq;
-        ctx.maxs_loc[MAX_LIN_G] = gmax;
+        ctx.maxs_loc[0] = gmax;
     }
 }
 
@@ -410,9 +410,9 @@ __global__ void schur_init_kernel(Ctx ctx, double radius_override) {
     if (i >= ctx.ldS) return;
     const bool lead = ctx.rank == 0;
     const int src = ctx.row_src[i];
-    if (src < 0) { ctx.S[(size_t)i * ctx.ldS + i] = lead ? 1.0 : 0.0; return; }     // identity padding
+    if (src < 0) { *s_elem(ctx, i, i) = lead ? 1.0 : 0.0; return; }     // identity padding
     const int c = src / 6, a = src % 6;
-    double *row = ctx.S + (size_t)i * ctx.ldS + ctx.cam_row[c];
+    double *row = s_elem(ctx, i, ctx.cam_row[c]);        // a camera's 6 x 6 block never straddles a tile (21 cameras per tile)
     if (ctx.cam_kind[c] == CAM_FREE) {
         const double *U = ctx.U + 36 * (size_t)c;
 #pragma unroll
@@ -431,7 +431,7 @@ __global__ void chol_rhs_kernel(Ctx ctx) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= ctx.ldS) return;
     const int src = ctx.row_src[i];
-    ctx.S[(size_t)ctx.ldS * ctx.ldS + i] = src >= 0 ? ctx.rhs[src] : 0.0;
+    ctx.S[ctx.S_toff[(size_t)ctx.S_T * ctx.S_T + (i >> 7)] + (i & 127)] = src >= 0 ? ctx.rhs[src] : 0.0;     // row 0 of rhs tile i / 128
 }
 __global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
     if (ctx.state->done) return;
@@ -559,8 +559,8 @@ __global__ void schur_segments_kernel(Ctx ctx, int force) {
     if (k < 36) {
         // block (camera x, camera y) of the lower triangle IN ELIMINATION ORDER: transposed if y comes later than x
         const int r = ctx.cam_row[cams.x] + k / 6, q = ctx.cam_row[cams.y] + k % 6;
-        if (ctx.cam_row[cams.x] >= ctx.cam_row[cams.y]) ctx.S[(size_t)r * ctx.ldS + q] -= t;
-        else ctx.S[(size_t)q * ctx.ldS + r] -= t;
+        if (ctx.cam_row[cams.x] >= ctx.cam_row[cams.y]) *s_elem(ctx, r, q) -= t;
+        else *s_elem(ctx, q, r) -= t;
     }
     else ctx.rhs[6 * (size_t)cams.x + (k - 36)] -= t;
 }
@@ -757,7 +757,9 @@ __global__ void lm_begin_iteration_kernel(Ctx ctx) {
     if (st->need_linearize) {
         st->x_cost = ctx.sums[SUM_LIN_COST];
         it.cost = st->x_cost;
-        it.gradient_max_norm = fmax(ctx.maxs[MAX_LIN_G], ctx.camsums[CS_GMAX]);
+        double gm = ctx.camsums[CS_GMAX];
+        for (int r = 0; r < max(ctx.n_ranks, 1); ++r) gm = fmax(gm, ctx.maxs[r]);      // one slot per rank (summed message)
+        it.gradient_max_norm = gm;
         it.gradient_norm = sqrt(ctx.sums[SUM_LIN_GSQ] + ctx.camsums[CS_GSQ]);
         st->x_norm = sqrt(ctx.sums[SUM_LIN_XSQ] + ctx.camsums[CS_XSQ]);
         if (it.iteration == 0) {
@@ -1002,23 +1004,6 @@ void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) 
         schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, 0, s>>>(ctx, force);
         schur_segments_kernel<<<(unsigned)(((long long)ctx.pairs.n_seg * 42 + 255) / 256), 256, 0, s>>>(ctx, force);
     }
-}
-
-// multi-GPU: only the tiles of S that a camera pair can touch travel through the all-reduce (packed contiguously)
-__global__ void __launch_bounds__(256) tiles_copy_kernel(double *__restrict__ S, int ld, const int2 *__restrict__ tiles,
-                                                          double *__restrict__ packed, int unpack) {
-    const int2 t = tiles[blockIdx.x];
-    double *src = S + (size_t)t.x * CHOL_NB * ld + (size_t)t.y * CHOL_NB;
-    double *pk = packed + (size_t)blockIdx.x * CHOL_NB * CHOL_NB;
-    for (int idx = threadIdx.x; idx < CHOL_NB * CHOL_NB / 2; idx += blockDim.x) {
-        const int r = idx / (CHOL_NB / 2), c2 = idx % (CHOL_NB / 2);
-        double2 *a = reinterpret_cast<double2 *>(src + (size_t)r * ld) + c2;
-        double2 *b = reinterpret_cast<double2 *>(pk + (size_t)r * CHOL_NB) + c2;
-        if (unpack) *a = *b; else *b = *a;
-    }
-}
-void launch_tiles_copy(double *S, int ld, const int2 *tiles, int n_tiles, double *packed, int unpack, cudaStream_t s) {
-    if (n_tiles > 0) tiles_copy_kernel<<<n_tiles, 256, 0, s>>>(S, ld, tiles, packed, unpack);
 }
 
 void launch_chol_rhs(const Ctx &ctx, cudaStream_t s) { chol_rhs_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx); }

@@ -20,7 +20,6 @@ void launch_lm_publish(const Ctx &ctx, int body, cudaStream_t s);        // verd
 void launch_pcg_publish(const Ctx &ctx, int iteration, cudaStream_t s);  // verdict as of the end of CG iteration -> host ring
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
-void launch_tiles_copy(double *S, int ld, const int2 *tiles, int n_tiles, double *packed, int unpack, cudaStream_t s);
 void launch_chol_rhs(const Ctx &ctx, cudaStream_t s);                       // rhs -> row ldS of S, in elimination order
 void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s);  // y (elimination order) -> yc
 void launch_backsub(const Ctx &ctx, cudaStream_t s);
@@ -70,17 +69,21 @@ int prep_group_map(const PairIndex &pi, int G, unsigned char *map, cudaStream_t 
 constexpr int CHOL_NB = 128;
 int chol_init();                                        // per-device kernel attribute setup; returns cudaError
 int chol_ld(int n);                                     // n_pad = ceil(n / 128) * 128 = leading dimension
-size_t chol_rows(int n);                                // n_pad + 128 rows
-size_t chol_matrix_doubles(int n);                      // rows * ld
 size_t chol_work_doubles(int n);
-// A: chol_rows(n) x chol_ld(n) row-major: lower triangle of the leading n x n block = S, rows/cols [n, n_pad) identity
-// padding, row n_pad = rhs^T, all other rows zero.  On exit y (n) holds the solution and A's lower triangle holds L.
+// A: the plan's tile-packed storage (plan->total_doubles doubles, see the layout contract in ba_cholesky.cu): 128 x 128
+// tiles, each contiguous and row-major, at plan->tile_off[i * T + j]; tile row T is the right-hand side (row 0 of each tile).
+// On exit y (n) holds the solution and the tiles hold L.
 // state may be nullptr (standalone use); otherwise the kernel early-exits on state->done and reports breakdown in
 // state->chol_fail.  fail_flag (device int, may be nullptr) is set on breakdown as well.  Returns a cudaError.
 // plan: tile-level sparsity plan of this matrix (nullptr = dense).
 struct CholPlan {
     int n = 0, T = 0, ntasks = 0;
     const int4 *task = nullptr; const int *klist = nullptr; const unsigned char *fill = nullptr;
+    const long long *tile_off = nullptr;      // device [(T + 1) * T]: offset of tile (i, j) in doubles, -1 = not in the plan
+    std::vector<long long> h_tile_off;        // host copy
+    long long front_doubles = 0;     // the tiles S itself can touch are stored first: [0, front_doubles)
+    long long extra_doubles = 0;     // caller-owned region right behind them (the reduced rhs in camera order)
+    long long total_doubles = 0;     // size of the packed matrix buffer
     long long filled_tiles = 0;      // tiles of L (T x T lower triangle) that can be nonzero
     double flops = 0.0;              // factorisation + both substitutions over the filled tiles
     int depth = 0;                   // longest dependency chain, in tasks
@@ -89,10 +92,11 @@ struct CholPlan {
 // nz: host T x T bytes, (i, j) != 0 where tile (i, j) or (j, i) of S can be nonzero (nullptr = dense); synchronises s.
 // Elimination order of the tiles from their adjacency (G x G bytes, lower triangle read): order[pos] = tile.
 void chol_tile_order(int G, const unsigned char *adj, std::vector<int> &order);
-int chol_plan_create(int n, const unsigned char *nz, CholPlan *plan, cudaStream_t s);
+int chol_plan_create(int n, const unsigned char *nz, CholPlan *plan, cudaStream_t s, size_t extra_doubles = 0);
+void chol_pack_host(const CholPlan *plan, const double *A, const double *b, std::vector<double> &out);   // host matrix -> packed tiles
 void chol_plan_destroy(CholPlan *plan);
-// zero A before S is assembled: the whole buffer, or only the tiles of the plan (the rest must already be zero)
-int chol_clear(double *A, const CholPlan *plan, bool everything, cudaStream_t s);
+// zero the packed matrix (all tiles of the plan + the extra region) before S is assembled
+int chol_clear(double *A, const CholPlan *plan, cudaStream_t s);
 void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *filled, double *flops);   // host only
 int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
 

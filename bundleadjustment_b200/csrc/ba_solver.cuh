@@ -25,8 +25,8 @@ enum : int {
     SUM_COUNT = 8
 };
 constexpr int SUM_LIN_BEGIN = 0, SUM_LIN_N = 3, SUM_STEP_BEGIN = 3, SUM_STEP_N = 4;
-// slots of the all-reduced (max) scalar vector
-enum : int { MAX_LIN_G = 0, MAX_COUNT = 2 };
+// The max over ranks of the landmark-side gradient norm travels in the summed message: ctx.maxs has one slot per rank, rank r
+// writes slot r (ctx.maxs_loc points at it), lm_begin_iteration takes the max of the slots.
 // camera-side scalars (replicated, never all-reduced)
 enum : int { CS_GSQ = 0, CS_GMAX, CS_XSQ, CS_DXSQ, CS_YB, CS_YHY, CS_COUNT = 8 };
 
@@ -112,6 +112,7 @@ struct Ctx {
     // Jacobi scaling
     double *scale_cam, *scale_pt;
     // normal-equation blocks (scaled space)
+    // [U | b_c | sums | max slots] are ONE contiguous buffer (the packed linearisation message, ba_capi.cu)
     double *U;               // [Nc][36]  (summed over ranks)
     double *bc;              // [Nc][6]   (summed over ranks)
     double *U_loc, *bc_loc;  // this rank's contribution (alias U / bc on a single GPU)
@@ -124,7 +125,10 @@ struct Ctx {
     // reduced system
     // One Cholesky tile (128 rows) holds CAMS_PER_TILE consecutive cameras (126 rows + 2 identity rows); the tiles are laid
     // out in elimination order (nested dissection of the camera-group graph), so camera c's block starts at row cam_row[c].
-    double *S;               // [ldS + 128][ldS] row-major, lower blocks; row ldS = rhs^T (see ba_cholesky.cu)
+    double *S;               // TILE-PACKED (ba_cholesky.cu layout contract): tile (i, j) of the padded lower triangle at S + S_toff[i * S_T + j],
+                             // 128 x 128 row-major; tile row S_T = the right-hand side (row 0 of each tile)
+    const long long *S_toff; // [(S_T + 1) * S_T] offsets in doubles, -1 = structurally zero tile
+    int S_T;                 // tiles per side = ldS / 128
     int ldS;                 // order of the padded system = 128 * number of camera groups
     const int *cam_row;      // [Nc]
     const int *row_src;      // [ldS] 6 c + a of the camera parameter in that row, -1 for padding rows
@@ -134,8 +138,8 @@ struct Ctx {
     double *part;            // [n_part][4]
     int n_part;
     double *sums;            // [SUM_COUNT]  (summed over ranks)
-    double *maxs;            // [MAX_COUNT]  (max over ranks)
-    double *sums_loc, *maxs_loc;   // this rank's contribution (alias sums / maxs on a single GPU)
+    double *maxs;            // [n_ranks] one slot per rank
+    double *sums_loc, *maxs_loc;   // this rank's contribution (alias sums / maxs on a single GPU); maxs_loc = this rank's slot
     double *camsums;         // [CS_COUNT]
     double *red_part;        // [RED_SLOTS][RED_MAX_GRID][4] per-CTA partials of the multi-CTA reductions (grid_sum3_max)
     unsigned *red_count;     // [RED_SLOTS] arrival tickets (zero between launches)
@@ -161,6 +165,10 @@ enum : int { RED_LIN = 0, RED_CAM_NORMS, RED_CAM_UPDATE, RED_STEP, RED_CG_CHECK,
 __host__ __device__ inline double *red_slot(const Ctx &ctx, int slot) { return ctx.red_part + (size_t)slot * RED_MAX_GRID * 4; }
 
 constexpr int CAMS_PER_TILE = 21;   // 6 * 21 = 126 <= 128 (CHOL_NB)
+// element (r, q), r >= q's tile row, of the tile-packed reduced system (the tile must be part of the plan)
+__device__ __forceinline__ double *s_elem(const Ctx &ctx, int r, int q) {
+    return ctx.S + ctx.S_toff[(size_t)(r >> 7) * ctx.S_T + (q >> 7)] + (size_t)(r & 127) * 128 + (q & 127);
+}
 constexpr int CHUNK = 128;   // observations per camera-side reduction unit
 constexpr int TILE_WIN = 192;   // observation window defining a landmark block of the tile kernels (ba_prep.cu)
 constexpr int TILE_THREADS = 256;

@@ -3,12 +3,13 @@ tools/mgpu_check.py): sharded against single-GPU, or the CUDA path against the C
 
 Tolerances are north_star's: per-iteration cost trajectory 1e-6 relative, final cost 1e-8 relative, poses 1e-6, landmarks
 
-    |x_a - x_b|  <=  1e-6 * max(1, |x|)  +  C_COND * eps * cond(V_p') * |x_final - x_initial|
+    |x_a - x_b|  <=  1e-6 * max(1, |x|)  +  cond(V_p') * (C_COND * eps * |x_final - x_initial| + C_CAM * max|cam_a - cam_b|)
 
 The second term is a STATED bound, not a waiver: a landmark seen along nearly parallel rays has an almost singular 3x3 block
 V_p' = sum Jp^T Jp + D_p^2 (depth is barely observable), and two correct solvers that add the same terms in different orders
 (landmark shards, tile plans, CPU vs GPU reductions) differ there by cond(V_p') times the rounding of their inputs, times the
-distance the landmark moved.  cond(V_p') is evaluated here, for the landmarks that need it only, from the pinhole Jacobians
+distance the landmark moved, plus the response of the back-substitution y_p = V_p'^-1 (b_p - W^T y_c) to the (gated,
+<= 1e-6) difference of the camera steps.  cond(V_p') is evaluated here, for the landmarks that need it only, from the pinhole Jacobians
 of the reference functors (ba_project/src/ba/Optimizer.h:54-76, 96-107) at solution b; a landmark outside the bound fails
 the gate."""
 from __future__ import annotations
@@ -17,6 +18,7 @@ import numpy as np
 
 EPS = float(np.finfo(np.float64).eps)
 C_COND = 64.0
+C_CAM = 8.0
 
 
 def _rodrigues(w: np.ndarray) -> np.ndarray:
@@ -80,7 +82,7 @@ def compare(pb, a: dict, b: dict, cost_rtol: float = 1e-6, final_rtol: float = 1
     if need.size:
         cond = landmark_condition(pb, b["cam"], b["pt"], need, float(b.get("radius", 1e4)))
         travel = np.linalg.norm(b["pt"][need] - pb.pt[need], axis=1)
-        bound = rel[need] + C_COND * EPS * cond * travel
+        bound = rel[need] + cond * (C_COND * EPS * travel + C_CAM * dcam)
         n_bad = int((diff[need] > bound).sum())
         worst_ratio = float((diff[need] / bound).max())
     ok = bool(same_len and cost_rel is not None and cost_rel <= cost_rtol and final_rel <= final_rtol and dcam <= 1e-6 and n_bad == 0)
@@ -88,4 +90,4 @@ def compare(pb, a: dict, b: dict, cost_rtol: float = 1e-6, final_rtol: float = 1
             "max_cam_diff": dcam, "max_pt_diff": float(diff.max()) if diff.size else 0.0,
             "pt_over_1e-6_rel": int(need.size), "pt_outside_cond_bound": n_bad, "pt_worst_diff_over_bound": worst_ratio,
             "tolerances": {"cost_trajectory_rel": cost_rtol, "final_cost_rel": final_rtol, "cam_abs": 1e-6,
-                           "pt": f"1e-6*max(1,|x|) + {C_COND:g}*eps*cond(V_p')*|x - x0|"}}
+                           "pt": f"1e-6*max(1,|x|) + cond(V_p')*({C_COND:g}*eps*|x - x0| + {C_CAM:g}*max_cam_diff)"}}

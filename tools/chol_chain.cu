@@ -10,18 +10,23 @@
 
 using namespace ba;
 
-__global__ void fill_pattern(double *A, int ld, size_t rows, const unsigned char *nz, int T) {
-    const size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (idx >= rows * (size_t)ld) return;
-    const int r = (int)(idx / ld), c = (int)(idx % ld);
-    double v = 0.0;
-    if (r < ld && c <= r && nz[(size_t)(r / 128) * T + c / 128]) {
-        unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
-        h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
-        v = ((h & 0xffff) / 65536.0 - 0.5) * 0.01;
-        if (r == c) v = 1.0 + 0.04 * sqrt((double)ld);
-    } else if (r == ld) v = 1.0;
-    A[idx] = v;
+// one CTA per tile slot (i, j) of the plan's tile-packed storage: pseudo-random SPD-dominant entries, rhs row = 1
+__global__ void fill_pattern(double *A, const long long *toff, int T, int ld) {
+    const int i = blockIdx.x / T, j = blockIdx.x % T;
+    const long long o = toff[(size_t)i * T + j];
+    if (o < 0) return;
+    for (int idx = threadIdx.x; idx < 128 * 128; idx += blockDim.x) {
+        const int r = i * 128 + idx / 128, c = j * 128 + idx % 128;
+        double v = 0.0;
+        if (i == T) v = (idx / 128 == 0) ? 1.0 : 0.0;
+        else if (c <= r) {
+            unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
+            h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
+            v = ((h & 0xffff) / 65536.0 - 0.5) * 0.01;
+            if (r == c) v = 1.0 + 0.04 * sqrt((double)ld);
+        }
+        A[o + idx] = v;
+    }
 }
 
 int main(int argc, char **argv) {
@@ -33,13 +38,11 @@ int main(int argc, char **argv) {
     if (natural) std::iota(order.begin(), order.end(), 0); else chol_tile_order(G, adj.data(), order);
     for (int p = 0; p < G; ++p) pos[order[p]] = p;
     for (int i = 0; i < G; ++i) for (int j = 0; j <= i; ++j) if (adj[(size_t)i * G + j]) nz[(size_t)std::max(pos[i], pos[j]) * G + std::min(pos[i], pos[j])] = 1;
-    const size_t rows = chol_rows(n);
-    double *A, *work, *y; unsigned char *dnz;
-    cudaMalloc(&A, 8 * rows * ld); cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld); cudaMalloc(&dnz, nz.size());
-    cudaMemcpy(dnz, nz.data(), nz.size(), cudaMemcpyHostToDevice);
+    double *A, *work, *y;
     if (chol_init()) { printf("chol_init failed\n"); return 1; }
     CholPlan plan;
     if (chol_plan_create(n, nz.data(), &plan, 0)) { printf("plan failed\n"); return 1; }
+    cudaMalloc(&A, 8 * (size_t)plan.total_doubles); cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMemset(work, 0, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
     printf("G=%d band=%d %s order: %lld filled tiles, %d tasks, depth %d, %.3f GFLOP\n", G, band, natural ? "natural" : "nested-dissection",
            plan.filled_tiles, plan.ntasks, plan.depth, plan.flops * 1e-9);
     const size_t nprof = 4 * (size_t)plan.ntasks + T;
@@ -47,7 +50,7 @@ int main(int argc, char **argv) {
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
     for (int r = 0; r < 4; ++r) {
-        fill_pattern<<<(unsigned)((rows * ld + 255) / 256), 256>>>(A, ld, rows, dnz, T);
+        fill_pattern<<<(T + 1) * T, 256>>>(A, plan.tile_off, T, ld);
         cudaMemset(g_chol_task_prof, 0, 8 * nprof);
         cudaEventRecord(e0);
         int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, &plan, 0);

@@ -9,28 +9,31 @@
 
 using namespace ba;
 
-__global__ void fill_spd(double *A, int n, int ld, size_t rows, int band) {
-    const size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (idx >= rows * (size_t)ld) return;
-    const int r = (int)(idx / ld), c = (int)(idx % ld);
-    double v = 0.0;
-    if (r < n && c <= r && r - c <= band) {
-        unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
-        h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
-        v = ((h & 0xffff) / 65536.0 - 0.5) * 0.01;
-        if (r == c) v = 1.0 + 0.04 * sqrt((double)n);
-    } else if (r < ld && r == c) v = 1.0;
-    else if (r == ld && c < n) v = 1.0;
-    A[idx] = v;
+// one CTA per tile slot (i, j) of the plan's tile-packed storage: banded pseudo-random SPD-dominant entries, rhs row = 1
+__global__ void fill_spd(double *A, const long long *toff, int T, int n, int band) {
+    const int i = blockIdx.x / T, j = blockIdx.x % T;
+    const long long o = toff[(size_t)i * T + j];
+    if (o < 0) return;
+    for (int idx = threadIdx.x; idx < 128 * 128; idx += blockDim.x) {
+        const int r = i * 128 + idx / 128, c = j * 128 + idx % 128;
+        double v = 0.0;
+        if (i == T) v = (idx / 128 == 0 && c < n) ? 1.0 : 0.0;
+        else if (r < n && c <= r && r - c <= band) {
+            unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
+            h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
+            v = ((h & 0xffff) / 65536.0 - 0.5) * 0.01;
+            if (r == c) v = 1.0 + 0.04 * sqrt((double)n);
+        } else if (r == c) v = 1.0;
+        A[o + idx] = v;
+    }
 }
 
 int main(int argc, char **argv) {
     const int n = argc > 1 ? atoi(argv[1]) : 10200;
     const int band = argc > 2 ? atoi(argv[2]) : n;
     const int ld = chol_ld(n);
-    const size_t rows = chol_rows(n);
     double *A, *work, *y;
-    cudaMalloc(&A, 8 * rows * ld); cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
+    cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMemset(work, 0, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
     cudaMalloc(&g_chol_prof, 8 * 8 * 256);
     if (chol_init()) { printf("chol_init failed\n"); return 1; }
     // tile plan of the band (exact tile pattern of fill_spd)
@@ -39,13 +42,14 @@ int main(int argc, char **argv) {
     for (int i = 0; i < Tp; ++i)
         for (int j = 0; j <= i; ++j) nz[(size_t)i * Tp + j] = (i * CHOL_NB - (j * CHOL_NB + CHOL_NB - 1)) <= band;
     CholPlan plan;
-    const CholPlan *plan_ptr = nullptr;
-    if (band < n) { if (chol_plan_create(n, nz.data(), &plan, 0)) { printf("plan failed\n"); return 1; } plan_ptr = &plan;
-        printf("band %d: %lld filled tiles, %d tasks, %.3f GFLOP\n", band, plan.filled_tiles, plan.ntasks, plan.flops * 1e-9); }
+    if (chol_plan_create(n, band < n ? nz.data() : nullptr, &plan, 0)) { printf("plan failed\n"); return 1; }
+    const CholPlan *plan_ptr = &plan;
+    if (band < n) printf("band %d: %lld filled tiles, %d tasks, %.3f GFLOP\n", band, plan.filled_tiles, plan.ntasks, plan.flops * 1e-9);
+    cudaMalloc(&A, 8 * (size_t)plan.total_doubles);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
     for (int r = 0; r < 4; ++r) {
-        fill_spd<<<(unsigned)((rows * ld + 255) / 256), 256>>>(A, n, ld, rows, band);
+        fill_spd<<<(Tp + 1) * Tp, 256>>>(A, plan.tile_off, Tp, n, band);
         cudaEventRecord(e0);
         int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, plan_ptr, 0);
         cudaEventRecord(e1);
