@@ -107,6 +107,7 @@ struct ba_handle {
     DevBuf part, cost_part, red_part, red_count, lin_red, lin_loc, camsums, state, iters, invL;   // lin_*: [U | b_c | sums | max slots], one all-reduce
     DevBuf cg_r, cg_p, cg_z, cg_q, cg_x, Minv, tp, cg_part, cg_qp;
     DevBuf ev_res, ev_jc, ev_jp;     // materialised evaluation outputs
+    DevBuf o_pose, o_extr, o_pt32, o_wb, o_ptr, o_xy, o_oct, o_xyz, o_mn, o_mx, o_has, o_out, o_kp_pt, o_kp_obs, o_masked, o_active;   // ba_solve_outer
     int *host_flags = nullptr;       // mapped pinned
     int *host_flags_dev = nullptr;
     // NCCL
@@ -137,7 +138,8 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &red_part, &red_count, &lin_red, &lin_loc,
                          &camsums, &state, &iters, &invL, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &tile_map, &cam_row, &row_src, &yperm};
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &tile_map, &cam_row, &row_src, &yperm,
+                         &o_pose, &o_extr, &o_pt32, &o_wb, &o_ptr, &o_xy, &o_oct, &o_xyz, &o_mn, &o_mx, &o_has, &o_out, &o_kp_pt, &o_kp_obs, &o_masked, &o_active};
         for (DevBuf *b : all) b->free();
         chol_plan_destroy(&chol_plan);
         scr.release(); scr2.release();
@@ -729,6 +731,92 @@ extern "C" int ba_set_reduced_system_mode(ba_handle *h, int32_t natural_order, i
     h->natural_tile_order = natural_order != 0;
     h->dense_tiles = dense_tiles != 0;
     h->pairs_built = false;
+    return BA_OK;
+}
+
+// Device-resident outer loop of GlobalBAOptimizerAngles / LocalBAOptimizerAngles::optimizeCamerasAndMapPoints
+// (Optimizer.cpp:222-271, 550-603).  The reference rebuilds the ceres::Problem from the object graph every outer iteration;
+// here the problem set by ba_set_problem stays on the device and every step between two solves is a kernel:
+//   write-back   landmarks -> float32 (Optimizer.cpp:252-258), poses of the written-back cameras -> inverse(f32 extrinsics)
+//                (:262-267); the next build's float -> double / pose -> angle-axis conversion (:282-299) gives the next
+//                initial parameters and the extrinsics a fixed-by-ID camera bakes in
+//   prune        pruneCorrespondences(frame, considerOutlier = false) over ALL keypoints of the problem's cameras (:270, :597-603)
+//   masking      observations whose keypoint became an outlier leave the problem (:308 / :640 isOutlier -> continue); cameras
+//                and landmarks left without observations leave it with them.  No re-upload, no index rebuild.
+extern "C" int ba_solve_outer(ba_handle *h, int32_t n_outer, const uint8_t *cam_writeback, float *pose, const int32_t *frame_ptr,
+                              const float *kp_xy, const int32_t *kp_octave, const int32_t *kp_pt, const float *kp_xyz,
+                              const float *pt_min_dist, const float *pt_max_dist, const uint8_t *has_point, const int32_t *kp_obs,
+                              uint8_t *outlier, float *pt_out, ba_summary *summary) {
+    if (!h || !h->has_problem) return fail(BA_ERR_STATE, "ba_solve_outer before ba_set_problem");
+    if (h->comm) return fail(BA_ERR_STATE, "ba_solve_outer runs on a single GPU (the outer loop's prune walks all keypoints)");
+    if (n_outer < 0 || !cam_writeback || !pose || !frame_ptr) return fail(BA_ERR_INVALID, "bad arguments");
+    CU(cudaSetDevice(h->device));
+    Ctx &ctx = h->ctx;
+    const int Nc = ctx.Nc, Np = ctx.Np, No = ctx.No, n_kp = frame_ptr[Nc];
+    for (int c = 0; c < Nc; ++c)
+        if (frame_ptr[c + 1] < frame_ptr[c]) return fail(BA_ERR_INVALID, "frame_ptr not monotone at %d", c);
+    if (n_kp && (!kp_xy || !kp_octave || !kp_pt || !kp_xyz || !pt_min_dist || !pt_max_dist || !has_point || !kp_obs || !outlier))
+        return fail(BA_ERR_INVALID, "NULL keypoint arrays");
+    for (int i = 0; i < n_kp; ++i)
+        if (kp_obs[i] >= No || kp_pt[i] >= Np) return fail(BA_ERR_INVALID, "keypoint %d references observation %d / landmark %d out of range", i, kp_obs[i], kp_pt[i]);
+    cudaStream_t s = h->stream;
+    int rc;
+    const size_t nk = (size_t)n_kp;
+    if ((rc = upload(h->o_pose, pose, 16 * (size_t)Nc, s))) return rc;
+    if ((rc = upload(h->o_wb, cam_writeback, (size_t)Nc, s))) return rc;
+    if ((rc = upload(h->o_ptr, frame_ptr, (size_t)Nc + 1, s))) return rc;
+    if ((rc = upload(h->o_xy, kp_xy, 2 * nk, s))) return rc;
+    if ((rc = upload(h->o_oct, kp_octave, nk, s))) return rc;
+    if ((rc = upload(h->o_xyz, kp_xyz, 3 * nk, s))) return rc;
+    if ((rc = upload(h->o_mn, pt_min_dist, nk, s))) return rc;
+    if ((rc = upload(h->o_mx, pt_max_dist, nk, s))) return rc;
+    if ((rc = upload(h->o_has, has_point, nk, s))) return rc;
+    if ((rc = upload(h->o_out, outlier, nk, s))) return rc;
+    if ((rc = upload(h->o_kp_pt, kp_pt, nk, s))) return rc;
+    if ((rc = upload(h->o_kp_obs, kp_obs, nk, s))) return rc;
+    CU(h->o_extr.alloc(64 * (size_t)Nc));
+    CU(h->o_pt32.alloc(12 * std::max<size_t>(Np, 1)));
+    CU(h->o_masked.alloc(std::max<size_t>(No, 1)));
+    CU(h->o_active.alloc(4 * (size_t)Nc));
+    CU(cudaMemsetAsync(h->o_masked.p, 0, std::max<size_t>(No, 1), s));
+    CU(cudaStreamSynchronize(s));                      // the caller's arrays may be pageable: uploads done before we go on
+    ba_summary sm;
+    std::memset(&sm, 0, sizeof(sm));
+    int launches = 0;
+    double seconds = 0.0;
+    for (int it = 0; it < n_outer; ++it) {
+        if (it > 0) {
+            // the next problem build: masked observations, cameras without observations, parameters from the float32 state
+            launch_outer_mask(n_kp, h->o_kp_obs.as<int>(), h->o_out.as<uint8_t>(), h->perm_dev.as<int>(), Nc, h->raw_fixed.as<unsigned char>(), No,
+                              ctx.pm_cam, h->o_masked.as<unsigned char>(), h->o_active.as<int>(), h->cam_kind.as<int>(), h->pm_camk.as<unsigned>(), s);
+            ctx.masked = 1;
+            if ((rc = ba_reset_parameters(h))) return rc;                  // x <- cam_init / pt_init (written by the write-back kernels)
+            launch_cam_prep(ctx, 0, 1, s);                                 // fixed cameras' extrinsics changed with their pose round trip
+            launch_cam_prep(ctx, 1, 1, s);
+            launches += 10;
+        }
+        if ((rc = ba_solve(h, &sm))) return rc;
+        launches += h->launches;
+        seconds += sm.seconds_total;
+        LMState st;
+        CU(cudaMemcpy(&st, ctx.state, sizeof(st), cudaMemcpyDeviceToHost));
+        launch_outer_writeback(Nc, h->o_wb.as<unsigned char>(), ctx.cam[st.cur], h->o_pose.as<float>(), ctx.cam_init, h->cam_extr.as<float>(),
+                               3 * (size_t)Np, ctx.pt[st.cur], h->o_pt32.as<float>(), ctx.pt_init, s);
+        if (n_kp) {
+            launch_outer_kp_xyz(n_kp, h->o_kp_pt.as<int>(), h->o_pt32.as<float>(), h->o_xyz.as<float>(), s);
+            launch_pose_inverse(Nc, h->o_pose.as<float>(), h->o_extr.as<float>(), s);       // Optimizer.cpp:10 (all cameras, written back or not)
+            launch_prune(Nc, h->o_pose.as<float>(), h->o_extr.as<float>(), ctx.cam_K, h->o_ptr.as<int>(), h->o_xy.as<float2>(), h->o_oct.as<int>(),
+                         h->o_xyz.as<float>(), h->o_mn.as<float>(), h->o_mx.as<float>(), h->o_has.as<uint8_t>(), h->o_out.as<uint8_t>(), 0, n_kp, s);
+        }
+        launches += 5;
+    }
+    CU(cudaMemcpyAsync(pose, h->o_pose.p, 64 * (size_t)Nc, cudaMemcpyDeviceToHost, s));
+    if (pt_out && Np && n_outer > 0) CU(cudaMemcpyAsync(pt_out, h->o_pt32.p, 12 * (size_t)Np, cudaMemcpyDeviceToHost, s));
+    if (n_kp) CU(cudaMemcpyAsync(outlier, h->o_out.p, nk, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    h->launches = launches;
+    if (summary) { *summary = sm; summary->seconds_total = seconds; }
     return BA_OK;
 }
 

@@ -127,8 +127,10 @@ __device__ __forceinline__ void load_record18(const double *__restrict__ sW, int
     for (int q = 0; q < 9; ++q) { const double2 v = src[q]; w[2 * q] = v.x; w[2 * q + 1] = v.y; }
 }
 
-enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2 };
-// pm_camk word: camera index | kind << 30
+enum : int { CAM_FREE = 0, CAM_FIXED = 1, CAM_INACTIVE = 2, OBS_MASKED = 3 };
+// pm_camk word: camera index | kind << 30.  kind = the camera's CAM_* kind, or OBS_MASKED for an observation that the device-
+// resident outer loop (ba_solve_outer) dropped after pruneCorrespondences flagged its keypoint: it contributes nothing, exactly
+// like a residual block the reference does not add when it rebuilds the problem (Optimizer.cpp:308: isOutlier -> continue).
 __device__ __forceinline__ int camk_cam(unsigned v) { return (int)(v & 0x3fffffffu); }
 __device__ __forceinline__ int camk_kind(unsigned v) { return (int)(v >> 30); }
 

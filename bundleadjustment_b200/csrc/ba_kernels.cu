@@ -143,11 +143,18 @@ __global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kerne
         const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
         const double sp[3] = {ctx.scale_pt[3 * (size_t)p], ctx.scale_pt[3 * (size_t)p + 1], ctx.scale_pt[3 * (size_t)p + 2]};
         double r[2], Jc[12], Jp[6], sc[6];
-        obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp, sc);
-        double rho0;
-        const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
-        const double sr = sqrt(rho1);
-        cost += 0.5 * rho0;
+        double sr = 0.0;
+        if (kind != OBS_MASKED) {
+            obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp, sc);
+            double rho0;
+            const double rho1 = huber_rho(r[0] * r[0] + r[1] * r[1], ctx.opt.huber_delta, ctx.opt.use_huber, rho0);
+            sr = sqrt(rho1);
+            cost += 0.5 * rho0;
+        } else {                                   // dropped by the outer loop's prune: no residual block
+            r[0] = r[1] = 0.0;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) Jp[j] = 0.0;
+        }
         r[0] *= sr; r[1] *= sr;
 #pragma unroll
         for (int j = 0; j < 3; ++j) { const double f = sr * sp[j]; Jp[j] *= f; Jp[3 + j] *= f; }
@@ -191,7 +198,8 @@ __global__ void __launch_bounds__(TILE_THREADS, MIN_CTAS) linearize_points_kerne
 #pragma unroll
             for (int j = 0; j < 3; ++j) b[j] += v[6 + j];
         }
-        if (hi > lo) {
+        // part of the problem = has a residual block; with masked observations (outer loop) that is "some Jp is nonzero"
+        if (hi > lo && (!ctx.masked || V[0] + V[3] + V[5] > 0.0)) {
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
                 const double x = ptx[3 * (size_t)p + j];
@@ -257,7 +265,7 @@ __global__ void __launch_bounds__(CAMS_WARPS * 32, MIN_CTAS) linearize_cams_kern
         const float2 uv = uv_n;
         const double X[3] = {Xn[0], Xn[1], Xn[2]};
         if (e + 32 < end) { uv_n = ctx.cm_uv[e + 32]; load_pt(ptx, (size_t)ctx.cm_pt[e + 32], Xn); }
-        if (e < end) {
+        if (e < end && !(ctx.masked && camk_kind(ctx.pm_camk[ctx.cm_obs[e]]) == OBS_MASKED)) {
             double Jp[6], sc[6];
             obs_linearize<true, false>(ce, CAM_FREE, X, uv, r, Jc, Jp, sc);
             double rho0;
@@ -711,9 +719,11 @@ __global__ void __launch_bounds__(256) eval_candidate_kernel(Ctx ctx, double *pa
     if (o < ctx.No) { ck_n = ctx.pm_camk[o]; p_n = ctx.pm_pt[o]; uv_n = ctx.pm_uv[o]; }
     for (; o < ctx.No; o += stride) {
         const int c = camk_cam(ck_n), p = p_n;
+        const bool live = camk_kind(ck_n) != OBS_MASKED;
         const float2 uv = uv_n;
         const int on = o + stride;
         if (on < ctx.No) { ck_n = ctx.pm_camk[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
+        if (!live) continue;
         double X[3];
         load_pt(ptc, (size_t)p, X);
         double r[2];
@@ -907,7 +917,12 @@ __global__ void __launch_bounds__(EV_WARPS * 32, 5) evaluate_materialize_kernel(
             if (run + nw < n_runs && on < ctx.No) { c_n = ctx.pm_camk[on]; p_n = ctx.pm_pt[on]; uv_n = ctx.pm_uv[on]; }
         }
         double r[2] = {0, 0}, Jc[12], Jp[6], sr = 0.0;
-        if (lane < n) {
+        if (lane < n && kind == OBS_MASKED) {
+#pragma unroll
+            for (int k = 0; k < 12; ++k) Jc[k] = 0.0;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) Jp[k] = 0.0;
+        } else if (lane < n) {
             const double X[3] = {ptx[3 * (size_t)p], ptx[3 * (size_t)p + 1], ptx[3 * (size_t)p + 2]};
             obs_linearize<true, true>(ctx.tab_x + c, kind, X, uv, r, Jc, Jp);
             double rho0;

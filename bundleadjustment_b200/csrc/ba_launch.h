@@ -118,6 +118,12 @@ void launch_pose_to_cam(int F, const float *pose, double *cam, cudaStream_t s); 
 void launch_cam_to_pose(int F, const double *cam, float *pose, float *extr, cudaStream_t s);          // write-back + extr = pose^-1
 void launch_pose_inverse(int F, const float *pose, float *extr, cudaStream_t s);                      // extr = pose^-1 (f32)
 void launch_pose_mask(int n_kp, const uint8_t *has_point, const uint8_t *outlier, uint8_t *mask, const float *xyz, float4 *Xh, cudaStream_t s);
+// device-resident outer loop of Global / Local BA (ba_solve_outer)
+void launch_outer_writeback(int Nc, const unsigned char *wb, const double *cam_cur, float *pose, double *cam_init, float *cam_extr,
+                            size_t n3, const double *pt_cur, float *pt32, double *pt_init, cudaStream_t s);
+void launch_outer_kp_xyz(int n_kp, const int *kp_pt, const float *pt32, float *kp_xyz, cudaStream_t s);
+void launch_outer_mask(int n_kp, const int *kp_obs, const unsigned char *outlier, const int *perm, int Nc, const unsigned char *fixed, int No,
+                       const int *pm_cam, unsigned char *obs_masked, int *cam_active, int *cam_kind, unsigned *pm_camk, cudaStream_t s);
 void launch_prune(int n_frames, const float *pose, const float *extr, const float *K, const int *frame_ptr, const float2 *kp_xy,
                   const int *kp_octave, const float *pt_xyz, const float *pt_min, const float *pt_max,
                   const uint8_t *has_point, uint8_t *outlier, int consider_outlier, int n_kp, cudaStream_t s);

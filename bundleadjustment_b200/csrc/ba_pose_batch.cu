@@ -361,6 +361,84 @@ __global__ void pose_mask_kernel(int n_kp, const uint8_t *__restrict__ has_point
     if (Xh) Xh[i] = make_float4(xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2], 1.0f);
 }
 
+// ---- device-resident outer loop of Global / LocalBAOptimizerAngles (Optimizer.cpp:222-271, 550-603) ------------------------
+// Write-back of one ceres::Solve and the start of the next: per camera with wb[c] != 0 (the frames the reference writes back:
+// its optimised list, frame ID 0 included)  pose = inverse(f32(R(cam), t))  (Optimizer.cpp:262-267), and the next problem build
+// reads that pose again:  extr = pose.inverse() (f32), cam = (angle-axis(extr), t)  (Optimizer.cpp:296-299) -- extr is what a
+// fixed-by-ID camera's point-only residuals bake in.  Cameras with wb == 0 (Local BA's fixed observers) keep pose and extr.
+__global__ void outer_cam_writeback_kernel(int Nc, const unsigned char *__restrict__ wb, const double *__restrict__ cam_cur,
+                                           float *__restrict__ pose, double *__restrict__ cam_init, float *__restrict__ cam_extr) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= Nc || !wb[c]) return;
+    double x[6], y[6];
+    float P[16], E[16];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) x[k] = cam_cur[6 * (size_t)c + k];
+    dev_cam_to_pose(x, P);
+    dev_pose_to_cam(P, y, E);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { pose[16 * (size_t)c + k] = P[k]; cam_extr[16 * (size_t)c + k] = E[k]; }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) cam_init[6 * (size_t)c + k] = y[k];
+}
+// landmarks: MapPoint::setPosition((float) x) (Optimizer.cpp:252-258), read back as double by the next build (:282-289)
+__global__ void outer_pt_writeback_kernel(size_t n3, const double *__restrict__ pt_cur, float *__restrict__ pt32, double *__restrict__ pt_init) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n3) return;
+    const float v = (float)pt_cur[i];
+    pt32[i] = v;
+    pt_init[i] = (double)v;
+}
+// per keypoint: the position pruneCorrespondences sees = the keypoint's map point after the write-back (a problem landmark) or
+// its constant position (a map point outside the problem)
+__global__ void outer_kp_xyz_kernel(int n_kp, const int *__restrict__ kp_pt, const float *__restrict__ pt32, float *__restrict__ kp_xyz) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_kp) return;
+    const int p = kp_pt[i];
+    if (p >= 0) { kp_xyz[3 * (size_t)i] = pt32[3 * (size_t)p]; kp_xyz[3 * (size_t)i + 1] = pt32[3 * (size_t)p + 1]; kp_xyz[3 * (size_t)i + 2] = pt32[3 * (size_t)p + 2]; }
+}
+// observations whose keypoint pruneCorrespondences flagged leave the problem (Optimizer.cpp:308), cameras left without any
+// observation leave it too (ceres: a parameter block without residual blocks is not part of the problem)
+__global__ void outer_mask_obs_kernel(int n_kp, const int *__restrict__ kp_obs, const unsigned char *__restrict__ outlier, const int *__restrict__ perm,
+                                      const int *__restrict__ pm_cam, unsigned char *__restrict__ obs_masked, int *__restrict__ cam_active) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_kp) return;
+    const int o = kp_obs[i];
+    if (o < 0) return;
+    const int e = perm[o];
+    const unsigned char m = outlier[i] ? 1 : 0;
+    obs_masked[e] = m;
+    if (!m) atomicAdd(cam_active + pm_cam[e], 1);
+}
+__global__ void outer_cam_kind_kernel(int Nc, const unsigned char *__restrict__ fixed, const int *__restrict__ cam_active, int *__restrict__ cam_kind) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= Nc) return;
+    cam_kind[c] = cam_active[c] > 0 ? (fixed[c] ? CAM_FIXED : CAM_FREE) : CAM_INACTIVE;
+}
+__global__ void outer_camk_kernel(int No, const int *__restrict__ pm_cam, const int *__restrict__ cam_kind, const unsigned char *__restrict__ obs_masked,
+                                  unsigned *__restrict__ pm_camk) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= No) return;
+    const int c = pm_cam[e];
+    pm_camk[e] = (unsigned)c | ((unsigned)(obs_masked[e] ? OBS_MASKED : cam_kind[c]) << 30);
+}
+
+void launch_outer_writeback(int Nc, const unsigned char *wb, const double *cam_cur, float *pose, double *cam_init, float *cam_extr,
+                            size_t n3, const double *pt_cur, float *pt32, double *pt_init, cudaStream_t s) {
+    if (Nc > 0) outer_cam_writeback_kernel<<<(Nc + 127) / 128, 128, 0, s>>>(Nc, wb, cam_cur, pose, cam_init, cam_extr);
+    if (n3 > 0) outer_pt_writeback_kernel<<<(unsigned)((n3 + 255) / 256), 256, 0, s>>>(n3, pt_cur, pt32, pt_init);
+}
+void launch_outer_kp_xyz(int n_kp, const int *kp_pt, const float *pt32, float *kp_xyz, cudaStream_t s) {
+    if (n_kp > 0) outer_kp_xyz_kernel<<<(n_kp + 255) / 256, 256, 0, s>>>(n_kp, kp_pt, pt32, kp_xyz);
+}
+void launch_outer_mask(int n_kp, const int *kp_obs, const unsigned char *outlier, const int *perm, int Nc, const unsigned char *fixed, int No,
+                       const int *pm_cam, unsigned char *obs_masked, int *cam_active, int *cam_kind, unsigned *pm_camk, cudaStream_t s) {
+    cudaMemsetAsync(cam_active, 0, 4 * (size_t)Nc, s);
+    if (n_kp > 0) outer_mask_obs_kernel<<<(n_kp + 255) / 256, 256, 0, s>>>(n_kp, kp_obs, outlier, perm, pm_cam, obs_masked, cam_active);
+    outer_cam_kind_kernel<<<(Nc + 127) / 128, 128, 0, s>>>(Nc, fixed, cam_active, cam_kind);
+    if (No > 0) outer_camk_kernel<<<(No + 255) / 256, 256, 0, s>>>(No, pm_cam, cam_kind, obs_masked, pm_camk);
+}
+
 void launch_pose_to_cam(int F, const float *pose, double *cam, cudaStream_t s) {
     if (F > 0) pose_to_cam_kernel<<<(F + 127) / 128, 128, 0, s>>>(F, pose, cam);
 }

@@ -99,6 +99,7 @@ struct Ctx {
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
     const int4 *blk_info;    // [n_blocks] {first landmark, end landmark, first observation, observation count}
     int n_blocks, tile_cap;
+    int masked;              // != 0: some observations carry OBS_MASKED (ba_solve_outer after a prune)
     // camera-major copy
     const float2 *cm_uv;
     const int *cm_pt;

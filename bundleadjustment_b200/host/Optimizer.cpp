@@ -192,15 +192,115 @@ bool BAOptimizer::solveOnce(const std::vector<std::shared_ptr<Frame>> &freeFrame
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// the whole outer loop of Global / Local BA (Optimizer.cpp:222-271, 550-603) in ONE device-resident call: the object graph is
+// walked once (problem arrays as in solveOnce + one record per keypoint of every frame for pruneCorrespondences), then
+// ba_set_problem + ba_solve_outer, then ONE write-back through the setters.  Between outer iterations nothing crosses PCIe and
+// no index is rebuilt; a concurrent viewer thread sees the final state instead of every intermediate one.
+// ------------------------------------------------------------------------------------------------------------
+bool BAOptimizer::solveOuter(const std::vector<std::shared_ptr<Frame>> &freeFrames, const std::vector<std::shared_ptr<Frame>> &fixedFrames,
+                             const std::vector<std::shared_ptr<MapPoint>> &points, unsigned nOuter) {
+    const int nFree = (int)freeFrames.size(), nFixed = (int)fixedFrames.size();
+    const int Nc = nFree + nFixed, Np = (int)points.size();
+    if (Nc == 0 || nOuter == 0) return true;
+    std::unordered_map<const MapPoint *, int> pointIndex;
+    pointIndex.reserve((size_t)Np * 2);
+    std::vector<double> pt(3 * (size_t)std::max(Np, 1));
+    for (int i = 0; i < Np; ++i) {
+        const Vector3f p = points[i]->getPosition();                       // Optimizer.cpp:282-289
+        pt[3 * (size_t)i] = (double)p(0); pt[3 * (size_t)i + 1] = (double)p(1); pt[3 * (size_t)i + 2] = (double)p(2);
+        pointIndex.emplace(points[i].get(), i);
+    }
+    std::vector<double> cam(6 * (size_t)Nc);
+    std::vector<uint8_t> camFixed(Nc, 0), writeBack(Nc, 0);
+    std::vector<float> pose(16 * (size_t)Nc), extr(16 * (size_t)Nc), K(9 * (size_t)Nc);
+    std::vector<int32_t> obsCam, obsPt, framePtr(Nc + 1, 0), kpOctave, kpPt, kpObs;
+    std::vector<float> obsUv, kpXy, kpXyz, kpMin, kpMax;
+    std::vector<uint8_t> kpHas, kpOut;
+    for (int i = 0; i < Nc; ++i) {
+        const bool isFixedList = i >= nFree;
+        const std::shared_ptr<Frame> &frame = isFixedList ? fixedFrames[i - nFree] : freeFrames[i];
+        toRowMajor4(frame->getPose(), &pose[16 * (size_t)i]);
+        ba_pose_to_cam(&pose[16 * (size_t)i], &cam[6 * (size_t)i], &extr[16 * (size_t)i]);       // Optimizer.cpp:296-299
+        toRowMajor3(frame->getIntrinsics(), &K[9 * (size_t)i]);
+        camFixed[i] = (isFixedList || frame->getID() == 0) ? 1 : 0;                              // Optimizer.cpp:315-321
+        writeBack[i] = isFixedList ? 0 : 1;                                                      // Optimizer.cpp:260-267
+        const std::vector<std::shared_ptr<MapPoint>> visible = frame->getMapPoints();
+        const int cnt = frame->getKeypointCount();
+        for (int j = 0; j < cnt; ++j) {
+            const cv::KeyPoint *kp = frame->getKeypoint(j);
+            const std::shared_ptr<MapPoint> mp = j < (int)visible.size() ? visible[j] : nullptr;
+            const bool out = frame->isOutlier(j);
+            kpXy.push_back(kp->pt.x); kpXy.push_back(kp->pt.y);
+            kpOctave.push_back(kp->octave);
+            kpOut.push_back(out ? 1 : 0);
+            int pIdx = -1, oIdx = -1;
+            float xyz[3] = {0.f, 0.f, 0.f}, mn = 0.f, mx = 0.f;
+            if (mp) {
+                const Vector3f p = mp->getPosition();
+                xyz[0] = p(0); xyz[1] = p(1); xyz[2] = p(2);
+                mn = mp->getMinDistance(); mx = mp->getMaxDistance();
+                auto it = pointIndex.find(mp.get());
+                if (it != pointIndex.end()) {
+                    pIdx = it->second;
+                    if (!out) {                                          // a residual block of the problem (Optimizer.cpp:308-328)
+                        const Vector2f uv = mp->getCorresponding2DKeyPointPosition(frame);
+                        oIdx = (int)obsCam.size();
+                        obsCam.push_back(i); obsPt.push_back(pIdx);
+                        obsUv.push_back(uv(0)); obsUv.push_back(uv(1));
+                    }
+                }
+            }
+            kpHas.push_back(mp ? 1 : 0);
+            kpPt.push_back(pIdx); kpObs.push_back(oIdx);
+            kpXyz.push_back(xyz[0]); kpXyz.push_back(xyz[1]); kpXyz.push_back(xyz[2]);
+            kpMin.push_back(mn); kpMax.push_back(mx);
+        }
+        framePtr[i + 1] = (int32_t)kpOut.size();
+    }
+    const int No = (int)obsCam.size();
+    ba_handle *h = handle();
+    if (!h) return false;
+    ba_options opt;
+    ba_default_options(&opt);                       // configureSolver (Optimizer.cpp:80-90) + Ceres defaults
+    opt.max_num_iterations = (int32_t)m_nMaxItPerBA;
+    if (fail(ba_set_options(h, &opt))) return false;
+    if (fail(ba_set_problem(h, Nc, cam.data(), camFixed.data(), extr.data(), K.data(), Np, pt.data(), No, obsCam.data(),
+                            obsPt.data(), obsUv.data())))
+        return false;
+    std::vector<uint8_t> before(kpOut);
+    std::vector<float> pt32(3 * (size_t)std::max(Np, 1));
+    ba_summary sm;
+    if (fail(ba_solve_outer(h, (int32_t)nOuter, writeBack.data(), pose.data(), framePtr.data(), kpXy.data(), kpOctave.data(), kpPt.data(),
+                            kpXyz.data(), kpMin.data(), kpMax.data(), kpHas.data(), kpObs.data(), kpOut.data(), pt32.data(), &sm)))
+        return false;
+    m_lastTermination = sm.termination_type;
+    m_lastInitialCost = sm.initial_cost;
+    m_lastFinalCost = sm.final_cost;
+    m_lastNumIterations = sm.num_iterations;
+    for (int i = 0; i < Np; ++i) {                                       // Optimizer.cpp:252-258
+        Vector3f p;
+        p(0) = pt32[3 * (size_t)i]; p(1) = pt32[3 * (size_t)i + 1]; p(2) = pt32[3 * (size_t)i + 2];
+        points[i]->setPosition(p);
+    }
+    for (int i = 0; i < nFree; ++i) freeFrames[i]->setPose(fromRowMajor4(&pose[16 * (size_t)i]));      // Optimizer.cpp:260-267
+    for (int i = 0; i < Nc; ++i) {                                       // pruneCorrespondences' verdicts (Optimizer.cpp:270, 597-603)
+        const std::shared_ptr<Frame> &frame = i >= nFree ? fixedFrames[i - nFree] : freeFrames[i];
+        for (int j = 0, cnt = framePtr[i + 1] - framePtr[i]; j < cnt; ++j) {
+            const size_t k = (size_t)framePtr[i] + j;
+            if (kpOut[k] == before[k]) continue;
+            if (kpOut[k]) frame->setOutlier(j); else frame->setInlier(j);
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // GlobalBAOptimizerAngles (Optimizer.cpp:216-277)
 // ------------------------------------------------------------------------------------------------------------
 void GlobalBAOptimizerAngles::optimizeCamerasAndMapPoints(SceneMap *optimizedMap, bool eraseOutliers, int currentFrameID) {
     auto frames = optimizedMap->getKeyFrames();
     auto points = optimizedMap->getMapPoints();
-    for (unsigned i = 0; i < m_nIterations; ++i) {
-        if (!solveOnce(frames, {}, points, false)) break;
-        pruneCorrespondences(frames, false);          // Optimizer.cpp:270, per frame in the reference
-    }
+    solveOuter(frames, {}, points, m_nIterations);   // m_nIterations x { Solve, write-back, prune } (Optimizer.cpp:222-271), on the device
     if (eraseOutliers) SfMHelper::getInstance()->eraseOutlier(optimizedMap, currentFrameID);
 }
 
@@ -231,12 +331,7 @@ void LocalBAOptimizerAngles::optimizeCamerasAndMapPoints(SceneMap *optimizedMap,
             if (seenFrame.emplace(kv.first.get(), 1).second) fixedFrames.push_back(kv.first);
         }
     }
-    for (unsigned i = 0; i < m_nIterations; ++i) {
-        if (!solveOnce(localFrames, fixedFrames, localMapPoints, true)) break;
-        std::vector<std::shared_ptr<Frame>> all(localFrames);
-        all.insert(all.end(), fixedFrames.begin(), fixedFrames.end());
-        pruneCorrespondences(all, false);            // Optimizer.cpp:597-603
-    }
+    solveOuter(localFrames, fixedFrames, localMapPoints, m_nIterations);   // Optimizer.cpp:550-603, on the device
     if (eraseOutliers) SfMHelper::getInstance()->eraseOutlier(optimizedMap, currentFrame->getID());
 }
 

@@ -57,7 +57,12 @@ protected:
     bool fail(int status);
     ba_handle *handle();
 
-    /** Shared by Global and Local BA: flatten (free frames | fixed frames | points) -> solve -> write back. */
+    /** Shared by Global and Local BA: the WHOLE outer loop (nOuter x { solve, write-back, prune }) in one device-resident call
+     *  (ba_set_problem + ba_solve_outer); the object graph is read once and written once. */
+    bool solveOuter(const std::vector<std::shared_ptr<Frame>> &freeFrames, const std::vector<std::shared_ptr<Frame>> &fixedFrames,
+                    const std::vector<std::shared_ptr<MapPoint>> &points, unsigned nOuter);
+    /** One outer iteration on the host side of the boundary: flatten (free frames | fixed frames | points) -> solve -> write back
+     *  (kept for callers that interleave their own work between outer iterations). */
     bool solveOnce(const std::vector<std::shared_ptr<Frame>> &freeFrames, const std::vector<std::shared_ptr<Frame>> &fixedFrames,
                    const std::vector<std::shared_ptr<MapPoint>> &points, bool fixedOnlyKnownPoints);
 };

@@ -126,6 +126,24 @@ int ba_get_cameras(ba_handle *h, double *cam /* 6*n_cam */);
 int ba_get_points(ba_handle *h, double *pt /* 3*n_pt */);
 int ba_get_iterations(ba_handle *h, ba_iteration *iters, int32_t cap, int32_t *n_written);
 
+/* ---- the OUTER loop of Global / LocalBAOptimizerAngles::optimizeCamerasAndMapPoints (Optimizer.cpp:222-271, 550-603), ----
+ * device-resident: n_outer x { ba_solve -> write-back (landmarks to float32, Optimizer.cpp:252-258; poses of the cameras with
+ * cam_writeback != 0 -- the optimised frame list, frame ID 0 included -- to inverse(f32 extrinsics), :262-267) ->
+ * pruneCorrespondences(frame, considerOutlier = false) over ALL keypoints of the problem's cameras (:270, :597-603) -> the
+ * observations whose keypoint became an outlier leave the problem (:308) }.  The problem set by ba_set_problem stays on the
+ * device: no re-upload and no index rebuild between outer iterations (masking, not re-sorting).
+ *   pose[16 Nc]      camera->world f32 row-major of every camera of the problem, in/out
+ *   frame_ptr[Nc+1]  camera c owns keypoints [frame_ptr[c], frame_ptr[c+1]) -- ALL its keypoints, as in ba_prune_frames
+ *   kp_pt            problem landmark of the keypoint's map point, -1 when it has none or it is not a problem landmark
+ *   kp_xyz           map point position (f32) of keypoints with has_point != 0 and kp_pt < 0 (constant during the call)
+ *   kp_obs           index of the keypoint's observation in the ba_set_problem arrays, -1 when it is not an observation
+ *   outlier          in/out;  pt_out[3 Np] (may be NULL): landmarks as float32;  summary: the LAST solve, seconds = all solves
+ * Single GPU only.  Afterwards the handle holds the masked problem; call ba_set_problem for the next one. */
+int ba_solve_outer(ba_handle *h, int32_t n_outer, const uint8_t *cam_writeback, float *pose, const int32_t *frame_ptr,
+                   const float *kp_xy, const int32_t *kp_octave, const int32_t *kp_pt, const float *kp_xyz,
+                   const float *pt_min_dist, const float *pt_max_dist, const uint8_t *has_point, const int32_t *kp_obs,
+                   uint8_t *outlier, float *pt_out, ba_summary *summary);
+
 /* ---- materialised evaluation at the current parameters (tests + the obs/sec metric) -------------------- *
  * Robustified exactly like Ceres' ResidualBlock::Evaluate + Corrector.  Outputs are in the CALLER's
  * observation order; any pointer may be NULL.  jac_cam rows of point-only blocks are zero. */

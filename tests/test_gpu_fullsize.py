@@ -99,15 +99,15 @@ def _solve_both(bab, orc, pb, max_it, label, threads=None, oracle_kw=None, **kw)
     return (sm, its, cam, pt), (osm, oits, ocam, opt_)
 
 
-def _full_check(orc, pb, g, o, label):
+def _full_check(orc, pb, g, o, label, final_rtol=1e-8, cam_atol=1e-6):
     (sm, its, cam, pt), (osm, oits, ocam, opt_) = g, o
     worst = _traj_check(its, oits)
     rel = abs(sm.final_cost - osm.final_cost) / osm.final_cost
     print(f"[{label}] trajectory max rel diff {worst:.3e}; final cost rel diff {rel:.3e}; max camera diff {np.abs(cam - ocam).max():.3e}")
     assert sm.termination_type == osm.termination_type
-    assert rel <= 1e-8
+    assert rel <= final_rtol
     assert abs(sm.initial_cost - osm.initial_cost) <= 1e-12 * osm.initial_cost
-    assert np.abs(cam - ocam).max() <= 1e-6
+    assert np.abs(cam - ocam).max() <= cam_atol
     check_landmarks(orc, pb, pt, opt_, ocam, oits[-1]["trust_region_radius"], label, dcam=float(np.abs(cam - ocam).max()))
 
 
@@ -119,7 +119,9 @@ def _pcg_checks(bab, orc, pb, max_it, label):
     import os
     g, o = _solve_both(bab, orc, pb, max_it, label + " fixed-CG", threads=os.cpu_count(), **FIXED_CG)
     assert [i["linear_solver_iterations"] for i in g[1]] == [i["linear_solver_iterations"] for i in o[1]]
-    _full_check(orc, pb, g, o, label + " fixed-CG")
+    # 25 CG iterations leave the linear solve far from converged: the step is a polynomial of degree 25 in S, which amplifies the
+    # rounding differences of the two matvecs; the trajectory still has to agree to 1e-6, the end point to 1e-6 / 1e-5
+    _full_check(orc, pb, g, o, label + " fixed-CG", final_rtol=1e-6, cam_atol=1e-5)
     g, o = _solve_both(bab, orc, pb, max_it, label + " ceres-rule", threads=os.cpu_count(), linear_solver=1)
     (sm, its, cam, pt), (osm, oits, ocam, opt_) = g, o
     assert len(its) == len(oits)
