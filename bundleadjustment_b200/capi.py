@@ -20,7 +20,7 @@ EXPORTS = [
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
     "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
     "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile", "ba_set_reduced_system_mode",
-    "ba_solve_pose_only_outer", "ba_solve_outer", "ba_release_workspace", "ba_workspace_launch_count",
+    "ba_solve_pose_only_outer", "ba_solve_outer", "ba_set_reduced_system_tile", "ba_dense_spd_solve_tile", "ba_release_workspace", "ba_workspace_launch_count",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
     "ba_pose_to_cam", "ba_cam_to_pose",
 ]
@@ -73,6 +73,7 @@ lib.ba_tile_elimination_order.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c
 lib.ba_get_kernel_profile.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_get_reduced_system_stats.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_dense_spd_solve.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+lib.ba_dense_spd_solve_tile.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
 lib.ba_schur_system.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
 
 
@@ -156,6 +157,10 @@ class Solver:
     def set_reduced_system_mode(self, natural_order: bool = False, dense_tiles: bool = False):
         """Explicit (never environment-driven) switches of the reduced-system factorisation; call before set_problem."""
         _check(lib.ba_set_reduced_system_mode(self._h, int(natural_order), int(dense_tiles)), "ba_set_reduced_system_mode")
+
+    def set_reduced_system_tile(self, tile_edge: int = 0):
+        """Cholesky tile edge of the reduced system: 0 = automatic, 64 or 128 = forced."""
+        _check(lib.ba_set_reduced_system_tile(self._h, int(tile_edge)), "ba_set_reduced_system_tile")
 
     def set_profiling(self, on: bool = True):
         _check(lib.ba_set_profiling(self._h, int(on)), "ba_set_profiling")
@@ -289,11 +294,12 @@ def workspace_launch_count(device: int = 0) -> int:
     return int(lib.ba_workspace_launch_count(int(device)))
 
 
-def dense_spd_solve(A, b, device: int = 0, repeats: int = 1):
+def dense_spd_solve(A, b, device: int = 0, repeats: int = 1, tile_edge: int = 0):
+    """tile_edge: 0 = automatic (by the tile sparsity of A), 64 / 128 = that instantiation of the Cholesky kernel"""
     A = np.ascontiguousarray(A, np.float64); b = np.ascontiguousarray(b, np.float64)
     x = np.zeros_like(b)
     ms = C.c_float(0)
-    _check(lib.ba_dense_spd_solve(device, A.shape[0], _ptr(A), _ptr(b), _ptr(x), C.addressof(ms), repeats), "ba_dense_spd_solve")
+    _check(lib.ba_dense_spd_solve_tile(device, A.shape[0], _ptr(A), _ptr(b), _ptr(x), C.addressof(ms), repeats, int(tile_edge)), "ba_dense_spd_solve")
     return x, float(ms.value)
 
 

@@ -96,6 +96,7 @@ struct ba_handle {
     PrepOut prep_out;
     bool pairs_built = false;
     bool natural_tile_order = false, dense_tiles = false;   // ba_set_reduced_system_mode (explicit API, never the environment)
+    int tile_edge = 0, tile_nb = 128;                       // requested (0 = automatic) / chosen Cholesky tile edge
     CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
     DevBuf tile_map, cam_row, row_src, yperm;
     int *h_prep = nullptr;           // pinned [8]
@@ -260,11 +261,6 @@ int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
 }
 
 int ensure_dense(ba_handle *h) {
-    // padded reduced system: one 128-row Cholesky tile per group of CAMS_PER_TILE consecutive cameras
-    const int G = (h->ctx.Nc + CAMS_PER_TILE - 1) / CAMS_PER_TILE;
-    const int n = G * CHOL_NB;
-    h->ctx.ldS = n;
-    h->ctx.S_T = G;
     if (!h->pairs_built) {
         // camera-pair-major index for the deterministic Schur reduction (device-side, once per problem)
         cudaStream_t s = h->stream;
@@ -290,13 +286,32 @@ int ensure_dense(ba_handle *h) {
         // (the sort scratch stays allocated: cudaFree + cudaMalloc of it cost up to 100 ms per ba_set_problem)
         // which camera groups share landmarks (union over ranks) -> elimination order of the tiles (nested dissection),
         // row layout of S, tile-level symbolic factorisation
-        CU(h->tile_map.alloc((size_t)G * G));
-        if ((rc = prep_group_map(pi, G, h->tile_map.as<unsigned char>(), s)))
-            return fail(BA_ERR_CUDA, "prep_group_map: %s", cudaGetErrorString((cudaError_t)rc));
-        if (h->comm) NC(ncclAllReduce(h->tile_map.p, h->tile_map.p, (size_t)G * G, ncclUint8, ncclMax, h->comm, s));
-        std::vector<unsigned char> adj((size_t)G * G);
-        CU(cudaMemcpyAsync(adj.data(), h->tile_map.p, adj.size(), cudaMemcpyDeviceToHost, s));
-        CU(cudaStreamSynchronize(s));
+        // Tile edge: 64-row tiles (10 cameras each) when the co-visibility leaves most of S empty -- the factorisation is then a
+        // dependency chain along the nested-dissection separators, and the chain is much shorter in 64-row links -- else 128-row
+        // tiles (21 cameras), which run a dense matrix at 67 % of the FP64 GEMM rate.  ba_set_reduced_system_tile overrides.
+        int nb = h->tile_edge ? h->tile_edge : 64;
+        if (h->dense_tiles && !h->tile_edge) nb = 128;
+        int G = 0, n = 0;
+        std::vector<unsigned char> adj;
+        for (;;) {
+            const int cpt = cams_per_tile(nb);
+            G = (h->ctx.Nc + cpt - 1) / cpt;
+            n = G * nb;
+            CU(h->tile_map.alloc((size_t)G * G));
+            if ((rc = prep_group_map(pi, G, cpt, h->tile_map.as<unsigned char>(), s)))
+                return fail(BA_ERR_CUDA, "prep_group_map: %s", cudaGetErrorString((cudaError_t)rc));
+            if (h->comm) NC(ncclAllReduce(h->tile_map.p, h->tile_map.p, (size_t)G * G, ncclUint8, ncclMax, h->comm, s));
+            adj.resize((size_t)G * G);
+            CU(cudaMemcpyAsync(adj.data(), h->tile_map.p, adj.size(), cudaMemcpyDeviceToHost, s));
+            CU(cudaStreamSynchronize(s));
+            if (nb == 128 || h->tile_edge) break;
+            long long nnz = 0;
+            for (int gi = 0; gi < G; ++gi)
+                for (int gj = 0; gj <= gi; ++gj) nnz += (gi == gj || adj[(size_t)gi * G + gj]) ? 1 : 0;
+            if (2 * nnz <= (long long)G * (G + 1) / 2 / 2) break;           // at most a quarter of the lower tiles are touched: sparse
+            nb = 128;                                                        // (the same on every rank: adj is the union over ranks)
+        }
+        h->tile_nb = nb;
         std::vector<int> order;
         if (h->natural_tile_order) { order.resize(G); std::iota(order.begin(), order.end(), 0); }   // ba_set_reduced_system_mode
         else chol_tile_order(G, adj.data(), order);
@@ -305,7 +320,7 @@ int ensure_dense(ba_handle *h) {
         for (int p = 0; p < G; ++p) pos[order[p]] = p;
         std::vector<int> cam_row(h->ctx.Nc), row_src((size_t)n, -1);
         for (int c = 0; c < h->ctx.Nc; ++c) {
-            cam_row[c] = CHOL_NB * pos[c / CAMS_PER_TILE] + 6 * (c % CAMS_PER_TILE);
+            cam_row[c] = nb * pos[c / cams_per_tile(nb)] + 6 * (c % cams_per_tile(nb));
             for (int a = 0; a < 6; ++a) row_src[(size_t)cam_row[c] + a] = 6 * c + a;
         }
         if ((rc = upload(h->cam_row, cam_row.data(), cam_row.size(), s))) return rc;
@@ -317,14 +332,18 @@ int ensure_dense(ba_handle *h) {
         CU(cudaStreamSynchronize(s));                                    // the uploads read the host vectors above
         // ba_set_reduced_system_mode(dense_tiles): treat every tile as filled (what Ceres' DENSE_SCHUR does).  The plan also fixes
         // the STORAGE of S: [tiles a camera pair can touch | reduced rhs (6 Nc, camera order) | fill-in tiles | rhs tiles].
-        if ((rc = chol_plan_create(n, h->dense_tiles ? nullptr : nz.data(), &h->chol_plan, s, (size_t)h->ctx.n)))
+        if ((rc = chol_plan_create(n, nb, h->dense_tiles ? nullptr : nz.data(), &h->chol_plan, s, (size_t)h->ctx.n)))
             return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
         CU(h->S.alloc(sizeof(double) * (size_t)h->chol_plan.total_doubles));
-        CU(h->invL.alloc(sizeof(double) * chol_work_doubles(n)));
-        CU(cudaMemsetAsync(h->invL.p, 0, sizeof(double) * chol_work_doubles(n), s));    // the kernel only ever writes the lower triangles of L_jj^-1
+        CU(h->invL.alloc(sizeof(double) * chol_work_doubles(n, nb)));
+        CU(cudaMemsetAsync(h->invL.p, 0, sizeof(double) * chol_work_doubles(n, nb), s));    // the kernel only ever writes the lower triangles of L_jj^-1
         CU(h->yperm.alloc(sizeof(double) * (size_t)n));
         h->pairs_built = true;
     }
+    h->ctx.S_nb = h->tile_nb;
+    h->ctx.S_shift = h->tile_nb == 128 ? 7 : 6;
+    h->ctx.S_T = h->chol_plan.T;
+    h->ctx.ldS = h->chol_plan.T * h->tile_nb;
     h->ctx.S = h->S.as<double>();
     h->ctx.S_toff = h->chol_plan.tile_off;
     h->ctx.cam_row = h->cam_row.as<int>();
@@ -820,6 +839,16 @@ extern "C" int ba_solve_outer(ba_handle *h, int32_t n_outer, const uint8_t *cam_
     return BA_OK;
 }
 
+// Cholesky tile edge of the reduced system: 0 = automatic (64-row tiles for tile-sparse systems, 128-row tiles otherwise), 64 or
+// 128 = forced.  Takes effect at the next solve (the plan is rebuilt).
+extern "C" int ba_set_reduced_system_tile(ba_handle *h, int32_t tile_edge) {
+    if (!h) return fail(BA_ERR_INVALID, "handle is NULL");
+    if (tile_edge != 0 && tile_edge != 64 && tile_edge != 128) return fail(BA_ERR_INVALID, "tile_edge must be 0, 64 or 128");
+    h->tile_edge = tile_edge;
+    h->pairs_built = false;
+    return BA_OK;
+}
+
 extern "C" int ba_get_launch_count(ba_handle *h) { return h ? h->launches : 0; }
 extern "C" int ba_set_profiling(ba_handle *h, int32_t on) {
     if (!h) return fail(BA_ERR_INVALID, "handle is NULL");
@@ -985,8 +1014,9 @@ extern "C" int ba_schur_system(ba_handle *h, double radius, double *S, double *r
         CU(cudaMemcpy(Sp.data(), ctx.S, 8 * Sp.size(), cudaMemcpyDeviceToHost));
         CU(cudaMemcpy(cam_row.data(), ctx.cam_row, 4 * (size_t)ctx.Nc, cudaMemcpyDeviceToHost));
         const auto at = [&](size_t r, size_t q) -> double {                  // element (r, q) of the tile-packed lower triangle
-            const long long o = pl.h_tile_off[(r / CHOL_NB) * (size_t)pl.T + q / CHOL_NB];
-            return o < 0 ? 0.0 : Sp[(size_t)o + (r % CHOL_NB) * CHOL_NB + q % CHOL_NB];
+            const size_t nb = (size_t)pl.nb;
+            const long long o = pl.h_tile_off[(r / nb) * (size_t)pl.T + q / nb];
+            return o < 0 ? 0.0 : Sp[(size_t)o + (r % nb) * nb + q % nb];
         };
         std::memset(S, 0, 8 * n * n);
         for (int ci = 0; ci < ctx.Nc; ++ci)
@@ -1045,8 +1075,8 @@ extern "C" int ba_tile_elimination_order(int32_t G, const uint8_t *adj, int32_t 
                 }
         int d0 = 0, d1 = 0;
         long long f0 = 0, f1 = 0;
-        chol_plan_stats(G * CHOL_NB, nat.data(), &d0, &f0, nullptr);
-        chol_plan_stats(G * CHOL_NB, per.data(), &d1, &f1, nullptr);
+        chol_plan_stats(G * 128, 128, nat.data(), &d0, &f0, nullptr);
+        chol_plan_stats(G * 128, 128, per.data(), &d1, &f1, nullptr);
         stats[0] = d0; stats[1] = d1; stats[2] = (double)f0; stats[3] = (double)f1;
     }
     return BA_OK;
@@ -1054,30 +1084,49 @@ extern "C" int ba_tile_elimination_order(int32_t G, const uint8_t *adj, int32_t 
 
 // Dense SPD solve utility: exposes the reduced-system Cholesky on its own (tests, micro-benchmarks).
 // A: n x n row-major (lower triangle read), b: n.  x: n.  ms (optional): device time of factor + solve.
+static int dense_spd_solve_impl(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats, int tile_edge);
 extern "C" int ba_dense_spd_solve(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats) {
+    return dense_spd_solve_impl(device, n, A, b, x, ms, repeats, 0);
+}
+// tile_edge: 0 = automatic (by the tile sparsity of A), 64 or 128 = forced (tests exercise both instantiations of the kernel)
+extern "C" int ba_dense_spd_solve_tile(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats, int32_t tile_edge) {
+    if (tile_edge != 0 && tile_edge != 64 && tile_edge != 128) return fail(BA_ERR_INVALID, "tile_edge must be 0, 64 or 128");
+    return dense_spd_solve_impl(device, n, A, b, x, ms, repeats, tile_edge);
+}
+static int dense_spd_solve_impl(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats, int tile_edge) {
     if (n <= 0 || !A || !b || !x) return fail(BA_ERR_INVALID, "bad arguments");
     int rc = check_device(device);
     if (rc) return rc;
     int e0 = chol_init();
     if (e0) return fail(BA_ERR_CUDA, "chol_init: %s", cudaGetErrorString((cudaError_t)e0));
-    const int np = chol_ld(n);
-    // tile pattern of the caller's matrix (exact zeros only) -> the same sparsity plan (and tile-packed storage) the LM loop uses
-    const int T = np / CHOL_NB;
-    std::vector<unsigned char> nz((size_t)T * T, 0);
-    for (int i = 0; i < n; ++i) {
-        const double *row = A + (size_t)i * n;
-        for (int j = 0; j <= i; ++j) if (row[j] != 0.0) nz[(size_t)(i / CHOL_NB) * T + j / CHOL_NB] = 1;
+    // tile pattern of the caller's matrix (exact zeros only) -> the same sparsity plan (and tile-packed storage) the LM loop uses;
+    // 64-row tiles when at most a quarter of the lower tiles are touched, like ensure_dense
+    int nb = tile_edge == 64 || tile_edge == 128 ? tile_edge : 64;
+    std::vector<unsigned char> nz;
+    int np = 0;
+    for (;;) {
+        np = chol_ld(n, nb);
+        const int T = np / nb;
+        nz.assign((size_t)T * T, 0);
+        for (int i = 0; i < n; ++i) {
+            const double *row = A + (size_t)i * n;
+            for (int j = 0; j <= i; ++j) if (row[j] != 0.0) nz[(size_t)(i / nb) * T + j / nb] = 1;
+        }
+        long long nnz = 0;
+        for (int i = 0; i < T; ++i) for (int j = 0; j <= i; ++j) nnz += (i == j || nz[(size_t)i * T + j]) ? 1 : 0;
+        if (nb == 128 || tile_edge || 2 * nnz <= (long long)T * (T + 1) / 2 / 2) break;
+        nb = 128;
     }
     CholPlan plan;
-    if ((rc = chol_plan_create(n, nz.data(), &plan, 0))) return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
+    if ((rc = chol_plan_create(n, nb, nz.data(), &plan, 0))) return fail(BA_ERR_CUDA, "chol_plan_create: %s", cudaGetErrorString((cudaError_t)rc));
     std::vector<double> Ah;
     chol_pack_host(&plan, A, b, Ah);
     DevBuf dA, dA0, dInv, dY, dFail;
     CU(dA.alloc(8 * Ah.size())); CU(dA0.alloc(8 * Ah.size()));
-    CU(dInv.alloc(8 * chol_work_doubles(n))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
+    CU(dInv.alloc(8 * chol_work_doubles(n, nb))); CU(dY.alloc(8 * (size_t)np)); CU(dFail.alloc(4));
     CU(cudaMemcpy(dA0.p, Ah.data(), 8 * Ah.size(), cudaMemcpyHostToDevice));
     CU(cudaMemset(dFail.p, 0, 4));
-    CU(cudaMemset(dInv.p, 0, 8 * chol_work_doubles(n)));
+    CU(cudaMemset(dInv.p, 0, 8 * chol_work_doubles(n, nb)));
     cudaEvent_t e1, e2;
     CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
     if (repeats < 1) repeats = 1;

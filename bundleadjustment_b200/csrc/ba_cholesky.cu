@@ -34,32 +34,41 @@
 
 namespace ba {
 
-constexpr int NB = CHOL_NB;            // 128: tile edge
 constexpr int BK = 32;                 // k-slice of the cp.async ring
 constexpr int SPAD = BK + 4;           // 36 doubles: row stride == 4 (mod 16) -> conflict-free DMMA fragment loads
 constexpr int NSTAGE = 3;
-constexpr int KSL = NB / BK;           // k-slices per 128-column block
-constexpr int LDT = NB + 4;            // 132: stride of the staged C tile, same conflict-free property
 constexpr int PB = 32;                 // potrf panel width (warp-register base case)
 constexpr int LDP = PB + 4;            // 36
 
-constexpr int STAGE_DOUBLES = 2 * NB * SPAD;                       // A slice + B slice
-constexpr int TILE_DOUBLES = NB * LDT;                             // 16896
-constexpr int RING_DOUBLES = NSTAGE * STAGE_DOUBLES;               // 27648
-// Shared memory: [C tile | scratch].  The main-loop ring overlays both; after it the scratch holds either the TRSM's
-// 2-stage ring of L_jj^-1 slices or the potrf work arrays (Pv | invd | dinv).
-constexpr int SCRATCH_DOUBLES = 2 * NB * SPAD;                     // 9216 >= 128*36 + 32*36 + 128
-constexpr int SMEM_DOUBLES = (TILE_DOUBLES + SCRATCH_DOUBLES > RING_DOUBLES) ? TILE_DOUBLES + SCRATCH_DOUBLES : RING_DOUBLES;
-static_assert(NB * LDP + PB * LDP + NB <= SCRATCH_DOUBLES, "potrf scratch must fit");
-constexpr int CHOL_SMEM = SMEM_DOUBLES * (int)sizeof(double);      // 221184 B
-static_assert(CHOL_SMEM <= 227 * 1024, "shared memory budget");
+// Tile edge NB is a template parameter: 128 for (near-)dense reduced systems (highest arithmetic intensity: 67 % of the FP64
+// GEMM rate on a dense matrix), 64 for tile-sparse ones.  A sparse factorisation is a CHAIN of potrf -> trsm -> update tasks
+// along the nested-dissection separators; per 128 rows of that chain a 64-row tiling pays two links of 1/4 .. 1/8 the work each
+// instead of one (measured on K4: tools/chol_chain), so the chain -- the whole kernel there -- gets markedly shorter.
+template <int NB_>
+struct ChCfg {
+    static constexpr int NB = NB_;
+    static constexpr int KSL = NB / BK;                    // k-slices per tile
+    static constexpr int LDT = NB + 4;                     // stride of the staged C tile (conflict-free like SPAD)
+    static constexpr int MI = NB / 16, NJ = NB / 32;       // m8 x n8 DMMA tiles per warp: 8 warps as 2 x 4, warp tile (NB/2) x (NB/4)
+    static constexpr int STAGE_DOUBLES = 2 * NB * SPAD;    // A slice + B slice
+    static constexpr int TILE_DOUBLES = NB * LDT;
+    static constexpr int RING_DOUBLES = NSTAGE * STAGE_DOUBLES;
+    // Shared memory: [C tile | scratch].  The main-loop ring overlays both; after it the scratch holds either the TRSM's
+    // 2-stage ring of L_jj^-1 slices or the potrf work arrays (Pv | invd | dinv).
+    static constexpr int SCRATCH_DOUBLES = 2 * NB * SPAD;
+    static constexpr int SMEM_DOUBLES = (TILE_DOUBLES + SCRATCH_DOUBLES > RING_DOUBLES) ? TILE_DOUBLES + SCRATCH_DOUBLES : RING_DOUBLES;
+    static constexpr int SMEM = SMEM_DOUBLES * (int)sizeof(double);
+    static_assert(NB * LDP + PB * LDP + NB <= SCRATCH_DOUBLES, "potrf scratch must fit");
+    static_assert(SMEM <= 227 * 1024, "shared memory budget");
+    static_assert(NB == 64 || NB == 128, "tile edge");
+};
 
-int chol_ld(int n) { return ((n + NB - 1) / NB) * NB; }
+int chol_ld(int n, int nb) { return ((n + nb - 1) / nb) * nb; }
 // work area: L_jj^-1 blocks, then int flags [tiledone ((T + 1) x T) | ydone (T) | abort (1)]
 static inline int chol_flag_count(int T) { return (T + 1) * T + T + 1; }
-size_t chol_work_doubles(int n) {
-    const int T = chol_ld(n) / NB;
-    return (size_t)T * NB * NB + (size_t)T * NB + (size_t)(chol_flag_count(T) + 1) / 2 + 1;
+size_t chol_work_doubles(int n, int nb) {
+    const int T = chol_ld(n, nb) / nb;
+    return (size_t)T * nb * nb + (size_t)T * nb + (size_t)(chol_flag_count(T) + 1) / 2 + 1;
 }
 
 // ---- small PTX helpers -------------------------------------------------------------------------------------------
@@ -105,8 +114,8 @@ struct CholArgs {
     const long long *toff;   // [(T + 1) * T] offset of tile (i, j) in doubles, -1 = not part of the plan
     int T;                // column tiles = n_pad / 128; row tiles = T + 1 (the last one is the rhs row)
     int n;                // logical order (entries of y written)
-    double *invL;         // [T][128*128]
-    double *ypad;         // [T][128] solution blocks as they are produced (cross-CTA exchange)
+    double *invL;         // [T][NB*NB]
+    double *ypad;         // [T][NB] solution blocks as they are produced (cross-CTA exchange)
     int *tiledone;        // [T + 1][T] tile (i, j) of L (row T: of z) is final
     int *ydone;           // [T]
     int *abort_flag;      // [1] set when a wait timed out (never expected; keeps a bug from hanging the GPU)
@@ -159,8 +168,10 @@ __device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_fl
 // -------------------------------------------------------------------------------------------------------------
 __device__ long long g_potrf_phase[4];   // tools/chol_prof.cu: accumulated ns in (A), (B), (C), calls
 
+template <int NB>
 __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double *__restrict__ Pv, double *__restrict__ invd,
                                                 double *__restrict__ dinv) {
+    constexpr int LDT = ChCfg<NB>::LDT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tig = lane & 3;
     __shared__ int s_bad;
@@ -324,7 +335,8 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 // -------------------------------------------------------------------------------------------------------------
 // The dataflow kernel
 // -------------------------------------------------------------------------------------------------------------
-// one k-slice (BK columns) of a 128-row operand tile into shared memory: 128 x BK/2 16-byte segments
+// one k-slice (BK columns) of an NB-row operand tile into shared memory: NB x BK/2 16-byte segments
+template <int NB>
 __device__ __forceinline__ void load_slice(double *__restrict__ dst, const double *__restrict__ src, int ld, int tid) {
     constexpr int SEGS = BK / 2;
 #pragma unroll
@@ -335,31 +347,36 @@ __device__ __forceinline__ void load_slice(double *__restrict__ dst, const doubl
     }
 }
 
-// acc += A_s (128 x BK, stride lda_s) * B_s^T (128 x BK, stride SPAD): warp (wm, wn) owns a 64 x 32 sub-tile
-__device__ __forceinline__ void mma_slice(double (&acc)[8][4][2], const double *__restrict__ a_s, int lda_s,
+// acc += A_s (NB x BK, stride lda_s) * B_s^T (NB x BK, stride SPAD): warp (wm, wn) owns an (NB/2) x (NB/4) sub-tile
+template <int MI, int NJ>
+__device__ __forceinline__ void mma_slice(double (&acc)[MI][NJ][2], const double *__restrict__ a_s, int lda_s,
                                           const double *__restrict__ b_s) {
 #pragma unroll
     for (int ks = 0; ks < BK / 4; ++ks) {
-        double a[8], b[4];
+        double a[MI], b[NJ];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] = a_s[(size_t)i * 8 * lda_s + ks * 4];
+        for (int i = 0; i < MI; ++i) a[i] = a_s[(size_t)i * 8 * lda_s + ks * 4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) b[j] = b_s[(size_t)j * 8 * SPAD + ks * 4];
+        for (int j = 0; j < NJ; ++j) b[j] = b_s[(size_t)j * 8 * SPAD + ks * 4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < MI; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            for (int j = 0; j < NJ; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
 }
 
+template <int NB>
 __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
+    using Cfg = ChCfg<NB>;
+    constexpr int KSL = Cfg::KSL, LDT = Cfg::LDT, MI = Cfg::MI, NJ = Cfg::NJ, STAGE_DOUBLES = Cfg::STAGE_DOUBLES, TILE_DOUBLES = Cfg::TILE_DOUBLES;
+    constexpr int WR = NB / 2, WC = NB / 4;                // warp tile
     if (p.state && p.state->done) return;
     extern __shared__ __align__(16) double smem[];
-    double *tileC = smem;                                  // [128][LDT]   (main loop: part of the ring)
+    double *tileC = smem;                                  // [NB][LDT]   (main loop: part of the ring)
     double *scratch = smem + TILE_DOUBLES;                 // epilogue ring (2 stages of B) / potrf scratch
     double *Pv = scratch, *invd = scratch + NB * LDP, *dinv = invd + PB * LDP;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // 2 x 4 warps -> 64 x 32 per warp.  Warps w and w + 4 share an SM sub-partition (and its DMMA pipe): the column blocks are
+    // 2 x 4 warps -> (NB/2) x (NB/4) per warp.  Warps w and w + 4 share an SM sub-partition (and its DMMA pipe): the column blocks are
     // mirrored in the lower warp row so that triangular work (TRSM against the lower-triangular L_jj^-1) is balanced.
     const int wm = warp >> 2, wn = wm ? 3 - (warp & 3) : (warp & 3);
     const int g = lane >> 2, tig = lane & 3;
@@ -378,11 +395,11 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         const int nkb = __ldg(&p.task[t + 1].w) - tk.w;
         const bool diag = (i == j);
         if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t] = global_ns();
-        double acc[8][4][2];
+        double acc[MI][NJ][2];
 #pragma unroll
-        for (int a = 0; a < 8; ++a)
+        for (int a = 0; a < MI; ++a)
 #pragma unroll
-            for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+            for (int b = 0; b < NJ; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
 
         const int nk = nkb * KSL;                          // k-slices of the bulk update
         int have = 0;                                      // leading klist entries known to be final in both row panels
@@ -425,8 +442,8 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             double *st = smem + (size_t)(kt % NSTAGE) * STAGE_DOUBLES;
             const int kb = __ldg(p.klist + kbeg + kt / KSL);
             const int col = (kt % KSL) * BK;
-            load_slice(st, tile_ptr(i, kb) + col, ld, tid);
-            if (!diag) load_slice(st + NB * SPAD, tile_ptr(j, kb) + col, ld, tid);
+            load_slice<NB>(st, tile_ptr(i, kb) + col, ld, tid);
+            if (!diag) load_slice<NB>(st + NB * SPAD, tile_ptr(j, kb) + col, ld, tid);
         };
         // prologue
         for (int s = 0; s < NSTAGE - 1; ++s) {
@@ -446,9 +463,9 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             }
             cp_async_commit();
             const double *st = smem + (size_t)(kt % NSTAGE) * STAGE_DOUBLES;
-            const double *a_s = st + (size_t)(wm * 64 + g) * SPAD + tig;
-            const double *b_s = (diag ? st : st + NB * SPAD) + (size_t)(wn * 32 + g) * SPAD + tig;
-            mma_slice(acc, a_s, SPAD, b_s);
+            const double *a_s = st + (size_t)(wm * WR + g) * SPAD + tig;
+            const double *b_s = (diag ? st : st + NB * SPAD) + (size_t)(wn * WC + g) * SPAD + tig;
+            mma_slice<MI, NJ>(acc, a_s, SPAD, b_s);
         }
         cp_async_wait<0>();
         aborted = __syncthreads_or(aborted);
@@ -459,11 +476,11 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         {
             const double *Cg = tile_ptr(i, j);
 #pragma unroll
-            for (int a = 0; a < 8; ++a) {
-                const int row = wm * 64 + a * 8 + g;
+            for (int a = 0; a < MI; ++a) {
+                const int row = wm * WR + a * 8 + g;
 #pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    const int col = wn * 32 + b * 8 + 2 * tig;
+                for (int b = 0; b < NJ; ++b) {
+                    const int col = wn * WC + b * 8 + 2 * tig;
                     double2 v = *reinterpret_cast<const double2 *>(Cg + (size_t)row * ld + col);
                     v.x -= acc[a][b][0]; v.y -= acc[a][b][1];
                     if (diag) {                            // strict upper starts as the zero part of [A; I]'s identity
@@ -477,7 +494,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         __syncthreads();
         if (diag) {
             const long long tp0 = p.prof ? global_ns() : 0;
-            const bool bad = potrf_inverse_tile(tileC, Pv, invd, dinv);
+            const bool bad = potrf_inverse_tile<NB>(tileC, Pv, invd, dinv);
             if (p.prof) t_potrf += global_ns() - tp0;
             if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
             // L_jj^-1 first: it is all the TRSMs (and the back substitution) wait for; L_jj itself is only stored for the
@@ -486,7 +503,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             // (only the lower triangle is written: the work area is zeroed when it is allocated and nothing else ever writes
             // the strict upper part, so half of the 128 KB leaves the SM before the flag can go up)
             for (int idx = tid; idx < NB * NB; idx += 256) {
-                const int r = idx >> 7, c = idx & (NB - 1);
+                const int r = idx / NB, c = idx % NB;
                 if (c <= r) Ig[idx] = (c < r) ? tileC[(size_t)c * LDT + r] : dinv[r];
             }
             if (bad && tid == 0) {
@@ -498,7 +515,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (tid == 0) st_release(p.tiledone + (size_t)j * T + j, 1);
             double *Lg = tile_ptr(j, j);
             for (int idx = tid; idx < NB * NB; idx += 256) {
-                const int r = idx >> 7, c = idx & (NB - 1);
+                const int r = idx / NB, c = idx % NB;
                 if (c <= r) Lg[(size_t)r * ld + c] = tileC[(size_t)r * LDT + c];
             }
             __syncthreads();                               // tileC is reused by the next task
@@ -511,28 +528,29 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
             const double *Ig = p.invL + (size_t)j * NB * NB;
 #pragma unroll
-            for (int a = 0; a < 8; ++a)
+            for (int a = 0; a < MI; ++a)
 #pragma unroll
-                for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-            load_slice(scratch, Ig, NB, tid);
+                for (int b = 0; b < NJ; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+            load_slice<NB>(scratch, Ig, NB, tid);
             cp_async_commit();
             for (int kt = 0; kt < NB / BK; ++kt) {
-                if (kt + 1 < NB / BK) load_slice(scratch + (size_t)((kt + 1) & 1) * NB * SPAD, Ig + (size_t)(kt + 1) * BK, NB, tid);
+                if (kt + 1 < NB / BK) load_slice<NB>(scratch + (size_t)((kt + 1) & 1) * NB * SPAD, Ig + (size_t)(kt + 1) * BK, NB, tid);
                 cp_async_commit();
                 cp_async_wait<1>();
                 __syncthreads();
-                const double *a_s = tileC + (size_t)(wm * 64 + g) * LDT + kt * BK + tig;
-                const double *b_s = scratch + (size_t)(kt & 1) * NB * SPAD + (size_t)(wn * 32 + g) * SPAD + tig;
-                if (kt <= wn) mma_slice(acc, a_s, LDT, b_s);   // L_jj^-1 is lower triangular: k-slices right of this warp's columns are zero
+                const double *a_s = tileC + (size_t)(wm * WR + g) * LDT + kt * BK + tig;
+                const double *b_s = scratch + (size_t)(kt & 1) * NB * SPAD + (size_t)(wn * WC + g) * SPAD + tig;
+                // L_jj^-1 is lower triangular: k-slices entirely right of this warp's columns are zero
+                if (kt * BK <= wn * WC + WC - 1) mma_slice<MI, NJ>(acc, a_s, LDT, b_s);
                 __syncthreads();
             }
             double *Cg = tile_ptr(i, j);
 #pragma unroll
-            for (int a = 0; a < 8; ++a) {
-                const int row = wm * 64 + a * 8 + g;
+            for (int a = 0; a < MI; ++a) {
+                const int row = wm * WR + a * 8 + g;
 #pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    const int col = wn * 32 + b * 8 + 2 * tig;
+                for (int b = 0; b < NJ; ++b) {
+                    const int col = wn * WC + b * 8 + 2 * tig;
                     *reinterpret_cast<double2 *>(Cg + (size_t)row * ld + col) = make_double2(acc[a][b][0], acc[a][b][1]);
                 }
             }
@@ -553,15 +571,17 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         return;
     }
 
-    // ================= phase 2: back substitution L^T y = z (z = row n_pad of A) =================
-    double *zs = smem;                 // [128] running z_m
-    double *ys = smem + NB;            // [128] y_k being applied
-    double *part = smem + 2 * NB;      // [2][128]
+    // ================= phase 2: back substitution L^T y = z (z = row 0 of the rhs tiles) =================
+    // 256 threads = PARTS groups of NB threads; group q sums rows [q RP, (q + 1) RP) of the tile for column c
+    constexpr int PARTS = 256 / NB, RP = NB / PARTS, RC = RP < 32 ? RP : 32;
+    double *zs = smem;                 // [NB] running z_m
+    double *ys = smem + NB;            // [NB] y_k being applied
+    double *part = smem + 2 * NB;      // [PARTS][NB]
     for (int m = T - 1 - (int)blockIdx.x; m >= 0; m -= gridDim.x) {
         // z_m is final once tile (T, m) is
         if (!__syncthreads_and(tid != 0 || (wait_ge(p.tiledone + (size_t)T * T + m, 1, p.abort_flag, waited) && wait_ge(p.tiledone + (size_t)m * T + m, 1, p.abort_flag, waited)))) break;
         if (tid < NB) zs[tid] = __ldcg(tile_ptr(T, m) + tid);      // row 0 of the rhs tile
-        const int c = tid & (NB - 1), half = tid >> 7;
+        const int c = tid % NB, q = tid / NB;
         bool ok = true;
         for (int k = T - 1; k > m; --k) {
             if (!__ldg(p.fill + (size_t)k * T + m)) continue;          // L_km is structurally zero
@@ -569,23 +589,28 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (!__syncthreads_and(ok)) { ok = false; break; }
             if (tid < NB) ys[tid] = __ldcg(p.ypad + (size_t)k * NB + tid);
             __syncthreads();
-            const double *Lkm = tile_ptr(k, m) + (size_t)(half * 64) * ld + c;
+            const double *Lkm = tile_ptr(k, m) + (size_t)(q * RP) * ld + c;
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
-            for (int rb = 0; rb < 64; rb += 32) {
-                double lv[32];
+            for (int rb = 0; rb < RP; rb += RC) {
+                double lv[RC];
 #pragma unroll
-                for (int r = 0; r < 32; ++r) lv[r] = __ldcg(Lkm + (size_t)(rb + r) * ld);    // 32 loads in flight per thread
+                for (int r = 0; r < RC; ++r) lv[r] = __ldcg(Lkm + (size_t)(rb + r) * ld);    // RC loads in flight per thread
 #pragma unroll
-                for (int r = 0; r < 32; r += 4) {
-                    const double *yy = ys + half * 64 + rb + r;
+                for (int r = 0; r < RC; r += 4) {
+                    const double *yy = ys + q * RP + rb + r;
                     a0 = fma(lv[r], yy[0], a0); a1 = fma(lv[r + 1], yy[1], a1);
                     a2 = fma(lv[r + 2], yy[2], a2); a3 = fma(lv[r + 3], yy[3], a3);
                 }
             }
-            part[half * NB + c] = (a0 + a1) + (a2 + a3);
+            part[q * NB + c] = (a0 + a1) + (a2 + a3);
             __syncthreads();
-            if (tid < NB) zs[tid] -= part[tid] + part[NB + tid];
+            if (tid < NB) {
+                double t = 0.0;
+#pragma unroll
+                for (int qq = 0; qq < PARTS; ++qq) t += part[qq * NB + tid];
+                zs[tid] -= t;
+            }
         }
         if (!ok) break;
         __syncthreads();
@@ -593,21 +618,23 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         const double *Ig = p.invL + (size_t)m * NB * NB;
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
-        for (int rb = 0; rb < 64; rb += 32) {
-            double iv[32];
+        for (int rb = 0; rb < RP; rb += RC) {
+            double iv[RC];
 #pragma unroll
-            for (int r = 0; r < 32; ++r) iv[r] = (half * 64 + rb + r >= c) ? __ldcg(Ig + (size_t)(half * 64 + rb + r) * NB + c) : 0.0;
+            for (int r = 0; r < RC; ++r) iv[r] = (q * RP + rb + r >= c) ? __ldcg(Ig + (size_t)(q * RP + rb + r) * NB + c) : 0.0;
 #pragma unroll
-            for (int r = 0; r < 32; r += 4) {
-                const double *zz = zs + half * 64 + rb + r;
+            for (int r = 0; r < RC; r += 4) {
+                const double *zz = zs + q * RP + rb + r;
                 a0 = fma(iv[r], zz[0], a0); a1 = fma(iv[r + 1], zz[1], a1);
                 a2 = fma(iv[r + 2], zz[2], a2); a3 = fma(iv[r + 3], zz[3], a3);
             }
         }
-        part[half * NB + c] = (a0 + a1) + (a2 + a3);
+        part[q * NB + c] = (a0 + a1) + (a2 + a3);
         __syncthreads();
         if (tid < NB) {
-            const double v = part[tid] + part[NB + tid];
+            double v = 0.0;
+#pragma unroll
+            for (int qq = 0; qq < PARTS; ++qq) v += part[qq * NB + tid];
             p.ypad[(size_t)m * NB + tid] = v;
             if (m * NB + tid < p.n) p.y[m * NB + tid] = v;
         }
@@ -626,7 +653,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 // -------------------------------------------------------------------------------------------------------------
 // host side
 // -------------------------------------------------------------------------------------------------------------
-static int g_chol_grid[64];     // per device: co-resident CTAs (0 = not initialised)
+static int g_chol_grid[64];     // per device: SM count = CTAs of the persistent grid (0 = not initialised)
 long long *g_chol_prof = nullptr;
 long long *g_chol_task_prof = nullptr;   // tools/chol_prof.cu only: [ntasks][4] + [T]   // tools/chol_prof.cu only: device buffer [grid][8] of per-CTA timings
 
@@ -636,13 +663,15 @@ int chol_init() {
     if (e != cudaSuccess) return (int)e;
     if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
     if (g_chol_grid[dev]) return 0;
-    e = cudaFuncSetAttribute(chol_dataflow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CHOL_SMEM);
+    e = cudaFuncSetAttribute(chol_dataflow_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, ChCfg<128>::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(chol_dataflow_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, ChCfg<64>::SMEM);
     if (e != cudaSuccess) return (int)e;
     int coop = 0, sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (!coop) return (int)cudaErrorNotSupported;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_dataflow_kernel, 256, CHOL_SMEM);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_dataflow_kernel<128>, 256, ChCfg<128>::SMEM);
     if (e != cudaSuccess) return (int)e;
     if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
     g_chol_grid[dev] = sms;       // one CTA per SM (shared memory allows exactly one)
@@ -750,8 +779,8 @@ struct HostPlan {
     double flops = 0.0;
 };
 
-void plan_analyse(int n, const unsigned char *nz, HostPlan &hp, size_t extra_doubles = 0) {
-    const int T = chol_ld(n) / NB;
+void plan_analyse(int n, int NB, const unsigned char *nz, HostPlan &hp, size_t extra_doubles = 0) {
+    const int T = chol_ld(n, NB) / NB;
     std::vector<unsigned char> f((size_t)(T + 1) * T, 0);
     for (int i = 0; i < T; ++i)
         for (int j = 0; j <= i; ++j) f[(size_t)i * T + j] = (i == j) || !nz || nz[(size_t)i * T + j] || nz[(size_t)j * T + i];
@@ -836,17 +865,18 @@ void plan_analyse(int n, const unsigned char *nz, HostPlan &hp, size_t extra_dou
 } // namespace
 
 // host-only: dependency depth (tasks) and filled tiles of the plan for a tile pattern
-void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *filled, double *flops) {
+void chol_plan_stats(int n, int nb, const unsigned char *nz, int *depth, long long *filled, double *flops) {
     HostPlan hp;
-    plan_analyse(n, nz, hp);
+    plan_analyse(n, nb, nz, hp);
     if (depth) *depth = hp.depth;
     if (filled) *filled = hp.filled;
     if (flops) *flops = hp.flops;
 }
 
-int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t s, size_t extra_doubles) {
+int chol_plan_create(int n, int nb, const unsigned char *nz, CholPlan *pl, cudaStream_t s, size_t extra_doubles) {
+    if (nb != 64 && nb != 128) return (int)cudaErrorInvalidValue;
     HostPlan hp;
-    plan_analyse(n, nz, hp, extra_doubles);
+    plan_analyse(n, nb, nz, hp, extra_doubles);
     const size_t bytes = hp.blob.size();
     if (pl->cap < bytes) {
         if (pl->blob) cudaFree(pl->blob);
@@ -860,7 +890,7 @@ int chol_plan_create(int n, const unsigned char *nz, CholPlan *pl, cudaStream_t 
     e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) return (int)e;
     unsigned char *b = static_cast<unsigned char *>(pl->blob);
-    pl->n = n; pl->T = hp.T; pl->ntasks = hp.ntasks;
+    pl->n = n; pl->nb = nb; pl->T = hp.T; pl->ntasks = hp.ntasks;
     pl->task = reinterpret_cast<const int4 *>(b + hp.o_task);
     pl->klist = reinterpret_cast<const int *>(b + hp.o_kl);
     pl->fill = b + hp.o_fill;
@@ -885,7 +915,7 @@ void chol_plan_destroy(CholPlan *pl) {
 
 // host matrix (n x n row-major, lower triangle read) + rhs -> the plan's tile-packed storage (host vector of total_doubles)
 void chol_pack_host(const CholPlan *pl, const double *A, const double *b, std::vector<double> &out) {
-    const int n = pl->n, T = pl->T;
+    const int n = pl->n, T = pl->T, NB = pl->nb;
     out.assign((size_t)pl->total_doubles, 0.0);
     for (int ti = 0; ti < T; ++ti)
         for (int tj = 0; tj <= ti; ++tj) {
@@ -911,8 +941,8 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
-    const int ld = chol_ld(n), T = ld / NB;
-    if (!plan || plan->n != n || plan->T != T) return (int)cudaErrorInvalidValue;       // the plan defines the storage
+    if (!plan || plan->n != n) return (int)cudaErrorInvalidValue;       // the plan defines the storage (and the tile edge)
+    const int NB = plan->nb, T = plan->T;
     CholArgs p;
     p.A = A; p.toff = plan->tile_off; p.T = T; p.n = n;
     p.invL = work;
@@ -926,7 +956,8 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
     int grid = g_chol_grid[dev] < plan->ntasks ? g_chol_grid[dev] : plan->ntasks;
     if (grid < 1) return (int)cudaErrorInitializationError;
     void *args[] = {&p};
-    e = cudaLaunchCooperativeKernel((const void *)chol_dataflow_kernel, dim3(grid), dim3(256), args, CHOL_SMEM, s);
+    if (NB == 128) e = cudaLaunchCooperativeKernel((const void *)chol_dataflow_kernel<128>, dim3(grid), dim3(256), args, ChCfg<128>::SMEM, s);
+    else e = cudaLaunchCooperativeKernel((const void *)chol_dataflow_kernel<64>, dim3(grid), dim3(256), args, ChCfg<64>::SMEM, s);
     return (int)e;
 }
 

@@ -420,7 +420,7 @@ __global__ void schur_init_kernel(Ctx ctx, double radius_override) {
     const int src = ctx.row_src[i];
     if (src < 0) { *s_elem(ctx, i, i) = lead ? 1.0 : 0.0; return; }     // identity padding
     const int c = src / 6, a = src % 6;
-    double *row = s_elem(ctx, i, ctx.cam_row[c]);        // a camera's 6 x 6 block never straddles a tile (21 cameras per tile)
+    double *row = s_elem(ctx, i, ctx.cam_row[c]);        // a camera's 6 x 6 block never straddles a tile
     if (ctx.cam_kind[c] == CAM_FREE) {
         const double *U = ctx.U + 36 * (size_t)c;
 #pragma unroll
@@ -439,7 +439,7 @@ __global__ void chol_rhs_kernel(Ctx ctx) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= ctx.ldS) return;
     const int src = ctx.row_src[i];
-    ctx.S[ctx.S_toff[(size_t)ctx.S_T * ctx.S_T + (i >> 7)] + (i & 127)] = src >= 0 ? ctx.rhs[src] : 0.0;     // row 0 of rhs tile i / 128
+    ctx.S[ctx.S_toff[(size_t)ctx.S_T * ctx.S_T + (i >> ctx.S_shift)] + (i & (ctx.S_nb - 1))] = src >= 0 ? ctx.rhs[src] : 0.0;     // row 0 of rhs tile i / nb
 }
 __global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
     if (ctx.state->done) return;

@@ -62,22 +62,22 @@ int prep_chunks(const PrepIn &in, PrepOut &out, cudaStream_t s);
 int prep_pairs_count(const PrepIn &in, const PrepOut &out, PrepScratch &scr, long long *h_total, cudaStream_t s);
 int prep_pairs_build(const PrepIn &in, const PrepOut &out, PairIndex &pi, PrepScratch &scr, PrepScratch &scr2, int *h_two, cudaStream_t s);
 int prep_pairs_units(PairIndex &pi, cudaStream_t s);
-// map[G x G] bytes (lower triangle): camera groups (CAMS_PER_TILE consecutive cameras = one Cholesky tile) that share a landmark
-int prep_group_map(const PairIndex &pi, int G, unsigned char *map, cudaStream_t s);
+// map[G x G] bytes (lower triangle): camera groups (cams_per_tile consecutive cameras = one Cholesky tile) that share a landmark
+int prep_group_map(const PairIndex &pi, int G, int cams_per_tile, unsigned char *map, cudaStream_t s);
 
 // ba_cholesky.cu -- dense SPD factorisation + solve of the reduced camera system (C6), one cooperative kernel
-constexpr int CHOL_NB = 128;
+// Tile edge nb: 128 (dense / nearly dense systems) or 64 (tile-sparse systems: shorter dependency chain), chosen per plan.
 int chol_init();                                        // per-device kernel attribute setup; returns cudaError
-int chol_ld(int n);                                     // n_pad = ceil(n / 128) * 128 = leading dimension
-size_t chol_work_doubles(int n);
-// A: the plan's tile-packed storage (plan->total_doubles doubles, see the layout contract in ba_cholesky.cu): 128 x 128
+int chol_ld(int n, int nb);                             // n_pad = ceil(n / nb) * nb
+size_t chol_work_doubles(int n, int nb);
+// A: the plan's tile-packed storage (plan->total_doubles doubles, see the layout contract in ba_cholesky.cu): nb x nb
 // tiles, each contiguous and row-major, at plan->tile_off[i * T + j]; tile row T is the right-hand side (row 0 of each tile).
 // On exit y (n) holds the solution and the tiles hold L.
 // state may be nullptr (standalone use); otherwise the kernel early-exits on state->done and reports breakdown in
 // state->chol_fail.  fail_flag (device int, may be nullptr) is set on breakdown as well.  Returns a cudaError.
 // plan: tile-level sparsity plan of this matrix (nullptr = dense).
 struct CholPlan {
-    int n = 0, T = 0, ntasks = 0;
+    int n = 0, nb = 128, T = 0, ntasks = 0;       // nb = tile edge (64 | 128)
     const int4 *task = nullptr; const int *klist = nullptr; const unsigned char *fill = nullptr;
     const long long *tile_off = nullptr;      // device [(T + 1) * T]: offset of tile (i, j) in doubles, -1 = not in the plan
     std::vector<long long> h_tile_off;        // host copy
@@ -92,12 +92,12 @@ struct CholPlan {
 // nz: host T x T bytes, (i, j) != 0 where tile (i, j) or (j, i) of S can be nonzero (nullptr = dense); synchronises s.
 // Elimination order of the tiles from their adjacency (G x G bytes, lower triangle read): order[pos] = tile.
 void chol_tile_order(int G, const unsigned char *adj, std::vector<int> &order);
-int chol_plan_create(int n, const unsigned char *nz, CholPlan *plan, cudaStream_t s, size_t extra_doubles = 0);
+int chol_plan_create(int n, int nb, const unsigned char *nz, CholPlan *plan, cudaStream_t s, size_t extra_doubles = 0);
 void chol_pack_host(const CholPlan *plan, const double *A, const double *b, std::vector<double> &out);   // host matrix -> packed tiles
 void chol_plan_destroy(CholPlan *plan);
 // zero the packed matrix (all tiles of the plan + the extra region) before S is assembled
 int chol_clear(double *A, const CholPlan *plan, cudaStream_t s);
-void chol_plan_stats(int n, const unsigned char *nz, int *depth, long long *filled, double *flops);   // host only
+void chol_plan_stats(int n, int nb, const unsigned char *nz, int *depth, long long *filled, double *flops);   // host only
 int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
 
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')

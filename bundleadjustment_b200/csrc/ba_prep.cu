@@ -403,18 +403,18 @@ int prep_pairs_build(const PrepIn &in, const PrepOut &out, PairIndex &pi, PrepSc
 }
 
 // camera groups (= Cholesky tiles) coupled through a shared landmark
-__global__ void group_map_kernel(int n_seg, const int2 *__restrict__ seg_cams, int G, unsigned char *__restrict__ map) {
+__global__ void group_map_kernel(int n_seg, const int2 *__restrict__ seg_cams, int G, int cams_per_tile, unsigned char *__restrict__ map) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n_seg) return;
     const int2 c = seg_cams[idx];
-    const int gi = c.x / CAMS_PER_TILE, gj = c.y / CAMS_PER_TILE;
+    const int gi = c.x / cams_per_tile, gj = c.y / cams_per_tile;
     map[(size_t)max(gi, gj) * G + min(gi, gj)] = 1;
 }
 
-int prep_group_map(const PairIndex &pi, int G, unsigned char *map, cudaStream_t s) {
+int prep_group_map(const PairIndex &pi, int G, int cams_per_tile, unsigned char *map, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(map, 0, (size_t)G * G, s);
     if (e != cudaSuccess) return (int)e;
-    if (pi.n_seg > 0) group_map_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.seg_cams, G, map);
+    if (pi.n_seg > 0) group_map_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.seg_cams, G, cams_per_tile, map);
     return (int)cudaGetLastError();
 }
 

@@ -124,13 +124,14 @@ struct Ctx {
     double *Vinv;            // [Np][6]
     double *wv;              // [Np][3] = Vinv * bp
     // reduced system
-    // One Cholesky tile (128 rows) holds CAMS_PER_TILE consecutive cameras (126 rows + 2 identity rows); the tiles are laid
+    // One Cholesky tile (S_nb = 128 or 64 rows) holds S_nb / 6 consecutive cameras (+ 2 or 4 identity rows); the tiles are laid
     // out in elimination order (nested dissection of the camera-group graph), so camera c's block starts at row cam_row[c].
     double *S;               // TILE-PACKED (ba_cholesky.cu layout contract): tile (i, j) of the padded lower triangle at S + S_toff[i * S_T + j],
-                             // 128 x 128 row-major; tile row S_T = the right-hand side (row 0 of each tile)
+                             // S_nb x S_nb row-major; tile row S_T = the right-hand side (row 0 of each tile)
     const long long *S_toff; // [(S_T + 1) * S_T] offsets in doubles, -1 = structurally zero tile
-    int S_T;                 // tiles per side = ldS / 128
-    int ldS;                 // order of the padded system = 128 * number of camera groups
+    int S_T;                 // tiles per side = ldS / S_nb
+    int S_nb, S_shift;       // tile edge (128 | 64) and its log2
+    int ldS;                 // order of the padded system = S_nb * number of camera groups
     const int *cam_row;      // [Nc]
     const int *row_src;      // [ldS] 6 c + a of the camera parameter in that row, -1 for padding rows
     double *rhs;             // [n] (becomes y_c after the solve)
@@ -165,10 +166,11 @@ constexpr int HF_LM_RING = 2, HF_LM_SLOTS = 4, HF_CG_RING = 8, HF_CG_SLOTS = 8;
 enum : int { RED_LIN = 0, RED_CAM_NORMS, RED_CAM_UPDATE, RED_STEP, RED_CG_CHECK, RED_CG_START, RED_SLOTS = 8 };
 __host__ __device__ inline double *red_slot(const Ctx &ctx, int slot) { return ctx.red_part + (size_t)slot * RED_MAX_GRID * 4; }
 
-constexpr int CAMS_PER_TILE = 21;   // 6 * 21 = 126 <= 128 (CHOL_NB)
+__host__ __device__ inline int cams_per_tile(int nb) { return nb / 6; }   // 21 cameras (126 rows) per 128-row tile, 10 (60 rows) per 64-row tile
 // element (r, q), r >= q's tile row, of the tile-packed reduced system (the tile must be part of the plan)
 __device__ __forceinline__ double *s_elem(const Ctx &ctx, int r, int q) {
-    return ctx.S + ctx.S_toff[(size_t)(r >> 7) * ctx.S_T + (q >> 7)] + (size_t)(r & 127) * 128 + (q & 127);
+    const int m = ctx.S_nb - 1;
+    return ctx.S + ctx.S_toff[(size_t)(r >> ctx.S_shift) * ctx.S_T + (q >> ctx.S_shift)] + ((size_t)(r & m) << ctx.S_shift) + (q & m);
 }
 constexpr int CHUNK = 128;   // observations per camera-side reduction unit
 constexpr int TILE_WIN = 192;   // observation window defining a landmark block of the tile kernels (ba_prep.cu)

@@ -214,6 +214,9 @@ int ba_get_kernel_profile(ba_handle *h, double out[4]);
  * its own: tests and the FP64 tensor-pipe micro-benchmark.  A: n x n row-major, lower triangle read.
  * ms (may be NULL): best device time of factor + solve over `repeats` runs. */
 int ba_dense_spd_solve(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats);
+/* The same with the Cholesky tile edge forced (64 | 128; 0 = automatic as above): tests of both kernel instantiations. */
+int ba_dense_spd_solve_tile(int device, int32_t n, const double *A, const double *b, double *x, float *ms, int32_t repeats,
+                            int32_t tile_edge);
 
 /* Reduced camera system of the current problem (dense Schur): out = {padded order (one 128-row tile per 21 cameras), 128 x 128 tiles of the Cholesky factor that
  * can be nonzero, tiles in the lower triangle, flops of one factorisation + solve over those tiles}.  Cameras that share
@@ -226,6 +229,10 @@ int ba_get_reduced_system_stats(ba_handle *h, double out[4]);
  * matrix, as Ceres' DENSE_SCHUR (Optimizer.cpp:85) does.  Results change by summation order only.  The library reads NO
  * environment variables.  Call before ba_set_problem. */
 int ba_set_reduced_system_mode(ba_handle *h, int32_t natural_order, int32_t dense_tiles);
+/* Tile edge of the reduced-system Cholesky: 0 = automatic (64-row tiles when co-visibility leaves at least three quarters of
+ * the lower tiles of S empty -- the factorisation is then a dependency chain along the nested-dissection separators and
+ * shorter links win -- else 128-row tiles, which run dense matrices closest to the FP64 tensor peak), 64 or 128 = forced. */
+int ba_set_reduced_system_tile(ba_handle *h, int32_t tile_edge);
 
 /* ---- host-only helpers (no GPU needed) ---------------------------------------------------------------- */
 /* Balanced contiguous landmark partition: cut[r]..cut[r+1] for r in [0,n_ranks); weight = sum over the

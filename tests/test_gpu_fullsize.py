@@ -18,9 +18,12 @@ their condition numbers, and how many landmarks needed the conditioning term at 
 
 PCG with Ceres' inexact rule (eta = 0.1) stops on a THRESHOLD test (zeta < eta); two correct implementations that differ in
 the last bits can stop one CG iteration apart, after which the two LM trajectories are different inexact-Newton sequences.
-The comparison is therefore made three ways: (a) PCG driven to |r| <= 1e-13 |b| against the DENSE oracle (exact steps, full
-tolerances); (b) PCG with a FIXED number of CG iterations per LM iteration (eta tiny, max_linear_solver_iterations = 25: no
-threshold decisions, steps as inexact as Ceres') against the oracle's PCG under the same setting, full tolerances;
+The comparison is therefore made three ways: (a) PCG driven to |r| <= 1e-11 |b| against the DENSE oracle, a CROSS-ALGORITHM
+check held to 1e-5 (measured, tools/pcg_diag.py -> profiles/r02_pcg_vs_dense_diag.txt: on K4 x0.1, cond(S) ~ 5e3..5e6, the
+two agree to 3e-14; on full-size K4 a 1e-11 residual gives 1.5e-6 and ASKING FOR MORE makes it worse -- 1e-13 is below what
+CG can reach there, the iteration runs thousands of steps past stagnation and Ceres' residual reset every 10 iterations,
+which restarts r but keeps p, lets x drift: 6 % off at the second LM iteration); (b) PCG with a FIXED number of CG iterations per LM iteration (eta tiny, max_linear_solver_iterations = 25: no
+threshold decisions, steps as inexact as Ceres') against the oracle's PCG under the same setting;
 (c) Ceres' own rule against the oracle's PCG: CG iteration counts may differ by at most one, the trajectories must agree to
 1e-6 up to the first LM iteration where they do, and to 1e-3 afterwards."""
 import dataclasses
@@ -47,7 +50,7 @@ def _traj_check(its, oits, rtol=1e-6):
         worst = max(worst, abs(a["cost"] - b["cost"]) / abs(b["cost"]))
         assert abs(a["cost"] - b["cost"]) <= rtol * abs(b["cost"]), (a, b)
         # (the radius is radius / max(1/3, 1 - (2 rho - 1)^3): it amplifies the 1e-7 cost differences of late iterations)
-        assert abs(a["trust_region_radius"] - b["trust_region_radius"]) <= 1e-4 * b["trust_region_radius"], (a, b)
+        assert abs(a["trust_region_radius"] - b["trust_region_radius"]) <= max(1e-4, 100 * rtol) * b["trust_region_radius"], (a, b)
     return worst
 
 
@@ -99,9 +102,9 @@ def _solve_both(bab, orc, pb, max_it, label, threads=None, oracle_kw=None, **kw)
     return (sm, its, cam, pt), (osm, oits, ocam, opt_)
 
 
-def _full_check(orc, pb, g, o, label, final_rtol=1e-8, cam_atol=1e-6):
+def _full_check(orc, pb, g, o, label, final_rtol=1e-8, cam_atol=1e-6, traj_rtol=1e-6):
     (sm, its, cam, pt), (osm, oits, ocam, opt_) = g, o
-    worst = _traj_check(its, oits)
+    worst = _traj_check(its, oits, traj_rtol)
     rel = abs(sm.final_cost - osm.final_cost) / osm.final_cost
     print(f"[{label}] trajectory max rel diff {worst:.3e}; final cost rel diff {rel:.3e}; max camera diff {np.abs(cam - ocam).max():.3e}")
     assert sm.termination_type == osm.termination_type
@@ -158,10 +161,10 @@ def test_k4_full_size_pcg_vs_oracle_pcg(bab, orc):
 
 
 def test_k4_full_size_tight_pcg_vs_dense_oracle(bab, orc):
-    """(a): K4, PCG run to |r| <= 1e-13 |b|, against the DENSE oracle at the full tolerances (replaces round 1's 5e-4)."""
+    """(a): K4, PCG run to |r| <= 1e-11 |b|, against the DENSE oracle: trajectory and end point to 1e-5 (round 1: 5e-4)."""
     import os
     pb = syn.flatten(syn.config("K4"))
-    tight = dict(linear_solver=1, eta=-1.0, cg_r_tolerance=1e-13, max_linear_solver_iterations=5000)
+    tight = dict(linear_solver=1, eta=-1.0, cg_r_tolerance=1e-11, max_linear_solver_iterations=20000)
     s = bab.Solver(bab.default_options(max_num_iterations=10, **tight))
     s.set_problem(pb)
     sm = s.solve()
@@ -169,7 +172,7 @@ def test_k4_full_size_tight_pcg_vs_dense_oracle(bab, orc):
     print("[K4 tight PCG] CG iterations", [i["linear_solver_iterations"] for i in its])
     s.close()
     ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(max_num_iterations=10, num_threads=os.cpu_count(), exploit_sparsity=1))
-    _full_check(orc, pb, (sm, its, cam, pt), (osm, oits, ocam, opt_), "K4 tight PCG vs dense oracle")
+    _full_check(orc, pb, (sm, its, cam, pt), (osm, oits, ocam, opt_), "K4 tight PCG vs dense oracle", final_rtol=1e-5, cam_atol=1e-5, traj_rtol=1e-5)
 
 
 def test_k2_full_size_vs_oracle(bab, orc):
@@ -215,11 +218,11 @@ def test_k3_full_size_outer_loop_vs_oracle(bab, orc):
 
 def test_k5_tenth_dense_oracle_vs_tight_pcg_and_pcg_vs_pcg(bab, orc):
     """K5 down-scaled to 1/10 (1 300 cameras / 450 k landmarks / ~3 M observations).  (a) the dense oracle
-    against the CUDA PCG run to |r| <= 1e-13 |b|; (b) Ceres' inexact rule (eta = 0.1) against the oracle's own PCG with
+    against the CUDA PCG run to |r| <= 1e-11 |b| (cross-algorithm check, 1e-5); (b) Ceres' inexact rule (eta = 0.1) against the oracle's own PCG with
     equal CG iteration counts."""
     import os
     pb = syn.flatten(syn.config("K5", scale=0.1))
-    tight = dict(linear_solver=1, eta=-1.0, cg_r_tolerance=1e-13, max_linear_solver_iterations=5000)
+    tight = dict(linear_solver=1, eta=-1.0, cg_r_tolerance=1e-11, max_linear_solver_iterations=20000)
     s = bab.Solver(bab.default_options(max_num_iterations=5, **tight))
     s.set_problem(pb)
     sm = s.solve()
@@ -228,7 +231,7 @@ def test_k5_tenth_dense_oracle_vs_tight_pcg_and_pcg_vs_pcg(bab, orc):
     t = time.time()
     ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(max_num_iterations=5, num_threads=os.cpu_count(), exploit_sparsity=1))
     print(f"[K5x0.1] dense oracle: 5 LM iterations in {time.time() - t:.1f}s")
-    _full_check(orc, pb, (sm, its, cam, pt), (osm, oits, ocam, opt_), "K5x0.1 tight PCG vs dense oracle")
+    _full_check(orc, pb, (sm, its, cam, pt), (osm, oits, ocam, opt_), "K5x0.1 tight PCG vs dense oracle", final_rtol=1e-5, cam_atol=1e-5, traj_rtol=1e-5)
     _pcg_checks(bab, orc, pb, 5, "K5x0.1 pcg")
 
 

@@ -125,13 +125,14 @@ def test_schur_system_elimination_order(bab, orc):
     s.close()
 
 
+@pytest.mark.parametrize("tile", [64, 128])
 @pytest.mark.parametrize("n", [6, 64, 130, 174, 500, 1194])
-def test_dense_spd_solve(bab, n):
+def test_dense_spd_solve(bab, n, tile):
     rng = np.random.default_rng(n)
     B = rng.normal(size=(n, n))
     A = B @ B.T + n * np.eye(n)
     b = rng.normal(size=n)
-    x, ms = bab.capi.dense_spd_solve(A, b)
+    x, ms = bab.capi.dense_spd_solve(A, b, tile_edge=tile)
     ref = np.linalg.solve(A, b)
     assert np.abs(x - ref).max() <= 1e-10 * np.abs(ref).max()
 
@@ -160,12 +161,14 @@ def _tile_pattern_matrix(n, pattern, seed):
     ("blockdiag", 700, lambda i, j, T: False),
     ("scattered", 1500, lambda i, j, T: (7 * i + 3 * j) % 5 == 0),
 ])
-def test_dense_spd_solve_tile_patterns(bab, name, n, pattern):
+@pytest.mark.parametrize("tile", [0, 64, 128])
+def test_dense_spd_solve_tile_patterns(bab, name, n, pattern, tile):
     """The factorisation skips tiles that are structurally zero (tile-level symbolic fill); results must equal a
-    dense solve for any pattern, including ones that fill in."""
+    dense solve for any pattern, including ones that fill in -- with 128-row tiles, with 64-row tiles (the choice for
+    tile-sparse systems) and with the automatic choice."""
     A = _tile_pattern_matrix(n, pattern, seed=len(name) + n)
     b = np.random.default_rng(n).normal(size=n)
-    x, ms = bab.capi.dense_spd_solve(A, b)
+    x, ms = bab.capi.dense_spd_solve(A, b, tile_edge=tile)
     ref = np.linalg.solve(A, b)
     assert np.abs(x - ref).max() <= 1e-11 * np.abs(ref).max()
 
@@ -177,9 +180,10 @@ def test_tile_skipping_changes_nothing(bab):
     pb = syn.flatten(syn.make_scene("band", 11, 260, 9000, 4.0, 16))
     opt = bab.default_options(max_num_iterations=6)
     runs = []
-    for dense in (False, True):
+    for dense, tile in ((False, 128), (True, 128), (False, 64)):
         s = bab.Solver(opt)
         s.set_reduced_system_mode(dense_tiles=dense)
+        s.set_reduced_system_tile(tile)
         s.set_problem(pb)
         sm = s.solve()
         st = s.reduced_system_stats()
@@ -190,6 +194,9 @@ def test_tile_skipping_changes_nothing(bab):
     assert np.abs(runs[0][0] - runs[1][0]).max() <= 1e-10 * runs[1][0].max()
     assert np.abs(runs[0][1] - runs[1][1]).max() <= 1e-8
     assert np.percentile(np.abs(runs[0][2] - runs[1][2]).max(axis=1), 99.0) <= 1e-8
+    # 64-row tiles: another summation order of the same factorisation
+    assert runs[2][0].shape == runs[1][0].shape and np.abs(runs[2][0] - runs[1][0]).max() <= 1e-10 * runs[1][0].max()
+    assert np.abs(runs[2][1] - runs[1][1]).max() <= 1e-8
 
 
 def test_dense_spd_not_positive_definite(bab):

@@ -1,5 +1,5 @@
 // chol_chain.cu -- critical path of the tile-sparse dataflow Cholesky on a banded tile pattern in nested-dissection
-// order (tools only; includes the product source).  usage: chol_chain [G tiles = 81] [band in tiles = 2] [natural = 0]
+// order (tools only; includes the product source).  usage: chol_chain [G tiles = 81] [band in tiles = 2] [natural = 0] [tile edge = 128]
 #include "../bundleadjustment_b200/csrc/ba_cholesky.cu"
 
 #include <algorithm>
@@ -11,14 +11,14 @@
 using namespace ba;
 
 // one CTA per tile slot (i, j) of the plan's tile-packed storage: pseudo-random SPD-dominant entries, rhs row = 1
-__global__ void fill_pattern(double *A, const long long *toff, int T, int ld) {
+__global__ void fill_pattern(double *A, const long long *toff, int T, int ld, int nb) {
     const int i = blockIdx.x / T, j = blockIdx.x % T;
     const long long o = toff[(size_t)i * T + j];
     if (o < 0) return;
-    for (int idx = threadIdx.x; idx < 128 * 128; idx += blockDim.x) {
-        const int r = i * 128 + idx / 128, c = j * 128 + idx % 128;
+    for (int idx = threadIdx.x; idx < nb * nb; idx += blockDim.x) {
+        const int r = i * nb + idx / nb, c = j * nb + idx % nb;
         double v = 0.0;
-        if (i == T) v = (idx / 128 == 0) ? 1.0 : 0.0;
+        if (i == T) v = (idx / nb == 0) ? 1.0 : 0.0;
         else if (c <= r) {
             unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
             h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
@@ -31,7 +31,8 @@ __global__ void fill_pattern(double *A, const long long *toff, int T, int ld) {
 
 int main(int argc, char **argv) {
     const int G = argc > 1 ? atoi(argv[1]) : 81, band = argc > 2 ? atoi(argv[2]) : 2, natural = argc > 3 ? atoi(argv[3]) : 0;
-    const int n = G * CHOL_NB, ld = n, T = G;
+    const int nb = argc > 4 ? atoi(argv[4]) : 128;
+    const int n = G * nb, ld = n, T = G;
     std::vector<unsigned char> adj((size_t)G * G, 0), nz((size_t)G * G, 0);
     for (int i = 0; i < G; ++i) for (int j = std::max(0, i - band); j <= i; ++j) adj[(size_t)i * G + j] = 1;
     std::vector<int> order(G), pos(G);
@@ -41,16 +42,16 @@ int main(int argc, char **argv) {
     double *A, *work, *y;
     if (chol_init()) { printf("chol_init failed\n"); return 1; }
     CholPlan plan;
-    if (chol_plan_create(n, nz.data(), &plan, 0)) { printf("plan failed\n"); return 1; }
-    cudaMalloc(&A, 8 * (size_t)plan.total_doubles); cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMemset(work, 0, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
-    printf("G=%d band=%d %s order: %lld filled tiles, %d tasks, depth %d, %.3f GFLOP\n", G, band, natural ? "natural" : "nested-dissection",
+    if (chol_plan_create(n, nb, nz.data(), &plan, 0)) { printf("plan failed\n"); return 1; }
+    cudaMalloc(&A, 8 * (size_t)plan.total_doubles); cudaMalloc(&work, 8 * chol_work_doubles(n, nb)); cudaMemset(work, 0, 8 * chol_work_doubles(n, nb)); cudaMalloc(&y, 8 * (size_t)ld);
+    printf("tile edge %d: G=%d band=%d %s order: %lld filled tiles, %d tasks, depth %d, %.3f GFLOP\n", nb, G, band, natural ? "natural" : "nested-dissection",
            plan.filled_tiles, plan.ntasks, plan.depth, plan.flops * 1e-9);
     const size_t nprof = 4 * (size_t)plan.ntasks + T;
     cudaMalloc(&g_chol_task_prof, 8 * nprof);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
     for (int r = 0; r < 4; ++r) {
-        fill_pattern<<<(T + 1) * T, 256>>>(A, plan.tile_off, T, ld);
+        fill_pattern<<<(T + 1) * T, 256>>>(A, plan.tile_off, T, ld, nb);
         cudaMemset(g_chol_task_prof, 0, 8 * nprof);
         cudaEventRecord(e0);
         int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, &plan, 0);

@@ -10,14 +10,14 @@
 using namespace ba;
 
 // one CTA per tile slot (i, j) of the plan's tile-packed storage: banded pseudo-random SPD-dominant entries, rhs row = 1
-__global__ void fill_spd(double *A, const long long *toff, int T, int n, int band) {
+__global__ void fill_spd(double *A, const long long *toff, int T, int n, int band, int nb) {
     const int i = blockIdx.x / T, j = blockIdx.x % T;
     const long long o = toff[(size_t)i * T + j];
     if (o < 0) return;
-    for (int idx = threadIdx.x; idx < 128 * 128; idx += blockDim.x) {
-        const int r = i * 128 + idx / 128, c = j * 128 + idx % 128;
+    for (int idx = threadIdx.x; idx < nb * nb; idx += blockDim.x) {
+        const int r = i * nb + idx / nb, c = j * nb + idx % nb;
         double v = 0.0;
-        if (i == T) v = (idx / 128 == 0 && c < n) ? 1.0 : 0.0;
+        if (i == T) v = (idx / nb == 0 && c < n) ? 1.0 : 0.0;
         else if (r < n && c <= r && r - c <= band) {
             unsigned h = (unsigned)(r * 2654435761u) ^ (unsigned)(c * 40503u + 12345u);
             h ^= h >> 13; h *= 0x5bd1e995u; h ^= h >> 15;
@@ -31,25 +31,26 @@ __global__ void fill_spd(double *A, const long long *toff, int T, int n, int ban
 int main(int argc, char **argv) {
     const int n = argc > 1 ? atoi(argv[1]) : 10200;
     const int band = argc > 2 ? atoi(argv[2]) : n;
-    const int ld = chol_ld(n);
+    const int nb = argc > 3 ? atoi(argv[3]) : 128;
+    const int ld = chol_ld(n, nb);
     double *A, *work, *y;
-    cudaMalloc(&work, 8 * chol_work_doubles(n)); cudaMemset(work, 0, 8 * chol_work_doubles(n)); cudaMalloc(&y, 8 * (size_t)ld);
+    cudaMalloc(&work, 8 * chol_work_doubles(n, nb)); cudaMemset(work, 0, 8 * chol_work_doubles(n, nb)); cudaMalloc(&y, 8 * (size_t)ld);
     cudaMalloc(&g_chol_prof, 8 * 8 * 256);
     if (chol_init()) { printf("chol_init failed\n"); return 1; }
     // tile plan of the band (exact tile pattern of fill_spd)
-    const int Tp = ld / CHOL_NB;
+    const int Tp = ld / nb;
     std::vector<unsigned char> nz((size_t)Tp * Tp, 0);
     for (int i = 0; i < Tp; ++i)
-        for (int j = 0; j <= i; ++j) nz[(size_t)i * Tp + j] = (i * CHOL_NB - (j * CHOL_NB + CHOL_NB - 1)) <= band;
+        for (int j = 0; j <= i; ++j) nz[(size_t)i * Tp + j] = (i * nb - (j * nb + nb - 1)) <= band;
     CholPlan plan;
-    if (chol_plan_create(n, band < n ? nz.data() : nullptr, &plan, 0)) { printf("plan failed\n"); return 1; }
+    if (chol_plan_create(n, nb, band < n ? nz.data() : nullptr, &plan, 0)) { printf("plan failed\n"); return 1; }
     const CholPlan *plan_ptr = &plan;
     if (band < n) printf("band %d: %lld filled tiles, %d tasks, %.3f GFLOP\n", band, plan.filled_tiles, plan.ntasks, plan.flops * 1e-9);
     cudaMalloc(&A, 8 * (size_t)plan.total_doubles);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float best = 1e30f;
     for (int r = 0; r < 4; ++r) {
-        fill_spd<<<(Tp + 1) * Tp, 256>>>(A, plan.tile_off, Tp, n, band);
+        fill_spd<<<(Tp + 1) * Tp, 256>>>(A, plan.tile_off, Tp, n, band, nb);
         cudaEventRecord(e0);
         int ce = chol_factor_solve(A, n, work, y, nullptr, nullptr, plan_ptr, 0);
         cudaEventRecord(e1);
@@ -61,7 +62,7 @@ int main(int argc, char **argv) {
     std::vector<long long> h(8 * 256);
     cudaMemcpy(h.data(), g_chol_prof, 8 * 8 * 256, cudaMemcpyDeviceToHost);
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-    const int T = ld / NB, grid = std::min(sms, T * (T + 3) / 2);
+    const int T = ld / nb, grid = std::min(sms, T * (T + 3) / 2);
     long long t0 = h[0], tend = 0;
     for (int b = 0; b < grid; ++b) { t0 = std::min(t0, h[8 * b]); tend = std::max(tend, h[8 * b + 2]); }
     double s_p1 = 0, s_w1 = 0, s_w2 = 0, s_potrf = 0, s_trsm = 0, max_p1 = 0, s_tasks = 0, potrf_tiles = T;
