@@ -102,7 +102,8 @@ struct ba_handle {
     int *h_prep = nullptr;           // pinned [8]
     // device buffers
     DevBuf cam0, cam1, pt0, pt1, cam_init, pt_init, cam_kind, cam_K, cam_extr;
-    DevBuf cm_obs, blk_first_pt, blk_info, pm_camk, pm_trk;
+    DevBuf cm_obs, blk_first_pt, blk_info, pm_camk, pm_trk, blk_ord;
+    bool ord_built = false;          // blk_ord (camera order inside each landmark block): built on the first PCG solve
     DevBuf pm_uv, pm_cam, pm_pt, pt_ptr, cm_uv, cm_pt, chunk_cam, chunk_beg, chunk_end, cam_chunk_ptr;
     DevBuf tab_x, tab_c, scale_cam, scale_pt, U, bc, V, bp, W, cam_part, Vinv, wv, S, rhs, yc;
     DevBuf part, cost_part, red_part, red_count, lin_red, lin_loc, camsums, state, iters, invL;   // lin_*: [U | b_c | sums | max slots], one all-reduce
@@ -139,7 +140,7 @@ struct ba_handle {
                          &scale_pt, &U, &bc, &V, &bp, &W, &cam_part, &Vinv, &wv, &S, &rhs, &yc, &part, &cost_part, &red_part, &red_count, &lin_red, &lin_loc,
                          &camsums, &state, &iters, &invL, &cg_r, &cg_p, &cg_z, &cg_q, &cg_x, &Minv, &tp, &cg_part, &cg_qp, &ev_res, &ev_jc, &ev_jp,
                          &raw_cam, &raw_pt, &raw_uv, &raw_fixed, &perm_dev, &cnt_cam, &cnt_cam_global, &cam_ptr, &prep_flags,
-                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &tile_map, &cam_row, &row_src, &yperm,
+                         &pair_obs, &seg_beg, &seg_cams, &unit_ptr, &unit_seg, &unit_beg, &unit_part, &cm_obs, &blk_first_pt, &blk_info, &pm_camk, &pm_trk, &blk_ord, &tile_map, &cam_row, &row_src, &yperm,
                          &o_pose, &o_extr, &o_pt32, &o_wb, &o_ptr, &o_xy, &o_oct, &o_xyz, &o_mn, &o_mx, &o_has, &o_out, &o_kp_pt, &o_kp_obs, &o_masked, &o_active};
         for (DevBuf *b : all) b->free();
         chol_plan_destroy(&chol_plan);
@@ -260,6 +261,25 @@ int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
     return BA_OK;
 }
 
+// PCG only, once per problem: camera order inside every landmark block + the matvec's private copies of q
+int ensure_pcg(ba_handle *h) {
+    Ctx &ctx = h->ctx;
+    if (!h->ord_built) {
+        cudaStream_t s = h->stream;
+        CU(h->blk_ord.alloc(4 * std::max<size_t>((size_t)ctx.No, 1)));
+        const int rc = prep_block_order(h->prep_out, ctx.Nc, h->blk_ord.as<unsigned>(), s);
+        if (rc == (int)cudaErrorInvalidValue) return fail(BA_ERR_INVALID, "the iterative solver supports up to 2^20 cameras and landmark blocks below 2048 observations");
+        if (rc) return fail(BA_ERR_CUDA, "prep_block_order: %s", cudaGetErrorString((cudaError_t)rc));
+        ctx.blk_ord = h->blk_ord.as<unsigned>();
+        ctx.mv_grid = pcg_matvec_grid(ctx);
+        CU(h->cg_qp.alloc(8 * (size_t)ctx.mv_grid * std::max<size_t>((size_t)ctx.n, 1)));
+        CU(cudaMemsetAsync(h->cg_qp.p, 0, h->cg_qp.bytes, s));
+        ctx.cg_qp = h->cg_qp.as<double>();
+        h->ord_built = true;
+    }
+    return BA_OK;
+}
+
 int ensure_dense(ba_handle *h) {
     if (!h->pairs_built) {
         // camera-pair-major index for the deterministic Schur reduction (device-side, once per problem)
@@ -368,6 +388,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     h->has_problem = false;
     h->perm_valid = false;
     h->pairs_built = false;
+    h->ord_built = false;
     cudaStream_t s = h->stream;
     Ctx &ctx = h->ctx;
     std::memset(&ctx, 0, sizeof(ctx));
@@ -467,8 +488,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     CU(cudaMemsetAsync(h->red_count.p, 0, 4 * RED_SLOTS, s));
     AL(state, sizeof(LMState)); AL(iters, sizeof(ba_iteration) * (size_t)(h->opt.max_num_iterations + 2));
     AL(cg_r, 8 * (size_t)ctx.n); AL(cg_p, 8 * (size_t)ctx.n + 64); AL(cg_z, 8 * (size_t)ctx.n); AL(cg_q, 8 * (size_t)ctx.n);
-    AL(cg_x, 8 * (size_t)ctx.n + 64); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np); AL(cg_part, 8 * 1024); AL(cg_qp, 8 * 32 * (size_t)ctx.n);
-    CU(cudaMemsetAsync(h->cg_qp.p, 0, 8 * 32 * (size_t)ctx.n, s));
+    AL(cg_x, 8 * (size_t)ctx.n + 64); AL(Minv, 8 * 36 * (size_t)Nc); AL(tp, 8 * 3 * (size_t)Np); AL(cg_part, 8 * 1024);
     ctx.cam[0] = h->cam0.as<double>(); ctx.cam[1] = h->cam1.as<double>();
     ctx.pt[0] = h->pt0.as<double>(); ctx.pt[1] = h->pt1.as<double>();
     ctx.cam_init = h->cam_init.as<double>(); ctx.pt_init = h->pt_init.as<double>();
@@ -492,7 +512,7 @@ extern "C" int ba_set_problem(ba_handle *h, int32_t n_cam, const double *cam, co
     ctx.part = h->part.as<double>(); ctx.camsums = h->camsums.as<double>();
     ctx.red_part = h->red_part.as<double>(); ctx.red_count = h->red_count.as<unsigned>();
     ctx.cg_r = h->cg_r.as<double>(); ctx.cg_p = h->cg_p.as<double>(); ctx.cg_z = h->cg_z.as<double>(); ctx.cg_q = h->cg_q.as<double>();
-    ctx.cg_x = h->cg_x.as<double>(); ctx.Minv = h->Minv.as<double>(); ctx.tp = h->tp.as<double>(); ctx.cg_part = h->cg_part.as<double>(); ctx.cg_qp = h->cg_qp.as<double>();
+    ctx.cg_x = h->cg_x.as<double>(); ctx.Minv = h->Minv.as<double>(); ctx.tp = h->tp.as<double>(); ctx.cg_part = h->cg_part.as<double>();
     ctx.state = h->state.as<LMState>(); ctx.iters = h->iters.as<ba_iteration>();
     ctx.host_flags = h->host_flags_dev;
 #undef AL
@@ -646,6 +666,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
     }
     ctx.rhs = h->rhs.as<double>();                  // (ensure_dense moves it into the S buffer: one message [S | rhs])
     if (h->opt.linear_solver == BA_DENSE_SCHUR && (rc = ensure_dense(h))) return rc;
+    if (h->opt.linear_solver != BA_DENSE_SCHUR && (rc = ensure_pcg(h))) return rc;
     h->launches = 0;
     h->prof_used = 0;
     h->dom_used = 0; h->dom_seconds = 0.0; h->dom_launches = 0;

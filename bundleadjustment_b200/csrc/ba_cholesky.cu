@@ -166,7 +166,7 @@ __device__ __forceinline__ bool wait_ge(const int *flag, int need, int *abort_fl
 // Non-positive / non-finite pivots are replaced by 1 and reported (no hang, Ceres' LINEAR_SOLVER_FAILURE semantics
 // are applied by the LM controller).
 // -------------------------------------------------------------------------------------------------------------
-__device__ long long g_potrf_phase[4];   // tools/chol_prof.cu: accumulated ns in (A), (B), (C), calls
+__device__ long long g_potrf_phase[12];  // tools/chol_prof.cu: accumulated ns in (A), (B), (C), calls; [4..8]: clocks inside (A): load, factor sweep, scale + store L, inverse sweep, stores
 
 template <int NB>
 __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double *__restrict__ Pv, double *__restrict__ invd,
@@ -186,11 +186,17 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 #endif
         // ---- (A) ----
         if (warp == 0) {
+#ifdef CHOL_PROFILE_PHASES
+            const long long ck0 = clock64();
+#endif
             double a[PB];
             const double *row = Ts + (size_t)(c0 + lane) * LDT + c0;
 #pragma unroll
             for (int k = 0; k < PB; ++k) a[k] = row[k];
             bool bad = false;
+#ifdef CHOL_PROFILE_PHASES
+            const long long ck1 = clock64();
+#endif
             // Square-root-free sweep (L D L^T): only a reciprocal sits on the serial pivot chain.  Column j of the
             // current matrix is broadcast through shared memory (one store per lane, 16-byte broadcast loads) instead of
             // 2 x (31 - j) shuffles; column j of the unit factor stays UNSCALED in a[j] (= l_ij d_j).
@@ -213,6 +219,9 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
                     a[c + 1] = fma(-ajs, ac.y, a[c + 1]);
                 }
             }
+#ifdef CHOL_PROFILE_PHASES
+            const long long ck2 = clock64();
+#endif
             // L = (unit factor) * sqrt(D): l_ij = a_ij / sqrt(d_j)
             const double mys = sqrt(myd), myis = 1.0 / mys;
             dinv[c0 + lane] = myis;
@@ -227,6 +236,9 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
             }
             if (bad && lane == 0) s_bad = 1;
             __syncwarp();
+#ifdef CHOL_PROFILE_PHASES
+            const long long ck3 = clock64();
+#endif
             // lane = column of X = L_d^-1, right-looking forward substitution (independent FMAs per pivot);
             // x[i] = 0 for i < lane falls out of the recurrence
             double x[PB];
@@ -244,6 +256,9 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
                 }
             }
             __syncwarp();                                    // LT fully consumed before invd is rewritten
+#ifdef CHOL_PROFILE_PHASES
+            const long long ck4 = clock64();
+#endif
             double *prow = Pv + (size_t)(c0 + lane) * LDP;
 #pragma unroll
             for (int k = 0; k < PB; ++k) {
@@ -251,6 +266,16 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
                 prow[k] = x[k];                         // E row incl. its diagonal (1 / l_rr) and zeros left of it
                 invd[(size_t)k * LDP + lane] = x[k];    // X row-major: X[k][lane]
             }
+#ifdef CHOL_PROFILE_PHASES
+            if (lane == 0) {
+                const long long ck5 = clock64();
+                atomicAdd((unsigned long long *)&g_potrf_phase[4], (unsigned long long)(ck1 - ck0));
+                atomicAdd((unsigned long long *)&g_potrf_phase[5], (unsigned long long)(ck2 - ck1));
+                atomicAdd((unsigned long long *)&g_potrf_phase[6], (unsigned long long)(ck3 - ck2));
+                atomicAdd((unsigned long long *)&g_potrf_phase[7], (unsigned long long)(ck4 - ck3));
+                atomicAdd((unsigned long long *)&g_potrf_phase[8], (unsigned long long)(ck5 - ck4));
+            }
+#endif
         }
         __syncthreads();
 #ifdef CHOL_PROFILE_PHASES

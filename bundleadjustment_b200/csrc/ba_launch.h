@@ -59,6 +59,9 @@ int prep_observations(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStre
 int prep_blocks(const PrepIn &in, PrepOut &out, cudaStream_t s);                            // needs pt_ptr
 int prep_camera_major(const PrepIn &in, PrepOut &out, PrepScratch &scr, cudaStream_t s);   // needs cnt_cam_global
 int prep_chunks(const PrepIn &in, PrepOut &out, cudaStream_t s);
+// per block: its observations in camera order (blk_ord word = camera << 12 | segment start << 11 | local index); cudaErrorInvalidValue
+// when a camera index needs more than 20 bits or a block holds 2048+ observations
+int prep_block_order(const PrepOut &out, int Nc, unsigned *blk_ord, cudaStream_t s);
 int prep_pairs_count(const PrepIn &in, const PrepOut &out, PrepScratch &scr, long long *h_total, cudaStream_t s);
 int prep_pairs_build(const PrepIn &in, const PrepOut &out, PairIndex &pi, PrepScratch &scr, PrepScratch &scr2, int *h_two, cudaStream_t s);
 int prep_pairs_units(PairIndex &pi, cudaStream_t s);
@@ -101,6 +104,7 @@ void chol_plan_stats(int n, int nb, const unsigned char *nz, int *depth, long lo
 int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
 
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
+int pcg_matvec_grid(const Ctx &ctx);                          // persistent CTAs of the matvec = private copies of q (cg_qp)
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s);       // local block-diag(S) + rhs (all-reduce Minv, rhs after)
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s);       // invert blocks, x = 0, r = b
 void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s, cudaEvent_t ev_before_matvec = nullptr, cudaEvent_t ev_after_matvec = nullptr);      // z = M^-1 r, p, local landmark part of q = S p

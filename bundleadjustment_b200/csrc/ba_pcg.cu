@@ -107,7 +107,6 @@ __global__ void pcg_setup_reduce_kernel(Ctx ctx) {
 // reduced per CTA, published, and after grid.sync() EVERY CTA sums the published partials in the same fixed order, so all
 // of them hold the identical scalar and go on to the dependent vector update -- one launch instead of a single-CTA kernel
 // (which left 147 SMs idle for ~120 us per call, the dominant replicated cost on 8 GPUs).
-constexpr int CG_QCOPIES = 32;                 // private accumulation copies of the matvec result (power of two)
 constexpr int CG_THREADS = 256;
 constexpr int CG_MAX_GRID = 1024;              // partial slots (grid is capped by co-residency, far below this)
 
@@ -218,90 +217,148 @@ __global__ void __launch_bounds__(CG_THREADS) pcg_precond_kernel(Ctx ctx, double
     }
 }
 
-// q -= sum_p W_p V'^-1 W_p^T v   (v = p or x).  Tile kernel: the block's W records are read from HBM ONCE (coalesced,
-// into shared memory) and serve both halves of the product: t_o = W_o^T v_c per observation, a_p = sum over the track
-// (in track order), s_p = V'^-1 a_p per landmark, then q_c -= W_o s_p per observation (fp64 reductions into the
-// L2-resident 6 Nc vector).
-__global__ void __launch_bounds__(TILE_THREADS, 5) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp) {
+// q -= sum_p W_p V'^-1 W_p^T v   (v = p or x): the landmark part of the implicit Schur product, one pass over W.
+//
+// PERSISTENT and DETERMINISTIC.  CTA g walks a contiguous range of landmark blocks with a 2-stage TMA ring: while block b is
+// computed, the W tile of block b + 1 (one cp.async.bulk) and its index words are already on their way, so a tile buffer is
+// being filled for the whole life of the CTA.  Per block:
+//   1. thread / observation:  t_o = W_o^T v_c                      (W from shared memory, v_c gathered)
+//   2. thread / observation:  a_p = sum of its landmark's t (track order), s_p = V'^-1 a_p, contribution c_o = -W_o s_p -> smem
+//   3. thread / observation in CAMERA order (blk_ord, sorted once per problem): the first observation of each camera sums its
+//      camera's contributions in that fixed order and adds the 6-vector to the CTA's PRIVATE copy of q -- a plain
+//      read-modify-write: within a block every camera has exactly one writer, between blocks the CTA barrier orders them, and
+//      no other CTA ever touches this copy.  No floating-point atomics: the product is bit-reproducible run to run
+//      (north_star (1): "segmented reductions keyed by camera").
+// pcg_fold_kernel then adds the copies in CTA order.
+constexpr int MV_CTAS_PER_SM = 2;
+__global__ void __launch_bounds__(TILE_THREADS, MV_CTAS_PER_SM) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp,
+                                                                                         int blocks_per_cta) {
     const LMState *st = ctx.state;
     CG_GUARD(st);
-    // the reductions go to one of CG_QCOPIES private copies of the vector (by CTA): when landmarks that are neighbours in
-    // index share cameras, concurrent CTAs would otherwise serialise on the same few addresses
-    double *__restrict__ q = qp + (size_t)(blockIdx.x & (CG_QCOPIES - 1)) * ctx.n;
+    const int b0 = blockIdx.x * blocks_per_cta, b1 = min(ctx.n_blocks, b0 + blocks_per_cta);
+    if (b0 >= b1) return;
+    double *q = qp + (size_t)blockIdx.x * ctx.n;
     extern __shared__ __align__(16) double tsm[];
-    double *sW = tsm;                              // [cap][18]
-    double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]
-    const int4 bi = ctx.blk_info[blockIdx.x];
-    const int o0 = bi.z, n = bi.w;
-    if (n == 0) return;
-    // in flight across the barrier below: the thread's camera word, track word and landmark (V'^-1 on its way into L2)
-    unsigned ck_first = 0u, trk_first = 0u;
-    int p_first = 0;
-    if (threadIdx.x < n) {
-        ck_first = ctx.pm_camk[o0 + threadIdx.x]; trk_first = ctx.pm_trk[o0 + threadIdx.x]; p_first = ctx.pm_pt[o0 + threadIdx.x];
-        prefetch_l2(ctx.Vinv + 6 * (size_t)p_first);
-    }
-    // the block's W records: one TMA bulk copy (thread 0) that streams in while the threads gather their camera entries of v
-    __shared__ unsigned long long wbar;
-    if (threadIdx.x == 0) mbar_init(&wbar, 1);
+    const size_t cap = (size_t)ctx.tile_cap;
+    double *sT = tsm + 36 * cap;                   // [cap][3]
+    double *sC = sT + 3 * cap;                     // [cap][6]
+    __shared__ unsigned long long bars[2];
+    if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
     __syncthreads();
-    if (threadIdx.x == 0) bulk_load(sW, ctx.W + 18 * (size_t)o0, 144u * (unsigned)n, &wbar);
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const int k = i;
-        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
-        const int c = camk_cam(ck);
-        double a3[3] = {0, 0, 0};
-        if (camk_kind(ck) == CAM_FREE) {
-            double x[6];
-            load_row6(v, (size_t)c, x);
-            mbar_wait(&wbar, 0);
-            double Wo[18];
-            load_record18(sW, k, Wo);
-#pragma unroll
-            for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
+    int4 bi = ctx.blk_info[b0];
+    if (threadIdx.x == 0 && bi.w > 0) bulk_load(tsm, ctx.W + 18 * (size_t)bi.z, 144u * (unsigned)bi.w, &bars[0]);
+    unsigned ck_n = 0u, trk_n = 0u, ord_n = 0u;
+    int p_n = 0;
+    if ((int)threadIdx.x < bi.w) {
+        const int o = bi.z + threadIdx.x;
+        ck_n = ctx.pm_camk[o]; trk_n = ctx.pm_trk[o]; p_n = ctx.pm_pt[o]; ord_n = ctx.blk_ord[o];
+        prefetch_l2(ctx.Vinv + 6 * (size_t)p_n);
+    }
+    unsigned parity0 = 0u, parity1 = 0u;
+    for (int b = b0; b < b1; ++b) {
+        const int stage = (b - b0) & 1;
+        const int o0 = bi.z, n = bi.w;
+        const unsigned ck_first = ck_n, trk_first = trk_n, ord_first = ord_n;
+        const int p_first = p_n;
+        // the CTA's next block: W into the other stage (free since the barrier that ended the previous iteration), index words
+        // into registers
+        int4 bin = make_int4(0, 0, 0, 0);
+        if (b + 1 < b1) {
+            bin = ctx.blk_info[b + 1];
+            if (threadIdx.x == 0 && bin.w > 0)
+                bulk_load(tsm + 18 * cap * (size_t)(stage ^ 1), ctx.W + 18 * (size_t)bin.z, 144u * (unsigned)bin.w, &bars[stage ^ 1]);
+            if ((int)threadIdx.x < bin.w) {
+                const int o = bin.z + threadIdx.x;
+                ck_n = ctx.pm_camk[o]; trk_n = ctx.pm_trk[o]; p_n = ctx.pm_pt[o]; ord_n = ctx.blk_ord[o];
+                prefetch_l2(ctx.Vinv + 6 * (size_t)p_n);
+            }
         }
-        sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
-    }
-    // The thread that started the bulk copy always sees it complete before the CTA can leave the tile: a block whose
-    // observations all belong to fixed cameras has no other waiter, and a CTA must not exit with a copy in flight.
-    if (threadIdx.x == 0) mbar_wait(&wbar, 0);
-    __syncthreads();
-    // Second half, still one thread per OBSERVATION and no further barrier: every thread sums its landmark's track in track
-    // order (the position/length word says where it starts: t shared-memory reads, the same for all observations of the
-    // landmark), applies V'^-1 and scatters W_o s_p.  Redundant per observation, but all eight warps work; the former
-    // thread-per-landmark pass kept two warps busy while six waited at a second barrier (33 % of the stall samples).
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
-        if (camk_kind(ck) != CAM_FREE) continue;
-        const int c = camk_cam(ck);
-        const unsigned trk = i == (int)threadIdx.x ? trk_first : ctx.pm_trk[o0 + i];
-        const int p = i == (int)threadIdx.x ? p_first : ctx.pm_pt[o0 + i];
-        const int lo = i - (int)(trk & 0xffffu), hi = lo + (int)(trk >> 16);
-        double vi[6];
-        load_row6(ctx.Vinv, (size_t)p, vi);
-        double a3[3] = {0, 0, 0};
-        for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
-        const double t0 = vi[0] * a3[0] + vi[1] * a3[1] + vi[2] * a3[2];
-        const double t1 = vi[1] * a3[0] + vi[3] * a3[1] + vi[4] * a3[2];
-        const double t2 = vi[2] * a3[0] + vi[4] * a3[1] + vi[5] * a3[2];
-        mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
-        double Wo[18];
-        load_record18(sW, i, Wo);
+        if (n > 0) {
+            const double *sW = tsm + 18 * cap * (size_t)stage;
+            unsigned long long *bar = &bars[stage];
+            const unsigned par = stage ? parity1 : parity0;
+            // ---- 1: t_o = W_o^T v_c ----
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+                double a3[3] = {0, 0, 0};
+                if (camk_kind(ck) == CAM_FREE) {
+                    double x[6];
+                    load_row6(v, (size_t)camk_cam(ck), x);
+                    mbar_wait(bar, par);
+                    double Wo[18];
+                    load_record18(sW, i, Wo);
 #pragma unroll
-        for (int a = 0; a < 6; ++a)
-            atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
+                    for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
+                }
+                sT[3 * (size_t)i] = a3[0]; sT[3 * (size_t)i + 1] = a3[1]; sT[3 * (size_t)i + 2] = a3[2];
+            }
+            // the issuing thread always sees the copy complete in THIS phase of the barrier: the stage may only be re-armed (and its
+            // parity flipped) once nobody can still be waiting on it
+            if (threadIdx.x == 0) mbar_wait(bar, par);
+            __syncthreads();
+            // ---- 2: per observation, its landmark's s_p (redundantly per observation: all eight warps work) and c_o = -W_o s_p ----
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+                double c6[6] = {0, 0, 0, 0, 0, 0};
+                if (camk_kind(ck) == CAM_FREE) {
+                    const unsigned trk = i == (int)threadIdx.x ? trk_first : ctx.pm_trk[o0 + i];
+                    const int p = i == (int)threadIdx.x ? p_first : ctx.pm_pt[o0 + i];
+                    const int lo = i - (int)(trk & 0xffffu), hi = lo + (int)(trk >> 16);
+                    double vi[6];
+                    load_row6(ctx.Vinv, (size_t)p, vi);
+                    double a3[3] = {0, 0, 0};
+                    for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
+                    const double t0 = vi[0] * a3[0] + vi[1] * a3[1] + vi[2] * a3[2];
+                    const double t1 = vi[1] * a3[0] + vi[3] * a3[1] + vi[4] * a3[2];
+                    const double t2 = vi[2] * a3[0] + vi[4] * a3[1] + vi[5] * a3[2];
+                    double Wo[18];
+                    load_record18(sW, i, Wo);
+#pragma unroll
+                    for (int a = 0; a < 6; ++a) c6[a] = -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2);
+                }
+                double2 *dst = reinterpret_cast<double2 *>(sC + 6 * (size_t)i);
+                dst[0] = make_double2(c6[0], c6[1]); dst[1] = make_double2(c6[2], c6[3]); dst[2] = make_double2(c6[4], c6[5]);
+            }
+            __syncthreads();
+            // ---- 3: camera-keyed ordered fold into the CTA's private copy of q ----
+            for (int j = threadIdx.x; j < n; j += blockDim.x) {
+                const unsigned w = j == (int)threadIdx.x ? ord_first : ctx.blk_ord[o0 + j];
+                if (!(w & 2048u)) continue;                                  // not the first observation of its camera in this block
+                const unsigned cam = w >> 12;
+                double acc[6];
+                {
+                    const double2 *src = reinterpret_cast<const double2 *>(sC + 6 * (size_t)(w & 2047u));
+                    const double2 u0 = src[0], u1 = src[1], u2 = src[2];
+                    acc[0] = u0.x; acc[1] = u0.y; acc[2] = u1.x; acc[3] = u1.y; acc[4] = u2.x; acc[5] = u2.y;
+                }
+                for (int k = j + 1; k < n; ++k) {
+                    const unsigned wk = ctx.blk_ord[o0 + k];
+                    if (wk & 2048u) break;                                   // next camera's segment
+                    const double2 *src = reinterpret_cast<const double2 *>(sC + 6 * (size_t)(wk & 2047u));
+                    const double2 u0 = src[0], u1 = src[1], u2 = src[2];
+                    acc[0] += u0.x; acc[1] += u0.y; acc[2] += u1.x; acc[3] += u1.y; acc[4] += u2.x; acc[5] += u2.y;
+                }
+                double2 *dst = reinterpret_cast<double2 *>(q + 6 * (size_t)cam);
+                double2 r0 = dst[0], r1 = dst[1], r2 = dst[2];
+                r0.x += acc[0]; r0.y += acc[1]; r1.x += acc[2]; r1.y += acc[3]; r2.x += acc[4]; r2.y += acc[5];
+                dst[0] = r0; dst[1] = r1; dst[2] = r2;
+            }
+            if (stage) parity1 ^= 1u; else parity0 ^= 1u;
+        }
+        __syncthreads();                           // sT, sC and this stage's W tile are free again; q updates ordered before the next block's
+        bi = bin;
     }
 }
 
 // out = sum of the private copies (fixed order), copies zeroed for the next product
-__global__ void pcg_fold_kernel(Ctx ctx, double *__restrict__ qp, double *__restrict__ out) {
+__global__ void pcg_fold_kernel(Ctx ctx, double *__restrict__ qp, double *__restrict__ out, int copies) {
     const LMState *st = ctx.state;
     CG_GUARD(st);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= ctx.n) return;
     double t = 0.0;
-#pragma unroll
-    for (int k = 0; k < CG_QCOPIES; ++k) { t += qp[(size_t)k * ctx.n + i]; qp[(size_t)k * ctx.n + i] = 0.0; }
+#pragma unroll 8
+    for (int k = 0; k < copies; ++k) { t += qp[(size_t)k * ctx.n + i]; qp[(size_t)k * ctx.n + i] = 0.0; }
     out[i] = t;
 }
 
@@ -412,14 +469,23 @@ void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
     if (ctx.n_chunks > 0) pcg_setup_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx);
     pcg_setup_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
 }
-static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 21 * (size_t)ctx.tile_cap; }
+static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 45 * (size_t)ctx.tile_cap; }   // 2 x 18 (W ring) + 3 (t) + 6 (c)
+// persistent CTAs of the matvec (= private copies of q): MV_CTAS_PER_SM per SM when shared memory allows, never more than blocks
+int pcg_matvec_grid(const Ctx &ctx) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int per_sm = pcg_tile_smem(ctx) * MV_CTAS_PER_SM + 4096 <= 227 * 1024 ? MV_CTAS_PER_SM : 1;
+    return std::max(1, std::min(ctx.n_blocks, std::max(sms, 1) * per_sm));
+}
 int pcg_tiles_init(const Ctx &ctx) {
     return (int)cudaFuncSetAttribute(pcg_matvec_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_tile_smem(ctx));
 }
 // local landmark part of  qp -= W V'^-1 W^T v
 static void launch_matvec(const Ctx &ctx, const double *v, cudaStream_t s) {
-    if (ctx.n_blocks <= 0) return;
-    pcg_matvec_points_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, v, ctx.cg_qp);
+    if (ctx.n_blocks <= 0 || ctx.mv_grid <= 0) return;
+    const int per = (ctx.n_blocks + ctx.mv_grid - 1) / ctx.mv_grid;
+    pcg_matvec_points_kernel<<<ctx.mv_grid, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, v, ctx.cg_qp, per);
 }
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s) {
     pcg_invert_blocks_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
@@ -449,7 +515,7 @@ void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s, cudaEvent_t ev0, cudaEven
     if (ev0) cudaEventRecord(ev0, s);
     launch_matvec(ctx, ctx.cg_p, s);
     if (ev1) cudaEventRecord(ev1, s);
-    pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_q);
+    pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_q, ctx.mv_grid);
 }
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
     Ctx c = ctx;
@@ -459,7 +525,7 @@ void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s) {
 }
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part of S x into cg_z
     launch_matvec(ctx, ctx.cg_x, s);
-    pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_z);
+    pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_z, ctx.mv_grid);
 }
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
 void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<std::max(1, std::min(cdiv(ctx.n, 2 * RED_THREADS), 256)), RED_THREADS, 0, s>>>(ctx); }

@@ -418,6 +418,48 @@ int prep_group_map(const PairIndex &pi, int G, int cams_per_tile, unsigned char 
     return (int)cudaGetLastError();
 }
 
+// Camera-sorted order of every landmark block's observations (PCG matvec: contributions to q are folded per camera in THIS
+// fixed order, one writer per (block, camera) -- no floating-point atomics, bit-reproducible).  One CTA per block: bitonic sort
+// of (camera << 11 | local index) in shared memory.  Output word: camera << 12 | (first of its camera in the block) << 11 |
+// local index.  Needs cameras < 2^20 and blocks < 2048 observations (checked by the caller).
+__global__ void __launch_bounds__(256) block_order_kernel(const int4 *__restrict__ blk_info, const int *__restrict__ pm_cam, unsigned *__restrict__ blk_ord, int n2) {
+    extern __shared__ unsigned keys[];
+    const int4 bi = blk_info[blockIdx.x];
+    const int o0 = bi.z, n = bi.w;
+    if (n <= 0) return;
+    int m = 1;
+    while (m < n) m <<= 1;                                   // this block's power of two (<= n2)
+    for (int i = threadIdx.x; i < m; i += blockDim.x) keys[i] = i < n ? ((unsigned)pm_cam[o0 + i] << 11) | (unsigned)i : 0xffffffffu;
+    __syncthreads();
+    for (int k = 2; k <= m; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < m; i += blockDim.x) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const unsigned a = keys[i], b = keys[l];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up) { keys[i] = b; keys[l] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned key = keys[i], cam = key >> 11, idx = key & 2047u;
+        const bool start = i == 0 || (keys[i - 1] >> 11) != cam;
+        blk_ord[o0 + i] = (cam << 12) | (start ? 2048u : 0u) | idx;
+    }
+    (void)n2;
+}
+
+int prep_block_order(const PrepOut &out, int Nc, unsigned *blk_ord, cudaStream_t s) {
+    if (out.n_blocks <= 0 || out.max_block_obs <= 0) return 0;
+    if (Nc >= (1 << 20) || out.max_block_obs >= 2048) return (int)cudaErrorInvalidValue;
+    int n2 = 1;
+    while (n2 < out.max_block_obs) n2 <<= 1;
+    block_order_kernel<<<out.n_blocks, 256, sizeof(unsigned) * (size_t)n2, s>>>(out.blk_info, out.pm_cam, blk_ord, n2);
+    return (int)cudaGetLastError();
+}
+
 int prep_pairs_units(PairIndex &pi, cudaStream_t s) {
     if (pi.n_seg > 0)
         pair_unit_fill_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.P, pi.seg_beg, pi.seg_cams, pi.unit_ptr, pi.unit_seg, pi.unit_beg);

@@ -94,6 +94,7 @@ struct Ctx {
     const int *pm_cam;
     const unsigned *pm_camk; // [No] camera | kind << 30 (CAM_* of that camera): what the per-observation kernels read
     const unsigned *pm_trk;  // [No] position inside the landmark's track | track length << 16
+    const unsigned *blk_ord; // [No] per landmark block: its observations in camera order (PCG matvec; built on first PCG solve)
     const int *pm_pt;
     const int *pt_ptr;       // [Np+1]
     const int *blk_first_pt; // [n_blocks+1] landmark blocks (whole landmarks, <= tile_cap observations)
@@ -148,7 +149,8 @@ struct Ctx {
     // PCG work vectors (n each) and block-Jacobi preconditioner
     double *cg_r, *cg_p, *cg_z, *cg_q, *cg_x, *Minv, *tp;
     double *cg_part;         // [1024] per-CTA partials of the cooperative CG kernels
-    double *cg_qp;           // [32][n] private accumulation copies of the matvec (all zero between products)
+    double *cg_qp;           // [mv_grid][n] private accumulation copies of the matvec, one per persistent CTA (all zero between products)
+    int mv_grid;             // persistent CTAs of the PCG matvec
     // control
     LMState *state;
     ba_iteration *iters;     // [max_num_iterations + 2]

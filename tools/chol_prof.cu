@@ -75,8 +75,13 @@ int main(int argc, char **argv) {
            (tend - t0) * 1e-6, max_p1 * 1e-6, s_p1 / grid * 1e-6, s_w1 / grid * 1e-6, s_trsm / grid * 1e-6);
     printf("  potrf: %.1f us per diagonal tile (%d tiles); phase 2 (back substitution) %.3f ms, mean wait there %.3f ms; tasks %.0f\n",
            s_potrf / potrf_tiles * 1e-3, T, (tend - t0 - max_p1) * 1e-6, s_w2 / grid * 1e-6, s_tasks);
-    long long ph[4];
+    long long ph[12];
     cudaMemcpyFromSymbol(ph, g_potrf_phase, sizeof(ph));
-    if (ph[3]) printf("  potrf phases per tile: (A) %.1f us  (B) %.1f us  (C) %.1f us  over %lld calls\n", ph[0] * 1e-3 / ph[3], ph[1] * 1e-3 / ph[3], ph[2] * 1e-3 / ph[3], ph[3]);
+    if (ph[3]) {
+        printf("  potrf phases per tile: (A) %.1f us  (B) %.1f us  (C) %.1f us  over %lld calls\n", ph[0] * 1e-3 / ph[3], ph[1] * 1e-3 / ph[3], ph[2] * 1e-3 / ph[3], ph[3]);
+        const double panels = (double)ph[3] * (nb / 32);
+        printf("  inside (A), SM clocks per 32 x 32 panel: load %.0f  factor sweep %.0f  scale + store L %.0f  inverse sweep %.0f  stores %.0f\n",
+               ph[4] / panels, ph[5] / panels, ph[6] / panels, ph[7] / panels, ph[8] / panels);
+    }
     return 0;
 }
