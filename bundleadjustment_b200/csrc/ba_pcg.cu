@@ -239,9 +239,9 @@ __global__ void __launch_bounds__(TILE_THREADS, MV_CTAS_PER_SM) pcg_matvec_point
     if (b0 >= b1) return;
     double *q = qp + (size_t)blockIdx.x * ctx.n;
     extern __shared__ __align__(16) double tsm[];
-    const size_t cap = (size_t)ctx.tile_cap;
+    const size_t cap = ((size_t)ctx.tile_cap + 1) & ~(size_t)1;      // even: every region below stays 16-byte aligned
     double *sT = tsm + 36 * cap;                   // [cap][3]
-    double *sC = sT + 3 * cap;                     // [cap][6]
+    double *sC = sT + 4 * cap;                     // [cap][6] (double2 accesses)
     __shared__ unsigned long long bars[2];
     if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
     __syncthreads();
@@ -469,7 +469,7 @@ void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
     if (ctx.n_chunks > 0) pcg_setup_cams_kernel<<<cdiv(ctx.n_chunks * 32, 128), 128, 0, s>>>(ctx);
     pcg_setup_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
 }
-static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 45 * (size_t)ctx.tile_cap; }   // 2 x 18 (W ring) + 3 (t) + 6 (c)
+static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 46 * (((size_t)ctx.tile_cap + 1) & ~(size_t)1); }   // 2 x 18 (W ring) + 4 (t, padded) + 6 (c)
 // persistent CTAs of the matvec (= private copies of q): MV_CTAS_PER_SM per SM when shared memory allows, never more than blocks
 int pcg_matvec_grid(const Ctx &ctx) {
     int dev = 0, sms = 0;
