@@ -20,7 +20,7 @@ EXPORTS = [
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
     "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
     "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile", "ba_set_reduced_system_mode",
-    "ba_solve_pose_only_outer", "ba_solve_outer", "ba_set_reduced_system_tile", "ba_dense_spd_solve_tile", "ba_release_workspace", "ba_workspace_launch_count",
+    "ba_solve_pose_only_outer", "ba_solve_outer", "ba_set_reduced_system_tile", "ba_dense_spd_solve_tile", "ba_set_pcg_mode", "ba_release_workspace", "ba_workspace_launch_count",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
     "ba_pose_to_cam", "ba_cam_to_pose",
 ]
@@ -161,6 +161,10 @@ class Solver:
     def set_reduced_system_tile(self, tile_edge: int = 0):
         """Cholesky tile edge of the reduced system: 0 = automatic, 64 or 128 = forced."""
         _check(lib.ba_set_reduced_system_tile(self._h, int(tile_edge)), "ba_set_reduced_system_tile")
+
+    def set_pcg_mode(self, mode: int = 0):
+        """PCG matvec accumulation: 0 automatic, 1 ordered (bit-reproducible), 2 f64 atomics."""
+        _check(lib.ba_set_pcg_mode(self._h, int(mode)), "ba_set_pcg_mode")
 
     def set_profiling(self, on: bool = True):
         _check(lib.ba_set_profiling(self._h, int(on)), "ba_set_profiling")

@@ -97,6 +97,7 @@ struct ba_handle {
     bool pairs_built = false;
     bool natural_tile_order = false, dense_tiles = false;   // ba_set_reduced_system_mode (explicit API, never the environment)
     int tile_edge = 0, tile_nb = 128;                       // requested (0 = automatic) / chosen Cholesky tile edge
+    int pcg_mode = 0;                                       // ba_set_pcg_mode: 0 automatic, 1 ordered (bit-reproducible), 2 atomic
     CholPlan chol_plan;              // tile-sparsity plan of the reduced camera matrix (dense Schur)
     DevBuf tile_map, cam_row, row_src, yperm;
     int *h_prep = nullptr;           // pinned [8]
@@ -271,6 +272,12 @@ int ensure_pcg(ba_handle *h) {
         if (rc == (int)cudaErrorInvalidValue) return fail(BA_ERR_INVALID, "the iterative solver supports up to 2^20 cameras and landmark blocks below 2048 observations");
         if (rc) return fail(BA_ERR_CUDA, "prep_block_order: %s", cudaGetErrorString((cudaError_t)rc));
         ctx.blk_ord = h->blk_ord.as<unsigned>();
+        // Matvec accumulation (ba_set_pcg_mode): the ordered kernel is bit-reproducible (no floating-point atomics) but keeps one
+        // private copy of q per persistent CTA; once those no longer fit in L2 every read-modify-write of a far camera goes to
+        // DRAM (K5: 296 x 624 KB = 185 MB, 2.56 ms per launch against 1.61 ms -- profiles/r02_K5_matvec_ordered_ncu.txt), so
+        // the automatic mode uses it up to 48 MB of copies and the atomic kernel beyond.
+        ctx.pcg_ordered = h->pcg_mode == 1 || (h->pcg_mode == 0 && pcg_ordered_copy_bytes(ctx) <= ((size_t)48 << 20));
+        if (sizeof(double) * 46 * (size_t)(ctx.tile_cap + 1) > 227 * 1024) ctx.pcg_ordered = 0;      // blocks too long for the two-stage ring
         ctx.mv_grid = pcg_matvec_grid(ctx);
         CU(h->cg_qp.alloc(8 * (size_t)ctx.mv_grid * std::max<size_t>((size_t)ctx.n, 1)));
         CU(cudaMemsetAsync(h->cg_qp.p, 0, h->cg_qp.bytes, s));
@@ -857,6 +864,15 @@ extern "C" int ba_solve_outer(ba_handle *h, int32_t n_outer, const uint8_t *cam_
     CU(cudaGetLastError());
     h->launches = launches;
     if (summary) { *summary = sm; summary->seconds_total = seconds; }
+    return BA_OK;
+}
+
+// Accumulation of the PCG matvec: 0 = automatic, 1 = ordered (camera-keyed fold, bit-reproducible), 2 = f64 atomics.
+extern "C" int ba_set_pcg_mode(ba_handle *h, int32_t mode) {
+    if (!h) return fail(BA_ERR_INVALID, "handle is NULL");
+    if (mode < 0 || mode > 2) return fail(BA_ERR_INVALID, "mode must be 0 (automatic), 1 (ordered) or 2 (atomic)");
+    h->pcg_mode = mode;
+    h->ord_built = false;
     return BA_OK;
 }
 

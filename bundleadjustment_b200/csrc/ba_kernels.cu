@@ -456,33 +456,23 @@ __global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
 // writer (schur_segments_kernel), so the reduced system is bit-reproducible run to run.
 // Traffic per entry: 2 x 144 B of W + 48 B V'^-1 (+ 24 B on diagonal blocks); consecutive segments share cameras, so all
 // but the first touch of a W block come from L2.
-constexpr int SCHUR_WARPS = 2;               // warps per CTA (each warp is independent: its own staging ring, no CTA barrier)
+constexpr int SCHUR_WARPS = 4;
 constexpr int SCHUR_K = 96;                  // stacked reduction index of one batch: 32 entries x 3 landmark coordinates
 constexpr int SCHUR_LD = SCHUR_K + 4;        // row stride 100 doubles: 100 mod 16 == 4 -> conflict-free DMMA fragment loads
 // The block of one camera pair is  sum_e Y_e W_b,e^T  with Y_e = W_a,e V'^-1 (6 x 3): stacked over the entries this is ONE
 // small GEMM  [Y_1 .. Y_E] (6 x 3E) * [W_b,1 .. W_b,E]^T (3E x 6), so the reduction over entries runs on the FP64 tensor
 // pipe (DMMA m8n8k4, 6 of 8 rows/columns used; column 6 carries the stacked b_p, which makes rhs_c -= W V'^-1 b_p fall out
-// of the same product).
-// Shared-memory staging (north_star (2)): the rows an entry needs -- W_a, W_b (144 B each) and V'^-1 (48 B) -- are scattered
-// over the landmark-major arrays, so every lane streams ITS entry's rows into a per-warp shared-memory stage with 16-byte
-// cp.async copies (no registers, no L1 allocation), one batch of 32 entries AHEAD of the batch being multiplied; the index
-// words run two batches ahead.  Per warp 2 x 10.5 KB are in flight at any time, which is what hides the L2 / HBM latency that
-// bound the register-gather version (occupancy 21 %, L1/TEX 80 % busy, 1.6 x the algorithmic DRAM traffic).
-struct __align__(16) SchurStage { double wa[32 * 18]; double wb[32 * 18]; double vi[32 * 6]; };      // 10 752 B
-static_assert(sizeof(SchurStage) == 10752, "SchurStage layout");
-struct SchurWarp { SchurStage st[2]; double sY[6 * SCHUR_LD]; double sB[7 * SCHUR_LD]; };               // 31 904 B
-constexpr int SCHUR_SMEM = SCHUR_WARPS * (int)sizeof(SchurWarp);
-
-__device__ __forceinline__ void cp_async16_cg(void *smem, const void *gmem) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_addr(smem)), "l"(gmem));
-}
-
+// of the same product).  Per batch of 32 entries each lane gathers its entry's rows, forms Y in registers and parks Y and
+// W_b k-major in shared memory; the warp then issues <= 24 DMMAs.  Two accumulator registers per lane instead of 42.
+// (Tried in round 2 and dropped after measuring: streaming each entry's rows into a per-warp shared-memory stage with cp.async one
+// batch ahead -- 32 KB of shared memory per warp leaves 6 warps per SM, 807 us on K4 against 381 us for this register-gather
+// form at 13 warps per SM: profiles/r02_K4_schur_units_cpasync_ncu.txt.)
 __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, int force) {
     const LMState *st = ctx.state;
     if (!force && st->done) return;
-    extern __shared__ __align__(16) unsigned char schur_smem[];
+    __shared__ __align__(16) double sY[SCHUR_WARPS][6 * SCHUR_LD];      // [a][k]: Y_e[a][q] at k = 3 e + q
+    __shared__ __align__(16) double sB[SCHUR_WARPS][7 * SCHUR_LD];      // [b][k]: W_b,e[b][q]; row 6: b_p of self entries
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    SchurWarp &sw = reinterpret_cast<SchurWarp *>(schur_smem)[warp];
     const int g = lane >> 2, tig = lane & 3;
     const int u = blockIdx.x * SCHUR_WARPS + warp;
     const PairIndex &pi = ctx.pairs;
@@ -491,64 +481,25 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
     const long long beg = pi.unit_beg[u];
     const long long end = beg + (info >> 1);
     const bool diag = info & 1;
-    double *Ys = sw.sY, *Bs = sw.sB;
+    double *Ys = sY[warp], *Bs = sB[warp];
     double acc[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};                // C[g][2 tig], C[g][2 tig + 1]: four independent DMMA chains
-    // index words: batch k+2 is loaded while batch k+1's rows are requested and batch k is multiplied
-    int2 ob_cur = make_int2(0, 0), ob_nx = make_int2(0, 0), ob_n2 = make_int2(0, 0);
-    int p_cur = 0, p_nx = 0, p_n2 = 0;
-    const auto load_index = [&](long long e, int2 &ob, int &p) {
-        if (e < end) { ob = pi.pair_obs[e]; p = ctx.pm_pt[ob.x]; }
-    };
-    // this lane's rows of one batch -> stage (nothing for dead lanes: their stage slots are never read)
-    const auto request_rows = [&](SchurStage &sg, bool live, int2 ob, int p) {
-        if (live) {
-            const double *wa = ctx.W + 18 * (size_t)ob.x, *wb = ctx.W + 18 * (size_t)ob.y, *vi = ctx.Vinv + 6 * (size_t)p;
-#pragma unroll
-            for (int q = 0; q < 9; ++q) cp_async16_cg(sg.wa + 18 * lane + 2 * q, wa + 2 * q);
-            if (ob.x != ob.y) {
-#pragma unroll
-                for (int q = 0; q < 9; ++q) cp_async16_cg(sg.wb + 18 * lane + 2 * q, wb + 2 * q);
-            }
-#pragma unroll
-            for (int q = 0; q < 3; ++q) cp_async16_cg(sg.vi + 6 * lane + 2 * q, vi + 2 * q);
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-    load_index(beg + lane, ob_cur, p_cur);
-    load_index(beg + 32 + lane, ob_nx, p_nx);
-    request_rows(sw.st[0], beg + lane < end, ob_cur, p_cur);
-    int sidx = 0;
-    for (long long base = beg; base < end; base += 32, sidx ^= 1) {
-        const long long e = base + lane;
+    long long e = beg + lane;
+    int2 ob_n = make_int2(0, 0);
+    int p_n = 0;
+    if (e < end) { ob_n = pi.pair_obs[e]; p_n = ctx.pm_pt[ob_n.x]; }
+    for (long long base = beg; base < end; base += 32, e += 32) {
         const bool live = e < end;
-        const int2 ob = ob_cur;
-        const int p = p_cur;
-        // rows of the next batch (its indices arrived during the previous iteration), indices of the one after
-        load_index(e + 64, ob_n2, p_n2);
-        request_rows(sw.st[sidx ^ 1], e + 32 < end, ob_nx, p_nx);
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");           // this batch's rows have landed (this lane's copies)
-        const SchurStage &sg = sw.st[sidx];
+        const int2 ob = live ? ob_n : make_int2(0, 0);                  // dead lanes read row 0 (finite data) and contribute Y = 0
+        const int p = live ? p_n : 0;
+        if (e + 32 < end) { ob_n = pi.pair_obs[e + 32]; p_n = ctx.pm_pt[ob_n.x]; }
+        // gathers as aligned 256-bit windows (12 sector requests per entry instead of 21); W_b is W_a on self entries
         double vi[6], wa[18], wb[18];
-        if (live) {
-            const double2 *a2 = reinterpret_cast<const double2 *>(sg.wa + 18 * lane);
+        load_row6(ctx.Vinv, (size_t)p, vi);
+        load_row18(ctx.W, (size_t)ob.x, wa);
+        if (ob.x != ob.y) load_row18(ctx.W, (size_t)ob.y, wb);
+        else {
 #pragma unroll
-            for (int q = 0; q < 9; ++q) { const double2 t = a2[q]; wa[2 * q] = t.x; wa[2 * q + 1] = t.y; }
-            if (ob.x != ob.y) {
-                const double2 *b2 = reinterpret_cast<const double2 *>(sg.wb + 18 * lane);
-#pragma unroll
-                for (int q = 0; q < 9; ++q) { const double2 t = b2[q]; wb[2 * q] = t.x; wb[2 * q + 1] = t.y; }
-            } else {
-#pragma unroll
-                for (int k = 0; k < 18; ++k) wb[k] = wa[k];
-            }
-            const double2 *v2 = reinterpret_cast<const double2 *>(sg.vi + 6 * lane);
-#pragma unroll
-            for (int q = 0; q < 3; ++q) { const double2 t = v2[q]; vi[2 * q] = t.x; vi[2 * q + 1] = t.y; }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 18; ++k) { wa[k] = 0.0; wb[k] = 0.0; }
-#pragma unroll
-            for (int k = 0; k < 6; ++k) vi[k] = 0.0;
+            for (int k = 0; k < 18; ++k) wb[k] = wa[k];
         }
         double b3[3] = {0.0, 0.0, 0.0};
         if (diag && live && ob.x == ob.y) {                             // the observation itself: its share of the rhs
@@ -556,10 +507,11 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
             b3[0] = bp[0]; b3[1] = bp[1]; b3[2] = bp[2];
         }
         __syncwarp();                                                   // previous batch's DMMAs have consumed the buffers
+        const double lv = live ? 1.0 : 0.0;
 #pragma unroll
         for (int h = 0; h < 3; ++h) {                                   // rows 2h, 2h+1 of W_a
-            const double r0[3] = {wa[6 * h], wa[6 * h + 1], wa[6 * h + 2]};
-            const double r1[3] = {wa[6 * h + 3], wa[6 * h + 4], wa[6 * h + 5]};
+            const double r0[3] = {wa[6 * h] * lv, wa[6 * h + 1] * lv, wa[6 * h + 2] * lv};
+            const double r1[3] = {wa[6 * h + 3] * lv, wa[6 * h + 4] * lv, wa[6 * h + 5] * lv};
             double *y0 = Ys + (2 * h) * SCHUR_LD + 3 * lane, *y1 = y0 + SCHUR_LD;
             y0[0] = r0[0] * vi[0] + r0[1] * vi[1] + r0[2] * vi[2];
             y0[1] = r0[0] * vi[1] + r0[1] * vi[3] + r0[2] * vi[4];
@@ -593,9 +545,7 @@ __global__ void __launch_bounds__(SCHUR_WARPS * 32) schur_units_kernel(Ctx ctx, 
             const double bv = brow ? Bs[g * SCHUR_LD + 4 * s4 + tig] : 0.0;
             dmma884_acc(acc[0][0], acc[0][1], av, bv);
         }
-        ob_cur = ob_nx; p_cur = p_nx; ob_nx = ob_n2; p_nx = p_n2;
     }
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     const double c0 = (acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]), c1 = (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]);
     double *dst = pi.unit_part + 42 * (size_t)u;
     if (g < 6) {
@@ -1025,8 +975,6 @@ int tiles_init(const Ctx &ctx) {
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem(ctx, 21));
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(schur_units_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SCHUR_SMEM);
-    if (e != cudaSuccess) return (int)e;
     return pcg_tiles_init(ctx);
 }
 
@@ -1071,7 +1019,7 @@ void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) 
     const int force = radius_override > 0;
     schur_init_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, radius_override);
     if (ctx.pairs.n_units > 0) {
-        schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, SCHUR_SMEM, s>>>(ctx, force);
+        schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, 0, s>>>(ctx, force);
         schur_segments_kernel<<<(unsigned)(((long long)ctx.pairs.n_seg * 42 + 255) / 256), 256, 0, s>>>(ctx, force);
     }
 }

@@ -104,7 +104,8 @@ void chol_plan_stats(int n, int nb, const unsigned char *nz, int *depth, long lo
 int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
 
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
-int pcg_matvec_grid(const Ctx &ctx);                          // persistent CTAs of the matvec = private copies of q (cg_qp)
+int pcg_matvec_grid(const Ctx &ctx);                          // private copies of q (cg_qp) for ctx.pcg_ordered
+size_t pcg_ordered_copy_bytes(const Ctx &ctx);                // bytes of the ordered kernel's private copies for this problem
 void launch_pcg_setup(const Ctx &ctx, cudaStream_t s);       // local block-diag(S) + rhs (all-reduce Minv, rhs after)
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s);       // invert blocks, x = 0, r = b
 void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s, cudaEvent_t ev_before_matvec = nullptr, cudaEvent_t ev_after_matvec = nullptr);      // z = M^-1 r, p, local landmark part of q = S p

@@ -217,6 +217,82 @@ __global__ void __launch_bounds__(CG_THREADS) pcg_precond_kernel(Ctx ctx, double
     }
 }
 
+// q -= sum_p W_p V'^-1 W_p^T v   (v = p or x), ATOMIC variant (pcg mode 2; the default when the ordered kernel's private copies
+// of q would not fit in L2).  Tile kernel: the block's W records are read from HBM ONCE (coalesced,
+// into shared memory) and serve both halves of the product: t_o = W_o^T v_c per observation, a_p = sum over the track
+// (in track order), s_p = V'^-1 a_p per landmark, then q_c -= W_o s_p per observation (fp64 reductions into the
+// L2-resident 6 Nc vector).
+__global__ void __launch_bounds__(TILE_THREADS, 5) pcg_matvec_atomic_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp) {
+    const LMState *st = ctx.state;
+    CG_GUARD(st);
+    // the reductions go to one of CG_QCOPIES private copies of the vector (by CTA): when landmarks that are neighbours in
+    // index share cameras, concurrent CTAs would otherwise serialise on the same few addresses
+    double *__restrict__ q = qp + (size_t)(blockIdx.x % (unsigned)ctx.mv_grid) * ctx.n;
+    extern __shared__ __align__(16) double tsm[];
+    double *sW = tsm;                              // [cap][18]
+    double *sT = tsm + 18 * (size_t)ctx.tile_cap;  // [cap][3]
+    const int4 bi = ctx.blk_info[blockIdx.x];
+    const int o0 = bi.z, n = bi.w;
+    if (n == 0) return;
+    // in flight across the barrier below: the thread's camera word, track word and landmark (V'^-1 on its way into L2)
+    unsigned ck_first = 0u, trk_first = 0u;
+    int p_first = 0;
+    if (threadIdx.x < n) {
+        ck_first = ctx.pm_camk[o0 + threadIdx.x]; trk_first = ctx.pm_trk[o0 + threadIdx.x]; p_first = ctx.pm_pt[o0 + threadIdx.x];
+        prefetch_l2(ctx.Vinv + 6 * (size_t)p_first);
+    }
+    // the block's W records: one TMA bulk copy (thread 0) that streams in while the threads gather their camera entries of v
+    __shared__ unsigned long long wbar;
+    if (threadIdx.x == 0) mbar_init(&wbar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) bulk_load(sW, ctx.W + 18 * (size_t)o0, 144u * (unsigned)n, &wbar);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int k = i;
+        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+        const int c = camk_cam(ck);
+        double a3[3] = {0, 0, 0};
+        if (camk_kind(ck) == CAM_FREE) {
+            double x[6];
+            load_row6(v, (size_t)c, x);
+            mbar_wait(&wbar, 0);
+            double Wo[18];
+            load_record18(sW, k, Wo);
+#pragma unroll
+            for (int a = 0; a < 6; ++a) { a3[0] += Wo[a * 3] * x[a]; a3[1] += Wo[a * 3 + 1] * x[a]; a3[2] += Wo[a * 3 + 2] * x[a]; }
+        }
+        sT[3 * (size_t)k] = a3[0]; sT[3 * (size_t)k + 1] = a3[1]; sT[3 * (size_t)k + 2] = a3[2];
+    }
+    // The thread that started the bulk copy always sees it complete before the CTA can leave the tile: a block whose
+    // observations all belong to fixed cameras has no other waiter, and a CTA must not exit with a copy in flight.
+    if (threadIdx.x == 0) mbar_wait(&wbar, 0);
+    __syncthreads();
+    // Second half, still one thread per OBSERVATION and no further barrier: every thread sums its landmark's track in track
+    // order (the position/length word says where it starts: t shared-memory reads, the same for all observations of the
+    // landmark), applies V'^-1 and scatters W_o s_p.  Redundant per observation, but all eight warps work; the former
+    // thread-per-landmark pass kept two warps busy while six waited at a second barrier (33 % of the stall samples).
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned ck = i == (int)threadIdx.x ? ck_first : ctx.pm_camk[o0 + i];
+        if (camk_kind(ck) != CAM_FREE) continue;
+        const int c = camk_cam(ck);
+        const unsigned trk = i == (int)threadIdx.x ? trk_first : ctx.pm_trk[o0 + i];
+        const int p = i == (int)threadIdx.x ? p_first : ctx.pm_pt[o0 + i];
+        const int lo = i - (int)(trk & 0xffffu), hi = lo + (int)(trk >> 16);
+        double vi[6];
+        load_row6(ctx.Vinv, (size_t)p, vi);
+        double a3[3] = {0, 0, 0};
+        for (int k = lo; k < hi; ++k) { a3[0] += sT[3 * (size_t)k]; a3[1] += sT[3 * (size_t)k + 1]; a3[2] += sT[3 * (size_t)k + 2]; }
+        const double t0 = vi[0] * a3[0] + vi[1] * a3[1] + vi[2] * a3[2];
+        const double t1 = vi[1] * a3[0] + vi[3] * a3[1] + vi[4] * a3[2];
+        const double t2 = vi[2] * a3[0] + vi[4] * a3[1] + vi[5] * a3[2];
+        mbar_wait(&wbar, 0);                       // (a thread whose camera was fixed in the first pass never waited)
+        double Wo[18];
+        load_record18(sW, i, Wo);
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+            atomicAdd(q + 6 * (size_t)c + a, -(Wo[a * 3] * t0 + Wo[a * 3 + 1] * t1 + Wo[a * 3 + 2] * t2));
+    }
+}
+
 // q -= sum_p W_p V'^-1 W_p^T v   (v = p or x): the landmark part of the implicit Schur product, one pass over W.
 //
 // PERSISTENT and DETERMINISTIC.  CTA g walks a contiguous range of landmark blocks with a 2-stage TMA ring: while block b is
@@ -231,8 +307,8 @@ __global__ void __launch_bounds__(CG_THREADS) pcg_precond_kernel(Ctx ctx, double
 //      (north_star (1): "segmented reductions keyed by camera").
 // pcg_fold_kernel then adds the copies in CTA order.
 constexpr int MV_CTAS_PER_SM = 2;
-__global__ void __launch_bounds__(TILE_THREADS, MV_CTAS_PER_SM) pcg_matvec_points_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp,
-                                                                                         int blocks_per_cta) {
+__global__ void __launch_bounds__(TILE_THREADS, MV_CTAS_PER_SM) pcg_matvec_ordered_kernel(Ctx ctx, const double *__restrict__ v, double *__restrict__ qp,
+                                                                                          int blocks_per_cta) {
     const LMState *st = ctx.state;
     CG_GUARD(st);
     const int b0 = blockIdx.x * blocks_per_cta, b1 = min(ctx.n_blocks, b0 + blocks_per_cta);
@@ -470,22 +546,38 @@ void launch_pcg_setup(const Ctx &ctx, cudaStream_t s) {
     pcg_setup_reduce_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);
 }
 static inline size_t pcg_tile_smem(const Ctx &ctx) { return sizeof(double) * 46 * (((size_t)ctx.tile_cap + 1) & ~(size_t)1); }   // 2 x 18 (W ring) + 4 (t, padded) + 6 (c)
-// persistent CTAs of the matvec (= private copies of q): MV_CTAS_PER_SM per SM when shared memory allows, never more than blocks
+static inline size_t pcg_atomic_smem(const Ctx &ctx) { return sizeof(double) * 21 * (size_t)ctx.tile_cap; }
+// Private copies of q.  Ordered (bit-reproducible) kernel: one per persistent CTA, MV_CTAS_PER_SM per SM when shared memory allows,
+// never more than blocks.  Atomic kernel: 32 copies, picked by block index, so that concurrent CTAs rarely hit the same address.
 int pcg_matvec_grid(const Ctx &ctx) {
+    if (!ctx.pcg_ordered) return 32;
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int per_sm = pcg_tile_smem(ctx) * MV_CTAS_PER_SM + 4096 <= 227 * 1024 ? MV_CTAS_PER_SM : 1;
     return std::max(1, std::min(ctx.n_blocks, std::max(sms, 1) * per_sm));
 }
+// ordered kernel's copies for a problem of this shape, in bytes (the automatic mode picks it while they stay L2-resident)
+size_t pcg_ordered_copy_bytes(const Ctx &ctx) {
+    Ctx c = ctx;
+    c.pcg_ordered = 1;
+    return sizeof(double) * (size_t)pcg_matvec_grid(c) * (size_t)ctx.n;
+}
 int pcg_tiles_init(const Ctx &ctx) {
-    return (int)cudaFuncSetAttribute(pcg_matvec_points_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_tile_smem(ctx));
+    cudaError_t e = cudaFuncSetAttribute(pcg_matvec_atomic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_atomic_smem(ctx));
+    if (e != cudaSuccess) return (int)e;
+    if (pcg_tile_smem(ctx) > 227 * 1024) return 0;           // (blocks too long for the ordered kernel's ring: atomic kernel only)
+    return (int)cudaFuncSetAttribute(pcg_matvec_ordered_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pcg_tile_smem(ctx));
 }
 // local landmark part of  qp -= W V'^-1 W^T v
 static void launch_matvec(const Ctx &ctx, const double *v, cudaStream_t s) {
     if (ctx.n_blocks <= 0 || ctx.mv_grid <= 0) return;
-    const int per = (ctx.n_blocks + ctx.mv_grid - 1) / ctx.mv_grid;
-    pcg_matvec_points_kernel<<<ctx.mv_grid, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, v, ctx.cg_qp, per);
+    if (ctx.pcg_ordered) {
+        const int per = (ctx.n_blocks + ctx.mv_grid - 1) / ctx.mv_grid;
+        pcg_matvec_ordered_kernel<<<ctx.mv_grid, TILE_THREADS, pcg_tile_smem(ctx), s>>>(ctx, v, ctx.cg_qp, per);
+    } else {
+        pcg_matvec_atomic_kernel<<<ctx.n_blocks, TILE_THREADS, pcg_atomic_smem(ctx), s>>>(ctx, v, ctx.cg_qp);
+    }
 }
 void launch_pcg_start(const Ctx &ctx, cudaStream_t s) {
     pcg_invert_blocks_kernel<<<cdiv(ctx.Nc, 128), 128, 0, s>>>(ctx);

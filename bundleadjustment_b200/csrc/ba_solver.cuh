@@ -150,7 +150,8 @@ struct Ctx {
     double *cg_r, *cg_p, *cg_z, *cg_q, *cg_x, *Minv, *tp;
     double *cg_part;         // [1024] per-CTA partials of the cooperative CG kernels
     double *cg_qp;           // [mv_grid][n] private accumulation copies of the matvec, one per persistent CTA (all zero between products)
-    int mv_grid;             // persistent CTAs of the PCG matvec
+    int mv_grid;             // private copies of q (= persistent CTAs of the ordered matvec; 32 for the atomic one)
+    int pcg_ordered;         // != 0: bit-reproducible matvec (camera-keyed ordered fold), else f64 atomics into the copies
     // control
     LMState *state;
     ba_iteration *iters;     // [max_num_iterations + 2]

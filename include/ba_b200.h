@@ -234,6 +234,13 @@ int ba_set_reduced_system_mode(ba_handle *h, int32_t natural_order, int32_t dens
  * shorter links win -- else 128-row tiles, which run dense matrices closest to the FP64 tensor peak), 64 or 128 = forced. */
 int ba_set_reduced_system_tile(ba_handle *h, int32_t tile_edge);
 
+/* Accumulation of the Schur-Jacobi PCG's implicit product q = S p over the landmark blocks.  1 = ORDERED: persistent CTAs fold
+ * the per-observation contributions per camera in a fixed order into per-CTA private copies of q (no floating-point atomics;
+ * the whole PCG path is then bit-reproducible run to run, like the dense path).  2 = ATOMIC: f64 atomicAdd into 32 copies of q
+ * (results vary in the last bits between runs).  0 = automatic (default): ordered while its private copies stay L2-resident
+ * (up to 48 MB), atomic beyond -- on the 30 M-observation problem the ordered kernel's copies (185 MB) cost 1.6 x the time. */
+int ba_set_pcg_mode(ba_handle *h, int32_t mode);
+
 /* ---- host-only helpers (no GPU needed) ---------------------------------------------------------------- */
 /* Balanced contiguous landmark partition: cut[r]..cut[r+1] for r in [0,n_ranks); weight = sum over the
  * landmark's track length t of t (iterative) or t*(t+1)/2 (dense Schur).  obs_pt must be sorted ascending. */

@@ -303,6 +303,37 @@ def test_pcg_ceres_rule_matches_oracle_pcg(bab, orc, k1_small):
     s.close()
 
 
+def test_pcg_matvec_modes(bab, orc):
+    """ba_set_pcg_mode: the ordered matvec (camera-keyed fold, no floating-point atomics) is bit-reproducible run to run and
+    is what the automatic mode picks for a problem of this size; the atomic variant follows the same trajectory."""
+    pb = syn.flatten(syn.config("K2", scale=0.3))
+    kw = dict(max_num_iterations=8, linear_solver=1)
+    runs = {}
+    for mode in (1, 1, 0, 2):
+        s = bab.Solver(bab.default_options(**kw))
+        s.set_pcg_mode(mode)
+        s.set_problem(pb)
+        s.solve()
+        runs.setdefault(mode, []).append(([i["cost"] for i in s.iterations()], [i["linear_solver_iterations"] for i in s.iterations()],
+                                          s.cameras(), s.points()))
+        if mode == 1 and len(runs[1]) == 1:                 # and again on the SAME handle
+            s.reset_parameters()
+            s.solve()
+            again = ([i["cost"] for i in s.iterations()], s.cameras(), s.points())
+            assert again[0] == runs[1][0][0] and np.array_equal(again[1], runs[1][0][2]) and np.array_equal(again[2], runs[1][0][3])
+        s.close()
+    a, b = runs[1]
+    assert a[0] == b[0] and np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])          # bit for bit across handles
+    auto = runs[0][0]
+    assert auto[0] == a[0] and np.array_equal(auto[2], a[2])                                   # automatic mode = ordered here
+    at = runs[2][0]
+    assert at[1] == a[1]
+    assert np.abs(np.array(at[0]) - np.array(a[0])).max() <= 1e-9 * max(a[0])
+    ocam, opt_, osm, oits = orc.solve(pb, orc.default_options(**kw))
+    _traj_check([dict(iteration=i, step_is_successful=o["step_is_successful"], cost=c, trust_region_radius=o["trust_region_radius"])
+                 for i, (c, o) in enumerate(zip(a[0], oits))], oits)
+
+
 def test_pose_only_batch(bab, orc):
     batch = syn.make_pose_batch(seed=3, n_prob=64, n_pts=200)
     opt = bab.default_options(max_num_iterations=20)
