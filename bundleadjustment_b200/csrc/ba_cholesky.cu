@@ -189,30 +189,28 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 #ifdef CHOL_PROFILE_PHASES
             const long long ck0 = clock64();
 #endif
-            // lane = row i of the 32 x 32 diagonal block.  Gaussian elimination of the AUGMENTED rows [A_i | I_i]: the row
-            // operations row_i -= l_ij row_j (i > j) turn A into D L^T and the identity into L_unit^-1 in the SAME sweep, so no
-            // second serial pass (forward substitution for the inverse) follows.  Square-root-free (L D L^T): only a reciprocal
-            // sits on the pivot chain, and the pivot itself travels by shuffle -- the shared-memory broadcast of column j feeds
-            // the bulk updates, which are off the chain.
-            double a[PB], e[PB];
+            double a[PB];
             const double *row = Ts + (size_t)(c0 + lane) * LDT + c0;
 #pragma unroll
-            for (int k = 0; k < PB; ++k) { a[k] = row[k]; e[k] = (k == lane) ? 1.0 : 0.0; }
+            for (int k = 0; k < PB; ++k) a[k] = row[k];
             bool bad = false;
 #ifdef CHOL_PROFILE_PHASES
             const long long ck1 = clock64();
 #endif
+            // Square-root-free sweep (L D L^T): only a reciprocal sits on the serial pivot chain.  Column j of the
+            // current matrix is broadcast through shared memory (one store per lane, 16-byte broadcast loads) instead of
+            // 2 x (31 - j) shuffles; column j of the unit factor stays UNSCALED in a[j] (= l_ij d_j).
             double *Lcol = invd;                             // [j][c], stride LDP (invd is rewritten at the end of (A))
             double myd = 1.0;                                // d_lane
 #pragma unroll
             for (int j = 0; j < PB; ++j) {
-                double d = __shfl_sync(0xffffffffu, a[j], j);
-                Lcol[j * LDP + lane] = a[j];                 // column j of the current matrix (= row j, by symmetry) for the bulk updates
+                Lcol[j * LDP + lane] = a[j];
                 __syncwarp();
+                double d = Lcol[j * LDP + j];
                 if (!(d > 1e-300) || isinf(d)) { d = 1.0; bad = true; }
                 const double rd = fast_rcp(d);
                 if (lane == j) myd = d;
-                const double ajs = a[j] * rd;                // l_ij for the rows below the pivot
+                const double ajs = a[j] * rd;
                 if (((j + 1) & 1) && j + 1 < PB) a[j + 1] = fma(-ajs, Lcol[j * LDP + j + 1], a[j + 1]);
 #pragma unroll
                 for (int c = (j + 2) & ~1; c < PB; c += 2) {          // 16-byte broadcast loads of column pairs
@@ -220,45 +218,58 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
                     a[c] = fma(-ajs, ac.x, a[c]);
                     a[c + 1] = fma(-ajs, ac.y, a[c + 1]);
                 }
-                // identity part: E_i -= l_ij E_j for i > j; row j of E (columns 0 .. j, E_jj = 1) is final and comes by shuffle
-                const double ls = lane > j ? ajs : 0.0;
-#pragma unroll
-                for (int c = 0; c < j; ++c) e[c] = fma(-ls, __shfl_sync(0xffffffffu, e[c], j), e[c]);
-                e[j] -= ls;
             }
 #ifdef CHOL_PROFILE_PHASES
             const long long ck2 = clock64();
 #endif
-            // L = L_unit sqrt(D),  X = L^-1 = D^-1/2 L_unit^-1.  1/sqrt(d) by rsqrt + one Newton step for sqrt(d) (no division)
-            const double myis = rsqrt(myd);
-            double mys = myd * myis;
-            mys = fma(fma(-mys, mys, myd), 0.5 * myis, mys);
+            // (Round 2 measured two alternatives of this phase on the 64-row banded system and dropped both, profiles/
+            // r02_chol_potrf_variants.txt: augmented elimination [A | I] with the pivot and row j of E travelling by shuffle
+            // -- no inverse sweep, but 496 double shuffles per panel: 12.5 k clocks per panel against 7.3 k for the two sweeps
+            // here; and this form with rsqrt + shuffled 1/sqrt(d_j) in the scaling loop: 29 k clocks in that loop alone.)
+            // L = (unit factor) * sqrt(D): l_ij = a_ij / sqrt(d_j)
+            const double mys = sqrt(myd), myis = 1.0 / mys;
             dinv[c0 + lane] = myis;
+            __syncwarp();
             double *trow = Ts + (size_t)(c0 + lane) * LDT + c0;
+            double *LT = invd;                               // [k][i] = l_ik: rows of L^T, contiguous in i
 #pragma unroll
             for (int j = 0; j < PB; ++j) {
-                const double isj = __shfl_sync(0xffffffffu, myis, j);          // 1 / sqrt(d_j)
-                const double lij = (lane == j) ? mys : a[j] * isj;             // a_ij holds l_ij d_j: l_ij sqrt(d_j) = a_ij / sqrt(d_j)
-                if (j <= lane) trow[j] = lij;                                  // L_d (lower, diag) into the tile
-                e[j] *= myis;                                                  // row i of X
+                a[j] = (lane == j) ? mys : a[j] * dinv[c0 + j];
+                if (j <= lane) trow[j] = a[j];               // L_d (lower, diag) into the tile
+                LT[j * LDP + lane] = a[j];
             }
             if (bad && lane == 0) s_bad = 1;
-            __syncwarp();                                    // Lcol fully consumed before invd is rewritten
+            __syncwarp();
 #ifdef CHOL_PROFILE_PHASES
             const long long ck3 = clock64();
-            const long long ck4 = ck3;
 #endif
-            // lane = row k of X.  E block of the tile = X^T in the strict upper triangle; Pv rows = E rows incl. diagonal and the
-            // zeros left of it; invd = X row-major.  For a fixed r the lanes write consecutive addresses (conflict-free).
+            // lane = column of X = L_d^-1, right-looking forward substitution (independent FMAs per pivot);
+            // x[i] = 0 for i < lane falls out of the recurrence
+            double x[PB];
 #pragma unroll
-            for (int r = 0; r < PB; ++r) {
-                const double v = r <= lane ? e[r] : 0.0;     // X[lane][r]
-                if (r < lane) Ts[(size_t)(c0 + r) * LDT + c0 + lane] = v;
-                Pv[(size_t)(c0 + r) * LDP + lane] = v;
+            for (int i = 0; i < PB; ++i) x[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+            for (int k = 0; k < PB; ++k) {
+                x[k] *= dinv[c0 + k];
+                if (((k + 1) & 1) && k + 1 < PB) x[k + 1] = fma(-LT[k * LDP + k + 1], x[k], x[k + 1]);
+#pragma unroll
+                for (int i = (k + 2) & ~1; i < PB; i += 2) {
+                    const double2 l2 = *reinterpret_cast<const double2 *>(LT + k * LDP + i);
+                    x[i] = fma(-l2.x, x[k], x[i]);
+                    x[i + 1] = fma(-l2.y, x[k], x[i + 1]);
+                }
             }
-            double2 *xrow = reinterpret_cast<double2 *>(invd + (size_t)lane * LDP);
+            __syncwarp();                                    // LT fully consumed before invd is rewritten
+#ifdef CHOL_PROFILE_PHASES
+            const long long ck4 = clock64();
+#endif
+            double *prow = Pv + (size_t)(c0 + lane) * LDP;
 #pragma unroll
-            for (int r = 0; r < PB; r += 2) xrow[r >> 1] = make_double2(r <= lane ? e[r] : 0.0, r + 1 <= lane ? e[r + 1] : 0.0);
+            for (int k = 0; k < PB; ++k) {
+                if (k > lane) trow[k] = x[k];           // E block = (L_d^-1)^T, strict upper: E[r][c] = X[c][r]
+                prow[k] = x[k];                         // E row incl. its diagonal (1 / l_rr) and zeros left of it
+                invd[(size_t)k * LDP + lane] = x[k];    // X row-major: X[k][lane]
+            }
 #ifdef CHOL_PROFILE_PHASES
             if (lane == 0) {
                 const long long ck5 = clock64();
