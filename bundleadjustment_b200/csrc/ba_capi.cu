@@ -84,6 +84,7 @@ struct ba_handle {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     cudaEvent_t ev_ring[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_lm[2] = {nullptr, nullptr};       // LM-body completion markers of the enqueue loop
     bool has_problem = false;
     Ctx ctx;
     // caller order -> landmark-major position (fetched from the device on first use)
@@ -207,6 +208,7 @@ int ba_create(const ba_options *opt, int device, ba_handle **out) {
     CU(cudaEventCreate(&h->ev_start));
     CU(cudaEventCreate(&h->ev_stop));
     for (auto &e : h->ev_ring) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : h->ev_lm) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CU(cudaHostAlloc((void **)&h->h_prep, 64, cudaHostAllocDefault));
     CU(cudaHostAlloc((void **)&h->host_flags, 64, cudaHostAllocMapped));
     std::memset(h->host_flags, 0, 64);
@@ -226,6 +228,7 @@ int ba_destroy(ba_handle *h) {
     if (h->host_flags) cudaFreeHost(h->host_flags);
     if (h->h_prep) cudaFreeHost(h->h_prep);
     for (auto &e : h->ev_ring) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev_lm) if (e) cudaEventDestroy(e);
     for (auto &e : h->prof_ev) cudaEventDestroy(e);
     for (auto &e : h->dom_ev) cudaEventDestroy(e);
     if (h->ev_start) cudaEventDestroy(h->ev_start);
@@ -689,9 +692,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         launch_compute_scale(ctx, s);
         h->launches += 1;
     }
-    cudaEvent_t ev_lm[2];
-    CU(cudaEventCreateWithFlags(&ev_lm[0], cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&ev_lm[1], cudaEventDisableTiming));
+    cudaEvent_t *ev_lm = h->ev_lm;                 // created once per handle (ba_create): no event creation per solve
     // At most max_num_iterations + 1 bodies: body k records iteration k and computes step k + 1.
     const int bodies = h->opt.max_num_iterations + 1;
     int status = BA_OK;
@@ -717,7 +718,6 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
     }
     cudaEventRecord(h->ev_stop, s);
     cudaError_t e = cudaStreamSynchronize(s);
-    cudaEventDestroy(ev_lm[0]); cudaEventDestroy(ev_lm[1]);
     if (status) return status;
     if (e != cudaSuccess) return fail(BA_ERR_CUDA, "LM loop: %s", cudaGetErrorString(e));
     CU(cudaGetLastError());

@@ -32,7 +32,7 @@ def main() -> int:
         pb = bab.sharding.landmark_major(syn.flatten(syn.config("K4", scale)))
         kw = dict(max_num_iterations=8)
         if solver_name == "pcg":
-            kw.update(linear_solver=bab.capi.ITERATIVE_SCHUR, eta=1e-14, cg_r_tolerance=1e-12, max_linear_solver_iterations=3000)
+            kw.update(linear_solver=bab.capi.ITERATIVE_SCHUR, eta=-1.0, cg_r_tolerance=1e-11, max_linear_solver_iterations=5000)
         opt = bab.default_options(**kw)
         # alone
         s1 = bab.Solver(opt, device=local)
@@ -59,23 +59,19 @@ def main() -> int:
         torch.cuda.synchronize()
         dist.barrier()
         s.close()
-        tol = 1e-9 if solver_name == "dense" else 1e-6
-        c1 = np.array([i["cost"] for i in its1]); c = np.array([i["cost"] for i in its])
-        ok = len(c1) == len(c) and np.all(np.abs(c - c1) <= tol * np.abs(c1))
-        ok = ok and abs(sm.final_cost - sm1.final_cost) <= tol * sm1.final_cost
-        # landmarks seen from two nearly parallel rays have an almost singular V_p: their update amplifies the 1e-11
-        # camera differences by cond(V_p), so the landmark criterion is a high percentile, not the maximum
-        dcam, dpt = float(np.abs(cam - cam1).max()), float(np.abs(pt - pt1).max())
-        dpt99 = float(np.percentile(np.abs(pt - pt1).max(axis=1), 99.0))
-        ok = ok and dcam <= (1e-6 if solver_name == "dense" else 1e-5) and dpt99 <= (1e-6 if solver_name == "dense" else 1e-4)
-        flag = torch.tensor([0 if ok else 1], device=f"cuda:{local}")
+        # the gate bench.py applies before its timed region (bundleadjustment_b200/parity.py): cost trajectory 1e-6, final cost
+        # 1e-8, cameras 1e-6, landmarks 1e-6 * max(1, |x|) + the stated conditioning bound -- no percentile waiver
+        sol = lambda its_, sm_, cam_, pt_: {"costs": [i["cost"] for i in its_], "final_cost": sm_.final_cost, "cam": cam_, "pt": pt_,
+                                            "radius": its_[-1]["trust_region_radius"]}
+        par = bab.parity.compare(pb, sol(its, sm, cam, pt), sol(its1, sm1, cam1, pt1))
+        flag = torch.tensor([0 if par["ok"] else 1], device=f"cuda:{local}")
         dist.all_reduce(flag)
         bad += int(flag.item())
         if rank == 0:
-            print(json.dumps({"case": f"K4 x{scale} {solver_name}", "world": world, "ok": bool(flag.item() == 0),
-                              "iterations": len(c), "final_cost_single": sm1.final_cost, "final_cost_sharded": sm.final_cost,
-                              "max_cost_rel_diff": float(np.max(np.abs(c - c1) / np.abs(c1))) if len(c) == len(c1) else None,
-                              "max_cam_diff": dcam, "p99_pt_diff": dpt99, "max_pt_diff": dpt}), flush=True)
+            print(json.dumps({"case": f"K4 x{scale} {solver_name}", "world": world, "ok": bool(flag.item() == 0), "iterations": len(its),
+                              "final_cost_single": sm1.final_cost, "final_cost_sharded": sm.final_cost,
+                              **{k: par[k] for k in ("max_cost_rel_diff", "final_cost_rel_diff", "max_cam_diff", "max_pt_diff", "pt_over_1e-6_rel",
+                                                     "pt_outside_cond_bound")}}), flush=True)
     dist.barrier()
     dist.destroy_process_group()
     return 1 if bad else 0
