@@ -18,7 +18,7 @@ EXPORTS = [
     "ba_version", "ba_last_error", "ba_default_options", "ba_create", "ba_destroy", "ba_set_options",
     "ba_set_problem", "ba_set_parameters", "ba_reset_parameters", "ba_solve", "ba_get_cameras", "ba_get_points",
     "ba_get_iterations", "ba_evaluate", "ba_evaluate_device", "ba_schur_system", "ba_solve_pose_only_batch",
-    "ba_prune_frames", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
+    "ba_prune_frames", "ba_prune_frames_noalloc", "ba_comm_unique_id", "ba_comm_init", "ba_get_launch_count", "ba_set_profiling", "ba_dense_spd_solve",
     "ba_get_reduced_system_stats", "ba_tile_elimination_order", "ba_get_kernel_profile", "ba_set_reduced_system_mode",
     "ba_solve_pose_only_outer", "ba_solve_outer", "ba_set_reduced_system_tile", "ba_dense_spd_solve_tile", "ba_set_pcg_mode", "ba_release_workspace", "ba_workspace_launch_count",
     "ba_partition_landmarks", "ba_inverse4x4_f32", "ba_angle_axis_to_rotation", "ba_rotation_to_angle_axis",
@@ -74,6 +74,7 @@ lib.ba_get_kernel_profile.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_get_reduced_system_stats.argtypes = [C.c_void_p, C.c_void_p]
 lib.ba_dense_spd_solve.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
 lib.ba_dense_spd_solve_tile.argtypes = [C.c_int, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
+lib.ba_prune_frames_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 10 + [C.c_int32]
 lib.ba_schur_system.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
 
 
@@ -264,6 +265,19 @@ def prune_frames(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max, h
                                _ptr(kp_octave), _ptr(pt_xyz), _ptr(pt_min), _ptr(pt_max), _ptr(has_point), _ptr(out),
                                int(consider_outlier)), "ba_prune_frames")
     return out
+
+
+PRUNE_NOALLOC_MAX_FRAMES = 4096          # BA_PRUNE_NOALLOC_MAX_FRAMES (include/ba_b200.h)
+
+
+def prune_frames_noalloc(n_frames: int, n_kp: int, d_pose: int, d_K: int, d_frame_ptr: int, d_kp_xy: int, d_kp_octave: int,
+                         d_pt_xyz: int, d_pt_min: int, d_pt_max: int, d_has_point: int, d_outlier: int, consider_outlier=True,
+                         device: int = 0, stream: int = 0) -> None:
+    """ba_prune_frames_noalloc: every d_* is a DEVICE address (int), `stream` a cudaStream_t handle (int, 0 = default stream).
+    Enqueues only -- synchronise the stream before reading d_outlier.  Allocates nothing (static device scratch)."""
+    _check(lib.ba_prune_frames_noalloc(int(device), C.c_void_p(stream or None), int(n_frames), int(n_kp), *[C.c_void_p(int(a)) for a in (
+        d_pose, d_K, d_frame_ptr, d_kp_xy, d_kp_octave, d_pt_xyz, d_pt_min, d_pt_max, d_has_point, d_outlier)], int(consider_outlier)),
+        "ba_prune_frames_noalloc")
 
 
 def solve_pose_only_outer(pose, K, frame_ptr, kp_xy, kp_octave, pt_xyz, pt_min, pt_max, has_point, outlier, n_outer=4,

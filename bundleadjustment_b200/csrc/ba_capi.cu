@@ -33,6 +33,11 @@ int fail(int code, const char *fmt, ...) {
     return code;
 }
 
+} // namespace
+// error text of entry points that live in other translation units (ba_pose_batch.cu: ba_prune_frames_noalloc)
+int ba::report_error(int code, const char *text) { return fail(code, "%s", text); }
+namespace {
+
 #define CU(expr)                                                                                     \
     do {                                                                                             \
         cudaError_t e__ = (expr);                                                                    \

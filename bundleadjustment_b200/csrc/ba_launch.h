@@ -133,4 +133,7 @@ void launch_prune(int n_frames, const float *pose, const float *extr, const floa
                   const int *kp_octave, const float *pt_xyz, const float *pt_min, const float *pt_max,
                   const uint8_t *has_point, uint8_t *outlier, int consider_outlier, int n_kp, cudaStream_t s);
 
+// ba_capi.cu: sets ba_last_error() of the calling thread, returns code (for entry points defined outside ba_capi.cu)
+int report_error(int code, const char *text);
+
 } // namespace ba

@@ -468,3 +468,82 @@ void launch_prune(int n_frames, const float *pose, const float *extr, const floa
 }
 
 } // namespace ba
+
+// =============================================================================================================
+// ba_prune_frames_noalloc: the prune path with its scratch in static device memory (include/ba_b200.h; no counterpart in
+// the reference -- added for callers that must not allocate)
+// =============================================================================================================
+#include <cstdio>
+#include <mutex>
+
+namespace {
+
+// extr = pose.inverse() of every frame of one call (what ba_prune_frames keeps in Workspace::extr).  One array per GPU
+// that loads this module, shared by every call on that GPU.  In HOST code this name is only a stand-in for the symbol:
+// the kernels get the address cudaGetSymbolAddress returns for the current device.
+static __device__ __align__(256) float g_prune_extr[16 * BA_PRUNE_NOALLOC_MAX_FRAMES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_prune_mu;
+float *g_prune_extr_ptr[NOALLOC_MAX_DEVICES];      // device address of g_prune_extr on device d, nullptr = not looked up yet
+
+int noalloc_fail(int code, const char *what, cudaError_t e) {
+    char buf[256];
+    std::snprintf(buf, sizeof(buf), "ba_prune_frames_noalloc: %s: %s", what, cudaGetErrorString(e));
+    return ba::report_error(code, buf);
+}
+
+// once per device, with that device current
+int prune_scratch(int device, float **out) {
+    std::lock_guard<std::mutex> lock(g_prune_mu);
+    if (!g_prune_extr_ptr[device]) {
+        int major = 0;
+        cudaError_t e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+        if (e != cudaSuccess) return noalloc_fail(BA_ERR_CUDA, "cudaDeviceGetAttribute", e);
+        if (major < 10) return ba::report_error(BA_ERR_CUDA, "ba_prune_frames_noalloc: this build targets sm_100a only");
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_prune_extr);
+        if (e != cudaSuccess || !p) return noalloc_fail(BA_ERR_CUDA, "cudaGetSymbolAddress(g_prune_extr)", e);
+        g_prune_extr_ptr[device] = static_cast<float *>(p);
+    }
+    *out = g_prune_extr_ptr[device];
+    return BA_OK;
+}
+
+} // namespace
+
+extern "C" int ba_prune_frames_noalloc(int device, void *stream, int32_t n_frames, int32_t n_kp, const float *d_pose,
+                                       const float *d_K, const int32_t *d_frame_ptr, const float *d_kp_xy,
+                                       const int32_t *d_kp_octave, const float *d_pt_xyz, const float *d_pt_min_dist,
+                                       const float *d_pt_max_dist, const uint8_t *d_has_point, uint8_t *d_outlier,
+                                       int32_t consider_outlier) {
+    char buf[256];
+    if (n_frames < 0 || n_kp < 0) return ba::report_error(BA_ERR_INVALID, "ba_prune_frames_noalloc: negative size");
+    if (n_frames > BA_PRUNE_NOALLOC_MAX_FRAMES) {
+        std::snprintf(buf, sizeof(buf), "ba_prune_frames_noalloc: n_frames %d exceeds BA_PRUNE_NOALLOC_MAX_FRAMES (%d): the scratch "
+                      "is a fixed static device array; use ba_prune_frames or split the batch", (int)n_frames, BA_PRUNE_NOALLOC_MAX_FRAMES);
+        return ba::report_error(BA_ERR_INVALID, buf);
+    }
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        cudaGetLastError();
+        return ba::report_error(BA_ERR_CUDA, "ba_prune_frames_noalloc: no CUDA device available; this library has no CPU fallback");
+    }
+    if (device < 0 || device >= n_dev || device >= NOALLOC_MAX_DEVICES) return ba::report_error(BA_ERR_INVALID, "ba_prune_frames_noalloc: device out of range");
+    if (n_frames == 0 || n_kp == 0) return BA_OK;
+    if (!d_pose || !d_K || !d_frame_ptr || !d_kp_xy || !d_kp_octave || !d_pt_xyz || !d_pt_min_dist || !d_pt_max_dist || !d_has_point || !d_outlier)
+        return ba::report_error(BA_ERR_INVALID, "ba_prune_frames_noalloc: NULL device array");
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return noalloc_fail(BA_ERR_CUDA, "cudaSetDevice", e);
+    float *extr = nullptr;
+    int rc = prune_scratch(device, &extr);
+    if (rc) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // the first n_frames entries of the shared scratch are rewritten here before prune_kernel reads them: nothing of the
+    // previous call's contents is ever read, so no clear is needed
+    ba::launch_pose_inverse(n_frames, d_pose, extr, s);                                   // extr = pose.inverse(), f32 (Optimizer.cpp:10)
+    ba::launch_prune(n_frames, d_pose, extr, d_K, d_frame_ptr, reinterpret_cast<const float2 *>(d_kp_xy), d_kp_octave, d_pt_xyz,
+                     d_pt_min_dist, d_pt_max_dist, d_has_point, d_outlier, consider_outlier, n_kp, s);
+    if ((e = cudaPeekAtLastError()) != cudaSuccess) return noalloc_fail(BA_ERR_CUDA, "kernel launch", e);
+    return BA_OK;
+}

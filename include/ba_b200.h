@@ -171,6 +171,30 @@ int ba_prune_frames(int device, int32_t n_frames, const float *pose /*16F*/, con
                     const float *pt_xyz, const float *pt_min_dist, const float *pt_max_dist,
                     const uint8_t *has_point, uint8_t *outlier /*in/out*/, int32_t consider_outlier);
 
+/* ---- ba_prune_frames without any allocation ----------------------------------------------------------- *
+ * NO counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two kernels and the
+ * same results as ba_prune_frames, but
+ *   - every array argument is a DEVICE pointer (readable / writable from `device`); n_kp = frame_ptr[n_frames] is
+ *     passed by value because frame_ptr lives on the device; outlier is updated in place;
+ *   - the kernels are ENQUEUED on `stream` (a cudaStream_t; NULL = the legacy default stream) and the call returns
+ *     without synchronising: results are ready when the stream reaches that point;
+ *   - the scratch ba_prune_frames keeps in its workspace (extr = pose.inverse(), 64 bytes per frame) lives in a
+ *     file-scope `static __device__` array of BA_PRUNE_NOALLOC_MAX_FRAMES x 64 B = 256 KiB that every GPU which
+ *     loads the library holds until the process exits.  n_frames beyond the maximum is rejected (BA_ERR_INVALID).
+ * The call issues no cudaMalloc / cudaFree / stream or event creation.  The array's device address is looked up once
+ * per device (cudaGetSymbolAddress, on the first call for that device: make that call outside a capture).
+ * ALL calls on one device share the one array and it keeps the previous call's contents: each call overwrites the
+ * n_frames entries it reads before reading them (nothing has to start at zero), and two calls whose kernels can
+ * overlap on the GPU (different streams without an ordering between them, or several host threads) RACE on it --
+ * order them on one stream or with events. */
+#define BA_PRUNE_NOALLOC_MAX_FRAMES 4096
+int ba_prune_frames_noalloc(int device, void *stream, int32_t n_frames, int32_t n_kp, const float *d_pose /*16F*/,
+                            const float *d_K /*9F*/, const int32_t *d_frame_ptr /*F+1*/, const float *d_kp_xy,
+                            const int32_t *d_kp_octave, const float *d_pt_xyz, const float *d_pt_min_dist,
+                            const float *d_pt_max_dist, const uint8_t *d_has_point, uint8_t *d_outlier /*in/out*/,
+                            int32_t consider_outlier);
+
 /* ---- SfMHelper::estimatePoseUsingBA's whole loop (SfMHelper.cpp:106-117: 4 outer iterations x <= 20 LM iterations,
  * Optimizer.cpp:417-457), batched over frames and DEVICE-RESIDENT: per outer iteration the pose -> parameter conversion
  * (Optimizer.cpp:462-465), the observation list (keypoints with a map point that are not outliers, :472), one ceres::Solve
