@@ -39,6 +39,13 @@ constexpr int SPAD = BK + 4;           // 36 doubles: row stride == 4 (mod 16) -
 constexpr int NSTAGE = 3;
 constexpr int PB = 32;                 // potrf panel width (warp-register base case)
 constexpr int LDP = PB + 4;            // 36
+constexpr int LDQ = PB + 2;            // 34: stride of the potrf hand-off buffers -- rows stay 16-byte aligned, column access is 2-way at worst
+// warp 0 -> warp 1 hand-off of a finished pivot column inside potrf: 2 = one mbarrier per pivot (arrive has CTA-scope release
+// semantics; try_wait suspends in hardware), 0 = st.release / ld.acquire on a progress word (the fence costs warp 0 ~50 clocks
+// per pivot), 1 = volatile progress word without a fence (measurement only: not ordered by the memory model)
+#ifndef POTRF_HANDOFF
+#define POTRF_HANDOFF 2
+#endif
 
 // Tile edge NB is a template parameter: 128 for (near-)dense reduced systems (highest arithmetic intensity: 67 % of the FP64
 // GEMM rate on a dense matrix), 64 for tile-sparse ones.  A sparse factorisation is a CHAIN of potrf -> trsm -> update tasks
@@ -58,7 +65,7 @@ struct ChCfg {
     static constexpr int SCRATCH_DOUBLES = 2 * NB * SPAD;
     static constexpr int SMEM_DOUBLES = (TILE_DOUBLES + SCRATCH_DOUBLES > RING_DOUBLES) ? TILE_DOUBLES + SCRATCH_DOUBLES : RING_DOUBLES;
     static constexpr int SMEM = SMEM_DOUBLES * (int)sizeof(double);
-    static_assert(NB * LDP + PB * LDP + NB <= SCRATCH_DOUBLES, "potrf scratch must fit");
+    static_assert(NB * LDP + PB * LDP + NB + 2 * PB * LDQ + 2 * PB <= SMEM_DOUBLES - TILE_DOUBLES, "potrf scratch (Pv | invd | dinv | Lc | XuT | rdv | sqv) must fit behind the tile");
     static_assert(SMEM <= 227 * 1024, "shared memory budget");
     static_assert(NB == 64 || NB == 128, "tile edge");
 };
@@ -97,6 +104,22 @@ __device__ __forceinline__ int ld_relaxed(const int *p) {
 }
 __device__ __forceinline__ void st_release(int *p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+
+// CTA-scope release / acquire on a shared-memory word (warp-to-warp hand-off inside potrf)
+__device__ __forceinline__ void st_release_cta(int *p, int v) {
+    asm volatile("st.release.cta.shared.s32 [%0], %1;\n" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_cta(const int *p) {
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];\n" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+
+// one arrival on an mbarrier (CTA-scope release: the arriving thread's earlier shared-memory writes, and those it has
+// synchronised with, are visible to whoever observes the phase completion)
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
 
 // 1 / d to ~1 ulp: MUFU seed (20+ bits) + two Newton steps; d must be a normal positive number
@@ -170,12 +193,17 @@ __device__ long long g_potrf_phase[12];  // tools/chol_prof.cu: accumulated ns i
 
 template <int NB>
 __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double *__restrict__ Pv, double *__restrict__ invd,
-                                                double *__restrict__ dinv) {
+                                                double *__restrict__ dinv, unsigned long long *piv, unsigned phase) {
     constexpr int LDT = ChCfg<NB>::LDT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tig = lane & 3;
-    __shared__ int s_bad;
-    if (tid == 0) s_bad = 0;
+    double *Lc = dinv + NB;                                  // [PB][LDQ] row j = column j of the matrix at pivot j (unscaled)
+    double *XuT = Lc + PB * LDQ;                             // [PB][LDQ] row c = column c of the unit factor's inverse
+    double *rdv = XuT + PB * LDQ, *sqv = rdv + PB;           // [PB] 1 / d_j, sqrt(d_j)
+    __shared__ int s_bad, s_prog;
+    int *prog = &s_prog;                                     // (hand-off variants 0 / 1) pivots published, counted over the tile
+    (void)prog; (void)piv; (void)phase;
+    if (tid == 0) { s_bad = 0; s_prog = 0; }
     __syncthreads();
 #ifdef CHOL_PROFILE_PHASES
     long long tA = 0, tB = 0, tC = 0;
@@ -185,6 +213,12 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
         const long long t0 = global_ns();
 #endif
         // ---- (A) ----
+        // Two warps, pipelined.  Warp 0 runs the square-root-free factor sweep (L D L^T: only a reciprocal sits on the serial
+        // pivot chain) and publishes every pivot column as soon as it is final; warp 1 runs the forward substitution for the
+        // inverse of the UNIT factor one pivot behind it (lane = column of the inverse), so the second serial sweep overlaps
+        // the first instead of following it.  The scaling by sqrt(D) and every store into the tile happen afterwards in an
+        // epilogue spread over all eight warps.  (Before: one warp ran factor sweep, scaling, inverse sweep and stores back to
+        // back, 10.3 k clocks per panel -- profiles/r02_chol_potrf_variants.txt.)
         if (warp == 0) {
 #ifdef CHOL_PROFILE_PHASES
             const long long ck0 = clock64();
@@ -197,90 +231,105 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 #ifdef CHOL_PROFILE_PHASES
             const long long ck1 = clock64();
 #endif
-            // Square-root-free sweep (L D L^T): only a reciprocal sits on the serial pivot chain.  Column j of the
-            // current matrix is broadcast through shared memory (one store per lane, 16-byte broadcast loads) instead of
-            // 2 x (31 - j) shuffles; column j of the unit factor stays UNSCALED in a[j] (= l_ij d_j).
-            double *Lcol = invd;                             // [j][c], stride LDP (invd is rewritten at the end of (A))
+            // Column j of the current matrix is broadcast through shared memory (one store per lane, 16-byte broadcast loads)
+            // instead of 2 x (31 - j) shuffles; column j of the unit factor stays UNSCALED in Lc[j][.] (= l_ij d_j).
             double myd = 1.0;                                // d_lane
 #pragma unroll
             for (int j = 0; j < PB; ++j) {
-                Lcol[j * LDP + lane] = a[j];
+                Lc[j * LDQ + lane] = a[j];
                 __syncwarp();
-                double d = Lcol[j * LDP + j];
+                double d = Lc[j * LDQ + j];
                 if (!(d > 1e-300) || isinf(d)) { d = 1.0; bad = true; }
                 const double rd = fast_rcp(d);
                 if (lane == j) myd = d;
+                if (lane == 0) {                                 // column j and 1 / d_j are final: hand them to warp 1
+                    rdv[j] = rd;
+#if POTRF_HANDOFF == 2
+                    mbar_arrive(&piv[c0 + j]);
+#elif POTRF_HANDOFF == 1
+                    *reinterpret_cast<volatile int *>(prog) = c0 + j + 1;
+#else
+                    st_release_cta(prog, c0 + j + 1);
+#endif
+                }
                 const double ajs = a[j] * rd;
-                if (((j + 1) & 1) && j + 1 < PB) a[j + 1] = fma(-ajs, Lcol[j * LDP + j + 1], a[j + 1]);
+                if (((j + 1) & 1) && j + 1 < PB) a[j + 1] = fma(-ajs, Lc[j * LDQ + j + 1], a[j + 1]);
 #pragma unroll
                 for (int c = (j + 2) & ~1; c < PB; c += 2) {          // 16-byte broadcast loads of column pairs
-                    const double2 ac = *reinterpret_cast<const double2 *>(Lcol + j * LDP + c);
+                    const double2 ac = *reinterpret_cast<const double2 *>(Lc + j * LDQ + c);
                     a[c] = fma(-ajs, ac.x, a[c]);
                     a[c + 1] = fma(-ajs, ac.y, a[c + 1]);
                 }
             }
-#ifdef CHOL_PROFILE_PHASES
-            const long long ck2 = clock64();
-#endif
-            // (Round 2 measured two alternatives of this phase on the 64-row banded system and dropped both, profiles/
+            // (Round 2 measured two alternatives of this sweep on the 64-row banded system and dropped both, profiles/
             // r02_chol_potrf_variants.txt: augmented elimination [A | I] with the pivot and row j of E travelling by shuffle
-            // -- no inverse sweep, but 496 double shuffles per panel: 12.5 k clocks per panel against 7.3 k for the two sweeps
-            // here; and this form with rsqrt + shuffled 1/sqrt(d_j) in the scaling loop: 29 k clocks in that loop alone.)
-            // L = (unit factor) * sqrt(D): l_ij = a_ij / sqrt(d_j)
-            const double mys = sqrt(myd), myis = 1.0 / mys;
-            dinv[c0 + lane] = myis;
-            __syncwarp();
-            double *trow = Ts + (size_t)(c0 + lane) * LDT + c0;
-            double *LT = invd;                               // [k][i] = l_ik: rows of L^T, contiguous in i
-#pragma unroll
-            for (int j = 0; j < PB; ++j) {
-                a[j] = (lane == j) ? mys : a[j] * dinv[c0 + j];
-                if (j <= lane) trow[j] = a[j];               // L_d (lower, diag) into the tile
-                LT[j * LDP + lane] = a[j];
-            }
+            // -- 496 double shuffles per panel, 12.5 k clocks; and rsqrt + shuffled 1/sqrt(d_j) in a scaling loop: 29 k clocks.)
+            const double mys = sqrt(myd);
+            sqv[lane] = mys;                                 // l_jj
+            dinv[c0 + lane] = 1.0 / mys;                     // 1 / l_jj
             if (bad && lane == 0) s_bad = 1;
-            __syncwarp();
 #ifdef CHOL_PROFILE_PHASES
-            const long long ck3 = clock64();
+            if (lane == 0) {
+                const long long ck2 = clock64();
+                atomicAdd((unsigned long long *)&g_potrf_phase[4], (unsigned long long)(ck1 - ck0));
+                atomicAdd((unsigned long long *)&g_potrf_phase[5], (unsigned long long)(ck2 - ck1));
+            }
 #endif
-            // lane = column of X = L_d^-1, right-looking forward substitution (independent FMAs per pivot);
-            // x[i] = 0 for i < lane falls out of the recurrence
+        } else if (warp == 1) {
+            // Xu = (unit factor)^-1, right-looking: x[i] -= l_ik x[k] with l_ik = Lc[k][i] / d_k; x[i] = 0 for i < lane falls
+            // out of the recurrence.  Step k only needs column k, which warp 0 has just published.
             double x[PB];
 #pragma unroll
             for (int i = 0; i < PB; ++i) x[i] = (i == lane) ? 1.0 : 0.0;
 #pragma unroll
-            for (int k = 0; k < PB; ++k) {
-                x[k] *= dinv[c0 + k];
-                if (((k + 1) & 1) && k + 1 < PB) x[k + 1] = fma(-LT[k * LDP + k + 1], x[k], x[k + 1]);
+            for (int k = 0; k < PB - 1; ++k) {
+#if POTRF_HANDOFF == 2
+                mbar_wait(&piv[c0 + k], phase);
+#elif POTRF_HANDOFF == 1
+                while (*reinterpret_cast<volatile int *>(prog) < c0 + k + 1) { }
+#else
+                while (ld_acquire_cta(prog) < c0 + k + 1) { }
+#endif
+                const double t = rdv[k] * x[k];
+                if (((k + 1) & 1)) x[k + 1] = fma(-Lc[k * LDQ + k + 1], t, x[k + 1]);
 #pragma unroll
                 for (int i = (k + 2) & ~1; i < PB; i += 2) {
-                    const double2 l2 = *reinterpret_cast<const double2 *>(LT + k * LDP + i);
-                    x[i] = fma(-l2.x, x[k], x[i]);
-                    x[i + 1] = fma(-l2.y, x[k], x[i + 1]);
+                    const double2 l2 = *reinterpret_cast<const double2 *>(Lc + k * LDQ + i);
+                    x[i] = fma(-l2.x, t, x[i]);
+                    x[i + 1] = fma(-l2.y, t, x[i + 1]);
                 }
             }
-            __syncwarp();                                    // LT fully consumed before invd is rewritten
-#ifdef CHOL_PROFILE_PHASES
-            const long long ck4 = clock64();
+#if POTRF_HANDOFF == 2
+            mbar_wait(&piv[c0 + PB - 1], phase);             // every barrier completes exactly one phase per call
 #endif
-            double *prow = Pv + (size_t)(c0 + lane) * LDP;
 #pragma unroll
-            for (int k = 0; k < PB; ++k) {
-                if (k > lane) trow[k] = x[k];           // E block = (L_d^-1)^T, strict upper: E[r][c] = X[c][r]
-                prow[k] = x[k];                         // E row incl. its diagonal (1 / l_rr) and zeros left of it
-                invd[(size_t)k * LDP + lane] = x[k];    // X row-major: X[k][lane]
-            }
-#ifdef CHOL_PROFILE_PHASES
-            if (lane == 0) {
-                const long long ck5 = clock64();
-                atomicAdd((unsigned long long *)&g_potrf_phase[4], (unsigned long long)(ck1 - ck0));
-                atomicAdd((unsigned long long *)&g_potrf_phase[5], (unsigned long long)(ck2 - ck1));
-                atomicAdd((unsigned long long *)&g_potrf_phase[6], (unsigned long long)(ck3 - ck2));
-                atomicAdd((unsigned long long *)&g_potrf_phase[7], (unsigned long long)(ck4 - ck3));
-                atomicAdd((unsigned long long *)&g_potrf_phase[8], (unsigned long long)(ck5 - ck4));
-            }
-#endif
+            for (int k = 0; k < PB; k += 2)                  // column `lane` of Xu, contiguous (16-byte stores, conflict-free at LDQ)
+                *reinterpret_cast<double2 *>(XuT + lane * LDQ + k) = make_double2(x[k], x[k + 1]);
         }
+        __syncthreads();
+#ifdef CHOL_PROFILE_PHASES
+        const long long ckE = clock64();
+#endif
+        // Epilogue, all warps.  X = L_d^-1 = D^-1/2 Xu (row k scaled by 1 / l_kk), L_d = (unit factor) sqrt(D).
+        // Row pass (lane = k): row c0 + c of the tile = [L_d row c | E row c] (E[r][c] = X[c][r], strict upper) and row c0 + c
+        // of Pv = column c of X (the E row incl. its diagonal 1 / l_cc and the zeros left of it) -- contiguous stores.
+#pragma unroll
+        for (int q = 0; q < PB / 8; ++q) {
+            const int c = warp + 8 * q, k = lane;
+            const double isk = dinv[c0 + k];
+            const double v = XuT[c * LDQ + k] * isk;
+            Pv[(size_t)(c0 + c) * LDP + k] = v;
+            Ts[(size_t)(c0 + c) * LDT + c0 + k] = (k > c) ? v : (k == c) ? sqv[k] : Lc[k * LDQ + c] * isk;
+        }
+        // Column pass (lane = c): X row-major into invd, the B operand of (B)
+#pragma unroll
+        for (int q = 0; q < PB / 8; ++q) {
+            const int k = warp + 8 * q;
+            invd[(size_t)k * LDP + lane] = XuT[lane * LDQ + k] * dinv[c0 + k];
+        }
+#ifdef CHOL_PROFILE_PHASES
+        if (tid == 0) atomicAdd((unsigned long long *)&g_potrf_phase[7], (unsigned long long)(clock64() - ckE));
+#endif
         __syncthreads();
 #ifdef CHOL_PROFILE_PHASES
         const long long t1 = global_ns();
@@ -405,6 +454,10 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     double *scratch = smem + TILE_DOUBLES;                 // epilogue ring (2 stages of B) / potrf scratch
     double *Pv = scratch, *invd = scratch + NB * LDP, *dinv = invd + PB * LDP;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ unsigned long long s_piv[NB];               // potrf: one mbarrier per pivot column (warp 0 -> warp 1 hand-off)
+    if (tid < NB) mbar_init(&s_piv[tid], 1);
+    unsigned potrf_calls = 0;                              // every call completes one phase of each of them
+    __syncthreads();
     // 2 x 4 warps -> (NB/2) x (NB/4) per warp.  Warps w and w + 4 share an SM sub-partition (and its DMMA pipe): the column blocks are
     // mirrored in the lower warp row so that triangular work (TRSM against the lower-triangular L_jj^-1) is balanced.
     const int wm = warp >> 2, wn = wm ? 3 - (warp & 3) : (warp & 3);
@@ -523,7 +576,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         __syncthreads();
         if (diag) {
             const long long tp0 = p.prof ? global_ns() : 0;
-            const bool bad = potrf_inverse_tile<NB>(tileC, Pv, invd, dinv);
+            const bool bad = potrf_inverse_tile<NB>(tileC, Pv, invd, dinv, s_piv, potrf_calls++ & 1u);
             if (p.prof) t_potrf += global_ns() - tp0;
             if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
             // L_jj^-1 first: it is all the TRSMs (and the back substitution) wait for; L_jj itself is only stored for the

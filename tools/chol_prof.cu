@@ -80,8 +80,8 @@ int main(int argc, char **argv) {
     if (ph[3]) {
         printf("  potrf phases per tile: (A) %.1f us  (B) %.1f us  (C) %.1f us  over %lld calls\n", ph[0] * 1e-3 / ph[3], ph[1] * 1e-3 / ph[3], ph[2] * 1e-3 / ph[3], ph[3]);
         const double panels = (double)ph[3] * (nb / 32);
-        printf("  inside (A), SM clocks per 32 x 32 panel: load %.0f  factor sweep %.0f  scale + store L %.0f  inverse sweep %.0f  stores %.0f\n",
-               ph[4] / panels, ph[5] / panels, ph[6] / panels, ph[7] / panels, ph[8] / panels);
+        printf("  inside (A), SM clocks per 32 x 32 panel: load %.0f  factor sweep (warp 0; warp 1 inverts one pivot behind) %.0f  epilogue (all warps) %.0f\n",
+               ph[4] / panels, ph[5] / panels, ph[7] / panels);
     }
     return 0;
 }
