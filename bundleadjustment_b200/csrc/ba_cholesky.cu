@@ -71,11 +71,12 @@ struct ChCfg {
 };
 
 int chol_ld(int n, int nb) { return ((n + nb - 1) / nb) * nb; }
-// work area: L_jj^-1 blocks, then int flags [tiledone ((T + 1) x T) | ydone (T) | abort (1)]
-static inline int chol_flag_count(int T) { return (T + 1) * T + T + 1; }
+// work area: L_jj^-1 blocks, y blocks, the chain-fusion hand-off tiles (one per tile row), then int flags
+// [tiledone ((T + 1) x T) | ydone (T) | c2done (T) | abort (1) | next task (1) | CTAs started per SM (256)]
+static inline int chol_flag_count(int T) { return (T + 1) * T + 2 * T + 2 + 256; }
 size_t chol_work_doubles(int n, int nb) {
     const int T = chol_ld(n, nb) / nb;
-    return (size_t)T * nb * nb + (size_t)T * nb + (size_t)(chol_flag_count(T) + 1) / 2 + 1;
+    return 2 * (size_t)T * nb * nb + (size_t)T * nb + (size_t)(chol_flag_count(T) + 1) / 2 + 1;
 }
 
 // ---- small PTX helpers -------------------------------------------------------------------------------------------
@@ -141,6 +142,11 @@ struct CholArgs {
     double *ypad;         // [T][NB] solution blocks as they are produced (cross-CTA exchange)
     int *tiledone;        // [T + 1][T] tile (i, j) of L (row T: of z) is final
     int *ydone;           // [T]
+    double *c2buf;        // [T][NB*NB] chain fusion: row i's last off-diagonal tile BEFORE its TRSM (C2 = A_ic - sum_k L_ik L_ck^T)
+    int *c2done;          // [T] c2buf[i] is complete
+    int *next_task;       // [1] tickets handed out beyond the first gridDim.x tasks
+    int *sm_slot;         // [256] CTAs that have started on each SM
+    const unsigned char *partner;   // [ntasks] != 0: off-diagonal task (i, c) whose column c is the LAST k-block of diagonal task (i, i)
     int *abort_flag;      // [1] set when a wait timed out (never expected; keeps a bug from hanging the GPU)
     double *y;            // [n]
     LMState *state;       // may be nullptr
@@ -193,7 +199,7 @@ __device__ long long g_potrf_phase[12];  // tools/chol_prof.cu: accumulated ns i
 
 template <int NB>
 __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double *__restrict__ Pv, double *__restrict__ invd,
-                                                double *__restrict__ dinv, unsigned long long *piv, unsigned phase) {
+                                                double *__restrict__ dinv, unsigned long long *piv, unsigned phase, int w0) {
     constexpr int LDT = ChCfg<NB>::LDT;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tig = lane & 3;
@@ -219,7 +225,7 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
         // the first instead of following it.  The scaling by sqrt(D) and every store into the tile happen afterwards in an
         // epilogue spread over all eight warps.  (Before: one warp ran factor sweep, scaling, inverse sweep and stores back to
         // back, 10.3 k clocks per panel -- profiles/r02_chol_potrf_variants.txt.)
-        if (warp == 0) {
+        if (warp == w0) {                                    // (w0 = 0 or 2: two co-resident CTAs keep their sweeps on different SM sub-partitions)
 #ifdef CHOL_PROFILE_PHASES
             const long long ck0 = clock64();
 #endif
@@ -275,7 +281,7 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
                 atomicAdd((unsigned long long *)&g_potrf_phase[5], (unsigned long long)(ck2 - ck1));
             }
 #endif
-        } else if (warp == 1) {
+        } else if (warp == w0 + 1) {
             // Xu = (unit factor)^-1, right-looking: x[i] -= l_ik x[k] with l_ik = Lc[k][i] / d_k; x[i] = 0 for i < lane falls
             // out of the recurrence.  Step k only needs column k, which warp 0 has just published.
             double x[PB];
@@ -443,8 +449,11 @@ __device__ __forceinline__ void mma_slice(double (&acc)[MI][NJ][2], const double
     }
 }
 
+// 64-row tiles: TWO CTAs per SM (110 KB of shared memory and <= 128 registers each).  A tile-sparse factorisation has far more
+// tasks in flight than arithmetic (each holds its CTA while it waits for operands), so the leaf levels were limited by the number
+// of CTAs, not by the SMs.  128-row tiles (dense systems, flop-bound) keep one CTA per SM with the full register file.
 template <int NB>
-__global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
+__global__ void __launch_bounds__(256, NB == 64 ? 2 : 1) chol_dataflow_kernel(CholArgs p) {
     using Cfg = ChCfg<NB>;
     constexpr int KSL = Cfg::KSL, LDT = Cfg::LDT, MI = Cfg::MI, NJ = Cfg::NJ, STAGE_DOUBLES = Cfg::STAGE_DOUBLES, TILE_DOUBLES = Cfg::TILE_DOUBLES;
     constexpr int WR = NB / 2, WC = NB / 4;                // warp tile
@@ -453,11 +462,24 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     double *tileC = smem;                                  // [NB][LDT]   (main loop: part of the ring)
     double *scratch = smem + TILE_DOUBLES;                 // epilogue ring (2 stages of B) / potrf scratch
     double *Pv = scratch, *invd = scratch + NB * LDP, *dinv = invd + PB * LDP;
+    // chain fusion: a diagonal task's own tile A_ii [NB][LDT], staged behind the TRSM's scratch while the ring is idle
+    // (consumed before potrf, whose work arrays reach into this area)
+    double *own = scratch + Cfg::SCRATCH_DOUBLES;
+    static_assert(NB != 64 || TILE_DOUBLES + Cfg::SCRATCH_DOUBLES + TILE_DOUBLES <= Cfg::SMEM_DOUBLES, "own-tile stage must fit the idle ring");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __shared__ unsigned long long s_piv[NB];               // potrf: one mbarrier per pivot column (warp 0 -> warp 1 hand-off)
     if (tid < NB) mbar_init(&s_piv[tid], 1);
     unsigned potrf_calls = 0;                              // every call completes one phase of each of them
+    // which of the SM's co-resident CTAs this is (64-row tiles run two per SM): the second one runs potrf's two serial sweeps on
+    // warps 2 / 3, i.e. on the SM sub-partitions the first one leaves alone
+    __shared__ int s_slot;
+    if (tid == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;\n" : "=r"(smid));
+        s_slot = NB == 64 ? (atomicAdd(p.sm_slot + (smid & 255u), 1) & 1) : 0;
+    }
     __syncthreads();
+    const int sweep_warp = 2 * s_slot;
     // 2 x 4 warps -> (NB/2) x (NB/4) per warp.  Warps w and w + 4 share an SM sub-partition (and its DMMA pipe): the column blocks are
     // mirrored in the lower warp row so that triangular work (TRSM against the lower-triangular L_jj^-1) is balanced.
     const int wm = warp >> 2, wn = wm ? 3 - (warp & 3) : (warp & 3);
@@ -471,7 +493,18 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
     const long long t_start = p.prof ? global_ns() : 0;
 
     // ================= phase 1: factorisation + forward substitution =================
-    for (int t = blockIdx.x; t < p.ntasks && !aborted; t += gridDim.x) {
+    // Tasks are handed out DYNAMICALLY in plan order (a topological order, so whoever holds the lowest unfinished task can always
+    // finish it: no deadlock): the first gridDim.x by CTA index, every later one through an atomic ticket.  With a static
+    // round-robin a CTA that sat waiting for the operands of one task also held back the tasks queued behind it, which showed as
+    // late pick-ups of critical-path tasks in the leaf levels of a tile-sparse system (tools/chol_chain).
+    __shared__ int s_next;
+    auto next_task = [&]() -> int {
+        __syncthreads();
+        if (tid == 0) s_next = atomicAdd(p.next_task, 1) + (int)gridDim.x;
+        __syncthreads();
+        return s_next;
+    };
+    for (int t = blockIdx.x; t < p.ntasks && !aborted; t = next_task()) {
         const int4 tk = __ldg(p.task + t);
         const int i = tk.x, j = tk.y, kbeg = tk.w;       // klist[kbeg ..): k-blocks with L_ik and L_jk both filled
         const int nkb = __ldg(&p.task[t + 1].w) - tk.w;
@@ -482,8 +515,21 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         for (int a = 0; a < MI; ++a)
 #pragma unroll
             for (int b = 0; b < NJ; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        // ---- chain fusion (64-row tiles) ----
+        // On a tile-sparse system the kernel IS the chain  potrf(c) -> trsm(i, c) -> last k-block of (i, i) -> potrf(i)  along the
+        // separators, and between two potrf's the data crossed the chip twice: the trsm task waited for L_cc^-1, published L_ic
+        // (global stores, fence, flag), and only then did the diagonal task find the flag and fetch the tile.  Instead, the
+        // off-diagonal task whose column c is the diagonal task's LAST k-block (plan: partner) hands over its tile BEFORE the
+        // TRSM (C2 = A_ic - sum_k L_ik L_ck^T, ready one link earlier); the diagonal task runs the TRSM itself as soon as
+        // L_cc^-1 is published, applies L_ic to its own tile straight from shared memory and goes into potrf(i).  Both tasks
+        // run the same TRSM code on the same C2, so the tile the trsm task publishes for everybody else is bit-identical.
+        constexpr bool FUSE = (NB == 64);                  // (128-row tiles: no registers for the second accumulator set)
+        const bool fused = FUSE && diag && nkb > 0;
+        const bool hands_over = FUSE && !diag && i < T && p.partner[t] != 0;
+        const int fc = fused ? __ldg(p.klist + kbeg + nkb - 1) : -1;
+        const int nkb_main = fused ? nkb - 1 : nkb;        // the fused k-block is applied from shared memory after the loop
 
-        const int nk = nkb * KSL;                          // k-slices of the bulk update
+        const int nk = nkb_main * KSL;                     // k-slices of the bulk update
         int have = 0;                                      // leading klist entries known to be final in both row panels
         // L_ik and L_jk final for klist entry q.  Called at uniform points by ALL threads; only warp 0 touches the flags:
         // lane l probes the flag of entry q + l / 2 (row panel i or j) with a relaxed load, one ballot finds how many
@@ -495,13 +541,13 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (warp == 0) {
                 const int e = q + (lane >> 1);
                 int ok = 1;
-                if (e < nkb && !(diag && (lane & 1))) {
+                if (e < nkb_main && !(diag && (lane & 1))) {
                     const int kb = __ldg(p.klist + kbeg + e);
                     ok = ld_relaxed(p.tiledone + (size_t)((lane & 1) ? j : i) * T + kb);
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, ok == 0);
                 int h = m ? (__ffs(m) - 1) >> 1 : 16;      // leading complete entries
-                h = min(q + h, nkb);
+                h = min(q + h, nkb_main);
                 if (h == q) {                              // entry q itself is pending: wait for it
                     if (lane == 0) {
                         const int kb = __ldg(p.klist + kbeg + q);
@@ -554,6 +600,90 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
         if (aborted) break;
         if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 1] = global_ns();
 
+        // r = (tile staged in tileC) * L_cc^-T : A operand = the staged tile, B operand = invL of column jc through a 2-stage ring
+        // in the scratch.  Ends with a CTA barrier (tileC and the scratch are free again).
+        auto trsm_mul = [&](double (&r)[MI][NJ][2], int jc) {
+            const double *Ig = p.invL + (size_t)jc * NB * NB;
+#pragma unroll
+            for (int a = 0; a < MI; ++a)
+#pragma unroll
+                for (int b = 0; b < NJ; ++b) r[a][b][0] = r[a][b][1] = 0.0;
+            if constexpr (NB / BK <= 2) {                  // both k-slices fit the scratch: one round trip to L2 instead of two
+#pragma unroll
+                for (int kt = 0; kt < NB / BK; ++kt) load_slice<NB>(scratch + (size_t)kt * NB * SPAD, Ig + (size_t)kt * BK, NB, tid);
+                cp_async_commit();
+                cp_async_wait<0>();
+                __syncthreads();
+#pragma unroll
+                for (int kt = 0; kt < NB / BK; ++kt) {
+                    const double *a_s = tileC + (size_t)(wm * WR + g) * LDT + kt * BK + tig;
+                    const double *b_s = scratch + (size_t)kt * NB * SPAD + (size_t)(wn * WC + g) * SPAD + tig;
+                    // L_cc^-1 is lower triangular: k-slices entirely right of this warp's columns are zero
+                    if (kt * BK <= wn * WC + WC - 1) mma_slice<MI, NJ>(r, a_s, LDT, b_s);
+                }
+                __syncthreads();
+            } else {
+                load_slice<NB>(scratch, Ig, NB, tid);
+                cp_async_commit();
+                for (int kt = 0; kt < NB / BK; ++kt) {
+                    if (kt + 1 < NB / BK) load_slice<NB>(scratch + (size_t)((kt + 1) & 1) * NB * SPAD, Ig + (size_t)(kt + 1) * BK, NB, tid);
+                    cp_async_commit();
+                    cp_async_wait<1>();
+                    __syncthreads();
+                    const double *a_s = tileC + (size_t)(wm * WR + g) * LDT + kt * BK + tig;
+                    const double *b_s = scratch + (size_t)(kt & 1) * NB * SPAD + (size_t)(wn * WC + g) * SPAD + tig;
+                    if (kt * BK <= wn * WC + WC - 1) mma_slice<MI, NJ>(r, a_s, LDT, b_s);
+                    __syncthreads();
+                }
+            }
+        };
+        if constexpr (FUSE) {
+            if (fused) {
+                // the own tile is needed right after the TRSM: it travels into shared memory (behind the TRSM's scratch; the ring is
+                // idle now) while the task waits for the hand-over and for potrf(c)
+                {
+                    const double *Aii = tile_ptr(i, i);
+                    for (int idx = tid; idx < NB * NB / 2; idx += 256) {
+                        const int r = idx / (NB / 2), c2 = (idx % (NB / 2)) * 2;
+                        cp_async16(own + (size_t)r * LDT + c2, Aii + (size_t)r * ld + c2);
+                    }
+                    cp_async_commit();
+                }
+                if (tid == 0 && !wait_ge(p.c2done + i, 1, p.abort_flag, waited)) aborted = true;
+                aborted = __syncthreads_or(aborted);
+                if (aborted) break;
+                const double *C2 = p.c2buf + (size_t)i * NB * NB;
+                for (int idx = tid; idx < NB * NB / 2; idx += 256) {
+                    const int r = idx / (NB / 2), c2 = (idx % (NB / 2)) * 2;
+                    *reinterpret_cast<double2 *>(tileC + (size_t)r * LDT + c2) = __ldcg(reinterpret_cast<const double2 *>(C2 + (size_t)r * NB + c2));
+                }
+                if (tid == 0 && !wait_ge(p.tiledone + (size_t)fc * T + fc, 1, p.abort_flag, waited)) aborted = true;
+                aborted = __syncthreads_or(aborted);       // (also: tileC is complete)
+                if (aborted) break;
+                if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 1] = global_ns();
+                double r[MI][NJ][2];
+                trsm_mul(r, fc);                           // r = L_ic
+                // L_ic as KSL k-slices in the scratch, then the diagonal tile's last k-block straight from shared memory
+#pragma unroll
+                for (int a = 0; a < MI; ++a) {
+                    const int row = wm * WR + a * 8 + g;
+#pragma unroll
+                    for (int b = 0; b < NJ; ++b) {
+                        const int col = wn * WC + b * 8 + 2 * tig;
+                        *reinterpret_cast<double2 *>(scratch + (size_t)(col / BK) * NB * SPAD + (size_t)row * SPAD + (col % BK)) =
+                            make_double2(r[a][b][0], r[a][b][1]);
+                    }
+                }
+                __syncthreads();
+#pragma unroll
+                for (int ks = 0; ks < KSL; ++ks) {
+                    const double *sl = scratch + (size_t)ks * NB * SPAD;
+                    mma_slice<MI, NJ>(acc, sl + (size_t)(wm * WR + g) * SPAD + tig, SPAD, sl + (size_t)(wn * WC + g) * SPAD + tig);
+                }
+                __syncthreads();                           // the scratch is potrf's work area next
+            }
+        }
+
         // C = A_ij - acc  -> shared tile
         {
             const double *Cg = tile_ptr(i, j);
@@ -563,20 +693,27 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 #pragma unroll
                 for (int b = 0; b < NJ; ++b) {
                     const int col = wn * WC + b * 8 + 2 * tig;
-                    double2 v = *reinterpret_cast<const double2 *>(Cg + (size_t)row * ld + col);
+                    double2 v = fused ? *reinterpret_cast<const double2 *>(own + (size_t)row * LDT + col)
+                                      : *reinterpret_cast<const double2 *>(Cg + (size_t)row * ld + col);
                     v.x -= acc[a][b][0]; v.y -= acc[a][b][1];
                     if (diag) {                            // strict upper starts as the zero part of [A; I]'s identity
                         if (col > row) v.x = 0.0;
                         if (col + 1 > row) v.y = 0.0;
                     }
                     *reinterpret_cast<double2 *>(tileC + (size_t)row * LDT + col) = v;
+                    if (hands_over) __stcg(reinterpret_cast<double2 *>(p.c2buf + (size_t)i * NB * NB + (size_t)row * NB + col), v);
                 }
             }
+        }
+        if (hands_over) {                                  // chain fusion: the row's diagonal task takes the tile from here
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) st_release(p.c2done + i, 1);
         }
         __syncthreads();
         if (diag) {
             const long long tp0 = p.prof ? global_ns() : 0;
-            const bool bad = potrf_inverse_tile<NB>(tileC, Pv, invd, dinv, s_piv, potrf_calls++ & 1u);
+            const bool bad = potrf_inverse_tile<NB>(tileC, Pv, invd, dinv, s_piv, potrf_calls++ & 1u, sweep_warp);
             if (p.prof) t_potrf += global_ns() - tp0;
             if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
             // L_jj^-1 first: it is all the TRSMs (and the back substitution) wait for; L_jj itself is only stored for the
@@ -608,24 +745,7 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
             if (aborted) break;
             const long long tt0 = p.prof ? global_ns() : 0;
             if (p.task_prof && tid == 0) p.task_prof[4 * (size_t)t + 2] = global_ns();
-            const double *Ig = p.invL + (size_t)j * NB * NB;
-#pragma unroll
-            for (int a = 0; a < MI; ++a)
-#pragma unroll
-                for (int b = 0; b < NJ; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-            load_slice<NB>(scratch, Ig, NB, tid);
-            cp_async_commit();
-            for (int kt = 0; kt < NB / BK; ++kt) {
-                if (kt + 1 < NB / BK) load_slice<NB>(scratch + (size_t)((kt + 1) & 1) * NB * SPAD, Ig + (size_t)(kt + 1) * BK, NB, tid);
-                cp_async_commit();
-                cp_async_wait<1>();
-                __syncthreads();
-                const double *a_s = tileC + (size_t)(wm * WR + g) * LDT + kt * BK + tig;
-                const double *b_s = scratch + (size_t)(kt & 1) * NB * SPAD + (size_t)(wn * WC + g) * SPAD + tig;
-                // L_jj^-1 is lower triangular: k-slices entirely right of this warp's columns are zero
-                if (kt * BK <= wn * WC + WC - 1) mma_slice<MI, NJ>(acc, a_s, LDT, b_s);
-                __syncthreads();
-            }
+            trsm_mul(acc, j);
             double *Cg = tile_ptr(i, j);
 #pragma unroll
             for (int a = 0; a < MI; ++a) {
@@ -735,7 +855,8 @@ __global__ void __launch_bounds__(256, 1) chol_dataflow_kernel(CholArgs p) {
 // -------------------------------------------------------------------------------------------------------------
 // host side
 // -------------------------------------------------------------------------------------------------------------
-static int g_chol_grid[64];     // per device: SM count = CTAs of the persistent grid (0 = not initialised)
+static int g_chol_grid[64];     // per device: CTAs of the persistent grid of the 128-row kernel (0 = not initialised)
+static int g_chol_grid64[64];   // ... and of the 64-row kernel (co-resident CTAs per SM from the occupancy query)
 long long *g_chol_prof = nullptr;
 long long *g_chol_task_prof = nullptr;   // tools/chol_prof.cu only: [ntasks][4] + [T]   // tools/chol_prof.cu only: device buffer [grid][8] of per-CTA timings
 
@@ -756,6 +877,11 @@ int chol_init() {
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_dataflow_kernel<128>, 256, ChCfg<128>::SMEM);
     if (e != cudaSuccess) return (int)e;
     if (per_sm < 1) return (int)cudaErrorLaunchOutOfResources;
+    int per_sm64 = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm64, chol_dataflow_kernel<64>, 256, ChCfg<64>::SMEM);
+    if (e != cudaSuccess) return (int)e;
+    if (per_sm64 < 1) return (int)cudaErrorLaunchOutOfResources;
+    g_chol_grid64[dev] = sms * std::min(per_sm64, 2);
     g_chol_grid[dev] = sms;       // one CTA per SM (shared memory allows exactly one)
     return 0;
 }
@@ -855,7 +981,7 @@ struct HostPlan {
     std::vector<unsigned char> blob;
     std::vector<long long> toff;          // [(T + 1) * T]
     long long front_doubles = 0, extra_doubles = 0, total_doubles = 0;
-    size_t o_task = 0, o_kl = 0, o_fill = 0, o_toff = 0;
+    size_t o_task = 0, o_kl = 0, o_fill = 0, o_toff = 0, o_partner = 0;
     int T = 0, ntasks = 0, depth = 0;
     long long filled = 0;
     double flops = 0.0;
@@ -933,9 +1059,23 @@ void plan_analyse(int n, int NB, const unsigned char *nz, HostPlan &hp, size_t e
     const size_t o_task = 0, o_kl = o_task + sizeof(int4) * task.size();
     const size_t o_fill = o_kl + sizeof(int) * std::max<size_t>(klist.size(), 1);
     const size_t o_toff = (o_fill + f.size() + 15) & ~(size_t)15;
-    const size_t bytes = o_toff + sizeof(long long) * hp.toff.size();
+    const size_t o_partner = o_toff + sizeof(long long) * hp.toff.size();
+    const size_t bytes = o_partner + task.size();
     std::vector<unsigned char> &blob = hp.blob;
     blob.assign(bytes, 0);
+    // chain fusion: the off-diagonal task (i, c) whose column is the LAST k-block of diagonal task (i, i) hands its
+    // pre-TRSM tile to that task
+    {
+        std::vector<int> at((size_t)(T + 1) * T, -1);
+        for (size_t q = 0; q + 1 < task.size(); ++q) at[(size_t)task[q].x * T + task[q].y] = (int)q;
+        for (size_t q = 0; q + 1 < task.size(); ++q) {
+            const int nkb = task[q + 1].w - task[q].w;
+            if (task[q].x != task[q].y || nkb <= 0) continue;
+            const int c = klist[(size_t)task[q].w + nkb - 1];
+            blob[o_partner + (size_t)at[(size_t)task[q].x * T + c]] = 1;
+        }
+    }
+    hp.o_partner = o_partner;
     std::memcpy(blob.data() + o_toff, hp.toff.data(), sizeof(long long) * hp.toff.size());
     hp.o_toff = o_toff;
     std::memcpy(blob.data() + o_task, task.data(), sizeof(int4) * task.size());
@@ -977,6 +1117,7 @@ int chol_plan_create(int n, int nb, const unsigned char *nz, CholPlan *pl, cudaS
     pl->klist = reinterpret_cast<const int *>(b + hp.o_kl);
     pl->fill = b + hp.o_fill;
     pl->tile_off = reinterpret_cast<const long long *>(b + hp.o_toff);
+    pl->partner = b + hp.o_partner;
     pl->h_tile_off = hp.toff;
     pl->front_doubles = hp.front_doubles; pl->extra_doubles = hp.extra_doubles; pl->total_doubles = hp.total_doubles;
     pl->filled_tiles = hp.filled;
@@ -1029,13 +1170,16 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
     p.A = A; p.toff = plan->tile_off; p.T = T; p.n = n;
     p.invL = work;
     p.ypad = work + (size_t)T * NB * NB;
-    int *flags = reinterpret_cast<int *>(p.ypad + (size_t)T * NB);
-    p.tiledone = flags; p.ydone = flags + (size_t)(T + 1) * T; p.abort_flag = p.ydone + T;
+    p.c2buf = p.ypad + (size_t)T * NB;
+    int *flags = reinterpret_cast<int *>(p.c2buf + (size_t)T * NB * NB);
+    p.tiledone = flags; p.ydone = flags + (size_t)(T + 1) * T; p.c2done = p.ydone + T; p.abort_flag = p.c2done + T; p.next_task = p.abort_flag + 1; p.sm_slot = p.next_task + 1;
+    p.partner = plan->partner;
     p.y = y; p.state = state; p.fail_flag = fail_flag; p.prof = g_chol_prof; p.task_prof = g_chol_task_prof;
     p.task = plan->task; p.klist = plan->klist; p.fill = plan->fill; p.ntasks = plan->ntasks;
     cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)chol_flag_count(T), s);
     if (e != cudaSuccess) return (int)e;
-    int grid = g_chol_grid[dev] < plan->ntasks ? g_chol_grid[dev] : plan->ntasks;
+    const int cap = NB == 64 ? g_chol_grid64[dev] : g_chol_grid[dev];
+    int grid = cap < plan->ntasks ? cap : plan->ntasks;
     if (grid < 1) return (int)cudaErrorInitializationError;
     void *args[] = {&p};
     if (NB == 128) e = cudaLaunchCooperativeKernel((const void *)chol_dataflow_kernel<128>, dim3(grid), dim3(256), args, ChCfg<128>::SMEM, s);

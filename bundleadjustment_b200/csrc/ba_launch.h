@@ -82,6 +82,7 @@ size_t chol_work_doubles(int n, int nb);
 struct CholPlan {
     int n = 0, nb = 128, T = 0, ntasks = 0;       // nb = tile edge (64 | 128)
     const int4 *task = nullptr; const int *klist = nullptr; const unsigned char *fill = nullptr;
+    const unsigned char *partner = nullptr;   // [ntasks] chain fusion: off-diagonal tasks that hand their pre-TRSM tile to the row's diagonal task
     const long long *tile_off = nullptr;      // device [(T + 1) * T]: offset of tile (i, j) in doubles, -1 = not in the plan
     std::vector<long long> h_tile_off;        // host copy
     long long front_doubles = 0;     // the tiles S itself can touch are stored first: [0, front_doubles)

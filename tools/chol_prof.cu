@@ -35,7 +35,7 @@ int main(int argc, char **argv) {
     const int ld = chol_ld(n, nb);
     double *A, *work, *y;
     cudaMalloc(&work, 8 * chol_work_doubles(n, nb)); cudaMemset(work, 0, 8 * chol_work_doubles(n, nb)); cudaMalloc(&y, 8 * (size_t)ld);
-    cudaMalloc(&g_chol_prof, 8 * 8 * 256);
+    cudaMalloc(&g_chol_prof, 8 * 8 * 512); cudaMemset(g_chol_prof, 0, 8 * 8 * 512);
     if (chol_init()) { printf("chol_init failed\n"); return 1; }
     // tile plan of the band (exact tile pattern of fill_spd)
     const int Tp = ld / nb;
@@ -59,10 +59,10 @@ int main(int argc, char **argv) {
         float ms; cudaEventElapsedTime(&ms, e0, e1);
         best = std::min(best, ms);
     }
-    std::vector<long long> h(8 * 256);
-    cudaMemcpy(h.data(), g_chol_prof, 8 * 8 * 256, cudaMemcpyDeviceToHost);
+    std::vector<long long> h(8 * 512);
+    cudaMemcpy(h.data(), g_chol_prof, 8 * 8 * 512, cudaMemcpyDeviceToHost);
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-    const int T = ld / nb, grid = std::min(sms, T * (T + 3) / 2);
+    const int T = ld / nb, grid = std::min(sms * (nb == 64 ? 2 : 1), T * (T + 3) / 2);
     long long t0 = h[0], tend = 0;
     for (int b = 0; b < grid; ++b) { t0 = std::min(t0, h[8 * b]); tend = std::max(tend, h[8 * b + 2]); }
     double s_p1 = 0, s_w1 = 0, s_w2 = 0, s_potrf = 0, s_trsm = 0, max_p1 = 0, s_tasks = 0, potrf_tiles = T;
