@@ -133,6 +133,16 @@ __device__ __forceinline__ double fast_rcp(double d) {
     return fma(r, e, r);
 }
 
+// the same with ONE third-order step, r (1 + e + e^2) with e = 1 - d r: three dependent FP64 operations after the seed instead of
+// four (relative error e^3 < 2^-60 for the >= 20-bit seed) -- for the serial pivot chain of potrf
+__device__ __forceinline__ double fast_rcp3(double d) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;\n" : "=d"(r) : "d"(d));
+    const double e = fma(-d, r, 1.0);
+    const double t = fma(e, e, e);
+    return fma(r, t, r);
+}
+
 struct CholArgs {
     double *A;            // tile-packed matrix (see the layout contract)
     const long long *toff;   // [(T + 1) * T] offset of tile (i, j) in doubles, -1 = not part of the plan
@@ -240,14 +250,30 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
             // Column j of the current matrix is broadcast through shared memory (one store per lane, 16-byte broadcast loads)
             // instead of 2 x (31 - j) shuffles; column j of the unit factor stays UNSCALED in Lc[j][.] (= l_ij d_j).
             double myd = 1.0;                                // d_lane
+            // Software-pipelined by one pivot: pivot j's update is applied EARLY only to column j + 1 (the next pivot column);
+            // its update of columns j + 2 .. is issued in the next iteration, in the shadow of that pivot's serial chain
+            // (store -> broadcast load -> reciprocal).  Every element still receives its updates in pivot order.
+            double ajs_prev = 0.0;
 #pragma unroll
             for (int j = 0; j < PB; ++j) {
                 Lc[j * LDQ + lane] = a[j];
                 __syncwarp();
                 double d = Lc[j * LDQ + j];
                 if (!(d > 1e-300) || isinf(d)) { d = 1.0; bad = true; }
-                const double rd = fast_rcp(d);
+                const double rd = fast_rcp3(d);
                 if (lane == j) myd = d;
+                if (j >= 1) {                                // deferred: pivot j - 1 on columns j + 1 .. PB - 1
+                    if ((j + 1) & 1) { if (j + 1 < PB) a[j + 1] = fma(-ajs_prev, Lc[(j - 1) * LDQ + j + 1], a[j + 1]); }
+#pragma unroll
+                    for (int c = (j + 2) & ~1; c < PB; c += 2) {      // 16-byte broadcast loads of column pairs
+                        const double2 ac = *reinterpret_cast<const double2 *>(Lc + (j - 1) * LDQ + c);
+                        a[c] = fma(-ajs_prev, ac.x, a[c]);
+                        a[c + 1] = fma(-ajs_prev, ac.y, a[c + 1]);
+                    }
+                }
+                const double ajs = a[j] * rd;
+                if (j + 1 < PB) a[j + 1] = fma(-ajs, Lc[j * LDQ + j + 1], a[j + 1]);      // early: the next pivot column
+                ajs_prev = ajs;
                 if (lane == 0) {                                 // column j and 1 / d_j are final: hand them to warp 1
                     rdv[j] = rd;
 #if POTRF_HANDOFF == 2
@@ -257,14 +283,6 @@ __device__ __noinline__ bool potrf_inverse_tile(double *__restrict__ Ts, double 
 #else
                     st_release_cta(prog, c0 + j + 1);
 #endif
-                }
-                const double ajs = a[j] * rd;
-                if (((j + 1) & 1) && j + 1 < PB) a[j + 1] = fma(-ajs, Lc[j * LDQ + j + 1], a[j + 1]);
-#pragma unroll
-                for (int c = (j + 2) & ~1; c < PB; c += 2) {          // 16-byte broadcast loads of column pairs
-                    const double2 ac = *reinterpret_cast<const double2 *>(Lc + j * LDQ + c);
-                    a[c] = fma(-ajs, ac.x, a[c]);
-                    a[c + 1] = fma(-ajs, ac.y, a[c + 1]);
                 }
             }
             // (Round 2 measured two alternatives of this sweep on the 64-row banded system and dropped both, profiles/
