@@ -388,7 +388,11 @@ def run_workload(D: Dist, bab, args, workload: str, solver_name: str, steps: int
     cpu = None
     if world > 1:
         if rank == 0:
-            parity = bab.parity.compare(pb_full, got_sol, ref_sol)
+            # (PCG: truncated-CG steps are inexact and the matvec's f64 atomics order differently on every run and shard count;
+            # the trajectory is held to 1e-5 for the reason given at the CPU-sample gate below.  Dense Schur: 1e-6.)
+            parity = bab.parity.compare(pb_full, got_sol, ref_sol, cost_rtol=1e-5 if solver_name == "pcg" else 1e-6)
+            if solver_name == "pcg":
+                parity["note"] = "inexact-Newton (truncated CG) trajectory: 1e-5 relative per iteration; final cost 1e-8, poses 1e-6, landmarks by the stated bound"
             parity["against"] = "single-GPU solve of the same problem (rank 0, no communicator)"
     elif with_cpu:
         cpu, cpu_sol = cpu_baseline(pb_full, workload, solver_name, args.lm_iters)       # the oracle as the CHECKER and the CPU baseline
@@ -421,10 +425,12 @@ def run_workload(D: Dist, bab, args, workload: str, solver_name: str, steps: int
     for _ in range(warmup):
         solver.reset_parameters()
         solver.solve()
-    D.barrier()
     sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.start()                 # (before the barrier: spawning nvidia-smi takes rank 0 tens of milliseconds, which the
+                                        # other ranks' first timed solve would otherwise spend waiting in its first collective)
+    torch.cuda.synchronize()
+    D.barrier()
     t_dev, t_lin, t_eval, t_dom, n_it, n_solves, launches, n_dom = 0.0, 0.0, 0.0, 0.0, 0, 0, 0, 0
     wall0 = time.perf_counter()
     last = None
