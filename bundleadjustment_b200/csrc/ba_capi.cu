@@ -611,24 +611,23 @@ int enqueue_linear_solve(ba_handle *h) {
     const Ctx &ctx = h->ctx;
     cudaStream_t s = h->stream;
     int rc;
-    launch_point_invert(ctx, -1.0, s);
-    h->launches += 1;
     if (h->opt.linear_solver == BA_DENSE_SCHUR) {
         if ((rc = chol_clear(ctx.S, &h->chol_plan, s))) return fail(BA_ERR_CUDA, "chol_clear: %s", cudaGetErrorString((cudaError_t)rc));
-        launch_schur_build(ctx, -1.0, s);
+        launch_point_invert_schur_build(ctx, s);          // (V + D^2)^-1 and the initialisation of S share one launch
         h->launches += 4;
         if ((rc = allreduce_S(h))) return rc;
-        // rhs^T becomes row ldS of the matrix: the forward substitution is then part of the factorisation's dataflow
-        launch_chol_rhs(ctx, s);
+        // rhs^T is row ldS of the matrix: the forward substitution is part of the factorisation's dataflow.  The kernel reads it
+        // from the camera-ordered rhs through row_src and writes the solution back in camera order (no permutation launches).
         if (h->profile) cudaEventRecord(h->dom_event(), s);
-        const int ce = chol_factor_solve(ctx.S, ctx.ldS, h->invL.as<double>(), h->yperm.as<double>(), ctx.state, nullptr, &h->chol_plan, s);
+        const CholPerm perm{ctx.row_src, ctx.rhs, ctx.yc};
+        const int ce = chol_factor_solve(ctx.S, ctx.ldS, h->invL.as<double>(), h->yperm.as<double>(), ctx.state, nullptr, &h->chol_plan, s, &perm);
         if (ce) return fail(BA_ERR_CUDA, "chol_factor_solve: %s", cudaGetErrorString((cudaError_t)ce));
         if (h->profile) cudaEventRecord(h->dom_event(), s);
-        launch_chol_unpermute(ctx, h->yperm.as<double>(), s);
-        h->launches += 3;
+        h->launches += 1;
     } else {
+        launch_point_invert(ctx, -1.0, s);
         launch_pcg_setup(ctx, s);
-        h->launches += 2;
+        h->launches += 3;
         if ((rc = allreduce_sum(h, ctx.Minv, 36 * (size_t)ctx.Nc))) return rc;
         if ((rc = allreduce_sum(h, ctx.rhs, (size_t)ctx.n))) return rc;
         launch_pcg_start(ctx, s);
@@ -654,9 +653,8 @@ int enqueue_linear_solve(ba_handle *h) {
                 launch_pcg_reset_b(ctx, s);
                 h->launches += 3;   // matvec, fold, reset
             }
-            launch_pcg_check(ctx, s);
-            launch_pcg_publish(ctx, it, s);
-            h->launches += 2;
+            launch_pcg_check(ctx, it, s);
+            h->launches += 1;
             CU(cudaEventRecord(h->ev_ring[it % R], s));
         }
         launch_pcg_finish(ctx, s);
@@ -716,9 +714,8 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         launch_backsub(ctx, s);
         launch_eval_candidate(ctx, h->cost_part.as<double>(), s);
         if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_STEP_BEGIN, ctx.sums + SUM_STEP_BEGIN, SUM_STEP_N))) { status = rc; break; }
-        launch_decide(ctx, s);
-        launch_lm_publish(ctx, k, s);
-        h->launches += 7;
+        launch_decide(ctx, k, s);
+        h->launches += 6;
         cudaEventRecord(ev_lm[k & 1], s);
     }
     cudaEventRecord(h->ev_stop, s);

@@ -156,6 +156,11 @@ struct CholArgs {
     int *c2done;          // [T] c2buf[i] is complete
     int *next_task;       // [1] tickets handed out beyond the first gridDim.x tasks
     int *sm_slot;         // [256] CTAs that have started on each SM
+    // optional (LM loop): right-hand side read as rhs_cam[row_src[i]] (0 where row_src[i] < 0) instead of the rhs tiles, solution also
+    // written to y_cam[row_src[i]] -- the camera-order <-> elimination-order permutations without launches of their own
+    const int *row_src;
+    const double *rhs_cam;
+    double *y_cam;
     const unsigned char *partner;   // [ntasks] != 0: off-diagonal task (i, c) whose column c is the LAST k-block of diagonal task (i, i)
     int *abort_flag;      // [1] set when a wait timed out (never expected; keeps a bug from hanging the GPU)
     double *y;            // [n]
@@ -711,8 +716,16 @@ __global__ void __launch_bounds__(256, NB == 64 ? 2 : 1) chol_dataflow_kernel(Ch
 #pragma unroll
                 for (int b = 0; b < NJ; ++b) {
                     const int col = wn * WC + b * 8 + 2 * tig;
-                    double2 v = fused ? *reinterpret_cast<const double2 *>(own + (size_t)row * LDT + col)
-                                      : *reinterpret_cast<const double2 *>(Cg + (size_t)row * ld + col);
+                    double2 v;
+                    if (fused) v = *reinterpret_cast<const double2 *>(own + (size_t)row * LDT + col);
+                    else if (i == T && p.rhs_cam) {        // rhs tile: row 0 = the camera-ordered right-hand side, permuted on the fly
+                        v = make_double2(0.0, 0.0);
+                        if (row == 0) {
+                            const int s0 = __ldg(p.row_src + j * NB + col), s1 = __ldg(p.row_src + j * NB + col + 1);
+                            v.x = s0 >= 0 ? __ldcg(p.rhs_cam + s0) : 0.0;
+                            v.y = s1 >= 0 ? __ldcg(p.rhs_cam + s1) : 0.0;
+                        }
+                    } else v = *reinterpret_cast<const double2 *>(Cg + (size_t)row * ld + col);
                     v.x -= acc[a][b][0]; v.y -= acc[a][b][1];
                     if (diag) {                            // strict upper starts as the zero part of [A; I]'s identity
                         if (col > row) v.x = 0.0;
@@ -856,7 +869,10 @@ __global__ void __launch_bounds__(256, NB == 64 ? 2 : 1) chol_dataflow_kernel(Ch
 #pragma unroll
             for (int qq = 0; qq < PARTS; ++qq) v += part[qq * NB + tid];
             p.ypad[(size_t)m * NB + tid] = v;
-            if (m * NB + tid < p.n) p.y[m * NB + tid] = v;
+            if (m * NB + tid < p.n) {
+                p.y[m * NB + tid] = v;
+                if (p.y_cam) { const int src = __ldg(p.row_src + m * NB + tid); if (src >= 0) p.y_cam[src] = v; }
+            }
         }
         __threadfence();
         __syncthreads();
@@ -1178,7 +1194,8 @@ void chol_pack_host(const CholPlan *pl, const double *A, const double *b, std::v
     }
 }
 
-int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s) {
+int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s,
+                      const CholPerm *perm) {
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
@@ -1192,6 +1209,7 @@ int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state,
     int *flags = reinterpret_cast<int *>(p.c2buf + (size_t)T * NB * NB);
     p.tiledone = flags; p.ydone = flags + (size_t)(T + 1) * T; p.c2done = p.ydone + T; p.abort_flag = p.c2done + T; p.next_task = p.abort_flag + 1; p.sm_slot = p.next_task + 1;
     p.partner = plan->partner;
+    p.row_src = perm ? perm->row_src : nullptr; p.rhs_cam = perm ? perm->rhs_cam : nullptr; p.y_cam = perm ? perm->y_cam : nullptr;
     p.y = y; p.state = state; p.fail_flag = fail_flag; p.prof = g_chol_prof; p.task_prof = g_chol_task_prof;
     p.task = plan->task; p.klist = plan->klist; p.fill = plan->fill; p.ntasks = plan->ntasks;
     cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)chol_flag_count(T), s);

@@ -383,11 +383,11 @@ __device__ __forceinline__ double lm_diag(const Ctx &ctx, double jtj, double rad
     return fmin(fmax(jtj, ctx.opt.min_lm_diagonal), ctx.opt.max_lm_diagonal) / radius;
 }
 
-__global__ void __launch_bounds__(128) point_invert_kernel(Ctx ctx, double radius_override) {
+__device__ __forceinline__ void point_invert_block(const Ctx &ctx, double radius_override, int bid) {
     const LMState *st = ctx.state;
     if (radius_override <= 0 && st->done) return;
     const double radius = radius_override > 0 ? radius_override : st->radius;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int p = bid * blockDim.x + threadIdx.x;
     if (p >= ctx.Np) return;
     const double *V = ctx.V + 6 * (size_t)p;
     double m[6] = {V[0], V[1], V[2], V[3], V[4], V[5]};
@@ -409,12 +409,14 @@ __global__ void __launch_bounds__(128) point_invert_kernel(Ctx ctx, double radiu
     w[2] = inv[2] * b[0] + inv[4] * b[1] + inv[5] * b[2];
 }
 
+__global__ void __launch_bounds__(128) point_invert_kernel(Ctx ctx, double radius_override) { point_invert_block(ctx, radius_override, blockIdx.x); }
+
 // diagonal blocks + rhs initialisation (S has been zeroed).  Only rank 0 contributes the replicated terms.
-__global__ void schur_init_kernel(Ctx ctx, double radius_override) {
+__device__ __forceinline__ void schur_init_block(const Ctx &ctx, double radius_override, int bid) {
     const LMState *st = ctx.state;
     if (radius_override <= 0 && st->done) return;
     const double radius = radius_override > 0 ? radius_override : st->radius;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one thread per row of S
+    const int i = bid * blockDim.x + threadIdx.x;             // one thread per row of S
     if (i >= ctx.ldS) return;
     const bool lead = ctx.rank == 0;
     const int src = ctx.row_src[i];
@@ -433,21 +435,16 @@ __global__ void schur_init_kernel(Ctx ctx, double radius_override) {
     }
 }
 
-// rhs (camera order) -> row ldS of S (elimination order); solution y (elimination order) -> yc (camera order)
-__global__ void chol_rhs_kernel(Ctx ctx) {
-    if (ctx.state->done) return;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= ctx.ldS) return;
-    const int src = ctx.row_src[i];
-    ctx.S[ctx.S_toff[(size_t)ctx.S_T * ctx.S_T + (i >> ctx.S_shift)] + (i & (ctx.S_nb - 1))] = src >= 0 ? ctx.rhs[src] : 0.0;     // row 0 of rhs tile i / nb
+__global__ void schur_init_kernel(Ctx ctx, double radius_override) { schur_init_block(ctx, radius_override, blockIdx.x); }
+// LM loop, dense Schur: (V + D^2)^-1 per landmark and the initialisation of S in ONE launch (independent work: the first
+// n_point_blocks CTAs take the landmarks, the rest the rows of S)
+__global__ void __launch_bounds__(128) point_invert_schur_init_kernel(Ctx ctx, int n_point_blocks) {
+    if ((int)blockIdx.x < n_point_blocks) point_invert_block(ctx, -1.0, blockIdx.x);
+    else schur_init_block(ctx, -1.0, blockIdx.x - n_point_blocks);
 }
-__global__ void chol_unpermute_kernel(Ctx ctx, const double *__restrict__ y) {
-    if (ctx.state->done) return;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= ctx.ldS) return;
-    const int src = ctx.row_src[i];
-    if (src >= 0) ctx.yc[src] = y[i];
-}
+
+// (The permutations rhs (camera order) -> rhs row of S (elimination order) and y (elimination order) -> yc (camera order)
+// happen inside the Cholesky kernel: CholArgs::rhs_cam / y_cam / row_src.)
 
 // C5 proper: S -= sum_p W_i V'^-1 W_j^T and rhs -= sum_p W_i V'^-1 b_p as DETERMINISTIC segmented reductions over the
 // camera-pair-major index (ba_prep.cu).  One warp per unit (<= PAIR_UNIT entries of ONE S block): each lane accumulates
@@ -808,7 +805,7 @@ __global__ void lm_begin_iteration_kernel(Ctx ctx) {
 }
 
 // controller, part 2 (single thread): step validity, tolerances, rho test, accept/reject, radius update
-__global__ void lm_decide_kernel(Ctx ctx) {
+__device__ void lm_decide(const Ctx &ctx) {
     LMState *st = ctx.state;
     if (st->done) return;
     const ba_options &o = ctx.opt;
@@ -869,8 +866,11 @@ __global__ void lm_decide_kernel(Ctx ctx) {
     }
 }
 
-// verdict as of the end of an LM body, for the host's enqueue loop (see HF_LM_RING)
-__global__ void lm_publish_kernel(Ctx ctx, int slot) { ctx.host_flags[HF_LM_RING + slot] = ctx.state->done; }
+// ... and, in the same launch, the verdict as of the end of this LM body for the host's enqueue loop (see HF_LM_RING)
+__global__ void lm_decide_kernel(Ctx ctx, int slot) {
+    lm_decide(ctx);
+    ctx.host_flags[HF_LM_RING + slot] = ctx.state->done;
+}
 
 __global__ void lm_init_state_kernel(Ctx ctx) {
     LMState *st = ctx.state;
@@ -1008,9 +1008,17 @@ void launch_compute_scale(const Ctx &ctx, cudaStream_t s) {
 }
 
 void launch_begin_iteration(const Ctx &ctx, cudaStream_t s) { lm_begin_iteration_kernel<<<1, 1, 0, s>>>(ctx); }
-void launch_decide(const Ctx &ctx, cudaStream_t s) { lm_decide_kernel<<<1, 1, 0, s>>>(ctx); }
-void launch_lm_publish(const Ctx &ctx, int body, cudaStream_t s) { lm_publish_kernel<<<1, 1, 0, s>>>(ctx, body % HF_LM_SLOTS); }
+void launch_decide(const Ctx &ctx, int body, cudaStream_t s) { lm_decide_kernel<<<1, 1, 0, s>>>(ctx, body % HF_LM_SLOTS); }
 
+// LM loop, dense Schur (S already cleared): point_invert + schur_init + schur_units + schur_segments as three launches
+void launch_point_invert_schur_build(const Ctx &ctx, cudaStream_t s) {
+    const int nA = cdiv(ctx.Np, 128);
+    point_invert_schur_init_kernel<<<nA + cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, nA);
+    if (ctx.pairs.n_units > 0) {
+        schur_units_kernel<<<cdiv(ctx.pairs.n_units, SCHUR_WARPS), SCHUR_WARPS * 32, 0, s>>>(ctx, 0);
+        schur_segments_kernel<<<(unsigned)(((long long)ctx.pairs.n_seg * 42 + 255) / 256), 256, 0, s>>>(ctx, 0);
+    }
+}
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s) {
     point_invert_kernel<<<cdiv(ctx.Np, 128), 128, 0, s>>>(ctx, radius_override);
 }
@@ -1024,8 +1032,6 @@ void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s) 
     }
 }
 
-void launch_chol_rhs(const Ctx &ctx, cudaStream_t s) { chol_rhs_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx); }
-void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s) { chol_unpermute_kernel<<<cdiv(ctx.ldS, 128), 128, 0, s>>>(ctx, y); }
 
 void launch_backsub(const Ctx &ctx, cudaStream_t s) {
     if (ctx.n_blocks > 0) backsub_kernel<<<ctx.n_blocks, TILE_THREADS, tile_smem(ctx, 21), s>>>(ctx);

@@ -15,13 +15,10 @@ void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s);
 void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s);
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s);
 void launch_begin_iteration(const Ctx &ctx, cudaStream_t s);
-void launch_decide(const Ctx &ctx, cudaStream_t s);
-void launch_lm_publish(const Ctx &ctx, int body, cudaStream_t s);        // verdict as of the end of LM body `body` -> host ring
-void launch_pcg_publish(const Ctx &ctx, int iteration, cudaStream_t s);  // verdict as of the end of CG iteration -> host ring
+void launch_decide(const Ctx &ctx, int body, cudaStream_t s);           // accept / reject + the verdict as of the end of LM body `body` -> host ring
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
+void launch_point_invert_schur_build(const Ctx &ctx, cudaStream_t s);   // LM loop, dense Schur: point_invert + schur_init in one launch, then units + segments
 void launch_schur_build(const Ctx &ctx, double radius_override, cudaStream_t s);
-void launch_chol_rhs(const Ctx &ctx, cudaStream_t s);                       // rhs -> row ldS of S, in elimination order
-void launch_chol_unpermute(const Ctx &ctx, const double *y, cudaStream_t s);  // y (elimination order) -> yc
 void launch_backsub(const Ctx &ctx, cudaStream_t s);
 void launch_eval_candidate(const Ctx &ctx, double *cost_part, cudaStream_t s);
 int tiles_init(const Ctx &ctx);                          // per-problem dynamic shared memory opt-in of the tile kernels
@@ -102,7 +99,11 @@ void chol_plan_destroy(CholPlan *plan);
 // zero the packed matrix (all tiles of the plan + the extra region) before S is assembled
 int chol_clear(double *A, const CholPlan *plan, cudaStream_t s);
 void chol_plan_stats(int n, int nb, const unsigned char *nz, int *depth, long long *filled, double *flops);   // host only
-int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s);
+// perm (may be nullptr): the LM loop's permutations folded into the kernel -- the right-hand side is READ from rhs_cam[row_src[i]]
+// (0 where row_src[i] < 0) instead of the rhs tiles, and the solution is ALSO written to y_cam[row_src[i]]
+struct CholPerm { const int *row_src; const double *rhs_cam; double *y_cam; };
+int chol_factor_solve(double *A, int n, double *work, double *y, LMState *state, int *fail_flag, const CholPlan *plan, cudaStream_t s,
+                      const CholPerm *perm = nullptr);
 
 // ba_pcg.cu -- Schur-Jacobi preconditioned CG on the implicit reduced system (C6')
 int pcg_matvec_grid(const Ctx &ctx);                          // private copies of q (cg_qp) for ctx.pcg_ordered
@@ -113,7 +114,7 @@ void launch_pcg_iter_a(const Ctx &ctx, cudaStream_t s, cudaEvent_t ev_before_mat
 void launch_pcg_iter_b(const Ctx &ctx, cudaStream_t s);      // q += (U+D^2) p, alpha, x, r   (after all-reduce of q)
 void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s);     // local landmark part of S x into cg_z
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s);     // r = b - S x                   (after all-reduce of cg_z)
-void launch_pcg_check(const Ctx &ctx, cudaStream_t s);       // stop rules
+void launch_pcg_check(const Ctx &ctx, int iteration, cudaStream_t s);   // stop rules + the verdict as of the end of this CG iteration -> host ring
 void launch_pcg_finish(const Ctx &ctx, cudaStream_t s);      // copies x -> yc, lin_iters
 
 // ba_pose_batch.cu

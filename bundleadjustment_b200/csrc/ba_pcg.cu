@@ -498,9 +498,13 @@ __global__ void __launch_bounds__(256) pcg_residual_reset_kernel(Ctx ctx) {
 }
 
 // Q1 = -x.(b + r); zeta = it (Q1 - Q0) / Q1 < eta -> stop; |r| <= r_tol |b| -> stop; it >= max -> stop
-__global__ void __launch_bounds__(RED_THREADS) pcg_check_kernel(Ctx ctx) {
+// ... and, in the same launch, the verdict as of the end of this CG iteration for the host's enqueue loop (see HF_CG_RING)
+__global__ void __launch_bounds__(RED_THREADS) pcg_check_kernel(Ctx ctx, int slot) {
     LMState *st = ctx.state;
-    CG_GUARD(st);
+    if (st->done || st->cg_done) {                 // (what CG_GUARD tests) already over: only the verdict is due
+        if (blockIdx.x == 0 && threadIdx.x == 0) ctx.host_flags[HF_CG_RING + slot] = 1;
+        return;
+    }
     __shared__ double red[128];
     double s = 0.0, rr = 0.0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ctx.n; i += gridDim.x * blockDim.x) {
@@ -520,13 +524,8 @@ __global__ void __launch_bounds__(RED_THREADS) pcg_check_kernel(Ctx ctx) {
         if (!stop && ctx.opt.cg_r_tolerance > 0 && sqrt(rr) <= ctx.opt.cg_r_tolerance * st->cg_norm_b) stop = true;
         if (!stop && it >= ctx.opt.max_linear_solver_iterations) stop = true;
         if (stop) { st->cg_done = 1; __threadfence_system(); ctx.host_flags[1] = 1; }
+        ctx.host_flags[HF_CG_RING + slot] = stop ? 1 : 0;
     }
-}
-
-// verdict as of the end of a CG iteration, for the host's enqueue loop (see HF_CG_RING)
-__global__ void pcg_publish_kernel(Ctx ctx, int slot) {
-    const LMState *st = ctx.state;
-    ctx.host_flags[HF_CG_RING + slot] = (st->done || st->cg_done) ? 1 : 0;
 }
 
 __global__ void pcg_finish_kernel(Ctx ctx) {
@@ -620,8 +619,9 @@ void launch_pcg_reset_a(const Ctx &ctx, cudaStream_t s) {     // landmark part o
     pcg_fold_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx, ctx.cg_qp, ctx.cg_z, ctx.mv_grid);
 }
 void launch_pcg_reset_b(const Ctx &ctx, cudaStream_t s) { pcg_residual_reset_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
-void launch_pcg_check(const Ctx &ctx, cudaStream_t s) { pcg_check_kernel<<<std::max(1, std::min(cdiv(ctx.n, 2 * RED_THREADS), 256)), RED_THREADS, 0, s>>>(ctx); }
-void launch_pcg_publish(const Ctx &ctx, int iteration, cudaStream_t s) { pcg_publish_kernel<<<1, 1, 0, s>>>(ctx, iteration % HF_CG_SLOTS); }
+void launch_pcg_check(const Ctx &ctx, int iteration, cudaStream_t s) {
+    pcg_check_kernel<<<std::max(1, std::min(cdiv(ctx.n, 2 * RED_THREADS), 256)), RED_THREADS, 0, s>>>(ctx, iteration % HF_CG_SLOTS);
+}
 void launch_pcg_finish(const Ctx &ctx, cudaStream_t s) { pcg_finish_kernel<<<cdiv(ctx.n, 256), 256, 0, s>>>(ctx); }
 
 } // namespace ba
