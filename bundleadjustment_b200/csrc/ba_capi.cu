@@ -593,7 +593,7 @@ int allreduce_S(ba_handle *h) {
 }
 
 // one linearisation at x: local blocks, then the replicated camera blocks are summed over ranks
-int enqueue_linearize(ba_handle *h, int force) {
+int enqueue_linearize(ba_handle *h, int force, int with_begin = 0) {
     const Ctx &ctx = h->ctx;
     launch_linearize_local(ctx, force, h->stream);
     h->launches += 5;
@@ -601,7 +601,7 @@ int enqueue_linearize(ba_handle *h, int force) {
     // ONE message [U | b_c | sums | max slots]; out-of-place so that a body that does not re-linearise reproduces the same
     // reduced blocks (the step slots of `sums` ride along and are overwritten by the step all-reduce before anyone reads them)
     if ((rc = allreduce_sum(h, h->lin_loc.as<double>(), h->lin_red.as<double>(), h->lin_count))) return rc;
-    launch_cam_norms(ctx, force, h->stream);
+    launch_cam_norms(ctx, force, with_begin, h->stream);
     h->launches += 1;
     return BA_OK;
 }
@@ -706,8 +706,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
             if (h->host_flags[HF_LM_RING + (k - 2) % HF_LM_SLOTS]) break;           // the verdict of body k - 2 (the same on every rank)
         }
         if (h->profile) cudaEventRecord(h->prof_event(), s);
-        if ((rc = enqueue_linearize(h, 0))) { status = rc; break; }
-        launch_begin_iteration(ctx, s);
+        if ((rc = enqueue_linearize(h, 0, 1))) { status = rc; break; }     // (the last kernel of it also runs controller part 1)
         if (h->profile) cudaEventRecord(h->prof_event(), s);
         if ((rc = enqueue_linear_solve(h))) { status = rc; break; }
         if (h->profile) cudaEventRecord(h->prof_event(), s);
@@ -715,7 +714,7 @@ extern "C" int ba_solve(ba_handle *h, ba_summary *summary) {
         launch_eval_candidate(ctx, h->cost_part.as<double>(), s);
         if ((rc = allreduce_sum(h, ctx.sums_loc + SUM_STEP_BEGIN, ctx.sums + SUM_STEP_BEGIN, SUM_STEP_N))) { status = rc; break; }
         launch_decide(ctx, k, s);
-        h->launches += 6;
+        h->launches += 5;
         cudaEventRecord(ev_lm[k & 1], s);
     }
     cudaEventRecord(h->ev_stop, s);

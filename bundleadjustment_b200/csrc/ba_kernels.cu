@@ -338,22 +338,32 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_lin_partials_kernel(Ctx ct
     }
 }
 
-// camera-side gradient / parameter norms from the (all-reduced) b_c; multi-CTA
-__global__ void __launch_bounds__(RED_THREADS) cam_norms_kernel(Ctx ctx, int force) {
+__device__ void lm_begin_iteration(const Ctx &ctx);      // controller, part 1 (below)
+
+// camera-side gradient / parameter norms from the (all-reduced) b_c; multi-CTA.  with_begin (LM loop): the last CTA to arrive
+// -- every CTA has read the controller state by then -- also runs controller part 1, which used to be a launch of its own;
+// when there was no re-linearisation the reduction runs on zeros just for that hand-over.
+__global__ void __launch_bounds__(RED_THREADS) cam_norms_kernel(Ctx ctx, int force, int with_begin) {
     const LMState *st = ctx.state;
-    if (!force && (st->done || !st->need_linearize)) return;
+    const bool active = force || (!st->done && st->need_linearize);
+    if (!active && !with_begin) return;
     __shared__ double red[128];
     const double *x = ctx.cam[st->cur];
     double gsq = 0, xsq = 0, gmax = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 6 * ctx.Nc; i += gridDim.x * blockDim.x) {
-        if (ctx.cam_kind[i / 6] != CAM_FREE) continue;
-        const double g = ctx.bc[i] / ctx.scale_cam[i];
-        const double d = x[i] - (x[i] + (-g));
-        gsq += d * d; gmax = fmax(gmax, fabs(d)); xsq += x[i] * x[i];
+    if (active) {
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 6 * ctx.Nc; i += gridDim.x * blockDim.x) {
+            if (ctx.cam_kind[i / 6] != CAM_FREE) continue;
+            const double g = ctx.bc[i] / ctx.scale_cam[i];
+            const double d = x[i] - (x[i] + (-g));
+            gsq += d * d; gmax = fmax(gmax, fabs(d)); xsq += x[i] * x[i];
+        }
     }
     double unused = 0.0;
     if (!grid_sum3_max(gsq, xsq, unused, gmax, red_slot(ctx, RED_CAM_NORMS), ctx.red_count + RED_CAM_NORMS, red)) return;
-    if (threadIdx.x == 0) { ctx.camsums[CS_GSQ] = gsq; ctx.camsums[CS_GMAX] = gmax; ctx.camsums[CS_XSQ] = xsq; }
+    if (threadIdx.x == 0) {
+        if (active) { ctx.camsums[CS_GSQ] = gsq; ctx.camsums[CS_GMAX] = gmax; ctx.camsums[CS_XSQ] = xsq; }
+        if (with_begin) lm_begin_iteration(ctx);
+    }
 }
 
 // Jacobi scaling from the iteration-0 (unscaled) blocks: scale = 1 / (1 + sqrt(diag(J^T J)))
@@ -759,7 +769,7 @@ __global__ void __launch_bounds__(RED_THREADS) reduce_step_partials_kernel(Ctx c
 // iteration that triggered it, records the iteration (FinalizeIterationAndCheckIfMinimizerCanContinue) and opens
 // the next one.
 // -------------------------------------------------------------------------------------------------------------
-__global__ void lm_begin_iteration_kernel(Ctx ctx) {
+__device__ void lm_begin_iteration(const Ctx &ctx) {
     LMState *st = ctx.state;
     if (st->done) return;
     const ba_options &o = ctx.opt;
@@ -1000,14 +1010,15 @@ void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s) {
     cam_reduce_kernel<<<cdiv(ctx.Nc * 32, 128), 128, 0, s>>>(ctx, force);
     reduce_lin_partials_kernel<<<red_grid(ctx.n_part, 4 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force);
 }
-void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s) { cam_norms_kernel<<<red_grid(6 * ctx.Nc, 2 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force); }
+void launch_cam_norms(const Ctx &ctx, int force, int with_begin, cudaStream_t s) {
+    cam_norms_kernel<<<red_grid(6 * ctx.Nc, 2 * RED_THREADS), RED_THREADS, 0, s>>>(ctx, force, with_begin);
+}
 
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s) {
     const int n = max(6 * ctx.Nc, 3 * ctx.Np);
     compute_scale_kernel<<<cdiv(n, 256), 256, 0, s>>>(ctx);
 }
 
-void launch_begin_iteration(const Ctx &ctx, cudaStream_t s) { lm_begin_iteration_kernel<<<1, 1, 0, s>>>(ctx); }
 void launch_decide(const Ctx &ctx, int body, cudaStream_t s) { lm_decide_kernel<<<1, 1, 0, s>>>(ctx, body % HF_LM_SLOTS); }
 
 // LM loop, dense Schur (S already cleared): point_invert + schur_init + schur_units + schur_segments as three launches

@@ -12,9 +12,8 @@ void launch_init_state(const Ctx &ctx, cudaStream_t s);
 void launch_fill(double *p, size_t n, double v, cudaStream_t s);
 void launch_cam_prep(const Ctx &ctx, int which, int force, cudaStream_t s);
 void launch_linearize_local(const Ctx &ctx, int force, cudaStream_t s);
-void launch_cam_norms(const Ctx &ctx, int force, cudaStream_t s);
+void launch_cam_norms(const Ctx &ctx, int force, int with_begin, cudaStream_t s);   // with_begin: + controller part 1 (the LM loop)
 void launch_compute_scale(const Ctx &ctx, cudaStream_t s);
-void launch_begin_iteration(const Ctx &ctx, cudaStream_t s);
 void launch_decide(const Ctx &ctx, int body, cudaStream_t s);           // accept / reject + the verdict as of the end of LM body `body` -> host ring
 void launch_point_invert(const Ctx &ctx, double radius_override, cudaStream_t s);
 void launch_point_invert_schur_build(const Ctx &ctx, cudaStream_t s);   // LM loop, dense Schur: point_invert + schur_init in one launch, then units + segments
