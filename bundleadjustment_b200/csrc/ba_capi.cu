@@ -270,6 +270,8 @@ int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
     return BA_OK;
 }
 
+// automatic Cholesky tile edge: dense systems of up to this many 64-row tile rows (3 072 rows, 480 cameras) keep 64-row tiles
+constexpr int CHOL_SMALL_TILE_ROWS = 48;
 // PCG only, once per problem: camera order inside every landmark block + the matvec's private copies of q
 int ensure_pcg(ba_handle *h) {
     Ctx &ctx = h->ctx;
@@ -344,6 +346,10 @@ int ensure_dense(ba_handle *h) {
             for (int gi = 0; gi < G; ++gi)
                 for (int gj = 0; gj <= gi; ++gj) nnz += (gi == gj || adj[(size_t)gi * G + gj]) ? 1 : 0;
             if (2 * nnz <= (long long)G * (G + 1) / 2 / 2) break;           // at most a quarter of the lower tiles are touched: sparse
+            // SMALL systems stay on 64-row tiles even when dense: up to a few thousand rows the factorisation is the chain
+            // potrf -> trsm -> update of the tile columns, not flops, and a 64-row link costs 17 us against 83 us for a 128-row
+            // one (keyframe-BA sizes: 30 cameras 67 us against 144 us, profiles/r02_chol_chain_small_systems.txt)
+            if (G <= CHOL_SMALL_TILE_ROWS) break;
             nb = 128;                                                        // (the same on every rank: adj is the union over ranks)
         }
         h->tile_nb = nb;
@@ -1152,7 +1158,7 @@ static int dense_spd_solve_impl(int device, int32_t n, const double *A, const do
         }
         long long nnz = 0;
         for (int i = 0; i < T; ++i) for (int j = 0; j <= i; ++j) nnz += (i == j || nz[(size_t)i * T + j]) ? 1 : 0;
-        if (nb == 128 || tile_edge || 2 * nnz <= (long long)T * (T + 1) / 2 / 2) break;
+        if (nb == 128 || tile_edge || 2 * nnz <= (long long)T * (T + 1) / 2 / 2 || T <= CHOL_SMALL_TILE_ROWS) break;
         nb = 128;
     }
     CholPlan plan;
