@@ -270,8 +270,10 @@ int upload(DevBuf &b, const T *src, size_t count, cudaStream_t s) {
     return BA_OK;
 }
 
-// automatic Cholesky tile edge: dense systems of up to this many 64-row tile rows (3 072 rows, 480 cameras) keep 64-row tiles
-constexpr int CHOL_SMALL_TILE_ROWS = 48;
+// automatic Cholesky tile edge: dense systems of up to this many 64-row tile rows (8 192 rows, 1 280 cameras) keep 64-row tiles
+// (measured on dense patterns, profiles/r02_chol_tile_crossover_dense.txt: n = 2 048: 0.67 ms against 1.37 ms on 128-row tiles,
+// 4 096: 1.71 / 2.83, 8 192: 8.05 / 8.51; beyond that the 128-row kernel's 68 % of the FP64 GEMM rate takes over)
+constexpr int CHOL_SMALL_TILE_ROWS = 128;
 // PCG only, once per problem: camera order inside every landmark block + the matvec's private copies of q
 int ensure_pcg(ba_handle *h) {
     Ctx &ctx = h->ctx;
@@ -346,7 +348,7 @@ int ensure_dense(ba_handle *h) {
             for (int gi = 0; gi < G; ++gi)
                 for (int gj = 0; gj <= gi; ++gj) nnz += (gi == gj || adj[(size_t)gi * G + gj]) ? 1 : 0;
             if (2 * nnz <= (long long)G * (G + 1) / 2 / 2) break;           // at most a quarter of the lower tiles are touched: sparse
-            // SMALL systems stay on 64-row tiles even when dense: up to a few thousand rows the factorisation is the chain
+            // SMALL and MEDIUM systems stay on 64-row tiles even when dense: up to several thousand rows the factorisation is the chain
             // potrf -> trsm -> update of the tile columns, not flops, and a 64-row link costs 17 us against 83 us for a 128-row
             // one (keyframe-BA sizes: 30 cameras 67 us against 144 us, profiles/r02_chol_chain_small_systems.txt)
             if (G <= CHOL_SMALL_TILE_ROWS) break;

@@ -254,7 +254,7 @@ int ba_get_reduced_system_stats(ba_handle *h, double out[4]);
  * environment variables.  Call before ba_set_problem. */
 int ba_set_reduced_system_mode(ba_handle *h, int32_t natural_order, int32_t dense_tiles);
 /* Tile edge of the reduced-system Cholesky: 0 = automatic (64-row tiles when co-visibility leaves at least three quarters of
- * the lower tiles of S empty, or when the system has at most 48 tile rows = 480 cameras -- the factorisation is then a
+ * the lower tiles of S empty, or when the system has at most 128 tile rows = 1 280 cameras -- the factorisation is then a
  * dependency chain of tile columns and shorter links win -- else 128-row tiles, which run large dense matrices closest to
  * the FP64 tensor peak), 64 or 128 = forced. */
 int ba_set_reduced_system_tile(ba_handle *h, int32_t tile_edge);
