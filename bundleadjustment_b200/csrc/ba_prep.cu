@@ -204,24 +204,24 @@ __global__ void pair_segments_kernel(long long P, int Nc, const int *__restrict_
     }
 }
 
-__global__ void pair_unit_count_kernel(int n_seg, long long P, const long long *__restrict__ seg_beg, int *__restrict__ unit_cnt) {
+__global__ void pair_unit_count_kernel(int n_seg, long long P, const long long *__restrict__ seg_beg, int *__restrict__ unit_cnt, int unit_len) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_seg) return;
     const long long e = (s + 1 < n_seg) ? seg_beg[s + 1] : P;
-    unit_cnt[s] = (int)((e - seg_beg[s] + PAIR_UNIT - 1) / PAIR_UNIT);
+    unit_cnt[s] = (int)((e - seg_beg[s] + unit_len - 1) / unit_len);
 }
 
 // unit record: first entry + (entry count << 1 | diagonal block), so that a unit starts with ONE round of loads
 __global__ void pair_unit_fill_kernel(int n_seg, long long P, const long long *__restrict__ seg_beg, const int2 *__restrict__ seg_cams,
-                                      const int *__restrict__ unit_ptr, int *__restrict__ unit_info, long long *__restrict__ unit_beg) {
+                                      const int *__restrict__ unit_ptr, int *__restrict__ unit_info, long long *__restrict__ unit_beg, int unit_len) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_seg) return;
     const long long e = (s + 1 < n_seg) ? seg_beg[s + 1] : P;
     const int2 c = seg_cams[s];
     const int diag = c.x == c.y;
     int u = unit_ptr[s];
-    for (long long b = seg_beg[s]; b < e; b += PAIR_UNIT, ++u) {
-        const long long cnt = (e - b < PAIR_UNIT) ? e - b : PAIR_UNIT;
+    for (long long b = seg_beg[s]; b < e; b += unit_len, ++u) {
+        const long long cnt = (e - b < unit_len) ? e - b : unit_len;
         unit_info[u] = ((int)cnt << 1) | diag;
         unit_beg[u] = b;
     }
@@ -391,7 +391,14 @@ int prep_pairs_build(const PrepIn &in, const PrepOut &out, PairIndex &pi, PrepSc
     // units
     int *unit_cnt = idx0;                                 // reuse (n_seg + 1 <= P + 1 ints; idx0 has room for P)
     PCU(cudaMemsetAsync(unit_cnt, 0, sizeof(int) * (size_t)(pi.n_seg + 1), s));
-    pair_unit_count_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, P, pi.seg_beg, unit_cnt);
+    // Unit length: a unit is one warp's serial walk over its entries in batches of 32, so a problem with FEW entries per SM
+    // (keyframe BA: 30 cameras, 200 k entries in 465 long segments) wants short units -- enough of them to fill the chip --
+    // and a large one (K4: 5 M entries) the full PAIR_UNIT.  Fixed per problem, so the sums stay reproducible.
+    {
+        const long long per = (P + PAIR_TARGET_UNITS - 1) / PAIR_TARGET_UNITS;
+        pi.unit_len = (int)std::min<long long>(PAIR_UNIT, std::max<long long>(32, (per + 31) / 32 * 32));
+    }
+    pair_unit_count_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, P, pi.seg_beg, unit_cnt, pi.unit_len);
     size_t sb2 = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, sb2, (int *)nullptr, (int *)nullptr, pi.n_seg + 1, s);
     if (sb2 > cub_bytes) return (int)cudaErrorInvalidValue;
@@ -462,7 +469,7 @@ int prep_block_order(const PrepOut &out, int Nc, unsigned *blk_ord, cudaStream_t
 
 int prep_pairs_units(PairIndex &pi, cudaStream_t s) {
     if (pi.n_seg > 0)
-        pair_unit_fill_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.P, pi.seg_beg, pi.seg_cams, pi.unit_ptr, pi.unit_seg, pi.unit_beg);
+        pair_unit_fill_kernel<<<cdivp(pi.n_seg, 256), 256, 0, s>>>(pi.n_seg, pi.P, pi.seg_beg, pi.seg_cams, pi.unit_ptr, pi.unit_seg, pi.unit_beg, pi.unit_len);
     return (int)cudaGetLastError();
 }
 

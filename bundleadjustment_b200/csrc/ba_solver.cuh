@@ -59,11 +59,13 @@ struct LMState {
 
 // Camera-pair-major view of the observations (dense Schur): entry k = (observation a, observation b) of ONE landmark with
 // camera(a) >= camera(b), entries sorted by (camera a, camera b); a segment = all entries of one S block, cut into
-// units of <= PAIR_UNIT entries (one warp each).
+// units of <= unit_len <= PAIR_UNIT entries (one warp each).
 constexpr int PAIR_UNIT = 256;
+constexpr int PAIR_TARGET_UNITS = 8192;   // units wanted at least (about 3.5 warps per SM sub-partition) before a unit grows beyond 32 entries
 struct PairIndex {
     long long P;             // entries
     int n_seg, n_units;
+    int unit_len;            // entries per unit of THIS problem: 32 .. PAIR_UNIT (ba_prep.cu: prep_pairs_build)
     size_t seg_cap;          // capacity of the seg_* arrays
     int2 *pair_obs;          // [P]
     long long *seg_beg;      // [n_seg]
